@@ -1,0 +1,554 @@
+// TEST INFRASTRUCTURE — not part of the product.
+//
+// Headless driver that links the UNMODIFIED reference classes (RN::SceneNode, RN::Camera, RN::SceneBasic,
+// RN::GenericParticleEmitter) built by oracle/build_ref.sh from /root/reference and runs them on a scene /
+// emitter description read from a file.  Its outputs are (1) the parity goldens the C restatement
+// (oracle/rn_oracle.c) and the CUDA path are checked against and (2) the timed CPU baseline ("reference" kind).
+//
+//   ref_harness scene     <in.bin> <out.bin>      run frames, dump render order / world TRS / matrices / lists
+//   ref_harness particles <in.bin> <out.bin>      run K emitter steps, dump every live particle
+//   ref_harness bench-scene     <in.bin> <frames> <warmup>   print JSON timing line (ms per frame)
+//   ref_harness bench-particles <in.bin> <steps>  <warmup>   print JSON timing line
+//
+// File formats are documented in oracle/refio.py (the only reader/writer on the Python side).
+//
+// Build notes (see build_ref.sh): compiled with -fno-access-control so that protected Scene::Update/Render,
+// private WorkQueue::InitializeQueues and ParticleEmitter::_particles are reachable; Base/RNBase.cpp is
+// #included so the file-static RN::__functionPool can be created (reference: Source/Base/RNBase.cpp:164,174).
+
+#include "Rayne.h"
+#include "Base/RNBase.cpp"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstdint>
+#include <vector>
+#include <chrono>
+#include <algorithm>
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+
+using namespace RN;
+
+// ---------------------------------------------------------------------------------------------------------
+// Null renderer: the reference constructors want an active renderer (ParticleEmitter fetches shaders and a
+// drawable, Source/Scene/RNParticleEmitter.cpp:38-54; Mesh wants buffers).  No graphics API is involved.
+// ---------------------------------------------------------------------------------------------------------
+namespace
+{
+	class NullBuffer : public GPUBuffer
+	{
+	public:
+		NullBuffer(size_t length) : _length(length) { _data = calloc(1, length ? length : 1); }
+		~NullBuffer() { free(_data); }
+		void *GetBuffer() override { return _data; }
+		void UnmapBuffer() override {}
+		void InvalidateRange(const Range &) override {}
+		void FlushRange(const Range &) override {}
+		size_t GetLength() const override { return _length; }
+	private:
+		void *_data;
+		size_t _length;
+	};
+
+	class NullShader : public Shader
+	{
+	public:
+		NullShader(ShaderLibrary *lib, Type type, const Shader::Options *options) : Shader(lib, type, false, options) {}
+		const String *GetName() const override { return RNCSTR("null"); }
+	};
+
+	class NullShaderLibrary : public ShaderLibrary
+	{
+	public:
+		Shader *GetShaderWithName(const String *, const Shader::Options *options) override
+		{
+			const Shader::Options *opts = options ? options : Shader::Options::WithNone();
+			return (new NullShader(this, Shader::Type::Vertex, opts))->Autorelease();
+		}
+		Shader *GetInstancedShaderForShader(Shader *shader) override { return shader; }
+	};
+
+	class NullRenderer : public Renderer
+	{
+	public:
+		NullRenderer() : Renderer(reinterpret_cast<RendererDescriptor *>(16), reinterpret_cast<RenderingDevice *>(16))
+		{
+			_library = new NullShaderLibrary();
+		}
+		Window *CreateAWindow(const Vector2 &, Screen *, const Window::SwapChainDescriptor &) override { return nullptr; }
+		Window *GetMainWindow() override { return nullptr; }
+		void SetMainWindow(Window *) override {}
+		void Render(Function &&function) override { function(); }
+		void SubmitCamera(Camera *camera, Function &&function) override { current = camera; function(); current = nullptr; }
+		bool SupportsTextureFormat(const String *) const override { return false; }
+		bool SupportsDrawMode(DrawMode) const override { return true; }
+		size_t GetAlignmentForType(PrimitiveType type) const override { return GetSizeForType(type); }
+		size_t GetSizeForType(PrimitiveType type) const override
+		{
+			switch(type)
+			{
+				case PrimitiveType::Uint8: case PrimitiveType::Int8: return 1;
+				case PrimitiveType::Uint16: case PrimitiveType::Int16: case PrimitiveType::Half: return 2;
+				case PrimitiveType::Uint32: case PrimitiveType::Int32: case PrimitiveType::Float: return 4;
+				case PrimitiveType::Vector2: return 8;
+				case PrimitiveType::Vector3: return 12;
+				case PrimitiveType::Vector4: case PrimitiveType::Color: case PrimitiveType::Quaternion: return 16;
+				case PrimitiveType::Matrix4x4: return 64;
+				default: return 16;
+			}
+		}
+		GPUBuffer *CreateBufferWithLength(size_t length, GPUResource::UsageOptions, GPUResource::AccessOptions, bool) override
+		{
+			return new NullBuffer(length);
+		}
+		ShaderLibrary *CreateShaderLibraryWithFile(const String *) override { return _library; }
+		ShaderLibrary *CreateShaderLibraryWithSource(const String *) override { return _library; }
+		Shader *GetDefaultShader(Shader::Type type, Shader::Options *options, Shader::UsageHint) override
+		{
+			const Shader::Options *opts = options ? options : Shader::Options::WithNone();
+			return (new NullShader(_library, type, opts))->Autorelease();
+		}
+		ShaderLibrary *GetDefaultShaderLibrary() override { return _library; }
+		Texture *CreateTextureWithDescriptor(const Texture::Descriptor &) override { return nullptr; }
+		Framebuffer *CreateFramebuffer(const Vector2 &) override { return nullptr; }
+		Drawable *CreateDrawable() override { return new Drawable(); }
+		void DeleteDrawable(Drawable *drawable) override { delete drawable; }
+		void SubmitDrawable(Drawable *) override {}
+		void SubmitLight(const Light *) override {}
+
+		Camera *current = nullptr;
+	private:
+		NullShaderLibrary *_library;
+	};
+
+	// A plain cull-only node: the base SceneNode::CanRender returns false (Source/Scene/RNSceneNode.cpp:419-422)
+	// and Entity needs a Model, so this does what Entity::CanRender does minus the model check
+	// (Source/Scene/RNEntity.cpp:154-159 -> SceneNode::CanRenderUtil).
+	struct Recorder
+	{
+		std::vector<std::vector<uint32_t>> lists; // per camera (harness camera index)
+		std::vector<Camera *> cameras;
+		bool touchMatrices = false;
+		float sink = 0.0f;
+	};
+	static Recorder *g_recorder = nullptr;
+
+	class CullNode : public SceneNode
+	{
+	public:
+		uint32_t id = 0;
+		bool CanRender(Renderer *renderer, Camera *camera) const override { return CanRenderUtil(renderer, camera); }
+		void Render(Renderer *renderer, Camera *camera) const override
+		{
+			SceneNode::Render(renderer, camera);
+			if(g_recorder)
+			{
+				for(size_t i = 0; i < g_recorder->cameras.size(); i++)
+				{
+					if(g_recorder->cameras[i] == camera)
+					{
+						g_recorder->lists[i].push_back(id);
+						break;
+					}
+				}
+				if(g_recorder->touchMatrices)
+				{
+					// what Drawable::Update does for a visible node (Source/Rendering/RNRenderer.h:65-76)
+					Matrix m = GetWorldTransform();
+					g_recorder->sink += m.m[12];
+				}
+			}
+		}
+	};
+
+	class HarnessScene : public SceneBasic
+	{
+	public:
+		HarnessScene() {}
+	};
+
+	// ---- tiny binary IO ----------------------------------------------------------------------------------
+	struct Reader
+	{
+		FILE *f;
+		explicit Reader(const char *path) { f = fopen(path, "rb"); if(!f) { perror(path); exit(2); } }
+		~Reader() { fclose(f); }
+		template<class T> T get() { T v; if(fread(&v, sizeof(T), 1, f) != 1) { fprintf(stderr, "short read\n"); exit(2); } return v; }
+		template<class T> std::vector<T> vec(size_t n) { std::vector<T> v(n); if(n && fread(v.data(), sizeof(T), n, f) != n) { fprintf(stderr, "short read\n"); exit(2); } return v; }
+	};
+	struct Writer
+	{
+		FILE *f;
+		explicit Writer(const char *path) { f = fopen(path, "wb"); if(!f) { perror(path); exit(2); } }
+		~Writer() { fclose(f); }
+		template<class T> void put(const T &v) { fwrite(&v, sizeof(T), 1, f); }
+		template<class T> void vec(const std::vector<T> &v) { if(!v.empty()) fwrite(v.data(), sizeof(T), v.size(), f); }
+	};
+
+	struct CameraDesc
+	{
+		uint32_t flags;       // Camera::Flags bits to OR into Defaults (Orthogonal, UseSimpleCulling, ...)
+		uint32_t renderGroup;
+		float pos[3], rot[4], scale[3];
+		float fov, aspect, clipNear, clipFar;
+		float ortho[4];       // left, right, bottom, top
+		float planeOffsets[4];// top, bottom, left, right (Camera::SetFrustumPlaneOffset order)
+		uint32_t hasProjection;
+		float projection[16];
+	};
+
+	struct SceneInput
+	{
+		uint32_t nNodes, nCameras, nFrames, options;
+		float rootTranslate[3];
+		std::vector<int32_t> parent;
+		std::vector<float> pos, scale, rot;
+		std::vector<uint32_t> flags, group;
+		std::vector<int32_t> priority;
+		std::vector<float> sphere;
+		std::vector<CameraDesc> cameras;
+	};
+
+	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1 };
+
+	SceneInput ReadScene(const char *path)
+	{
+		Reader r(path);
+		SceneInput in;
+		uint32_t magic = r.get<uint32_t>();
+		uint32_t version = r.get<uint32_t>();
+		if(magic != 0x49534e52u || version != 1) { fprintf(stderr, "bad scene file\n"); exit(2); }
+		in.nNodes = r.get<uint32_t>(); in.nCameras = r.get<uint32_t>(); in.nFrames = r.get<uint32_t>(); in.options = r.get<uint32_t>();
+		for(int i = 0; i < 3; i++) in.rootTranslate[i] = r.get<float>();
+		size_t n = in.nNodes;
+		in.parent = r.vec<int32_t>(n);
+		in.pos = r.vec<float>(n * 3); in.scale = r.vec<float>(n * 3); in.rot = r.vec<float>(n * 4);
+		in.flags = r.vec<uint32_t>(n); in.group = r.vec<uint32_t>(n); in.priority = r.vec<int32_t>(n);
+		in.sphere = r.vec<float>(n * 4);
+		in.cameras = r.vec<CameraDesc>(in.nCameras);
+		return in;
+	}
+
+	struct BuiltScene
+	{
+		HarnessScene *scene;
+		std::vector<CullNode *> nodes;
+		std::vector<CullNode *> roots;
+		std::vector<Camera *> cameras;
+	};
+
+	BuiltScene BuildScene(const SceneInput &in)
+	{
+		BuiltScene b;
+		b.scene = new HarnessScene();
+		b.nodes.resize(in.nNodes);
+		for(uint32_t i = 0; i < in.nNodes; i++)
+		{
+			CullNode *node = new CullNode();
+			node->id = i;
+			node->SetPosition(Vector3(in.pos[i*3], in.pos[i*3+1], in.pos[i*3+2]));
+			node->SetScale(Vector3(in.scale[i*3], in.scale[i*3+1], in.scale[i*3+2]));
+			node->SetRotation(Quaternion(in.rot[i*4], in.rot[i*4+1], in.rot[i*4+2], in.rot[i*4+3]));
+			node->SetFlags(in.flags[i]);
+			node->SetRenderGroup(static_cast<uint8>(in.group[i]));
+			if(in.priority[i] != SceneNode::RenderNormal) node->SetRenderPriority(in.priority[i]);
+			Sphere s(Vector3(in.sphere[i*4], in.sphere[i*4+1], in.sphere[i*4+2]), in.sphere[i*4+3]);
+			node->SetBoundingSphere(s);
+			b.nodes[i] = node;
+		}
+		// the trees are completed BEFORE their roots enter the scene (keeps every tree contiguous in the render list)
+		for(uint32_t i = 0; i < in.nNodes; i++)
+		{
+			if(in.parent[i] >= 0) b.nodes[in.parent[i]]->AddChild(b.nodes[i]);
+			else b.roots.push_back(b.nodes[i]);
+		}
+		for(CullNode *root : b.roots) b.scene->AddNode(root);
+
+		for(uint32_t c = 0; c < in.nCameras; c++)
+		{
+			const CameraDesc &d = in.cameras[c];
+			Camera *camera = new Camera();
+			camera->SetFlags(camera->GetFlags() | d.flags);
+			camera->SetRenderGroup(static_cast<uint8>(d.renderGroup));
+			camera->SetPosition(Vector3(d.pos[0], d.pos[1], d.pos[2]));
+			camera->SetRotation(Quaternion(d.rot[0], d.rot[1], d.rot[2], d.rot[3]));
+			camera->SetScale(Vector3(d.scale[0], d.scale[1], d.scale[2]));
+			camera->SetFOV(d.fov);
+			camera->SetAspectRatio(d.aspect);
+			camera->SetClipNear(d.clipNear);
+			camera->SetClipFar(d.clipFar);
+			if(d.flags & Camera::Flags::Orthogonal)
+				camera->SetOrthogonalFrustum(d.ortho[3], d.ortho[2], d.ortho[0], d.ortho[1]);
+			camera->SetFrustumPlaneOffset(d.planeOffsets[0], d.planeOffsets[1], d.planeOffsets[2], d.planeOffsets[3]);
+			if(d.hasProjection)
+			{
+				Matrix m;
+				for(int i = 0; i < 16; i++) m.m[i] = d.projection[i];
+				camera->SetProjectionMatrix(m);
+			}
+			b.scene->AddNode(camera);
+			b.cameras.push_back(camera);
+		}
+		return b;
+	}
+
+	void RunFrame(const SceneInput &in, BuiltScene &b, Renderer *renderer, bool translate)
+	{
+		if(translate)
+		{
+			Vector3 t(in.rootTranslate[0], in.rootTranslate[1], in.rootTranslate[2]);
+			for(CullNode *root : b.roots) root->Translate(t);
+		}
+		b.scene->Update(1.0f / 60.0f);
+		b.scene->Render(renderer);
+	}
+
+	int CmdScene(const char *inPath, const char *outPath, Renderer *renderer)
+	{
+		SceneInput in = ReadScene(inPath);
+		BuiltScene b = BuildScene(in);
+		Recorder rec;
+		rec.cameras = b.cameras;
+		rec.lists.resize(b.cameras.size());
+		rec.touchMatrices = (in.options & kOptTouchMatrices) != 0;
+		g_recorder = &rec;
+		uint32_t frames = in.nFrames ? in.nFrames : 1;
+		for(uint32_t f = 0; f < frames; f++)
+		{
+			for(auto &l : rec.lists) l.clear();
+			RunFrame(in, b, renderer, f > 0);
+		}
+		g_recorder = nullptr;
+
+		Writer w(outPath);
+		w.put<uint32_t>(0x4f534e52u); w.put<uint32_t>(1);
+		w.put<uint32_t>(in.nNodes); w.put<uint32_t>(in.nCameras);
+		// render-list order (SceneBasic::_renderNodes, head to tail) as creation ids
+		std::vector<uint32_t> order;
+		for(IntrusiveList<SceneNode>::Member *m = b.scene->_renderNodes.GetHead(); m; m = m->GetNext())
+			order.push_back(static_cast<CullNode *>(m->Get())->id);
+		w.put<uint32_t>(static_cast<uint32_t>(order.size()));
+		w.vec(order);
+		std::vector<float> wpos(in.nNodes * 3), wrot(in.nNodes * 4), wscale(in.nNodes * 3), wmat((size_t)in.nNodes * 16), sph((size_t)in.nNodes * 4);
+		std::vector<float> winv;
+		if(in.options & kOptInverse) winv.resize((size_t)in.nNodes * 16);
+		for(uint32_t i = 0; i < in.nNodes; i++)
+		{
+			CullNode *node = b.nodes[i];
+			Vector3 p = node->GetWorldPosition(); Quaternion q = node->GetWorldRotation(); Vector3 s = node->GetWorldScale();
+			wpos[i*3] = p.x; wpos[i*3+1] = p.y; wpos[i*3+2] = p.z;
+			wrot[i*4] = q.x; wrot[i*4+1] = q.y; wrot[i*4+2] = q.z; wrot[i*4+3] = q.w;
+			wscale[i*3] = s.x; wscale[i*3+1] = s.y; wscale[i*3+2] = s.z;
+			Matrix m = node->GetWorldTransform();
+			for(int k = 0; k < 16; k++) wmat[(size_t)i*16 + k] = m.m[k];
+			if(in.options & kOptInverse)
+			{
+				Matrix inv = node->GetInverseWorldTransform();
+				for(int k = 0; k < 16; k++) winv[(size_t)i*16 + k] = inv.m[k];
+			}
+			Sphere bs = node->GetBoundingSphere();
+			Vector3 c = bs.position + bs.offset;
+			sph[i*4] = c.x; sph[i*4+1] = c.y; sph[i*4+2] = c.z; sph[i*4+3] = bs.radius;
+		}
+		w.vec(wpos); w.vec(wrot); w.vec(wscale); w.vec(wmat); w.vec(sph);
+		w.put<uint32_t>((in.options & kOptInverse) ? 1 : 0);
+		w.vec(winv);
+		for(size_t c = 0; c < b.cameras.size(); c++)
+		{
+			Camera *cam = b.cameras[c];
+			float fr[28];
+			fr[0] = cam->_frustumCenter.x; fr[1] = cam->_frustumCenter.y; fr[2] = cam->_frustumCenter.z; fr[3] = cam->_frustumRadius;
+			const Plane *planes[6] = { &cam->frustums._frustumLeft, &cam->frustums._frustumRight, &cam->frustums._frustumTop,
+			                           &cam->frustums._frustumBottom, &cam->frustums._frustumNear, &cam->frustums._frustumFar };
+			for(int k = 0; k < 6; k++)
+			{
+				fr[4 + k*4 + 0] = planes[k]->_normal.x; fr[4 + k*4 + 1] = planes[k]->_normal.y;
+				fr[4 + k*4 + 2] = planes[k]->_normal.z; fr[4 + k*4 + 3] = planes[k]->_d;
+			}
+			for(int k = 0; k < 28; k++) w.put<float>(fr[k]);
+			w.put<uint32_t>(static_cast<uint32_t>(cam->GetFlags()));
+			w.put<uint32_t>(static_cast<uint32_t>(cam->GetRenderGroup()));
+			w.put<uint32_t>(static_cast<uint32_t>(rec.lists[c].size()));
+			w.vec(rec.lists[c]);
+		}
+		return 0;
+	}
+
+	int CmdBenchScene(const char *inPath, int frames, int warmup, Renderer *renderer)
+	{
+		SceneInput in = ReadScene(inPath);
+		BuiltScene b = BuildScene(in);
+		Recorder rec;
+		rec.cameras = b.cameras;
+		rec.lists.resize(b.cameras.size());
+		rec.touchMatrices = true;
+		g_recorder = &rec;
+		for(int f = 0; f < warmup; f++) { for(auto &l : rec.lists) l.clear(); RunFrame(in, b, renderer, true); }
+		double best = 1e30, total = 0.0;
+		size_t visible = 0;
+		for(int f = 0; f < frames; f++)
+		{
+			for(auto &l : rec.lists) l.clear();
+			auto t0 = std::chrono::steady_clock::now();
+			RunFrame(in, b, renderer, true);
+			auto t1 = std::chrono::steady_clock::now();
+			double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+			best = std::min(best, ms); total += ms;
+			visible = 0; for(auto &l : rec.lists) visible += l.size();
+		}
+		g_recorder = nullptr;
+		printf("{\"kind\": \"reference\", \"what\": \"scene\", \"nodes\": %u, \"cameras\": %u, \"frames\": %d, \"ms_best\": %.6f, \"ms_mean\": %.6f, \"visible\": %zu, \"sink\": %g}\n",
+		       in.nNodes, in.nCameras, frames, best, total / frames, visible, (double)rec.sink);
+		return 0;
+	}
+
+	// ---- particles -----------------------------------------------------------------------------------------
+	struct EmitterDesc
+	{
+		uint32_t seed, maxParticles;
+		float spawnRate;
+		float lifeSpan[2];
+		float startColor[4], endColor[4];
+		float startSize[2], endSize[2], startRotation[2], endRotation[2];
+		float gravity[3], velocity[3], velMin[3], velMax[3], posMin[3], posMax[3];
+	};
+
+	struct ParticleInput
+	{
+		uint32_t nEmitters, nSteps;
+		float delta;
+		std::vector<EmitterDesc> emitters;
+	};
+
+	ParticleInput ReadParticles(const char *path)
+	{
+		Reader r(path);
+		ParticleInput in;
+		uint32_t magic = r.get<uint32_t>(); uint32_t version = r.get<uint32_t>();
+		if(magic != 0x49504e52u || version != 1) { fprintf(stderr, "bad particle file\n"); exit(2); }
+		in.nEmitters = r.get<uint32_t>(); in.nSteps = r.get<uint32_t>(); in.delta = r.get<float>();
+		in.emitters = r.vec<EmitterDesc>(in.nEmitters);
+		return in;
+	}
+
+	std::vector<GenericParticleEmitter *> BuildEmitters(const ParticleInput &in, HarnessScene *scene)
+	{
+		std::vector<GenericParticleEmitter *> out;
+		for(const EmitterDesc &d : in.emitters)
+		{
+			GenericParticleEmitter *e = new GenericParticleEmitter();
+			e->GetGenerator()->Seed(d.seed);
+			e->SetMaxParticles(d.maxParticles);
+			e->SetSpawnRate(d.spawnRate);
+			e->SetLifeSpan(Vector2(d.lifeSpan[0], d.lifeSpan[1]));
+			e->SetStartColor(Color(d.startColor[0], d.startColor[1], d.startColor[2], d.startColor[3]));
+			e->SetEndColor(Color(d.endColor[0], d.endColor[1], d.endColor[2], d.endColor[3]));
+			e->SetStartSize(Vector2(d.startSize[0], d.startSize[1]));
+			e->SetEndSize(Vector2(d.endSize[0], d.endSize[1]));
+			e->SetStartRotation(Vector2(d.startRotation[0], d.startRotation[1]));
+			e->SetEndRotation(Vector2(d.endRotation[0], d.endRotation[1]));
+			e->SetGravity(Vector3(d.gravity[0], d.gravity[1], d.gravity[2]));
+			e->SetVelocity(Vector3(d.velocity[0], d.velocity[1], d.velocity[2]));
+			e->SetVelocityRandomizeMin(Vector3(d.velMin[0], d.velMin[1], d.velMin[2]));
+			e->SetVelocityRandomizeMax(Vector3(d.velMax[0], d.velMax[1], d.velMax[2]));
+			e->SetPositionRandomizeMin(Vector3(d.posMin[0], d.posMin[1], d.posMin[2]));
+			e->SetPositionRandomizeMax(Vector3(d.posMax[0], d.posMax[1], d.posMax[2]));
+			scene->AddNode(e);
+			out.push_back(e);
+		}
+		return out;
+	}
+
+	int CmdParticles(const char *inPath, const char *outPath)
+	{
+		ParticleInput in = ReadParticles(inPath);
+		HarnessScene *scene = new HarnessScene();
+		std::vector<GenericParticleEmitter *> emitters = BuildEmitters(in, scene);
+		for(uint32_t s = 0; s < in.nSteps; s++) scene->Update(in.delta);
+
+		Writer w(outPath);
+		w.put<uint32_t>(0x4f504e52u); w.put<uint32_t>(1); w.put<uint32_t>(in.nEmitters);
+		for(GenericParticleEmitter *e : emitters)
+		{
+			uint32_t count = static_cast<uint32_t>(e->_particles.size());
+			w.put<uint32_t>(count);
+			w.put<float>(e->_time);
+			// per particle 24 floats: position3 velocity3 time lifespan duration sizeStart sizeEnd rotStart rotEnd | rotation size2 color4 | gravity3
+			std::vector<float> rec((size_t)count * 24);
+			for(uint32_t i = 0; i < count; i++)
+			{
+				GenericParticle *p = static_cast<GenericParticle *>(e->_particles[i]);
+				float *o = &rec[(size_t)i * 24];
+				o[0] = p->position.x; o[1] = p->position.y; o[2] = p->position.z;
+				o[3] = p->velocity.x; o[4] = p->velocity.y; o[5] = p->velocity.z;
+				o[6] = p->time; o[7] = p->lifespan; o[8] = p->sizeInterpolator._duration;
+				o[9] = p->sizeInterpolator._startValue.x; o[10] = p->sizeInterpolator._endValue.x;
+				o[11] = p->rotationInterpolator._startValue; o[12] = p->rotationInterpolator._endValue;
+				o[13] = p->rotation; o[14] = p->size.x; o[15] = p->size.y;
+				o[16] = p->color.r; o[17] = p->color.g; o[18] = p->color.b; o[19] = p->color.a;
+				o[20] = p->gravity.x; o[21] = p->gravity.y; o[22] = p->gravity.z; o[23] = 0.0f;
+			}
+			w.vec(rec);
+		}
+		return 0;
+	}
+
+	int CmdBenchParticles(const char *inPath, int steps, int warmup)
+	{
+		ParticleInput in = ReadParticles(inPath);
+		HarnessScene *scene = new HarnessScene();
+		std::vector<GenericParticleEmitter *> emitters = BuildEmitters(in, scene);
+		for(int s = 0; s < warmup; s++) scene->Update(in.delta);
+		double best = 1e30, total = 0.0;
+		for(int s = 0; s < steps; s++)
+		{
+			auto t0 = std::chrono::steady_clock::now();
+			scene->Update(in.delta);
+			auto t1 = std::chrono::steady_clock::now();
+			double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+			best = std::min(best, ms); total += ms;
+		}
+		size_t live = 0;
+		for(GenericParticleEmitter *e : emitters) live += e->_particles.size();
+		printf("{\"kind\": \"reference\", \"what\": \"particles\", \"emitters\": %u, \"live\": %zu, \"steps\": %d, \"ms_best\": %.6f, \"ms_mean\": %.6f}\n",
+		       in.nEmitters, live, steps, best, total / steps);
+		return 0;
+	}
+}
+
+static void OnSegv(int)
+{
+	void *frames[48];
+	int n = backtrace(frames, 48);
+	backtrace_symbols_fd(frames, n, 2);
+	_Exit(139);
+}
+
+int main(int argc, char **argv)
+{
+	signal(SIGSEGV, OnSegv);
+	if(argc < 3)
+	{
+		fprintf(stderr, "usage: %s scene|particles|bench-scene|bench-particles <in> ...\n", argv[0]);
+		return 2;
+	}
+	// Minimal bootstrap: no Kernel, no manifest, no files (reference: RNBase.cpp:164-176, RNWorkQueue.cpp:65-71).
+	RN::__functionPool = new MemoryPool();
+	AutoreleasePool *pool = new AutoreleasePool(); // before anything that autoreleases (RNCSTR in InitializeQueues)
+	WorkQueue::InitializeQueues();
+	NullRenderer *renderer = new NullRenderer();
+	renderer->Activate();
+
+	std::string cmd = argv[1];
+	int rc = 2;
+	if(cmd == "scene" && argc >= 4) rc = CmdScene(argv[2], argv[3], renderer);
+	else if(cmd == "particles" && argc >= 4) rc = CmdParticles(argv[2], argv[3]);
+	else if(cmd == "bench-scene" && argc >= 5) rc = CmdBenchScene(argv[2], atoi(argv[3]), atoi(argv[4]), renderer);
+	else if(cmd == "bench-particles" && argc >= 5) rc = CmdBenchParticles(argv[2], atoi(argv[3]), atoi(argv[4]));
+	else fprintf(stderr, "bad arguments\n");
+	fflush(stdout);
+	(void)pool;
+	_Exit(rc); // skip static destructors of the half-booted engine
+}

@@ -1,0 +1,158 @@
+"""TEST INFRASTRUCTURE - file IO for oracle/_ref/ref_harness_* (the reference itself, compiled by build_ref.sh).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+
+Scene input  ("RNSI" v1): header u32 magic, version, n_nodes, n_cameras, n_frames, options; f32 root_translate[3];
+    i32 parent[n]; f32 pos[n,3]; f32 scale[n,3]; f32 rot[n,4]; u32 flags[n]; u32 group[n]; i32 priority[n];
+    f32 sphere[n,4]; CAMERA_DTYPE cameras[n_cameras]           (all creation order, little endian)
+Scene output ("RNSO" v1): u32 magic, version, n_nodes, n_cameras; u32 n_order; u32 order[n_order] (render list,
+    head->tail, creation ids); f32 wpos[n,3]; wrot[n,4]; wscale[n,3]; wmat[n,16]; sphere[n,4] (centre, radius);
+    u32 has_inv; f32 winv[n,16] if has_inv; per camera: f32 frustum[28] (centre3, radius, 6x(normal3, d) in the
+    order left,right,top,bottom,near,far), u32 flags, u32 group, u32 count, u32 list[count] (creation ids)
+Particle input ("RNPI" v1): u32 magic, version, n_emitters, n_steps; f32 delta; EMITTER_DTYPE emitters[n]
+Particle output ("RNPO" v1): u32 magic, version, n_emitters; per emitter u32 count, f32 time, f32 rec[count,24]
+"""
+from __future__ import annotations
+
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+from rayne_b200.scenegen import CAMERA_DTYPE, EMITTER_DTYPE, Scene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+
+OPT_INVERSE = 1
+OPT_TOUCH_MATRICES = 2
+
+# columns of the 24-float particle record written by the harness
+P_POS, P_VEL, P_TIME, P_LIFE, P_DUR = slice(0, 3), slice(3, 6), 6, 7, 8
+P_SIZE0, P_SIZE1, P_ROT0, P_ROT1, P_ROT = 9, 10, 11, 12, 13
+P_SIZE, P_COLOR, P_GRAVITY = slice(14, 16), slice(16, 20), slice(20, 23)
+
+
+def harness_path(kind: str = "strict") -> str:
+    return os.path.join(REF_DIR, f"ref_harness_{kind}")
+
+
+def have_harness(kind: str = "strict") -> bool:
+    return os.access(harness_path(kind), os.X_OK)
+
+
+def write_scene_input(path: str, scene: Scene, cameras: np.ndarray, frames: int = 1, options: int = 0,
+                      root_translate=(0.0, 0.0, 0.0)) -> None:
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    with open(path, "wb") as f:
+        f.write(np.array([0x49534E52, 1, scene.n, cameras.shape[0], frames, options], dtype="<u4").tobytes())
+        f.write(np.asarray(root_translate, dtype="<f4").tobytes())
+        f.write(np.ascontiguousarray(scene.parent, dtype="<i4").tobytes())
+        f.write(np.ascontiguousarray(scene.pos, dtype="<f4").tobytes())
+        f.write(np.ascontiguousarray(scene.scale, dtype="<f4").tobytes())
+        f.write(np.ascontiguousarray(scene.rot, dtype="<f4").tobytes())
+        f.write(np.ascontiguousarray(scene.flags, dtype="<u4").tobytes())
+        f.write(np.ascontiguousarray(scene.group, dtype="<u4").tobytes())
+        f.write(np.ascontiguousarray(scene.priority, dtype="<i4").tobytes())
+        f.write(np.ascontiguousarray(scene.sphere, dtype="<f4").tobytes())
+        f.write(cameras.tobytes())
+
+
+def read_scene_output(path: str) -> dict:
+    buf = np.fromfile(path, dtype=np.uint8)
+    off = 0
+
+    def take(dtype, count):
+        nonlocal off
+        dt = np.dtype(dtype)
+        a = np.frombuffer(buf, dtype=dt, count=count, offset=off)
+        off += dt.itemsize * count
+        return a
+
+    magic, version, n, ncam = take("<u4", 4)
+    assert magic == 0x4F534E52 and version == 1
+    n = int(n); ncam = int(ncam)
+    norder = int(take("<u4", 1)[0])
+    out = {"order": take("<u4", norder).copy()}
+    out["wpos"] = take("<f4", n * 3).reshape(n, 3).copy()
+    out["wrot"] = take("<f4", n * 4).reshape(n, 4).copy()
+    out["wscale"] = take("<f4", n * 3).reshape(n, 3).copy()
+    out["wmat"] = take("<f4", n * 16).reshape(n, 16).copy()
+    out["sphere"] = take("<f4", n * 4).reshape(n, 4).copy()
+    has_inv = int(take("<u4", 1)[0])
+    out["winv"] = take("<f4", n * 16).reshape(n, 16).copy() if has_inv else None
+    out["frustum"] = np.zeros((ncam, 28), dtype=np.float32)
+    out["cam_flags"] = np.zeros(ncam, dtype=np.uint32)
+    out["cam_group"] = np.zeros(ncam, dtype=np.uint32)
+    out["lists"] = []
+    for c in range(ncam):
+        out["frustum"][c] = take("<f4", 28)
+        out["cam_flags"][c], out["cam_group"][c], cnt = take("<u4", 3)
+        out["lists"].append(take("<u4", int(cnt)).copy())
+    assert off == buf.shape[0], (off, buf.shape[0])
+    return out
+
+
+def run_scene(scene: Scene, cameras: np.ndarray, frames: int = 1, options: int = 0,
+              root_translate=(0.0, 0.0, 0.0), kind: str = "strict") -> dict:
+    """Run the real reference (SceneBasic::Update + Render) on the scene; returns the parsed dump."""
+    with tempfile.TemporaryDirectory() as tmp:
+        fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
+        write_scene_input(fin, scene, cameras, frames, options, root_translate)
+        subprocess.run([harness_path(kind), "scene", fin, fout], check=True, stdout=subprocess.DEVNULL)
+        return read_scene_output(fout)
+
+
+def bench_scene(scene: Scene, cameras: np.ndarray, frames: int, warmup: int,
+                root_translate=(0.01, 0.0, 0.0), kind: str = "release") -> dict:
+    with tempfile.TemporaryDirectory() as tmp:
+        fin = os.path.join(tmp, "in.bin")
+        write_scene_input(fin, scene, cameras, 1, OPT_TOUCH_MATRICES, root_translate)
+        r = subprocess.run([harness_path(kind), "bench-scene", fin, str(frames), str(warmup)], check=True,
+                           capture_output=True, text=True)
+        return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float) -> None:
+    emitters = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+    with open(path, "wb") as f:
+        f.write(np.array([0x49504E52, 1, emitters.shape[0], steps], dtype="<u4").tobytes())
+        f.write(np.array([delta], dtype="<f4").tobytes())
+        f.write(emitters.tobytes())
+
+
+def read_particle_output(path: str) -> list[dict]:
+    buf = np.fromfile(path, dtype=np.uint8)
+    magic, version, ne = np.frombuffer(buf, dtype="<u4", count=3)
+    assert magic == 0x4F504E52 and version == 1
+    off = 12
+    out = []
+    for _ in range(int(ne)):
+        cnt = int(np.frombuffer(buf, dtype="<u4", count=1, offset=off)[0])
+        time = float(np.frombuffer(buf, dtype="<f4", count=1, offset=off + 4)[0])
+        off += 8
+        rec = np.frombuffer(buf, dtype="<f4", count=cnt * 24, offset=off).reshape(cnt, 24).copy()
+        off += cnt * 96
+        out.append({"count": cnt, "time": np.float32(time), "rec": rec})
+    assert off == buf.shape[0]
+    return out
+
+
+def run_particles(emitters: np.ndarray, steps: int, delta: float = 1.0 / 60.0, kind: str = "strict") -> list[dict]:
+    with tempfile.TemporaryDirectory() as tmp:
+        fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
+        write_particle_input(fin, emitters, steps, delta)
+        subprocess.run([harness_path(kind), "particles", fin, fout], check=True, stdout=subprocess.DEVNULL)
+        return read_particle_output(fout)
+
+
+def bench_particles(emitters: np.ndarray, steps: int, warmup: int, delta: float = 1.0 / 60.0,
+                    kind: str = "release") -> dict:
+    with tempfile.TemporaryDirectory() as tmp:
+        fin = os.path.join(tmp, "in.bin")
+        write_particle_input(fin, emitters, 0, delta)
+        r = subprocess.run([harness_path(kind), "bench-particles", fin, str(steps), str(warmup)], check=True,
+                           capture_output=True, text=True)
+        return json.loads(r.stdout.strip().splitlines()[-1])
