@@ -1,0 +1,219 @@
+/*
+ * rn_cuda.h - C ABI of librn_cuda: the B200-native (sm_100a) implementation of Rayne's per-frame scene hot path.
+ *
+ * Drop-in boundary.  A Rayne `RN::Scene` subclass keeps RN::SceneNode /
+ * RN::Camera / RN::ParticleEmitter as the front end and calls these entry points instead of walking its
+ * node lists on the CPU.  No Rayne, torch or C++ types cross this boundary: plain pointers, sizes, PODs.
+ *
+ * Every function returns RN_OK (0) or a negative rn_status; the message is available per thread through
+ * rn_last_error().  Nothing here throws, aborts or falls back to a CPU implementation: if no CUDA device is
+ * usable, rn_scene_create fails with RN_ERR_CUDA.
+ *
+ * Index spaces
+ *   rank : position of a node in the reference's render list (SceneBasic::_renderNodes head -> tail,
+ *          Source/Scene/RNSceneBasic.cpp:652-676,683-736).  All host-facing node arrays are in rank order.
+ *   slot : storage index inside the library (ranks are permuted inside small tiles so that each hierarchy
+ *          level of a tile is contiguous).  Visibility lists hold *slots*, ordered by ascending *rank* - i.e.
+ *          exactly the order in which SceneBasic::Render would have submitted the nodes.  rn_scene_slot_table
+ *          converts between the two.
+ */
+#ifndef RN_CUDA_H
+#define RN_CUDA_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RN_ABI_VERSION 1
+#define RN_MAX_CAMERAS 8          /* views culled by one rn_cull call (stereo + 4 cascades = 6) */
+#define RN_NO_PARENT 0xffffffffu
+
+typedef enum rn_status {
+	RN_OK = 0,
+	RN_ERR_INVALID = -1,      /* bad argument */
+	RN_ERR_CUDA = -2,         /* CUDA runtime error (message in rn_last_error) */
+	RN_ERR_NOMEM = -3,
+	RN_ERR_STATE = -4,        /* call order violated (e.g. cull before upload) */
+	RN_ERR_CAPACITY = -5,     /* exceeds the capacities given at creation */
+	RN_ERR_NCCL = -6
+} rn_status;
+
+typedef struct rn_scene rn_scene_t;
+
+/* RN::SceneNode::Flags bits the path looks at (Source/Scene/RNSceneNode.h:56-68). */
+#define RN_NODE_STATIC     (1u << 0)
+#define RN_NODE_HIDDEN     (1u << 1)
+#define RN_NODE_NOCULLING  (1u << 2)
+/* RN::Camera::Flags bits the path looks at (Source/Scene/RNCamera.h:30-50). */
+#define RN_CAMERA_ORTHOGONAL         (1u << 21)
+#define RN_CAMERA_USE_SIMPLE_CULLING (1u << 26)
+
+typedef struct rn_scene_desc {
+	int32_t  device;                     /* CUDA device ordinal */
+	uint32_t max_nodes;                  /* capacity of the node columns */
+	uint32_t tile_nodes;                 /* nodes per tile (0 = default 512; 64..1024) */
+	uint32_t max_emitters;               /* 0 = no particle storage */
+	uint32_t max_particles_per_emitter;  /* < 16383 (Source/Scene/RNParticleEmitter.cpp:115) */
+	uint32_t reserved[3];
+} rn_scene_desc;
+
+/* Host node columns in RANK order.  Replaces the per-object state SceneNode keeps
+ * (Source/Scene/RNSceneNode.h:204-246: _position/_scale/_rotation, _parent, _flags, _renderGroup,
+ * _boundingSphere).  A NULL column is left untouched on partial updates. */
+typedef struct rn_node_columns {
+	const float    *position;         /* 3 floats per node                                   */
+	const float    *scale;            /* 3 floats per node                                   */
+	const float    *rotation;         /* 4 floats per node: quaternion x, y, z, w            */
+	const uint32_t *parent;           /* rank of the parent or RN_NO_PARENT                  */
+	const uint32_t *flags;            /* RN::SceneNode::Flags                                */
+	const uint32_t *render_group;     /* low 8 bits = SceneNode::_renderGroup                */
+	const float    *bounding_sphere;  /* 4 floats per node: local offset x, y, z and radius  */
+} rn_node_columns;
+
+/* What Camera::PostUpdate / UpdateFrustum leave behind for the cull test
+ * (Source/Scene/RNCamera.cpp:296-384,440-473): bounding sphere of the frustum, six planes in the order
+ * left, right, top, bottom, near, far (normal xyz, d), camera flags and render group. */
+typedef struct rn_camera_frustum {
+	float    center[3];
+	float    radius;
+	float    planes[6][4];
+	uint32_t flags;
+	uint32_t render_group;
+} rn_camera_frustum;
+
+/* Camera parameters - the state RN::Camera holds (Source/Scene/RNCamera.cpp:60-95,136-228). */
+typedef struct rn_camera_desc {
+	uint32_t flags;
+	uint32_t render_group;
+	float    world_position[3];
+	float    world_rotation[4];       /* x, y, z, w */
+	float    scale[3];                /* the camera's LOCAL scale (RNCamera.cpp:305) */
+	float    fov, aspect, clip_near, clip_far;
+	float    ortho[4];                /* left, right, bottom, top */
+	float    plane_offsets[4];        /* top, bottom, left, right (Camera::SetFrustumPlaneOffset) */
+	uint32_t has_projection;          /* 1: `projection` was set through Camera::SetProjectionMatrix */
+	float    projection[16];          /* column-major */
+} rn_camera_desc;
+
+/* Result of rn_cull for one camera.  `slots` is DEVICE memory owned by the scene, valid until the next
+ * rn_cull / rn_transform_cull on the same scene; `count` is valid after the stream has been synchronised
+ * (or use rn_cull_read_counts). */
+typedef struct rn_vis_list {
+	const uint32_t *slots;            /* device pointer, `capacity` entries available           */
+	const uint32_t *count;            /* device pointer to the number of visible nodes           */
+	uint32_t        capacity;
+	uint32_t        reserved;
+} rn_vis_list;
+
+typedef enum rn_download_what {
+	RN_DL_WORLD_POSITION = 0,   /* 3 floats per node  (SceneNode::GetWorldPosition)  */
+	RN_DL_WORLD_ROTATION = 1,   /* 4 floats per node  (SceneNode::GetWorldRotation)  */
+	RN_DL_WORLD_SCALE    = 2,   /* 3 floats per node  (SceneNode::GetWorldScale)     */
+	RN_DL_WORLD_MATRIX   = 3,   /* 16 floats per node, column-major (GetWorldTransform) */
+	RN_DL_SLOT_OF_RANK   = 4,   /* uint32 per node */
+	RN_DL_RANK_OF_SLOT   = 5    /* uint32 per node */
+} rn_download_what;
+
+/* ---- life cycle ------------------------------------------------------------------------------------------ */
+const char *rn_last_error(void);
+int rn_abi_version(void);
+int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc);
+void rn_scene_destroy(rn_scene_t *scene);
+
+/* ---- nodes -------------------------------------------------------------------------------------------------
+ * rn_scene_upload: replaces SceneBasic::AddNode's list building + the per-node state of SceneNode.
+ *   cols->parent != NULL : full (re)definition of the scene; `first` must be 0 and `count` the node count.
+ *                          Rebuilds the tiling.  All columns must be non-NULL.
+ *   cols->parent == NULL : overwrite the given columns of ranks [first, first+count) (SetPosition & co).
+ * rn_scene_update_nodes : the same partial update for a scattered set of ranks (the dirty set of a frame).
+ * Host arrays are consumed before the call returns. */
+int rn_scene_upload(rn_scene_t *scene, const rn_node_columns *cols, uint32_t first, uint32_t count);
+int rn_scene_update_nodes(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count);
+int rn_scene_node_count(const rn_scene_t *scene, uint32_t *out_count);
+
+/* rn_transform_propagate: SceneNode::UpdateInternalData + UpdateInternalTransformData for every node
+ * (Source/Scene/RNSceneNode.cpp:501-546): world position/rotation/scale and the world matrix.
+ * rn_cull: SceneNode::CanRenderUtil + Camera::InFrustum(sphere) for every node and camera
+ * (Source/Scene/RNSceneNode.cpp:405-417,570-588; Source/Scene/RNCamera.cpp:440-473), compacted in render-list
+ * order.  Uses the world TRS left by the last rn_transform_propagate.
+ * rn_transform_cull: both in one pass over the nodes (the reference evaluates transforms lazily inside the
+ * cull loop, Source/Scene/RNSceneBasic.cpp:576-593, so fusing them is faithful to its frame).
+ * All three are asynchronous on `cuda_stream` (a cudaStream_t, NULL = default stream). */
+int rn_transform_propagate(rn_scene_t *scene, void *cuda_stream);
+int rn_cull(rn_scene_t *scene, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists,
+            void *cuda_stream);
+int rn_transform_cull(rn_scene_t *scene, const rn_camera_frustum *cameras, uint32_t n_cameras,
+                      rn_vis_list *out_lists, void *cuda_stream);
+/* Synchronises the stream and copies the per-camera visible counts of the last cull to the host. */
+int rn_cull_read_counts(rn_scene_t *scene, uint32_t *out_counts, uint32_t n_cameras, void *cuda_stream);
+/* Copies the visibility list of one camera to the host (synchronous). `out_slots` has `capacity` entries. */
+int rn_cull_read_list(rn_scene_t *scene, uint32_t camera, uint32_t *out_slots, uint32_t capacity,
+                      uint32_t *out_count, void *cuda_stream);
+
+/* Synchronous read-back in RANK order (parity tests, SetWorldPosition & co on the host side). */
+int rn_scene_download(rn_scene_t *scene, rn_download_what what, uint32_t first, uint32_t count, void *dst);
+/* Device pointers of the outputs in SLOT order (for GPU consumers: instance buffers etc.).
+ * world_matrix: 16 floats per slot; world_pos_sx: float4 (x, y, z, scale.x); world_rot: float4;
+ * world_scale_yz: float2. */
+int rn_scene_device_outputs(rn_scene_t *scene, const float **world_matrix, const float **world_pos_sx,
+                            const float **world_rot, const float **world_scale_yz);
+
+/* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
+ * Pure host function; V <= 8 cameras per frame make this negligible. */
+int rn_camera_build_frustum(const rn_camera_desc *camera, rn_camera_frustum *out);
+
+/* SceneBasic::AddNode / AddRenderNode list order (Source/Scene/RNSceneBasic.cpp:652-676,683-736 and
+ * Source/Scene/RNSceneNode.cpp:270-294) for nodes given in CREATION order: parent[i] < i is the creation index of
+ * the parent or -1; every tree is complete when its root is added; roots are added in creation order.
+ * Writes order[rank] = creation index.  Pure host function. */
+int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, const int32_t *render_priority, uint32_t *order);
+
+/* ---- particles ------------------------------------------------------------------------------------------- */
+/* GenericParticleEmitter state (Source/Scene/RNParticleEmitter.cpp:24-36,379-395). */
+typedef struct rn_emitter_desc {
+	uint32_t seed;                    /* RandomNumberGenerator::Seed (Source/Math/RNRandom.cpp:313-323) */
+	uint32_t max_particles;           /* SetMaxParticles: hard and soft maximum */
+	float    spawn_rate;              /* seconds between spawns */
+	float    life_span[2];
+	float    start_color[4], end_color[4];
+	float    start_size[2], end_size[2], start_rotation[2], end_rotation[2];
+	float    gravity[3], velocity[3], velocity_min[3], velocity_max[3], position_min[3], position_max[3];
+} rn_emitter_desc;
+
+typedef enum rn_particle_field {
+	RN_PF_POSITION = 0,   /* 3 floats */
+	RN_PF_VELOCITY = 1,   /* 3 floats */
+	RN_PF_TIMING   = 2,   /* 3 floats: time, lifespan, duration */
+	RN_PF_RANGES   = 3,   /* 4 floats: size start, size end, rotation start, rotation end */
+	RN_PF_DERIVED  = 4,   /* 7 floats: rotation, size x, size y, color r, g, b, a */
+	RN_PF_SORTED   = 5    /* 1 uint32: per-emitter depth-sorted particle indices (after rn_particles_sort) */
+} rn_particle_field;
+
+/* (Re)creates `count` emitters with no live particles (new GenericParticleEmitter + Seed). */
+int rn_particles_configure(rn_scene_t *scene, const rn_emitter_desc *emitters, uint32_t count);
+/* ParticleEmitter::UpdateParticles for every emitter (Source/Scene/RNParticleEmitter.cpp:180-211):
+ * integrate/age/interpolate, order-preserving kill, spawn with the emitter's own MT19937 stream. */
+int rn_particles_step(rn_scene_t *scene, float delta, void *cuda_stream);
+/* Extension (no live reference behaviour, Source/Scene/RNParticleEmitter.cpp:364 is a comment): per-emitter
+ * ascending sort of the live particles by distance to `camera_world_position`; ties keep vector order. */
+int rn_particles_sort(rn_scene_t *scene, const float camera_world_position[3], void *cuda_stream);
+int rn_particles_counts(rn_scene_t *scene, uint32_t *out_counts, float *out_times, uint32_t n_emitters);
+/* Copies one field of the live particles of one emitter, in vector order (synchronous). */
+int rn_particles_download(rn_scene_t *scene, uint32_t emitter, rn_particle_field field, void *dst,
+                          uint32_t capacity_particles, uint32_t *out_count);
+
+/* ---- introspection for the bench / tests ---------------------------------------------------------------- */
+typedef struct rn_scene_stats {
+	uint32_t nodes, tiles, spine_nodes, spine_levels, max_depth, tile_nodes;
+	uint64_t device_bytes;
+	uint64_t kernel_launches;         /* kernels launched by this scene since creation */
+} rn_scene_stats;
+int rn_scene_get_stats(const rn_scene_t *scene, rn_scene_stats *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RN_CUDA_H */

@@ -1,0 +1,146 @@
+"""TEST INFRASTRUCTURE - ctypes wrapper of oracle/rn_oracle.c (the CPU restatement of the reference path).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from rayne_b200.scenegen import CAMERA_DTYPE, EMITTER_DTYPE, Scene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "rn_oracle.c")
+OUT_DIR = os.path.join(HERE, "_build")
+LIB = os.path.join(OUT_DIR, "librn_oracle.so")
+
+FRUSTUM_DTYPE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("planes", "<f4", (6, 4)),
+                          ("flags", "<u4"), ("render_group", "<u4")])
+RN_NO_PARENT = 0xFFFFFFFF
+REC = 24
+
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """gcc -O2 -ffp-contract=off: strict IEEE evaluation, one rounding per operation."""
+    os.makedirs(OUT_DIR, exist_ok=True)
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(SRC):
+        subprocess.run(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-std=c11", "-Wall", "-o", LIB, SRC, "-lm"],
+                       check=True)
+    return LIB
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if os.path.exists(SRC):
+            try:
+                build()
+            except Exception:
+                if not os.path.exists(LIB):
+                    raise
+        _lib = C.CDLL(LIB)
+        _lib.rn_oracle_cull.restype = C.c_uint32
+        _lib.rn_oracle_emitters_create.restype = C.c_void_p
+        _lib.rn_oracle_emitter_read.restype = C.c_uint32
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def render_order(parent: np.ndarray, priority: np.ndarray | None) -> np.ndarray:
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    prio = None if priority is None else np.ascontiguousarray(priority, dtype=np.int32)
+    order = np.zeros(parent.shape[0], dtype=np.uint32)
+    import sys
+    old = sys.getrecursionlimit()
+    rc = load().rn_oracle_render_order(C.c_uint32(parent.shape[0]), _p(parent), _p(prio), _p(order))
+    assert rc == 0
+    return order
+
+
+def world(parent_u32: np.ndarray, pos: np.ndarray, scale: np.ndarray, rot: np.ndarray):
+    """World TRS + matrices for arrays in any common order (parent = index into the same arrays / RN_NO_PARENT)."""
+    n = parent_u32.shape[0]
+    parent_u32 = np.ascontiguousarray(parent_u32, dtype=np.uint32)
+    pos = np.ascontiguousarray(pos, dtype=np.float32); scale = np.ascontiguousarray(scale, dtype=np.float32)
+    rot = np.ascontiguousarray(rot, dtype=np.float32)
+    wpos = np.zeros((n, 3), np.float32); wrot = np.zeros((n, 4), np.float32); wscale = np.zeros((n, 3), np.float32)
+    wmat = np.zeros((n, 16), np.float32)
+    load().rn_oracle_world(C.c_uint32(n), _p(parent_u32), _p(pos), _p(scale), _p(rot), _p(wpos), _p(wrot), _p(wscale), _p(wmat))
+    return wpos, wrot, wscale, wmat
+
+
+def frustums(cameras: np.ndarray) -> np.ndarray:
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    out = np.zeros(cameras.shape[0], dtype=FRUSTUM_DTYPE)
+    for i in range(cameras.shape[0]):
+        load().rn_oracle_frustum(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(out[i:i + 1].ctypes.data))
+    return out
+
+
+def cull(wpos, wrot, wscale, sphere, flags, group, frustum: np.ndarray, want_sphere: bool = False):
+    """Visible indices (into the given arrays, ascending) for ONE frustum record."""
+    n = wpos.shape[0]
+    arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in (wpos, wrot, wscale, sphere)]
+    flags = np.ascontiguousarray(flags, dtype=np.uint32); group = np.ascontiguousarray(group, dtype=np.uint32)
+    fr = np.ascontiguousarray(frustum, dtype=FRUSTUM_DTYPE).reshape(1)
+    out = np.zeros(n, dtype=np.uint32)
+    sph = np.zeros((n, 4), np.float32) if want_sphere else None
+    cnt = load().rn_oracle_cull(C.c_uint32(n), _p(arrs[0]), _p(arrs[1]), _p(arrs[2]), _p(arrs[3]), _p(flags), _p(group),
+                                C.c_void_p(fr.ctypes.data), _p(out), _p(sph))
+    return (out[:cnt].copy(), sph) if want_sphere else out[:cnt].copy()
+
+
+def scene_reference(scene: Scene, frustum_records: np.ndarray) -> dict:
+    """Full oracle frame for a scenegen.Scene: order, world TRS/matrices (creation order), lists of creation ids."""
+    order = render_order(scene.parent, scene.priority)
+    parent = np.where(scene.parent >= 0, scene.parent, RN_NO_PARENT).astype(np.uint32)
+    wpos, wrot, wscale, wmat = world(parent, scene.pos, scene.scale, scene.rot)
+    lists = []
+    for fr in np.atleast_1d(frustum_records):
+        vis = cull(wpos[order], wrot[order], wscale[order], scene.sphere[order], scene.flags[order], scene.group[order], fr)
+        lists.append(order[vis])
+    return {"order": order, "wpos": wpos, "wrot": wrot, "wscale": wscale, "wmat": wmat, "lists": lists}
+
+
+class Emitters:
+    def __init__(self, emitters: np.ndarray):
+        self.em = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+        self.n = self.em.shape[0]
+        self.h = C.c_void_p(load().rn_oracle_emitters_create(_p(self.em), C.c_uint32(self.n)))
+
+    def step(self, delta: float, steps: int = 1) -> None:
+        for _ in range(steps):
+            load().rn_oracle_emitters_step(self.h, C.c_uint32(self.n), C.c_float(delta))
+
+    def read(self, k: int):
+        t = C.c_float()
+        cap = int(self.em["max_particles"][k]) + 1
+        rec = np.zeros((cap, REC), np.float32)
+        cnt = load().rn_oracle_emitter_read(self.h, C.c_uint32(k), _p(rec), C.c_uint32(cap), C.byref(t))
+        return rec[:cnt].copy(), np.float32(t.value)
+
+    def sort(self, k: int, cam):
+        rec, _ = self.read(k)
+        idx = np.zeros(rec.shape[0], np.uint32); key = np.zeros(rec.shape[0], np.float32)
+        camv = (C.c_float * 3)(*[float(x) for x in cam])
+        load().rn_oracle_emitter_sort(self.h, C.c_uint32(k), camv, _p(idx), _p(key))
+        return idx, key
+
+    def close(self):
+        if self.h:
+            load().rn_oracle_emitters_destroy(self.h, C.c_uint32(self.n))
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,610 @@
+/*
+ * TEST INFRASTRUCTURE - NOT PART OF THE PRODUCT.
+ *
+ * rn_oracle.c: a plain-C, scalar, CPU restatement of the reference's scene hot path (uberpixel/Rayne @ 451a96e5),
+ * written function by function from the reference sources cited below.  Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline leg may load it; librn_cuda never links or calls it.
+ *
+ * Parity pin: the reference has NO tests, golden vectors or fixtures for this path (Tests/ covers only
+ * Objects/String/Number/KVO and is disabled, Tests/CMakeLists.txt:6-7).  This restatement is pinned instead
+ * against the reference ITSELF: oracle/_ref/ref_harness_strict links the unmodified RN::SceneNode / RN::Camera /
+ * RN::SceneBasic / RN::GenericParticleEmitter built from /root/reference (oracle/build_ref.sh) and
+ * tests/test_oracle_vs_reference.py + tests/golden/ compare the two bit for bit.
+ *
+ * Build: gcc -O2 -ffp-contract=off -fPIC -shared (see oracle/build_oracle.py).  No fast-math: every expression is
+ * evaluated in the reference's order with one rounding per operation.
+ */
+#include <math.h>
+#include <float.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define RN_NO_PARENT 0xffffffffu
+#define NODE_HIDDEN (1u << 1)
+#define NODE_NOCULLING (1u << 2)
+#define CAM_ORTHOGONAL (1u << 21)
+#define CAM_SIMPLE (1u << 26)
+
+typedef struct { float x, y, z; } vec3;
+typedef struct { float x, y, z, w; } quat;
+typedef struct { float m[16]; } mat4;
+
+/* ---- Source/Math -------------------------------------------------------------------------------------------- */
+
+/* Quaternion::operator*= , Source/Math/RNQuaternion.h:64-74 */
+static quat quat_mul(quat a, quat o)
+{
+	quat r;
+	r.w = -a.x * o.x - a.y * o.y - a.z * o.z + a.w * o.w;
+	r.x = a.x * o.w + a.y * o.z - a.z * o.y + a.w * o.x;
+	r.y = -a.x * o.z + a.y * o.w + a.z * o.x + a.w * o.y;
+	r.z = a.x * o.y - a.y * o.x + a.z * o.w + a.w * o.z;
+	return r;
+}
+
+/* Quaternion::GetRotatedVector, Source/Math/RNQuaternion.h:454-459 (conjugate :433-436) */
+static vec3 quat_rotate(quat q, vec3 v)
+{
+	quat vq = {v.x, v.y, v.z, 0.0f};
+	quat conj = {-q.x, -q.y, -q.z, q.w};
+	quat r = quat_mul(quat_mul(q, vq), conj);
+	vec3 out = {r.x, r.y, r.z};
+	return out;
+}
+
+static mat4 mat_identity(void)
+{
+	mat4 r;
+	memset(&r, 0, sizeof(r));
+	r.m[0] = r.m[5] = r.m[10] = r.m[15] = 1.0f;
+	return r;
+}
+
+/* Matrix::operator* / operator*=, Source/Math/RNMatrix.h:32-142 */
+static mat4 mat_mul(const mat4 *a, const mat4 *o)
+{
+	mat4 r;
+	for(int c = 0; c < 4; c++)
+		for(int i = 0; i < 4; i++)
+			r.m[c * 4 + i] = a->m[i] * o->m[c * 4] + a->m[4 + i] * o->m[c * 4 + 1] + a->m[8 + i] * o->m[c * 4 + 2] + a->m[12 + i] * o->m[c * 4 + 3];
+	return r;
+}
+
+/* Quaternion::GetRotationMatrix, Source/Math/RNQuaternion.h:468-493 */
+static mat4 quat_matrix(quat q)
+{
+	mat4 r = mat_identity();
+	float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z, xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w, yz = q.y * q.z,
+	      yw = q.y * q.w, zw = q.z * q.w;
+	r.m[0] = 1.0f - 2.0f * (yy + zz);
+	r.m[4] = 2.0f * (xy - zw);
+	r.m[8] = 2.0f * (xz + yw);
+	r.m[1] = 2.0f * (xy + zw);
+	r.m[5] = 1.0f - 2.0f * (xx + zz);
+	r.m[9] = 2.0f * (yz - xw);
+	r.m[2] = 2.0f * (xz - yw);
+	r.m[6] = 2.0f * (yz + xw);
+	r.m[10] = 1.0f - 2.0f * (xx + yy);
+	return r;
+}
+
+/* Matrix::WithTranslation; Rotate; Scale - SceneNode::UpdateInternalTransformData, Source/Scene/RNSceneNode.cpp:530-532 */
+static mat4 local_matrix(vec3 p, quat q, vec3 s)
+{
+	mat4 t = mat_identity();
+	t.m[12] = p.x; t.m[13] = p.y; t.m[14] = p.z;
+	mat4 r = quat_matrix(q);
+	t = mat_mul(&t, &r);
+	mat4 sc = mat_identity();
+	sc.m[0] = s.x; sc.m[5] = s.y; sc.m[10] = s.z;
+	return mat_mul(&t, &sc);
+}
+
+/* Matrix::GetDeterminant / GetSubmatrixDeterminant / GetInverse, Source/Math/RNMatrix.h:245-257,438-465 */
+static float mat_det(const float *m)
+{
+	float det = m[0] * (m[5] * m[10] * m[15] + m[6] * m[11] * m[13] + m[7] * m[9] * m[14] - m[7] * m[10] * m[13] - m[6] * m[9] * m[15] - m[5] * m[11] * m[14]);
+	det -= m[1] * (m[4] * m[10] * m[15] + m[6] * m[11] * m[12] + m[7] * m[8] * m[14] - m[7] * m[10] * m[12] - m[6] * m[8] * m[15] - m[4] * m[11] * m[14]);
+	det += m[2] * (m[4] * m[9] * m[15] + m[5] * m[11] * m[12] + m[7] * m[8] * m[13] - m[7] * m[9] * m[12] - m[5] * m[8] * m[15] - m[4] * m[11] * m[13]);
+	det -= m[3] * (m[4] * m[9] * m[14] + m[5] * m[10] * m[12] + m[6] * m[8] * m[13] - m[6] * m[9] * m[12] - m[5] * m[8] * m[14] - m[4] * m[10] * m[13]);
+	return det;
+}
+static float mat_subdet(const float *m, int k)
+{
+	int i = k % 4, j = k / 4;
+	int i1 = (i == 0), i2 = i1 + 1 + (i == 1), i3 = i2 + 1 + (i == 2);
+	int j1 = (j == 0), j2 = j1 + 1 + (j == 1), j3 = j2 + 1 + (j == 2);
+	i1 *= 4; i2 *= 4; i3 *= 4;
+	float det = m[i1 + j1] * m[i2 + j2] * m[i3 + j3] + m[i1 + j2] * m[i2 + j3] * m[i3 + j1] + m[i1 + j3] * m[i2 + j1] * m[i3 + j2]
+	          - m[i1 + j3] * m[i2 + j2] * m[i3 + j1] - m[i1 + j1] * m[i2 + j3] * m[i3 + j2] - m[i1 + j2] * m[i2 + j1] * m[i3 + j3];
+	det *= 1 - 2 * ((i + j) % 2);
+	return det;
+}
+static mat4 mat_inverse(const mat4 *a)
+{
+	mat4 r;
+	float det = mat_det(a->m);
+	for(int i = 0; i < 16; i++) r.m[i] = mat_subdet(a->m, i) / det;
+	return r;
+}
+
+/* Vector3::Normalize, Source/Math/RNVector.h:519-530; Math::InverseSqrt, Source/Math/RNMath.cpp:21-24 */
+static vec3 vec_normalize(vec3 v)
+{
+	if(v.x * v.x + v.y * v.y + v.z * v.z > FLT_EPSILON)
+	{
+		float inv = 1.0f * (float)(1.0 / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z));
+		v.x *= inv; v.y *= inv; v.z *= inv;
+	}
+	return v;
+}
+static float vec_dot(vec3 a, vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; } /* RNVector.h:489-492 */
+static vec3 vec_cross(vec3 a, vec3 b)                                               /* RNVector.h:494-503 */
+{
+	vec3 r = {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+	return r;
+}
+static float fmax_std(float a, float b) { return (a < b) ? b : a; } /* std::max */
+static float fmin_std(float a, float b) { return (b < a) ? b : a; } /* std::min */
+
+/* ---- ordering: SceneBasic::AddNode / AddRenderNode ---------------------------------------------------------- */
+
+/* Source/Scene/RNSceneBasic.cpp:652-676,683-736; Source/Scene/RNSceneNode.cpp:270-294.
+ * parent[] in creation order (-1 = root, parent index < child index), roots are added in creation order after
+ * their trees are complete.  order[rank] = creation index.  Recursive like the reference (depth-bounded inputs). */
+typedef struct
+{
+	const int32_t *prio;
+	uint32_t *next, *prev, head, tail;
+	const uint32_t *child_ofs, *child;
+} order_ctx;
+
+static void add_render_node(order_ctx *c, uint32_t node)
+{
+	const uint32_t NIL = 0xffffffffu;
+	int32_t p = c->prio ? c->prio[node] : 0;
+	if(c->head == NIL || (c->prio ? c->prio[c->head] : 0) >= p)
+	{
+		c->next[node] = c->head; c->prev[node] = NIL;
+		if(c->head != NIL) c->prev[c->head] = node; else c->tail = node;
+		c->head = node;
+	}
+	else if((c->prio ? c->prio[c->tail] : 0) <= p)
+	{
+		c->prev[node] = c->tail; c->next[node] = NIL;
+		c->next[c->tail] = node;
+		c->tail = node;
+	}
+	else
+	{
+		uint32_t m = c->tail;
+		while(c->prio[m] > p) m = c->prev[m];
+		uint32_t after = c->next[m];
+		c->next[m] = node; c->prev[node] = m; c->next[node] = after;
+		if(after != NIL) c->prev[after] = node; else c->tail = node;
+	}
+}
+static void add_node(order_ctx *c, uint32_t node)
+{
+	for(uint32_t k = c->child_ofs[node]; k < c->child_ofs[node + 1]; k++) add_node(c, c->child[k]); /* UpdateSceneInfo */
+	add_render_node(c, node);
+}
+
+int rn_oracle_render_order(uint32_t n, const int32_t *parent, const int32_t *prio, uint32_t *order)
+{
+	uint32_t *ofs = calloc(n + 2, 4), *child = malloc(4 * (n + 1)), *fill = malloc(4 * (n + 1));
+	order_ctx c;
+	c.prio = prio;
+	c.next = malloc(4 * (n + 1)); c.prev = malloc(4 * (n + 1));
+	c.head = c.tail = 0xffffffffu;
+	for(uint32_t i = 0; i < n; i++) if(parent[i] >= 0) ofs[parent[i] + 1]++;
+	for(uint32_t i = 0; i < n; i++) ofs[i + 1] += ofs[i];
+	memcpy(fill, ofs, 4 * (n + 1));
+	for(uint32_t i = 0; i < n; i++) if(parent[i] >= 0) child[fill[parent[i]]++] = i;
+	c.child_ofs = ofs; c.child = child;
+	for(uint32_t i = 0; i < n; i++) if(parent[i] < 0) add_node(&c, i);
+	uint32_t r = 0;
+	for(uint32_t i = c.head; i != 0xffffffffu; i = c.next[i]) order[r++] = i;
+	free(ofs); free(child); free(fill); free(c.next); free(c.prev);
+	return r == n ? 0 : -1;
+}
+
+/* ---- SceneNode world transforms ----------------------------------------------------------------------------- */
+
+/* SceneNode::UpdateInternalData (Source/Scene/RNSceneNode.cpp:501-524) and UpdateInternalTransformData (:526-546).
+ * Arrays are indexed by any ordering in which parent[i] (an index into the same arrays, RN_NO_PARENT for roots) is
+ * resolved recursively like the reference's lazy evaluation; here: iterate until all ancestors are done. */
+int rn_oracle_world(uint32_t n, const uint32_t *parent, const float *pos, const float *scale, const float *rot,
+                    float *wpos, float *wrot, float *wscale, float *wmat)
+{
+	uint8_t *done = calloc(n ? n : 1, 1);
+	uint32_t *stack = malloc(4 * (n + 1));
+	for(uint32_t start = 0; start < n; start++)
+	{
+		uint32_t sp = 0;
+		uint32_t u = start;
+		while(!done[u]) { stack[sp++] = u; if(parent[u] == RN_NO_PARENT) break; u = parent[u]; }
+		while(sp)
+		{
+			u = stack[--sp];
+			vec3 p = {pos[u * 3], pos[u * 3 + 1], pos[u * 3 + 2]};
+			vec3 s = {scale[u * 3], scale[u * 3 + 1], scale[u * 3 + 2]};
+			quat q = {rot[u * 4], rot[u * 4 + 1], rot[u * 4 + 2], rot[u * 4 + 3]};
+			mat4 local = local_matrix(p, q, s);
+			if(parent[u] != RN_NO_PARENT)
+			{
+				uint32_t P = parent[u];
+				vec3 pwp = {wpos[P * 3], wpos[P * 3 + 1], wpos[P * 3 + 2]};
+				vec3 pws = {wscale[P * 3], wscale[P * 3 + 1], wscale[P * 3 + 2]};
+				quat pwr = {wrot[P * 4], wrot[P * 4 + 1], wrot[P * 4 + 2], wrot[P * 4 + 3]};
+				vec3 rv = quat_rotate(pwr, p);
+				/* _parent->GetWorldPosition() + _parent->GetWorldScale() * rotated   (:509) */
+				wpos[u * 3] = pwp.x + pws.x * rv.x; wpos[u * 3 + 1] = pwp.y + pws.y * rv.y; wpos[u * 3 + 2] = pwp.z + pws.z * rv.z;
+				quat wr = quat_mul(pwr, q); /* :510, never renormalised */
+				wrot[u * 4] = wr.x; wrot[u * 4 + 1] = wr.y; wrot[u * 4 + 2] = wr.z; wrot[u * 4 + 3] = wr.w;
+				wscale[u * 3] = pws.x * s.x; wscale[u * 3 + 1] = pws.y * s.y; wscale[u * 3 + 2] = pws.z * s.z; /* :511 */
+				mat4 pm;
+				memcpy(pm.m, wmat + (size_t)P * 16, 64);
+				mat4 w = mat_mul(&pm, &local); /* :537 */
+				memcpy(wmat + (size_t)u * 16, w.m, 64);
+			}
+			else
+			{
+				memcpy(wpos + u * 3, pos + u * 3, 12);
+				memcpy(wrot + u * 4, rot + u * 4, 16);
+				memcpy(wscale + u * 3, scale + u * 3, 12);
+				memcpy(wmat + (size_t)u * 16, local.m, 64);
+			}
+			done[u] = 1;
+		}
+	}
+	free(done); free(stack);
+	return 0;
+}
+
+/* ---- Camera -------------------------------------------------------------------------------------------------- */
+
+typedef struct
+{
+	uint32_t flags, render_group;
+	float pos[3], rot[4], scale[3];
+	float fov, aspect, clip_near, clip_far;
+	float ortho[4];         /* left right bottom top */
+	float plane_offsets[4]; /* top bottom left right */
+	uint32_t has_projection;
+	float projection[16];
+} oracle_camera;
+
+typedef struct
+{
+	float center[3], radius, planes[6][4];
+	uint32_t flags, render_group;
+} oracle_frustum;
+
+static vec3 to_world(const mat4 *m, float x, float y, float z)
+{
+	/* Camera::__ToWorld, Source/Scene/RNCamera.cpp:386-396; Matrix * Vector4 Source/Math/RNMatrix.h:226-232 */
+	float vx = m->m[0] * x + m->m[4] * y + m->m[8] * z + m->m[12] * 1.0f;
+	float vy = m->m[1] * x + m->m[5] * y + m->m[9] * z + m->m[13] * 1.0f;
+	float vz = m->m[2] * x + m->m[6] * y + m->m[10] * z + m->m[14] * 1.0f;
+	float vw = m->m[3] * x + m->m[7] * y + m->m[11] * z + m->m[15] * 1.0f;
+	vec3 r = {vx / vw, vy / vw, vz / vw};
+	return r;
+}
+
+static void plane_triangle(vec3 p1, vec3 p2, vec3 p3, float dirfac, float offset, float out[4])
+{
+	/* Plane::WithTriangle + CalculateD, Source/Math/RNPlane.h:68-107 */
+	vec3 d1 = {p2.x - p1.x, p2.y - p1.y, p2.z - p1.z}, d2 = {p3.x - p1.x, p3.y - p1.y, p3.z - p1.z};
+	vec3 n = vec_cross(d1, d2);
+	n.x *= dirfac; n.y *= dirfac; n.z *= dirfac;
+	n = vec_normalize(n);
+	out[0] = n.x; out[1] = n.y; out[2] = n.z;
+	out[3] = vec_dot(n, p1) + offset;
+}
+static void plane_posnormal(vec3 p, vec3 n, float out[4])
+{
+	/* Plane::WithPositionNormal, Source/Math/RNPlane.h:56-66 */
+	n = vec_normalize(n);
+	out[0] = n.x; out[1] = n.y; out[2] = n.z;
+	out[3] = vec_dot(n, p) + 0.0f;
+}
+
+/* Camera::PostUpdate / UpdateProjection / UpdateFrustum, Source/Scene/RNCamera.cpp:296-384 */
+int rn_oracle_frustum(const oracle_camera *cam, oracle_frustum *out)
+{
+	memset(out, 0, sizeof(*out));
+	out->flags = cam->flags;
+	out->render_group = cam->render_group;
+	if(cam->flags & CAM_SIMPLE)
+	{
+		out->center[2] = cam->clip_far * 0.5f;
+		out->radius = (float)(cam->clip_far * 1.5);
+		for(int k = 0; k < 6; k++) out->planes[k][1] = 1.0f; /* default Plane(), RNPlane.h:49-54 */
+		return 0;
+	}
+	vec3 wp = {cam->pos[0], cam->pos[1], cam->pos[2]}, sc = {cam->scale[0], cam->scale[1], cam->scale[2]};
+	quat wr = {cam->rot[0], cam->rot[1], cam->rot[2], cam->rot[3]};
+	mat4 inv_view = local_matrix(wp, wr, sc); /* :303-305 */
+	mat4 proj = mat_identity();
+	if(cam->has_projection)
+		memcpy(proj.m, cam->projection, 64);
+	else if(cam->flags & CAM_ORTHOGONAL)
+	{
+		/* Matrix::WithProjectionOrthogonal, Source/Math/RNMatrix.h:339-364 */
+		float left = cam->ortho[0], right = cam->ortho[1], bottom = cam->ortho[2], top = cam->ortho[3];
+		float rl = right - left, tb = top - bottom, fn = cam->clip_far - cam->clip_near;
+		float tx = -(right + left) / (right - left), ty = -(top + bottom) / (top - bottom);
+		float tz = -(cam->clip_near) / (cam->clip_far - cam->clip_near);
+		proj.m[0] = 2.0f / rl; proj.m[5] = 2.0f / tb; proj.m[10] = 1.0f / fn;
+		proj.m[12] = tx; proj.m[13] = ty; proj.m[14] = (float)(-tz + 1.0); proj.m[15] = 1.0f;
+	}
+	else
+	{
+		/* Matrix::WithProjectionPerspective, Source/Math/RNMatrix.h:366-386 */
+		float rad = cam->fov * 3.14159265358979323846264338327950288f / 180.0f;
+		float h = cosf(0.5f * rad) / sinf(0.5f * rad);
+		float w = h / cam->aspect;
+		proj.m[0] = w; proj.m[5] = h;
+		proj.m[10] = (float)(cam->clip_far / (cam->clip_far - cam->clip_near) - 1.0);
+		proj.m[11] = -1.0f;
+		proj.m[14] = (cam->clip_far * cam->clip_near) / (cam->clip_far - cam->clip_near);
+		proj.m[15] = 0.0f;
+	}
+	mat4 inv_proj = mat_inverse(&proj);
+	mat4 tw = mat_mul(&inv_view, &inv_proj);
+	vec3 pos1 = to_world(&tw, -1.0f, 1.0f, 1.0f), pos2 = to_world(&tw, -1.0f, 1.0f, 0.0f), pos3 = to_world(&tw, -1.0f, -1.0f, 0.0f);
+	vec3 pos4 = to_world(&tw, 1.0f, -1.0f, 1.0f), pos5 = to_world(&tw, 1.0f, 1.0f, 0.0f), pos6 = to_world(&tw, 1.0f, -1.0f, 0.0f);
+	vec3 fwd = {0.0f, 0.0f, -1.0f};
+	vec3 dir = quat_rotate(wr, fwd);
+#define MAX6(f) fmax_std(pos1.f, fmax_std(pos4.f, fmax_std(pos2.f, fmax_std(pos3.f, fmax_std(pos5.f, pos6.f)))))
+#define MIN6(f) fmin_std(pos1.f, fmin_std(pos4.f, fmin_std(pos2.f, fmin_std(pos3.f, fmin_std(pos5.f, pos6.f)))))
+	vec3 vmax = {MAX6(x), MAX6(y), MAX6(z)}, vmin = {MIN6(x), MIN6(y), MIN6(z)};
+	vec3 c = {(vmax.x + vmin.x) * 0.5f, (vmax.y + vmin.y) * 0.5f, (vmax.z + vmin.z) * 0.5f};
+	out->center[0] = c.x; out->center[1] = c.y; out->center[2] = c.z;
+	float dx = c.x - vmax.x, dy = c.y - vmax.y, dz = c.z - vmax.z;
+	out->radius = sqrtf(dx * dx + dy * dy + dz * dz);
+	const float *o = cam->plane_offsets;
+	plane_triangle(pos1, pos2, pos3, 1.0f, -o[2], out->planes[0]);
+	plane_triangle(pos4, pos5, pos6, -1.0f, o[3], out->planes[1]);
+	plane_triangle(pos1, pos2, pos5, -1.0f, o[0], out->planes[2]);
+	plane_triangle(pos4, pos3, pos6, 1.0f, -o[1], out->planes[3]);
+	float dn = fmin_std(cam->clip_near, cam->clip_far), df = fmax_std(cam->clip_near, cam->clip_far);
+	vec3 pn = {wp.x + dir.x * dn, wp.y + dir.y * dn, wp.z + dir.z * dn}, pf = {wp.x + dir.x * df, wp.y + dir.y * df, wp.z + dir.z * df};
+	vec3 ndir = {-dir.x, -dir.y, -dir.z};
+	plane_posnormal(pn, ndir, out->planes[4]);
+	plane_posnormal(pf, dir, out->planes[5]);
+	return 0;
+}
+
+/* ---- culling ------------------------------------------------------------------------------------------------- */
+
+/* SceneNode::UpdateInternalBoundsData sphere (Source/Scene/RNSceneNode.cpp:579-583, Source/Math/RNSphere.h:62-73),
+ * SceneNode::CanRenderUtil (RNSceneNode.cpp:405-417), Camera::InFrustum (Source/Scene/RNCamera.cpp:440-473).
+ * Node arrays are in render-list (rank) order; out_list receives the ranks of the visible nodes in that order. */
+uint32_t rn_oracle_cull(uint32_t n, const float *wpos, const float *wrot, const float *wscale, const float *sphere,
+                        const uint32_t *flags, const uint32_t *group, const oracle_frustum *cam, uint32_t *out_list,
+                        float *out_sphere /* optional n*4 */)
+{
+	uint32_t count = 0;
+	for(uint32_t i = 0; i < n; i++)
+	{
+		vec3 ws = {wscale[i * 3], wscale[i * 3 + 1], wscale[i * 3 + 2]};
+		quat wr = {wrot[i * 4], wrot[i * 4 + 1], wrot[i * 4 + 2], wrot[i * 4 + 3]};
+		float s = fmax_std(fmax_std(ws.x, ws.y), ws.z);
+		float radius = sphere[i * 4 + 3] * s;
+		vec3 off = {sphere[i * 4] * s, sphere[i * 4 + 1] * s, sphere[i * 4 + 2] * s};
+		off = quat_rotate(wr, off);
+		vec3 p = {wpos[i * 3] + off.x, wpos[i * 3 + 1] + off.y, wpos[i * 3 + 2] + off.z};
+		if(out_sphere) { out_sphere[i * 4] = p.x; out_sphere[i * 4 + 1] = p.y; out_sphere[i * 4 + 2] = p.z; out_sphere[i * 4 + 3] = radius; }
+		if(flags[i] & NODE_HIDDEN) continue;
+		if(((group[i] & 0xffu) & (cam->render_group & 0xffu)) == 0) continue;
+		if(!(flags[i] & NODE_NOCULLING))
+		{
+			float dx = cam->center[0] - p.x, dy = cam->center[1] - p.y, dz = cam->center[2] - p.z;
+			if(sqrtf(dx * dx + dy * dy + dz * dz) > cam->radius + radius) continue;
+			if(!(cam->flags & CAM_SIMPLE))
+			{
+				int inside = 1;
+				for(int k = 0; k < 6 && inside; k++)
+				{
+					float d = (p.x * cam->planes[k][0] + p.y * cam->planes[k][1] + p.z * cam->planes[k][2]) - cam->planes[k][3];
+					if(d > radius) inside = 0;
+				}
+				if(!inside) continue;
+			}
+		}
+		out_list[count++] = i;
+	}
+	return count;
+}
+
+/* Extension restated from the commented-out body of Camera::InFrustum(const AABB&), Source/Scene/RNCamera.cpp:479-496 */
+
+/* ---- particles ----------------------------------------------------------------------------------------------- */
+
+typedef struct
+{
+	uint32_t seed, max_particles;
+	float spawn_rate;
+	float life_span[2];
+	float start_color[4], end_color[4];
+	float start_size[2], end_size[2], start_rotation[2], end_rotation[2];
+	float gravity[3], velocity[3], vel_min[3], vel_max[3], pos_min[3], pos_max[3];
+} oracle_emitter;
+
+typedef struct
+{
+	uint32_t mt[624];
+	uint32_t offset;
+} oracle_mt;
+
+/* MersenneTwister::Seed, Source/Math/RNRandom.cpp:313-323 */
+static void mt_seed(oracle_mt *g, uint32_t seed)
+{
+	g->offset = 0;
+	g->mt[0] = seed;
+	for(uint32_t i = 1; i < 624; i++) g->mt[i] = 1812433253u * (g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) + i;
+}
+/* MersenneTwister::GetRandomInt32, Source/Math/RNRandom.cpp:325-358 */
+static int32_t mt_next(oracle_mt *g)
+{
+	uint32_t y, a;
+	if(g->offset >= 624)
+	{
+		g->offset = 0;
+		for(uint32_t i = 0; i < 623; i++)
+		{
+			y = (g->mt[i] & 0x80000000u) | (g->mt[i + 1] & 0x7fffffffu);
+			a = (y & 1u) ? 0x9908b0dfu : 0u;
+			g->mt[i] = g->mt[(i + 397) % 624] ^ (y >> 1) ^ a;
+		}
+		y = (g->mt[623] & 0x80000000u) | (g->mt[0] & 0x7fffffffu);
+		a = (y & 1u) ? 0x9908b0dfu : 0u;
+		g->mt[623] = g->mt[396] ^ (y >> 1) ^ a;
+	}
+	y = g->mt[g->offset++];
+	y ^= (y >> 11);
+	y ^= (y << 7) & 0x9d2c5680u;
+	y ^= (y << 15) & 0xefc60000u;
+	y ^= (y >> 18);
+	return (int32_t)(y & 0x7fffffffu);
+}
+/* Generator::GetRandomFloatRange / GetUniformDeviate, Source/Math/RNRandom.cpp:213-222 */
+static float rand_range(oracle_mt *g, float lo, float hi)
+{
+	float range = hi - lo;
+	return (float)(((double)mt_next(g) * (1.0 / (2147483647 + 1.0))) * range + lo);
+}
+
+/* particle record: 24 floats, same layout as the harness dump (oracle/refio.py) */
+enum { PX = 0, VX = 3, PT = 6, PL = 7, PD = 8, S0 = 9, S1 = 10, R0 = 11, R1 = 12, ROT = 13, SZ = 14, COL = 16, GR = 20, REC = 24 };
+
+/* GenericParticle::Update, Source/Scene/RNParticle.cpp:31-53; Interpolator Linear Source/Math/RNInterpolation.h:101-103 */
+static void particle_update(float *p, const oracle_emitter *e, float delta)
+{
+	p[PT] += delta;
+	p[PL] -= delta;
+	float t = p[PT], d = p[PD];
+	p[ROT] = p[R0] + ((p[R1] - p[R0]) * t / d);
+	for(int c = 0; c < 4; c++) p[COL + c] = e->start_color[c] + ((e->end_color[c] - e->start_color[c]) * t / d);
+	p[SZ] = p[S0] + ((p[S1] - p[S0]) * t / d);
+	p[SZ + 1] = p[SZ];
+	for(int c = 0; c < 3; c++) p[VX + c] += p[GR + c] * delta;
+	for(int c = 0; c < 3; c++) p[PX + c] += p[VX + c] * delta;
+}
+
+typedef struct
+{
+	oracle_emitter e;
+	oracle_mt rng;
+	float time;
+	uint32_t count, cap;
+	float *rec; /* cap * REC */
+} oracle_emitter_state;
+
+oracle_emitter_state *rn_oracle_emitters_create(const oracle_emitter *e, uint32_t n)
+{
+	oracle_emitter_state *s = calloc(n, sizeof(*s));
+	for(uint32_t i = 0; i < n; i++)
+	{
+		s[i].e = e[i];
+		mt_seed(&s[i].rng, e[i].seed);
+		s[i].cap = e[i].max_particles + 1;
+		s[i].rec = malloc(sizeof(float) * REC * s[i].cap);
+	}
+	return s;
+}
+void rn_oracle_emitters_destroy(oracle_emitter_state *s, uint32_t n)
+{
+	for(uint32_t i = 0; i < n; i++) free(s[i].rec);
+	free(s);
+}
+
+/* ParticleEmitter::UpdateParticles, Source/Scene/RNParticleEmitter.cpp:180-211;
+ * GenericParticleEmitter::CreateParticle :416-454 (isLocal == true) */
+void rn_oracle_emitters_step(oracle_emitter_state *s, uint32_t n, float delta)
+{
+	for(uint32_t k = 0; k < n; k++)
+	{
+		oracle_emitter_state *em = &s[k];
+		const oracle_emitter *e = &em->e;
+		uint32_t out = 0;
+		for(uint32_t i = 0; i < em->count; i++)
+		{
+			float *p = em->rec + (size_t)i * REC;
+			particle_update(p, e, delta);
+			if(p[PL] <= 0.0f) continue; /* delete + erase, order preserved */
+			if(out != i) memcpy(em->rec + (size_t)out * REC, p, sizeof(float) * REC);
+			out++;
+		}
+		em->count = out;
+		if(e->spawn_rate < FLT_EPSILON) continue;
+		uint32_t spawn = (uint32_t)floorf((em->time + delta) / e->spawn_rate);
+		em->time = fmodf((em->time + delta), e->spawn_rate);
+		if(spawn > 0)
+		{
+			if(e->max_particles > 0)
+			{
+				uint32_t room = e->max_particles - em->count;
+				spawn = room < spawn ? room : spawn;
+			}
+			for(uint32_t j = 0; j < spawn; j++)
+			{
+				float *p = em->rec + (size_t)em->count * REC;
+				memset(p, 0, sizeof(float) * REC);
+				for(int c = 0; c < 3; c++) p[PX + c] = rand_range(&em->rng, fmin_std(e->pos_min[c], e->pos_max[c]), fmax_std(e->pos_min[c], e->pos_max[c]));
+				float lifespan = rand_range(&em->rng, e->life_span[0], e->life_span[1]);
+				p[PL] = lifespan;
+				for(int c = 0; c < 3; c++) p[GR + c] = e->gravity[c];
+				for(int c = 0; c < 3; c++) p[VX + c] = e->velocity[c] + rand_range(&em->rng, fmin_std(e->vel_min[c], e->vel_max[c]), fmax_std(e->vel_min[c], e->vel_max[c]));
+				float sizeScale = 1.0f;
+				p[S0] = rand_range(&em->rng, e->start_size[0], e->start_size[1]) * sizeScale;
+				p[S1] = rand_range(&em->rng, e->end_size[0], e->end_size[1]) * sizeScale;
+				p[PD] = lifespan;
+				p[R0] = rand_range(&em->rng, e->start_rotation[0], e->start_rotation[1]) * 0.01745329251994329577f;
+				p[R1] = rand_range(&em->rng, e->end_rotation[0], e->end_rotation[1]) * 0.01745329251994329577f;
+				p[PT] = 0.0f;
+				particle_update(p, e, 0.0f);
+				em->count++;
+			}
+		}
+	}
+}
+
+uint32_t rn_oracle_emitter_read(const oracle_emitter_state *s, uint32_t k, float *rec_out, uint32_t cap, float *time_out)
+{
+	if(time_out) *time_out = s[k].time;
+	uint32_t c = s[k].count < cap ? s[k].count : cap;
+	if(rec_out) memcpy(rec_out, s[k].rec, sizeof(float) * REC * c);
+	return s[k].count;
+}
+
+/* Extension P7 (no live reference behaviour): the comparator of the commented-out std::sort in
+ * ParticleEmitter::Render, Source/Scene/RNParticleEmitter.cpp:364 - ascending distance to the camera position,
+ * made stable (ties keep vector order).  idx_out[i] = index of the i-th nearest particle, key_out = distances. */
+typedef struct { float key; uint32_t idx; } sort_item;
+static int sort_cmp(const void *a, const void *b)
+{
+	const sort_item *x = a, *y = b;
+	if(x->key < y->key) return -1;
+	if(x->key > y->key) return 1;
+	return x->idx < y->idx ? -1 : (x->idx > y->idx);
+}
+void rn_oracle_emitter_sort(const oracle_emitter_state *s, uint32_t k, const float cam[3], uint32_t *idx_out, float *key_out)
+{
+	uint32_t n = s[k].count;
+	sort_item *it = malloc(sizeof(sort_item) * (n ? n : 1));
+	for(uint32_t i = 0; i < n; i++)
+	{
+		const float *p = s[k].rec + (size_t)i * REC;
+		float dx = p[PX] - cam[0], dy = p[PX + 1] - cam[1], dz = p[PX + 2] - cam[2];
+		it[i].key = sqrtf(dx * dx + dy * dy + dz * dz);
+		it[i].idx = i;
+		if(key_out) key_out[i] = it[i].key;
+	}
+	qsort(it, n, sizeof(sort_item), sort_cmp);
+	for(uint32_t i = 0; i < n; i++) idx_out[i] = it[i].idx;
+	free(it);
+}

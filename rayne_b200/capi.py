@@ -1,0 +1,285 @@
+"""ctypes binding of librn_cuda.so (include/rn_cuda.h) - the call path a Rayne `Scene` subclass would use.
+
+There is deliberately no fallback: if the shared library is missing or a CUDA call fails, the error surfaces
+as `RNError`.  numpy arrays are host buffers; everything on the device is owned by the library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+from .scenegen import CAMERA_DTYPE, EMITTER_DTYPE, Scene
+
+RN_MAX_CAMERAS = 8
+RN_NO_PARENT = 0xFFFFFFFF
+
+DL_WORLD_POSITION, DL_WORLD_ROTATION, DL_WORLD_SCALE, DL_WORLD_MATRIX, DL_SLOT_OF_RANK, DL_RANK_OF_SLOT = range(6)
+PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
+
+EXPORTS = [
+    "rn_last_error", "rn_abi_version", "rn_scene_create", "rn_scene_destroy", "rn_scene_upload",
+    "rn_scene_update_nodes", "rn_scene_node_count", "rn_transform_propagate", "rn_cull", "rn_transform_cull",
+    "rn_cull_read_counts", "rn_cull_read_list", "rn_scene_download", "rn_scene_device_outputs",
+    "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
+    "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
+]
+
+
+class RNError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"rn_status {status}: {message}")
+        self.status = status
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_nodes", C.c_uint32), ("tile_nodes", C.c_uint32),
+                ("max_emitters", C.c_uint32), ("max_particles_per_emitter", C.c_uint32), ("reserved", C.c_uint32 * 3)]
+
+
+class NodeColumns(C.Structure):
+    _fields_ = [("position", C.c_void_p), ("scale", C.c_void_p), ("rotation", C.c_void_p), ("parent", C.c_void_p),
+                ("flags", C.c_void_p), ("render_group", C.c_void_p), ("bounding_sphere", C.c_void_p)]
+
+
+class VisList(C.Structure):
+    _fields_ = [("slots", C.c_void_p), ("count", C.c_void_p), ("capacity", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class SceneStats(C.Structure):
+    _fields_ = [("nodes", C.c_uint32), ("tiles", C.c_uint32), ("spine_nodes", C.c_uint32), ("spine_levels", C.c_uint32),
+                ("max_depth", C.c_uint32), ("tile_nodes", C.c_uint32), ("device_bytes", C.c_uint64),
+                ("kernel_launches", C.c_uint64)]
+
+
+FRUSTUM_DTYPE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("planes", "<f4", (6, 4)),
+                          ("flags", "<u4"), ("render_group", "<u4")])
+assert FRUSTUM_DTYPE.itemsize == 120
+# rn_camera_desc has the same layout as scenegen.CAMERA_DTYPE (pos/rot are the WORLD position/rotation)
+assert CAMERA_DTYPE.itemsize == 164
+assert EMITTER_DTYPE.itemsize == 156
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _build.LIB
+
+
+def load(build: bool = True) -> C.CDLL:
+    """Loads (building first if the sources are newer) librn_cuda.so.  Raises if it cannot be had."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if build and os.path.isdir(_build.CSRC):
+        try:
+            _build.build()
+        except Exception:
+            if not os.path.exists(_build.LIB):
+                raise
+    if not os.path.exists(_build.LIB):
+        raise RNError(-2, f"{_build.LIB} is missing: build it with `python -m rayne_b200.build` (no CPU fallback exists)")
+    lib = C.CDLL(_build.LIB)
+    lib.rn_last_error.restype = C.c_char_p
+    for name in EXPORTS:
+        getattr(lib, name)  # raises AttributeError if the ABI is incomplete
+    _lib = lib
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RNError(rc, load().rn_last_error().decode("utf-8", "replace"))
+
+
+def _f32(a, shape_last=None) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if shape_last is not None:
+        assert a.shape[-1] == shape_last, a.shape
+    return a
+
+
+def _ptr(a: np.ndarray | None):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def frustum_from_harness(fr28: np.ndarray, flags: int, group: int) -> np.ndarray:
+    """Packs the 28 frustum floats dumped by the reference harness into an rn_camera_frustum record."""
+    f = np.zeros((), dtype=FRUSTUM_DTYPE)
+    f["center"] = fr28[0:3]
+    f["radius"] = fr28[3]
+    f["planes"] = fr28[4:28].reshape(6, 4)
+    f["flags"] = flags
+    f["render_group"] = group
+    return f
+
+
+def build_frustums(cameras: np.ndarray) -> np.ndarray:
+    """rn_camera_build_frustum for an array of camera records (scenegen.CAMERA_DTYPE)."""
+    lib = load()
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    out = np.zeros(cameras.shape[0], dtype=FRUSTUM_DTYPE)
+    for i in range(cameras.shape[0]):
+        _check(lib.rn_camera_build_frustum(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(out[i:i + 1].ctypes.data)))
+    return out
+
+
+def render_order(parent: np.ndarray, priority: np.ndarray | None = None) -> np.ndarray:
+    """rn_scenebasic_render_order: order[rank] = creation index."""
+    lib = load()
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    prio = None if priority is None else np.ascontiguousarray(priority, dtype=np.int32)
+    order = np.zeros(parent.shape[0], dtype=np.uint32)
+    _check(lib.rn_scenebasic_render_order(C.c_uint32(parent.shape[0]), _ptr(parent), _ptr(prio), _ptr(order)))
+    return order
+
+
+class RankedScene:
+    """A scenegen.Scene re-ordered into the reference's render-list order (what a Scene subclass hands over)."""
+
+    def __init__(self, scene: Scene):
+        self.order = render_order(scene.parent, scene.priority)          # rank -> creation id
+        self.rank_of = np.empty(scene.n, dtype=np.uint32)                # creation id -> rank
+        self.rank_of[self.order] = np.arange(scene.n, dtype=np.uint32)
+        o = self.order
+        self.position = np.ascontiguousarray(scene.pos[o])
+        self.scale = np.ascontiguousarray(scene.scale[o])
+        self.rotation = np.ascontiguousarray(scene.rot[o])
+        p = scene.parent[o]
+        self.parent = np.where(p >= 0, self.rank_of[np.maximum(p, 0)], RN_NO_PARENT).astype(np.uint32)
+        self.flags = np.ascontiguousarray(scene.flags[o])
+        self.group = np.ascontiguousarray(scene.group[o])
+        self.sphere = np.ascontiguousarray(scene.sphere[o])
+        self.n = scene.n
+        self.roots = np.nonzero(self.parent == RN_NO_PARENT)[0].astype(np.uint32)
+
+
+class SceneHandle:
+    """Owns one rn_scene_t."""
+
+    def __init__(self, max_nodes: int, device: int = 0, tile_nodes: int = 0, max_emitters: int = 0,
+                 max_particles_per_emitter: int = 0):
+        self.lib = load()
+        desc = SceneDesc(device, max_nodes, tile_nodes, max_emitters, max_particles_per_emitter)
+        self._h = C.c_void_p()
+        _check(self.lib.rn_scene_create(C.byref(self._h), C.byref(desc)))
+        self.max_nodes = max_nodes
+        self.n = 0
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.lib.rn_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- nodes ----
+    def upload(self, rs: RankedScene) -> None:
+        cols = NodeColumns(_ptr(_f32(rs.position, 3)), _ptr(_f32(rs.scale, 3)), _ptr(_f32(rs.rotation, 4)),
+                           _ptr(np.ascontiguousarray(rs.parent, dtype=np.uint32)),
+                           _ptr(np.ascontiguousarray(rs.flags, dtype=np.uint32)),
+                           _ptr(np.ascontiguousarray(rs.group, dtype=np.uint32)), _ptr(_f32(rs.sphere, 4)))
+        _check(self.lib.rn_scene_upload(self._h, C.byref(cols), 0, rs.n))
+        self.n = rs.n
+
+    def update_nodes(self, ranks: np.ndarray, position=None, scale=None, rotation=None, flags=None, group=None,
+                     sphere=None) -> None:
+        ranks = np.ascontiguousarray(ranks, dtype=np.uint32)
+        keep = [None if a is None else _f32(a) for a in (position, scale, rotation, sphere)]
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
+        gr = None if group is None else np.ascontiguousarray(group, dtype=np.uint32)
+        cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, _ptr(fl), _ptr(gr), _ptr(keep[3]))
+        _check(self.lib.rn_scene_update_nodes(self._h, C.byref(cols), _ptr(ranks), ranks.shape[0]))
+
+    def update_range(self, first: int, count: int, position=None, scale=None, rotation=None) -> None:
+        keep = [None if a is None else _f32(a) for a in (position, scale, rotation)]
+        cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, None, None, None)
+        _check(self.lib.rn_scene_upload(self._h, C.byref(cols), first, count))
+
+    def transform_propagate(self, stream: int = 0) -> None:
+        _check(self.lib.rn_transform_propagate(self._h, C.c_void_p(stream)))
+
+    def _cull(self, fn, frustums: np.ndarray, stream: int):
+        fr = np.ascontiguousarray(np.atleast_1d(frustums), dtype=FRUSTUM_DTYPE)
+        lists = (VisList * RN_MAX_CAMERAS)()
+        _check(fn(self._h, _ptr(fr), C.c_uint32(fr.shape[0]), lists, C.c_void_p(stream)))
+        self.ncams = fr.shape[0]
+        return lists
+
+    def cull(self, frustums: np.ndarray, stream: int = 0):
+        return self._cull(self.lib.rn_cull, frustums, stream)
+
+    def transform_cull(self, frustums: np.ndarray, stream: int = 0):
+        return self._cull(self.lib.rn_transform_cull, frustums, stream)
+
+    def read_counts(self, stream: int = 0) -> np.ndarray:
+        out = np.zeros(self.ncams, dtype=np.uint32)
+        _check(self.lib.rn_cull_read_counts(self._h, _ptr(out), self.ncams, C.c_void_p(stream)))
+        return out
+
+    def read_list(self, camera: int, stream: int = 0) -> np.ndarray:
+        cnt = C.c_uint32()
+        _check(self.lib.rn_cull_read_list(self._h, camera, None, 0, C.byref(cnt), C.c_void_p(stream)))
+        out = np.zeros(cnt.value, dtype=np.uint32)
+        if cnt.value:
+            _check(self.lib.rn_cull_read_list(self._h, camera, _ptr(out), cnt.value, C.byref(cnt), C.c_void_p(stream)))
+        return out
+
+    def read_list_into(self, camera: int, out_ptr: int, capacity: int, stream: int = 0) -> int:
+        cnt = C.c_uint32()
+        _check(self.lib.rn_cull_read_list(self._h, camera, C.c_void_p(out_ptr), capacity, C.byref(cnt), C.c_void_p(stream)))
+        return cnt.value
+
+    def download(self, what: int, first: int = 0, count: int | None = None) -> np.ndarray:
+        count = self.n - first if count is None else count
+        width, dt = {DL_WORLD_POSITION: (3, np.float32), DL_WORLD_ROTATION: (4, np.float32), DL_WORLD_SCALE: (3, np.float32),
+                     DL_WORLD_MATRIX: (16, np.float32), DL_SLOT_OF_RANK: (1, np.uint32), DL_RANK_OF_SLOT: (1, np.uint32)}[what]
+        out = np.zeros((count, width), dtype=dt)
+        _check(self.lib.rn_scene_download(self._h, what, first, count, _ptr(out)))
+        return out[:, 0] if width == 1 else out
+
+    def stats(self) -> SceneStats:
+        st = SceneStats()
+        _check(self.lib.rn_scene_get_stats(self._h, C.byref(st)))
+        return st
+
+    # ---- particles ----
+    def particles_configure(self, emitters: np.ndarray) -> None:
+        em = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+        _check(self.lib.rn_particles_configure(self._h, _ptr(em), em.shape[0]))
+        self.n_emitters = em.shape[0]
+
+    def particles_step(self, delta: float, stream: int = 0) -> None:
+        _check(self.lib.rn_particles_step(self._h, C.c_float(delta), C.c_void_p(stream)))
+
+    def particles_sort(self, camera_pos, stream: int = 0) -> None:
+        cp = (C.c_float * 3)(*[float(x) for x in camera_pos])
+        _check(self.lib.rn_particles_sort(self._h, cp, C.c_void_p(stream)))
+
+    def particles_counts(self) -> tuple[np.ndarray, np.ndarray]:
+        counts = np.zeros(self.n_emitters, dtype=np.uint32)
+        times = np.zeros(self.n_emitters, dtype=np.float32)
+        _check(self.lib.rn_particles_counts(self._h, _ptr(counts), _ptr(times), self.n_emitters))
+        return counts, times
+
+    def particles_download(self, emitter: int, field: int) -> np.ndarray:
+        cnt = C.c_uint32()
+        _check(self.lib.rn_particles_download(self._h, emitter, field, None, 0, C.byref(cnt)))
+        width, dt = {PF_POSITION: (3, np.float32), PF_VELOCITY: (3, np.float32), PF_TIMING: (3, np.float32),
+                     PF_RANGES: (4, np.float32), PF_DERIVED: (7, np.float32), PF_SORTED: (1, np.uint32)}[field]
+        out = np.zeros((cnt.value, width), dtype=dt)
+        if cnt.value:
+            _check(self.lib.rn_particles_download(self._h, emitter, field, _ptr(out), cnt.value, C.byref(cnt)))
+        return out[:, 0] if width == 1 else out

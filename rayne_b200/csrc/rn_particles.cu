@@ -1,0 +1,564 @@
+// librn_cuda - particle emitters (sm_100a).
+//
+// Reference behaviour being replaced (file:line relative to the Rayne tree):
+//   GenericParticle::Update                    Source/Scene/RNParticle.cpp:31-53     age, interpolate, integrate
+//   Interpolator<T>::GetValue (Linear)         Source/Math/RNInterpolation.h:101-103 start + (difference * t / duration)
+//   ParticleEmitter::UpdateParticles           Source/Scene/RNParticleEmitter.cpp:180-211 ordered kill, spawn count
+//   GenericParticleEmitter::CreateParticle     Source/Scene/RNParticleEmitter.cpp:416-454 11 RNG draws per particle
+//   Random::MersenneTwister                    Source/Math/RNRandom.cpp:313-358      _offset = 0 after Seed, 31-bit outputs
+//   Generator::GetRandomFloatRange             Source/Math/RNRandom.cpp:213-222      float(double(k) * 2^-31 * range + min)
+//
+// Layout in HBM: every emitter owns a fixed segment of `cap` particle slots in SoA float4 columns; the live
+// particles of an emitter are the first `count` slots of its segment, in the reference's vector order.  A step
+// reads generation g and writes the compacted survivors + the newly spawned particles to generation g^1.
+// One CTA per emitter.  Compiled with -fmad=false (no contraction, fp32 and fp64).
+#include "rn_internal.h"
+
+#include <cfloat>
+#include <cstring>
+#include <new>
+
+namespace rn {
+
+constexpr uint32_t kMTN = 624;
+constexpr uint32_t kMTM = 397;
+constexpr uint32_t kDrawsPerParticle = 11;
+constexpr uint32_t kParticleThreads = 256;
+constexpr uint32_t kSpawnBatch = 256;
+
+struct EmitterState
+{
+	rn_emitter_desc d;
+	float time;        // ParticleEmitter::_time
+	uint32_t count;    // _particles.size()
+	uint32_t mt_index; // MersenneTwister::_offset
+	uint32_t pad;
+};
+
+struct ParticleBuffers
+{
+	float4 *a;  // position xyz, time
+	float4 *b;  // velocity xyz, lifespan
+	float4 *c;  // duration, size start, size end, rotation start
+	float *d;   // rotation end
+};
+
+struct ParticleStore
+{
+	uint32_t n_emitters = 0;
+	uint32_t cap = 0;
+	uint32_t gen = 0;
+	ParticleBuffers buf[2] = {};
+	float4 *color = nullptr;   // derived: colour rgba
+	float4 *misc = nullptr;    // derived: rotation, size x, size y, distance key (after sort)
+	uint32_t *sorted = nullptr;
+	EmitterState *emitters = nullptr;
+	uint32_t *mt = nullptr;    // [n_emitters][624]
+};
+
+struct ParticleView
+{
+	ParticleBuffers in, out;
+	float4 *color, *misc;
+	EmitterState *emitters;
+	uint32_t *mt;
+	uint32_t cap;
+	float delta;
+};
+
+struct PState
+{
+	float px, py, pz, time;
+	float vx, vy, vz, life;
+	float dur, s0, s1, r0, r1;
+};
+
+// GenericParticle::Update (RNParticle.cpp:43-53) for one particle; writes the derived fields.
+__device__ __forceinline__ void particle_update(PState &p, float delta, const rn_emitter_desc &e, float4 &color, float4 &misc)
+{
+	p.time += delta;
+	p.life -= delta;
+	const float t = p.time, dur = p.dur;
+	// Interpolator Linear: start + ((difference * time) / duration), difference = end - start cached at spawn
+	const float rotation = p.r0 + ((p.r1 - p.r0) * t) / dur;
+	color.x = e.start_color[0] + ((e.end_color[0] - e.start_color[0]) * t) / dur;
+	color.y = e.start_color[1] + ((e.end_color[1] - e.start_color[1]) * t) / dur;
+	color.z = e.start_color[2] + ((e.end_color[2] - e.start_color[2]) * t) / dur;
+	color.w = e.start_color[3] + ((e.end_color[3] - e.start_color[3]) * t) / dur;
+	const float size = p.s0 + ((p.s1 - p.s0) * t) / dur;
+	misc = make_float4(rotation, size, size, 0.0f);
+	// velocity += gravity * delta; position += velocity * delta
+	p.vx += e.gravity[0] * delta; p.vy += e.gravity[1] * delta; p.vz += e.gravity[2] * delta;
+	p.px += p.vx * delta; p.py += p.vy * delta; p.pz += p.vz * delta;
+}
+
+__device__ __forceinline__ void store_particle(const ParticleBuffers &o, size_t i, const PState &p)
+{
+	o.a[i] = make_float4(p.px, p.py, p.pz, p.time);
+	o.b[i] = make_float4(p.vx, p.vy, p.vz, p.life);
+	o.c[i] = make_float4(p.dur, p.s0, p.s1, p.r0);
+	o.d[i] = p.r1;
+}
+
+// Generator::GetRandomFloatRange (RNRandom.cpp:213-222): double(k) * 2^-31 * range + min, one rounding to float.
+__device__ __forceinline__ float random_range(uint32_t k31, float lo, float hi)
+{
+	const float range = hi - lo;
+	const double u = (double)(int32_t)k31 * (1.0 / 2147483648.0);
+	return (float)(u * (double)range + (double)lo);
+}
+
+__device__ __forceinline__ float fmin_std(float a, float b) { return (b < a) ? b : a; } // std::min
+__device__ __forceinline__ float fmax_std(float a, float b) { return (a < b) ? b : a; } // std::max
+
+// MT19937 block regeneration (RNRandom.cpp:330-347), restructured into three data-parallel phases + the last word.
+__device__ void mt_twist(uint32_t *mt, uint32_t tid)
+{
+	const uint32_t U = 0x80000000u, L = 0x7fffffffu, A = 0x9908b0dfu;
+	const uint32_t bounds[4] = {0, kMTN - kMTM, 2 * (kMTN - kMTM), kMTN - 1};
+#pragma unroll
+	for(int ph = 0; ph < 3; ph++)
+	{
+		uint32_t v[1];
+		const uint32_t i = bounds[ph] + tid;
+		const bool on = i < bounds[ph + 1];
+		if(on)
+		{
+			const uint32_t y = (mt[i] & U) | (mt[i + 1] & L);
+			const uint32_t src = (i + kMTM) % kMTN;
+			v[0] = mt[src] ^ (y >> 1) ^ ((y & 1u) ? A : 0u);
+		}
+		__syncthreads();
+		if(on) mt[i] = v[0];
+		__syncthreads();
+	}
+	if(tid == 0)
+	{
+		const uint32_t y = (mt[kMTN - 1] & U) | (mt[0] & L);
+		mt[kMTN - 1] = mt[kMTM - 1] ^ (y >> 1) ^ ((y & 1u) ? A : 0u);
+	}
+	__syncthreads();
+}
+
+__global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(ParticleView pv)
+{
+	__shared__ uint32_t s_mt[kMTN];
+	__shared__ uint32_t s_draws[kSpawnBatch * kDrawsPerParticle];
+	__shared__ uint32_t s_wtot[kParticleThreads / 32];
+	__shared__ rn_emitter_desc s_e;
+	__shared__ uint32_t s_spawn, s_index;
+
+	const uint32_t e = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	EmitterState *es = pv.emitters + e;
+	if(tid < sizeof(rn_emitter_desc) / 4)
+		reinterpret_cast<uint32_t *>(&s_e)[tid] = reinterpret_cast<const uint32_t *>(&es->d)[tid];
+	const uint32_t count = es->count;
+	const float etime = es->time;
+	const uint32_t mt_index = es->mt_index;
+	__syncthreads();
+	const size_t seg = (size_t)e * pv.cap;
+	const float delta = pv.delta;
+
+	// ---- update + order-preserving kill (RNParticleEmitter.cpp:182-196) ----
+	uint32_t out = 0;
+	for(uint32_t base = 0; base < count; base += kParticleThreads)
+	{
+		const uint32_t i = base + tid;
+		PState p;
+		float4 color, misc;
+		bool alive = false;
+		if(i < count)
+		{
+			const float4 a = pv.in.a[seg + i], b = pv.in.b[seg + i], c = pv.in.c[seg + i];
+			p.px = a.x; p.py = a.y; p.pz = a.z; p.time = a.w;
+			p.vx = b.x; p.vy = b.y; p.vz = b.z; p.life = b.w;
+			p.dur = c.x; p.s0 = c.y; p.s1 = c.z; p.r0 = c.w;
+			p.r1 = pv.in.d[seg + i];
+			particle_update(p, delta, s_e, color, misc);
+			alive = !(p.life <= 0.0f);
+		}
+		const uint32_t m = __ballot_sync(0xffffffffu, alive);
+		if(lane == 0) s_wtot[warp] = __popc(m);
+		__syncthreads();
+		uint32_t pre = 0, tot = 0;
+#pragma unroll
+		for(uint32_t w = 0; w < kParticleThreads / 32; w++)
+		{
+			const uint32_t x = s_wtot[w];
+			pre += w < warp ? x : 0;
+			tot += x;
+		}
+		if(alive)
+		{
+			const size_t o = seg + out + pre + __popc(m & ((1u << lane) - 1u));
+			store_particle(pv.out, o, p);
+			pv.color[o] = color;
+			pv.misc[o] = misc;
+		}
+		out += tot;
+		__syncthreads();
+	}
+
+	// ---- spawn count (RNParticleEmitter.cpp:198-210) ----
+	if(tid == 0)
+	{
+		uint32_t spawn = 0;
+		float newtime = etime;
+		if(!(s_e.spawn_rate < FLT_EPSILON))
+		{
+			const float t = etime + delta;
+			spawn = (uint32_t)floorf(t / s_e.spawn_rate);
+			newtime = fmodf(t, s_e.spawn_rate);
+			if(spawn > 0 && s_e.max_particles > 0)
+			{
+				const uint32_t room = s_e.max_particles - out; // unsigned, like the reference
+				spawn = room < spawn ? room : spawn;
+			}
+		}
+		s_spawn = spawn;
+		es->time = newtime;
+	}
+	__syncthreads();
+	const uint32_t spawn = s_spawn;
+	if(spawn == 0)
+	{
+		if(tid == 0) es->count = out;
+		return;
+	}
+
+	// ---- spawn (SpawnParticles -> CreateParticle, RNParticleEmitter.cpp:156-171,416-454) ----
+	uint32_t *gmt = pv.mt + (size_t)e * kMTN;
+	for(uint32_t k = tid; k < kMTN; k += kParticleThreads) s_mt[k] = gmt[k];
+	if(tid == 0) s_index = mt_index;
+	__syncthreads();
+	for(uint32_t done = 0; done < spawn; done += kSpawnBatch)
+	{
+		const uint32_t batch = min(kSpawnBatch, spawn - done);
+		const uint32_t need = batch * kDrawsPerParticle;
+		uint32_t produced = 0;
+		while(produced < need)
+		{
+			uint32_t index = s_index;
+			__syncthreads();
+			if(index >= kMTN)
+			{
+				mt_twist(s_mt, tid);
+				index = 0;
+			}
+			const uint32_t take = min(kMTN - index, need - produced);
+			for(uint32_t k = tid; k < take; k += kParticleThreads)
+			{
+				uint32_t y = s_mt[index + k];
+				y ^= (y >> 11);
+				y ^= (y << 7) & 0x9d2c5680u;
+				y ^= (y << 15) & 0xefc60000u;
+				y ^= (y >> 18);
+				s_draws[produced + k] = y & 0x7fffffffu;
+			}
+			produced += take;
+			__syncthreads();
+			if(tid == 0) s_index = index + take;
+			__syncthreads();
+		}
+		if(tid < batch)
+		{
+			const uint32_t *dr = s_draws + tid * kDrawsPerParticle;
+			const rn_emitter_desc &d = s_e;
+			PState p;
+			// GetRandomVector3Range swaps min/max per component (RNRandom.cpp:250-252)
+			p.px = random_range(dr[0], fmin_std(d.position_min[0], d.position_max[0]), fmax_std(d.position_min[0], d.position_max[0]));
+			p.py = random_range(dr[1], fmin_std(d.position_min[1], d.position_max[1]), fmax_std(d.position_min[1], d.position_max[1]));
+			p.pz = random_range(dr[2], fmin_std(d.position_min[2], d.position_max[2]), fmax_std(d.position_min[2], d.position_max[2]));
+			const float lifespan = random_range(dr[3], d.life_span[0], d.life_span[1]);
+			p.life = lifespan;
+			p.vx = d.velocity[0] + random_range(dr[4], fmin_std(d.velocity_min[0], d.velocity_max[0]), fmax_std(d.velocity_min[0], d.velocity_max[0]));
+			p.vy = d.velocity[1] + random_range(dr[5], fmin_std(d.velocity_min[1], d.velocity_max[1]), fmax_std(d.velocity_min[1], d.velocity_max[1]));
+			p.vz = d.velocity[2] + random_range(dr[6], fmin_std(d.velocity_min[2], d.velocity_max[2]), fmax_std(d.velocity_min[2], d.velocity_max[2]));
+			p.s0 = random_range(dr[7], d.start_size[0], d.start_size[1]) * 1.0f;
+			p.s1 = random_range(dr[8], d.end_size[0], d.end_size[1]) * 1.0f;
+			p.r0 = random_range(dr[9], d.start_rotation[0], d.start_rotation[1]) * 0.01745329251994329577f;
+			p.r1 = random_range(dr[10], d.end_rotation[0], d.end_rotation[1]) * 0.01745329251994329577f;
+			p.dur = lifespan;
+			p.time = 0.0f;
+			float4 color, misc;
+			particle_update(p, 0.0f, d, color, misc); // particle->Update(0.0f), RNParticleEmitter.cpp:451
+			const size_t o = seg + out + done + tid;
+			store_particle(pv.out, o, p);
+			pv.color[o] = color;
+			pv.misc[o] = misc;
+		}
+		__syncthreads();
+	}
+	for(uint32_t k = tid; k < kMTN; k += kParticleThreads) gmt[k] = s_mt[k];
+	if(tid == 0)
+	{
+		es->mt_index = s_index;
+		es->count = out + spawn;
+	}
+}
+
+// Extension P7: per-emitter ascending distance sort (stable), bitonic network in shared memory on
+// (distance bits, index) keys.  One CTA per emitter.
+__global__ void __launch_bounds__(512) particles_sort_kernel(ParticleBuffers cur, float4 *misc, uint32_t *sorted,
+                                                           const EmitterState *emitters, uint32_t cap, float cx, float cy, float cz,
+                                                           uint32_t padded)
+{
+	extern __shared__ unsigned long long s_keys[];
+	const uint32_t e = blockIdx.x, tid = threadIdx.x;
+	const uint32_t count = emitters[e].count;
+	const size_t seg = (size_t)e * cap;
+	// smallest power of two >= count (<= padded)
+	uint32_t n2 = 1;
+	while(n2 < count) n2 <<= 1;
+	(void)padded;
+	for(uint32_t i = tid; i < n2; i += blockDim.x)
+	{
+		unsigned long long key = ~0ull;
+		if(i < count)
+		{
+			const float4 a = cur.a[seg + i];
+			// Vector3::GetDistance (RNVector.h:537-541): length(position - camera)
+			const float dx = a.x - cx, dy = a.y - cy, dz = a.z - cz;
+			const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+			float4 m = misc[seg + i];
+			m.w = dist;
+			misc[seg + i] = m;
+			key = ((unsigned long long)__float_as_uint(dist) << 32) | i; // dist >= 0: bit pattern is monotone
+		}
+		s_keys[i] = key;
+	}
+	__syncthreads();
+	for(uint32_t k = 2; k <= n2; k <<= 1)
+	{
+		for(uint32_t j = k >> 1; j > 0; j >>= 1)
+		{
+			for(uint32_t i = tid; i < n2; i += blockDim.x)
+			{
+				const uint32_t ixj = i ^ j;
+				if(ixj > i)
+				{
+					const unsigned long long x = s_keys[i], y = s_keys[ixj];
+					const bool up = (i & k) == 0;
+					if((x > y) == up)
+					{
+						s_keys[i] = y;
+						s_keys[ixj] = x;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	}
+	for(uint32_t i = tid; i < count; i += blockDim.x)
+		sorted[seg + i] = (uint32_t)(s_keys[i] & 0xffffffffu);
+}
+
+static void free_store(ParticleStore *p)
+{
+	if(!p) return;
+	for(int g = 0; g < 2; g++)
+	{
+		if(p->buf[g].a) cudaFree(p->buf[g].a);
+		if(p->buf[g].b) cudaFree(p->buf[g].b);
+		if(p->buf[g].c) cudaFree(p->buf[g].c);
+		if(p->buf[g].d) cudaFree(p->buf[g].d);
+	}
+	if(p->color) cudaFree(p->color);
+	if(p->misc) cudaFree(p->misc);
+	if(p->sorted) cudaFree(p->sorted);
+	if(p->emitters) cudaFree(p->emitters);
+	if(p->mt) cudaFree(p->mt);
+	delete p;
+}
+
+int particles_destroy(rn_scene *scene)
+{
+	free_store(scene->particles);
+	scene->particles = nullptr;
+	return RN_OK;
+}
+
+template <class T>
+static int palloc(rn_scene *s, T **p, size_t count)
+{
+	*p = nullptr;
+	if(count == 0) count = 1;
+	RN_CUDA(cudaMalloc(reinterpret_cast<void **>(p), count * sizeof(T)));
+	s->device_bytes += count * sizeof(T);
+	return RN_OK;
+}
+
+} // namespace rn
+
+using namespace rn;
+
+extern "C" int rn_particles_configure(rn_scene_t *s, const rn_emitter_desc *emitters, uint32_t count)
+{
+	RN_REQUIRE(s && emitters, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(count > 0 && count <= s->desc.max_emitters, RN_ERR_CAPACITY, "%u emitters exceed max_emitters %u", count, s->desc.max_emitters);
+	const uint32_t cap = s->desc.max_particles_per_emitter;
+	RN_REQUIRE(cap > 0, RN_ERR_CAPACITY, "the scene was created without particle storage");
+	for(uint32_t i = 0; i < count; i++)
+	{
+		RN_REQUIRE(emitters[i].max_particles > 0 && emitters[i].max_particles <= cap, RN_ERR_CAPACITY,
+		           "emitter %u: max_particles %u must be in 1..%u", i, emitters[i].max_particles, cap);
+	}
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	particles_destroy(s);
+	ParticleStore *p = new(std::nothrow) ParticleStore();
+	RN_REQUIRE(p, RN_ERR_NOMEM, "out of host memory");
+	s->particles = p;
+	p->n_emitters = count;
+	p->cap = cap;
+	const size_t total = (size_t)s->desc.max_emitters * cap;
+	int rc = RN_OK;
+	for(int g = 0; g < 2 && !rc; g++)
+	{
+		if(!rc) rc = palloc(s, &p->buf[g].a, total);
+		if(!rc) rc = palloc(s, &p->buf[g].b, total);
+		if(!rc) rc = palloc(s, &p->buf[g].c, total);
+		if(!rc) rc = palloc(s, &p->buf[g].d, total);
+	}
+	if(!rc) rc = palloc(s, &p->color, total);
+	if(!rc) rc = palloc(s, &p->misc, total);
+	if(!rc) rc = palloc(s, &p->sorted, total);
+	if(!rc) rc = palloc(s, &p->emitters, (size_t)count);
+	if(!rc) rc = palloc(s, &p->mt, (size_t)count * kMTN);
+	if(rc)
+	{
+		particles_destroy(s);
+		return rc;
+	}
+	// MersenneTwister::Seed (RNRandom.cpp:313-323): _offset = 0, so the first 624 outputs are the tempered seed words
+	std::vector<EmitterState> es(count);
+	std::vector<uint32_t> mt((size_t)count * kMTN);
+	for(uint32_t i = 0; i < count; i++)
+	{
+		memset(&es[i], 0, sizeof(EmitterState));
+		es[i].d = emitters[i];
+		uint32_t *m = &mt[(size_t)i * kMTN];
+		m[0] = emitters[i].seed;
+		for(uint32_t k = 1; k < kMTN; k++)
+			m[k] = 1812433253u * (m[k - 1] ^ (m[k - 1] >> 30)) + k;
+	}
+	RN_CUDA(cudaMemcpy(p->emitters, es.data(), sizeof(EmitterState) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(p->mt, mt.data(), sizeof(uint32_t) * mt.size(), cudaMemcpyHostToDevice));
+	return RN_OK;
+}
+
+extern "C" int rn_particles_step(rn_scene_t *s, float delta, void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	ParticleView pv;
+	pv.in = p->buf[p->gen];
+	pv.out = p->buf[p->gen ^ 1];
+	pv.color = p->color;
+	pv.misc = p->misc;
+	pv.emitters = p->emitters;
+	pv.mt = p->mt;
+	pv.cap = p->cap;
+	pv.delta = delta;
+	particles_step_kernel<<<p->n_emitters, kParticleThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(pv);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	p->gen ^= 1;
+	return RN_OK;
+}
+
+extern "C" int rn_particles_sort(rn_scene_t *s, const float cam[3], void *cuda_stream)
+{
+	RN_REQUIRE(s && cam, RN_ERR_INVALID, "NULL argument");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	uint32_t padded = 1;
+	while(padded < p->cap) padded <<= 1;
+	const size_t smem = (size_t)padded * sizeof(unsigned long long);
+	static bool configured = false;
+	if(!configured)
+	{
+		RN_CUDA(cudaFuncSetAttribute(particles_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
+		configured = true;
+	}
+	particles_sort_kernel<<<p->n_emitters, 512, smem, static_cast<cudaStream_t>(cuda_stream)>>>(p->buf[p->gen], p->misc, p->sorted, p->emitters,
+	                                                                                          p->cap, cam[0], cam[1], cam[2], padded);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
+extern "C" int rn_particles_counts(rn_scene_t *s, uint32_t *out_counts, float *out_times, uint32_t n_emitters)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && n_emitters <= p->n_emitters, RN_ERR_STATE, "%u emitters requested, %u configured", n_emitters, p ? p->n_emitters : 0);
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	std::vector<EmitterState> es(n_emitters);
+	RN_CUDA(cudaMemcpy(es.data(), p->emitters, sizeof(EmitterState) * n_emitters, cudaMemcpyDeviceToHost));
+	for(uint32_t i = 0; i < n_emitters; i++)
+	{
+		if(out_counts) out_counts[i] = es[i].count;
+		if(out_times) out_times[i] = es[i].time;
+	}
+	return RN_OK;
+}
+
+extern "C" int rn_particles_download(rn_scene_t *s, uint32_t emitter, rn_particle_field field, void *dst, uint32_t capacity,
+                                     uint32_t *out_count)
+{
+	RN_REQUIRE(s && out_count, RN_ERR_INVALID, "NULL argument");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && emitter < p->n_emitters, RN_ERR_INVALID, "emitter %u out of range", emitter);
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	EmitterState es;
+	RN_CUDA(cudaMemcpy(&es, p->emitters + emitter, sizeof(es), cudaMemcpyDeviceToHost));
+	const uint32_t n = es.count;
+	*out_count = n;
+	if(!dst || n == 0) return RN_OK;
+	RN_REQUIRE(n <= capacity, RN_ERR_CAPACITY, "emitter %u has %u particles, buffer holds %u", emitter, n, capacity);
+	const size_t seg = (size_t)emitter * p->cap;
+	const ParticleBuffers &b = p->buf[p->gen];
+	std::vector<float4> t0(n), t1(n), t2(n);
+	std::vector<float> t3(n);
+	float *out = static_cast<float *>(dst);
+	switch(field)
+	{
+		case RN_PF_POSITION:
+		case RN_PF_VELOCITY:
+		case RN_PF_TIMING:
+		case RN_PF_RANGES:
+			RN_CUDA(cudaMemcpy(t0.data(), b.a + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(t1.data(), b.b + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(t2.data(), b.c + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(t3.data(), b.d + seg, sizeof(float) * n, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < n; i++)
+			{
+				if(field == RN_PF_POSITION) { out[i * 3] = t0[i].x; out[i * 3 + 1] = t0[i].y; out[i * 3 + 2] = t0[i].z; }
+				else if(field == RN_PF_VELOCITY) { out[i * 3] = t1[i].x; out[i * 3 + 1] = t1[i].y; out[i * 3 + 2] = t1[i].z; }
+				else if(field == RN_PF_TIMING) { out[i * 3] = t0[i].w; out[i * 3 + 1] = t1[i].w; out[i * 3 + 2] = t2[i].x; }
+				else { out[i * 4] = t2[i].y; out[i * 4 + 1] = t2[i].z; out[i * 4 + 2] = t2[i].w; out[i * 4 + 3] = t3[i]; }
+			}
+			break;
+		case RN_PF_DERIVED:
+			RN_CUDA(cudaMemcpy(t0.data(), p->misc + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(t1.data(), p->color + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < n; i++)
+			{
+				out[i * 7] = t0[i].x; out[i * 7 + 1] = t0[i].y; out[i * 7 + 2] = t0[i].z;
+				out[i * 7 + 3] = t1[i].x; out[i * 7 + 4] = t1[i].y; out[i * 7 + 5] = t1[i].z; out[i * 7 + 6] = t1[i].w;
+			}
+			break;
+		case RN_PF_SORTED:
+			RN_CUDA(cudaMemcpy(dst, p->sorted + seg, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+			break;
+		default:
+			RN_REQUIRE(false, RN_ERR_INVALID, "unknown particle field %d", (int)field);
+	}
+	return RN_OK;
+}

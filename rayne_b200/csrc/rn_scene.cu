@@ -1,0 +1,1262 @@
+// librn_cuda - scene nodes: upload + tiling (host), world-transform propagation and frustum culling (sm_100a).
+//
+// Reference behaviour being replaced (file:line relative to the Rayne tree):
+//   SceneNode::UpdateInternalData            Source/Scene/RNSceneNode.cpp:501-524   world position/rotation/scale
+//   SceneNode::UpdateInternalTransformData   Source/Scene/RNSceneNode.cpp:526-546   world matrix = P.world * local
+//   SceneNode::UpdateInternalBoundsData      Source/Scene/RNSceneNode.cpp:570-588   transformed bounding sphere
+//   SceneNode::CanRenderUtil                 Source/Scene/RNSceneNode.cpp:405-417   hidden / group / NoCulling / frustum
+//   Camera::InFrustum(Vector3, float)        Source/Scene/RNCamera.cpp:440-467      frustum sphere + 6 planes, strict >
+//   SceneBasic::Render cull loop             Source/Scene/RNSceneBasic.cpp:576-593  list order = render-list order
+//
+// Data layout in HBM: nodes live in *slots*; the slot range of a tile equals its rank range, and
+// inside a tile the nodes are sorted by sublevel (0 = spine nodes whose world transform was computed by the
+// pre-pass, k >= 1 = depth k-1 inside a compact subtree).  One CTA processes one tile: the four input columns of
+// the tile are staged into shared memory with four TMA bulk copies, the tile's levels are walked with the parents'
+// world TRS + world matrix read from shared memory, results are written once.
+//
+// Compiled with -fmad=false: see rn_math.cuh.
+#include "rn_internal.h"
+#include "rn_math.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+
+namespace rn {
+
+// ---------------------------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------------------------
+static thread_local char g_error[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_error, sizeof(g_error), fmt, ap);
+	va_end(ap);
+}
+
+int cuda_fail(cudaError_t err, const char *what, const char *file, int line)
+{
+	set_error("CUDA error %d (%s) in %s at %s:%d", (int)err, cudaGetErrorString(err), what, file, line);
+	return err == cudaErrorMemoryAllocation ? RN_ERR_NOMEM : RN_ERR_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// device helpers: mbarrier + TMA bulk copy (cp.async.bulk, 1-D)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+	             ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+	asm volatile(
+	    "{\n"
+	    ".reg .pred p;\n"
+	    "RN_WAIT:\n"
+	    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+	    "@p bra RN_DONE;\n"
+	    "bra RN_WAIT;\n"
+	    "RN_DONE:\n"
+	    "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kFlagSpine = 1u << 31;
+constexpr uint32_t kLRankShift = 16;
+constexpr uint32_t kLRankMask = 0x7ffu;
+
+struct SceneView
+{
+	const float4 *c0, *c1, *c2, *c3;
+	float4 *wpos, *wrot;
+	float2 *wsyz;
+	float4 *wmat;
+	uint8_t *vis;
+	const TileMeta *tiles;
+	uint32_t *tile_counts;
+	uint32_t n_tiles;
+	uint32_t tile_cap;
+};
+
+struct CullParams
+{
+	rn_camera_frustum cam[RN_MAX_CAMERAS];
+	uint32_t n;
+};
+
+struct NodeWorld
+{
+	Vec3 wp;
+	Quat wr;
+	Vec3 ws;
+	Affine M;
+};
+
+__device__ __forceinline__ float std_max(float a, float b) { return (a < b) ? b : a; } // std::max
+
+// SceneNode::UpdateInternalBoundsData (sphere part) + SceneNode::CanRenderUtil + Camera::InFrustum for all cameras.
+// Returns the camera bit mask.
+__device__ __forceinline__ uint32_t cull_node(const CullParams &cp, uint32_t flagsword, const Vec3 &wp, const Quat &wr,
+                                              const Vec3 &ws, const float4 &sph)
+{
+	if(flagsword & RN_NODE_HIDDEN)
+		return 0;
+	const uint32_t group = (flagsword >> 8) & 0xffu;
+
+	// Sphere::operator*=(Vector3) then SetRotation (Source/Math/RNSphere.h:62-73)
+	const float s = std_max(std_max(ws.x, ws.y), ws.z);
+	const float radius = sph.w * s;
+	Vec3 off = {sph.x * s, sph.y * s, sph.z * s};
+	off = quat_rotate(wr, off);
+	// Camera::InFrustum(const Sphere&): position + offset (Source/Scene/RNCamera.cpp:469-473)
+	const float px = wp.x + off.x, py = wp.y + off.y, pz = wp.z + off.z;
+
+	uint32_t mask = 0;
+	for(uint32_t c = 0; c < cp.n; c++)
+	{
+		const rn_camera_frustum &cam = cp.cam[c];
+		if((group & cam.render_group & 0xffu) == 0)
+			continue;
+		if(flagsword & RN_NODE_NOCULLING)
+		{
+			mask |= 1u << c;
+			continue;
+		}
+		// _frustumCenter.GetDistance(position) > _frustumRadius + radius
+		const float dx = cam.center[0] - px, dy = cam.center[1] - py, dz = cam.center[2] - pz;
+		const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+		if(dist > cam.radius + radius)
+			continue;
+		bool inside = true;
+		if(!(cam.flags & RN_CAMERA_USE_SIMPLE_CULLING))
+		{
+#pragma unroll
+			for(int k = 0; k < 6; k++)
+			{
+				// Plane::GetDistance: position.Dot(normal) - d   (Source/Math/RNPlane.h:99-102)
+				const float d = px * cam.planes[k][0] + py * cam.planes[k][1] + pz * cam.planes[k][2] - cam.planes[k][3];
+				if(d > radius)
+					inside = false;
+			}
+		}
+		if(inside)
+			mask |= 1u << c;
+	}
+	return mask;
+}
+
+__device__ __forceinline__ void compute_world(const Vec3 &pos, const Quat &rot, const Vec3 &scale, bool hasParent,
+                                              const NodeWorld &P, NodeWorld &out)
+{
+	const Affine L = local_matrix(pos, rot, scale);
+	if(hasParent)
+	{
+		// SceneNode::UpdateInternalData (RNSceneNode.cpp:509-511)
+		const Vec3 rv = quat_rotate(P.wr, pos);
+		out.wp.x = P.wp.x + P.ws.x * rv.x;
+		out.wp.y = P.wp.y + P.ws.y * rv.y;
+		out.wp.z = P.wp.z + P.ws.z * rv.z;
+		out.wr = quat_mul(P.wr, rot);
+		out.ws.x = P.ws.x * scale.x;
+		out.ws.y = P.ws.y * scale.y;
+		out.ws.z = P.ws.z * scale.z;
+		// SceneNode::UpdateInternalTransformData (RNSceneNode.cpp:537)
+		out.M = affine_mul(P.M, L);
+	}
+	else
+	{
+		out.wp = pos;
+		out.wr = rot;
+		out.ws = scale;
+		out.M = L;
+	}
+}
+
+__device__ __forceinline__ void load_world_global(const SceneView &sv, uint32_t slot, NodeWorld &w)
+{
+	const float4 a = sv.wpos[slot];
+	const float4 b = sv.wrot[slot];
+	const float2 c = sv.wsyz[slot];
+	w.wp = {a.x, a.y, a.z};
+	w.wr = {b.x, b.y, b.z, b.w};
+	w.ws = {a.w, c.x, c.y};
+	const float4 m0 = sv.wmat[slot * 4u + 0], m1 = sv.wmat[slot * 4u + 1], m2 = sv.wmat[slot * 4u + 2],
+	             m3 = sv.wmat[slot * 4u + 3];
+	w.M.m[0] = m0.x; w.M.m[1] = m0.y; w.M.m[2] = m0.z;
+	w.M.m[3] = m1.x; w.M.m[4] = m1.y; w.M.m[5] = m1.z;
+	w.M.m[6] = m2.x; w.M.m[7] = m2.y; w.M.m[8] = m2.z;
+	w.M.m[9] = m3.x; w.M.m[10] = m3.y; w.M.m[11] = m3.z;
+}
+
+__device__ __forceinline__ void store_world_global(const SceneView &sv, uint32_t slot, const NodeWorld &w)
+{
+	sv.wpos[slot] = make_float4(w.wp.x, w.wp.y, w.wp.z, w.ws.x);
+	sv.wrot[slot] = make_float4(w.wr.x, w.wr.y, w.wr.z, w.wr.w);
+	sv.wsyz[slot] = make_float2(w.ws.y, w.ws.z);
+	sv.wmat[slot * 4u + 0] = make_float4(w.M.m[0], w.M.m[1], w.M.m[2], 0.0f);
+	sv.wmat[slot * 4u + 1] = make_float4(w.M.m[3], w.M.m[4], w.M.m[5], 0.0f);
+	sv.wmat[slot * 4u + 2] = make_float4(w.M.m[6], w.M.m[7], w.M.m[8], 0.0f);
+	sv.wmat[slot * 4u + 3] = make_float4(w.M.m[9], w.M.m[10], w.M.m[11], 1.0f);
+}
+
+// Spine pre-pass: one launch per hierarchy depth of the spine (the few nodes whose subtree does not fit a tile).
+__global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t *__restrict__ slots, uint32_t count)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= count)
+		return;
+	const uint32_t slot = slots[i];
+	const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
+	const Vec3 pos = {a.x, a.y, a.z};
+	const Vec3 scale = {a.w, c.x, c.y};
+	const Quat rot = {b.x, b.y, b.z, b.w};
+	const uint32_t parent = __float_as_uint(c.z);
+	NodeWorld P, W;
+	const bool hasParent = parent != RN_NO_PARENT;
+	if(hasParent)
+		load_world_global(sv, parent, P);
+	compute_world(pos, rot, scale, hasParent, P, W);
+	store_world_global(sv, slot, W);
+}
+
+struct TileSmem
+{
+	float4 *in0, *in1, *in2, *in3;
+	float4 *wpos, *wrot, *m0, *m1, *m2;
+	float2 *wsyz;
+	uint8_t *vis;
+	uint64_t *bar;
+	uint32_t *cnt;
+};
+
+__host__ __device__ inline size_t tile_smem_bytes(uint32_t cap)
+{
+	// 4 input columns + wpos, wrot, m0..m2 (float4) + wsyz (float2) + vis bytes + barrier + counters
+	return (size_t)cap * (9 * 16 + 8) + ((cap + 15) & ~15u) + 16 + RN_MAX_CAMERAS * 4;
+}
+
+__device__ __forceinline__ TileSmem carve_smem(unsigned char *base, uint32_t cap)
+{
+	TileSmem s;
+	float4 *f = reinterpret_cast<float4 *>(base);
+	s.in0 = f; s.in1 = f + cap; s.in2 = f + 2 * cap; s.in3 = f + 3 * cap;
+	s.wpos = f + 4 * cap; s.wrot = f + 5 * cap; s.m0 = f + 6 * cap; s.m1 = f + 7 * cap; s.m2 = f + 8 * cap;
+	s.wsyz = reinterpret_cast<float2 *>(f + 9 * cap);
+	s.vis = reinterpret_cast<uint8_t *>(s.wsyz + cap);
+	s.bar = reinterpret_cast<uint64_t *>(s.vis + ((cap + 15) & ~15u));
+	s.cnt = reinterpret_cast<uint32_t *>(s.bar + 2);
+	return s;
+}
+
+__device__ __forceinline__ void load_world_smem(const TileSmem &s, uint32_t j, NodeWorld &w)
+{
+	const float4 a = s.wpos[j], b = s.wrot[j];
+	const float2 c = s.wsyz[j];
+	const float4 q0 = s.m0[j], q1 = s.m1[j], q2 = s.m2[j];
+	w.wp = {a.x, a.y, a.z};
+	w.wr = {b.x, b.y, b.z, b.w};
+	w.ws = {a.w, c.x, c.y};
+	w.M.m[0] = q0.x; w.M.m[1] = q0.y; w.M.m[2] = q0.z; w.M.m[3] = q0.w;
+	w.M.m[4] = q1.x; w.M.m[5] = q1.y; w.M.m[6] = q1.z; w.M.m[7] = q1.w;
+	w.M.m[8] = q2.x; w.M.m[9] = q2.y; w.M.m[10] = q2.z; w.M.m[11] = q2.w;
+}
+
+__device__ __forceinline__ void store_world_smem(const TileSmem &s, uint32_t j, const NodeWorld &w)
+{
+	s.wpos[j] = make_float4(w.wp.x, w.wp.y, w.wp.z, w.ws.x);
+	s.wrot[j] = make_float4(w.wr.x, w.wr.y, w.wr.z, w.wr.w);
+	s.wsyz[j] = make_float2(w.ws.y, w.ws.z);
+	s.m0[j] = make_float4(w.M.m[0], w.M.m[1], w.M.m[2], w.M.m[3]);
+	s.m1[j] = make_float4(w.M.m[4], w.M.m[5], w.M.m[6], w.M.m[7]);
+	s.m2[j] = make_float4(w.M.m[8], w.M.m[9], w.M.m[10], w.M.m[11]);
+}
+
+// One CTA per tile.  XF: compute world transforms (else read the stored world TRS); CULL: evaluate visibility.
+template <bool XF, bool CULL>
+__global__ void __launch_bounds__(kTileThreads) tile_kernel(SceneView sv, CullParams cp)
+{
+	extern __shared__ __align__(128) unsigned char smem_raw[];
+	const TileSmem s = carve_smem(smem_raw, sv.tile_cap);
+	__shared__ TileMeta meta;
+
+	const uint32_t tile = blockIdx.x;
+	const uint32_t tid = threadIdx.x;
+	if(tid < 16)
+		reinterpret_cast<uint32_t *>(&meta)[tid] = reinterpret_cast<const uint32_t *>(&sv.tiles[tile])[tid];
+	if(tid < RN_MAX_CAMERAS)
+		s.cnt[tid] = 0;
+	if(tid == 0)
+	{
+		mbar_init(s.bar, 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	const uint32_t start = meta.start;
+	const uint32_t count = meta.count;
+
+	// Stage the tile's input columns with TMA bulk copies (one elected thread).
+	if(tid == 0)
+	{
+		const uint32_t bytes = count * 16u;
+		if(XF)
+		{
+			mbar_expect_tx(s.bar, bytes * 4u);
+			bulk_g2s(s.in0, sv.c0 + start, bytes, s.bar);
+			bulk_g2s(s.in1, sv.c1 + start, bytes, s.bar);
+			bulk_g2s(s.in2, sv.c2 + start, bytes, s.bar);
+			bulk_g2s(s.in3, sv.c3 + start, bytes, s.bar);
+		}
+		else
+		{
+			mbar_expect_tx(s.bar, bytes * 4u);
+			bulk_g2s(s.in2, sv.c2 + start, bytes, s.bar);
+			bulk_g2s(s.in3, sv.c3 + start, bytes, s.bar);
+			bulk_g2s(s.wpos, sv.wpos + start, bytes, s.bar);
+			bulk_g2s(s.wrot, sv.wrot + start, bytes, s.bar);
+		}
+	}
+	mbar_wait(s.bar, 0);
+
+	if(XF)
+	{
+		// sublevel 0: spine nodes inside this tile - world transform already in global memory (pre-pass)
+		for(uint32_t j = tid; j < meta.lvl_end[0]; j += kTileThreads)
+		{
+			NodeWorld W;
+			load_world_global(sv, start + j, W);
+			store_world_smem(s, j, W);
+			if(CULL)
+			{
+				const uint32_t fw = __float_as_uint(s.in2[j].w);
+				s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, s.in3[j]);
+			}
+		}
+		__syncthreads();
+		for(uint32_t lev = 1; lev < meta.nlev; lev++)
+		{
+			const uint32_t jend = meta.lvl_end[lev];
+			for(uint32_t j = meta.lvl_end[lev - 1] + tid; j < jend; j += kTileThreads)
+			{
+				const float4 a = s.in0[j], b = s.in1[j], c = s.in2[j];
+				const Vec3 pos = {a.x, a.y, a.z};
+				const Vec3 scale = {a.w, c.x, c.y};
+				const Quat rot = {b.x, b.y, b.z, b.w};
+				const uint32_t parent = __float_as_uint(c.z);
+				const uint32_t fw = __float_as_uint(c.w);
+				NodeWorld P, W;
+				const bool hasParent = parent != RN_NO_PARENT;
+				if(hasParent)
+				{
+					const uint32_t pl = parent - start;
+					if(pl < count)
+						load_world_smem(s, pl, P);
+					else
+						load_world_global(sv, parent, P);
+				}
+				compute_world(pos, rot, scale, hasParent, P, W);
+				store_world_smem(s, j, W);
+				store_world_global(sv, start + j, W);
+				if(CULL)
+					s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, s.in3[j]);
+			}
+			__syncthreads();
+		}
+	}
+	else if(CULL)
+	{
+		for(uint32_t j = tid; j < count; j += kTileThreads)
+		{
+			const float4 a = s.wpos[j], b = s.wrot[j];
+			const float2 c = sv.wsyz[start + j];
+			const uint32_t fw = __float_as_uint(s.in2[j].w);
+			const Vec3 wp = {a.x, a.y, a.z};
+			const Quat wr = {b.x, b.y, b.z, b.w};
+			const Vec3 ws = {a.w, c.x, c.y};
+			s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, wp, wr, ws, s.in3[j]);
+		}
+		__syncthreads();
+	}
+
+	if(CULL)
+	{
+		// visibility bytes in RANK order + per-camera counts of this tile
+		uint32_t local[RN_MAX_CAMERAS];
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			local[c] = 0;
+		for(uint32_t t = tid; t < count; t += kTileThreads)
+		{
+			const uint32_t v = s.vis[t];
+			sv.vis[start + t] = (uint8_t)v;
+#pragma unroll
+			for(int c = 0; c < RN_MAX_CAMERAS; c++)
+				local[c] += (v >> c) & 1u;
+		}
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		{
+			if((uint32_t)c < cp.n)
+			{
+				uint32_t v = local[c];
+#pragma unroll
+				for(int o = 16; o > 0; o >>= 1)
+					v += __shfl_xor_sync(0xffffffffu, v, o);
+				if((tid & 31) == 0 && v)
+					atomicAdd(&s.cnt[c], v);
+			}
+		}
+		__syncthreads();
+		if(tid < cp.n)
+			sv.tile_counts[tid * sv.n_tiles + tile] = s.cnt[tid];
+	}
+}
+
+// Exclusive scan of the per-tile counts, one CTA per camera; also publishes the camera's total.
+__global__ void __launch_bounds__(1024) scan_kernel(const uint32_t *__restrict__ counts, uint32_t *__restrict__ offsets,
+                                                   uint32_t *__restrict__ totals, uint32_t n_tiles)
+{
+	__shared__ uint32_t warp_sums[32];
+	__shared__ uint32_t carry;
+	const uint32_t cam = blockIdx.x;
+	const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	counts += (size_t)cam * n_tiles;
+	offsets += (size_t)cam * n_tiles;
+	if(tid == 0)
+		carry = 0;
+	__syncthreads();
+	for(uint32_t base = 0; base < n_tiles; base += 1024)
+	{
+		const uint32_t i = base + tid;
+		const uint32_t v = i < n_tiles ? counts[i] : 0;
+		uint32_t x = v;
+#pragma unroll
+		for(int o = 1; o < 32; o <<= 1)
+		{
+			const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+			if(lane >= (uint32_t)o)
+				x += y;
+		}
+		if(lane == 31)
+			warp_sums[warp] = x;
+		__syncthreads();
+		if(warp == 0)
+		{
+			uint32_t w = warp_sums[lane];
+#pragma unroll
+			for(int o = 1; o < 32; o <<= 1)
+			{
+				const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+				if(lane >= (uint32_t)o)
+					w += y;
+			}
+			warp_sums[lane] = w; // inclusive
+		}
+		__syncthreads();
+		const uint32_t before = carry + (warp ? warp_sums[warp - 1] : 0) + (x - v);
+		if(i < n_tiles)
+			offsets[i] = before;
+		__syncthreads();
+		if(tid == 1023)
+			carry = before + v;
+		__syncthreads();
+	}
+	if(tid == 0)
+		totals[cam] = carry;
+}
+
+struct EmitView
+{
+	const uint8_t *vis;
+	const uint16_t *lslot;
+	const TileMeta *tiles;
+	const uint32_t *tile_counts;
+	const uint32_t *tile_offsets;
+	uint32_t *lists[RN_MAX_CAMERAS];
+	uint32_t n_tiles;
+	uint32_t n_cams;
+};
+
+// Order-preserving compaction: walks the tile's ranks in order and writes the slots of the visible ones.
+__global__ void __launch_bounds__(256) emit_kernel(EmitView ev)
+{
+	__shared__ uint32_t wtot[RN_MAX_CAMERAS][8];
+	__shared__ uint32_t any;
+	const uint32_t tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	if(tid == 0)
+	{
+		uint32_t a = 0;
+		for(uint32_t c = 0; c < ev.n_cams; c++)
+			a |= ev.tile_counts[c * ev.n_tiles + tile];
+		any = a;
+	}
+	__syncthreads();
+	if(!any)
+		return;
+	const uint32_t start = ev.tiles[tile].start, count = ev.tiles[tile].count;
+	uint32_t run[RN_MAX_CAMERAS];
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		run[c] = (uint32_t)c < ev.n_cams ? ev.tile_offsets[c * ev.n_tiles + tile] : 0;
+	for(uint32_t base = 0; base < count; base += 256)
+	{
+		const uint32_t t = base + tid;
+		uint32_t v = 0, slot = 0;
+		if(t < count)
+		{
+			v = ev.vis[start + t];
+			slot = start + ev.lslot[start + t];
+		}
+		uint32_t before[RN_MAX_CAMERAS];
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		{
+			const uint32_t m = __ballot_sync(0xffffffffu, (v >> c) & 1u);
+			before[c] = __popc(m & ((1u << lane) - 1u));
+			if(lane == 0)
+				wtot[c][warp] = __popc(m);
+		}
+		__syncthreads();
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		{
+			if((uint32_t)c < ev.n_cams)
+			{
+				uint32_t pre = 0, tot = 0;
+#pragma unroll
+				for(int w = 0; w < 8; w++)
+				{
+					const uint32_t x = wtot[c][w];
+					pre += (uint32_t)w < warp ? x : 0;
+					tot += x;
+				}
+				if((v >> c) & 1u)
+					ev.lists[c][run[c] + pre + before[c]] = slot;
+				run[c] += tot;
+			}
+		}
+		__syncthreads();
+	}
+}
+
+// Scatter update of local columns (SetPosition / SetScale / SetRotation / SetFlags ... on a dirty set).
+struct UpdateView
+{
+	float4 *c0, *c1, *c2, *c3;
+	const uint32_t *slots;
+	const float *pos, *scale, *rot, *sphere;
+	const uint32_t *flags, *group;
+	uint32_t count;
+};
+
+__global__ void __launch_bounds__(256) update_kernel(UpdateView u)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= u.count)
+		return;
+	const uint32_t slot = u.slots[i];
+	if(u.pos || u.scale)
+	{
+		float4 a = u.c0[slot];
+		if(u.pos) { a.x = u.pos[i * 3]; a.y = u.pos[i * 3 + 1]; a.z = u.pos[i * 3 + 2]; }
+		if(u.scale) a.w = u.scale[i * 3];
+		u.c0[slot] = a;
+	}
+	if(u.rot)
+		u.c1[slot] = make_float4(u.rot[i * 4], u.rot[i * 4 + 1], u.rot[i * 4 + 2], u.rot[i * 4 + 3]);
+	if(u.scale || u.flags || u.group)
+	{
+		float4 c = u.c2[slot];
+		if(u.scale) { c.x = u.scale[i * 3 + 1]; c.y = u.scale[i * 3 + 2]; }
+		uint32_t fw = __float_as_uint(c.w);
+		if(u.flags) fw = (fw & ~0xffu) | (u.flags[i] & 0xffu);
+		if(u.group) fw = (fw & ~0xff00u) | ((u.group[i] & 0xffu) << 8);
+		c.w = __uint_as_float(fw);
+		u.c2[slot] = c;
+	}
+	if(u.sphere)
+		u.c3[slot] = make_float4(u.sphere[i * 4], u.sphere[i * 4 + 1], u.sphere[i * 4 + 2], u.sphere[i * 4 + 3]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: tiling
+// ---------------------------------------------------------------------------------------------------------------
+struct Tiling
+{
+	std::vector<uint32_t> slot_of_rank, rank_of_slot, depth;
+	std::vector<uint8_t> spine;       // by rank
+	std::vector<uint8_t> sublevel;    // by rank: 0 spine, k>=1 depth inside unit + 1
+	std::vector<TileMeta> tiles;
+	std::vector<uint32_t> spine_slots;      // grouped by depth
+	std::vector<uint32_t> spine_level_ofs;
+	uint32_t max_depth = 0;
+};
+
+// Builds the tiling described in DESIGN.md §3.  O(n) time and memory; returns false on an invalid hierarchy.
+static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tiling &t)
+{
+	const uint32_t kMaxHeight = kMaxSublevels - 2; // sublevels 1..kMaxSublevels-1 hold depths 0..kMaxHeight
+	t.depth.assign(n, 0);
+	// children CSR
+	std::vector<uint32_t> child_ofs(n + 1, 0);
+	for(uint32_t i = 0; i < n; i++)
+	{
+		if(parent[i] != RN_NO_PARENT)
+		{
+			if(parent[i] >= n || parent[i] == i) { set_error("node %u has an invalid parent %u", i, parent[i]); return false; }
+			child_ofs[parent[i] + 1]++;
+		}
+	}
+	for(uint32_t i = 0; i < n; i++) child_ofs[i + 1] += child_ofs[i];
+	std::vector<uint32_t> child(child_ofs[n]);
+	{
+		std::vector<uint32_t> fill(child_ofs.begin(), child_ofs.end() - 1);
+		for(uint32_t i = 0; i < n; i++)
+			if(parent[i] != RN_NO_PARENT) child[fill[parent[i]]++] = i;
+	}
+	// BFS order from the roots
+	std::vector<uint32_t> bfs;
+	bfs.reserve(n);
+	for(uint32_t i = 0; i < n; i++)
+		if(parent[i] == RN_NO_PARENT) bfs.push_back(i);
+	for(size_t h = 0; h < bfs.size(); h++)
+	{
+		const uint32_t u = bfs[h];
+		for(uint32_t k = child_ofs[u]; k < child_ofs[u + 1]; k++)
+		{
+			t.depth[child[k]] = t.depth[u] + 1;
+			bfs.push_back(child[k]);
+		}
+	}
+	if(bfs.size() != n) { set_error("the parent column contains a cycle"); return false; }
+
+	// subtree extent / size / height, children before parents
+	std::vector<uint32_t> lo(n), hi(n), size(n, 1), height(n, 0);
+	for(uint32_t i = 0; i < n; i++) lo[i] = hi[i] = i;
+	for(size_t h = n; h-- > 0;)
+	{
+		const uint32_t u = bfs[h];
+		const uint32_t p = parent[u];
+		if(p != RN_NO_PARENT)
+		{
+			lo[p] = std::min(lo[p], lo[u]);
+			hi[p] = std::max(hi[p], hi[u]);
+			size[p] += size[u];
+			height[p] = std::max(height[p], height[u] + 1);
+		}
+	}
+	// covered = inside a compact subtree (contiguous rank range, fits a tile); the rest is the spine
+	std::vector<uint32_t> unit_root(n, RN_NO_PARENT);
+	t.spine.assign(n, 0);
+	t.sublevel.assign(n, 0);
+	t.max_depth = 0;
+	for(size_t h = 0; h < n; h++)
+	{
+		const uint32_t u = bfs[h];
+		const uint32_t p = parent[u];
+		t.max_depth = std::max(t.max_depth, t.depth[u]);
+		if(p != RN_NO_PARENT && unit_root[p] != RN_NO_PARENT)
+			unit_root[u] = unit_root[p];
+		else if(hi[u] - lo[u] + 1 == size[u] && size[u] <= cap && height[u] <= kMaxHeight)
+			unit_root[u] = u;
+		if(unit_root[u] == RN_NO_PARENT)
+			t.spine[u] = 1;
+		else
+			t.sublevel[u] = (uint8_t)(t.depth[u] - t.depth[unit_root[u]] + 1);
+	}
+	// greedy packing of units (a spine rank or the rank range of a compact subtree) into tiles
+	t.tiles.clear();
+	t.slot_of_rank.assign(n, 0);
+	t.rank_of_slot.assign(n, 0);
+	uint32_t r = 0;
+	while(r < n)
+	{
+		const uint32_t a = r;
+		uint32_t b = r;
+		while(b < n)
+		{
+			uint32_t ue;
+			if(t.spine[b])
+				ue = b + 1;
+			else
+			{
+				const uint32_t root = unit_root[b];
+				if(lo[root] != b) { set_error("internal tiling error at rank %u", b); return false; }
+				ue = hi[root] + 1;
+			}
+			if(ue - a > cap)
+				break;
+			b = ue;
+		}
+		if(b == a) { set_error("internal tiling error: empty tile at rank %u", a); return false; }
+		TileMeta tm;
+		memset(&tm, 0, sizeof(tm));
+		tm.start = a;
+		tm.count = (uint16_t)(b - a);
+		// counting sort of the tile's ranks by sublevel (stable in rank)
+		uint32_t hist[kMaxSublevels + 1] = {0};
+		uint32_t nlev = 1;
+		for(uint32_t x = a; x < b; x++)
+		{
+			hist[t.sublevel[x] + 1]++;
+			nlev = std::max<uint32_t>(nlev, t.sublevel[x] + 1u);
+		}
+		for(uint32_t k = 0; k < kMaxSublevels; k++) hist[k + 1] += hist[k];
+		for(uint32_t k = 0; k < kMaxSublevels; k++) tm.lvl_end[k] = (uint16_t)hist[k + 1];
+		tm.nlev = (uint16_t)nlev;
+		for(uint32_t x = a; x < b; x++)
+		{
+			const uint32_t slot = a + hist[t.sublevel[x]]++;
+			t.slot_of_rank[x] = slot;
+			t.rank_of_slot[slot] = x;
+		}
+		t.tiles.push_back(tm);
+		r = b;
+	}
+	// spine slots grouped by depth
+	std::vector<uint32_t> per_depth(t.max_depth + 2, 0);
+	uint32_t spine_max_depth = 0;
+	bool any_spine = false;
+	for(uint32_t i = 0; i < n; i++)
+		if(t.spine[i]) { per_depth[t.depth[i] + 1]++; spine_max_depth = std::max(spine_max_depth, t.depth[i]); any_spine = true; }
+	const uint32_t levels = any_spine ? spine_max_depth + 1 : 0;
+	t.spine_level_ofs.assign(levels + 1, 0);
+	for(uint32_t d = 0; d < levels; d++) t.spine_level_ofs[d + 1] = t.spine_level_ofs[d] + per_depth[d + 1];
+	t.spine_slots.assign(t.spine_level_ofs[levels], 0);
+	{
+		std::vector<uint32_t> fill(t.spine_level_ofs.begin(), t.spine_level_ofs.end());
+		for(uint32_t slot = 0; slot < n; slot++)
+		{
+			const uint32_t rk = t.rank_of_slot[slot];
+			if(t.spine[rk]) t.spine_slots[fill[t.depth[rk]]++] = slot;
+		}
+	}
+	return true;
+}
+
+template <class T>
+static int dev_alloc(rn_scene *s, T **p, size_t count)
+{
+	*p = nullptr;
+	if(count == 0) count = 1;
+	RN_CUDA(cudaMalloc(reinterpret_cast<void **>(p), count * sizeof(T)));
+	s->device_bytes += count * sizeof(T);
+	return RN_OK;
+}
+
+static void free_nodes(rn_scene *s)
+{
+	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->lrank, s->lslot, s->vis, s->tiles,
+	                s->tile_counts, s->tile_offsets, s->list_counts, s->spine_slots, s->scratch_idx, s->scratch_cols};
+	for(void *p : ptrs)
+		if(p) cudaFree(p);
+	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		if(s->lists[c]) { cudaFree(s->lists[c]); s->lists[c] = nullptr; }
+	s->c0 = s->c1 = s->c2 = s->c3 = s->wpos = s->wrot = s->wmat = nullptr;
+	s->wsyz = nullptr; s->lrank = s->lslot = nullptr; s->vis = nullptr; s->tiles = nullptr;
+	s->tile_counts = s->tile_offsets = s->list_counts = s->spine_slots = s->scratch_idx = nullptr;
+	s->scratch_cols = nullptr;
+}
+
+static SceneView make_view(const rn_scene *s)
+{
+	SceneView v;
+	v.c0 = s->c0; v.c1 = s->c1; v.c2 = s->c2; v.c3 = s->c3;
+	v.wpos = s->wpos; v.wrot = s->wrot; v.wsyz = s->wsyz; v.wmat = s->wmat;
+	v.vis = s->vis; v.tiles = s->tiles; v.tile_counts = s->tile_counts;
+	v.n_tiles = s->n_tiles; v.tile_cap = s->tile_cap;
+	return v;
+}
+
+static int ensure_lists(rn_scene *s, uint32_t ncams)
+{
+	for(uint32_t c = 0; c < ncams; c++)
+	{
+		if(!s->lists[c])
+		{
+			int rc = dev_alloc(s, &s->lists[c], s->desc.max_nodes);
+			if(rc) return rc;
+		}
+	}
+	return RN_OK;
+}
+
+static int launch_spine(rn_scene *s, cudaStream_t stream)
+{
+	const SceneView v = make_view(s);
+	for(size_t d = 0; d + 1 < s->spine_level_ofs.size(); d++)
+	{
+		const uint32_t cnt = s->spine_level_ofs[d + 1] - s->spine_level_ofs[d];
+		if(!cnt) continue;
+		spine_kernel<<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots + s->spine_level_ofs[d], cnt);
+		s->launches++;
+	}
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
+template <bool XF, bool CULL>
+static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
+{
+	const size_t smem = tile_smem_bytes(s->tile_cap);
+	static bool configured = false;
+	if(!configured)
+	{
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<XF, CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+		configured = true;
+	}
+	tile_kernel<XF, CULL><<<s->n_tiles, kTileThreads, smem, stream>>>(make_view(s), cp);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
+static int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
+{
+	scan_kernel<<<ncams, 1024, 0, stream>>>(s->tile_counts, s->tile_offsets, s->list_counts, s->n_tiles);
+	EmitView ev;
+	ev.vis = s->vis; ev.lslot = s->lslot; ev.tiles = s->tiles;
+	ev.tile_counts = s->tile_counts; ev.tile_offsets = s->tile_offsets;
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) ev.lists[c] = s->lists[c];
+	ev.n_tiles = s->n_tiles; ev.n_cams = ncams;
+	emit_kernel<<<s->n_tiles, 256, 0, stream>>>(ev);
+	s->launches += 2;
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
+static int fill_cull_params(const rn_camera_frustum *cams, uint32_t ncams, CullParams &cp)
+{
+	RN_REQUIRE(cams != nullptr, RN_ERR_INVALID, "cameras is NULL");
+	RN_REQUIRE(ncams >= 1 && ncams <= RN_MAX_CAMERAS, RN_ERR_INVALID, "n_cameras must be 1..%d, got %u", RN_MAX_CAMERAS, ncams);
+	memset(&cp, 0, sizeof(cp));
+	memcpy(cp.cam, cams, sizeof(rn_camera_frustum) * ncams);
+	cp.n = ncams;
+	return RN_OK;
+}
+
+static void fill_lists(rn_scene *s, uint32_t ncams, rn_vis_list *out)
+{
+	if(!out) return;
+	for(uint32_t c = 0; c < ncams; c++)
+	{
+		out[c].slots = s->lists[c];
+		out[c].count = s->list_counts + c;
+		out[c].capacity = s->desc.max_nodes;
+		out[c].reserved = 0;
+	}
+}
+
+} // namespace rn
+
+using namespace rn;
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" const char *rn_last_error(void) { return g_error; }
+extern "C" int rn_abi_version(void) { return RN_ABI_VERSION; }
+
+extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
+{
+	RN_REQUIRE(out && desc, RN_ERR_INVALID, "rn_scene_create: NULL argument");
+	*out = nullptr;
+	RN_REQUIRE(desc->max_nodes > 0, RN_ERR_INVALID, "max_nodes must be > 0");
+	uint32_t cap = desc->tile_nodes ? desc->tile_nodes : 512;
+	RN_REQUIRE(cap >= 64 && cap <= 1024 && (cap % 16) == 0, RN_ERR_INVALID, "tile_nodes must be a multiple of 16 in 64..1024, got %u", cap);
+	RN_REQUIRE(desc->max_particles_per_emitter < 16383, RN_ERR_INVALID,
+	           "max_particles_per_emitter must be < 16383 (reference: RNParticleEmitter.cpp:115)");
+	int ndev = 0;
+	RN_CUDA(cudaGetDeviceCount(&ndev));
+	RN_REQUIRE(desc->device >= 0 && desc->device < ndev, RN_ERR_CUDA, "CUDA device %d not available (%d devices)", desc->device, ndev);
+	RN_CUDA(cudaSetDevice(desc->device));
+	cudaDeviceProp prop;
+	RN_CUDA(cudaGetDeviceProperties(&prop, desc->device));
+	RN_REQUIRE(prop.major >= 9, RN_ERR_CUDA, "device %d is sm_%d%d; librn_cuda is built for sm_100a only", desc->device, prop.major, prop.minor);
+	rn_scene *s = new(std::nothrow) rn_scene();
+	RN_REQUIRE(s, RN_ERR_NOMEM, "out of host memory");
+	s->desc = *desc;
+	s->device = desc->device;
+	s->tile_cap = cap;
+	const size_t n = desc->max_nodes;
+	int rc = RN_OK;
+	if(!rc) rc = dev_alloc(s, &s->c0, n);
+	if(!rc) rc = dev_alloc(s, &s->c1, n);
+	if(!rc) rc = dev_alloc(s, &s->c2, n);
+	if(!rc) rc = dev_alloc(s, &s->c3, n);
+	if(!rc) rc = dev_alloc(s, &s->wpos, n);
+	if(!rc) rc = dev_alloc(s, &s->wrot, n);
+	if(!rc) rc = dev_alloc(s, &s->wsyz, n);
+	if(!rc) rc = dev_alloc(s, &s->wmat, n * 4);
+	if(!rc) rc = dev_alloc(s, &s->lslot, n);
+	if(!rc) rc = dev_alloc(s, &s->vis, n);
+	if(!rc) rc = dev_alloc(s, &s->list_counts, (size_t)RN_MAX_CAMERAS);
+	if(!rc) rc = dev_alloc(s, &s->spine_slots, n);
+	if(rc)
+	{
+		free_nodes(s);
+		delete s;
+		return rc;
+	}
+	cudaMemset(s->list_counts, 0, sizeof(uint32_t) * RN_MAX_CAMERAS);
+	*out = s;
+	return RN_OK;
+}
+
+extern "C" void rn_scene_destroy(rn_scene_t *s)
+{
+	if(!s) return;
+	cudaSetDevice(s->device);
+	cudaDeviceSynchronize();
+	particles_destroy(s);
+	free_nodes(s);
+	delete s;
+}
+
+extern "C" int rn_scene_node_count(const rn_scene_t *s, uint32_t *out_count)
+{
+	RN_REQUIRE(s && out_count, RN_ERR_INVALID, "NULL argument");
+	*out_count = s->n;
+	return RN_OK;
+}
+
+static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
+{
+	RN_REQUIRE(cols->position && cols->scale && cols->rotation && cols->parent && cols->flags && cols->render_group && cols->bounding_sphere,
+	           RN_ERR_INVALID, "a full upload needs every column");
+	RN_REQUIRE(count <= s->desc.max_nodes, RN_ERR_CAPACITY, "%u nodes exceed max_nodes %u", count, s->desc.max_nodes);
+	Tiling t;
+	if(!build_tiling(count, cols->parent, s->tile_cap, t))
+		return RN_ERR_INVALID;
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+
+	// pack the columns in slot order
+	std::vector<float4> h0(count), h1(count), h2(count), h3(count);
+	std::vector<uint16_t> hlslot(count);
+	for(const TileMeta &tm : t.tiles)
+	{
+		for(uint32_t j = 0; j < tm.count; j++)
+		{
+			const uint32_t slot = tm.start + j;
+			const uint32_t r = t.rank_of_slot[slot];
+			const float *p = cols->position + (size_t)r * 3, *sc = cols->scale + (size_t)r * 3, *q = cols->rotation + (size_t)r * 4,
+			            *sp = cols->bounding_sphere + (size_t)r * 4;
+			const uint32_t pr = cols->parent[r];
+			const uint32_t pslot = pr == RN_NO_PARENT ? RN_NO_PARENT : t.slot_of_rank[pr];
+			uint32_t fw = (cols->flags[r] & 0xffu) | ((cols->render_group[r] & 0xffu) << 8) | ((r - tm.start) << kLRankShift);
+			if(t.spine[r]) fw |= kFlagSpine;
+			uint32_t pbits = pslot;
+			float pf, ff;
+			memcpy(&pf, &pbits, 4);
+			memcpy(&ff, &fw, 4);
+			h0[slot] = make_float4(p[0], p[1], p[2], sc[0]);
+			h1[slot] = make_float4(q[0], q[1], q[2], q[3]);
+			h2[slot] = make_float4(sc[1], sc[2], pf, ff);
+			h3[slot] = make_float4(sp[0], sp[1], sp[2], sp[3]);
+			hlslot[r] = (uint16_t)(slot - tm.start);
+		}
+	}
+	RN_CUDA(cudaMemcpy(s->c0, h0.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c1, h1.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c2, h2.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c3, h3.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->lslot, hlslot.data(), sizeof(uint16_t) * count, cudaMemcpyHostToDevice));
+	if(!t.spine_slots.empty())
+		RN_CUDA(cudaMemcpy(s->spine_slots, t.spine_slots.data(), sizeof(uint32_t) * t.spine_slots.size(), cudaMemcpyHostToDevice));
+
+	// per-tile arrays
+	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
+	if(s->tile_counts) { cudaFree(s->tile_counts); s->tile_counts = nullptr; }
+	if(s->tile_offsets) { cudaFree(s->tile_offsets); s->tile_offsets = nullptr; }
+	const size_t nt = t.tiles.size();
+	int rc = dev_alloc(s, &s->tiles, nt);
+	if(!rc) rc = dev_alloc(s, &s->tile_counts, nt * RN_MAX_CAMERAS);
+	if(!rc) rc = dev_alloc(s, &s->tile_offsets, nt * RN_MAX_CAMERAS);
+	if(rc) return rc;
+	if(nt) RN_CUDA(cudaMemcpy(s->tiles, t.tiles.data(), sizeof(TileMeta) * nt, cudaMemcpyHostToDevice));
+
+	s->n = count;
+	s->n_tiles = (uint32_t)nt;
+	s->max_depth = t.max_depth;
+	s->spine_nodes = (uint32_t)t.spine_slots.size();
+	s->spine_level_ofs = t.spine_level_ofs;
+	s->slot_of_rank.swap(t.slot_of_rank);
+	s->rank_of_slot.swap(t.rank_of_slot);
+	s->have_world = false;
+	s->last_ncams = 0;
+	return RN_OK;
+}
+
+static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t first, uint32_t count)
+{
+	RN_REQUIRE(cols->parent == nullptr, RN_ERR_INVALID, "the hierarchy can only change through a full upload");
+	if(count == 0) return RN_OK;
+	RN_CUDA(cudaSetDevice(s->device));
+	// staging layout: slots | pos | scale | rot | sphere | flags | group  (only the present ones)
+	const size_t words = (size_t)count * (1 + 3 + 3 + 4 + 4 + 1 + 1);
+	if(s->scratch_cap < count)
+	{
+		if(s->scratch_cols) { cudaFree(s->scratch_cols); s->scratch_cols = nullptr; }
+		int rc = dev_alloc(s, &s->scratch_cols, words);
+		if(rc) return rc;
+		s->scratch_cap = count;
+	}
+	std::vector<uint32_t> slots(count);
+	for(uint32_t i = 0; i < count; i++)
+	{
+		const uint32_t r = ranks ? ranks[i] : first + i;
+		RN_REQUIRE(r < s->n, RN_ERR_INVALID, "rank %u out of range (%u nodes)", r, s->n);
+		slots[i] = s->slot_of_rank[r];
+	}
+	float *d = s->scratch_cols;
+	UpdateView u;
+	memset(&u, 0, sizeof(u));
+	u.c0 = s->c0; u.c1 = s->c1; u.c2 = s->c2; u.c3 = s->c3;
+	u.count = count;
+	RN_CUDA(cudaMemcpy(d, slots.data(), sizeof(uint32_t) * count, cudaMemcpyHostToDevice));
+	u.slots = reinterpret_cast<const uint32_t *>(d); d += count;
+	if(cols->position) { RN_CUDA(cudaMemcpy(d, cols->position, sizeof(float) * 3 * count, cudaMemcpyHostToDevice)); u.pos = d; }
+	d += (size_t)count * 3;
+	if(cols->scale) { RN_CUDA(cudaMemcpy(d, cols->scale, sizeof(float) * 3 * count, cudaMemcpyHostToDevice)); u.scale = d; }
+	d += (size_t)count * 3;
+	if(cols->rotation) { RN_CUDA(cudaMemcpy(d, cols->rotation, sizeof(float) * 4 * count, cudaMemcpyHostToDevice)); u.rot = d; }
+	d += (size_t)count * 4;
+	if(cols->bounding_sphere) { RN_CUDA(cudaMemcpy(d, cols->bounding_sphere, sizeof(float) * 4 * count, cudaMemcpyHostToDevice)); u.sphere = d; }
+	d += (size_t)count * 4;
+	if(cols->flags) { RN_CUDA(cudaMemcpy(d, cols->flags, sizeof(uint32_t) * count, cudaMemcpyHostToDevice)); u.flags = reinterpret_cast<const uint32_t *>(d); }
+	d += count;
+	if(cols->render_group) { RN_CUDA(cudaMemcpy(d, cols->render_group, sizeof(uint32_t) * count, cudaMemcpyHostToDevice)); u.group = reinterpret_cast<const uint32_t *>(d); }
+	update_kernel<<<(count + 255) / 256, 256>>>(u);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	s->have_world = false;
+	return RN_OK;
+}
+
+extern "C" int rn_scene_upload(rn_scene_t *s, const rn_node_columns *cols, uint32_t first, uint32_t count)
+{
+	RN_REQUIRE(s && cols, RN_ERR_INVALID, "NULL argument");
+	if(cols->parent)
+	{
+		RN_REQUIRE(first == 0, RN_ERR_INVALID, "a full upload (parent column given) must start at rank 0");
+		return upload_full(s, cols, count);
+	}
+	RN_REQUIRE((uint64_t)first + count <= s->n, RN_ERR_INVALID, "range [%u, %u) exceeds the %u uploaded nodes", first, first + count, s->n);
+	return update_scattered(s, cols, nullptr, first, count);
+}
+
+extern "C" int rn_scene_update_nodes(rn_scene_t *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count)
+{
+	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
+	return update_scattered(s, cols, ranks, 0, count);
+}
+
+extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	int rc = launch_spine(s, stream);
+	if(rc) return rc;
+	CullParams cp;
+	memset(&cp, 0, sizeof(cp));
+	rc = launch_tiles<true, false>(s, cp, stream);
+	if(rc) return rc;
+	s->have_world = true;
+	return RN_OK;
+}
+
+extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists, void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
+	RN_REQUIRE(s->have_world, RN_ERR_STATE, "rn_cull needs world transforms: call rn_transform_propagate first (or rn_transform_cull)");
+	CullParams cp;
+	int rc = fill_cull_params(cameras, n_cameras, cp);
+	if(rc) return rc;
+	RN_CUDA(cudaSetDevice(s->device));
+	rc = ensure_lists(s, n_cameras);
+	if(rc) return rc;
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	rc = launch_tiles<false, true>(s, cp, stream);
+	if(!rc) rc = launch_compaction(s, n_cameras, stream);
+	if(rc) return rc;
+	s->last_ncams = n_cameras;
+	fill_lists(s, n_cameras, out_lists);
+	return RN_OK;
+}
+
+extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists,
+                                 void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
+	CullParams cp;
+	int rc = fill_cull_params(cameras, n_cameras, cp);
+	if(rc) return rc;
+	RN_CUDA(cudaSetDevice(s->device));
+	rc = ensure_lists(s, n_cameras);
+	if(rc) return rc;
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	rc = launch_spine(s, stream);
+	if(!rc) rc = launch_tiles<true, true>(s, cp, stream);
+	if(!rc) rc = launch_compaction(s, n_cameras, stream);
+	if(rc) return rc;
+	s->have_world = true;
+	s->last_ncams = n_cameras;
+	fill_lists(s, n_cameras, out_lists);
+	return RN_OK;
+}
+
+extern "C" int rn_cull_read_counts(rn_scene_t *s, uint32_t *out_counts, uint32_t n_cameras, void *cuda_stream)
+{
+	RN_REQUIRE(s && out_counts, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(n_cameras <= s->last_ncams, RN_ERR_STATE, "the last cull had %u cameras, %u requested", s->last_ncams, n_cameras);
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	RN_CUDA(cudaMemcpyAsync(out_counts, s->list_counts, sizeof(uint32_t) * n_cameras, cudaMemcpyDeviceToHost, stream));
+	RN_CUDA(cudaStreamSynchronize(stream));
+	return RN_OK;
+}
+
+extern "C" int rn_cull_read_list(rn_scene_t *s, uint32_t camera, uint32_t *out_slots, uint32_t capacity, uint32_t *out_count,
+                                 void *cuda_stream)
+{
+	RN_REQUIRE(s && out_count, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(camera < s->last_ncams, RN_ERR_STATE, "camera %u was not part of the last cull (%u cameras)", camera, s->last_ncams);
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	uint32_t cnt = 0;
+	RN_CUDA(cudaMemcpyAsync(&cnt, s->list_counts + camera, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+	RN_CUDA(cudaStreamSynchronize(stream));
+	*out_count = cnt;
+	if(out_slots)
+	{
+		RN_REQUIRE(cnt <= capacity, RN_ERR_CAPACITY, "list of camera %u has %u entries, buffer holds %u", camera, cnt, capacity);
+		if(cnt)
+		{
+			RN_CUDA(cudaMemcpyAsync(out_slots, s->lists[camera], sizeof(uint32_t) * cnt, cudaMemcpyDeviceToHost, stream));
+			RN_CUDA(cudaStreamSynchronize(stream));
+		}
+	}
+	return RN_OK;
+}
+
+extern "C" int rn_scene_download(rn_scene_t *s, rn_download_what what, uint32_t first, uint32_t count, void *dst)
+{
+	RN_REQUIRE(s && dst, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE((uint64_t)first + count <= s->n, RN_ERR_INVALID, "range [%u, %u) exceeds the %u uploaded nodes", first, first + count, s->n);
+	if(count == 0) return RN_OK;
+	if(what == RN_DL_SLOT_OF_RANK)
+	{
+		memcpy(dst, s->slot_of_rank.data() + first, sizeof(uint32_t) * count);
+		return RN_OK;
+	}
+	if(what == RN_DL_RANK_OF_SLOT)
+	{
+		memcpy(dst, s->rank_of_slot.data() + first, sizeof(uint32_t) * count);
+		return RN_OK;
+	}
+	RN_REQUIRE(s->have_world, RN_ERR_STATE, "no world transforms yet: call rn_transform_propagate / rn_transform_cull first");
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	uint32_t slo = 0xffffffffu, shi = 0;
+	for(uint32_t r = first; r < first + count; r++)
+	{
+		slo = std::min(slo, s->slot_of_rank[r]);
+		shi = std::max(shi, s->slot_of_rank[r]);
+	}
+	const size_t span = (size_t)shi - slo + 1;
+	float *out = static_cast<float *>(dst);
+	switch(what)
+	{
+		case RN_DL_WORLD_POSITION:
+		case RN_DL_WORLD_SCALE:
+		{
+			std::vector<float4> a(span);
+			std::vector<float2> b(span);
+			RN_CUDA(cudaMemcpy(a.data(), s->wpos + slo, sizeof(float4) * span, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(b.data(), s->wsyz + slo, sizeof(float2) * span, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < count; i++)
+			{
+				const size_t k = s->slot_of_rank[first + i] - slo;
+				if(what == RN_DL_WORLD_POSITION) { out[i * 3] = a[k].x; out[i * 3 + 1] = a[k].y; out[i * 3 + 2] = a[k].z; }
+				else { out[i * 3] = a[k].w; out[i * 3 + 1] = b[k].x; out[i * 3 + 2] = b[k].y; }
+			}
+			break;
+		}
+		case RN_DL_WORLD_ROTATION:
+		{
+			std::vector<float4> a(span);
+			RN_CUDA(cudaMemcpy(a.data(), s->wrot + slo, sizeof(float4) * span, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < count; i++)
+			{
+				const size_t k = s->slot_of_rank[first + i] - slo;
+				out[i * 4] = a[k].x; out[i * 4 + 1] = a[k].y; out[i * 4 + 2] = a[k].z; out[i * 4 + 3] = a[k].w;
+			}
+			break;
+		}
+		case RN_DL_WORLD_MATRIX:
+		{
+			std::vector<float4> a(span * 4);
+			RN_CUDA(cudaMemcpy(a.data(), s->wmat + (size_t)slo * 4, sizeof(float4) * span * 4, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < count; i++)
+			{
+				const size_t k = s->slot_of_rank[first + i] - slo;
+				memcpy(out + (size_t)i * 16, &a[k * 4], 64);
+			}
+			break;
+		}
+		default:
+			RN_REQUIRE(false, RN_ERR_INVALID, "unknown download selector %d", (int)what);
+	}
+	return RN_OK;
+}
+
+extern "C" int rn_scene_device_outputs(rn_scene_t *s, const float **world_matrix, const float **world_pos_sx, const float **world_rot,
+                                       const float **world_scale_yz)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	if(world_matrix) *world_matrix = reinterpret_cast<const float *>(s->wmat);
+	if(world_pos_sx) *world_pos_sx = reinterpret_cast<const float *>(s->wpos);
+	if(world_rot) *world_rot = reinterpret_cast<const float *>(s->wrot);
+	if(world_scale_yz) *world_scale_yz = reinterpret_cast<const float *>(s->wsyz);
+	return RN_OK;
+}
+
+extern "C" int rn_scene_get_stats(const rn_scene_t *s, rn_scene_stats *out)
+{
+	RN_REQUIRE(s && out, RN_ERR_INVALID, "NULL argument");
+	out->nodes = s->n;
+	out->tiles = s->n_tiles;
+	out->spine_nodes = s->spine_nodes;
+	out->spine_levels = s->spine_level_ofs.empty() ? 0 : (uint32_t)s->spine_level_ofs.size() - 1;
+	out->max_depth = s->max_depth;
+	out->tile_nodes = s->tile_cap;
+	out->device_bytes = s->device_bytes;
+	out->kernel_launches = s->launches;
+	return RN_OK;
+}

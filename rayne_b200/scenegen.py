@@ -263,7 +263,7 @@ def six_view_rig(seed: int = 7) -> np.ndarray:
         edges.append(lin * (1.0 - factor) + log * factor)
     for i in range(splits):
         centre = 0.5 * (edges[i] + edges[i + 1])
-        dist = max(0.75 * (edges[i + 1] - edges[i]), 4.0)
+        dist = max(0.75 * (edges[i + 1] - edges[i]), 40.0)
         # light looks down at 50 degrees; camera sits 250 units up-light from the split centre
         cams.append(make_camera(pos=(0.3 * centre, 190.0, -centre + 160.0), euler=(0.0, -50.0, 0.0),
                                 flags=CAM_ORTHOGONAL, near=1.0, far=600.0,
