@@ -1,0 +1,73 @@
+"""Shared helpers for the parity tests: run the CUDA path through the C ABI and compare it with the oracle."""
+from __future__ import annotations
+
+import numpy as np
+
+from oracle import oracle
+from rayne_b200 import capi, scenegen as sg
+
+REL_TOL = 1e-5  # north star: world matrices / particle state within 1e-5 relative fp32
+
+
+def same_floats(a, b) -> bool:
+    """Bit-exact up to the sign of zero (the CUDA path drops the reference's `* 0` terms, see rn_math.cuh)."""
+    a = np.ascontiguousarray(a, np.float32); b = np.ascontiguousarray(b, np.float32)
+    return bool(((a == b) | (a.view(np.uint32) == b.view(np.uint32))).all())
+
+
+def rel_close(a, b, tol=REL_TOL) -> bool:
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    scale = max(1.0, float(np.abs(b).max()) if b.size else 1.0)
+    return bool((np.abs(a - b) <= tol * np.maximum(np.abs(b), 1e-3 * scale)).all())
+
+
+def standard_cameras() -> np.ndarray:
+    return np.stack([
+        sg.make_camera(),
+        sg.make_camera(pos=(10, 5, -3), euler=(30, -20, 10), fov=90, aspect=1.3, near=0.5, far=300,
+                       plane_offsets=(0.1, 0.2, -0.3, 0.05), render_group=3),
+        sg.make_camera(flags=sg.CAM_USE_SIMPLE_CULLING),
+    ] + list(sg.six_view_rig())[:5])
+
+
+def run_cuda(scene: sg.Scene, frustums: np.ndarray, tile_nodes: int = 0, fused: bool = True):
+    """Returns dict with order, world TRS/matrix in CREATION order, lists of creation ids, stats."""
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=max(scene.n, 1), tile_nodes=tile_nodes) as h:
+        h.upload(rs)
+        if fused:
+            h.transform_cull(frustums)
+        else:
+            h.transform_propagate()
+            h.cull(frustums)
+        out = {"order": rs.order}
+        rank_of_slot = h.download(capi.DL_RANK_OF_SLOT)
+        for key, what in (("wpos", capi.DL_WORLD_POSITION), ("wrot", capi.DL_WORLD_ROTATION),
+                          ("wscale", capi.DL_WORLD_SCALE), ("wmat", capi.DL_WORLD_MATRIX)):
+            ranked = h.download(what)
+            full = np.zeros_like(ranked)
+            full[rs.order] = ranked
+            out[key] = full
+        out["counts"] = h.read_counts()
+        out["lists"] = [rs.order[rank_of_slot[h.read_list(c)]] for c in range(len(np.atleast_1d(frustums)))]
+        out["slot_lists_rank"] = [rank_of_slot[h.read_list(c)] for c in range(len(np.atleast_1d(frustums)))]
+        st = h.stats()
+        out["stats"] = {k: getattr(st, k) for k, _ in st._fields_}
+    return out
+
+
+def check_against_oracle(scene: sg.Scene, cameras: np.ndarray, **kw):
+    fr = capi.build_frustums(cameras)
+    assert fr.tobytes() == oracle.frustums(cameras).tobytes()
+    got = run_cuda(scene, fr, **kw)
+    ref = oracle.scene_reference(scene, fr)
+    assert np.array_equal(got["order"], ref["order"])
+    for key in ("wpos", "wrot", "wscale"):
+        assert same_floats(got[key], ref[key]), key
+    assert same_floats(got["wmat"], ref["wmat"]) or rel_close(got["wmat"], ref["wmat"]), "wmat"
+    for c, (a, b) in enumerate(zip(got["lists"], ref["lists"])):
+        assert a.shape == b.shape and np.array_equal(a, b), f"visibility list of camera {c} differs"
+        assert got["counts"][c] == len(b)
+        r = got["slot_lists_rank"][c]
+        assert (np.diff(r.astype(np.int64)) > 0).all(), "list is not in render-list order"
+    return got, ref
