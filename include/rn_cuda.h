@@ -212,6 +212,10 @@ typedef struct rn_scene_stats {
 	uint64_t kernel_launches;         /* kernels launched by this scene since creation */
 } rn_scene_stats;
 int rn_scene_get_stats(const rn_scene_t *scene, rn_scene_stats *out);
+/* Optional in-stream timing of the dominant kernel (the tile kernel) with CUDA events, for the roofline line of
+ * bench.py: enable, run frames, then read the summed duration (ms) and the number of timed launches (resets). */
+int rn_scene_profile(rn_scene_t *scene, int enable);
+int rn_scene_profile_read(rn_scene_t *scene, float *tile_ms_sum, uint32_t *tile_launches);
 
 #ifdef __cplusplus
 }

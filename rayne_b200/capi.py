@@ -25,6 +25,7 @@ EXPORTS = [
     "rn_cull_read_counts", "rn_cull_read_list", "rn_scene_download", "rn_scene_device_outputs",
     "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
     "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
+    "rn_scene_profile", "rn_scene_profile_read",
 ]
 
 
@@ -254,6 +255,14 @@ class SceneHandle:
         st = SceneStats()
         _check(self.lib.rn_scene_get_stats(self._h, C.byref(st)))
         return st
+
+    def profile(self, enable: bool) -> None:
+        _check(self.lib.rn_scene_profile(self._h, int(enable)))
+
+    def profile_read(self) -> tuple[float, int]:
+        ms = C.c_float(); cnt = C.c_uint32()
+        _check(self.lib.rn_scene_profile_read(self._h, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
 
     # ---- particles ----
     def particles_configure(self, emitters: np.ndarray) -> None:

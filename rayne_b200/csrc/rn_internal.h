@@ -74,9 +74,17 @@ struct rn_scene
 	uint32_t list_capacity = 0;
 	uint32_t *spine_slots = nullptr;   // all spine slots grouped by depth
 	std::vector<uint32_t> spine_level_ofs; // host: offsets into spine_slots per depth (size levels+1)
-	uint32_t *scratch_idx = nullptr;   // staging for rn_scene_update_nodes
-	float *scratch_cols = nullptr;
+	uint32_t *scratch_idx = nullptr;   // (unused)
+	float *scratch_cols = nullptr;     // device staging for rn_scene_update_nodes
+	float *scratch_host = nullptr;     // pinned host staging
 	uint32_t scratch_cap = 0;
+	cudaEvent_t scratch_done = nullptr;
+
+	// optional profiling of the tile kernel
+	bool profile = false;
+	static constexpr int kProfileSlots = 256;
+	cudaEvent_t prof_ev[kProfileSlots][2] = {};
+	int prof_used = 0;
 
 	// host mirrors
 	std::vector<uint32_t> slot_of_rank, rank_of_slot;

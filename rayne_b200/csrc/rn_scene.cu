@@ -773,6 +773,11 @@ static void free_nodes(rn_scene *s)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
 		if(s->lists[c]) { cudaFree(s->lists[c]); s->lists[c] = nullptr; }
+	if(s->scratch_host) { cudaFreeHost(s->scratch_host); s->scratch_host = nullptr; }
+	if(s->scratch_done) { cudaEventDestroy(s->scratch_done); s->scratch_done = nullptr; }
+	for(int i = 0; i < rn_scene::kProfileSlots; i++)
+		for(int k = 0; k < 2; k++)
+			if(s->prof_ev[i][k]) { cudaEventDestroy(s->prof_ev[i][k]); s->prof_ev[i][k] = nullptr; }
 	s->c0 = s->c1 = s->c2 = s->c3 = s->wpos = s->wrot = s->wmat = nullptr;
 	s->wsyz = nullptr; s->lrank = s->lslot = nullptr; s->vis = nullptr; s->tiles = nullptr;
 	s->tile_counts = s->tile_offsets = s->list_counts = s->spine_slots = s->scratch_idx = nullptr;
@@ -826,8 +831,23 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 		RN_CUDA(cudaFuncSetAttribute(tile_kernel<XF, CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
 		configured = true;
 	}
+	const bool prof = s->profile && s->prof_used < rn_scene::kProfileSlots;
+	if(prof)
+	{
+		if(!s->prof_ev[s->prof_used][0])
+		{
+			RN_CUDA(cudaEventCreate(&s->prof_ev[s->prof_used][0]));
+			RN_CUDA(cudaEventCreate(&s->prof_ev[s->prof_used][1]));
+		}
+		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][0], stream));
+	}
 	tile_kernel<XF, CULL><<<s->n_tiles, kTileThreads, smem, stream>>>(make_view(s), cp);
 	s->launches++;
+	if(prof)
+	{
+		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][1], stream));
+		s->prof_used++;
+	}
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
@@ -1014,40 +1034,56 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 	RN_REQUIRE(cols->parent == nullptr, RN_ERR_INVALID, "the hierarchy can only change through a full upload");
 	if(count == 0) return RN_OK;
 	RN_CUDA(cudaSetDevice(s->device));
-	// staging layout: slots | pos | scale | rot | sphere | flags | group  (only the present ones)
-	const size_t words = (size_t)count * (1 + 3 + 3 + 4 + 4 + 1 + 1);
+	// staging layout (words): slots | pos | scale | rot | sphere | flags | group ; packed into ONE pinned buffer
+	// and moved with ONE async copy on the legacy default stream, followed by the scatter kernel.
+	const size_t per = 1 + 3 + 3 + 4 + 4 + 1 + 1;
 	if(s->scratch_cap < count)
 	{
+		if(s->scratch_done) RN_CUDA(cudaEventSynchronize(s->scratch_done));
 		if(s->scratch_cols) { cudaFree(s->scratch_cols); s->scratch_cols = nullptr; }
-		int rc = dev_alloc(s, &s->scratch_cols, words);
+		if(s->scratch_host) { cudaFreeHost(s->scratch_host); s->scratch_host = nullptr; }
+		const uint32_t cap = std::max<uint32_t>(count, 1024);
+		int rc = dev_alloc(s, &s->scratch_cols, per * cap);
 		if(rc) return rc;
-		s->scratch_cap = count;
+		RN_CUDA(cudaMallocHost(reinterpret_cast<void **>(&s->scratch_host), per * cap * sizeof(float)));
+		s->scratch_cap = cap;
+		if(!s->scratch_done) RN_CUDA(cudaEventCreateWithFlags(&s->scratch_done, cudaEventDisableTiming));
 	}
-	std::vector<uint32_t> slots(count);
-	for(uint32_t i = 0; i < count; i++)
-	{
-		const uint32_t r = ranks ? ranks[i] : first + i;
-		RN_REQUIRE(r < s->n, RN_ERR_INVALID, "rank %u out of range (%u nodes)", r, s->n);
-		slots[i] = s->slot_of_rank[r];
-	}
+	else if(s->scratch_done)
+		RN_CUDA(cudaEventSynchronize(s->scratch_done)); // the previous copy out of the pinned buffer has finished
+	float *h = s->scratch_host;
 	float *d = s->scratch_cols;
 	UpdateView u;
 	memset(&u, 0, sizeof(u));
 	u.c0 = s->c0; u.c1 = s->c1; u.c2 = s->c2; u.c3 = s->c3;
 	u.count = count;
-	RN_CUDA(cudaMemcpy(d, slots.data(), sizeof(uint32_t) * count, cudaMemcpyHostToDevice));
-	u.slots = reinterpret_cast<const uint32_t *>(d); d += count;
-	if(cols->position) { RN_CUDA(cudaMemcpy(d, cols->position, sizeof(float) * 3 * count, cudaMemcpyHostToDevice)); u.pos = d; }
-	d += (size_t)count * 3;
-	if(cols->scale) { RN_CUDA(cudaMemcpy(d, cols->scale, sizeof(float) * 3 * count, cudaMemcpyHostToDevice)); u.scale = d; }
-	d += (size_t)count * 3;
-	if(cols->rotation) { RN_CUDA(cudaMemcpy(d, cols->rotation, sizeof(float) * 4 * count, cudaMemcpyHostToDevice)); u.rot = d; }
-	d += (size_t)count * 4;
-	if(cols->bounding_sphere) { RN_CUDA(cudaMemcpy(d, cols->bounding_sphere, sizeof(float) * 4 * count, cudaMemcpyHostToDevice)); u.sphere = d; }
-	d += (size_t)count * 4;
-	if(cols->flags) { RN_CUDA(cudaMemcpy(d, cols->flags, sizeof(uint32_t) * count, cudaMemcpyHostToDevice)); u.flags = reinterpret_cast<const uint32_t *>(d); }
-	d += count;
-	if(cols->render_group) { RN_CUDA(cudaMemcpy(d, cols->render_group, sizeof(uint32_t) * count, cudaMemcpyHostToDevice)); u.group = reinterpret_cast<const uint32_t *>(d); }
+	uint32_t *hs = reinterpret_cast<uint32_t *>(h);
+	for(uint32_t i = 0; i < count; i++)
+	{
+		const uint32_t r = ranks ? ranks[i] : first + i;
+		RN_REQUIRE(r < s->n, RN_ERR_INVALID, "rank %u out of range (%u nodes)", r, s->n);
+		hs[i] = s->slot_of_rank[r];
+	}
+	size_t ofs = count;
+	u.slots = reinterpret_cast<const uint32_t *>(d);
+	auto stage = [&](const void *src, size_t words) -> const float * {
+		const float *dev = nullptr;
+		if(src)
+		{
+			memcpy(h + ofs, src, words * sizeof(float));
+			dev = d + ofs;
+			ofs += words;
+		}
+		return dev;
+	};
+	u.pos = stage(cols->position, (size_t)count * 3);
+	u.scale = stage(cols->scale, (size_t)count * 3);
+	u.rot = stage(cols->rotation, (size_t)count * 4);
+	u.sphere = stage(cols->bounding_sphere, (size_t)count * 4);
+	u.flags = reinterpret_cast<const uint32_t *>(stage(cols->flags, count));
+	u.group = reinterpret_cast<const uint32_t *>(stage(cols->render_group, count));
+	RN_CUDA(cudaMemcpyAsync(d, h, ofs * sizeof(float), cudaMemcpyHostToDevice, 0));
+	RN_CUDA(cudaEventRecord(s->scratch_done, 0));
 	update_kernel<<<(count + 255) / 256, 256>>>(u);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
@@ -1258,5 +1294,31 @@ extern "C" int rn_scene_get_stats(const rn_scene_t *s, rn_scene_stats *out)
 	out->tile_nodes = s->tile_cap;
 	out->device_bytes = s->device_bytes;
 	out->kernel_launches = s->launches;
+	return RN_OK;
+}
+
+extern "C" int rn_scene_profile(rn_scene_t *s, int enable)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	s->profile = enable != 0;
+	s->prof_used = 0;
+	return RN_OK;
+}
+
+extern "C" int rn_scene_profile_read(rn_scene_t *s, float *tile_ms_sum, uint32_t *tile_launches)
+{
+	RN_REQUIRE(s && tile_ms_sum && tile_launches, RN_ERR_INVALID, "NULL argument");
+	RN_CUDA(cudaSetDevice(s->device));
+	float sum = 0.0f;
+	for(int i = 0; i < s->prof_used; i++)
+	{
+		RN_CUDA(cudaEventSynchronize(s->prof_ev[i][1]));
+		float ms = 0.0f;
+		RN_CUDA(cudaEventElapsedTime(&ms, s->prof_ev[i][0], s->prof_ev[i][1]));
+		sum += ms;
+	}
+	*tile_ms_sum = sum;
+	*tile_launches = (uint32_t)s->prof_used;
+	s->prof_used = 0;
 	return RN_OK;
 }
