@@ -1,0 +1,68 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (oracle/_ref/ref_harness_strict, built by
+oracle/build_ref.sh from /root/reference) on small seeded scenes and emitter sets.
+
+    python -m tests.golden.make_golden
+
+Each fixture stores the inputs (creation-order node columns, camera records, emitter records) and the reference's
+outputs (render-list order, world TRS + matrices, the 28 frustum floats per camera, the per-camera visibility
+lists; per-emitter particle records after K steps).  The reference publishes no golden vectors for this path
+(SURVEY.md §4), so these files - produced by the reference's own code - are the pin of the oracle and of the
+CUDA path on machines where /root/reference does not exist.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from oracle import refio
+from rayne_b200 import scenegen as sg
+from tests.helpers import standard_cameras
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+SCENES = {
+    "scene_uniform": dict(n_trees=3, branching=3, depth=5, seed=101),
+    "scene_nonuniform_groups_prio": dict(n_trees=5, branching=4, depth=5, seed=102, nonuniform_scale=True,
+                                         random_bounds=True, random_groups=True, priorities=True),
+    "scene_ragged": dict(ragged_nodes=1500, depth=8, seed=103, random_bounds=True),
+    "scene_deep_chain": dict(n_trees=2, branching=1, depth=40, seed=104),
+}
+PARTICLES = {
+    "particles_default": (dict(n=3, max_particles=300, spawn_rate=0.004), 240),
+    "particles_varied": (dict(n=4, max_particles=500, spawn_rate=0.0021, vary=True), 90),
+    "particles_burst": (dict(n=2, max_particles=1500, spawn_rate=0.00002), 6),
+}
+SCENE_COLS = ("parent", "pos", "scale", "rot", "flags", "group", "priority", "sphere")
+
+
+def main() -> None:
+    assert refio.have_harness("strict"), "run oracle/build_ref.sh strict first"
+    for name, kw in SCENES.items():
+        scene = sg.make_scene(**kw)
+        cams = standard_cameras()
+        ref = refio.run_scene(scene, cams, options=refio.OPT_INVERSE)
+        out = {f"in_{k}": getattr(scene, k) for k in SCENE_COLS}
+        out["in_cameras"] = cams
+        for k in ("order", "wpos", "wrot", "wscale", "wmat", "winv", "sphere", "frustum", "cam_flags", "cam_group"):
+            out[f"ref_{k}"] = ref[k]
+        for c, lst in enumerate(ref["lists"]):
+            out[f"ref_list{c}"] = lst
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+        print(name, scene.n, [len(l) for l in ref["lists"]])
+    for name, (kw, steps) in PARTICLES.items():
+        kw = dict(kw)
+        em = sg.make_emitters(kw.pop("n"), **kw)
+        if name == "particles_burst":
+            em["life_span"] = (0.05, 0.2)
+        ref = refio.run_particles(em, steps)
+        out = {"in_emitters": em, "in_steps": np.int32(steps), "in_delta": np.float32(1.0 / 60.0)}
+        for k, r in enumerate(ref):
+            out[f"ref_rec{k}"] = r["rec"]
+            out[f"ref_time{k}"] = r["time"]
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+        print(name, [r["count"] for r in ref])
+
+
+if __name__ == "__main__":
+    main()

@@ -1,12 +1,22 @@
 """Shared helpers for the parity tests: run the CUDA path through the C ABI and compare it with the oracle."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from oracle import oracle
 from rayne_b200 import capi, scenegen as sg
 
 REL_TOL = 1e-5  # north star: world matrices / particle state within 1e-5 relative fp32
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_golden_scene(name: str):
+    """(scene, cameras, npz) of a fixture written by tests/golden/make_golden.py (outputs of the reference)."""
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    scene = sg.Scene(**{k: g["in_" + k] for k in ("parent", "pos", "scale", "rot", "flags", "group", "priority", "sphere")})
+    return scene, g["in_cameras"], g
 
 
 def same_floats(a, b) -> bool:

@@ -1,0 +1,122 @@
+"""CPU: the oracle (oracle/rn_oracle.c) against the golden fixtures produced by the unmodified reference
+(tests/golden/make_golden.py), and - where oracle/_ref exists - against the reference harness run live.
+Everything is bit-exact: the oracle and the strict-FP reference build evaluate the same fp32 operation sequence."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle, refio
+from rayne_b200 import scenegen as sg
+from tests.helpers import same_floats, standard_cameras, load_golden_scene, GOLDEN_DIR
+
+SCENE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "scene_*.npz")))
+PARTICLE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "particles_*.npz")))
+
+
+def test_fixtures_present():
+    assert len(SCENE_FIXTURES) >= 4 and len(PARTICLE_FIXTURES) >= 3
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_oracle_scene_matches_golden(name):
+    scene, cams, g = load_golden_scene(name)
+    fr = oracle.frustums(cams)
+    assert np.array_equal(fr["center"], g["ref_frustum"][:, 0:3])
+    assert np.array_equal(fr["radius"], g["ref_frustum"][:, 3])
+    assert np.array_equal(fr["planes"].reshape(-1, 24), g["ref_frustum"][:, 4:28])
+    assert np.array_equal(fr["flags"], g["ref_cam_flags"]) and np.array_equal(fr["render_group"], g["ref_cam_group"])
+    o = oracle.scene_reference(scene, fr)
+    assert np.array_equal(o["order"], g["ref_order"])
+    for k in ("wpos", "wrot", "wscale", "wmat"):
+        assert same_floats(o[k], g["ref_" + k]), k
+    for c in range(len(cams)):
+        assert np.array_equal(o["lists"][c], g[f"ref_list{c}"]), f"camera {c}"
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_oracle_bounding_sphere_matches_golden(name):
+    """SceneNode::GetBoundingSphere (RNSceneNode.cpp:570-588): centre = position + rotated offset, scaled radius."""
+    scene, cams, g = load_golden_scene(name)
+    fr = oracle.frustums(cams)[:1]
+    _, sph = oracle.cull(g["ref_wpos"], g["ref_wrot"], g["ref_wscale"], scene.sphere, scene.flags, scene.group, fr[0],
+                         want_sphere=True)
+    assert same_floats(sph, g["ref_sphere"])
+
+
+@pytest.mark.parametrize("name", PARTICLE_FIXTURES)
+def test_oracle_particles_match_golden(name):
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    em = g["in_emitters"]
+    o = oracle.Emitters(em)
+    o.step(np.float32(g["in_delta"]), int(g["in_steps"]))
+    for k in range(len(em)):
+        rec, t = o.read(k)
+        ref = g[f"ref_rec{k}"]
+        assert rec.shape == ref.shape, (k, rec.shape, ref.shape)
+        assert same_floats(rec[:, :23], ref[:, :23]), f"emitter {k}"
+        assert same_floats(t, g[f"ref_time{k}"])
+
+
+def test_mt_stream_known_answer():
+    """MT19937 with Rayne's Seed (RNRandom.cpp:313-323): _offset = 0, so the first outputs are the tempered
+    seed-initialised words (NOT the standard first outputs of mt19937).  Known answer computed by hand here."""
+    seed = 5489
+    mt = [seed]
+    for k in range(1, 624):
+        mt.append((1812433253 * (mt[-1] ^ (mt[-1] >> 30)) + k) & 0xFFFFFFFF)
+
+    def temper(y):
+        y ^= y >> 11
+        y ^= (y << 7) & 0x9D2C5680
+        y ^= (y << 15) & 0xEFC60000
+        y ^= y >> 18
+        return y & 0x7FFFFFFF
+
+    em = sg.make_emitters(1, max_particles=10, spawn_rate=1.0 / 60.0)
+    em["seed"] = seed
+    em["position_min"] = (0, 0, 0); em["position_max"] = (1, 1, 1)
+    o = oracle.Emitters(em)
+    o.step(np.float32(1.0 / 60.0 + 1e-4), 1)
+    rec, _ = o.read(0)
+    assert rec.shape[0] == 1
+    want = [np.float32(float(temper(mt[i])) * (1.0 / 2147483648.0) * 1.0 + 0.0) for i in range(3)]
+    # the particle was advanced by Update(0): position unchanged by a zero step
+    assert same_floats(rec[0, 0:3], np.array(want, np.float32))
+
+
+@pytest.mark.ref
+@pytest.mark.skipif(not refio.have_harness("strict"), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("kw", [
+    dict(n_trees=10, branching=9, depth=4, seed=12345),
+    dict(n_trees=4, branching=4, depth=7, seed=9, nonuniform_scale=True, random_bounds=True, random_groups=True,
+         priorities=True),
+    dict(ragged_nodes=20000, depth=8, seed=13, random_bounds=True),
+])
+def test_oracle_matches_live_reference(kw):
+    scene = sg.make_scene(**kw)
+    cams = standard_cameras()
+    ref = refio.run_scene(scene, cams)
+    fr = oracle.frustums(cams)
+    assert np.array_equal(fr["planes"].reshape(-1, 24), ref["frustum"][:, 4:28])
+    o = oracle.scene_reference(scene, fr)
+    assert np.array_equal(o["order"], ref["order"])
+    for k in ("wpos", "wrot", "wscale", "wmat"):
+        assert same_floats(o[k], ref[k]), k
+    for a, b in zip(o["lists"], ref["lists"]):
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.ref
+@pytest.mark.skipif(not refio.have_harness("strict"), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_particles_match_live_reference():
+    em = sg.make_emitters(6, max_particles=600, spawn_rate=0.0017, vary=True)
+    ref = refio.run_particles(em, 150)
+    o = oracle.Emitters(em)
+    o.step(np.float32(1.0 / 60.0), 150)
+    for k in range(len(em)):
+        rec, t = o.read(k)
+        assert rec.shape == ref[k]["rec"].shape
+        assert same_floats(rec[:, :23], ref[k]["rec"][:, :23])
+        assert same_floats(t, ref[k]["time"])
