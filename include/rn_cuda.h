@@ -13,7 +13,7 @@
  *   rank : position of a node in the reference's render list (SceneBasic::_renderNodes head -> tail,
  *          Source/Scene/RNSceneBasic.cpp:652-676,683-736).  All host-facing node arrays are in rank order.
  *   slot : storage index inside the library (ranks are permuted inside small tiles so that each hierarchy
- *          level of a tile is contiguous).  Visibility lists hold *slots*, ordered by ascending *rank* - i.e.
+ *          level of a tile is contiguous, parents first).  Visibility lists hold *slots*, ordered by ascending *rank* - i.e.
  *          exactly the order in which SceneBasic::Render would have submitted the nodes.  rn_scene_slot_table
  *          converts between the two.
  */
@@ -57,7 +57,8 @@ typedef struct rn_scene_desc {
 	uint32_t tile_nodes;                 /* nodes per tile (0 = default 512; 64..1024) */
 	uint32_t max_emitters;               /* 0 = no particle storage */
 	uint32_t max_particles_per_emitter;  /* < 16383 (Source/Scene/RNParticleEmitter.cpp:115) */
-	uint32_t reserved[3];
+	uint32_t tile_inner_nodes;           /* nodes WITH children per tile, kept in shared memory (0 = default 96; 16..1024) */
+	uint32_t reserved[2];
 } rn_scene_desc;
 
 /* Host node columns in RANK order.  Replaces the per-object state SceneNode keeps

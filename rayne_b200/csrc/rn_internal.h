@@ -22,18 +22,20 @@ int cuda_fail(cudaError_t err, const char *what, const char *file, int line);
 		if(!(cond)) { rn::set_error(__VA_ARGS__); return (status); }                   \
 	} while(0)
 
-constexpr uint32_t kMaxSublevels = 16;   // sublevel 0 = spine nodes of the tile, 1.. = depth inside a unit
-constexpr uint32_t kTileThreads = 256;
+constexpr uint32_t kMaxSublevels = 12;   // sublevel 0 = spine nodes of the tile, 1.. = depth inside a unit
+constexpr uint32_t kWarpsPerCta = 4;     // tile kernel: one tile per warp
+constexpr uint32_t kTileThreads = kWarpsPerCta * 32;
 
 // One tile = a contiguous range of ranks [start, start+count) stored at the same slots, permuted so that each
-// sublevel is contiguous.  64 bytes.
+// sublevel is contiguous and, inside a sublevel, the inner nodes (nodes with children) come first.  64 bytes.
 struct TileMeta
 {
 	uint32_t start;
 	uint16_t count;
 	uint16_t nlev;
-	uint16_t lvl_end[kMaxSublevels]; // end offset (exclusive) of sublevel k inside the tile
-	uint32_t pad[6];
+	uint16_t lvl_end[kMaxSublevels];   // end offset (exclusive) of sublevel k inside the tile
+	uint16_t inner_end[kMaxSublevels]; // number of inner nodes in sublevels 1..k (sublevel 0 holds none)
+	uint32_t pad[2];
 };
 static_assert(sizeof(TileMeta) == 64, "TileMeta must be 64 bytes");
 
@@ -46,6 +48,7 @@ struct rn_scene
 	rn_scene_desc desc{};
 	int device = 0;
 	uint32_t tile_cap = 512;
+	uint32_t inner_cap = 96;     // inner nodes (parents kept in shared memory) per tile
 	uint32_t n = 0;              // nodes
 	uint32_t n_tiles = 0;
 	uint32_t max_depth = 0;
@@ -63,18 +66,17 @@ struct rn_scene
 	float4 *wrot = nullptr;      // world rotation
 	float2 *wsyz = nullptr;      // world scale y, z
 	float4 *wmat = nullptr;      // 4 x float4 per slot (column-major 4x4)
-	uint16_t *lrank = nullptr;   // slot -> rank - tile.start
-	uint16_t *lslot = nullptr;   // rank -> slot - tile.start
-	uint8_t *vis = nullptr;      // rank -> camera bit mask of the last cull
+	uint32_t *d_slot_of_rank = nullptr; // rank -> slot
+	uint8_t *vis = nullptr;      // slot -> camera bit mask of the last cull
 	rn::TileMeta *tiles = nullptr;
-	uint32_t *tile_counts = nullptr;   // [RN_MAX_CAMERAS][n_tiles]
-	uint32_t *tile_offsets = nullptr;  // [RN_MAX_CAMERAS][n_tiles]
+	unsigned long long *status = nullptr; // compaction look-back state [chunks][RN_MAX_CAMERAS]
+	uint32_t *ticket = nullptr;        // compaction chunk ticket
+	uint32_t epoch = 0;                // compaction epoch (one per cull)
 	uint32_t *list_counts = nullptr;   // [RN_MAX_CAMERAS]
 	uint32_t *lists[RN_MAX_CAMERAS] = {};
 	uint32_t list_capacity = 0;
 	uint32_t *spine_slots = nullptr;   // all spine slots grouped by depth
 	std::vector<uint32_t> spine_level_ofs; // host: offsets into spine_slots per depth (size levels+1)
-	uint32_t *scratch_idx = nullptr;   // (unused)
 	float *scratch_cols = nullptr;     // device staging for rn_scene_update_nodes
 	float *scratch_host = nullptr;     // pinned host staging
 	uint32_t scratch_cap = 0;

@@ -83,9 +83,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 // ---------------------------------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------------------------------
-constexpr uint32_t kFlagSpine = 1u << 31;
-constexpr uint32_t kLRankShift = 16;
-constexpr uint32_t kLRankMask = 0x7ffu;
+constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 struct SceneView
 {
@@ -93,11 +91,12 @@ struct SceneView
 	float4 *wpos, *wrot;
 	float2 *wsyz;
 	float4 *wmat;
-	uint8_t *vis;
+	uint8_t *vis;              // camera bit mask per SLOT
 	const TileMeta *tiles;
-	uint32_t *tile_counts;
 	uint32_t n_tiles;
-	uint32_t tile_cap;
+	uint32_t inner_cap;        // P: parents kept in shared memory per tile
+	uint32_t warp_smem;        // bytes of shared memory per warp
+	uint32_t n;
 };
 
 struct CullParams
@@ -116,6 +115,36 @@ struct NodeWorld
 
 __device__ __forceinline__ float std_max(float a, float b) { return (a < b) ? b : a; } // std::max
 
+// SceneNode::CanRenderUtil + Camera::InFrustum for ONE camera (index known at compile time, so that the 28 frustum
+// floats are read as constant-bank operands).  px,py,pz / radius: the transformed bounding sphere.
+template <int C>
+__device__ __forceinline__ uint32_t cull_camera(const CullParams &cp, uint32_t flagsword, float px, float py, float pz, float radius)
+{
+	const rn_camera_frustum &cam = cp.cam[C];
+	const uint32_t group = (flagsword >> 8) & 0xffu;
+	if((group & cam.render_group & 0xffu) == 0)
+		return 0;
+	if(flagsword & RN_NODE_NOCULLING)
+		return 1u << C;
+	// _frustumCenter.GetDistance(position) > _frustumRadius + radius  (Source/Scene/RNCamera.cpp:444-445)
+	const float dx = cam.center[0] - px, dy = cam.center[1] - py, dz = cam.center[2] - pz;
+	const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+	if(dist > cam.radius + radius)
+		return 0;
+	if(cam.flags & RN_CAMERA_USE_SIMPLE_CULLING)
+		return 1u << C;
+	bool inside = true;
+#pragma unroll
+	for(int k = 0; k < 6; k++)
+	{
+		// Plane::GetDistance: position.Dot(normal) - d   (Source/Math/RNPlane.h:99-102)
+		const float d = px * cam.planes[k][0] + py * cam.planes[k][1] + pz * cam.planes[k][2] - cam.planes[k][3];
+		if(d > radius)
+			inside = false;
+	}
+	return inside ? (1u << C) : 0u;
+}
+
 // SceneNode::UpdateInternalBoundsData (sphere part) + SceneNode::CanRenderUtil + Camera::InFrustum for all cameras.
 // Returns the camera bit mask.
 __device__ __forceinline__ uint32_t cull_node(const CullParams &cp, uint32_t flagsword, const Vec3 &wp, const Quat &wr,
@@ -123,47 +152,29 @@ __device__ __forceinline__ uint32_t cull_node(const CullParams &cp, uint32_t fla
 {
 	if(flagsword & RN_NODE_HIDDEN)
 		return 0;
-	const uint32_t group = (flagsword >> 8) & 0xffu;
-
 	// Sphere::operator*=(Vector3) then SetRotation (Source/Math/RNSphere.h:62-73)
 	const float s = std_max(std_max(ws.x, ws.y), ws.z);
 	const float radius = sph.w * s;
-	Vec3 off = {sph.x * s, sph.y * s, sph.z * s};
-	off = quat_rotate(wr, off);
-	// Camera::InFrustum(const Sphere&): position + offset (Source/Scene/RNCamera.cpp:469-473)
-	const float px = wp.x + off.x, py = wp.y + off.y, pz = wp.z + off.z;
-
-	uint32_t mask = 0;
-	for(uint32_t c = 0; c < cp.n; c++)
+	float px = wp.x, py = wp.y, pz = wp.z;
+	// A zero offset stays (+-)0 through the scaling and the rotation and `position + offset` returns the position:
+	// skipping the rotation is exact (up to the sign of a zero, which no comparison below can see).
+	if(sph.x != 0.0f || sph.y != 0.0f || sph.z != 0.0f)
 	{
-		const rn_camera_frustum &cam = cp.cam[c];
-		if((group & cam.render_group & 0xffu) == 0)
-			continue;
-		if(flagsword & RN_NODE_NOCULLING)
-		{
-			mask |= 1u << c;
-			continue;
-		}
-		// _frustumCenter.GetDistance(position) > _frustumRadius + radius
-		const float dx = cam.center[0] - px, dy = cam.center[1] - py, dz = cam.center[2] - pz;
-		const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
-		if(dist > cam.radius + radius)
-			continue;
-		bool inside = true;
-		if(!(cam.flags & RN_CAMERA_USE_SIMPLE_CULLING))
-		{
-#pragma unroll
-			for(int k = 0; k < 6; k++)
-			{
-				// Plane::GetDistance: position.Dot(normal) - d   (Source/Math/RNPlane.h:99-102)
-				const float d = px * cam.planes[k][0] + py * cam.planes[k][1] + pz * cam.planes[k][2] - cam.planes[k][3];
-				if(d > radius)
-					inside = false;
-			}
-		}
-		if(inside)
-			mask |= 1u << c;
+		Vec3 off = {sph.x * s, sph.y * s, sph.z * s};
+		off = quat_rotate(wr, off);
+		// Camera::InFrustum(const Sphere&): position + offset (Source/Scene/RNCamera.cpp:469-473)
+		px = wp.x + off.x; py = wp.y + off.y; pz = wp.z + off.z;
 	}
+	uint32_t mask = 0;
+	const uint32_t nc = cp.n;
+	mask |= cull_camera<0>(cp, flagsword, px, py, pz, radius);
+	if(nc > 1) mask |= cull_camera<1>(cp, flagsword, px, py, pz, radius);
+	if(nc > 2) mask |= cull_camera<2>(cp, flagsword, px, py, pz, radius);
+	if(nc > 3) mask |= cull_camera<3>(cp, flagsword, px, py, pz, radius);
+	if(nc > 4) mask |= cull_camera<4>(cp, flagsword, px, py, pz, radius);
+	if(nc > 5) mask |= cull_camera<5>(cp, flagsword, px, py, pz, radius);
+	if(nc > 6) mask |= cull_camera<6>(cp, flagsword, px, py, pz, radius);
+	if(nc > 7) mask |= cull_camera<7>(cp, flagsword, px, py, pz, radius);
 	return mask;
 }
 
@@ -241,39 +252,34 @@ __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t
 	store_world_global(sv, slot, W);
 }
 
-struct TileSmem
+// Per-warp shared memory: the world TRS + matrix of the tile's INNER nodes (nodes with children), SoA, followed by
+// the tile descriptor.  88 bytes per inner node.
+struct WarpSmem
 {
-	float4 *in0, *in1, *in2, *in3;
-	float4 *wpos, *wrot, *m0, *m1, *m2;
-	float2 *wsyz;
-	uint8_t *vis;
-	uint64_t *bar;
-	uint32_t *cnt;
+	float4 *a, *b, *m0, *m1, *m2;   // (wp.xyz, ws.x) ; wr ; matrix floats 0-3, 4-7, 8-11
+	float2 *syz;                    // ws.y, ws.z
+	const TileMeta *meta;
 };
 
-__host__ __device__ inline size_t tile_smem_bytes(uint32_t cap)
+__host__ __device__ inline uint32_t warp_smem_bytes(uint32_t inner_cap)
 {
-	// 4 input columns + wpos, wrot, m0..m2 (float4) + wsyz (float2) + vis bytes + barrier + counters
-	return (size_t)cap * (9 * 16 + 8) + ((cap + 15) & ~15u) + 16 + RN_MAX_CAMERAS * 4;
+	return inner_cap * 88u + (uint32_t)sizeof(TileMeta);
 }
 
-__device__ __forceinline__ TileSmem carve_smem(unsigned char *base, uint32_t cap)
+__device__ __forceinline__ WarpSmem carve_warp_smem(unsigned char *base, uint32_t P)
 {
-	TileSmem s;
+	WarpSmem s;
 	float4 *f = reinterpret_cast<float4 *>(base);
-	s.in0 = f; s.in1 = f + cap; s.in2 = f + 2 * cap; s.in3 = f + 3 * cap;
-	s.wpos = f + 4 * cap; s.wrot = f + 5 * cap; s.m0 = f + 6 * cap; s.m1 = f + 7 * cap; s.m2 = f + 8 * cap;
-	s.wsyz = reinterpret_cast<float2 *>(f + 9 * cap);
-	s.vis = reinterpret_cast<uint8_t *>(s.wsyz + cap);
-	s.bar = reinterpret_cast<uint64_t *>(s.vis + ((cap + 15) & ~15u));
-	s.cnt = reinterpret_cast<uint32_t *>(s.bar + 2);
+	s.a = f; s.b = f + P; s.m0 = f + 2 * P; s.m1 = f + 3 * P; s.m2 = f + 4 * P;
+	s.syz = reinterpret_cast<float2 *>(f + 5 * P);
+	s.meta = reinterpret_cast<const TileMeta *>(s.syz + P);
 	return s;
 }
 
-__device__ __forceinline__ void load_world_smem(const TileSmem &s, uint32_t j, NodeWorld &w)
+__device__ __forceinline__ void load_world_smem(const WarpSmem &s, uint32_t j, NodeWorld &w)
 {
-	const float4 a = s.wpos[j], b = s.wrot[j];
-	const float2 c = s.wsyz[j];
+	const float4 a = s.a[j], b = s.b[j];
+	const float2 c = s.syz[j];
 	const float4 q0 = s.m0[j], q1 = s.m1[j], q2 = s.m2[j];
 	w.wp = {a.x, a.y, a.z};
 	w.wr = {b.x, b.y, b.z, b.w};
@@ -283,174 +289,208 @@ __device__ __forceinline__ void load_world_smem(const TileSmem &s, uint32_t j, N
 	w.M.m[8] = q2.x; w.M.m[9] = q2.y; w.M.m[10] = q2.z; w.M.m[11] = q2.w;
 }
 
-__device__ __forceinline__ void store_world_smem(const TileSmem &s, uint32_t j, const NodeWorld &w)
+__device__ __forceinline__ void store_world_smem(const WarpSmem &s, uint32_t j, const NodeWorld &w)
 {
-	s.wpos[j] = make_float4(w.wp.x, w.wp.y, w.wp.z, w.ws.x);
-	s.wrot[j] = make_float4(w.wr.x, w.wr.y, w.wr.z, w.wr.w);
-	s.wsyz[j] = make_float2(w.ws.y, w.ws.z);
+	s.a[j] = make_float4(w.wp.x, w.wp.y, w.wp.z, w.ws.x);
+	s.b[j] = make_float4(w.wr.x, w.wr.y, w.wr.z, w.wr.w);
+	s.syz[j] = make_float2(w.ws.y, w.ws.z);
 	s.m0[j] = make_float4(w.M.m[0], w.M.m[1], w.M.m[2], w.M.m[3]);
 	s.m1[j] = make_float4(w.M.m[4], w.M.m[5], w.M.m[6], w.M.m[7]);
 	s.m2[j] = make_float4(w.M.m[8], w.M.m[9], w.M.m[10], w.M.m[11]);
 }
 
-// One CTA per tile.  XF: compute world transforms (else read the stored world TRS); CULL: evaluate visibility.
-template <bool XF, bool CULL>
-__global__ void __launch_bounds__(kTileThreads) tile_kernel(SceneView sv, CullParams cp)
+// World-transform propagation (+ culling) of one tile per WARP.  A tile is a contiguous slot range holding whole
+// compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every sublevel first.
+// The warp walks the sublevels in order, 32 nodes per pass: coalesced float4 loads of the four input columns,
+// parent world TRS + matrix from the warp's shared memory (written by an earlier pass of the same warp, so only
+// __syncwarp separates the levels - no block barrier, the warps of a CTA never wait for each other), one coalesced
+// write of the outputs.  Every node is read once and written once; parents never come back from HBM.
+template <bool CULL>
+__global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
-	const TileSmem s = carve_smem(smem_raw, sv.tile_cap);
-	__shared__ TileMeta meta;
-
-	const uint32_t tile = blockIdx.x;
-	const uint32_t tid = threadIdx.x;
-	if(tid < 16)
-		reinterpret_cast<uint32_t *>(&meta)[tid] = reinterpret_cast<const uint32_t *>(&sv.tiles[tile])[tid];
-	if(tid < RN_MAX_CAMERAS)
-		s.cnt[tid] = 0;
-	if(tid == 0)
-	{
-		mbar_init(s.bar, 1);
-		mbar_fence_init();
-	}
-	__syncthreads();
-	const uint32_t start = meta.start;
-	const uint32_t count = meta.count;
-
-	// Stage the tile's input columns with TMA bulk copies (one elected thread).
-	if(tid == 0)
-	{
-		const uint32_t bytes = count * 16u;
-		if(XF)
-		{
-			mbar_expect_tx(s.bar, bytes * 4u);
-			bulk_g2s(s.in0, sv.c0 + start, bytes, s.bar);
-			bulk_g2s(s.in1, sv.c1 + start, bytes, s.bar);
-			bulk_g2s(s.in2, sv.c2 + start, bytes, s.bar);
-			bulk_g2s(s.in3, sv.c3 + start, bytes, s.bar);
-		}
-		else
-		{
-			mbar_expect_tx(s.bar, bytes * 4u);
-			bulk_g2s(s.in2, sv.c2 + start, bytes, s.bar);
-			bulk_g2s(s.in3, sv.c3 + start, bytes, s.bar);
-			bulk_g2s(s.wpos, sv.wpos + start, bytes, s.bar);
-			bulk_g2s(s.wrot, sv.wrot + start, bytes, s.bar);
-		}
-	}
-	mbar_wait(s.bar, 0);
-
-	if(XF)
-	{
-		// sublevel 0: spine nodes inside this tile - world transform already in global memory (pre-pass)
-		for(uint32_t j = tid; j < meta.lvl_end[0]; j += kTileThreads)
-		{
-			NodeWorld W;
-			load_world_global(sv, start + j, W);
-			store_world_smem(s, j, W);
-			if(CULL)
-			{
-				const uint32_t fw = __float_as_uint(s.in2[j].w);
-				s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, s.in3[j]);
-			}
-		}
-		__syncthreads();
-		for(uint32_t lev = 1; lev < meta.nlev; lev++)
-		{
-			const uint32_t jend = meta.lvl_end[lev];
-			for(uint32_t j = meta.lvl_end[lev - 1] + tid; j < jend; j += kTileThreads)
-			{
-				const float4 a = s.in0[j], b = s.in1[j], c = s.in2[j];
-				const Vec3 pos = {a.x, a.y, a.z};
-				const Vec3 scale = {a.w, c.x, c.y};
-				const Quat rot = {b.x, b.y, b.z, b.w};
-				const uint32_t parent = __float_as_uint(c.z);
-				const uint32_t fw = __float_as_uint(c.w);
-				NodeWorld P, W;
-				const bool hasParent = parent != RN_NO_PARENT;
-				if(hasParent)
-				{
-					const uint32_t pl = parent - start;
-					if(pl < count)
-						load_world_smem(s, pl, P);
-					else
-						load_world_global(sv, parent, P);
-				}
-				compute_world(pos, rot, scale, hasParent, P, W);
-				store_world_smem(s, j, W);
-				store_world_global(sv, start + j, W);
-				if(CULL)
-					s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, s.in3[j]);
-			}
-			__syncthreads();
-		}
-	}
-	else if(CULL)
-	{
-		for(uint32_t j = tid; j < count; j += kTileThreads)
-		{
-			const float4 a = s.wpos[j], b = s.wrot[j];
-			const float2 c = sv.wsyz[start + j];
-			const uint32_t fw = __float_as_uint(s.in2[j].w);
-			const Vec3 wp = {a.x, a.y, a.z};
-			const Quat wr = {b.x, b.y, b.z, b.w};
-			const Vec3 ws = {a.w, c.x, c.y};
-			s.vis[(fw >> kLRankShift) & kLRankMask] = (uint8_t)cull_node(cp, fw, wp, wr, ws, s.in3[j]);
-		}
-		__syncthreads();
-	}
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
+	if(tile >= sv.n_tiles)
+		return;
+	const WarpSmem s = carve_warp_smem(smem_raw + (size_t)warp * sv.warp_smem, sv.inner_cap);
+	if(lane < sizeof(TileMeta) / 4)
+		reinterpret_cast<uint32_t *>(const_cast<TileMeta *>(s.meta))[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
+	__syncwarp();
+	const uint32_t start = s.meta->start;
+	const uint32_t nlev = s.meta->nlev;
 
 	if(CULL)
 	{
-		// visibility bytes in RANK order + per-camera counts of this tile
-		uint32_t local[RN_MAX_CAMERAS];
-#pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
-			local[c] = 0;
-		for(uint32_t t = tid; t < count; t += kTileThreads)
+		// sublevel 0: spine nodes stored inside this tile - world transform already computed by the pre-pass
+		const uint32_t e0 = s.meta->lvl_end[0];
+		for(uint32_t j = lane; j < e0; j += 32)
 		{
-			const uint32_t v = s.vis[t];
-			sv.vis[start + t] = (uint8_t)v;
-#pragma unroll
-			for(int c = 0; c < RN_MAX_CAMERAS; c++)
-				local[c] += (v >> c) & 1u;
+			const uint32_t slot = start + j;
+			const float4 a = sv.wpos[slot], b = sv.wrot[slot];
+			const float2 c = sv.wsyz[slot];
+			const uint32_t fw = __float_as_uint(sv.c2[slot].w);
+			const Vec3 wp = {a.x, a.y, a.z};
+			const Quat wr = {b.x, b.y, b.z, b.w};
+			const Vec3 ws = {a.w, c.x, c.y};
+			sv.vis[slot] = (uint8_t)cull_node(cp, fw, wp, wr, ws, sv.c3[slot]);
 		}
-#pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+	}
+	for(uint32_t lev = 1; lev < nlev; lev++)
+	{
+		const uint32_t jb = s.meta->lvl_end[lev - 1], je = s.meta->lvl_end[lev];
+		const uint32_t ib = s.meta->inner_end[lev - 1], ni = s.meta->inner_end[lev] - ib;
+		for(uint32_t j = jb + lane; j < je; j += 32)
 		{
-			if((uint32_t)c < cp.n)
+			const uint32_t slot = start + j;
+			const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
+			float4 d;
+			if(CULL) d = sv.c3[slot];
+			const Vec3 pos = {a.x, a.y, a.z};
+			const Vec3 scale = {a.w, c.x, c.y};
+			const Quat rot = {b.x, b.y, b.z, b.w};
+			const uint32_t parent = __float_as_uint(c.z);
+			const uint32_t fw = __float_as_uint(c.w);
+			NodeWorld P, W;
+			const bool hasParent = parent != RN_NO_PARENT;
+			if(hasParent)
 			{
-				uint32_t v = local[c];
-#pragma unroll
-				for(int o = 16; o > 0; o >>= 1)
-					v += __shfl_xor_sync(0xffffffffu, v, o);
-				if((tid & 31) == 0 && v)
-					atomicAdd(&s.cnt[c], v);
+				if(parent & kParentInTile)
+					load_world_smem(s, parent & 0xffffu, P);
+				else
+					load_world_global(sv, parent, P);
 			}
+			compute_world(pos, rot, scale, hasParent, P, W);
+			store_world_global(sv, slot, W);
+			if(j - jb < ni)
+				store_world_smem(s, ib + (j - jb), W);
+			if(CULL)
+				sv.vis[slot] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, d);
 		}
-		__syncthreads();
-		if(tid < cp.n)
-			sv.tile_counts[tid * sv.n_tiles + tile] = s.cnt[tid];
+		__syncwarp();
 	}
 }
 
-// Exclusive scan of the per-tile counts, one CTA per camera; also publishes the camera's total.
-__global__ void __launch_bounds__(1024) scan_kernel(const uint32_t *__restrict__ counts, uint32_t *__restrict__ offsets,
-                                                   uint32_t *__restrict__ totals, uint32_t n_tiles)
+// rn_cull on stored world transforms: one thread per slot.
+__global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
-	__shared__ uint32_t warp_sums[32];
-	__shared__ uint32_t carry;
-	const uint32_t cam = blockIdx.x;
-	const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	counts += (size_t)cam * n_tiles;
-	offsets += (size_t)cam * n_tiles;
-	if(tid == 0)
-		carry = 0;
-	__syncthreads();
-	for(uint32_t base = 0; base < n_tiles; base += 1024)
+	for(uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < sv.n; slot += gridDim.x * blockDim.x)
 	{
-		const uint32_t i = base + tid;
-		const uint32_t v = i < n_tiles ? counts[i] : 0;
-		uint32_t x = v;
+		const float4 a = sv.wpos[slot], b = sv.wrot[slot];
+		const float2 c = sv.wsyz[slot];
+		const uint32_t fw = __float_as_uint(sv.c2[slot].w);
+		const Vec3 wp = {a.x, a.y, a.z};
+		const Quat wr = {b.x, b.y, b.z, b.w};
+		const Vec3 ws = {a.w, c.x, c.y};
+		sv.vis[slot] = (uint8_t)cull_node(cp, fw, wp, wr, ws, sv.c3[slot]);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Ordered stream compaction of the visibility masks into one list per camera, single pass (decoupled look-back).
+// A chunk = 4096 consecutive RANKS (render-list positions); chunk numbers are handed out by an atomic ticket so a
+// chunk's predecessors are always running or finished.  status[chunk][camera] packs {epoch:30, state:2, count:32}
+// in one 64-bit word (state 1 = the chunk's own count, 2 = inclusive prefix); the epoch makes a reset between
+// frames unnecessary.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kCompactThreads = 256;
+constexpr uint32_t kCompactPerThread = 16;
+constexpr uint32_t kCompactChunk = kCompactThreads * kCompactPerThread;
+
+struct CompactView
+{
+	const uint8_t *vis;
+	const uint32_t *slot_of_rank;
+	uint32_t *lists[RN_MAX_CAMERAS];
+	uint32_t *list_counts;
+	unsigned long long *status;
+	uint32_t *ticket;
+	uint32_t n, n_cams, n_chunks, epoch;
+};
+
+__device__ __forceinline__ unsigned long long status_pack(uint32_t epoch, uint32_t state, uint32_t value)
+{
+	return ((unsigned long long)epoch << 34) | ((unsigned long long)state << 32) | value;
+}
+
+__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const __grid_constant__ CompactView cv)
+{
+	__shared__ uint32_t s_chunk;
+	__shared__ uint32_t s_warp[kCompactThreads / 32][4];
+	__shared__ uint32_t s_base[RN_MAX_CAMERAS];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	if(tid == 0)
+	{
+		const uint32_t t = atomicAdd(cv.ticket, 1u);
+		if(t == cv.n_chunks - 1)
+			*cv.ticket = 0; // every chunk of this launch has its ticket: rearm for the next launch
+		s_chunk = t;
+	}
+	__syncthreads();
+	const uint32_t chunk = s_chunk;
+	const uint32_t r0 = chunk * kCompactChunk + tid * kCompactPerThread;
+
+	uint32_t slots[kCompactPerThread];
+	uint32_t vb[kCompactPerThread / 4];
+	if(r0 + kCompactPerThread <= cv.n)
+	{
+		const uint4 *p = reinterpret_cast<const uint4 *>(cv.slot_of_rank + r0);
+#pragma unroll
+		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
+		{
+			const uint4 v = p[q];
+			slots[q * 4 + 0] = v.x; slots[q * 4 + 1] = v.y; slots[q * 4 + 2] = v.z; slots[q * 4 + 3] = v.w;
+		}
+#pragma unroll
+		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
+		{
+			vb[q] = (uint32_t)cv.vis[slots[q * 4 + 0]] | ((uint32_t)cv.vis[slots[q * 4 + 1]] << 8) |
+			        ((uint32_t)cv.vis[slots[q * 4 + 2]] << 16) | ((uint32_t)cv.vis[slots[q * 4 + 3]] << 24);
+		}
+	}
+	else
+	{
+#pragma unroll
+		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
+		{
+			vb[q] = 0;
+#pragma unroll
+			for(int k = 0; k < 4; k++)
+			{
+				const uint32_t r = r0 + q * 4 + k;
+				slots[q * 4 + k] = 0;
+				if(r < cv.n)
+				{
+					const uint32_t sl = cv.slot_of_rank[r];
+					slots[q * 4 + k] = sl;
+					vb[q] |= (uint32_t)cv.vis[sl] << (8 * k);
+				}
+			}
+		}
+	}
+
+	// per-thread counts, two cameras per word (16 bits each: a chunk holds 4096 nodes)
+	uint32_t pk[4];
+#pragma unroll
+	for(int h = 0; h < 4; h++)
+	{
+		uint32_t lo = 0, hi = 0;
+#pragma unroll
+		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
+		{
+			lo += (vb[q] >> (2 * h)) & 0x01010101u;
+			hi += (vb[q] >> (2 * h + 1)) & 0x01010101u;
+		}
+		lo = (lo * 0x01010101u) >> 24;
+		hi = (hi * 0x01010101u) >> 24;
+		pk[h] = lo | (hi << 16);
+	}
+	// inclusive scan inside the warp, then across the warps
+	uint32_t inc[4];
+#pragma unroll
+	for(int h = 0; h < 4; h++)
+	{
+		uint32_t x = pk[h];
 #pragma unroll
 		for(int o = 1; o < 32; o <<= 1)
 		{
@@ -458,105 +498,90 @@ __global__ void __launch_bounds__(1024) scan_kernel(const uint32_t *__restrict__
 			if(lane >= (uint32_t)o)
 				x += y;
 		}
+		inc[h] = x;
 		if(lane == 31)
-			warp_sums[warp] = x;
-		__syncthreads();
-		if(warp == 0)
-		{
-			uint32_t w = warp_sums[lane];
-#pragma unroll
-			for(int o = 1; o < 32; o <<= 1)
-			{
-				const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
-				if(lane >= (uint32_t)o)
-					w += y;
-			}
-			warp_sums[lane] = w; // inclusive
-		}
-		__syncthreads();
-		const uint32_t before = carry + (warp ? warp_sums[warp - 1] : 0) + (x - v);
-		if(i < n_tiles)
-			offsets[i] = before;
-		__syncthreads();
-		if(tid == 1023)
-			carry = before + v;
-		__syncthreads();
-	}
-	if(tid == 0)
-		totals[cam] = carry;
-}
-
-struct EmitView
-{
-	const uint8_t *vis;
-	const uint16_t *lslot;
-	const TileMeta *tiles;
-	const uint32_t *tile_counts;
-	const uint32_t *tile_offsets;
-	uint32_t *lists[RN_MAX_CAMERAS];
-	uint32_t n_tiles;
-	uint32_t n_cams;
-};
-
-// Order-preserving compaction: walks the tile's ranks in order and writes the slots of the visible ones.
-__global__ void __launch_bounds__(256) emit_kernel(EmitView ev)
-{
-	__shared__ uint32_t wtot[RN_MAX_CAMERAS][8];
-	__shared__ uint32_t any;
-	const uint32_t tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	if(tid == 0)
-	{
-		uint32_t a = 0;
-		for(uint32_t c = 0; c < ev.n_cams; c++)
-			a |= ev.tile_counts[c * ev.n_tiles + tile];
-		any = a;
+			s_warp[warp][h] = x;
 	}
 	__syncthreads();
-	if(!any)
-		return;
-	const uint32_t start = ev.tiles[tile].start, count = ev.tiles[tile].count;
-	uint32_t run[RN_MAX_CAMERAS];
+	uint32_t excl[4], total[4];
 #pragma unroll
-	for(int c = 0; c < RN_MAX_CAMERAS; c++)
-		run[c] = (uint32_t)c < ev.n_cams ? ev.tile_offsets[c * ev.n_tiles + tile] : 0;
-	for(uint32_t base = 0; base < count; base += 256)
+	for(int h = 0; h < 4; h++)
 	{
-		const uint32_t t = base + tid;
-		uint32_t v = 0, slot = 0;
-		if(t < count)
-		{
-			v = ev.vis[start + t];
-			slot = start + ev.lslot[start + t];
-		}
-		uint32_t before[RN_MAX_CAMERAS];
+		uint32_t pre = 0, tot = 0;
 #pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		for(uint32_t w = 0; w < kCompactThreads / 32; w++)
 		{
-			const uint32_t m = __ballot_sync(0xffffffffu, (v >> c) & 1u);
-			before[c] = __popc(m & ((1u << lane) - 1u));
+			const uint32_t x = s_warp[w][h];
+			pre += w < warp ? x : 0;
+			tot += x;
+		}
+		excl[h] = pre + inc[h] - pk[h];
+		total[h] = tot;
+	}
+
+	// decoupled look-back: warp c resolves camera c
+	if(warp < cv.n_cams)
+	{
+		const uint32_t cam = warp;
+		uint32_t tw = total[0];
+		if((cam >> 1) == 1) tw = total[1];
+		if((cam >> 1) == 2) tw = total[2];
+		if((cam >> 1) == 3) tw = total[3];
+		const uint32_t mine = (tw >> (16 * (cam & 1))) & 0xffffu;
+		volatile unsigned long long *st = cv.status;
+		uint32_t base = 0;
+		if(chunk > 0)
+		{
 			if(lane == 0)
-				wtot[c][warp] = __popc(m);
-		}
-		__syncthreads();
-#pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
-		{
-			if((uint32_t)c < ev.n_cams)
+				st[(size_t)chunk * RN_MAX_CAMERAS + cam] = status_pack(cv.epoch, 1, mine);
+			int p = (int)chunk - 1;
+			while(true)
 			{
-				uint32_t pre = 0, tot = 0;
+				const int idx = p - (int)lane;
+				unsigned long long sw = status_pack(cv.epoch, 2, 0); // virtual predecessor of chunk 0
+				if(idx >= 0)
+					sw = st[(size_t)idx * RN_MAX_CAMERAS + cam];
+				const uint32_t state = ((uint32_t)(sw >> 34) == cv.epoch) ? (uint32_t)(sw >> 32) & 3u : 0u;
+				const uint32_t inc_mask = __ballot_sync(0xffffffffu, state == 2);
+				const uint32_t inv_mask = __ballot_sync(0xffffffffu, state == 0);
+				const uint32_t first = inc_mask ? (uint32_t)__ffs((int)inc_mask) - 1u : 31u;
+				const uint32_t need = (2u << first) - 1u; // lanes 0..first
+				if(inv_mask & need)
+					continue; // a predecessor has not published yet
+				uint32_t v = ((need >> lane) & 1u) ? (uint32_t)sw : 0u;
 #pragma unroll
-				for(int w = 0; w < 8; w++)
-				{
-					const uint32_t x = wtot[c][w];
-					pre += (uint32_t)w < warp ? x : 0;
-					tot += x;
-				}
-				if((v >> c) & 1u)
-					ev.lists[c][run[c] + pre + before[c]] = slot;
-				run[c] += tot;
+				for(int o = 16; o > 0; o >>= 1)
+					v += __shfl_xor_sync(0xffffffffu, v, o);
+				base += v;
+				if(inc_mask)
+					break;
+				p -= 32;
 			}
 		}
-		__syncthreads();
+		if(lane == 0)
+		{
+			st[(size_t)chunk * RN_MAX_CAMERAS + cam] = status_pack(cv.epoch, 2, base + mine);
+			s_base[cam] = base;
+			if(chunk == cv.n_chunks - 1)
+				cv.list_counts[cam] = base + mine;
+		}
+	}
+	__syncthreads();
+
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+	{
+		if((uint32_t)c < cv.n_cams)
+		{
+			uint32_t pos = s_base[c] + ((excl[c >> 1] >> (16 * (c & 1))) & 0xffffu);
+			uint32_t *out = cv.lists[c];
+#pragma unroll
+			for(int k = 0; k < (int)kCompactPerThread; k++)
+			{
+				if((vb[k >> 2] >> (8 * (k & 3) + c)) & 1u)
+					out[pos++] = slots[k];
+			}
+		}
 	}
 }
 
@@ -607,6 +632,8 @@ struct Tiling
 	std::vector<uint32_t> slot_of_rank, rank_of_slot, depth;
 	std::vector<uint8_t> spine;       // by rank
 	std::vector<uint8_t> sublevel;    // by rank: 0 spine, k>=1 depth inside unit + 1
+	std::vector<uint8_t> is_inner;    // by rank: non-spine node with at least one child
+	std::vector<uint16_t> inner_idx;  // by rank: index of an inner node among the inner nodes of its tile
 	std::vector<TileMeta> tiles;
 	std::vector<uint32_t> spine_slots;      // grouped by depth
 	std::vector<uint32_t> spine_level_ofs;
@@ -614,7 +641,7 @@ struct Tiling
 };
 
 // Builds the tiling described in DESIGN.md §3.  O(n) time and memory; returns false on an invalid hierarchy.
-static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tiling &t)
+static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint32_t inner_cap, Tiling &t)
 {
 	const uint32_t kMaxHeight = kMaxSublevels - 2; // sublevels 1..kMaxSublevels-1 hold depths 0..kMaxHeight
 	t.depth.assign(n, 0);
@@ -652,8 +679,12 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 	if(bfs.size() != n) { set_error("the parent column contains a cycle"); return false; }
 
 	// subtree extent / size / height, children before parents
-	std::vector<uint32_t> lo(n), hi(n), size(n, 1), height(n, 0);
-	for(uint32_t i = 0; i < n; i++) lo[i] = hi[i] = i;
+	std::vector<uint32_t> lo(n), hi(n), size(n, 1), height(n, 0), inner(n, 0);
+	for(uint32_t i = 0; i < n; i++)
+	{
+		lo[i] = hi[i] = i;
+		inner[i] = child_ofs[i + 1] > child_ofs[i] ? 1u : 0u;
+	}
 	for(size_t h = n; h-- > 0;)
 	{
 		const uint32_t u = bfs[h];
@@ -663,6 +694,7 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 			lo[p] = std::min(lo[p], lo[u]);
 			hi[p] = std::max(hi[p], hi[u]);
 			size[p] += size[u];
+			inner[p] += inner[u];
 			height[p] = std::max(height[p], height[u] + 1);
 		}
 	}
@@ -678,7 +710,7 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 		t.max_depth = std::max(t.max_depth, t.depth[u]);
 		if(p != RN_NO_PARENT && unit_root[p] != RN_NO_PARENT)
 			unit_root[u] = unit_root[p];
-		else if(hi[u] - lo[u] + 1 == size[u] && size[u] <= cap && height[u] <= kMaxHeight)
+		else if(hi[u] - lo[u] + 1 == size[u] && size[u] <= cap && inner[u] <= inner_cap && height[u] <= kMaxHeight)
 			unit_root[u] = u;
 		if(unit_root[u] == RN_NO_PARENT)
 			t.spine[u] = 1;
@@ -689,14 +721,19 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 	t.tiles.clear();
 	t.slot_of_rank.assign(n, 0);
 	t.rank_of_slot.assign(n, 0);
+	t.is_inner.assign(n, 0);
+	t.inner_idx.assign(n, 0);
+	for(uint32_t i = 0; i < n; i++)
+		t.is_inner[i] = (!t.spine[i] && child_ofs[i + 1] > child_ofs[i]) ? 1 : 0;
 	uint32_t r = 0;
 	while(r < n)
 	{
 		const uint32_t a = r;
 		uint32_t b = r;
+		uint32_t tile_inner = 0;
 		while(b < n)
 		{
-			uint32_t ue;
+			uint32_t ue, ui = 0;
 			if(t.spine[b])
 				ue = b + 1;
 			else
@@ -704,9 +741,11 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 				const uint32_t root = unit_root[b];
 				if(lo[root] != b) { set_error("internal tiling error at rank %u", b); return false; }
 				ue = hi[root] + 1;
+				ui = inner[root];
 			}
-			if(ue - a > cap)
+			if(ue - a > cap || tile_inner + ui > inner_cap)
 				break;
+			tile_inner += ui;
 			b = ue;
 		}
 		if(b == a) { set_error("internal tiling error: empty tile at rank %u", a); return false; }
@@ -714,22 +753,32 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, Tilin
 		memset(&tm, 0, sizeof(tm));
 		tm.start = a;
 		tm.count = (uint16_t)(b - a);
-		// counting sort of the tile's ranks by sublevel (stable in rank)
-		uint32_t hist[kMaxSublevels + 1] = {0};
+		// counting sort of the tile's ranks by (sublevel, inner nodes first), stable in rank
+		uint32_t hist[2 * kMaxSublevels + 1] = {0};
 		uint32_t nlev = 1;
 		for(uint32_t x = a; x < b; x++)
 		{
-			hist[t.sublevel[x] + 1]++;
+			hist[2 * t.sublevel[x] + (t.is_inner[x] ? 0 : 1) + 1]++;
 			nlev = std::max<uint32_t>(nlev, t.sublevel[x] + 1u);
 		}
-		for(uint32_t k = 0; k < kMaxSublevels; k++) hist[k + 1] += hist[k];
-		for(uint32_t k = 0; k < kMaxSublevels; k++) tm.lvl_end[k] = (uint16_t)hist[k + 1];
+		uint32_t inner_run = 0;
+		for(uint32_t k = 0; k < kMaxSublevels; k++)
+		{
+			inner_run += hist[2 * k + 1];
+			tm.inner_end[k] = (uint16_t)inner_run;
+		}
+		for(uint32_t k = 0; k < 2 * kMaxSublevels; k++) hist[k + 1] += hist[k];
+		for(uint32_t k = 0; k < kMaxSublevels; k++) tm.lvl_end[k] = (uint16_t)hist[2 * k + 2];
 		tm.nlev = (uint16_t)nlev;
+		uint32_t inner_fill[kMaxSublevels];
+		for(uint32_t k = 0; k < kMaxSublevels; k++) inner_fill[k] = k ? tm.inner_end[k - 1] : 0;
 		for(uint32_t x = a; x < b; x++)
 		{
-			const uint32_t slot = a + hist[t.sublevel[x]]++;
+			const uint32_t slot = a + hist[2 * t.sublevel[x] + (t.is_inner[x] ? 0 : 1)]++;
 			t.slot_of_rank[x] = slot;
 			t.rank_of_slot[slot] = x;
+			if(t.is_inner[x])
+				t.inner_idx[x] = (uint16_t)inner_fill[t.sublevel[x]]++;
 		}
 		t.tiles.push_back(tm);
 		r = b;
@@ -767,8 +816,8 @@ static int dev_alloc(rn_scene *s, T **p, size_t count)
 
 static void free_nodes(rn_scene *s)
 {
-	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->lrank, s->lslot, s->vis, s->tiles,
-	                s->tile_counts, s->tile_offsets, s->list_counts, s->spine_slots, s->scratch_idx, s->scratch_cols};
+	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->d_slot_of_rank, s->vis, s->tiles,
+	                s->status, s->ticket, s->list_counts, s->spine_slots, s->scratch_cols};
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
@@ -779,8 +828,8 @@ static void free_nodes(rn_scene *s)
 		for(int k = 0; k < 2; k++)
 			if(s->prof_ev[i][k]) { cudaEventDestroy(s->prof_ev[i][k]); s->prof_ev[i][k] = nullptr; }
 	s->c0 = s->c1 = s->c2 = s->c3 = s->wpos = s->wrot = s->wmat = nullptr;
-	s->wsyz = nullptr; s->lrank = s->lslot = nullptr; s->vis = nullptr; s->tiles = nullptr;
-	s->tile_counts = s->tile_offsets = s->list_counts = s->spine_slots = s->scratch_idx = nullptr;
+	s->wsyz = nullptr; s->d_slot_of_rank = nullptr; s->vis = nullptr; s->tiles = nullptr;
+	s->status = nullptr; s->ticket = s->list_counts = s->spine_slots = nullptr;
 	s->scratch_cols = nullptr;
 }
 
@@ -789,8 +838,8 @@ static SceneView make_view(const rn_scene *s)
 	SceneView v;
 	v.c0 = s->c0; v.c1 = s->c1; v.c2 = s->c2; v.c3 = s->c3;
 	v.wpos = s->wpos; v.wrot = s->wrot; v.wsyz = s->wsyz; v.wmat = s->wmat;
-	v.vis = s->vis; v.tiles = s->tiles; v.tile_counts = s->tile_counts;
-	v.n_tiles = s->n_tiles; v.tile_cap = s->tile_cap;
+	v.vis = s->vis; v.tiles = s->tiles;
+	v.n_tiles = s->n_tiles; v.inner_cap = s->inner_cap; v.warp_smem = warp_smem_bytes(s->inner_cap); v.n = s->n;
 	return v;
 }
 
@@ -821,15 +870,16 @@ static int launch_spine(rn_scene *s, cudaStream_t stream)
 	return RN_OK;
 }
 
-template <bool XF, bool CULL>
+template <bool CULL>
 static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 {
-	const size_t smem = tile_smem_bytes(s->tile_cap);
-	static bool configured = false;
-	if(!configured)
+	const size_t smem = (size_t)warp_smem_bytes(s->inner_cap) * kWarpsPerCta;
+	static size_t configured = 0;
+	if(configured < smem)
 	{
-		RN_CUDA(cudaFuncSetAttribute(tile_kernel<XF, CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-		configured = true;
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		configured = smem;
 	}
 	const bool prof = s->profile && s->prof_used < rn_scene::kProfileSlots;
 	if(prof)
@@ -841,7 +891,8 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 		}
 		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][0], stream));
 	}
-	tile_kernel<XF, CULL><<<s->n_tiles, kTileThreads, smem, stream>>>(make_view(s), cp);
+	const uint32_t grid = (s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
+	tile_kernel<CULL><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
 	s->launches++;
 	if(prof)
 	{
@@ -852,16 +903,38 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 	return RN_OK;
 }
 
+static int launch_cull_flat(rn_scene *s, const CullParams &cp, cudaStream_t stream)
+{
+	const uint32_t grid = std::min<uint32_t>((s->n + 255) / 256, 148u * 64u);
+	cull_kernel<<<grid, 256, 0, stream>>>(make_view(s), cp);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
 static int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
 {
-	scan_kernel<<<ncams, 1024, 0, stream>>>(s->tile_counts, s->tile_offsets, s->list_counts, s->n_tiles);
-	EmitView ev;
-	ev.vis = s->vis; ev.lslot = s->lslot; ev.tiles = s->tiles;
-	ev.tile_counts = s->tile_counts; ev.tile_offsets = s->tile_offsets;
-	for(int c = 0; c < RN_MAX_CAMERAS; c++) ev.lists[c] = s->lists[c];
-	ev.n_tiles = s->n_tiles; ev.n_cams = ncams;
-	emit_kernel<<<s->n_tiles, 256, 0, stream>>>(ev);
-	s->launches += 2;
+	CompactView cv;
+	cv.vis = s->vis;
+	cv.slot_of_rank = s->d_slot_of_rank;
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) cv.lists[c] = s->lists[c];
+	cv.list_counts = s->list_counts;
+	cv.status = s->status;
+	cv.ticket = s->ticket;
+	cv.n = s->n;
+	cv.n_cams = ncams;
+	cv.n_chunks = (s->n + kCompactChunk - 1) / kCompactChunk;
+	s->epoch = (s->epoch + 1) & 0x3fffffffu;
+	if(s->epoch == 0)
+	{
+		// the 30-bit epoch wrapped: forget every stale entry
+		const size_t chunks = ((size_t)s->desc.max_nodes + kCompactChunk - 1) / kCompactChunk;
+		RN_CUDA(cudaMemsetAsync(s->status, 0, chunks * RN_MAX_CAMERAS * sizeof(unsigned long long), stream));
+		s->epoch = 1;
+	}
+	cv.epoch = s->epoch;
+	compact_kernel<<<cv.n_chunks, kCompactThreads, 0, stream>>>(cv);
+	s->launches++;
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
@@ -905,6 +978,11 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	RN_REQUIRE(desc->max_nodes > 0, RN_ERR_INVALID, "max_nodes must be > 0");
 	uint32_t cap = desc->tile_nodes ? desc->tile_nodes : 512;
 	RN_REQUIRE(cap >= 64 && cap <= 1024 && (cap % 16) == 0, RN_ERR_INVALID, "tile_nodes must be a multiple of 16 in 64..1024, got %u", cap);
+	RN_REQUIRE(desc->max_nodes < 0x80000000u, RN_ERR_INVALID, "max_nodes must be below 2^31");
+	uint32_t inner_cap = desc->tile_inner_nodes ? desc->tile_inner_nodes : 96;
+	RN_REQUIRE(inner_cap >= 16 && inner_cap <= 1024 && (inner_cap % 2) == 0 &&
+	           (size_t)warp_smem_bytes(inner_cap) * kWarpsPerCta <= 227u * 1024u,
+	           RN_ERR_INVALID, "tile_inner_nodes must be an even number in 16..%u, got %u", (227u * 1024u / kWarpsPerCta - 64u) / 88u, inner_cap);
 	RN_REQUIRE(desc->max_particles_per_emitter < 16383, RN_ERR_INVALID,
 	           "max_particles_per_emitter must be < 16383 (reference: RNParticleEmitter.cpp:115)");
 	int ndev = 0;
@@ -919,6 +997,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	s->desc = *desc;
 	s->device = desc->device;
 	s->tile_cap = cap;
+	s->inner_cap = inner_cap;
 	const size_t n = desc->max_nodes;
 	int rc = RN_OK;
 	if(!rc) rc = dev_alloc(s, &s->c0, n);
@@ -929,8 +1008,11 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	if(!rc) rc = dev_alloc(s, &s->wrot, n);
 	if(!rc) rc = dev_alloc(s, &s->wsyz, n);
 	if(!rc) rc = dev_alloc(s, &s->wmat, n * 4);
-	if(!rc) rc = dev_alloc(s, &s->lslot, n);
+	if(!rc) rc = dev_alloc(s, &s->d_slot_of_rank, n);
 	if(!rc) rc = dev_alloc(s, &s->vis, n);
+	const size_t chunks = (n + kCompactChunk - 1) / kCompactChunk;
+	if(!rc) rc = dev_alloc(s, &s->status, chunks * RN_MAX_CAMERAS);
+	if(!rc) rc = dev_alloc(s, &s->ticket, (size_t)1);
 	if(!rc) rc = dev_alloc(s, &s->list_counts, (size_t)RN_MAX_CAMERAS);
 	if(!rc) rc = dev_alloc(s, &s->spine_slots, n);
 	if(rc)
@@ -940,6 +1022,8 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 		return rc;
 	}
 	cudaMemset(s->list_counts, 0, sizeof(uint32_t) * RN_MAX_CAMERAS);
+	cudaMemset(s->status, 0, chunks * RN_MAX_CAMERAS * sizeof(unsigned long long));
+	cudaMemset(s->ticket, 0, sizeof(uint32_t));
 	*out = s;
 	return RN_OK;
 }
@@ -967,14 +1051,13 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	           RN_ERR_INVALID, "a full upload needs every column");
 	RN_REQUIRE(count <= s->desc.max_nodes, RN_ERR_CAPACITY, "%u nodes exceed max_nodes %u", count, s->desc.max_nodes);
 	Tiling t;
-	if(!build_tiling(count, cols->parent, s->tile_cap, t))
+	if(!build_tiling(count, cols->parent, s->tile_cap, s->inner_cap, t))
 		return RN_ERR_INVALID;
 	RN_CUDA(cudaSetDevice(s->device));
 	RN_CUDA(cudaDeviceSynchronize());
 
 	// pack the columns in slot order
 	std::vector<float4> h0(count), h1(count), h2(count), h3(count);
-	std::vector<uint16_t> hlslot(count);
 	for(const TileMeta &tm : t.tiles)
 	{
 		for(uint32_t j = 0; j < tm.count; j++)
@@ -984,10 +1067,12 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 			const float *p = cols->position + (size_t)r * 3, *sc = cols->scale + (size_t)r * 3, *q = cols->rotation + (size_t)r * 4,
 			            *sp = cols->bounding_sphere + (size_t)r * 4;
 			const uint32_t pr = cols->parent[r];
-			const uint32_t pslot = pr == RN_NO_PARENT ? RN_NO_PARENT : t.slot_of_rank[pr];
-			uint32_t fw = (cols->flags[r] & 0xffu) | ((cols->render_group[r] & 0xffu) << 8) | ((r - tm.start) << kLRankShift);
-			if(t.spine[r]) fw |= kFlagSpine;
-			uint32_t pbits = pslot;
+			// parent reference: a parent inside the same compact subtree lives in the warp's shared memory
+			// (index among the tile's inner nodes); a spine parent is read from global memory by slot
+			uint32_t pbits = RN_NO_PARENT;
+			if(pr != RN_NO_PARENT)
+				pbits = (!t.spine[r] && !t.spine[pr]) ? (kParentInTile | t.inner_idx[pr]) : t.slot_of_rank[pr];
+			const uint32_t fw = (cols->flags[r] & 0xffu) | ((cols->render_group[r] & 0xffu) << 8);
 			float pf, ff;
 			memcpy(&pf, &pbits, 4);
 			memcpy(&ff, &fw, 4);
@@ -995,25 +1080,20 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 			h1[slot] = make_float4(q[0], q[1], q[2], q[3]);
 			h2[slot] = make_float4(sc[1], sc[2], pf, ff);
 			h3[slot] = make_float4(sp[0], sp[1], sp[2], sp[3]);
-			hlslot[r] = (uint16_t)(slot - tm.start);
 		}
 	}
 	RN_CUDA(cudaMemcpy(s->c0, h0.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
 	RN_CUDA(cudaMemcpy(s->c1, h1.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
 	RN_CUDA(cudaMemcpy(s->c2, h2.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
 	RN_CUDA(cudaMemcpy(s->c3, h3.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
-	RN_CUDA(cudaMemcpy(s->lslot, hlslot.data(), sizeof(uint16_t) * count, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->d_slot_of_rank, t.slot_of_rank.data(), sizeof(uint32_t) * count, cudaMemcpyHostToDevice));
 	if(!t.spine_slots.empty())
 		RN_CUDA(cudaMemcpy(s->spine_slots, t.spine_slots.data(), sizeof(uint32_t) * t.spine_slots.size(), cudaMemcpyHostToDevice));
 
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
-	if(s->tile_counts) { cudaFree(s->tile_counts); s->tile_counts = nullptr; }
-	if(s->tile_offsets) { cudaFree(s->tile_offsets); s->tile_offsets = nullptr; }
 	const size_t nt = t.tiles.size();
 	int rc = dev_alloc(s, &s->tiles, nt);
-	if(!rc) rc = dev_alloc(s, &s->tile_counts, nt * RN_MAX_CAMERAS);
-	if(!rc) rc = dev_alloc(s, &s->tile_offsets, nt * RN_MAX_CAMERAS);
 	if(rc) return rc;
 	if(nt) RN_CUDA(cudaMemcpy(s->tiles, t.tiles.data(), sizeof(TileMeta) * nt, cudaMemcpyHostToDevice));
 
@@ -1119,7 +1199,7 @@ extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
 	if(rc) return rc;
 	CullParams cp;
 	memset(&cp, 0, sizeof(cp));
-	rc = launch_tiles<true, false>(s, cp, stream);
+	rc = launch_tiles<false>(s, cp, stream);
 	if(rc) return rc;
 	s->have_world = true;
 	return RN_OK;
@@ -1137,7 +1217,7 @@ extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t
 	rc = ensure_lists(s, n_cameras);
 	if(rc) return rc;
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-	rc = launch_tiles<false, true>(s, cp, stream);
+	rc = launch_cull_flat(s, cp, stream);
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->last_ncams = n_cameras;
@@ -1158,7 +1238,7 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	if(rc) return rc;
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 	rc = launch_spine(s, stream);
-	if(!rc) rc = launch_tiles<true, true>(s, cp, stream);
+	if(!rc) rc = launch_tiles<true>(s, cp, stream);
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->have_world = true;
