@@ -115,24 +115,43 @@ struct NodeWorld
 
 __device__ __forceinline__ float std_max(float a, float b) { return (a < b) ? b : a; } // std::max
 
-// SceneNode::CanRenderUtil + Camera::InFrustum for ONE camera (index known at compile time, so that the 28 frustum
-// floats are read as constant-bank operands).  px,py,pz / radius: the transformed bounding sphere.
+// ---------------------------------------------------------------------------------------------------------------
+// Culling.  The predicate of the reference, per node and camera (SceneNode::CanRenderUtil,
+// Source/Scene/RNSceneNode.cpp:405-417; Camera::InFrustum, Source/Scene/RNCamera.cpp:440-473):
+//     !Hidden && (group & cameraGroup) && (NoCulling || (!(dist(centre, p) > R + r) && (simple || all 6 planes: !(n.p - d > r))))
+// cull_exact<C> evaluates it per lane in the reference's fp32 operation order.  In front of it sits a warp-level
+// classifier: the 32 nodes of a pass are siblings / cousins, i.e. spatially close, so for most (camera, test) pairs
+// ALL of them fall on the same side.  The warp reduces the bounding box of its sphere centres and the radius range,
+// every lane classifies one (camera, plane) or (camera, frustum sphere) pair against that box with a rigorous
+// rounding margin, and a camera whose outcome is decided for the whole warp never runs the per-node tests.
+// Undecided cameras (the box straddles a plane, NaNs, negative radii) take the exact path, so the result is always
+// bit-identical to the reference's.
+// ---------------------------------------------------------------------------------------------------------------
+struct CullTable
+{
+	float4 test[RN_MAX_CAMERAS * 7];   // [c*7] = frustum sphere (centre xyz, radius); [c*7 + 1 + k] = plane k (normal xyz, d)
+	uint8_t group_mask[256];           // _renderGroup byte -> bit mask of the cameras whose render group intersects it
+};
+
+// Per-lane constants of the classifier: round 0 = lane l < 30 tests plane l%6 of camera l/6 (cameras 0-4);
+// round 1 = lane l < 18 tests plane l%6 of camera 5 + l/6, lanes 18-25 test the frustum sphere of camera l-18.
+struct LaneTests
+{
+	float4 e0, e1;
+	uint32_t kind0, kind1;   // 0 = none, 1 = plane, 2 = plane of a simple-culling camera (always inside), 3 = sphere
+};
+
 template <int C>
-__device__ __forceinline__ uint32_t cull_camera(const CullParams &cp, uint32_t flagsword, float px, float py, float pz, float radius)
+__device__ __forceinline__ bool cull_exact(const CullParams &cp, float px, float py, float pz, float radius)
 {
 	const rn_camera_frustum &cam = cp.cam[C];
-	const uint32_t group = (flagsword >> 8) & 0xffu;
-	if((group & cam.render_group & 0xffu) == 0)
-		return 0;
-	if(flagsword & RN_NODE_NOCULLING)
-		return 1u << C;
 	// _frustumCenter.GetDistance(position) > _frustumRadius + radius  (Source/Scene/RNCamera.cpp:444-445)
 	const float dx = cam.center[0] - px, dy = cam.center[1] - py, dz = cam.center[2] - pz;
 	const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
 	if(dist > cam.radius + radius)
-		return 0;
+		return false;
 	if(cam.flags & RN_CAMERA_USE_SIMPLE_CULLING)
-		return 1u << C;
+		return true;
 	bool inside = true;
 #pragma unroll
 	for(int k = 0; k < 6; k++)
@@ -142,16 +161,73 @@ __device__ __forceinline__ uint32_t cull_camera(const CullParams &cp, uint32_t f
 		if(d > radius)
 			inside = false;
 	}
-	return inside ? (1u << C) : 0u;
+	return inside;
 }
 
-// SceneNode::UpdateInternalBoundsData (sphere part) + SceneNode::CanRenderUtil + Camera::InFrustum for all cameras.
-// Returns the camera bit mask.
-__device__ __forceinline__ uint32_t cull_node(const CullParams &cp, uint32_t flagsword, const Vec3 &wp, const Quat &wr,
-                                              const Vec3 &ws, const float4 &sph)
+__device__ __forceinline__ int float_to_ordered(float f)
 {
-	if(flagsword & RN_NODE_HIDDEN)
-		return 0;
+	const int i = __float_as_int(f);
+	return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+__device__ __forceinline__ float warp_min(float f) { return ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(f))); }
+__device__ __forceinline__ float warp_max(float f) { return ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(f))); }
+
+struct WarpBox
+{
+	float lox, hix, loy, hiy, loz, hiz, rlo, rhi;
+};
+
+constexpr float kMargin = 1.9073486328125e-6f;   // 2^-19 = 32 ulp(1): covers the <= 8 roundings of either evaluation
+
+// Classifies one plane against the box: bit 0 = every node is outside (culled), bit 1 = every node is inside.
+// Reference value per node: d = fl(fl(fl(px nx + py ny) + pz nz) - dd), |d - exact| <= 4u * S with
+// S = |px nx| + |py ny| + |pz nz| + |dd|; the bounds below carry at most 6u * S more.
+__device__ __forceinline__ uint32_t classify_plane(const float4 &e, const WarpBox &b)
+{
+	const float a0 = e.x * b.lox, a1 = e.x * b.hix, b0 = e.y * b.loy, b1 = e.y * b.hiy, c0 = e.z * b.loz, c1 = e.z * b.hiz;
+	const float lo = fminf(a0, a1) + fminf(b0, b1) + fminf(c0, c1) - e.w;
+	const float hi = fmaxf(a0, a1) + fmaxf(b0, b1) + fmaxf(c0, c1) - e.w;
+	const float sum = fabsf(e.x) * (fabsf(b.lox) + fabsf(b.hix)) + fabsf(e.y) * (fabsf(b.loy) + fabsf(b.hiy)) +
+	                  fabsf(e.z) * (fabsf(b.loz) + fabsf(b.hiz)) + fabsf(e.w);
+	const float m = kMargin * sum + 1e-30f;
+	uint32_t r = 0;
+	if(lo - m > b.rhi) r = 1;          // even the nearest point of the box is farther out than the largest radius
+	if(hi + m <= b.rlo) r = 2;         // even the farthest point is within the smallest radius
+	return r;
+}
+
+// Classifies the frustum-sphere pre-test: node culled iff sqrt(|c - p|^2) > R + r (relative error of either side < 5u).
+__device__ __forceinline__ uint32_t classify_sphere(const float4 &e, const WarpBox &b)
+{
+	const float ux = b.lox - e.x, vx = e.x - b.hix, uy = b.loy - e.y, vy = e.y - b.hiy, uz = b.loz - e.z, vz = e.z - b.hiz;
+	const float gx = fmaxf(fmaxf(ux, vx), 0.0f), gy = fmaxf(fmaxf(uy, vy), 0.0f), gz = fmaxf(fmaxf(uz, vz), 0.0f);
+	const float Gx = fmaxf(fabsf(ux), fabsf(vx)), Gy = fmaxf(fabsf(uy), fabsf(vy)), Gz = fmaxf(fabsf(uz), fabsf(vz));
+	const float near2 = gx * gx + gy * gy + gz * gz;
+	const float far2 = Gx * Gx + Gy * Gy + Gz * Gz;
+	const float tlo = e.w + b.rlo, thi = e.w + b.rhi;
+	uint32_t r = 0;
+	if(tlo >= 0.0f)
+	{
+		if(near2 * (1.0f - 2.0f * kMargin) > thi * thi * (1.0f + 2.0f * kMargin)) r = 1;
+		if(far2 * (1.0f + 2.0f * kMargin) <= tlo * tlo * (1.0f - 2.0f * kMargin)) r = 2;
+	}
+	return r;
+}
+
+__device__ __forceinline__ uint32_t classify(uint32_t kind, const float4 &e, const WarpBox &b)
+{
+	if(kind == 1) return classify_plane(e, b);
+	if(kind == 3) return classify_sphere(e, b);
+	return kind == 2 ? 2u : 0u;
+}
+
+// SceneNode::UpdateInternalBoundsData (sphere part) + the predicate above for all cameras.
+// Converged call (all 32 lanes); a lane without a node passes a copy of a real node and active = false.
+// Returns the camera bit mask.
+__device__ __forceinline__ uint32_t cull_node(const CullParams &cp, const CullTable &tab, const LaneTests &lt, bool active,
+                                              uint32_t flagsword, const Vec3 &wp, const Quat &wr, const Vec3 &ws, const float4 &sph)
+{
 	// Sphere::operator*=(Vector3) then SetRotation (Source/Math/RNSphere.h:62-73)
 	const float s = std_max(std_max(ws.x, ws.y), ws.z);
 	const float radius = sph.w * s;
@@ -165,17 +241,93 @@ __device__ __forceinline__ uint32_t cull_node(const CullParams &cp, uint32_t fla
 		// Camera::InFrustum(const Sphere&): position + offset (Source/Scene/RNCamera.cpp:469-473)
 		px = wp.x + off.x; py = wp.y + off.y; pz = wp.z + off.z;
 	}
-	uint32_t mask = 0;
+	__syncwarp();
+	WarpBox b;
+	b.lox = warp_min(px); b.hix = warp_max(px);
+	b.loy = warp_min(py); b.hiy = warp_max(py);
+	b.loz = warp_min(pz); b.hiz = warp_max(pz);
+	b.rlo = warp_min(radius); b.rhi = warp_max(radius);
+	// NaN / inf-inf anywhere makes `guard` NaN: then nothing is decided at warp level
+	const float guard = (b.lox - b.hix) + (b.loy - b.hiy) + (b.loz - b.hiz) + (b.rlo - b.rhi);
+	const bool sane = guard <= 0.0f;
 	const uint32_t nc = cp.n;
-	mask |= cull_camera<0>(cp, flagsword, px, py, pz, radius);
-	if(nc > 1) mask |= cull_camera<1>(cp, flagsword, px, py, pz, radius);
-	if(nc > 2) mask |= cull_camera<2>(cp, flagsword, px, py, pz, radius);
-	if(nc > 3) mask |= cull_camera<3>(cp, flagsword, px, py, pz, radius);
-	if(nc > 4) mask |= cull_camera<4>(cp, flagsword, px, py, pz, radius);
-	if(nc > 5) mask |= cull_camera<5>(cp, flagsword, px, py, pz, radius);
-	if(nc > 6) mask |= cull_camera<6>(cp, flagsword, px, py, pz, radius);
-	if(nc > 7) mask |= cull_camera<7>(cp, flagsword, px, py, pz, radius);
-	return mask;
+	const uint32_t r0 = sane ? classify(lt.kind0, lt.e0, b) : 0u;
+	const uint32_t out0 = __ballot_sync(0xffffffffu, r0 == 1), in0 = __ballot_sync(0xffffffffu, r0 == 2);
+	const uint32_t r1 = sane ? classify(lt.kind1, lt.e1, b) : 0u;
+	const uint32_t out1 = __ballot_sync(0xffffffffu, r1 == 1), in1 = __ballot_sync(0xffffffffu, r1 == 2);
+
+	uint32_t frustum = 0;   // per lane: cameras whose frustum test the node passes
+#define RN_CULL_CAM(C)                                                                                              \
+	if(nc > C)                                                                                                      \
+	{                                                                                                               \
+		const uint32_t pout = C < 5 ? (out0 >> (6 * C)) & 63u : (out1 >> (6 * (C - 5))) & 63u;                      \
+		const uint32_t pin = C < 5 ? (in0 >> (6 * C)) & 63u : (in1 >> (6 * (C - 5))) & 63u;                         \
+		const uint32_t sout = (out1 >> (18 + C)) & 1u, sin = (in1 >> (18 + C)) & 1u;                                \
+		if(sout | pout) { }                                                                                         \
+		else if(sin && pin == 63u) frustum |= 1u << C;                                                              \
+		else if(cull_exact<C>(cp, px, py, pz, radius)) frustum |= 1u << C;                                          \
+	}
+	RN_CULL_CAM(0) RN_CULL_CAM(1) RN_CULL_CAM(2) RN_CULL_CAM(3) RN_CULL_CAM(4) RN_CULL_CAM(5) RN_CULL_CAM(6) RN_CULL_CAM(7)
+#undef RN_CULL_CAM
+	__syncwarp();
+	if(!active || (flagsword & RN_NODE_HIDDEN))
+		return 0;
+	const uint32_t groups = tab.group_mask[(flagsword >> 8) & 0xffu];
+	return (flagsword & RN_NODE_NOCULLING) ? groups : (groups & frustum);
+}
+
+// Fills the CTA's cull table and the lane constants (all threads of the CTA; contains a __syncthreads).
+__device__ __forceinline__ void cull_setup(const CullParams &cp, CullTable &tab, LaneTests &lt)
+{
+	for(uint32_t t = threadIdx.x; t < RN_MAX_CAMERAS * 7; t += blockDim.x)
+	{
+		const uint32_t c = t / 7, k = t % 7;
+		float4 e = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+		for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
+		{
+			if(c == (uint32_t)cc)
+			{
+				const rn_camera_frustum &cam = cp.cam[cc];
+				e = make_float4(cam.center[0], cam.center[1], cam.center[2], cam.radius);
+#pragma unroll
+				for(int kk = 0; kk < 6; kk++)
+					if(k == (uint32_t)kk + 1) e = make_float4(cam.planes[kk][0], cam.planes[kk][1], cam.planes[kk][2], cam.planes[kk][3]);
+			}
+		}
+		tab.test[t] = e;
+	}
+	uint32_t simple = 0;
+#pragma unroll
+	for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
+		if(cp.cam[cc].flags & RN_CAMERA_USE_SIMPLE_CULLING) simple |= 1u << cc;
+	for(uint32_t g = threadIdx.x; g < 256; g += blockDim.x)
+	{
+		uint32_t m = 0;
+#pragma unroll
+		for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
+			if((uint32_t)cc < cp.n && (g & cp.cam[cc].render_group & 0xffu)) m |= 1u << cc;
+		tab.group_mask[g] = (uint8_t)m;
+	}
+	__syncthreads();
+	const uint32_t lane = threadIdx.x & 31u;
+	lt.kind0 = lt.kind1 = 0;
+	lt.e0 = lt.e1 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+	if(lane < 30)
+	{
+		const uint32_t c = lane / 6, k = lane % 6;
+		if(c < cp.n) { lt.kind0 = ((simple >> c) & 1u) ? 2u : 1u; lt.e0 = tab.test[c * 7 + 1 + k]; }
+	}
+	if(lane < 18)
+	{
+		const uint32_t c = 5 + lane / 6, k = lane % 6;
+		if(c < cp.n) { lt.kind1 = ((simple >> c) & 1u) ? 2u : 1u; lt.e1 = tab.test[c * 7 + 1 + k]; }
+	}
+	else if(lane < 26)
+	{
+		const uint32_t c = lane - 18;
+		if(c < cp.n) { lt.kind1 = 3u; lt.e1 = tab.test[c * 7]; }
+	}
 }
 
 __device__ __forceinline__ void compute_world(const Vec3 &pos, const Quat &rot, const Vec3 &scale, bool hasParent,
@@ -299,16 +451,27 @@ __device__ __forceinline__ void store_world_smem(const WarpSmem &s, uint32_t j, 
 	s.m2[j] = make_float4(w.M.m[8], w.M.m[9], w.M.m[10], w.M.m[11]);
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p)
+{
+	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 // World-transform propagation (+ culling) of one tile per WARP.  A tile is a contiguous slot range holding whole
 // compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every sublevel first.
 // The warp walks the sublevels in order, 32 nodes per pass: coalesced float4 loads of the four input columns,
 // parent world TRS + matrix from the warp's shared memory (written by an earlier pass of the same warp, so only
 // __syncwarp separates the levels - no block barrier, the warps of a CTA never wait for each other), one coalesced
 // write of the outputs.  Every node is read once and written once; parents never come back from HBM.
+// The lanes of a pass stay converged (a lane without a node recomputes the last node of the level and stores
+// nothing) so that the cull can use warp votes.
 template <bool CULL>
 __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
+	__shared__ CullTable tab;
+	LaneTests lt;
+	if(CULL)
+		cull_setup(cp, tab, lt);
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
 	if(tile >= sv.n_tiles)
@@ -318,34 +481,50 @@ __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constan
 		reinterpret_cast<uint32_t *>(const_cast<TileMeta *>(s.meta))[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
 	__syncwarp();
 	const uint32_t start = s.meta->start;
+	const uint32_t count = s.meta->count;
 	const uint32_t nlev = s.meta->nlev;
 
 	if(CULL)
 	{
 		// sublevel 0: spine nodes stored inside this tile - world transform already computed by the pre-pass
 		const uint32_t e0 = s.meta->lvl_end[0];
-		for(uint32_t j = lane; j < e0; j += 32)
+		for(uint32_t j0 = 0; j0 < e0; j0 += 32)
 		{
-			const uint32_t slot = start + j;
+			const bool active = j0 + lane < e0;
+			const uint32_t slot = start + (active ? j0 + lane : e0 - 1);
 			const float4 a = sv.wpos[slot], b = sv.wrot[slot];
 			const float2 c = sv.wsyz[slot];
 			const uint32_t fw = __float_as_uint(sv.c2[slot].w);
 			const Vec3 wp = {a.x, a.y, a.z};
 			const Quat wr = {b.x, b.y, b.z, b.w};
 			const Vec3 ws = {a.w, c.x, c.y};
-			sv.vis[slot] = (uint8_t)cull_node(cp, fw, wp, wr, ws, sv.c3[slot]);
+			const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
+			if(active)
+				sv.vis[slot] = (uint8_t)mask;
 		}
 	}
 	for(uint32_t lev = 1; lev < nlev; lev++)
 	{
 		const uint32_t jb = s.meta->lvl_end[lev - 1], je = s.meta->lvl_end[lev];
 		const uint32_t ib = s.meta->inner_end[lev - 1], ni = s.meta->inner_end[lev] - ib;
-		for(uint32_t j = jb + lane; j < je; j += 32)
+		for(uint32_t j0 = jb; j0 < je; j0 += 32)
 		{
-			const uint32_t slot = start + j;
+			const uint32_t j = j0 + lane;
+			const bool active = j < je;
+			const uint32_t slot = start + (active ? j : je - 1);
 			const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
 			float4 d;
 			if(CULL) d = sv.c3[slot];
+			// pull the next pass's four 512-byte column segments from HBM into L2 while this pass computes
+			{
+				const uint32_t nj = j0 + 32 + (lane & 3u) * 8u;
+				if(nj < count)
+				{
+					const float4 *col = (lane >> 2) == 0 ? sv.c0 : (lane >> 2) == 1 ? sv.c1 : (lane >> 2) == 2 ? sv.c2 : sv.c3;
+					if((lane >> 2) < (CULL ? 4u : 3u))
+						prefetch_l2(col + start + nj);
+				}
+			}
 			const Vec3 pos = {a.x, a.y, a.z};
 			const Vec3 scale = {a.w, c.x, c.y};
 			const Quat rot = {b.x, b.y, b.z, b.w};
@@ -361,28 +540,46 @@ __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constan
 					load_world_global(sv, parent, P);
 			}
 			compute_world(pos, rot, scale, hasParent, P, W);
-			store_world_global(sv, slot, W);
-			if(j - jb < ni)
-				store_world_smem(s, ib + (j - jb), W);
+			if(active)
+			{
+				store_world_global(sv, slot, W);
+				if(j - jb < ni)
+					store_world_smem(s, ib + (j - jb), W);
+			}
+			__syncwarp();
 			if(CULL)
-				sv.vis[slot] = (uint8_t)cull_node(cp, fw, W.wp, W.wr, W.ws, d);
+			{
+				const uint32_t mask = cull_node(cp, tab, lt, active, fw, W.wp, W.wr, W.ws, d);
+				if(active)
+					sv.vis[slot] = (uint8_t)mask;
+			}
 		}
 		__syncwarp();
 	}
 }
 
-// rn_cull on stored world transforms: one thread per slot.
+// rn_cull on stored world transforms: one warp per 32 consecutive slots.
 __global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
-	for(uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < sv.n; slot += gridDim.x * blockDim.x)
+	__shared__ CullTable tab;
+	LaneTests lt;
+	cull_setup(cp, tab, lt);
+	const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t npass = (sv.n + 31u) / 32u;
+	for(uint32_t p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < npass; p += nwarps)
 	{
+		const bool active = p * 32u + lane < sv.n;
+		const uint32_t slot = active ? p * 32u + lane : sv.n - 1;
 		const float4 a = sv.wpos[slot], b = sv.wrot[slot];
 		const float2 c = sv.wsyz[slot];
 		const uint32_t fw = __float_as_uint(sv.c2[slot].w);
 		const Vec3 wp = {a.x, a.y, a.z};
 		const Quat wr = {b.x, b.y, b.z, b.w};
 		const Vec3 ws = {a.w, c.x, c.y};
-		sv.vis[slot] = (uint8_t)cull_node(cp, fw, wp, wr, ws, sv.c3[slot]);
+		const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
+		if(active)
+			sv.vis[slot] = (uint8_t)mask;
 	}
 }
 
