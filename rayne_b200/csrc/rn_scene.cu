@@ -404,18 +404,23 @@ __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t
 	store_world_global(sv, slot, W);
 }
 
-// Per-warp shared memory: the world TRS + matrix of the tile's INNER nodes (nodes with children), SoA, followed by
-// the tile descriptor.  88 bytes per inner node.
+// Per-warp shared memory: the world TRS + matrix of the tile's INNER nodes (nodes with children), SoA (88 bytes
+// per inner node), the tile descriptor, one staging buffer for the four input columns of a pass (4 x 32 x float4,
+// filled by TMA bulk copies) and the mbarrier those copies complete on.
 struct WarpSmem
 {
 	float4 *a, *b, *m0, *m1, *m2;   // (wp.xyz, ws.x) ; wr ; matrix floats 0-3, 4-7, 8-11
 	float2 *syz;                    // ws.y, ws.z
 	const TileMeta *meta;
+	float4 *stage;                  // [4][32]
+	uint64_t *bar;
 };
+
+constexpr uint32_t kStageBytes = 4u * 32u * 16u;
 
 __host__ __device__ inline uint32_t warp_smem_bytes(uint32_t inner_cap)
 {
-	return inner_cap * 88u + (uint32_t)sizeof(TileMeta);
+	return inner_cap * 88u + (uint32_t)sizeof(TileMeta) + kStageBytes + 16u;
 }
 
 __device__ __forceinline__ WarpSmem carve_warp_smem(unsigned char *base, uint32_t P)
@@ -425,6 +430,8 @@ __device__ __forceinline__ WarpSmem carve_warp_smem(unsigned char *base, uint32_
 	s.a = f; s.b = f + P; s.m0 = f + 2 * P; s.m1 = f + 3 * P; s.m2 = f + 4 * P;
 	s.syz = reinterpret_cast<float2 *>(f + 5 * P);
 	s.meta = reinterpret_cast<const TileMeta *>(s.syz + P);
+	s.stage = reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(s.syz + P) + sizeof(TileMeta));
+	s.bar = reinterpret_cast<uint64_t *>(s.stage + 128);
 	return s;
 }
 
@@ -465,7 +472,7 @@ __device__ __forceinline__ void prefetch_l2(const void *p)
 // The lanes of a pass stay converged (a lane without a node recomputes the last node of the level and stores
 // nothing) so that the cull can use warp votes.
 template <bool CULL>
-__global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
+__global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	__shared__ CullTable tab;
@@ -479,9 +486,13 @@ __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constan
 	const WarpSmem s = carve_warp_smem(smem_raw + (size_t)warp * sv.warp_smem, sv.inner_cap);
 	if(lane < sizeof(TileMeta) / 4)
 		reinterpret_cast<uint32_t *>(const_cast<TileMeta *>(s.meta))[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
+	if(lane == 0)
+	{
+		mbar_init(s.bar, 1);
+		mbar_fence_init();
+	}
 	__syncwarp();
 	const uint32_t start = s.meta->start;
-	const uint32_t count = s.meta->count;
 	const uint32_t nlev = s.meta->nlev;
 
 	if(CULL)
@@ -503,28 +514,51 @@ __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constan
 				sv.vis[slot] = (uint8_t)mask;
 		}
 	}
-	for(uint32_t lev = 1; lev < nlev; lev++)
+	// ---- the passes of sublevels 1.. : a flat sequence over the tile's slots, 32 at a time, never across a level ----
+	// The four input columns of pass p+1 are fetched by TMA bulk copies (one elected lane, completion on the warp's
+	// mbarrier) while pass p computes; a pass starts by moving its 4 x float4 from the stage to registers.
+	const uint32_t ncols = CULL ? 4u : 3u;
+	auto issue = [&](uint32_t j0, uint32_t cnt) {
+		const uint32_t bytes = cnt * 16u;
+		mbar_expect_tx(s.bar, bytes * ncols);
+		bulk_g2s(s.stage, sv.c0 + start + j0, bytes, s.bar);
+		bulk_g2s(s.stage + 32, sv.c1 + start + j0, bytes, s.bar);
+		bulk_g2s(s.stage + 64, sv.c2 + start + j0, bytes, s.bar);
+		if(CULL) bulk_g2s(s.stage + 96, sv.c3 + start + j0, bytes, s.bar);
+	};
+	if(nlev > 1)
 	{
-		const uint32_t jb = s.meta->lvl_end[lev - 1], je = s.meta->lvl_end[lev];
-		const uint32_t ib = s.meta->inner_end[lev - 1], ni = s.meta->inner_end[lev] - ib;
-		for(uint32_t j0 = jb; j0 < je; j0 += 32)
+		uint32_t lev = 1;
+		uint32_t j0 = s.meta->lvl_end[0], je = s.meta->lvl_end[1], jb = j0;
+		uint32_t ib = 0, ni = s.meta->inner_end[1];
+		uint32_t phase = 0;
+		if(lane == 0)
+			issue(j0, min(32u, je - j0));
+		for(;;)
 		{
-			const uint32_t j = j0 + lane;
-			const bool active = j < je;
-			const uint32_t slot = start + (active ? j : je - 1);
-			const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
+			const uint32_t n_cur = min(32u, je - j0);
+			const bool active = lane < n_cur;
+			const uint32_t l = active ? lane : n_cur - 1;
+			const uint32_t j = j0 + l;
+			const uint32_t slot = start + j;
+			mbar_wait(s.bar, phase);
+			phase ^= 1u;
+			const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
 			float4 d;
-			if(CULL) d = sv.c3[slot];
-			// pull the next pass's four 512-byte column segments from HBM into L2 while this pass computes
+			if(CULL) d = s.stage[96 + l];
+			__syncwarp();
+			// next pass
+			uint32_t nlv = lev, nj0 = j0 + 32, nje = je;
+			if(nj0 >= je)
 			{
-				const uint32_t nj = j0 + 32 + (lane & 3u) * 8u;
-				if(nj < count)
-				{
-					const float4 *col = (lane >> 2) == 0 ? sv.c0 : (lane >> 2) == 1 ? sv.c1 : (lane >> 2) == 2 ? sv.c2 : sv.c3;
-					if((lane >> 2) < (CULL ? 4u : 3u))
-						prefetch_l2(col + start + nj);
-				}
+				nlv = lev + 1;
+				nj0 = je;
+				nje = s.meta->lvl_end[nlv < nlev ? nlv : lev];
 			}
+			const bool has_next = nlv < nlev;
+			if(has_next && lane == 0)
+				issue(nj0, min(32u, nje - nj0));
+
 			const Vec3 pos = {a.x, a.y, a.z};
 			const Vec3 scale = {a.w, c.x, c.y};
 			const Quat rot = {b.x, b.y, b.z, b.w};
@@ -553,8 +587,16 @@ __global__ void __launch_bounds__(kTileThreads) tile_kernel(const __grid_constan
 				if(active)
 					sv.vis[slot] = (uint8_t)mask;
 			}
+			if(!has_next)
+				break;
+			if(nlv != lev)
+			{
+				jb = nj0;
+				ib = s.meta->inner_end[lev];
+				ni = s.meta->inner_end[nlv] - ib;
+			}
+			lev = nlv; j0 = nj0; je = nje;
 		}
-		__syncwarp();
 	}
 }
 
@@ -1179,7 +1221,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	uint32_t inner_cap = desc->tile_inner_nodes ? desc->tile_inner_nodes : 96;
 	RN_REQUIRE(inner_cap >= 16 && inner_cap <= 1024 && (inner_cap % 2) == 0 &&
 	           (size_t)warp_smem_bytes(inner_cap) * kWarpsPerCta <= 227u * 1024u,
-	           RN_ERR_INVALID, "tile_inner_nodes must be an even number in 16..%u, got %u", (227u * 1024u / kWarpsPerCta - 64u) / 88u, inner_cap);
+	           RN_ERR_INVALID, "tile_inner_nodes must be an even number in 16..%u, got %u", (227u * 1024u / kWarpsPerCta - 64u - kStageBytes - 16u) / 88u, inner_cap);
 	RN_REQUIRE(desc->max_particles_per_emitter < 16383, RN_ERR_INVALID,
 	           "max_particles_per_emitter must be < 16383 (reference: RNParticleEmitter.cpp:115)");
 	int ndev = 0;
