@@ -69,9 +69,8 @@ struct rn_scene
 	uint32_t *d_slot_of_rank = nullptr; // rank -> slot
 	uint8_t *vis = nullptr;      // slot -> camera bit mask of the last cull
 	rn::TileMeta *tiles = nullptr;
-	unsigned long long *status = nullptr; // compaction look-back state [chunks][RN_MAX_CAMERAS]
-	uint32_t *ticket = nullptr;        // compaction chunk ticket
-	uint32_t epoch = 0;                // compaction epoch (one per cull)
+	uint32_t *tile_counts = nullptr;   // [n_tiles][RN_MAX_CAMERAS] visible nodes per tile (last cull)
+	uint32_t *super_totals = nullptr;  // [n_tiles / 256][RN_MAX_CAMERAS]
 	uint32_t *list_counts = nullptr;   // [RN_MAX_CAMERAS]
 	uint32_t *lists[RN_MAX_CAMERAS] = {};
 	uint32_t list_capacity = 0;

@@ -83,6 +83,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 // ---------------------------------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kSuperTiles = 256;              // tiles per superblock of the compaction offsets
 constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 struct SceneView
@@ -92,6 +93,8 @@ struct SceneView
 	float2 *wsyz;
 	float4 *wmat;
 	uint8_t *vis;              // camera bit mask per SLOT
+	uint32_t *tile_counts;     // [tile][RN_MAX_CAMERAS] visible nodes of the last cull
+	uint32_t *super_totals;    // [tile / kSuperTiles][RN_MAX_CAMERAS]
 	const TileMeta *tiles;
 	uint32_t n_tiles;
 	uint32_t inner_cap;        // P: parents kept in shared memory per tile
@@ -330,6 +333,38 @@ __device__ __forceinline__ void cull_setup(const CullParams &cp, CullTable &tab,
 	}
 }
 
+// Per-lane visible counters of a tile, one byte per camera (a tile has at most 255 passes).
+struct VisCount
+{
+	uint32_t lo, hi;   // cameras 0-3, 4-7
+};
+
+__device__ __forceinline__ void vis_count_add(VisCount &vc, uint32_t mask)
+{
+	// bit i of a nibble -> byte i
+	vc.lo += ((mask & 0xfu) * 0x00204081u) & 0x01010101u;
+	vc.hi += (((mask >> 4) & 0xfu) * 0x00204081u) & 0x01010101u;
+}
+
+// Warp-reduces the counters and publishes them: tile_counts[tile][camera], super_totals[tile / 256][camera] += .
+__device__ __forceinline__ void vis_count_store(const SceneView &sv, uint32_t tile, const VisCount &vc, uint32_t lane)
+{
+	uint32_t mine = 0;
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+	{
+		const uint32_t v = __reduce_add_sync(0xffffffffu, ((c < 4 ? vc.lo : vc.hi) >> (8 * (c & 3))) & 0xffu);
+		if(lane == (uint32_t)c)
+			mine = v;
+	}
+	if(lane < RN_MAX_CAMERAS)
+	{
+		sv.tile_counts[tile * RN_MAX_CAMERAS + lane] = mine;
+		if(mine)
+			atomicAdd(&sv.super_totals[(tile / kSuperTiles) * RN_MAX_CAMERAS + lane], mine);
+	}
+}
+
 __device__ __forceinline__ void compute_world(const Vec3 &pos, const Quat &rot, const Vec3 &scale, bool hasParent,
                                               const NodeWorld &P, NodeWorld &out)
 {
@@ -494,6 +529,7 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 	__syncwarp();
 	const uint32_t start = s.meta->start;
 	const uint32_t nlev = s.meta->nlev;
+	VisCount vc = {0u, 0u};
 
 	if(CULL)
 	{
@@ -512,6 +548,7 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 			const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
 			if(active)
 				sv.vis[slot] = (uint8_t)mask;
+			vis_count_add(vc, mask);
 		}
 	}
 	// ---- the passes of sublevels 1.. : a flat sequence over the tile's slots, 32 at a time, never across a level ----
@@ -586,6 +623,7 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 				const uint32_t mask = cull_node(cp, tab, lt, active, fw, W.wp, W.wr, W.ws, d);
 				if(active)
 					sv.vis[slot] = (uint8_t)mask;
+				vis_count_add(vc, mask);
 			}
 			if(!has_next)
 				break;
@@ -598,21 +636,26 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 			lev = nlv; j0 = nj0; je = nje;
 		}
 	}
+	if(CULL)
+		vis_count_store(sv, tile, vc, lane);
 }
 
-// rn_cull on stored world transforms: one warp per 32 consecutive slots.
+// rn_cull on stored world transforms: one warp per tile, 32 consecutive slots per pass.
 __global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	__shared__ CullTable tab;
 	LaneTests lt;
 	cull_setup(cp, tab, lt);
-	const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
 	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t npass = (sv.n + 31u) / 32u;
-	for(uint32_t p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < npass; p += nwarps)
+	const uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if(tile >= sv.n_tiles)
+		return;
+	const uint32_t start = sv.tiles[tile].start, count = sv.tiles[tile].count;
+	VisCount vc = {0u, 0u};
+	for(uint32_t j0 = 0; j0 < count; j0 += 32)
 	{
-		const bool active = p * 32u + lane < sv.n;
-		const uint32_t slot = active ? p * 32u + lane : sv.n - 1;
+		const bool active = j0 + lane < count;
+		const uint32_t slot = start + (active ? j0 + lane : count - 1);
 		const float4 a = sv.wpos[slot], b = sv.wrot[slot];
 		const float2 c = sv.wsyz[slot];
 		const uint32_t fw = __float_as_uint(sv.c2[slot].w);
@@ -622,114 +665,53 @@ __global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ Scene
 		const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
 		if(active)
 			sv.vis[slot] = (uint8_t)mask;
+		vis_count_add(vc, mask);
 	}
+	vis_count_store(sv, tile, vc, lane);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Ordered stream compaction of the visibility masks into one list per camera, single pass (decoupled look-back).
-// A chunk = 4096 consecutive RANKS (render-list positions); chunk numbers are handed out by an atomic ticket so a
-// chunk's predecessors are always running or finished.  status[chunk][camera] packs {epoch:30, state:2, count:32}
-// in one 64-bit word (state 1 = the chunk's own count, 2 = inclusive prefix); the epoch makes a reset between
-// frames unnecessary.
+// Ordered stream compaction of the visibility masks into one list per camera.
+// The cull kernels leave per-tile per-camera counts (a tile is a rank range AND a slot range, so its count does not
+// depend on the order inside) and add them into per-superblock totals (256 tiles).  A CTA of the emit kernel owns 32
+// consecutive tiles: its base offset = totals of the earlier superblocks + counts of the earlier tiles of its own
+// superblock (two short coalesced sums, no look-back, no spinning), then every warp walks its tiles' RANKS in order
+// and writes the slots of the visible nodes with ballot/popc ranking.  List order = render-list order, exactly.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr uint32_t kCompactThreads = 256;
-constexpr uint32_t kCompactPerThread = 16;
-constexpr uint32_t kCompactChunk = kCompactThreads * kCompactPerThread;
+constexpr uint32_t kEmitThreads = 256;
+constexpr uint32_t kEmitTiles = 32;
+constexpr uint32_t kEmitUnroll = 4;
 
-struct CompactView
+struct EmitView
 {
 	const uint8_t *vis;
 	const uint32_t *slot_of_rank;
+	const TileMeta *tiles;
+	const uint32_t *tile_counts;    // [tile][RN_MAX_CAMERAS]
+	const uint32_t *super_totals;   // [superblock][RN_MAX_CAMERAS]
 	uint32_t *lists[RN_MAX_CAMERAS];
 	uint32_t *list_counts;
-	unsigned long long *status;
-	uint32_t *ticket;
-	uint32_t n, n_cams, n_chunks, epoch;
+	uint32_t n_tiles, n_cams;
 };
 
-__device__ __forceinline__ unsigned long long status_pack(uint32_t epoch, uint32_t state, uint32_t value)
+__global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constant__ EmitView ev)
 {
-	return ((unsigned long long)epoch << 34) | ((unsigned long long)state << 32) | value;
-}
-
-__global__ void __launch_bounds__(kCompactThreads) compact_kernel(const __grid_constant__ CompactView cv)
-{
-	__shared__ uint32_t s_chunk;
-	__shared__ uint32_t s_warp[kCompactThreads / 32][4];
-	__shared__ uint32_t s_base[RN_MAX_CAMERAS];
+	__shared__ uint32_t s_off[kEmitTiles][RN_MAX_CAMERAS];
+	__shared__ uint32_t s_cnt[kEmitTiles][RN_MAX_CAMERAS];
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-	if(tid == 0)
+	const uint32_t first = blockIdx.x * kEmitTiles;
+	const uint32_t sb = first / kSuperTiles;
 	{
-		const uint32_t t = atomicAdd(cv.ticket, 1u);
-		if(t == cv.n_chunks - 1)
-			*cv.ticket = 0; // every chunk of this launch has its ticket: rearm for the next launch
-		s_chunk = t;
-	}
-	__syncthreads();
-	const uint32_t chunk = s_chunk;
-	const uint32_t r0 = chunk * kCompactChunk + tid * kCompactPerThread;
-
-	uint32_t slots[kCompactPerThread];
-	uint32_t vb[kCompactPerThread / 4];
-	if(r0 + kCompactPerThread <= cv.n)
-	{
-		const uint4 *p = reinterpret_cast<const uint4 *>(cv.slot_of_rank + r0);
-#pragma unroll
-		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
-		{
-			const uint4 v = p[q];
-			slots[q * 4 + 0] = v.x; slots[q * 4 + 1] = v.y; slots[q * 4 + 2] = v.z; slots[q * 4 + 3] = v.w;
-		}
-#pragma unroll
-		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
-		{
-			vb[q] = (uint32_t)cv.vis[slots[q * 4 + 0]] | ((uint32_t)cv.vis[slots[q * 4 + 1]] << 8) |
-			        ((uint32_t)cv.vis[slots[q * 4 + 2]] << 16) | ((uint32_t)cv.vis[slots[q * 4 + 3]] << 24);
-		}
-	}
-	else
-	{
-#pragma unroll
-		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
-		{
-			vb[q] = 0;
-#pragma unroll
-			for(int k = 0; k < 4; k++)
-			{
-				const uint32_t r = r0 + q * 4 + k;
-				slots[q * 4 + k] = 0;
-				if(r < cv.n)
-				{
-					const uint32_t sl = cv.slot_of_rank[r];
-					slots[q * 4 + k] = sl;
-					vb[q] |= (uint32_t)cv.vis[sl] << (8 * k);
-				}
-			}
-		}
-	}
-
-	// per-thread counts, two cameras per word (16 bits each: a chunk holds 4096 nodes)
-	uint32_t pk[4];
-#pragma unroll
-	for(int h = 0; h < 4; h++)
-	{
-		uint32_t lo = 0, hi = 0;
-#pragma unroll
-		for(int q = 0; q < (int)kCompactPerThread / 4; q++)
-		{
-			lo += (vb[q] >> (2 * h)) & 0x01010101u;
-			hi += (vb[q] >> (2 * h + 1)) & 0x01010101u;
-		}
-		lo = (lo * 0x01010101u) >> 24;
-		hi = (hi * 0x01010101u) >> 24;
-		pk[h] = lo | (hi << 16);
-	}
-	// inclusive scan inside the warp, then across the warps
-	uint32_t inc[4];
-#pragma unroll
-	for(int h = 0; h < 4; h++)
-	{
-		uint32_t x = pk[h];
+		const uint32_t c = warp; // 8 warps = RN_MAX_CAMERAS
+		uint32_t acc = 0;
+		for(uint32_t q = lane; q < sb; q += 32)
+			acc += ev.super_totals[q * RN_MAX_CAMERAS + c];
+		for(uint32_t t = sb * kSuperTiles + lane; t < first; t += 32)
+			acc += ev.tile_counts[t * RN_MAX_CAMERAS + c];
+		acc = __reduce_add_sync(0xffffffffu, acc);
+		const uint32_t t = first + lane;
+		const uint32_t cnt = t < ev.n_tiles ? ev.tile_counts[t * RN_MAX_CAMERAS + c] : 0u;
+		uint32_t x = cnt;
 #pragma unroll
 		for(int o = 1; o < 32; o <<= 1)
 		{
@@ -737,88 +719,57 @@ __global__ void __launch_bounds__(kCompactThreads) compact_kernel(const __grid_c
 			if(lane >= (uint32_t)o)
 				x += y;
 		}
-		inc[h] = x;
-		if(lane == 31)
-			s_warp[warp][h] = x;
+		s_off[lane][c] = acc + x - cnt;
+		s_cnt[lane][c] = cnt;
+		if(blockIdx.x == gridDim.x - 1 && lane == 31 && c < ev.n_cams)
+			ev.list_counts[c] = acc + x;
 	}
 	__syncthreads();
-	uint32_t excl[4], total[4];
-#pragma unroll
-	for(int h = 0; h < 4; h++)
+	const uint32_t lt_mask = (1u << lane) - 1u;
+	for(uint32_t k = warp; k < kEmitTiles; k += kEmitThreads / 32)
 	{
-		uint32_t pre = 0, tot = 0;
+		const uint32_t t = first + k;
+		if(t >= ev.n_tiles)
+			break;
+		// cameras that see anything of this tile (most tiles are invisible to most cameras)
+		uint32_t cams = 0;
+		uint32_t off[RN_MAX_CAMERAS];
 #pragma unroll
-		for(uint32_t w = 0; w < kCompactThreads / 32; w++)
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
 		{
-			const uint32_t x = s_warp[w][h];
-			pre += w < warp ? x : 0;
-			tot += x;
+			off[c] = s_off[k][c];
+			if((uint32_t)c < ev.n_cams && s_cnt[k][c])
+				cams |= 1u << c;
 		}
-		excl[h] = pre + inc[h] - pk[h];
-		total[h] = tot;
-	}
-
-	// decoupled look-back: warp c resolves camera c
-	if(warp < cv.n_cams)
-	{
-		const uint32_t cam = warp;
-		uint32_t tw = total[0];
-		if((cam >> 1) == 1) tw = total[1];
-		if((cam >> 1) == 2) tw = total[2];
-		if((cam >> 1) == 3) tw = total[3];
-		const uint32_t mine = (tw >> (16 * (cam & 1))) & 0xffffu;
-		volatile unsigned long long *st = cv.status;
-		uint32_t base = 0;
-		if(chunk > 0)
+		if(!cams)
+			continue;
+		const uint32_t start = ev.tiles[t].start, count = ev.tiles[t].count;
+		for(uint32_t r0 = 0; r0 < count; r0 += 32 * kEmitUnroll)
 		{
-			if(lane == 0)
-				st[(size_t)chunk * RN_MAX_CAMERAS + cam] = status_pack(cv.epoch, 1, mine);
-			int p = (int)chunk - 1;
-			while(true)
-			{
-				const int idx = p - (int)lane;
-				unsigned long long sw = status_pack(cv.epoch, 2, 0); // virtual predecessor of chunk 0
-				if(idx >= 0)
-					sw = st[(size_t)idx * RN_MAX_CAMERAS + cam];
-				const uint32_t state = ((uint32_t)(sw >> 34) == cv.epoch) ? (uint32_t)(sw >> 32) & 3u : 0u;
-				const uint32_t inc_mask = __ballot_sync(0xffffffffu, state == 2);
-				const uint32_t inv_mask = __ballot_sync(0xffffffffu, state == 0);
-				const uint32_t first = inc_mask ? (uint32_t)__ffs((int)inc_mask) - 1u : 31u;
-				const uint32_t need = (2u << first) - 1u; // lanes 0..first
-				if(inv_mask & need)
-					continue; // a predecessor has not published yet
-				uint32_t v = ((need >> lane) & 1u) ? (uint32_t)sw : 0u;
+			uint32_t slot[kEmitUnroll], v[kEmitUnroll];
 #pragma unroll
-				for(int o = 16; o > 0; o >>= 1)
-					v += __shfl_xor_sync(0xffffffffu, v, o);
-				base += v;
-				if(inc_mask)
-					break;
-				p -= 32;
+			for(int u = 0; u < (int)kEmitUnroll; u++)
+			{
+				const uint32_t r = r0 + u * 32 + lane;
+				slot[u] = r < count ? ev.slot_of_rank[start + r] : 0xffffffffu;
 			}
-		}
-		if(lane == 0)
-		{
-			st[(size_t)chunk * RN_MAX_CAMERAS + cam] = status_pack(cv.epoch, 2, base + mine);
-			s_base[cam] = base;
-			if(chunk == cv.n_chunks - 1)
-				cv.list_counts[cam] = base + mine;
-		}
-	}
-	__syncthreads();
-
 #pragma unroll
-	for(int c = 0; c < RN_MAX_CAMERAS; c++)
-	{
-		if((uint32_t)c < cv.n_cams)
-		{
-			uint32_t pos = s_base[c] + ((excl[c >> 1] >> (16 * (c & 1))) & 0xffffu);
-			uint32_t *out = cv.lists[c];
+			for(int u = 0; u < (int)kEmitUnroll; u++)
+				v[u] = slot[u] != 0xffffffffu ? ev.vis[slot[u]] : 0u;
 #pragma unroll
-			for(int k = 0; k < (int)kCompactPerThread; k++)
+			for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			{
-				if((vb[k >> 2] >> (8 * (k & 3) + c)) & 1u)
-					out[pos++] = slots[k];
+				if((cams >> c) & 1u)
+				{
+#pragma unroll
+					for(int u = 0; u < (int)kEmitUnroll; u++)
+					{
+						const uint32_t m = __ballot_sync(0xffffffffu, (v[u] >> c) & 1u);
+						if((v[u] >> c) & 1u)
+							ev.lists[c][off[c] + __popc(m & lt_mask)] = slot[u];
+						off[c] += __popc(m);
+					}
+				}
 			}
 		}
 	}
@@ -1056,7 +1007,7 @@ static int dev_alloc(rn_scene *s, T **p, size_t count)
 static void free_nodes(rn_scene *s)
 {
 	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->d_slot_of_rank, s->vis, s->tiles,
-	                s->status, s->ticket, s->list_counts, s->spine_slots, s->scratch_cols};
+	                s->tile_counts, s->super_totals, s->list_counts, s->spine_slots, s->scratch_cols};
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
@@ -1068,7 +1019,7 @@ static void free_nodes(rn_scene *s)
 			if(s->prof_ev[i][k]) { cudaEventDestroy(s->prof_ev[i][k]); s->prof_ev[i][k] = nullptr; }
 	s->c0 = s->c1 = s->c2 = s->c3 = s->wpos = s->wrot = s->wmat = nullptr;
 	s->wsyz = nullptr; s->d_slot_of_rank = nullptr; s->vis = nullptr; s->tiles = nullptr;
-	s->status = nullptr; s->ticket = s->list_counts = s->spine_slots = nullptr;
+	s->tile_counts = s->super_totals = s->list_counts = s->spine_slots = nullptr;
 	s->scratch_cols = nullptr;
 }
 
@@ -1077,7 +1028,7 @@ static SceneView make_view(const rn_scene *s)
 	SceneView v;
 	v.c0 = s->c0; v.c1 = s->c1; v.c2 = s->c2; v.c3 = s->c3;
 	v.wpos = s->wpos; v.wrot = s->wrot; v.wsyz = s->wsyz; v.wmat = s->wmat;
-	v.vis = s->vis; v.tiles = s->tiles;
+	v.vis = s->vis; v.tiles = s->tiles; v.tile_counts = s->tile_counts; v.super_totals = s->super_totals;
 	v.n_tiles = s->n_tiles; v.inner_cap = s->inner_cap; v.warp_smem = warp_smem_bytes(s->inner_cap); v.n = s->n;
 	return v;
 }
@@ -1142,9 +1093,16 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 	return RN_OK;
 }
 
+static int clear_super_totals(rn_scene *s, cudaStream_t stream)
+{
+	const size_t supers = (s->n_tiles + kSuperTiles - 1) / kSuperTiles;
+	RN_CUDA(cudaMemsetAsync(s->super_totals, 0, supers * RN_MAX_CAMERAS * sizeof(uint32_t), stream));
+	return RN_OK;
+}
+
 static int launch_cull_flat(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 {
-	const uint32_t grid = std::min<uint32_t>((s->n + 255) / 256, 148u * 64u);
+	const uint32_t grid = (s->n_tiles + 7) / 8;
 	cull_kernel<<<grid, 256, 0, stream>>>(make_view(s), cp);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
@@ -1153,26 +1111,17 @@ static int launch_cull_flat(rn_scene *s, const CullParams &cp, cudaStream_t stre
 
 static int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
 {
-	CompactView cv;
-	cv.vis = s->vis;
-	cv.slot_of_rank = s->d_slot_of_rank;
-	for(int c = 0; c < RN_MAX_CAMERAS; c++) cv.lists[c] = s->lists[c];
-	cv.list_counts = s->list_counts;
-	cv.status = s->status;
-	cv.ticket = s->ticket;
-	cv.n = s->n;
-	cv.n_cams = ncams;
-	cv.n_chunks = (s->n + kCompactChunk - 1) / kCompactChunk;
-	s->epoch = (s->epoch + 1) & 0x3fffffffu;
-	if(s->epoch == 0)
-	{
-		// the 30-bit epoch wrapped: forget every stale entry
-		const size_t chunks = ((size_t)s->desc.max_nodes + kCompactChunk - 1) / kCompactChunk;
-		RN_CUDA(cudaMemsetAsync(s->status, 0, chunks * RN_MAX_CAMERAS * sizeof(unsigned long long), stream));
-		s->epoch = 1;
-	}
-	cv.epoch = s->epoch;
-	compact_kernel<<<cv.n_chunks, kCompactThreads, 0, stream>>>(cv);
+	EmitView ev;
+	ev.vis = s->vis;
+	ev.slot_of_rank = s->d_slot_of_rank;
+	ev.tiles = s->tiles;
+	ev.tile_counts = s->tile_counts;
+	ev.super_totals = s->super_totals;
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) ev.lists[c] = s->lists[c];
+	ev.list_counts = s->list_counts;
+	ev.n_tiles = s->n_tiles;
+	ev.n_cams = ncams;
+	emit_kernel<<<(s->n_tiles + kEmitTiles - 1) / kEmitTiles, kEmitThreads, 0, stream>>>(ev);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
@@ -1249,9 +1198,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	if(!rc) rc = dev_alloc(s, &s->wmat, n * 4);
 	if(!rc) rc = dev_alloc(s, &s->d_slot_of_rank, n);
 	if(!rc) rc = dev_alloc(s, &s->vis, n);
-	const size_t chunks = (n + kCompactChunk - 1) / kCompactChunk;
-	if(!rc) rc = dev_alloc(s, &s->status, chunks * RN_MAX_CAMERAS);
-	if(!rc) rc = dev_alloc(s, &s->ticket, (size_t)1);
+
 	if(!rc) rc = dev_alloc(s, &s->list_counts, (size_t)RN_MAX_CAMERAS);
 	if(!rc) rc = dev_alloc(s, &s->spine_slots, n);
 	if(rc)
@@ -1261,8 +1208,6 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 		return rc;
 	}
 	cudaMemset(s->list_counts, 0, sizeof(uint32_t) * RN_MAX_CAMERAS);
-	cudaMemset(s->status, 0, chunks * RN_MAX_CAMERAS * sizeof(unsigned long long));
-	cudaMemset(s->ticket, 0, sizeof(uint32_t));
 	*out = s;
 	return RN_OK;
 }
@@ -1331,8 +1276,12 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
+	if(s->tile_counts) { cudaFree(s->tile_counts); s->tile_counts = nullptr; }
+	if(s->super_totals) { cudaFree(s->super_totals); s->super_totals = nullptr; }
 	const size_t nt = t.tiles.size();
 	int rc = dev_alloc(s, &s->tiles, nt);
+	if(!rc) rc = dev_alloc(s, &s->tile_counts, nt * RN_MAX_CAMERAS);
+	if(!rc) rc = dev_alloc(s, &s->super_totals, ((nt + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS);
 	if(rc) return rc;
 	if(nt) RN_CUDA(cudaMemcpy(s->tiles, t.tiles.data(), sizeof(TileMeta) * nt, cudaMemcpyHostToDevice));
 
@@ -1456,7 +1405,8 @@ extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t
 	rc = ensure_lists(s, n_cameras);
 	if(rc) return rc;
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-	rc = launch_cull_flat(s, cp, stream);
+	rc = clear_super_totals(s, stream);
+	if(!rc) rc = launch_cull_flat(s, cp, stream);
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->last_ncams = n_cameras;
@@ -1476,7 +1426,8 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	rc = ensure_lists(s, n_cameras);
 	if(rc) return rc;
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-	rc = launch_spine(s, stream);
+	rc = clear_super_totals(s, stream);
+	if(!rc) rc = launch_spine(s, stream);
 	if(!rc) rc = launch_tiles<true>(s, cp, stream);
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
