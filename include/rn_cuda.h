@@ -148,11 +148,20 @@ int rn_cull(rn_scene_t *scene, const rn_camera_frustum *cameras, uint32_t n_came
             void *cuda_stream);
 int rn_transform_cull(rn_scene_t *scene, const rn_camera_frustum *cameras, uint32_t n_cameras,
                       rn_vis_list *out_lists, void *cuda_stream);
+/* What the visibility lists hold.  ranks == 0 (default): slots (index the device outputs directly).
+ * ranks != 0: render-list ranks plus `rank_offset` - the form in which the lists of the GPUs of one box are
+ * exchanged (each GPU owns an ascending rank range starting at its rank_offset). */
+int rn_scene_set_list_mode(rn_scene_t *scene, int ranks, uint32_t rank_offset);
 /* Synchronises the stream and copies the per-camera visible counts of the last cull to the host. */
 int rn_cull_read_counts(rn_scene_t *scene, uint32_t *out_counts, uint32_t n_cameras, void *cuda_stream);
 /* Copies the visibility list of one camera to the host (synchronous). `out_slots` has `capacity` entries. */
 int rn_cull_read_list(rn_scene_t *scene, uint32_t camera, uint32_t *out_slots, uint32_t capacity,
                       uint32_t *out_count, void *cuda_stream);
+
+/* Copies the counts and the lists of cameras 0..n_cameras-1 of the last cull to the host in one go (one
+ * synchronisation for the counts, then all list copies back to back).  out_slots[c] has capacities[c] entries. */
+int rn_cull_read_lists(rn_scene_t *scene, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
+                       uint32_t *out_counts, void *cuda_stream);
 
 /* Synchronous read-back in RANK order (parity tests, SetWorldPosition & co on the host side). */
 int rn_scene_download(rn_scene_t *scene, rn_download_what what, uint32_t first, uint32_t count, void *dst);

@@ -22,7 +22,7 @@ PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
 EXPORTS = [
     "rn_last_error", "rn_abi_version", "rn_scene_create", "rn_scene_destroy", "rn_scene_upload",
     "rn_scene_update_nodes", "rn_scene_node_count", "rn_transform_propagate", "rn_cull", "rn_transform_cull",
-    "rn_cull_read_counts", "rn_cull_read_list", "rn_scene_download", "rn_scene_device_outputs",
+    "rn_scene_set_list_mode", "rn_cull_read_counts", "rn_cull_read_list", "rn_cull_read_lists", "rn_scene_download", "rn_scene_device_outputs",
     "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
     "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
     "rn_scene_profile", "rn_scene_profile_read",
@@ -188,7 +188,8 @@ class SceneHandle:
         self.close()
 
     # ---- nodes ----
-    def upload(self, rs: RankedScene) -> None:
+    def upload(self, rs) -> None:
+        """rs: RankedScene or shard.ShardColumns (node columns in rank order)."""
         cols = NodeColumns(_ptr(_f32(rs.position, 3)), _ptr(_f32(rs.scale, 3)), _ptr(_f32(rs.rotation, 4)),
                            _ptr(np.ascontiguousarray(rs.parent, dtype=np.uint32)),
                            _ptr(np.ascontiguousarray(rs.flags, dtype=np.uint32)),
@@ -226,6 +227,9 @@ class SceneHandle:
     def transform_cull(self, frustums: np.ndarray, stream: int = 0):
         return self._cull(self.lib.rn_transform_cull, frustums, stream)
 
+    def set_list_mode(self, ranks: bool, rank_offset: int = 0) -> None:
+        _check(self.lib.rn_scene_set_list_mode(self._h, int(ranks), C.c_uint32(rank_offset)))
+
     def read_counts(self, stream: int = 0) -> np.ndarray:
         out = np.zeros(self.ncams, dtype=np.uint32)
         _check(self.lib.rn_cull_read_counts(self._h, _ptr(out), self.ncams, C.c_void_p(stream)))
@@ -243,6 +247,15 @@ class SceneHandle:
         cnt = C.c_uint32()
         _check(self.lib.rn_cull_read_list(self._h, camera, C.c_void_p(out_ptr), capacity, C.byref(cnt), C.c_void_p(stream)))
         return cnt.value
+
+    def read_lists_into(self, out_ptrs: list[int], capacities: list[int], stream: int = 0) -> np.ndarray:
+        """rn_cull_read_lists into caller-owned (pinned) host buffers; returns the counts."""
+        n = len(out_ptrs)
+        ptrs = (C.c_void_p * n)(*out_ptrs)
+        caps = (C.c_uint32 * n)(*capacities)
+        counts = np.zeros(n, dtype=np.uint32)
+        _check(self.lib.rn_cull_read_lists(self._h, n, ptrs, caps, _ptr(counts), C.c_void_p(stream)))
+        return counts
 
     def download(self, what: int, first: int = 0, count: int | None = None) -> np.ndarray:
         count = self.n - first if count is None else count

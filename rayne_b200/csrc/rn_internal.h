@@ -57,6 +57,8 @@ struct rn_scene
 	uint64_t launches = 0;
 	bool have_world = false;     // world TRS valid (a propagate ran since the last upload)
 	uint32_t last_ncams = 0;
+	uint32_t list_rank_mode = 0;     // 1: visibility lists hold rank + list_rank_offset instead of slots
+	uint32_t list_rank_offset = 0;
 
 	// node columns, slot order (float4 each): c0 = pos.xyz, scale.x ; c1 = rot ; c2 = scale.y, scale.z,
 	// parent slot (bits), flags|group<<8 (bits) ; c3 = sphere offset.xyz, radius

@@ -679,7 +679,7 @@ __global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ Scene
 // and writes the slots of the visible nodes with ballot/popc ranking.  List order = render-list order, exactly.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr uint32_t kEmitThreads = 256;
-constexpr uint32_t kEmitTiles = 32;
+constexpr uint32_t kEmitTiles = 16;
 constexpr uint32_t kEmitUnroll = 4;
 
 struct EmitView
@@ -692,9 +692,11 @@ struct EmitView
 	uint32_t *lists[RN_MAX_CAMERAS];
 	uint32_t *list_counts;
 	uint32_t n_tiles, n_cams;
+	uint32_t rank_mode;             // 0: lists hold slots; 1: lists hold rank + rank_offset (multi-GPU exchange)
+	uint32_t rank_offset;
 };
 
-__global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constant__ EmitView ev)
+__global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_constant__ EmitView ev)
 {
 	__shared__ uint32_t s_off[kEmitTiles][RN_MAX_CAMERAS];
 	__shared__ uint32_t s_cnt[kEmitTiles][RN_MAX_CAMERAS];
@@ -710,7 +712,7 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constan
 			acc += ev.tile_counts[t * RN_MAX_CAMERAS + c];
 		acc = __reduce_add_sync(0xffffffffu, acc);
 		const uint32_t t = first + lane;
-		const uint32_t cnt = t < ev.n_tiles ? ev.tile_counts[t * RN_MAX_CAMERAS + c] : 0u;
+		const uint32_t cnt = (lane < kEmitTiles && t < ev.n_tiles) ? ev.tile_counts[t * RN_MAX_CAMERAS + c] : 0u;
 		uint32_t x = cnt;
 #pragma unroll
 		for(int o = 1; o < 32; o <<= 1)
@@ -719,8 +721,11 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constan
 			if(lane >= (uint32_t)o)
 				x += y;
 		}
-		s_off[lane][c] = acc + x - cnt;
-		s_cnt[lane][c] = cnt;
+		if(lane < kEmitTiles)
+		{
+			s_off[lane][c] = acc + x - cnt;
+			s_cnt[lane][c] = cnt;
+		}
 		if(blockIdx.x == gridDim.x - 1 && lane == 31 && c < ev.n_cams)
 			ev.list_counts[c] = acc + x;
 	}
@@ -755,7 +760,11 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constan
 			}
 #pragma unroll
 			for(int u = 0; u < (int)kEmitUnroll; u++)
+			{
 				v[u] = slot[u] != 0xffffffffu ? ev.vis[slot[u]] : 0u;
+				if(ev.rank_mode)
+					slot[u] = start + r0 + u * 32 + lane + ev.rank_offset;
+			}
 #pragma unroll
 			for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			{
@@ -765,9 +774,12 @@ __global__ void __launch_bounds__(kEmitThreads) emit_kernel(const __grid_constan
 					for(int u = 0; u < (int)kEmitUnroll; u++)
 					{
 						const uint32_t m = __ballot_sync(0xffffffffu, (v[u] >> c) & 1u);
-						if((v[u] >> c) & 1u)
-							ev.lists[c][off[c] + __popc(m & lt_mask)] = slot[u];
-						off[c] += __popc(m);
+						if(m)
+						{
+							if((v[u] >> c) & 1u)
+								ev.lists[c][off[c] + __popc(m & lt_mask)] = slot[u];
+							off[c] += __popc(m);
+						}
 					}
 				}
 			}
@@ -1121,6 +1133,8 @@ static int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
 	ev.list_counts = s->list_counts;
 	ev.n_tiles = s->n_tiles;
 	ev.n_cams = ncams;
+	ev.rank_mode = s->list_rank_mode;
+	ev.rank_offset = s->list_rank_offset;
 	emit_kernel<<<(s->n_tiles + kEmitTiles - 1) / kEmitTiles, kEmitThreads, 0, stream>>>(ev);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
@@ -1437,6 +1451,14 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	return RN_OK;
 }
 
+extern "C" int rn_scene_set_list_mode(rn_scene_t *s, int ranks, uint32_t rank_offset)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	s->list_rank_mode = ranks ? 1u : 0u;
+	s->list_rank_offset = ranks ? rank_offset : 0u;
+	return RN_OK;
+}
+
 extern "C" int rn_cull_read_counts(rn_scene_t *s, uint32_t *out_counts, uint32_t n_cameras, void *cuda_stream)
 {
 	RN_REQUIRE(s && out_counts, RN_ERR_INVALID, "NULL argument");
@@ -1468,6 +1490,25 @@ extern "C" int rn_cull_read_list(rn_scene_t *s, uint32_t camera, uint32_t *out_s
 			RN_CUDA(cudaStreamSynchronize(stream));
 		}
 	}
+	return RN_OK;
+}
+
+extern "C" int rn_cull_read_lists(rn_scene_t *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
+                                  uint32_t *out_counts, void *cuda_stream)
+{
+	RN_REQUIRE(s && out_slots && capacities && out_counts, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(n_cameras <= s->last_ncams, RN_ERR_STATE, "the last cull had %u cameras, %u requested", s->last_ncams, n_cameras);
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	RN_CUDA(cudaMemcpyAsync(out_counts, s->list_counts, sizeof(uint32_t) * n_cameras, cudaMemcpyDeviceToHost, stream));
+	RN_CUDA(cudaStreamSynchronize(stream));
+	for(uint32_t c = 0; c < n_cameras; c++)
+	{
+		RN_REQUIRE(out_counts[c] <= capacities[c], RN_ERR_CAPACITY, "list of camera %u has %u entries, buffer holds %u", c, out_counts[c], capacities[c]);
+		if(out_counts[c] && out_slots[c])
+			RN_CUDA(cudaMemcpyAsync(out_slots[c], s->lists[c], sizeof(uint32_t) * out_counts[c], cudaMemcpyDeviceToHost, stream));
+	}
+	RN_CUDA(cudaStreamSynchronize(stream));
 	return RN_OK;
 }
 

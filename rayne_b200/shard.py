@@ -1,0 +1,132 @@
+"""Multi-GPU sharding of the scene path: one process per GPU, node ranges cut at subtree
+boundaries, no data-path collective until the per-camera visibility lists are gathered.
+
+* ``plan_shards``    - contiguous ranges of render-list RANKS, cut only where no parent/child edge crosses, so every
+                       rank's world transforms depend on local nodes alone (no halo, no transform exchange).
+* ``extract_shard``  - the node columns of one range with the parent column rebased to local ranks.
+* ``ListExchange``   - the path's only collective: all-gather of the per-camera visible counts, then of the index
+                       lists (padded to the largest count), over ``torch.distributed`` (NCCL on the GPUs, gloo in the
+                       CPU tests).  Lists travel as GLOBAL ranks; concatenating the ranks' lists in rank order IS the
+                       reference's render-list order because every rank owns an ascending rank range and its local
+                       compaction is order-stable.
+
+Nothing here computes transforms or visibility: that is librn_cuda's job on each GPU.
+"""
+from __future__ import annotations
+
+import dataclasses
+
+import numpy as np
+
+RN_NO_PARENT = 0xFFFFFFFF
+
+
+@dataclasses.dataclass
+class ShardColumns:
+    """What capi.SceneHandle.upload needs (same attribute names as capi.RankedScene) for one rank range."""
+    first: int
+    position: np.ndarray
+    scale: np.ndarray
+    rotation: np.ndarray
+    parent: np.ndarray
+    flags: np.ndarray
+    group: np.ndarray
+    sphere: np.ndarray
+
+    @property
+    def n(self) -> int:
+        return int(self.parent.shape[0])
+
+
+def valid_cuts(parent: np.ndarray) -> np.ndarray:
+    """Boolean array c[0..n]: c[r] is True iff no parent/child edge crosses the boundary between ranks r-1 and r."""
+    parent = np.asarray(parent)
+    n = parent.shape[0]
+    child = np.nonzero(parent != RN_NO_PARENT)[0].astype(np.int64)
+    par = parent[child].astype(np.int64)
+    lo = np.minimum(child, par)
+    hi = np.maximum(child, par)
+    # the edge (lo, hi) crosses every boundary r with lo < r <= hi
+    cover = np.zeros(n + 2, dtype=np.int64)
+    np.add.at(cover, lo + 1, 1)
+    np.add.at(cover, hi + 1, -1)
+    crossing = np.cumsum(cover)[: n + 1]
+    return crossing == 0
+
+
+def plan_shards(parent: np.ndarray, world: int) -> list[tuple[int, int]]:
+    """Splits ranks [0, n) into ``world`` contiguous ranges of near-equal size whose boundaries cross no edge.
+    Raises ValueError if the hierarchy offers fewer than ``world`` independent pieces."""
+    n = int(np.asarray(parent).shape[0])
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    ok = np.nonzero(valid_cuts(parent))[0]          # sorted, always contains 0 and n
+    if ok.shape[0] < world + 1:
+        raise ValueError(f"the hierarchy cannot be split into {world} edge-free rank ranges "
+                         f"(only {ok.shape[0] - 1} independent pieces)")
+    idx = [0]
+    for k in range(1, world):
+        target = (n * k) // world
+        lo_i = idx[-1] + 1                          # strictly after the previous cut
+        hi_i = ok.shape[0] - 1 - (world - k)        # leave one cut for every later boundary
+        i = int(np.searchsorted(ok, target))
+        cands = [j for j in (i - 1, i) if lo_i <= j <= hi_i]
+        if not cands:
+            cands = [min(max(i, lo_i), hi_i)]
+        idx.append(min(cands, key=lambda j: abs(int(ok[j]) - target)))
+    bounds = [int(ok[j]) for j in idx] + [n]
+    return list(zip(bounds[:-1], bounds[1:]))
+
+
+def extract_shard(rs, first: int, last: int) -> ShardColumns:
+    """Columns of ranks [first, last) of a capi.RankedScene (or anything with its attributes)."""
+    p = np.asarray(rs.parent[first:last])
+    has = p != RN_NO_PARENT
+    if has.any():
+        inside = (p[has] >= first) & (p[has] < last)
+        if not inside.all():
+            raise ValueError("a parent/child edge crosses the shard boundary: use plan_shards")
+    local = np.where(has, p.astype(np.int64) - first, RN_NO_PARENT).astype(np.uint32)
+    sl = slice(first, last)
+    return ShardColumns(first, np.ascontiguousarray(rs.position[sl]), np.ascontiguousarray(rs.scale[sl]),
+                        np.ascontiguousarray(rs.rotation[sl]), local, np.ascontiguousarray(rs.flags[sl]),
+                        np.ascontiguousarray(rs.group[sl]), np.ascontiguousarray(rs.sphere[sl]))
+
+
+class ListExchange:
+    """All-gather of per-camera visibility lists across the ranks of a torch.distributed process group."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+
+    def gather_counts(self, counts):
+        """counts: int32 tensor [ncams] on the collective's device -> int32 tensor [world, ncams]."""
+        import torch
+        out = torch.empty(self.world * counts.numel(), dtype=counts.dtype, device=counts.device)
+        self.dist.all_gather_into_tensor(out, counts.contiguous(), group=self.group)
+        return out.view(self.world, counts.numel())
+
+    def gather_lists(self, lists, all_counts_host):
+        """lists[c]: 1-D int32 tensor with at least max-over-ranks(count[c]) readable entries (global ranks, only the
+        first count[c] are meaningful).  all_counts_host: [world, ncams] on the host.
+        Returns per camera a list of ``world`` views (rank r's visible global ranks), i.e. the concatenation order."""
+        import torch
+        result = []
+        for c, src in enumerate(lists):
+            m = int(all_counts_host[:, c].max())
+            if m == 0:
+                result.append([src[:0] for _ in range(self.world)])
+                continue
+            dst = torch.empty(self.world * m, dtype=src.dtype, device=src.device)
+            self.dist.all_gather_into_tensor(dst, src[:m].contiguous(), group=self.group)
+            result.append([dst[r * m: r * m + int(all_counts_host[r, c])] for r in range(self.world)])
+        return result
+
+    def exchange(self, counts, lists):
+        """Full exchange.  Returns (all_counts_host [world, ncams], per-camera list of per-rank views)."""
+        all_counts = self.gather_counts(counts).cpu()
+        return all_counts, self.gather_lists(lists, all_counts)

@@ -1,0 +1,117 @@
+"""CPU: the C-ABI library loads, exports every symbol include/rn_cuda.h declares, its PODs have the layout the
+ctypes binding assumes, the host-side entry points (camera frustum, render-list order) match the reference, and the
+device entry points fail loudly - not silently on a CPU path - when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from rayne_b200 import capi, scenegen as sg
+from tests.conftest import have_gpu
+from tests.helpers import GOLDEN_DIR, load_golden_scene, standard_cameras
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "rn_cuda.h")
+
+
+def declared_functions() -> list[str]:
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rn_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_the_north_star_entry_points():
+    names = declared_functions()
+    for must in ("rn_scene_upload", "rn_transform_propagate", "rn_cull", "rn_particles_step"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    lib = capi.load()
+    names = declared_functions()
+    assert len(names) >= 20
+    for name in names:
+        assert hasattr(lib, name), f"{name} is declared in include/rn_cuda.h but not exported by librn_cuda.so"
+    assert sorted(capi.EXPORTS) == names, "capi.EXPORTS and the header disagree"
+    lib.rn_abi_version.restype = C.c_int
+    assert lib.rn_abi_version() == 1
+
+
+def test_pod_layouts_match_the_header():
+    # sizes computed from the header's field lists (all 4-byte members, pointers 8 bytes)
+    assert C.sizeof(capi.SceneDesc) == 8 * 4
+    assert C.sizeof(capi.NodeColumns) == 7 * 8
+    assert C.sizeof(capi.VisList) == 2 * 8 + 8
+    assert capi.FRUSTUM_DTYPE.itemsize == (3 + 1 + 24) * 4 + 8
+    assert sg.CAMERA_DTYPE.itemsize == (2 + 3 + 4 + 3 + 4 + 4 + 4 + 1 + 16) * 4
+    assert sg.EMITTER_DTYPE.itemsize == (2 + 1 + 2 + 8 + 8 + 18) * 4
+    assert C.sizeof(capi.SceneStats) == 6 * 4 + 2 * 8
+
+
+def test_build_frustum_matches_oracle_and_golden():
+    cams = standard_cameras()
+    got = capi.build_frustums(cams)
+    assert got.tobytes() == oracle.frustums(cams).tobytes()
+    _, gcams, g = load_golden_scene("scene_ragged")
+    fr = capi.build_frustums(gcams)
+    assert np.array_equal(fr["center"], g["ref_frustum"][:, 0:3])
+    assert np.array_equal(fr["radius"], g["ref_frustum"][:, 3])
+    assert np.array_equal(fr["planes"].reshape(-1, 24), g["ref_frustum"][:, 4:28])
+
+
+@pytest.mark.parametrize("name", ["scene_uniform", "scene_nonuniform_groups_prio", "scene_ragged", "scene_deep_chain"])
+def test_render_order_matches_golden(name):
+    scene, _, g = load_golden_scene(name)
+    assert np.array_equal(capi.render_order(scene.parent, scene.priority), g["ref_order"])
+
+
+def test_render_order_probe_from_the_survey():
+    """tree 0{1{3,4},2{5,6}}, then 7, 9 (Transparent), 8 (Early), 10 (Normal)."""
+    parent = np.array([-1, 0, 0, 1, 1, 2, 2, -1, -1, -1, -1], np.int32)
+    prio = np.zeros(11, np.int32)
+    # creation order of the last three roots: 7, then 9 (transparent), 8 (early), 10 (normal)
+    # AddNode is called in creation order of the ROOTS, so renumber: ids 8 and 9 swap roles via priorities
+    prio[8] = sg.RENDER_TRANSPARENT   # added third  (the survey's node 9)
+    prio[9] = sg.RENDER_EARLY         # added fourth (the survey's node 8)
+    order = capi.render_order(parent, prio)
+    assert order.tolist() == [9, 7, 0, 2, 6, 5, 1, 4, 3, 10, 8]
+    assert np.array_equal(order, oracle.render_order(parent, prio))
+
+
+def test_render_order_rejects_bad_hierarchy():
+    with pytest.raises(capi.RNError):
+        capi.render_order(np.array([1, -1], np.int32), None)   # parent after child
+
+
+def test_argument_errors_do_not_need_a_device():
+    lib = capi.load()
+    assert lib.rn_scene_create(None, None) == -1
+    assert b"NULL" in lib.rn_last_error()
+    out = C.c_void_p()
+    desc = capi.SceneDesc(0, 0, 0, 0, 0, 0)
+    assert lib.rn_scene_create(C.byref(out), C.byref(desc)) == -1      # max_nodes = 0
+    desc = capi.SceneDesc(0, 16, 100, 0, 0, 0)
+    assert lib.rn_scene_create(C.byref(out), C.byref(desc)) == -1      # tile_nodes not a multiple of 16
+
+
+@pytest.mark.skipif(have_gpu(), reason="only meaningful on a machine without a CUDA device")
+def test_no_cpu_fallback_without_a_device():
+    """On a CPU-only box the product path must fail loudly (RN_ERR_CUDA), never compute on the host."""
+    with pytest.raises(capi.RNError) as e:
+        capi.SceneHandle(max_nodes=16)
+    assert e.value.status == -2
+    assert "CUDA" in str(e.value)
+
+
+def test_product_sources_never_touch_the_oracle():
+    """oracle/ is test infrastructure: nothing under rayne_b200/ may import, link or execute it."""
+    pkg = os.path.join(ROOT, "rayne_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+                assert "rn_oracle" not in text and "oracle/_ref" not in text, f

@@ -1,0 +1,111 @@
+"""CPU, world_size 2 over gloo: the multi-GPU host logic (rank-range planning at subtree boundaries, shard extraction,
+count + list all-gather) reproduces the single-process visibility lists.  The per-rank cull itself is stood in by the
+oracle here (there is no GPU); on the GPU box tests/test_gpu_scene.py::test_sharded_matches_single runs the same
+planner against librn_cuda."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import oracle
+from rayne_b200 import capi, scenegen as sg, shard
+from tests.helpers import standard_cameras
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_valid_cuts_and_plan():
+    #      0        3      5
+    #     / \       |
+    #    1   2      4          ranks given directly (parent by rank)
+    parent = np.array([shard.RN_NO_PARENT, 0, 0, shard.RN_NO_PARENT, 3, shard.RN_NO_PARENT], np.uint32)
+    cuts = shard.valid_cuts(parent)
+    assert cuts.tolist() == [True, False, False, True, False, True, True]
+    assert shard.plan_shards(parent, 2) == [(0, 3), (3, 6)]
+    assert shard.plan_shards(parent, 3) == [(0, 3), (3, 5), (5, 6)]
+    with pytest.raises(ValueError):
+        shard.plan_shards(parent, 5)
+    # a child ranked before its parent (render-list order is reverse post-order in the reference)
+    parent = np.array([1, shard.RN_NO_PARENT, 3, shard.RN_NO_PARENT], np.uint32)
+    assert shard.valid_cuts(parent).tolist() == [True, False, True, False, True]
+
+
+def test_plan_balances_a_forest():
+    scene = sg.make_scene(n_trees=64, branching=4, depth=5, seed=5)
+    rs = capi.RankedScene(scene)
+    for world in (2, 4, 8):
+        ranges = shard.plan_shards(rs.parent, world)
+        sizes = [b - a for a, b in ranges]
+        assert sum(sizes) == scene.n and ranges[0][0] == 0 and ranges[-1][1] == scene.n
+        assert max(sizes) - min(sizes) <= 341  # one tree
+        for a, b in ranges:
+            sh = shard.extract_shard(rs, a, b)
+            assert sh.n == b - a
+            p = sh.parent[sh.parent != shard.RN_NO_PARENT]
+            assert (p < sh.n).all()
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank: int, world: int, port: int, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        scene = sg.make_scene(n_trees=24, branching=4, depth=5, seed=31, random_bounds=True, random_groups=True)
+        cams = standard_cameras()
+        fr = oracle.frustums(cams)
+        rs = capi.RankedScene(scene)
+        ranges = shard.plan_shards(rs.parent, world)
+        a, b = ranges[rank]
+        sh = shard.extract_shard(rs, a, b)
+        # stand-in for librn_cuda on this rank's GPU: world transforms + cull of the local range only
+        wpos, wrot, wscale, _ = oracle.world(sh.parent, sh.position, sh.scale, sh.rotation)
+        local = [oracle.cull(wpos, wrot, wscale, sh.sphere, sh.flags, sh.group, f) for f in fr]
+        cap = max(sh.n, 1)
+        lists = []
+        for l in local:
+            t = torch.zeros(scene.n, dtype=torch.int32)      # capacity >= any rank's count
+            t[: len(l)] = torch.from_numpy((l.astype(np.int64) + a).astype(np.int32))
+            lists.append(t)
+        counts = torch.tensor([len(l) for l in local], dtype=torch.int32)
+        ex = shard.ListExchange()
+        all_counts, gathered = ex.exchange(counts, lists)
+        merged = [torch.cat(parts).numpy().astype(np.uint32) for parts in gathered]
+        if rank == 0:
+            q.put((all_counts.numpy(), merged, ranges))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_exchange_matches_single_process():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    all_counts, merged, ranges = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    scene = sg.make_scene(n_trees=24, branching=4, depth=5, seed=31, random_bounds=True, random_groups=True)
+    cams = standard_cameras()
+    ref = oracle.scene_reference(scene, oracle.frustums(cams))
+    rs = capi.RankedScene(scene)
+    assert len(ranges) == 2 and all_counts.shape == (2, len(cams))
+    for c in range(len(cams)):
+        want_ranks = rs.rank_of[ref["lists"][c]]            # creation ids -> global ranks, already ascending
+        assert np.array_equal(merged[c], want_ranks), f"camera {c}"
+        assert int(all_counts[:, c].sum()) == len(want_ranks)

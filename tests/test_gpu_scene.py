@@ -99,3 +99,51 @@ def test_full_size_properties():
     got2 = run_cuda(scene, fr, fused=False)
     assert all(np.array_equal(a, b) for a, b in zip(got["lists"], got2["lists"]))
     assert same_floats(got["wmat"], got2["wmat"])
+
+
+def test_sharded_matches_single():
+    """rank ranges cut at subtree boundaries, each culled on its own handle (one per GPU in
+    production), lists in global-rank form; their concatenation is the single-GPU / reference list."""
+    from rayne_b200 import shard
+    from oracle import oracle
+    scene = sg.make_scene(n_trees=40, branching=4, depth=6, seed=17, random_bounds=True, random_groups=True)
+    cams = standard_cameras()
+    fr = capi.build_frustums(cams)
+    rs = capi.RankedScene(scene)
+    ref = oracle.scene_reference(scene, fr)
+    want = [rs.rank_of[l] for l in ref["lists"]]
+    for world in (1, 3, 8):
+        parts = [[] for _ in fr]
+        for a, b in shard.plan_shards(rs.parent, world):
+            with capi.SceneHandle(max_nodes=b - a) as h:
+                h.upload(shard.extract_shard(rs, a, b))
+                h.set_list_mode(True, a)
+                h.transform_cull(fr)
+                for c in range(len(fr)):
+                    parts[c].append(h.read_list(c))
+        for c in range(len(fr)):
+            assert np.array_equal(np.concatenate(parts[c]), want[c]), (world, c)
+
+
+def test_classifier_edge_cases():
+    """Negative and huge scales, zero radii, nodes exactly on planes, clusters straddling every plane: the warp-level
+    classifier must never change a decision of the exact test."""
+    scene = sg.make_scene(n_trees=30, branching=4, depth=5, seed=77, random_bounds=True, nonuniform_scale=True)
+    rng = np.random.Generator(np.random.PCG64(5))
+    n = scene.n
+    neg = rng.random(n) < 0.05
+    scene.scale[neg] *= np.float32(-1.0)                     # negative world scale -> negative radius (signed max)
+    big = rng.random(n) < 0.01
+    scene.scale[big] *= np.float32(1e4)
+    scene.sphere[rng.random(n) < 0.05, 3] = 0.0
+    # shrink the scene so that many subtrees straddle the frustum planes of the cameras at the origin
+    scene.pos *= np.float32(0.05)
+    check_against_oracle(scene, standard_cameras())
+    # positions that make plane distances exactly equal to the radius for axis-aligned planes
+    flat = sg.make_scene(n_trees=2000, branching=1, depth=1, seed=3)
+    flat.pos[:, 0] = np.float32(0.0)
+    flat.pos[:, 1] = np.float32(0.0)
+    flat.pos[:, 2] = -np.linspace(0.0, 510.0, flat.n, dtype=np.float32)
+    flat.sphere[:, 3] = np.float32(1.0)
+    flat.scale[:] = np.float32(1.0)
+    check_against_oracle(flat, standard_cameras())
