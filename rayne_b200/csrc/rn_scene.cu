@@ -730,7 +730,6 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 			ev.list_counts[c] = acc + x;
 	}
 	__syncthreads();
-	const uint32_t lt_mask = (1u << lane) - 1u;
 	for(uint32_t k = warp; k < kEmitTiles; k += kEmitThreads / 32)
 	{
 		const uint32_t t = first + k;
@@ -749,37 +748,48 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 		if(!cams)
 			continue;
 		const uint32_t start = ev.tiles[t].start, count = ev.tiles[t].count;
+		// 128 ranks per iteration, four consecutive ranks per lane: one warp scan per camera instead of four ballots
 		for(uint32_t r0 = 0; r0 < count; r0 += 32 * kEmitUnroll)
 		{
-			uint32_t slot[kEmitUnroll], v[kEmitUnroll];
+			const uint32_t r = r0 + lane * kEmitUnroll;
+			uint32_t slot[kEmitUnroll];
+			uint32_t vv = 0;
+#pragma unroll
+			for(int u = 0; u < (int)kEmitUnroll; u++)
+				slot[u] = r + u < count ? ev.slot_of_rank[start + r + u] : 0xffffffffu;
 #pragma unroll
 			for(int u = 0; u < (int)kEmitUnroll; u++)
 			{
-				const uint32_t r = r0 + u * 32 + lane;
-				slot[u] = r < count ? ev.slot_of_rank[start + r] : 0xffffffffu;
-			}
-#pragma unroll
-			for(int u = 0; u < (int)kEmitUnroll; u++)
-			{
-				v[u] = slot[u] != 0xffffffffu ? ev.vis[slot[u]] : 0u;
+				if(slot[u] != 0xffffffffu)
+					vv |= (uint32_t)ev.vis[slot[u]] << (8 * u);
 				if(ev.rank_mode)
-					slot[u] = start + r0 + u * 32 + lane + ev.rank_offset;
+					slot[u] = start + r + u + ev.rank_offset;
 			}
 #pragma unroll
 			for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			{
 				if((cams >> c) & 1u)
 				{
-#pragma unroll
-					for(int u = 0; u < (int)kEmitUnroll; u++)
+					const uint32_t bits = (vv >> c) & 0x01010101u;
+					if(__any_sync(0xffffffffu, bits != 0))
 					{
-						const uint32_t m = __ballot_sync(0xffffffffu, (v[u] >> c) & 1u);
-						if(m)
+						const uint32_t cnt = __popc(bits);
+						uint32_t x = cnt;
+#pragma unroll
+						for(int o = 1; o < 32; o <<= 1)
 						{
-							if((v[u] >> c) & 1u)
-								ev.lists[c][off[c] + __popc(m & lt_mask)] = slot[u];
-							off[c] += __popc(m);
+							const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+							if(lane >= (uint32_t)o)
+								x += y;
 						}
+						uint32_t *out = ev.lists[c] + off[c] + (x - cnt);
+#pragma unroll
+						for(int u = 0; u < (int)kEmitUnroll; u++)
+						{
+							if((bits >> (8 * u)) & 1u)
+								*out++ = slot[u];
+						}
+						off[c] += __shfl_sync(0xffffffffu, x, 31);
 					}
 				}
 			}
