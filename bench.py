@@ -100,6 +100,18 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic(nodes: int, views: int):
+    """dram__bytes_read + dram__bytes_write of the tile kernel from the committed ncu capture (same workload only)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)["tile_kernel"]
+        if t["nodes"] == nodes and t["views"] == views:
+            return t["dram_bytes_read"] + t["dram_bytes_write"], t["source"]
+    except Exception:
+        pass
+    return None, None
+
+
 def build_scene(trees: int, seed: int):
     t0 = time.time()
     scene = sg.make_scene(n_trees=trees, branching=4, depth=8, seed=seed)
@@ -295,6 +307,7 @@ def run_ours(args) -> dict:
             dist.destroy_process_group()
         return {}
     peak, peak_kind = measured_peak()
+    traffic, traffic_src = ncu_traffic(n, ncam)
     alg_bytes = n * (BYTES_PER_NODE + 4.0 * sum(vis_frac))
     tile_avg_ms = tile_ms / max(tile_n, 1)
     achieved = alg_bytes / (tile_avg_ms * 1e-3) / 1e9
@@ -312,7 +325,7 @@ def run_ours(args) -> dict:
                 "what": "rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + 6 lists) into pinned host buffers"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "rn::tile_kernel<true,true>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "peak_kind": peak_kind, "traffic": None,
+                     "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
                      "kernel_share_of_step": tile_avg_ms / ms_step,
                      "step_frac": alg_bytes / (ms_step * 1e-3) / 1e9 / peak},
