@@ -77,6 +77,59 @@ def world(parent_u32: np.ndarray, pos: np.ndarray, scale: np.ndarray, rot: np.nd
     return wpos, wrot, wscale, wmat
 
 
+def inverse(parent_u32: np.ndarray, pos: np.ndarray, scale: np.ndarray, rot: np.ndarray) -> np.ndarray:
+    """A3: inverse world matrices (same index conventions as world())."""
+    n = parent_u32.shape[0]
+    parent_u32 = np.ascontiguousarray(parent_u32, dtype=np.uint32)
+    pos = np.ascontiguousarray(pos, dtype=np.float32); scale = np.ascontiguousarray(scale, dtype=np.float32)
+    rot = np.ascontiguousarray(rot, dtype=np.float32)
+    winv = np.zeros((n, 16), np.float32)
+    load().rn_oracle_inverse(C.c_uint32(n), _p(parent_u32), _p(pos), _p(scale), _p(rot), _p(winv))
+    return winv
+
+
+def bounds(wrot: np.ndarray, wscale: np.ndarray, box: np.ndarray | None) -> np.ndarray:
+    """A4: transformed AABB extents (minExtend, maxExtend relative to the world position) per node."""
+    n = wrot.shape[0]
+    wrot = np.ascontiguousarray(wrot, dtype=np.float32); wscale = np.ascontiguousarray(wscale, dtype=np.float32)
+    box = None if box is None else np.ascontiguousarray(box, dtype=np.float32)
+    out = np.zeros((n, 6), np.float32)
+    load().rn_oracle_bounds(C.c_uint32(n), _p(wrot), _p(wscale), _p(box), _p(out))
+    return out
+
+
+def cull_aabb(wpos, aabb, flags, frustum: np.ndarray, in_list: np.ndarray) -> np.ndarray:
+    """Extension C5a: filters `in_list` (indices into the arrays) with the AABB-vs-planes test."""
+    wpos = np.ascontiguousarray(wpos, dtype=np.float32); aabb = np.ascontiguousarray(aabb, dtype=np.float32)
+    flags = np.ascontiguousarray(flags, dtype=np.uint32)
+    in_list = np.ascontiguousarray(in_list, dtype=np.uint32)
+    fr = np.ascontiguousarray(frustum, dtype=FRUSTUM_DTYPE).reshape(1)
+    out = np.zeros(in_list.shape[0], dtype=np.uint32)
+    cnt = load().rn_oracle_cull_aabb(C.c_uint32(wpos.shape[0]), _p(wpos), _p(aabb), _p(flags), C.c_void_p(fr.ctypes.data),
+                                     _p(in_list), C.c_uint32(in_list.shape[0]), _p(out))
+    return out[:cnt].copy()
+
+
+def vislist_order(parent: np.ndarray) -> np.ndarray:
+    """A10: SceneWithVisibilityLists default-volume order (creation ids)."""
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    order = np.zeros(parent.shape[0], dtype=np.uint32)
+    rc = load().rn_oracle_vislist_order(C.c_uint32(parent.shape[0]), _p(parent), _p(order))
+    assert rc == 0
+    return order
+
+
+def sort_list(lst: np.ndarray, prio: np.ndarray, wpos: np.ndarray, cam_pos, front_to_back: bool,
+              transparent_back_to_front: bool) -> np.ndarray:
+    """A11: the post-cull sorts of SceneBasic::Render on one list of indices into prio / wpos."""
+    lst = np.ascontiguousarray(lst, dtype=np.uint32).copy()
+    prio = np.ascontiguousarray(prio, dtype=np.int32); wpos = np.ascontiguousarray(wpos, dtype=np.float32)
+    cam = (C.c_float * 3)(*[float(x) for x in cam_pos])
+    load().rn_oracle_sort_list(_p(lst), C.c_uint32(lst.shape[0]), _p(prio), _p(wpos), cam, C.c_int(int(front_to_back)),
+                               C.c_int(int(transparent_back_to_front)))
+    return lst
+
+
 def frustums(cameras: np.ndarray) -> np.ndarray:
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
     out = np.zeros(cameras.shape[0], dtype=FRUSTUM_DTYPE)
@@ -133,6 +186,17 @@ class Emitters:
         camv = (C.c_float * 3)(*[float(x) for x in cam])
         load().rn_oracle_emitter_sort(self.h, C.c_uint32(k), camv, _p(idx), _p(key))
         return idx, key
+
+    def mesh(self, k: int, world_scale_x: float = 1.0, roll: bool = False, inversed: bool = False) -> dict:
+        """P6: the render mesh ParticleEmitter::UpdateMesh would build for emitter k."""
+        mx = int(self.em["max_particles"][k])
+        out = {"mesh_pos": np.zeros((mx * 4, 3), np.float32), "mesh_color": np.zeros((mx * 4, 4), np.float32),
+               "mesh_uv0": np.zeros((mx * 4, 2), np.float32), "mesh_uv1": np.zeros((mx * 4, 2), np.float32),
+               "mesh_idx": np.zeros(mx * 6, np.uint16)}
+        load().rn_oracle_emitter_mesh(self.h, C.c_uint32(k), C.c_float(world_scale_x), C.c_int(int(roll)), C.c_int(int(inversed)),
+                                      _p(out["mesh_pos"]), _p(out["mesh_color"]), _p(out["mesh_uv0"]), _p(out["mesh_uv1"]),
+                                      _p(out["mesh_idx"]))
+        return out
 
     def close(self):
         if self.h:

@@ -169,6 +169,12 @@ namespace
 		HarnessScene() {}
 	};
 
+	class HarnessVisScene : public SceneWithVisibilityLists
+	{
+	public:
+		HarnessVisScene() {}
+	};
+
 	// ---- tiny binary IO ----------------------------------------------------------------------------------
 	struct Reader
 	{
@@ -208,10 +214,13 @@ namespace
 		std::vector<uint32_t> flags, group;
 		std::vector<int32_t> priority;
 		std::vector<float> sphere;
+		std::vector<float> box;   // optional (kOptBox): minExtend xyz, maxExtend xyz per node
 		std::vector<CameraDesc> cameras;
 	};
 
-	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1 };
+	// kOptVisLists: drive SceneWithVisibilityLists (default volume only) instead of SceneBasic.
+	// kOptBox: the input carries a local AABB column (SceneNode::SetBoundingBox).
+	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1, kOptVisLists = 1u << 2, kOptBox = 1u << 3 };
 
 	SceneInput ReadScene(const char *path)
 	{
@@ -227,13 +236,16 @@ namespace
 		in.pos = r.vec<float>(n * 3); in.scale = r.vec<float>(n * 3); in.rot = r.vec<float>(n * 4);
 		in.flags = r.vec<uint32_t>(n); in.group = r.vec<uint32_t>(n); in.priority = r.vec<int32_t>(n);
 		in.sphere = r.vec<float>(n * 4);
+		if(in.options & kOptBox) in.box = r.vec<float>(n * 6);
 		in.cameras = r.vec<CameraDesc>(in.nCameras);
 		return in;
 	}
 
 	struct BuiltScene
 	{
-		HarnessScene *scene;
+		Scene *scene;
+		HarnessScene *basic = nullptr;
+		HarnessVisScene *vis = nullptr;
 		std::vector<CullNode *> nodes;
 		std::vector<CullNode *> roots;
 		std::vector<Camera *> cameras;
@@ -242,7 +254,8 @@ namespace
 	BuiltScene BuildScene(const SceneInput &in)
 	{
 		BuiltScene b;
-		b.scene = new HarnessScene();
+		if(in.options & kOptVisLists) b.scene = b.vis = new HarnessVisScene();
+		else b.scene = b.basic = new HarnessScene();
 		b.nodes.resize(in.nNodes);
 		for(uint32_t i = 0; i < in.nNodes; i++)
 		{
@@ -254,6 +267,8 @@ namespace
 			node->SetFlags(in.flags[i]);
 			node->SetRenderGroup(static_cast<uint8>(in.group[i]));
 			if(in.priority[i] != SceneNode::RenderNormal) node->SetRenderPriority(in.priority[i]);
+			if(in.options & kOptBox)
+				node->SetBoundingBox(AABB(Vector3(in.box[i*6], in.box[i*6+1], in.box[i*6+2]), Vector3(in.box[i*6+3], in.box[i*6+4], in.box[i*6+5])), false);
 			Sphere s(Vector3(in.sphere[i*4], in.sphere[i*4+1], in.sphere[i*4+2]), in.sphere[i*4+3]);
 			node->SetBoundingSphere(s);
 			b.nodes[i] = node;
@@ -323,16 +338,25 @@ namespace
 		g_recorder = nullptr;
 
 		Writer w(outPath);
-		w.put<uint32_t>(0x4f534e52u); w.put<uint32_t>(1);
+		w.put<uint32_t>(0x4f534e52u); w.put<uint32_t>(2);
 		w.put<uint32_t>(in.nNodes); w.put<uint32_t>(in.nCameras);
-		// render-list order (SceneBasic::_renderNodes, head to tail) as creation ids
+		// render-list order as creation ids: SceneBasic::_renderNodes head to tail, or the default volume of
+		// SceneWithVisibilityLists (cameras are nodes of that volume too; they are not CullNodes and are skipped)
 		std::vector<uint32_t> order;
-		for(IntrusiveList<SceneNode>::Member *m = b.scene->_renderNodes.GetHead(); m; m = m->GetNext())
-			order.push_back(static_cast<CullNode *>(m->Get())->id);
+		if(b.basic)
+		{
+			for(IntrusiveList<SceneNode>::Member *m = b.basic->_renderNodes.GetHead(); m; m = m->GetNext())
+				order.push_back(static_cast<CullNode *>(m->Get())->id);
+		}
+		else
+		{
+			for(SceneNode *node : b.vis->_defaultVolume->nodes)
+				if(!node->IsKindOfClass(Camera::GetMetaClass())) order.push_back(static_cast<CullNode *>(node)->id);
+		}
 		w.put<uint32_t>(static_cast<uint32_t>(order.size()));
 		w.vec(order);
 		std::vector<float> wpos(in.nNodes * 3), wrot(in.nNodes * 4), wscale(in.nNodes * 3), wmat((size_t)in.nNodes * 16), sph((size_t)in.nNodes * 4);
-		std::vector<float> winv;
+		std::vector<float> winv, aabb((size_t)in.nNodes * 6);
 		if(in.options & kOptInverse) winv.resize((size_t)in.nNodes * 16);
 		for(uint32_t i = 0; i < in.nNodes; i++)
 		{
@@ -351,10 +375,14 @@ namespace
 			Sphere bs = node->GetBoundingSphere();
 			Vector3 c = bs.position + bs.offset;
 			sph[i*4] = c.x; sph[i*4+1] = c.y; sph[i*4+2] = c.z; sph[i*4+3] = bs.radius;
+			AABB bb = node->GetBoundingBox();   // position == world position; extents relative to it
+			aabb[(size_t)i*6+0] = bb.minExtend.x; aabb[(size_t)i*6+1] = bb.minExtend.y; aabb[(size_t)i*6+2] = bb.minExtend.z;
+			aabb[(size_t)i*6+3] = bb.maxExtend.x; aabb[(size_t)i*6+4] = bb.maxExtend.y; aabb[(size_t)i*6+5] = bb.maxExtend.z;
 		}
 		w.vec(wpos); w.vec(wrot); w.vec(wscale); w.vec(wmat); w.vec(sph);
 		w.put<uint32_t>((in.options & kOptInverse) ? 1 : 0);
 		w.vec(winv);
+		w.vec(aabb);
 		for(size_t c = 0; c < b.cameras.size(); c++)
 		{
 			Camera *cam = b.cameras[c];
@@ -415,10 +443,14 @@ namespace
 		float gravity[3], velocity[3], velMin[3], velMax[3], posMin[3], posMax[3];
 	};
 
+	// options: the emitter switches UpdateMesh looks at (Source/Scene/RNParticleEmitter.cpp:229,235) + "dump the mesh"
+	enum : uint32_t { kPOptRoll = 1u << 0, kPOptInversed = 1u << 1, kPOptMesh = 1u << 2 };
+
 	struct ParticleInput
 	{
 		uint32_t nEmitters, nSteps;
 		float delta;
+		uint32_t options;
 		std::vector<EmitterDesc> emitters;
 	};
 
@@ -427,8 +459,8 @@ namespace
 		Reader r(path);
 		ParticleInput in;
 		uint32_t magic = r.get<uint32_t>(); uint32_t version = r.get<uint32_t>();
-		if(magic != 0x49504e52u || version != 1) { fprintf(stderr, "bad particle file\n"); exit(2); }
-		in.nEmitters = r.get<uint32_t>(); in.nSteps = r.get<uint32_t>(); in.delta = r.get<float>();
+		if(magic != 0x49504e52u || version != 2) { fprintf(stderr, "bad particle file\n"); exit(2); }
+		in.nEmitters = r.get<uint32_t>(); in.nSteps = r.get<uint32_t>(); in.delta = r.get<float>(); in.options = r.get<uint32_t>();
 		in.emitters = r.vec<EmitterDesc>(in.nEmitters);
 		return in;
 	}
@@ -455,6 +487,8 @@ namespace
 			e->SetVelocityRandomizeMax(Vector3(d.velMax[0], d.velMax[1], d.velMax[2]));
 			e->SetPositionRandomizeMin(Vector3(d.posMin[0], d.posMin[1], d.posMin[2]));
 			e->SetPositionRandomizeMax(Vector3(d.posMax[0], d.posMax[1], d.posMax[2]));
+			e->SetCanRollParticles((in.options & kPOptRoll) != 0);
+			e->SetIsRenderedInversed((in.options & kPOptInversed) != 0);
 			scene->AddNode(e);
 			out.push_back(e);
 		}
@@ -469,7 +503,7 @@ namespace
 		for(uint32_t s = 0; s < in.nSteps; s++) scene->Update(in.delta);
 
 		Writer w(outPath);
-		w.put<uint32_t>(0x4f504e52u); w.put<uint32_t>(1); w.put<uint32_t>(in.nEmitters);
+		w.put<uint32_t>(0x4f504e52u); w.put<uint32_t>(2); w.put<uint32_t>(in.nEmitters);
 		for(GenericParticleEmitter *e : emitters)
 		{
 			uint32_t count = static_cast<uint32_t>(e->_particles.size());
@@ -491,6 +525,30 @@ namespace
 				o[20] = p->gravity.x; o[21] = p->gravity.y; o[22] = p->gravity.z; o[23] = 0.0f;
 			}
 			w.vec(rec);
+			w.put<uint32_t>((in.options & kPOptMesh) ? e->_maxParticles : 0u);
+			if(in.options & kPOptMesh)
+			{
+				// the mesh ParticleEmitter::UpdateMesh built in the last Update (RNParticleEmitter.cpp:213-336,345),
+				// read back through the Mesh's own chunk iterators (layout independent)
+				const uint32_t nv = e->_maxParticles * 4, ni = e->_maxParticles * 6;
+				Mesh::Chunk chunk = e->_mesh->GetChunk();
+				Mesh::ElementIterator<Vector3> vi = chunk.GetIterator<Vector3>(Mesh::VertexAttribute::Feature::Vertices);
+				Mesh::ElementIterator<Color> ci = chunk.GetIterator<Color>(Mesh::VertexAttribute::Feature::Color0);
+				Mesh::ElementIterator<Vector2> ti = chunk.GetIterator<Vector2>(Mesh::VertexAttribute::Feature::UVCoords0);
+				Mesh::ElementIterator<Vector2> si = chunk.GetIterator<Vector2>(Mesh::VertexAttribute::Feature::UVCoords1);
+				Mesh::ElementIterator<RN::uint16> ii = chunk.GetIterator<RN::uint16>(Mesh::VertexAttribute::Feature::Indices);
+				std::vector<float> vp((size_t)nv * 3), vc((size_t)nv * 4), vt((size_t)nv * 2), vs((size_t)nv * 2);
+				std::vector<uint16_t> idx(ni);
+				for(uint32_t v = 0; v < nv; v++)
+				{
+					Vector3 a = *vi++; Color c = *ci++; Vector2 t = *ti++; Vector2 z = *si++;
+					vp[v*3] = a.x; vp[v*3+1] = a.y; vp[v*3+2] = a.z;
+					vc[v*4] = c.r; vc[v*4+1] = c.g; vc[v*4+2] = c.b; vc[v*4+3] = c.a;
+					vt[v*2] = t.x; vt[v*2+1] = t.y; vs[v*2] = z.x; vs[v*2+1] = z.y;
+				}
+				for(uint32_t k = 0; k < ni; k++) idx[k] = *ii++;
+				w.vec(vp); w.vec(vc); w.vec(vt); w.vec(vs); w.vec(idx);
+			}
 		}
 		return 0;
 	}

@@ -2,15 +2,16 @@
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
 
-Scene input  ("RNSI" v1): header u32 magic, version, n_nodes, n_cameras, n_frames, options; f32 root_translate[3];
+Scene input  ("RNSI" v1; + f32 box[n,6] after sphere when options & OPT_BOX): header u32 magic, version, n_nodes, n_cameras, n_frames, options; f32 root_translate[3];
     i32 parent[n]; f32 pos[n,3]; f32 scale[n,3]; f32 rot[n,4]; u32 flags[n]; u32 group[n]; i32 priority[n];
     f32 sphere[n,4]; CAMERA_DTYPE cameras[n_cameras]           (all creation order, little endian)
-Scene output ("RNSO" v1): u32 magic, version, n_nodes, n_cameras; u32 n_order; u32 order[n_order] (render list,
+Scene output ("RNSO" v2: + f32 aabb[n,6] (world minExtend, maxExtend) after winv): u32 magic, version, n_nodes, n_cameras; u32 n_order; u32 order[n_order] (render list,
     head->tail, creation ids); f32 wpos[n,3]; wrot[n,4]; wscale[n,3]; wmat[n,16]; sphere[n,4] (centre, radius);
     u32 has_inv; f32 winv[n,16] if has_inv; per camera: f32 frustum[28] (centre3, radius, 6x(normal3, d) in the
     order left,right,top,bottom,near,far), u32 flags, u32 group, u32 count, u32 list[count] (creation ids)
-Particle input ("RNPI" v1): u32 magic, version, n_emitters, n_steps; f32 delta; EMITTER_DTYPE emitters[n]
-Particle output ("RNPO" v1): u32 magic, version, n_emitters; per emitter u32 count, f32 time, f32 rec[count,24]
+Particle input ("RNPI" v2): u32 magic, version, n_emitters, n_steps; f32 delta; u32 options; EMITTER_DTYPE emitters[n]
+Particle output ("RNPO" v2): u32 magic, version, n_emitters; per emitter u32 count, f32 time, f32 rec[count,24],
+    u32 mesh_max (0 = no mesh); if mesh_max: f32 pos[4m,3], color[4m,4], uv0[4m,2], uv1[4m,2], u16 idx[6m]
 """
 from __future__ import annotations
 
@@ -28,6 +29,9 @@ REF_DIR = os.path.join(HERE, "_ref")
 
 OPT_INVERSE = 1
 OPT_TOUCH_MATRICES = 2
+OPT_VISLISTS = 4      # SceneWithVisibilityLists (default volume) instead of SceneBasic
+OPT_BOX = 8           # the input carries scene.box (local AABB column)
+POPT_ROLL, POPT_INVERSED, POPT_MESH = 1, 2, 4
 
 # columns of the 24-float particle record written by the harness
 P_POS, P_VEL, P_TIME, P_LIFE, P_DUR = slice(0, 3), slice(3, 6), 6, 7, 8
@@ -57,6 +61,8 @@ def write_scene_input(path: str, scene: Scene, cameras: np.ndarray, frames: int 
         f.write(np.ascontiguousarray(scene.group, dtype="<u4").tobytes())
         f.write(np.ascontiguousarray(scene.priority, dtype="<i4").tobytes())
         f.write(np.ascontiguousarray(scene.sphere, dtype="<f4").tobytes())
+        if options & OPT_BOX:
+            f.write(np.ascontiguousarray(scene.box, dtype="<f4").tobytes())
         f.write(cameras.tobytes())
 
 
@@ -72,7 +78,7 @@ def read_scene_output(path: str) -> dict:
         return a
 
     magic, version, n, ncam = take("<u4", 4)
-    assert magic == 0x4F534E52 and version == 1
+    assert magic == 0x4F534E52 and version == 2
     n = int(n); ncam = int(ncam)
     norder = int(take("<u4", 1)[0])
     out = {"order": take("<u4", norder).copy()}
@@ -83,6 +89,7 @@ def read_scene_output(path: str) -> dict:
     out["sphere"] = take("<f4", n * 4).reshape(n, 4).copy()
     has_inv = int(take("<u4", 1)[0])
     out["winv"] = take("<f4", n * 16).reshape(n, 16).copy() if has_inv else None
+    out["aabb"] = take("<f4", n * 6).reshape(n, 6).copy()
     out["frustum"] = np.zeros((ncam, 28), dtype=np.float32)
     out["cam_flags"] = np.zeros(ncam, dtype=np.uint32)
     out["cam_group"] = np.zeros(ncam, dtype=np.uint32)
@@ -115,18 +122,19 @@ def bench_scene(scene: Scene, cameras: np.ndarray, frames: int, warmup: int,
         return json.loads(r.stdout.strip().splitlines()[-1])
 
 
-def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float) -> None:
+def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float, options: int = 0) -> None:
     emitters = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
     with open(path, "wb") as f:
-        f.write(np.array([0x49504E52, 1, emitters.shape[0], steps], dtype="<u4").tobytes())
+        f.write(np.array([0x49504E52, 2, emitters.shape[0], steps], dtype="<u4").tobytes())
         f.write(np.array([delta], dtype="<f4").tobytes())
+        f.write(np.array([options], dtype="<u4").tobytes())
         f.write(emitters.tobytes())
 
 
 def read_particle_output(path: str) -> list[dict]:
     buf = np.fromfile(path, dtype=np.uint8)
     magic, version, ne = np.frombuffer(buf, dtype="<u4", count=3)
-    assert magic == 0x4F504E52 and version == 1
+    assert magic == 0x4F504E52 and version == 2
     off = 12
     out = []
     for _ in range(int(ne)):
@@ -135,15 +143,25 @@ def read_particle_output(path: str) -> list[dict]:
         off += 8
         rec = np.frombuffer(buf, dtype="<f4", count=cnt * 24, offset=off).reshape(cnt, 24).copy()
         off += cnt * 96
-        out.append({"count": cnt, "time": np.float32(time), "rec": rec})
+        item = {"count": cnt, "time": np.float32(time), "rec": rec}
+        mx = int(np.frombuffer(buf, dtype="<u4", count=1, offset=off)[0])
+        off += 4
+        if mx:
+            for name, width in (("mesh_pos", 3), ("mesh_color", 4), ("mesh_uv0", 2), ("mesh_uv1", 2)):
+                item[name] = np.frombuffer(buf, dtype="<f4", count=mx * 4 * width, offset=off).reshape(mx * 4, width).copy()
+                off += mx * 4 * width * 4
+            item["mesh_idx"] = np.frombuffer(buf, dtype="<u2", count=mx * 6, offset=off).copy()
+            off += mx * 12
+        out.append(item)
     assert off == buf.shape[0]
     return out
 
 
-def run_particles(emitters: np.ndarray, steps: int, delta: float = 1.0 / 60.0, kind: str = "strict") -> list[dict]:
+def run_particles(emitters: np.ndarray, steps: int, delta: float = 1.0 / 60.0, kind: str = "strict",
+                  options: int = 0) -> list[dict]:
     with tempfile.TemporaryDirectory() as tmp:
         fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
-        write_particle_input(fin, emitters, steps, delta)
+        write_particle_input(fin, emitters, steps, delta, options)
         subprocess.run([harness_path(kind), "particles", fin, fout], check=True, stdout=subprocess.DEVNULL)
         return read_particle_output(fout)
 

@@ -420,7 +420,149 @@ uint32_t rn_oracle_cull(uint32_t n, const float *wpos, const float *wrot, const 
 	return count;
 }
 
-/* Extension restated from the commented-out body of Camera::InFrustum(const AABB&), Source/Scene/RNCamera.cpp:479-496 */
+/* ---- A3: inverse world matrices ------------------------------------------------------------------------------ */
+
+/* SceneNode::UpdateInternalInverseTransformData, Source/Scene/RNSceneNode.cpp:548-568:
+ *   invLocal = WithScaling(scale != 0 ? 1/scale : 0); .Rotate(conj(rot)); .Translate(pos * -1)
+ *   invWorld = invLocal * parent.invWorld
+ * `scale != 0.0f` is Vector3::operator!=(Vector3(0)) - an epsilon compare of all three components
+ * (Source/Math/RNVector.h:403-409, k::EpsilonFloat = FLT_EPSILON); Matrix::Translate Source/Math/RNMatrix.h:514-527. */
+static mat4 inverse_local_matrix(vec3 p, quat q, vec3 s)
+{
+	vec3 is = {0.0f, 0.0f, 0.0f};
+	if(!(fabsf(s.x - 0.0f) <= FLT_EPSILON && fabsf(s.y - 0.0f) <= FLT_EPSILON && fabsf(s.z - 0.0f) <= FLT_EPSILON))
+	{
+		is.x = 1.0f / s.x; is.y = 1.0f / s.y; is.z = 1.0f / s.z;
+	}
+	mat4 m = mat_identity();
+	m.m[0] = is.x; m.m[5] = is.y; m.m[10] = is.z;
+	quat c = {-q.x, -q.y, -q.z, q.w};
+	mat4 r = quat_matrix(c);
+	m = mat_mul(&m, &r);
+	vec3 t = {p.x * -1.0f, p.y * -1.0f, p.z * -1.0f};
+	float tmp[4];
+	for(int i = 0; i < 4; i++)
+		tmp[i] = m.m[i] * t.x + m.m[4 + i] * t.y + m.m[8 + i] * t.z + m.m[12 + i];
+	for(int i = 0; i < 4; i++) m.m[12 + i] = tmp[i];
+	return m;
+}
+
+int rn_oracle_inverse(uint32_t n, const uint32_t *parent, const float *pos, const float *scale, const float *rot, float *winv)
+{
+	uint8_t *done = calloc(n ? n : 1, 1);
+	uint32_t *stack = malloc(4 * (n + 1));
+	for(uint32_t start = 0; start < n; start++)
+	{
+		uint32_t sp = 0, u = start;
+		while(!done[u]) { stack[sp++] = u; if(parent[u] == RN_NO_PARENT) break; u = parent[u]; }
+		while(sp)
+		{
+			u = stack[--sp];
+			vec3 p = {pos[u * 3], pos[u * 3 + 1], pos[u * 3 + 2]};
+			vec3 s = {scale[u * 3], scale[u * 3 + 1], scale[u * 3 + 2]};
+			quat q = {rot[u * 4], rot[u * 4 + 1], rot[u * 4 + 2], rot[u * 4 + 3]};
+			mat4 il = inverse_local_matrix(p, q, s);
+			if(parent[u] != RN_NO_PARENT)
+			{
+				mat4 pm;
+				memcpy(pm.m, winv + (size_t)parent[u] * 16, 64);
+				mat4 w = mat_mul(&il, &pm); /* :559 */
+				memcpy(winv + (size_t)u * 16, w.m, 64);
+			}
+			else
+				memcpy(winv + (size_t)u * 16, il.m, 64);
+			done[u] = 1;
+		}
+	}
+	free(done); free(stack);
+	return 0;
+}
+
+/* ---- A4: transformed bounding box ---------------------------------------------------------------------------- */
+
+/* Matrix::operator*(Vector3), Source/Math/RNMatrix.h:145-151 */
+static vec3 mat_mul_vec(const mat4 *m, vec3 v)
+{
+	vec3 r;
+	r.x = m->m[0] * v.x + m->m[4] * v.y + m->m[8] * v.z + m->m[12];
+	r.y = m->m[1] * v.x + m->m[5] * v.y + m->m[9] * v.z + m->m[13];
+	r.z = m->m[2] * v.x + m->m[6] * v.y + m->m[10] * v.z + m->m[14];
+	return r;
+}
+
+/* SceneNode::UpdateInternalBoundsData box part (Source/Scene/RNSceneNode.cpp:576-579): position = world position;
+ * AABB::operator*=(Vector3) Source/Math/RNAABB.h:108-114; AABB::SetRotation :152-177.
+ * box: local minExtend xyz, maxExtend xyz (NULL = the default AABB(-1, 1), RNSceneNode.cpp:34); out: 6 floats. */
+static void world_aabb(const float *box, vec3 ws, quat wr, float *out)
+{
+	vec3 mn = {-1.0f, -1.0f, -1.0f}, mx = {1.0f, 1.0f, 1.0f};
+	if(box) { mn.x = box[0]; mn.y = box[1]; mn.z = box[2]; mx.x = box[3]; mx.y = box[4]; mx.z = box[5]; }
+	mn.x *= ws.x; mn.y *= ws.y; mn.z *= ws.z;
+	mx.x *= ws.x; mx.y *= ws.y; mx.z *= ws.z;
+	mat4 m = quat_matrix(wr);
+	vec3 corners[4];
+	vec3 c0 = {mn.x, mn.y, mx.z}, c1 = {mn.x, mx.y, mx.z}, c2 = {mx.x, mx.y, mn.z}, c3 = {mx.x, mn.y, mn.z};
+	corners[0] = mat_mul_vec(&m, c0); corners[1] = mat_mul_vec(&m, c1);
+	corners[2] = mat_mul_vec(&m, c2); corners[3] = mat_mul_vec(&m, c3);
+	mn = mat_mul_vec(&m, mn);
+	mx = mat_mul_vec(&m, mx);
+	for(int i = 0; i < 4; i++)
+	{
+		mn.x = (corners[i].x < mn.x) ? corners[i].x : mn.x;
+		mn.y = (corners[i].y < mn.y) ? corners[i].y : mn.y;
+		mn.z = (corners[i].z < mn.z) ? corners[i].z : mn.z;
+		mx.x = (corners[i].x > mx.x) ? corners[i].x : mx.x;
+		mx.y = (corners[i].y > mx.y) ? corners[i].y : mx.y;
+		mx.z = (corners[i].z > mx.z) ? corners[i].z : mx.z;
+	}
+	out[0] = mn.x; out[1] = mn.y; out[2] = mn.z; out[3] = mx.x; out[4] = mx.y; out[5] = mx.z;
+}
+
+int rn_oracle_bounds(uint32_t n, const float *wrot, const float *wscale, const float *box /* n*6 or NULL */, float *out_aabb /* n*6 */)
+{
+	for(uint32_t i = 0; i < n; i++)
+	{
+		vec3 ws = {wscale[i * 3], wscale[i * 3 + 1], wscale[i * 3 + 2]};
+		quat wr = {wrot[i * 4], wrot[i * 4 + 1], wrot[i * 4 + 2], wrot[i * 4 + 3]};
+		world_aabb(box ? box + (size_t)i * 6 : NULL, ws, wr, out_aabb + (size_t)i * 6);
+	}
+	return 0;
+}
+
+/* Extension restated from the commented-out body of Camera::InFrustum(const AABB&), Source/Scene/RNCamera.cpp:479-496
+ * (NO live reference behaviour: the live function returns true).  The comment tests, per plane, the box centre
+ * against the plane with the box's projected half extent `width . |normal|`.  Restated on the LIVE plane convention
+ * (Plane::GetDistance = p.n - d, a point is outside when the distance is positive, RNCamera.cpp:456-464):
+ *     centre = position + (min + max) * 0.5 ; half = (max - min) * 0.5
+ *     outside plane k  <=>  GetDistance_k(centre) > half.x*|n.x| + half.y*|n.y| + half.z*|n.z|
+ * applied AFTER the reference's sphere predicate (a node must pass both).  Lists produced with it are a subset of
+ * the reference's lists. */
+uint32_t rn_oracle_cull_aabb(uint32_t n, const float *wpos, const float *aabb, const uint32_t *flags, const oracle_frustum *cam,
+                             const uint32_t *in_list, uint32_t in_count, uint32_t *out_list)
+{
+	uint32_t count = 0;
+	(void)n;
+	for(uint32_t q = 0; q < in_count; q++)
+	{
+		uint32_t i = in_list[q];
+		int inside = 1;
+		if(!(flags[i] & NODE_NOCULLING) && !(cam->flags & CAM_SIMPLE))
+		{
+			const float *b = aabb + (size_t)i * 6;
+			vec3 c = {wpos[i * 3] + (b[0] + b[3]) * 0.5f, wpos[i * 3 + 1] + (b[1] + b[4]) * 0.5f, wpos[i * 3 + 2] + (b[2] + b[5]) * 0.5f};
+			vec3 h = {(b[3] - b[0]) * 0.5f, (b[4] - b[1]) * 0.5f, (b[5] - b[2]) * 0.5f};
+			for(int k = 0; k < 6 && inside; k++)
+			{
+				float d = (c.x * cam->planes[k][0] + c.y * cam->planes[k][1] + c.z * cam->planes[k][2]) - cam->planes[k][3];
+				float r = h.x * fabsf(cam->planes[k][0]) + h.y * fabsf(cam->planes[k][1]) + h.z * fabsf(cam->planes[k][2]);
+				if(d > r) inside = 0;
+			}
+		}
+		if(inside) out_list[count++] = i;
+	}
+	return count;
+}
+
 
 /* ---- particles ----------------------------------------------------------------------------------------------- */
 
@@ -607,4 +749,145 @@ void rn_oracle_emitter_sort(const oracle_emitter_state *s, uint32_t k, const flo
 	qsort(it, n, sizeof(sort_item), sort_cmp);
 	for(uint32_t i = 0; i < n; i++) idx_out[i] = it[i].idx;
 	free(it);
+}
+
+/* ---- A10: SceneWithVisibilityLists default-volume order ------------------------------------------------------- */
+
+/* SceneWithVisibilityLists::AddNode (Source/Scene/RNSceneWithVisibilityLists.cpp:210-236): UpdateSceneInfo adds the
+ * children first (recursively, in child order, Source/Scene/RNSceneNode.cpp:286-291), then the node itself is
+ * push_back-ed into _defaultVolume->nodes: post-order, no priority sort.  Nodes in creation order, parent[i] < i or -1,
+ * children of a node in creation order, roots added in creation order. */
+int rn_oracle_vislist_order(uint32_t n, const int32_t *parent, uint32_t *order)
+{
+	uint32_t *first = malloc(4 * (n + 1)), *next = malloc(4 * (n + 1)), *last = malloc(4 * (n + 1));
+	uint32_t *stack = malloc(4 * (n + 1)), *cursor = malloc(4 * (n + 1));
+	const uint32_t NIL = 0xffffffffu;
+	for(uint32_t i = 0; i < n; i++) first[i] = next[i] = last[i] = NIL;
+	for(uint32_t i = 0; i < n; i++)
+	{
+		if(parent[i] < 0) continue;
+		uint32_t p = (uint32_t)parent[i];
+		if(first[p] == NIL) first[p] = i; else next[last[p]] = i;
+		last[p] = i;
+	}
+	uint32_t out = 0;
+	for(uint32_t r = 0; r < n; r++)
+	{
+		if(parent[r] >= 0) continue;
+		uint32_t sp = 0;
+		stack[sp] = r; cursor[sp] = first[r]; sp++;
+		while(sp)
+		{
+			uint32_t u = stack[sp - 1], c = cursor[sp - 1];
+			if(c != NIL) { cursor[sp - 1] = next[c]; stack[sp] = c; cursor[sp] = first[c]; sp++; }
+			else { order[out++] = u; sp--; }
+		}
+	}
+	free(first); free(next); free(last); free(stack); free(cursor);
+	return out == n ? 0 : -1;
+}
+
+/* ---- A11: post-cull sorts of SceneBasic::Render ---------------------------------------------------------------- */
+
+/* Source/Scene/RNSceneBasic.cpp:576-616.  `list` holds indices into the per-node arrays (prio, wpos) in the order
+ * the cull loop pushed them.  flags: bit 5 = Camera::Flags::SortFrontToBack... the caller passes the two booleans.
+ * firstTransparentIndex == 0 doubles as "unset" (:583-587): a transparent node at list index 0 never becomes
+ * `first`.  std::sort is unstable: equal keys may come out in any order; this restatement keeps them in list order
+ * (a stable sort), which is one of the permitted outcomes.  Vector3::GetSquaredDistance Source/Math/RNVector.h:543-547. */
+#define PRIO_SKY 200000
+#define PRIO_TRANSPARENT 300000
+typedef struct { float key; int32_t prio; uint32_t pos; uint32_t id; } list_item;
+static float sq_dist(const float *wpos, uint32_t i, const float cam[3])
+{
+	float dx = wpos[i * 3] - cam[0], dy = wpos[i * 3 + 1] - cam[1], dz = wpos[i * 3 + 2] - cam[2];
+	return dx * dx + dy * dy + dz * dz;
+}
+static int cmp_front_to_back(const void *a, const void *b)
+{
+	const list_item *x = a, *y = b;
+	if(x->prio == y->prio && y->prio < PRIO_SKY) { if(x->key < y->key) return -1; if(y->key < x->key) return 1; }
+	else { if(x->prio < y->prio) return -1; if(y->prio < x->prio) return 1; }
+	return x->pos < y->pos ? -1 : (x->pos > y->pos ? 1 : 0);
+}
+static int cmp_back_to_front(const void *a, const void *b)
+{
+	const list_item *x = a, *y = b;
+	if(x->key > y->key) return -1;
+	if(y->key > x->key) return 1;
+	return x->pos < y->pos ? -1 : (x->pos > y->pos ? 1 : 0);
+}
+int rn_oracle_sort_list(uint32_t *list, uint32_t count, const int32_t *prio, const float *wpos, const float cam[3],
+                        int front_to_back, int transparent_back_to_front)
+{
+	size_t first = 0, last = 0;
+	for(uint32_t q = 0; q < count; q++)
+	{
+		if(prio[list[q]] == PRIO_TRANSPARENT)
+		{
+			if(first == 0) first = q;
+			last = q;
+		}
+	}
+	list_item *it = malloc(sizeof(list_item) * (count ? count : 1));
+	if(front_to_back)
+	{
+		for(uint32_t q = 0; q < count; q++) { it[q].id = list[q]; it[q].pos = q; it[q].prio = prio[list[q]]; it[q].key = sq_dist(wpos, list[q], cam); }
+		qsort(it, count, sizeof(list_item), cmp_front_to_back);
+		for(uint32_t q = 0; q < count; q++) list[q] = it[q].id;
+	}
+	if(transparent_back_to_front && first < last)
+	{
+		uint32_t m = (uint32_t)(last - first + 1);
+		for(uint32_t q = 0; q < m; q++) { it[q].id = list[first + q]; it[q].pos = q; it[q].prio = 0; it[q].key = sq_dist(wpos, list[first + q], cam); }
+		qsort(it, m, sizeof(list_item), cmp_back_to_front);
+		for(uint32_t q = 0; q < m; q++) list[first + q] = it[q].id;
+	}
+	free(it);
+	return 0;
+}
+
+/* ---- P6: ParticleEmitter::UpdateMesh --------------------------------------------------------------------------- */
+
+/* Source/Scene/RNParticleEmitter.cpp:213-336.  Outputs (mesh capacity max = e.max_particles): pos[4*max*3],
+ * color[4*max*4], uv0[4*max*2], uv1[4*max*2], idx[6*max] (uint16).  Quad k (k-th written) belongs to particle
+ * i = k (or stop-1-k when rendered inversed) but its six indices are i*4 + {0,1,2,2,1,3} - the reference indexes
+ * with the particle index, not with the write position (:283-288).  Unused index slots are degenerate (:322-330);
+ * unused vertices are left untouched (the caller passes zeroed arrays, as the reference's calloc'ed buffers are).
+ * world_scale_x = GetWorldScale().x of the emitter node (:223). */
+void rn_oracle_emitter_mesh(const oracle_emitter_state *s, uint32_t k, float world_scale_x, int roll, int inversed,
+                            float *pos, float *color, float *uv0, float *uv1, uint16_t *idx)
+{
+	const oracle_emitter_state *st = s + k;
+	const int maxp = (int)st->e.max_particles;
+	int stop = (int)st->count < maxp ? (int)st->count : maxp;
+	int start = 0, inc = 1;
+	if(inversed) { start = stop - 1; inc = -1; }
+	static const float tex[8] = {0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 1.0f, 1.0f, 1.0f};
+	uint32_t w = 0;
+	for(int i = start; i >= 0 && i < stop; i += inc, w++)
+	{
+		const float *p = st->rec + (size_t)i * REC;
+		for(int v = 0; v < 4; v++)
+		{
+			for(int c = 0; c < 3; c++) pos[(w * 4 + v) * 3 + c] = p[c];
+			for(int c = 0; c < 4; c++) color[(w * 4 + v) * 4 + c] = p[16 + c];
+			uv0[(w * 4 + v) * 2] = tex[v * 2]; uv0[(w * 4 + v) * 2 + 1] = tex[v * 2 + 1];
+		}
+		/* particle->size / 2.0f * scale */
+		float hx = p[14] / 2.0f * world_scale_x, hy = p[15] / 2.0f * world_scale_x;
+		float tx, ty, bx, by;
+		if(!roll) { tx = hx; ty = hy; bx = hx; by = -hy; }
+		else
+		{
+			float cs = cosf(p[13]), sn = sinf(p[13]);
+			tx = cs * hx - sn * hy; ty = sn * hx + cs * hy;
+			bx = cs * hx + sn * hy; by = sn * hx - cs * hy;
+		}
+		float *o = uv1 + (size_t)w * 8;
+		o[0] = -tx; o[1] = -ty; o[2] = bx; o[3] = by; o[4] = -bx; o[5] = -by; o[6] = tx; o[7] = ty;
+		static const int q[6] = {0, 1, 2, 2, 1, 3};
+		for(int c = 0; c < 6; c++) idx[w * 6 + c] = (uint16_t)(i * 4 + q[c]);
+	}
+	for(int i = stop; i < maxp; i++)
+		for(int c = 0; c < 6; c++) idx[(size_t)i * 6 + c] = (uint16_t)(i * 4);
 }

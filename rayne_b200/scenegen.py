@@ -44,6 +44,7 @@ class Scene:
     group: np.ndarray       # uint32 [n]   (only the low 8 bits are used: uint8 _renderGroup)
     priority: np.ndarray    # int32 [n]
     sphere: np.ndarray      # float32 [n,4]  (offset xyz, radius)
+    box: np.ndarray | None = None   # float32 [n,6] local AABB (minExtend xyz, maxExtend xyz); None = default +-1
 
     @property
     def n(self) -> int:
@@ -138,7 +139,8 @@ _LEVEL_EDGE = np.array([600.0, 60.0, 20.0, 5.0, 2.0, 1.0, 0.5, 0.25, 0.125, 0.06
 
 def make_scene(n_trees: int = 10, branching: int = 4, depth: int = 8, seed: int = 12345, *,
                ragged_nodes: int = 0, nonuniform_scale: bool = False, random_bounds: bool = False,
-               random_groups: bool = False, priorities: bool = False,
+               random_groups: bool = False, priorities: bool = False, random_boxes: bool = False,
+               transparent_frac: float = 0.0,
                hidden_frac: float = 0.01, nocull_frac: float = 0.01) -> Scene:
     """SURVEY.md §8(d) synthetic scene.  `ragged_nodes` > 0 selects the skewed variant (random branching 1-8)."""
     rng = np.random.Generator(np.random.PCG64(seed))
@@ -178,7 +180,15 @@ def make_scene(n_trees: int = 10, branching: int = 4, depth: int = 8, seed: int 
     if random_bounds:
         sphere[:, :3] = ((rng.random((n, 3)) - 0.5) * 2.0).astype(np.float32)
         sphere[:, 3] = (0.25 + 3.0 * rng.random(n)).astype(np.float32)
-    return Scene(parent=parent, pos=pos, scale=scale, rot=rot, flags=flags, group=group, priority=prio, sphere=sphere)
+    box = None
+    if random_boxes:
+        lo = (-0.2 - 2.0 * rng.random((n, 3))).astype(np.float32)
+        hi = (0.2 + 2.0 * rng.random((n, 3))).astype(np.float32)
+        box = np.concatenate([lo, hi], axis=1)
+    if transparent_frac > 0.0:
+        prio[rng.random(n) < transparent_frac] = RENDER_TRANSPARENT
+    return Scene(parent=parent, pos=pos, scale=scale, rot=rot, flags=flags, group=group, priority=prio, sphere=sphere,
+                 box=box)
 
 
 def flat_scene(n: int, seed: int = 1) -> Scene:
