@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RN_ABI_VERSION 1
+#define RN_ABI_VERSION 2
 #define RN_MAX_CAMERAS 8          /* views culled by one rn_cull call (stereo + 4 cascades = 6) */
 #define RN_NO_PARENT 0xffffffffu
 
@@ -50,6 +50,15 @@ typedef struct rn_scene rn_scene_t;
 /* RN::Camera::Flags bits the path looks at (Source/Scene/RNCamera.h:30-50). */
 #define RN_CAMERA_ORTHOGONAL         (1u << 21)
 #define RN_CAMERA_USE_SIMPLE_CULLING (1u << 26)
+#define RN_CAMERA_SORT_TRANSPARENT_BACK_TO_FRONT (1u << 5)   /* part of Camera::Flags::Defaults */
+#define RN_CAMERA_SORT_FRONT_TO_BACK             (1u << 6)
+/* Library extension (not a Rayne flag; bit 31 is unused by RN::Camera::Flags): additionally require the node's
+ * transformed AABB to pass the plane test that Camera::InFrustum(const AABB&) carries as a comment
+ * (Source/Scene/RNCamera.cpp:479-496; the live function returns true).  See rn_cull. */
+#define RN_CAMERA_TEST_AABB          (1u << 31)
+/* RN::SceneNode::RenderPriority values the sorts look at (Source/Scene/RNSceneNode.h:44-54). */
+#define RN_RENDER_SKY         200000
+#define RN_RENDER_TRANSPARENT 300000
 
 typedef struct rn_scene_desc {
 	int32_t  device;                     /* CUDA device ordinal */
@@ -72,6 +81,10 @@ typedef struct rn_node_columns {
 	const uint32_t *flags;            /* RN::SceneNode::Flags                                */
 	const uint32_t *render_group;     /* low 8 bits = SceneNode::_renderGroup                */
 	const float    *bounding_sphere;  /* 4 floats per node: local offset x, y, z and radius  */
+	const float    *bounding_box;     /* optional, 6 floats per node: local AABB minExtend xyz, maxExtend xyz
+	                                     (SceneNode::SetBoundingBox); NULL = the default AABB(-1, 1); full uploads only */
+	const int32_t  *render_priority;  /* optional: SceneNode::_renderPriority; NULL = RenderNormal for all.
+	                                     Only rn_cull_sort reads it (full uploads only)                        */
 } rn_node_columns;
 
 /* What Camera::PostUpdate / UpdateFrustum leave behind for the cull test
@@ -115,7 +128,10 @@ typedef enum rn_download_what {
 	RN_DL_WORLD_SCALE    = 2,   /* 3 floats per node  (SceneNode::GetWorldScale)     */
 	RN_DL_WORLD_MATRIX   = 3,   /* 16 floats per node, column-major (GetWorldTransform) */
 	RN_DL_SLOT_OF_RANK   = 4,   /* uint32 per node */
-	RN_DL_RANK_OF_SLOT   = 5    /* uint32 per node */
+	RN_DL_RANK_OF_SLOT   = 5,   /* uint32 per node */
+	RN_DL_INVERSE_WORLD_MATRIX = 6, /* 16 floats per node (GetInverseWorldTransform), after rn_transform_inverse */
+	RN_DL_BOUNDING_SPHERE = 7,  /* 4 floats per node: position + offset (the tested centre) and radius, after rn_bounds_update */
+	RN_DL_BOUNDING_BOX    = 8   /* 6 floats per node: world minExtend, maxExtend (relative to the world position) */
 } rn_download_what;
 
 /* ---- life cycle ------------------------------------------------------------------------------------------ */
@@ -171,6 +187,33 @@ int rn_scene_download(rn_scene_t *scene, rn_download_what what, uint32_t first, 
 int rn_scene_device_outputs(rn_scene_t *scene, const float **world_matrix, const float **world_pos_sx,
                             const float **world_rot, const float **world_scale_yz);
 
+/* SceneNode::UpdateInternalInverseTransformData for every node (Source/Scene/RNSceneNode.cpp:548-568): inverse local
+ * matrix = WithScaling(1/scale or 0) . Rotate(conj(rot)) . Translate(-pos), inverse world = inverse local * parent's
+ * inverse world.  Lazy in the reference (computed when GetInverseWorldTransform is called, e.g. by Drawable::Update);
+ * here an explicit pass over the node columns, independent of rn_transform_propagate.  Storage is allocated on the
+ * first call (64 bytes per node). */
+int rn_transform_inverse(rn_scene_t *scene, void *cuda_stream);
+/* SceneNode::UpdateInternalBoundsData for every node (Source/Scene/RNSceneNode.cpp:570-588): transformed bounding
+ * sphere (Source/Math/RNSphere.h:62-73) and transformed AABB (Source/Math/RNAABB.h:108-114,152-177) from the world
+ * TRS left by the last propagate.  The cull kernels evaluate the sphere on the fly and do not need this call; it
+ * materialises what GetBoundingSphere / GetBoundingBox return (occlusion tests, picking, debugging). */
+int rn_bounds_update(rn_scene_t *scene, void *cuda_stream);
+/* Device pointers (slot order) of the optional outputs; NULL if the producing call has not run yet.
+ * inverse_world_matrix: 16 floats; bounding_sphere: float4 (centre xyz, radius); bounding_box: 6 floats. */
+int rn_scene_device_extras(rn_scene_t *scene, const float **inverse_world_matrix, const float **bounding_sphere,
+                           const float **bounding_box);
+
+/* The post-cull sorts of SceneBasic::Render (Source/Scene/RNSceneBasic.cpp:596-616) applied in place to the lists of
+ * the last rn_cull / rn_transform_cull, per camera according to the flags it was culled with:
+ *   RN_CAMERA_SORT_FRONT_TO_BACK: whole list by (render priority; squared distance of the node's world position to
+ *       the camera ascending inside equal priorities below RenderSky);
+ *   RN_CAMERA_SORT_TRANSPARENT_BACK_TO_FRONT: the range [first, last] of RenderTransparent entries by squared
+ *       distance descending, where - as in the reference - an entry at list index 0 never counts as `first`.
+ * camera_world_positions: 3 floats per camera of the last cull.  std::sort leaves the order of equal keys
+ * unspecified; this implementation is stable (equal keys keep render-list order).  Needs the render_priority
+ * column for anything but an all-RenderNormal scene.  Asynchronous on `cuda_stream`, no host synchronisation. */
+int rn_cull_sort(rn_scene_t *scene, const float *camera_world_positions, uint32_t n_cameras, void *cuda_stream);
+
 /* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
  * Pure host function; V <= 8 cameras per frame make this negligible. */
 int rn_camera_build_frustum(const rn_camera_desc *camera, rn_camera_frustum *out);
@@ -180,6 +223,12 @@ int rn_camera_build_frustum(const rn_camera_desc *camera, rn_camera_frustum *out
  * the parent or -1; every tree is complete when its root is added; roots are added in creation order.
  * Writes order[rank] = creation index.  Pure host function. */
 int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, const int32_t *render_priority, uint32_t *order);
+
+/* SceneWithVisibilityLists::AddNode order of the default volume (Source/Scene/RNSceneWithVisibilityLists.cpp:210-236):
+ * children first (recursively, in child order), then the node; no priority sort.  Same conventions as
+ * rn_scenebasic_render_order.  Upload the node columns in this order to get the lists RenderVolumeList would
+ * submit for the default volume (:116-123). */
+int rn_scenevis_default_volume_order(uint32_t n, const int32_t *parent, uint32_t *order);
 
 /* ---- particles ------------------------------------------------------------------------------------------- */
 /* GenericParticleEmitter state (Source/Scene/RNParticleEmitter.cpp:24-36,379-395). */
@@ -214,6 +263,29 @@ int rn_particles_counts(rn_scene_t *scene, uint32_t *out_counts, float *out_time
 /* Copies one field of the live particles of one emitter, in vector order (synchronous). */
 int rn_particles_download(rn_scene_t *scene, uint32_t emitter, rn_particle_field field, void *dst,
                           uint32_t capacity_particles, uint32_t *out_count);
+
+/* ParticleEmitter::UpdateMesh for every emitter (Source/Scene/RNParticleEmitter.cpp:213-336): per live particle four
+ * vertices (position, colour, UV (0,0)(1,0)(0,1)(1,1), half-size corner vector in UV1 - rotated by the particle's
+ * rotation when `can_roll`) and six uint16 indices; degenerate indices for unused slots.  Output is a headless
+ * device buffer per attribute, emitter e at element offset e * max_particles_per_emitter * 4 (vertices) or * 6
+ * (indices); an emitter's mesh capacity is its own max_particles.  world_scale_x: GetWorldScale().x per emitter
+ * (NULL = 1).  flags per emitter (NULL = 0). */
+#define RN_EMITTER_CAN_ROLL          (1u << 0)   /* ParticleEmitter::SetCanRollParticles   */
+#define RN_EMITTER_RENDERED_INVERSED (1u << 1)   /* ParticleEmitter::SetIsRenderedInversed */
+typedef struct rn_particle_mesh {
+	const float    *position;   /* device, 3 floats per vertex */
+	const float    *color;      /* device, 4 floats per vertex */
+	const float    *uv0;        /* device, 2 floats per vertex */
+	const float    *uv1;        /* device, 2 floats per vertex */
+	const uint16_t *indices;    /* device, 6 per particle slot */
+	uint32_t        vertex_stride_per_emitter;   /* = max_particles_per_emitter * 4 */
+	uint32_t        index_stride_per_emitter;    /* = max_particles_per_emitter * 6 */
+} rn_particle_mesh;
+int rn_particles_build_mesh(rn_scene_t *scene, const float *world_scale_x, const uint32_t *flags, rn_particle_mesh *out,
+                            void *cuda_stream);
+/* Copies the mesh of one emitter to the host (synchronous): max_particles*4 vertices, max_particles*6 indices. */
+int rn_particles_download_mesh(rn_scene_t *scene, uint32_t emitter, float *position, float *color, float *uv0, float *uv1,
+                               uint16_t *indices);
 
 /* ---- introspection for the bench / tests ---------------------------------------------------------------- */
 typedef struct rn_scene_stats {

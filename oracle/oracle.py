@@ -151,16 +151,31 @@ def cull(wpos, wrot, wscale, sphere, flags, group, frustum: np.ndarray, want_sph
     return (out[:cnt].copy(), sph) if want_sphere else out[:cnt].copy()
 
 
-def scene_reference(scene: Scene, frustum_records: np.ndarray) -> dict:
-    """Full oracle frame for a scenegen.Scene: order, world TRS/matrices (creation order), lists of creation ids."""
-    order = render_order(scene.parent, scene.priority)
+def scene_reference(scene: Scene, frustum_records: np.ndarray, cameras: np.ndarray | None = None,
+                    vislists: bool = False, aabb_test: bool = False) -> dict:
+    """Full oracle frame for a scenegen.Scene: order, world TRS/matrices/inverse/AABB (creation order), lists of
+    creation ids.  `cameras` (scenegen.CAMERA_DTYPE records): also apply the post-cull sorts of SceneBasic::Render
+    with each camera's flags | Camera::Flags::Defaults (A11).  vislists: SceneWithVisibilityLists default-volume
+    order, no sorts (A10).  aabb_test: the RN_CAMERA_TEST_AABB extension on every camera."""
+    from rayne_b200.scenegen import CAM_DEFAULTS
+    order = vislist_order(scene.parent) if vislists else render_order(scene.parent, scene.priority)
     parent = np.where(scene.parent >= 0, scene.parent, RN_NO_PARENT).astype(np.uint32)
     wpos, wrot, wscale, wmat = world(parent, scene.pos, scene.scale, scene.rot)
-    lists = []
-    for fr in np.atleast_1d(frustum_records):
+    winv = inverse(parent, scene.pos, scene.scale, scene.rot)
+    aabb = bounds(wrot, wscale, scene.box)
+    lists, unsorted = [], []
+    for c, fr in enumerate(np.atleast_1d(frustum_records)):
         vis = cull(wpos[order], wrot[order], wscale[order], scene.sphere[order], scene.flags[order], scene.group[order], fr)
-        lists.append(order[vis])
-    return {"order": order, "wpos": wpos, "wrot": wrot, "wscale": wscale, "wmat": wmat, "lists": lists}
+        lst = order[vis]
+        if aabb_test:
+            lst = cull_aabb(wpos, aabb, scene.flags, fr, lst)
+        unsorted.append(lst)
+        if cameras is not None and not vislists:
+            flags = int(np.atleast_1d(cameras)[c]["flags"]) | CAM_DEFAULTS
+            lst = sort_list(lst, scene.priority, wpos, np.atleast_1d(cameras)[c]["pos"], bool(flags & (1 << 6)), bool(flags & (1 << 5)))
+        lists.append(lst)
+    return {"order": order, "wpos": wpos, "wrot": wrot, "wscale": wscale, "wmat": wmat, "winv": winv, "aabb": aabb,
+            "lists": lists, "lists_unsorted": unsorted}
 
 
 class Emitters:

@@ -17,6 +17,9 @@ RN_MAX_CAMERAS = 8
 RN_NO_PARENT = 0xFFFFFFFF
 
 DL_WORLD_POSITION, DL_WORLD_ROTATION, DL_WORLD_SCALE, DL_WORLD_MATRIX, DL_SLOT_OF_RANK, DL_RANK_OF_SLOT = range(6)
+DL_INVERSE_WORLD_MATRIX, DL_BOUNDING_SPHERE, DL_BOUNDING_BOX = 6, 7, 8
+CAM_SORT_TRANSPARENT_BACK_TO_FRONT, CAM_SORT_FRONT_TO_BACK, CAM_TEST_AABB = 1 << 5, 1 << 6, 1 << 31
+EMITTER_CAN_ROLL, EMITTER_RENDERED_INVERSED = 1, 2
 PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
 
 EXPORTS = [
@@ -26,6 +29,8 @@ EXPORTS = [
     "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
     "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
     "rn_scene_profile", "rn_scene_profile_read",
+    "rn_transform_inverse", "rn_bounds_update", "rn_scene_device_extras", "rn_cull_sort",
+    "rn_scenevis_default_volume_order", "rn_particles_build_mesh", "rn_particles_download_mesh",
 ]
 
 
@@ -43,7 +48,13 @@ class SceneDesc(C.Structure):
 
 class NodeColumns(C.Structure):
     _fields_ = [("position", C.c_void_p), ("scale", C.c_void_p), ("rotation", C.c_void_p), ("parent", C.c_void_p),
-                ("flags", C.c_void_p), ("render_group", C.c_void_p), ("bounding_sphere", C.c_void_p)]
+                ("flags", C.c_void_p), ("render_group", C.c_void_p), ("bounding_sphere", C.c_void_p),
+                ("bounding_box", C.c_void_p), ("render_priority", C.c_void_p)]
+
+
+class ParticleMesh(C.Structure):
+    _fields_ = [("position", C.c_void_p), ("color", C.c_void_p), ("uv0", C.c_void_p), ("uv1", C.c_void_p),
+                ("indices", C.c_void_p), ("vertex_stride_per_emitter", C.c_uint32), ("index_stride_per_emitter", C.c_uint32)]
 
 
 class VisList(C.Structure):
@@ -138,11 +149,21 @@ def render_order(parent: np.ndarray, priority: np.ndarray | None = None) -> np.n
     return order
 
 
-class RankedScene:
-    """A scenegen.Scene re-ordered into the reference's render-list order (what a Scene subclass hands over)."""
+def vislist_order(parent: np.ndarray) -> np.ndarray:
+    """rn_scenevis_default_volume_order: order[rank] = creation index (SceneWithVisibilityLists default volume)."""
+    lib = load()
+    parent = np.ascontiguousarray(parent, dtype=np.int32)
+    order = np.zeros(parent.shape[0], dtype=np.uint32)
+    _check(lib.rn_scenevis_default_volume_order(C.c_uint32(parent.shape[0]), _ptr(parent), _ptr(order)))
+    return order
 
-    def __init__(self, scene: Scene):
-        self.order = render_order(scene.parent, scene.priority)          # rank -> creation id
+
+class RankedScene:
+    """A scenegen.Scene re-ordered into the reference's render-list order (what a Scene subclass hands over).
+    vislists=True: the default-volume order of SceneWithVisibilityLists instead of SceneBasic's render list."""
+
+    def __init__(self, scene: Scene, vislists: bool = False):
+        self.order = vislist_order(scene.parent) if vislists else render_order(scene.parent, scene.priority)
         self.rank_of = np.empty(scene.n, dtype=np.uint32)                # creation id -> rank
         self.rank_of[self.order] = np.arange(scene.n, dtype=np.uint32)
         o = self.order
@@ -154,6 +175,8 @@ class RankedScene:
         self.flags = np.ascontiguousarray(scene.flags[o])
         self.group = np.ascontiguousarray(scene.group[o])
         self.sphere = np.ascontiguousarray(scene.sphere[o])
+        self.box = None if scene.box is None else np.ascontiguousarray(scene.box[o])
+        self.priority = np.ascontiguousarray(scene.priority[o]) if np.any(scene.priority != 0) else None
         self.n = scene.n
         self.roots = np.nonzero(self.parent == RN_NO_PARENT)[0].astype(np.uint32)
 
@@ -194,6 +217,12 @@ class SceneHandle:
                            _ptr(np.ascontiguousarray(rs.parent, dtype=np.uint32)),
                            _ptr(np.ascontiguousarray(rs.flags, dtype=np.uint32)),
                            _ptr(np.ascontiguousarray(rs.group, dtype=np.uint32)), _ptr(_f32(rs.sphere, 4)))
+        box = getattr(rs, "box", None)
+        prio = getattr(rs, "priority", None)
+        keep_box = None if box is None else _f32(box, 6)
+        keep_prio = None if prio is None else np.ascontiguousarray(prio, dtype=np.int32)
+        cols.bounding_box = _ptr(keep_box)
+        cols.render_priority = _ptr(keep_prio)
         _check(self.lib.rn_scene_upload(self._h, C.byref(cols), 0, rs.n))
         self.n = rs.n
 
@@ -226,6 +255,16 @@ class SceneHandle:
 
     def transform_cull(self, frustums: np.ndarray, stream: int = 0):
         return self._cull(self.lib.rn_transform_cull, frustums, stream)
+
+    def transform_inverse(self, stream: int = 0) -> None:
+        _check(self.lib.rn_transform_inverse(self._h, C.c_void_p(stream)))
+
+    def bounds_update(self, stream: int = 0) -> None:
+        _check(self.lib.rn_bounds_update(self._h, C.c_void_p(stream)))
+
+    def cull_sort(self, camera_positions: np.ndarray, stream: int = 0) -> None:
+        cp = _f32(np.atleast_2d(camera_positions), 3)
+        _check(self.lib.rn_cull_sort(self._h, _ptr(cp), C.c_uint32(cp.shape[0]), C.c_void_p(stream)))
 
     def set_list_mode(self, ranks: bool, rank_offset: int = 0) -> None:
         _check(self.lib.rn_scene_set_list_mode(self._h, int(ranks), C.c_uint32(rank_offset)))
@@ -260,7 +299,9 @@ class SceneHandle:
     def download(self, what: int, first: int = 0, count: int | None = None) -> np.ndarray:
         count = self.n - first if count is None else count
         width, dt = {DL_WORLD_POSITION: (3, np.float32), DL_WORLD_ROTATION: (4, np.float32), DL_WORLD_SCALE: (3, np.float32),
-                     DL_WORLD_MATRIX: (16, np.float32), DL_SLOT_OF_RANK: (1, np.uint32), DL_RANK_OF_SLOT: (1, np.uint32)}[what]
+                     DL_WORLD_MATRIX: (16, np.float32), DL_SLOT_OF_RANK: (1, np.uint32), DL_RANK_OF_SLOT: (1, np.uint32),
+                     DL_INVERSE_WORLD_MATRIX: (16, np.float32), DL_BOUNDING_SPHERE: (4, np.float32),
+                     DL_BOUNDING_BOX: (6, np.float32)}[what]
         out = np.zeros((count, width), dtype=dt)
         _check(self.lib.rn_scene_download(self._h, what, first, count, _ptr(out)))
         return out[:, 0] if width == 1 else out
@@ -290,6 +331,21 @@ class SceneHandle:
     def particles_sort(self, camera_pos, stream: int = 0) -> None:
         cp = (C.c_float * 3)(*[float(x) for x in camera_pos])
         _check(self.lib.rn_particles_sort(self._h, cp, C.c_void_p(stream)))
+
+    def particles_build_mesh(self, world_scale_x=None, flags=None, stream: int = 0) -> ParticleMesh:
+        sc = None if world_scale_x is None else _f32(world_scale_x)
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
+        out = ParticleMesh()
+        _check(self.lib.rn_particles_build_mesh(self._h, _ptr(sc), _ptr(fl), C.byref(out), C.c_void_p(stream)))
+        return out
+
+    def particles_download_mesh(self, emitter: int, max_particles: int) -> dict:
+        out = {"mesh_pos": np.zeros((max_particles * 4, 3), np.float32), "mesh_color": np.zeros((max_particles * 4, 4), np.float32),
+               "mesh_uv0": np.zeros((max_particles * 4, 2), np.float32), "mesh_uv1": np.zeros((max_particles * 4, 2), np.float32),
+               "mesh_idx": np.zeros(max_particles * 6, np.uint16)}
+        _check(self.lib.rn_particles_download_mesh(self._h, emitter, _ptr(out["mesh_pos"]), _ptr(out["mesh_color"]),
+                                                   _ptr(out["mesh_uv0"]), _ptr(out["mesh_uv1"]), _ptr(out["mesh_idx"])))
+        return out
 
     def particles_counts(self) -> tuple[np.ndarray, np.ndarray]:
         counts = np.zeros(self.n_emitters, dtype=np.uint32)

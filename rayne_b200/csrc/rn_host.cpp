@@ -358,3 +358,51 @@ extern "C" int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, con
 	RN_REQUIRE(r == n, RN_ERR_INVALID, "internal error: %u of %u nodes ordered", r, n);
 	return RN_OK;
 }
+
+// SceneWithVisibilityLists::AddNode (RNSceneWithVisibilityLists.cpp:210-236): UpdateSceneInfo adds the children first
+// (RNSceneNode.cpp:286-291), then the node is push_back-ed into the default volume: plain post-order, no priorities.
+extern "C" int rn_scenevis_default_volume_order(uint32_t n, const int32_t *parent, uint32_t *order)
+{
+	RN_REQUIRE(parent && order, RN_ERR_INVALID, "NULL argument");
+	if(n == 0) return RN_OK;
+	std::vector<uint32_t> ofs(n + 1, 0), child;
+	for(uint32_t i = 0; i < n; i++)
+	{
+		RN_REQUIRE(parent[i] < (int32_t)i, RN_ERR_INVALID, "parent[%u] = %d must precede its child", i, parent[i]);
+		if(parent[i] >= 0) ofs[parent[i] + 1]++;
+	}
+	for(uint32_t i = 0; i < n; i++) ofs[i + 1] += ofs[i];
+	child.resize(ofs[n]);
+	{
+		std::vector<uint32_t> fill(ofs.begin(), ofs.end() - 1);
+		for(uint32_t i = 0; i < n; i++)
+			if(parent[i] >= 0) child[fill[parent[i]]++] = i;
+	}
+	std::vector<uint32_t> stack_node, stack_pos;
+	uint32_t r = 0;
+	for(uint32_t root = 0; root < n; root++)
+	{
+		if(parent[root] >= 0) continue;
+		stack_node.push_back(root);
+		stack_pos.push_back(ofs[root]);
+		while(!stack_node.empty())
+		{
+			const uint32_t u = stack_node.back();
+			uint32_t &k = stack_pos.back();
+			if(k < ofs[u + 1])
+			{
+				const uint32_t c = child[k++];
+				stack_node.push_back(c);
+				stack_pos.push_back(ofs[c]);
+			}
+			else
+			{
+				order[r++] = u;
+				stack_node.pop_back();
+				stack_pos.pop_back();
+			}
+		}
+	}
+	RN_REQUIRE(r == n, RN_ERR_INVALID, "internal error: %u of %u nodes ordered", r, n);
+	return RN_OK;
+}

@@ -25,6 +25,8 @@ int cuda_fail(cudaError_t err, const char *what, const char *file, int line);
 constexpr uint32_t kMaxSublevels = 12;   // sublevel 0 = spine nodes of the tile, 1.. = depth inside a unit
 constexpr uint32_t kWarpsPerCta = 4;     // tile kernel: one tile per warp
 constexpr uint32_t kTileThreads = kWarpsPerCta * 32;
+constexpr uint32_t kSuperTiles = 256;    // tiles per superblock of the compaction offsets
+constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 // One tile = a contiguous range of ranks [start, start+count) stored at the same slots, permuted so that each
 // sublevel is contiguous and, inside a sublevel, the inner nodes (nodes with children) come first.  64 bytes.
@@ -76,6 +78,22 @@ struct rn_scene
 	uint32_t *list_counts = nullptr;   // [RN_MAX_CAMERAS]
 	uint32_t *lists[RN_MAX_CAMERAS] = {};
 	uint32_t list_capacity = 0;
+	// optional columns / outputs (allocated on first use; rn_bounds.cu, rn_sort.cu)
+	float4 *box0 = nullptr;      // local AABB: minExtend xyz, maxExtend x   (nullptr = default AABB(-1, 1))
+	float2 *box1 = nullptr;      // local AABB: maxExtend y, z
+	float4 *winv = nullptr;      // inverse world matrix, 4 x float4 per slot (rn_transform_inverse)
+	float4 *bsphere = nullptr;   // transformed bounding sphere: centre xyz, radius (rn_bounds_update)
+	float2 *baabb = nullptr;     // transformed AABB: 3 x float2 per slot = min xyz, max xyz (rn_bounds_update)
+	bool have_inverse = false, have_bounds = false;
+	uint8_t *prio_group = nullptr;     // per slot: dense index of the node's render priority (ascending)
+	uint32_t n_prio_groups = 1;
+	uint32_t transparent_group = 0xffffffffu;  // dense index of RN_RENDER_TRANSPARENT, or none
+	uint32_t first_sky_group = 0xffffffffu;    // first dense index whose priority is >= RN_RENDER_SKY, or none
+	uint32_t last_cam_flags[RN_MAX_CAMERAS] = {};
+	uint32_t *sort_scratch = nullptr;  // radix sort: 4 arrays of max_nodes + histograms
+	uint32_t *sort_hist = nullptr;
+	uint32_t *sort_ranges = nullptr;   // [RN_MAX_CAMERAS][2]: transparent range begin, end (device)
+	uint32_t sort_blocks_cap = 0;
 	uint32_t *spine_slots = nullptr;   // all spine slots grouped by depth
 	std::vector<uint32_t> spine_level_ofs; // host: offsets into spine_slots per depth (size levels+1)
 	float *scratch_cols = nullptr;     // device staging for rn_scene_update_nodes
@@ -97,4 +115,18 @@ struct rn_scene
 
 namespace rn {
 int particles_destroy(rn_scene *scene);
+void extras_free(rn_scene *scene);      // rn_bounds.cu / rn_sort.cu storage
+// Extension RN_CAMERA_TEST_AABB: clears the visibility bits of the flagged cameras for nodes whose transformed AABB
+// fails the plane test and recounts tile_counts / super_totals (between the cull kernel and the emit kernel).
+int aabb_filter_launch(rn_scene *scene, const rn_camera_frustum *cams, uint32_t ncams, cudaStream_t stream);
+
+template <class T>
+inline int dev_alloc(rn_scene *s, T **p, size_t count)
+{
+	*p = nullptr;
+	if(count == 0) count = 1;
+	RN_CUDA(cudaMalloc(reinterpret_cast<void **>(p), count * sizeof(T)));
+	s->device_bytes += count * sizeof(T);
+	return RN_OK;
+}
 }

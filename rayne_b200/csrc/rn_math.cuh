@@ -85,4 +85,83 @@ __device__ __forceinline__ Affine affine_mul(const Affine &P, const Affine &L)
 	return o;
 }
 
+// ---- A3: inverse transforms -----------------------------------------------------------------------------------
+// SceneNode::UpdateInternalInverseTransformData (reference: Source/Scene/RNSceneNode.cpp:552-554):
+//   WithScaling(scale != 0 ? 1 / scale : 0); Rotate(conj(rot)); Translate(pos * -1)
+// `scale != 0.0f` is the epsilon compare of all three components (Source/Math/RNVector.h:403-409).  The rotation
+// matrix of the conjugate is, float for float, the transpose of the rotation matrix of rot (x*y == (-x)*(-y),
+// a - (-b) == a + b), S * Rc scales ROW r by 1/scale_r, Matrix::Translate (Source/Math/RNMatrix.h:514-527) adds
+// the dot products of the rows with -pos to a zero translation.
+__device__ __forceinline__ Affine inverse_local_matrix(const Vec3 &p, const Quat &q, const Vec3 &s)
+{
+	const float eps = 1.1920928955078125e-7f; // k::EpsilonFloat = FLT_EPSILON
+	Vec3 is = {0.0f, 0.0f, 0.0f};
+	if(!(fabsf(s.x) <= eps && fabsf(s.y) <= eps && fabsf(s.z) <= eps))
+	{
+		is.x = 1.0f / s.x; is.y = 1.0f / s.y; is.z = 1.0f / s.z;
+	}
+	float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
+	float xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w;
+	float yz = q.y * q.z, yw = q.y * q.w, zw = q.z * q.w;
+	// R(q), row-major names: rRC
+	float r00 = 1.0f - 2.0f * (yy + zz), r01 = 2.0f * (xy - zw), r02 = 2.0f * (xz + yw);
+	float r10 = 2.0f * (xy + zw), r11 = 1.0f - 2.0f * (xx + zz), r12 = 2.0f * (yz - xw);
+	float r20 = 2.0f * (xz - yw), r21 = 2.0f * (yz + xw), r22 = 1.0f - 2.0f * (xx + yy);
+	Affine a;   // a.m[c*3 + r] = is_r * Rc[r][c] = is_r * R[c][r]
+	a.m[0] = is.x * r00; a.m[1] = is.y * r01; a.m[2] = is.z * r02;
+	a.m[3] = is.x * r10; a.m[4] = is.y * r11; a.m[5] = is.z * r12;
+	a.m[6] = is.x * r20; a.m[7] = is.y * r21; a.m[8] = is.z * r22;
+	const float tx = p.x * -1.0f, ty = p.y * -1.0f, tz = p.z * -1.0f;
+#pragma unroll
+	for(int r = 0; r < 3; r++)
+		a.m[9 + r] = a.m[r] * tx + a.m[3 + r] * ty + a.m[6 + r] * tz;
+	return a;
+}
+
+// ---- A4: transformed AABB -------------------------------------------------------------------------------------
+// AABB::operator*=(Vector3) then AABB::SetRotation (reference: Source/Math/RNAABB.h:108-114,152-177;
+// Matrix::operator*(Vector3) Source/Math/RNMatrix.h:145-151 with a zero translation).
+struct Box { Vec3 mn, mx; };
+
+__device__ __forceinline__ Vec3 rot_apply(const float (&m)[9], float x, float y, float z)
+{
+	Vec3 r;   // m[c*3 + r]
+	r.x = m[0] * x + m[3] * y + m[6] * z;
+	r.y = m[1] * x + m[4] * y + m[7] * z;
+	r.z = m[2] * x + m[5] * y + m[8] * z;
+	return r;
+}
+
+__device__ __forceinline__ Box world_aabb(const Box &local, const Vec3 &ws, const Quat &q)
+{
+	Vec3 mn = {local.mn.x * ws.x, local.mn.y * ws.y, local.mn.z * ws.z};
+	Vec3 mx = {local.mx.x * ws.x, local.mx.y * ws.y, local.mx.z * ws.z};
+	float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
+	float xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w;
+	float yz = q.y * q.z, yw = q.y * q.w, zw = q.z * q.w;
+	float m[9];
+	m[0] = 1.0f - 2.0f * (yy + zz); m[3] = 2.0f * (xy - zw); m[6] = 2.0f * (xz + yw);
+	m[1] = 2.0f * (xy + zw); m[4] = 1.0f - 2.0f * (xx + zz); m[7] = 2.0f * (yz - xw);
+	m[2] = 2.0f * (xz - yw); m[5] = 2.0f * (yz + xw); m[8] = 1.0f - 2.0f * (xx + yy);
+	Vec3 c[4];
+	c[0] = rot_apply(m, mn.x, mn.y, mx.z);
+	c[1] = rot_apply(m, mn.x, mx.y, mx.z);
+	c[2] = rot_apply(m, mx.x, mx.y, mn.z);
+	c[3] = rot_apply(m, mx.x, mn.y, mn.z);
+	Box o;
+	o.mn = rot_apply(m, mn.x, mn.y, mn.z);
+	o.mx = rot_apply(m, mx.x, mx.y, mx.z);
+#pragma unroll
+	for(int i = 0; i < 4; i++)
+	{
+		o.mn.x = (c[i].x < o.mn.x) ? c[i].x : o.mn.x;
+		o.mn.y = (c[i].y < o.mn.y) ? c[i].y : o.mn.y;
+		o.mn.z = (c[i].z < o.mn.z) ? c[i].z : o.mn.z;
+		o.mx.x = (c[i].x > o.mx.x) ? c[i].x : o.mx.x;
+		o.mx.y = (c[i].y > o.mx.y) ? c[i].y : o.mx.y;
+		o.mx.z = (c[i].z > o.mx.z) ? c[i].z : o.mx.z;
+	}
+	return o;
+}
+
 } // namespace rn

@@ -54,6 +54,14 @@ struct ParticleStore
 	uint32_t *sorted = nullptr;
 	EmitterState *emitters = nullptr;
 	uint32_t *mt = nullptr;    // [n_emitters][624]
+	// render mesh (rn_particles_build_mesh), allocated on first use: per emitter cap*4 vertices, cap*6 indices
+	float *mesh_pos = nullptr;      // 3 floats per vertex
+	float4 *mesh_color = nullptr;
+	float2 *mesh_uv0 = nullptr, *mesh_uv1 = nullptr;
+	uint16_t *mesh_idx = nullptr;
+	float *mesh_scale = nullptr;    // per emitter: GetWorldScale().x
+	uint32_t *mesh_flags = nullptr; // per emitter: RN_EMITTER_*
+	bool have_mesh = false;
 };
 
 struct ParticleView
@@ -353,9 +361,77 @@ __global__ void __launch_bounds__(512) particles_sort_kernel(ParticleBuffers cur
 		sorted[seg + i] = (uint32_t)(s_keys[i] & 0xffffffffu);
 }
 
+// ParticleEmitter::UpdateMesh (Source/Scene/RNParticleEmitter.cpp:213-336).  One thread per particle slot of the
+// emitter's mesh: quad w holds particle w (or stop-1-w when rendered inversed); its six indices are
+// particle*4 + {0,1,2,2,1,3} (the reference indexes with the particle index, :283-288); slots >= stop get degenerate
+// indices slot*4 (:322-330) and their vertices are left alone.  188 bytes written per live particle, 48 read.
+struct MeshView
+{
+	const float4 *a, *color, *misc;
+	const EmitterState *emitters;
+	const float *scale;
+	const uint32_t *flags;
+	float *pos;
+	float4 *col;
+	float2 *uv0, *uv1;
+	uint16_t *idx;
+	uint32_t cap;
+};
+
+__global__ void __launch_bounds__(128) particles_mesh_kernel(MeshView mv)
+{
+	const uint32_t e = blockIdx.y;
+	const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t maxp = mv.emitters[e].d.max_particles;
+	if(w >= maxp)
+		return;
+	const uint32_t count = mv.emitters[e].count;
+	const uint32_t stop = count < maxp ? count : maxp;
+	const size_t seg = (size_t)e * mv.cap;
+	uint32_t *idx32 = reinterpret_cast<uint32_t *>(mv.idx + (seg + w) * 6);
+	if(w >= stop)
+	{
+		const uint32_t v = (w * 4u) & 0xffffu;
+		idx32[0] = idx32[1] = idx32[2] = v | (v << 16);
+		return;
+	}
+	const uint32_t flags = mv.flags[e];
+	const uint32_t pi = (flags & RN_EMITTER_RENDERED_INVERSED) ? stop - 1u - w : w;
+	const float4 a = mv.a[seg + pi], c = mv.color[seg + pi], m = mv.misc[seg + pi];
+	const float scale = mv.scale[e];
+	// Vector2 halfSize = particle->size / 2.0f * scale
+	const float hx = m.y / 2.0f * scale, hy = m.z / 2.0f * scale;
+	float tx = hx, ty = hy, bx = hx, by = -hy;
+	if(flags & RN_EMITTER_CAN_ROLL)
+	{
+		const float cs = cosf(m.x), sn = sinf(m.x);
+		tx = cs * hx - sn * hy; ty = sn * hx + cs * hy;
+		bx = cs * hx + sn * hy; by = sn * hx - cs * hy;
+	}
+	float4 *pos4 = reinterpret_cast<float4 *>(mv.pos + (seg + w) * 12);
+	pos4[0] = make_float4(a.x, a.y, a.z, a.x);
+	pos4[1] = make_float4(a.y, a.z, a.x, a.y);
+	pos4[2] = make_float4(a.z, a.x, a.y, a.z);
+	float4 *col = mv.col + (seg + w) * 4;
+	col[0] = c; col[1] = c; col[2] = c; col[3] = c;
+	float4 *uv0 = reinterpret_cast<float4 *>(mv.uv0 + (seg + w) * 4);
+	uv0[0] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+	uv0[1] = make_float4(0.0f, 1.0f, 1.0f, 1.0f);
+	float4 *uv1 = reinterpret_cast<float4 *>(mv.uv1 + (seg + w) * 4);
+	uv1[0] = make_float4(-tx, -ty, bx, by);
+	uv1[1] = make_float4(-bx, -by, tx, ty);
+	const uint32_t b = pi * 4u;
+	idx32[0] = ((b + 0u) & 0xffffu) | (((b + 1u) & 0xffffu) << 16);
+	idx32[1] = ((b + 2u) & 0xffffu) | (((b + 2u) & 0xffffu) << 16);
+	idx32[2] = ((b + 1u) & 0xffffu) | (((b + 3u) & 0xffffu) << 16);
+}
+
 static void free_store(ParticleStore *p)
 {
 	if(!p) return;
+	void *mesh[] = {p->mesh_pos, p->mesh_color, p->mesh_uv0, p->mesh_uv1, p->mesh_idx, p->mesh_scale, p->mesh_flags};
+	for(void *q : mesh)
+		if(q) cudaFree(q);
 	for(int g = 0; g < 2; g++)
 	{
 		if(p->buf[g].a) cudaFree(p->buf[g].a);
@@ -560,5 +636,82 @@ extern "C" int rn_particles_download(rn_scene_t *s, uint32_t emitter, rn_particl
 		default:
 			RN_REQUIRE(false, RN_ERR_INVALID, "unknown particle field %d", (int)field);
 	}
+	return RN_OK;
+}
+
+extern "C" int rn_particles_build_mesh(rn_scene_t *s, const float *world_scale_x, const uint32_t *flags, rn_particle_mesh *out,
+                                       void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	const size_t total = (size_t)s->desc.max_emitters * p->cap;
+	if(!p->mesh_pos)
+	{
+		int rc = palloc(s, &p->mesh_pos, total * 12);
+		if(!rc) rc = palloc(s, &p->mesh_color, total * 4);
+		if(!rc) rc = palloc(s, &p->mesh_uv0, total * 4);
+		if(!rc) rc = palloc(s, &p->mesh_uv1, total * 4);
+		if(!rc) rc = palloc(s, &p->mesh_idx, total * 6);
+		if(!rc) rc = palloc(s, &p->mesh_scale, (size_t)p->n_emitters);
+		if(!rc) rc = palloc(s, &p->mesh_flags, (size_t)p->n_emitters);
+		if(rc) return rc;
+		// the reference's mesh buffers start zeroed (calloc'ed staging); unused vertices stay that way
+		RN_CUDA(cudaMemsetAsync(p->mesh_pos, 0, total * 12 * sizeof(float), stream));
+		RN_CUDA(cudaMemsetAsync(p->mesh_color, 0, total * 4 * sizeof(float4), stream));
+		RN_CUDA(cudaMemsetAsync(p->mesh_uv0, 0, total * 4 * sizeof(float2), stream));
+		RN_CUDA(cudaMemsetAsync(p->mesh_uv1, 0, total * 4 * sizeof(float2), stream));
+		RN_CUDA(cudaMemsetAsync(p->mesh_idx, 0, total * 6 * sizeof(uint16_t), stream));
+	}
+	{
+		std::vector<float> sc(p->n_emitters, 1.0f);
+		std::vector<uint32_t> fl(p->n_emitters, 0u);
+		if(world_scale_x) memcpy(sc.data(), world_scale_x, sizeof(float) * p->n_emitters);
+		if(flags) memcpy(fl.data(), flags, sizeof(uint32_t) * p->n_emitters);
+		// small synchronous parameter copies (pageable host memory): n_emitters * 8 bytes
+		RN_CUDA(cudaMemcpyAsync(p->mesh_scale, sc.data(), sizeof(float) * p->n_emitters, cudaMemcpyHostToDevice, stream));
+		RN_CUDA(cudaMemcpyAsync(p->mesh_flags, fl.data(), sizeof(uint32_t) * p->n_emitters, cudaMemcpyHostToDevice, stream));
+		RN_CUDA(cudaStreamSynchronize(stream));
+	}
+	MeshView mv;
+	mv.a = p->buf[p->gen].a; mv.color = p->color; mv.misc = p->misc;
+	mv.emitters = p->emitters; mv.scale = p->mesh_scale; mv.flags = p->mesh_flags;
+	mv.pos = p->mesh_pos; mv.col = p->mesh_color; mv.uv0 = p->mesh_uv0; mv.uv1 = p->mesh_uv1; mv.idx = p->mesh_idx;
+	mv.cap = p->cap;
+	const dim3 grid((p->cap + 127) / 128, p->n_emitters);
+	particles_mesh_kernel<<<grid, 128, 0, stream>>>(mv);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	p->have_mesh = true;
+	if(out)
+	{
+		out->position = p->mesh_pos; out->color = reinterpret_cast<const float *>(p->mesh_color);
+		out->uv0 = reinterpret_cast<const float *>(p->mesh_uv0); out->uv1 = reinterpret_cast<const float *>(p->mesh_uv1);
+		out->indices = p->mesh_idx;
+		out->vertex_stride_per_emitter = p->cap * 4;
+		out->index_stride_per_emitter = p->cap * 6;
+	}
+	return RN_OK;
+}
+
+extern "C" int rn_particles_download_mesh(rn_scene_t *s, uint32_t emitter, float *position, float *color, float *uv0, float *uv1,
+                                          uint16_t *indices)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && emitter < p->n_emitters, RN_ERR_INVALID, "emitter %u out of range", emitter);
+	RN_REQUIRE(p->have_mesh, RN_ERR_STATE, "rn_particles_build_mesh has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	EmitterState es;
+	RN_CUDA(cudaMemcpy(&es, p->emitters + emitter, sizeof(es), cudaMemcpyDeviceToHost));
+	const size_t seg = (size_t)emitter * p->cap, nv = (size_t)es.d.max_particles * 4, ni = (size_t)es.d.max_particles * 6;
+	if(position) RN_CUDA(cudaMemcpy(position, p->mesh_pos + seg * 12, nv * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	if(color) RN_CUDA(cudaMemcpy(color, p->mesh_color + seg * 4, nv * sizeof(float4), cudaMemcpyDeviceToHost));
+	if(uv0) RN_CUDA(cudaMemcpy(uv0, p->mesh_uv0 + seg * 4, nv * sizeof(float2), cudaMemcpyDeviceToHost));
+	if(uv1) RN_CUDA(cudaMemcpy(uv1, p->mesh_uv1 + seg * 4, nv * sizeof(float2), cudaMemcpyDeviceToHost));
+	if(indices) RN_CUDA(cudaMemcpy(indices, p->mesh_idx + seg * 6, ni * sizeof(uint16_t), cudaMemcpyDeviceToHost));
 	return RN_OK;
 }

@@ -83,8 +83,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 // ---------------------------------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------------------------------
-constexpr uint32_t kSuperTiles = 256;              // tiles per superblock of the compaction offsets
-constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 struct SceneView
 {
@@ -1016,16 +1014,6 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint3
 	return true;
 }
 
-template <class T>
-static int dev_alloc(rn_scene *s, T **p, size_t count)
-{
-	*p = nullptr;
-	if(count == 0) count = 1;
-	RN_CUDA(cudaMalloc(reinterpret_cast<void **>(p), count * sizeof(T)));
-	s->device_bytes += count * sizeof(T);
-	return RN_OK;
-}
-
 static void free_nodes(rn_scene *s)
 {
 	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->d_slot_of_rank, s->vis, s->tiles,
@@ -1034,6 +1022,7 @@ static void free_nodes(rn_scene *s)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
 		if(s->lists[c]) { cudaFree(s->lists[c]); s->lists[c] = nullptr; }
+	extras_free(s);
 	if(s->scratch_host) { cudaFreeHost(s->scratch_host); s->scratch_host = nullptr; }
 	if(s->scratch_done) { cudaEventDestroy(s->scratch_done); s->scratch_done = nullptr; }
 	for(int i = 0; i < rn_scene::kProfileSlots; i++)
@@ -1298,6 +1287,59 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	if(!t.spine_slots.empty())
 		RN_CUDA(cudaMemcpy(s->spine_slots, t.spine_slots.data(), sizeof(uint32_t) * t.spine_slots.size(), cudaMemcpyHostToDevice));
 
+	// optional columns: local AABB (A4 / C5a) and render priority (A11)
+	if(cols->bounding_box)
+	{
+		std::vector<float4> hb0(count);
+		std::vector<float2> hb1(count);
+		for(uint32_t slot = 0; slot < count; slot++)
+		{
+			const float *b = cols->bounding_box + (size_t)t.rank_of_slot[slot] * 6;
+			hb0[slot] = make_float4(b[0], b[1], b[2], b[3]);
+			hb1[slot] = make_float2(b[4], b[5]);
+		}
+		int brc = RN_OK;
+		if(!s->box0) brc = dev_alloc(s, &s->box0, (size_t)s->desc.max_nodes);
+		if(!brc && !s->box1) brc = dev_alloc(s, &s->box1, (size_t)s->desc.max_nodes);
+		if(brc) return brc;
+		RN_CUDA(cudaMemcpy(s->box0, hb0.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
+		RN_CUDA(cudaMemcpy(s->box1, hb1.data(), sizeof(float2) * count, cudaMemcpyHostToDevice));
+	}
+	else
+	{
+		if(s->box0) { cudaFree(s->box0); s->box0 = nullptr; }
+		if(s->box1) { cudaFree(s->box1); s->box1 = nullptr; }
+	}
+	s->n_prio_groups = 1;
+	s->transparent_group = s->first_sky_group = 0xffffffffu;
+	if(cols->render_priority)
+	{
+		std::vector<int32_t> distinct(cols->render_priority, cols->render_priority + count);
+		std::sort(distinct.begin(), distinct.end());
+		distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
+		RN_REQUIRE(distinct.size() <= 256, RN_ERR_CAPACITY, "%zu distinct render priorities; rn_cull_sort supports 256", distinct.size());
+		std::vector<uint8_t> hg(count);
+		for(uint32_t slot = 0; slot < count; slot++)
+		{
+			const int32_t p = cols->render_priority[t.rank_of_slot[slot]];
+			hg[slot] = (uint8_t)(std::lower_bound(distinct.begin(), distinct.end(), p) - distinct.begin());
+		}
+		s->n_prio_groups = (uint32_t)distinct.size();
+		for(size_t g = 0; g < distinct.size(); g++)
+		{
+			if(distinct[g] == RN_RENDER_TRANSPARENT) s->transparent_group = (uint32_t)g;
+			if(distinct[g] >= RN_RENDER_SKY && s->first_sky_group == 0xffffffffu) s->first_sky_group = (uint32_t)g;
+		}
+		if(!s->prio_group)
+		{
+			int prc = dev_alloc(s, &s->prio_group, (size_t)s->desc.max_nodes);
+			if(prc) return prc;
+		}
+		RN_CUDA(cudaMemcpy(s->prio_group, hg.data(), count, cudaMemcpyHostToDevice));
+	}
+	else if(s->prio_group) { cudaFree(s->prio_group); s->prio_group = nullptr; }
+	s->have_inverse = s->have_bounds = false;
+
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
 	if(s->tile_counts) { cudaFree(s->tile_counts); s->tile_counts = nullptr; }
@@ -1324,6 +1366,8 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t first, uint32_t count)
 {
 	RN_REQUIRE(cols->parent == nullptr, RN_ERR_INVALID, "the hierarchy can only change through a full upload");
+	RN_REQUIRE(cols->bounding_box == nullptr && cols->render_priority == nullptr, RN_ERR_INVALID,
+	           "bounding_box / render_priority can only be set through a full upload");
 	if(count == 0) return RN_OK;
 	RN_CUDA(cudaSetDevice(s->device));
 	// staging layout (words): slots | pos | scale | rot | sphere | flags | group ; packed into ONE pinned buffer
@@ -1380,6 +1424,7 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
 	s->have_world = false;
+	s->have_inverse = s->have_bounds = false;
 	return RN_OK;
 }
 
@@ -1414,6 +1459,33 @@ extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
 	rc = launch_tiles<false>(s, cp, stream);
 	if(rc) return rc;
 	s->have_world = true;
+	s->have_bounds = false;
+	return RN_OK;
+}
+
+static bool wants_aabb(const rn_camera_frustum *cams, uint32_t n)
+{
+	for(uint32_t c = 0; c < n; c++)
+		if(cams[c].flags & RN_CAMERA_TEST_AABB) return true;
+	return false;
+}
+
+// rn_cull on stored transforms; with RN_CAMERA_TEST_AABB cameras the mask is post-filtered before the compaction
+static int cull_stored(rn_scene *s, const rn_camera_frustum *cameras, uint32_t n_cameras, const CullParams &cp, rn_vis_list *out_lists,
+                       cudaStream_t stream)
+{
+	int rc = clear_super_totals(s, stream);
+	if(!rc) rc = launch_cull_flat(s, cp, stream);
+	if(!rc && wants_aabb(cameras, n_cameras))
+	{
+		rc = clear_super_totals(s, stream);
+		if(!rc) rc = aabb_filter_launch(s, cameras, n_cameras, stream);
+	}
+	if(!rc) rc = launch_compaction(s, n_cameras, stream);
+	if(rc) return rc;
+	s->last_ncams = n_cameras;
+	for(uint32_t c = 0; c < n_cameras; c++) s->last_cam_flags[c] = cameras[c].flags;
+	fill_lists(s, n_cameras, out_lists);
 	return RN_OK;
 }
 
@@ -1428,14 +1500,7 @@ extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t
 	RN_CUDA(cudaSetDevice(s->device));
 	rc = ensure_lists(s, n_cameras);
 	if(rc) return rc;
-	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-	rc = clear_super_totals(s, stream);
-	if(!rc) rc = launch_cull_flat(s, cp, stream);
-	if(!rc) rc = launch_compaction(s, n_cameras, stream);
-	if(rc) return rc;
-	s->last_ncams = n_cameras;
-	fill_lists(s, n_cameras, out_lists);
-	return RN_OK;
+	return cull_stored(s, cameras, n_cameras, cp, out_lists, static_cast<cudaStream_t>(cuda_stream));
 }
 
 extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists,
@@ -1450,13 +1515,25 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	rc = ensure_lists(s, n_cameras);
 	if(rc) return rc;
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	if(wants_aabb(cameras, n_cameras))
+	{
+		// extension path: the AABB filter works on stored transforms
+		rc = launch_spine(s, stream);
+		if(!rc) rc = launch_tiles<false>(s, cp, stream);
+		if(rc) return rc;
+		s->have_world = true;
+		s->have_bounds = false;
+		return cull_stored(s, cameras, n_cameras, cp, out_lists, stream);
+	}
 	rc = clear_super_totals(s, stream);
 	if(!rc) rc = launch_spine(s, stream);
 	if(!rc) rc = launch_tiles<true>(s, cp, stream);
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->have_world = true;
+	s->have_bounds = false;
 	s->last_ncams = n_cameras;
+	for(uint32_t c = 0; c < n_cameras; c++) s->last_cam_flags[c] = cameras[c].flags;
 	fill_lists(s, n_cameras, out_lists);
 	return RN_OK;
 }
@@ -1537,7 +1614,12 @@ extern "C" int rn_scene_download(rn_scene_t *s, rn_download_what what, uint32_t 
 		memcpy(dst, s->rank_of_slot.data() + first, sizeof(uint32_t) * count);
 		return RN_OK;
 	}
-	RN_REQUIRE(s->have_world, RN_ERR_STATE, "no world transforms yet: call rn_transform_propagate / rn_transform_cull first");
+	if(what == RN_DL_INVERSE_WORLD_MATRIX)
+		RN_REQUIRE(s->have_inverse, RN_ERR_STATE, "no inverse world matrices yet: call rn_transform_inverse first");
+	else if(what == RN_DL_BOUNDING_SPHERE || what == RN_DL_BOUNDING_BOX)
+		RN_REQUIRE(s->have_bounds, RN_ERR_STATE, "no transformed bounds yet: call rn_bounds_update after the propagate");
+	else
+		RN_REQUIRE(s->have_world, RN_ERR_STATE, "no world transforms yet: call rn_transform_propagate / rn_transform_cull first");
 	RN_CUDA(cudaSetDevice(s->device));
 	RN_CUDA(cudaDeviceSynchronize());
 	uint32_t slo = 0xffffffffu, shi = 0;
@@ -1576,10 +1658,27 @@ extern "C" int rn_scene_download(rn_scene_t *s, rn_download_what what, uint32_t 
 			}
 			break;
 		}
+		case RN_DL_BOUNDING_SPHERE:
+		{
+			std::vector<float4> a(span);
+			RN_CUDA(cudaMemcpy(a.data(), s->bsphere + slo, sizeof(float4) * span, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < count; i++)
+				memcpy(out + (size_t)i * 4, &a[s->slot_of_rank[first + i] - slo], 16);
+			break;
+		}
+		case RN_DL_BOUNDING_BOX:
+		{
+			std::vector<float2> a(span * 3);
+			RN_CUDA(cudaMemcpy(a.data(), s->baabb + (size_t)slo * 3, sizeof(float2) * span * 3, cudaMemcpyDeviceToHost));
+			for(uint32_t i = 0; i < count; i++)
+				memcpy(out + (size_t)i * 6, &a[(s->slot_of_rank[first + i] - slo) * 3], 24);
+			break;
+		}
 		case RN_DL_WORLD_MATRIX:
+		case RN_DL_INVERSE_WORLD_MATRIX:
 		{
 			std::vector<float4> a(span * 4);
-			RN_CUDA(cudaMemcpy(a.data(), s->wmat + (size_t)slo * 4, sizeof(float4) * span * 4, cudaMemcpyDeviceToHost));
+			RN_CUDA(cudaMemcpy(a.data(), (what == RN_DL_WORLD_MATRIX ? s->wmat : s->winv) + (size_t)slo * 4, sizeof(float4) * span * 4, cudaMemcpyDeviceToHost));
 			for(uint32_t i = 0; i < count; i++)
 			{
 				const size_t k = s->slot_of_rank[first + i] - slo;

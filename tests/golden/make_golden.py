@@ -17,7 +17,7 @@ import numpy as np
 
 from oracle import refio
 from rayne_b200 import scenegen as sg
-from tests.helpers import standard_cameras
+from tests.helpers import sort_cameras, standard_cameras
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -27,6 +27,9 @@ SCENES = {
                                          random_bounds=True, random_groups=True, priorities=True),
     "scene_ragged": dict(ragged_nodes=1500, depth=8, seed=103, random_bounds=True),
     "scene_deep_chain": dict(n_trees=2, branching=1, depth=40, seed=104),
+    # local AABBs, RenderTransparent nodes (post-cull sorts), sort cameras; also run through SceneWithVisibilityLists
+    "scene_boxes_transparent": dict(n_trees=6, branching=4, depth=5, seed=105, nonuniform_scale=True, random_bounds=True,
+                                    random_boxes=True, priorities=True, transparent_frac=0.25),
 }
 PARTICLES = {
     "particles_default": (dict(n=3, max_particles=300, spawn_rate=0.004), 240),
@@ -41,13 +44,23 @@ def main() -> None:
     for name, kw in SCENES.items():
         scene = sg.make_scene(**kw)
         cams = standard_cameras()
-        ref = refio.run_scene(scene, cams, options=refio.OPT_INVERSE)
+        if scene.box is not None:
+            cams = np.concatenate([cams, sort_cameras()])
+        opts = refio.OPT_INVERSE | (refio.OPT_BOX if scene.box is not None else 0)
+        ref = refio.run_scene(scene, cams, options=opts)
         out = {f"in_{k}": getattr(scene, k) for k in SCENE_COLS}
+        if scene.box is not None:
+            out["in_box"] = scene.box
         out["in_cameras"] = cams
-        for k in ("order", "wpos", "wrot", "wscale", "wmat", "winv", "sphere", "frustum", "cam_flags", "cam_group"):
+        for k in ("order", "wpos", "wrot", "wscale", "wmat", "winv", "aabb", "sphere", "frustum", "cam_flags", "cam_group"):
             out[f"ref_{k}"] = ref[k]
         for c, lst in enumerate(ref["lists"]):
             out[f"ref_list{c}"] = lst
+        # the same scene through SceneWithVisibilityLists (default volume): A10 order + its lists
+        vis = refio.run_scene(scene, cams, options=opts | refio.OPT_VISLISTS)
+        out["ref_vis_order"] = vis["order"]
+        for c, lst in enumerate(vis["lists"]):
+            out[f"ref_vis_list{c}"] = lst
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
         print(name, scene.n, [len(l) for l in ref["lists"]])
     for name, (kw, steps) in PARTICLES.items():
@@ -60,6 +73,13 @@ def main() -> None:
         for k, r in enumerate(ref):
             out[f"ref_rec{k}"] = r["rec"]
             out[f"ref_time{k}"] = r["time"]
+        if name == "particles_varied":
+            # P6: the render mesh of the same emitters - plain, rendered inversed, rolled
+            for tag, popt in (("", 0), ("_inv", refio.POPT_INVERSED), ("_roll", refio.POPT_ROLL)):
+                mref = refio.run_particles(em, steps, options=refio.POPT_MESH | popt)
+                for k, r in enumerate(mref):
+                    for key in ("mesh_pos", "mesh_color", "mesh_uv0", "mesh_uv1", "mesh_idx"):
+                        out[f"ref_{key}{tag}{k}"] = r[key]
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
         print(name, [r["count"] for r in ref])
 

@@ -37,13 +37,14 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} is declared in include/rn_cuda.h but not exported by librn_cuda.so"
     assert sorted(capi.EXPORTS) == names, "capi.EXPORTS and the header disagree"
     lib.rn_abi_version.restype = C.c_int
-    assert lib.rn_abi_version() == 1
+    assert lib.rn_abi_version() == 2
 
 
 def test_pod_layouts_match_the_header():
     # sizes computed from the header's field lists (all 4-byte members, pointers 8 bytes)
     assert C.sizeof(capi.SceneDesc) == 8 * 4
-    assert C.sizeof(capi.NodeColumns) == 7 * 8
+    assert C.sizeof(capi.NodeColumns) == 9 * 8
+    assert C.sizeof(capi.ParticleMesh) == 5 * 8 + 8
     assert C.sizeof(capi.VisList) == 2 * 8 + 8
     assert capi.FRUSTUM_DTYPE.itemsize == (3 + 1 + 24) * 4 + 8
     assert sg.CAMERA_DTYPE.itemsize == (2 + 3 + 4 + 3 + 4 + 4 + 4 + 1 + 16) * 4

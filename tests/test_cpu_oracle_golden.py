@@ -9,7 +9,7 @@ import pytest
 
 from oracle import oracle, refio
 from rayne_b200 import scenegen as sg
-from tests.helpers import same_floats, standard_cameras, load_golden_scene, GOLDEN_DIR
+from tests.helpers import same_floats, same_list_mod_ties, standard_cameras, load_golden_scene, GOLDEN_DIR
 
 SCENE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "scene_*.npz")))
 PARTICLE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "particles_*.npz")))
@@ -30,12 +30,53 @@ def test_oracle_scene_matches_golden(name):
     path_flags = sg.CAM_ORTHOGONAL | sg.CAM_USE_SIMPLE_CULLING
     assert np.array_equal(fr["flags"] & path_flags, g["ref_cam_flags"] & path_flags)
     assert np.array_equal(fr["render_group"], g["ref_cam_group"])
-    o = oracle.scene_reference(scene, fr)
+    # the reference's lists are what node->Render saw: AFTER the post-cull sorts of SceneBasic::Render (A11)
+    o = oracle.scene_reference(scene, fr, cameras=cams)
     assert np.array_equal(o["order"], g["ref_order"])
-    for k in ("wpos", "wrot", "wscale", "wmat"):
+    for k in ("wpos", "wrot", "wscale", "wmat", "winv", "aabb"):   # A1, A2, A3, A4
         assert same_floats(o[k], g["ref_" + k]), k
     for c in range(len(cams)):
-        assert np.array_equal(o["lists"][c], g[f"ref_list{c}"]), f"camera {c}"
+        ftb = bool(int(cams[c]["flags"]) & (1 << 6))
+        assert same_list_mod_ties(o["lists"][c], g[f"ref_list{c}"], scene.priority, ftb), f"camera {c}"
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_oracle_vislist_order_and_lists_match_golden(name):
+    """A10: SceneWithVisibilityLists default volume - post-order, no priority sort, no post-cull sorts."""
+    scene, cams, g = load_golden_scene(name)
+    o = oracle.scene_reference(scene, oracle.frustums(cams), vislists=True)
+    assert np.array_equal(o["order"], g["ref_vis_order"])
+    for c in range(len(cams)):
+        assert np.array_equal(o["lists"][c], g[f"ref_vis_list{c}"]), f"camera {c}"
+
+
+def test_sorted_fixture_really_sorts():
+    """The A11 fixture must exercise both sorts: lists differ from render-list order, and the transparent range of
+    the plain cameras is back to front."""
+    scene, cams, g = load_golden_scene("scene_boxes_transparent")
+    o = oracle.scene_reference(scene, oracle.frustums(cams), cameras=cams)
+    changed = [not np.array_equal(a, b) for a, b in zip(o["lists"], o["lists_unsorted"])]
+    assert changed[2] and changed[8] and changed[9]
+    lst = o["lists"][2]
+    tr = np.nonzero(scene.priority[lst] == sg.RENDER_TRANSPARENT)[0]
+    d = ((o["wpos"][lst[tr]] - cams[2]["pos"]) ** 2).sum(axis=1)
+    assert (np.diff(d[1:]) <= 1e-3).all()
+
+
+def test_oracle_particle_mesh_matches_golden():
+    """P6: ParticleEmitter::UpdateMesh - plain and rendered-inversed bit-exact (no transcendental), rolled bit-exact
+    too on this libm (same cosf/sinf on both sides)."""
+    g = np.load(os.path.join(GOLDEN_DIR, "particles_varied.npz"))
+    em = g["in_emitters"]
+    o = oracle.Emitters(em)
+    o.step(np.float32(g["in_delta"]), int(g["in_steps"]))
+    for tag, kw in (("", {}), ("_inv", dict(inversed=True)), ("_roll", dict(roll=True))):
+        for k in range(len(em)):
+            m = o.mesh(k, **kw)
+            live = 4 * min(int(g[f"ref_rec{k}"].shape[0]), int(em["max_particles"][k]))
+            for key in ("mesh_pos", "mesh_color", "mesh_uv0", "mesh_uv1"):
+                assert same_floats(m[key][:live], g[f"ref_{key}{tag}{k}"][:live]), (tag, k, key)
+            assert np.array_equal(m["mesh_idx"], g[f"ref_mesh_idx{tag}{k}"]), (tag, k)
 
 
 @pytest.mark.parametrize("name", SCENE_FIXTURES)

@@ -1,0 +1,225 @@
+"""GPU parity of the rows next to transform + cull (§8(f) particle mesh):
+inverse world matrices, transformed bounds, SceneWithVisibilityLists order, post-cull sorts, the AABB extension and
+the particle render mesh - against the golden fixtures written by the unmodified reference and against the oracle."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from rayne_b200 import capi, scenegen as sg
+from tests.helpers import (GOLDEN_DIR, load_golden_scene, same_floats, same_list_mod_ties, sort_cameras,
+                           standard_cameras)
+
+pytestmark = pytest.mark.gpu
+
+SCENE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "scene_*.npz")))
+
+
+def by_creation(rs, ranked):
+    full = np.zeros_like(ranked)
+    full[rs.order] = ranked
+    return full
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_inverse_and_bounds_match_golden(name):
+    """A3 + A4 bit-exact against the reference's GetInverseWorldTransform / GetBoundingSphere / GetBoundingBox."""
+    scene, cams, g = load_golden_scene(name)
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        with pytest.raises(capi.RNError):
+            h.download(capi.DL_INVERSE_WORLD_MATRIX)     # not computed yet: loud, not stale
+        h.transform_inverse()
+        h.transform_propagate()
+        with pytest.raises(capi.RNError):
+            h.download(capi.DL_BOUNDING_BOX)
+        h.bounds_update()
+        assert same_floats(by_creation(rs, h.download(capi.DL_INVERSE_WORLD_MATRIX)), g["ref_winv"])
+        assert same_floats(by_creation(rs, h.download(capi.DL_BOUNDING_BOX)), g["ref_aabb"])
+        assert same_floats(by_creation(rs, h.download(capi.DL_BOUNDING_SPHERE)), g["ref_sphere"])
+        assert same_floats(by_creation(rs, h.download(capi.DL_WORLD_MATRIX)), g["ref_wmat"])
+
+
+@pytest.mark.parametrize("kw", [
+    dict(n_trees=3, branching=4, depth=8, seed=2, nonuniform_scale=True, random_boxes=True),
+    dict(ragged_nodes=60000, depth=8, seed=5, random_bounds=True),
+    dict(n_trees=2, branching=700, depth=3, seed=8),
+    dict(n_trees=2, branching=1, depth=40, seed=7, nonuniform_scale=True),
+])
+@pytest.mark.parametrize("tile", [0, 64])
+def test_inverse_and_bounds_match_oracle(kw, tile):
+    scene = sg.make_scene(**kw)
+    scene.scale[::97] = 0.0                 # `scale != 0` false -> zero inverse scale (RNSceneNode.cpp:552)
+    scene.scale[5::211, 1] = 0.0            # one zero component -> 1/0 = inf, like the reference
+    ref = oracle.scene_reference(scene, oracle.frustums(standard_cameras()[:1]))
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=scene.n, tile_nodes=tile) as h:
+        h.upload(rs)
+        h.transform_inverse()
+        h.transform_propagate()
+        h.bounds_update()
+        winv = by_creation(rs, h.download(capi.DL_INVERSE_WORLD_MATRIX))
+        aabb = by_creation(rs, h.download(capi.DL_BOUNDING_BOX))
+    both_nan = np.isnan(winv) & np.isnan(ref["winv"])
+    assert same_floats(np.where(both_nan, 0, winv), np.where(both_nan, 0, ref["winv"]))
+    both_nan = np.isnan(aabb) & np.isnan(ref["aabb"])
+    assert same_floats(np.where(both_nan, 0, aabb), np.where(both_nan, 0, ref["aabb"]))
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_vislist_order_and_lists_match_golden(name):
+    """A10: nodes uploaded in SceneWithVisibilityLists' default-volume order give RenderVolumeList's lists."""
+    scene, cams, g = load_golden_scene(name)
+    rs = capi.RankedScene(scene, vislists=True)
+    assert np.array_equal(rs.order, g["ref_vis_order"])
+    fr = capi.build_frustums(cams)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        h.transform_cull(fr)
+        ros = h.download(capi.DL_RANK_OF_SLOT)
+        for c in range(len(cams)):
+            assert np.array_equal(rs.order[ros[h.read_list(c)]], g[f"ref_vis_list{c}"]), f"camera {c}"
+
+
+def cull_sorted(scene, cams, rank_mode=False, fused=True):
+    fr = capi.build_frustums(cams)
+    fr["flags"] |= sg.CAM_DEFAULTS          # Camera::GetFlags() of a Rayne camera carries Flags::Defaults
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        if rank_mode:
+            h.set_list_mode(True, 1000)
+        if fused:
+            h.transform_cull(fr)
+        else:
+            h.transform_propagate()
+            h.cull(fr)
+        before = [h.read_list(c) for c in range(len(cams))]
+        h.cull_sort(cams["pos"])
+        after = [h.read_list(c) for c in range(len(cams))]
+        ros = h.download(capi.DL_RANK_OF_SLOT)
+    conv = (lambda l: rs.order[l - 1000]) if rank_mode else (lambda l: rs.order[ros[l]])
+    return [conv(l) for l in before], [conv(l) for l in after]
+
+
+def test_sorted_lists_match_golden():
+    """A11 against the reference: its recorded lists are post-sort (SceneBasic::Render :596-616)."""
+    scene, cams, g = load_golden_scene("scene_boxes_transparent")
+    for rank_mode in (False, True):
+        before, after = cull_sorted(scene, cams, rank_mode=rank_mode)
+        for c in range(len(cams)):
+            ftb = bool(int(cams[c]["flags"]) & (1 << 6))
+            assert same_list_mod_ties(after[c], g[f"ref_list{c}"], scene.priority, ftb), f"camera {c}"
+            assert np.array_equal(np.sort(before[c]), np.sort(after[c]))
+
+
+@pytest.mark.parametrize("kw", [
+    dict(n_trees=40, branching=4, depth=6, seed=31, random_bounds=True, priorities=True, transparent_frac=0.2),
+    dict(n_trees=3000, branching=1, depth=1, seed=32, transparent_frac=1.0),        # everything transparent
+    dict(n_trees=300, branching=3, depth=3, seed=33, transparent_frac=0.001),       # 0-2 transparent nodes
+    dict(n_trees=64, branching=4, depth=5, seed=34),                                # no priorities at all
+])
+def test_sorted_lists_match_oracle(kw):
+    scene = sg.make_scene(**kw)
+    cams = np.concatenate([standard_cameras()[:3], sort_cameras()])
+    ref = oracle.scene_reference(scene, oracle.frustums(cams), cameras=cams)
+    _, after = cull_sorted(scene, cams, fused=False)
+    for c in range(len(cams)):
+        # the oracle sorts stably, and so does rn_cull_sort: exact equality, ties included
+        assert np.array_equal(after[c], ref["lists"][c]), f"camera {c}"
+
+
+def test_sort_full_size_properties():
+    """1 M nodes, front-to-back over ~all of them: permutation of the cull result, keys monotone per priority."""
+    scene = sg.make_scene(n_trees=48, branching=4, depth=8, seed=12345, priorities=True, transparent_frac=0.05)
+    cams = sort_cameras()[:1]
+    before, after = cull_sorted(scene, cams)
+    a, b = before[0], after[0]
+    assert a.shape[0] > 900000 and np.array_equal(np.sort(a), np.sort(b))
+    pr = scene.priority[b]
+    assert (np.diff(pr.astype(np.int64)) >= 0).all()
+    parent = np.where(scene.parent >= 0, scene.parent, 0xFFFFFFFF).astype(np.uint32)
+    wpos = oracle.world(parent, scene.pos, scene.scale, scene.rot)[0]
+    d = wpos[b] - cams[0]["pos"]
+    key = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+    for p in np.unique(pr):
+        k = key[pr == p]
+        if p < sg.RENDER_SKY:
+            assert (np.diff(k) >= 0).all()
+        elif p == sg.RENDER_TRANSPARENT:
+            assert (np.diff(k[1:]) <= 0).all()
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_aabb_extension_matches_oracle(fused):
+    """C5a extension (no live reference behaviour): the AABB-vs-planes filter on top of the sphere predicate."""
+    scene = sg.make_scene(n_trees=30, branching=4, depth=6, seed=41, random_bounds=True, random_boxes=True,
+                          nonuniform_scale=True, random_groups=True)
+    scene.sphere[:, 3] *= 4.0       # fat spheres, so that the boxes decide
+    cams = standard_cameras()
+    fr = capi.build_frustums(cams)
+    ref = oracle.scene_reference(scene, fr, aabb_test=True)
+    plain = oracle.scene_reference(scene, fr)
+    assert sum(len(a) for a in ref["lists"]) < sum(len(a) for a in plain["lists"])
+    fr2 = fr.copy()
+    fr2["flags"][::2] |= capi.CAM_TEST_AABB          # every other camera carries the flag
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        if fused:
+            h.transform_cull(fr2)
+        else:
+            h.transform_propagate()
+            h.cull(fr2)
+        ros = h.download(capi.DL_RANK_OF_SLOT)
+        counts = h.read_counts()
+        for c in range(len(cams)):
+            want = (ref if c % 2 == 0 else plain)["lists"][c]
+            got = rs.order[ros[h.read_list(c)]]
+            assert np.array_equal(got, want), f"camera {c}"
+            assert counts[c] == len(want)
+
+
+def test_particle_mesh_matches_golden_and_oracle():
+    """P6: plain / rendered-inversed meshes bit-exact against the reference; rolled within 2 ulp-scale tolerance
+    (cosf / sinf of the device are not libm's)."""
+    g = np.load(os.path.join(GOLDEN_DIR, "particles_varied.npz"))
+    em = g["in_emitters"]
+    with capi.SceneHandle(max_nodes=1, max_emitters=len(em), max_particles_per_emitter=int(em["max_particles"].max())) as h:
+        h.particles_configure(em)
+        for _ in range(int(g["in_steps"])):
+            h.particles_step(float(np.float32(g["in_delta"])))
+        counts, _ = h.particles_counts()
+        for tag, flags in (("", 0), ("_inv", capi.EMITTER_RENDERED_INVERSED), ("_roll", capi.EMITTER_CAN_ROLL)):
+            h.particles_build_mesh(flags=np.full(len(em), flags, np.uint32))
+            for k in range(len(em)):
+                mx = int(em["max_particles"][k])
+                m = h.particles_download_mesh(k, mx)
+                live = 4 * min(int(counts[k]), mx)
+                for key in ("mesh_pos", "mesh_color", "mesh_uv0"):
+                    assert same_floats(m[key][:live], g[f"ref_{key}{tag}{k}"][:live]), (tag, k, key)
+                if tag == "_roll":
+                    assert np.allclose(m["mesh_uv1"][:live], g[f"ref_mesh_uv1{tag}{k}"][:live], rtol=0, atol=2e-6)
+                else:
+                    assert same_floats(m["mesh_uv1"][:live], g[f"ref_mesh_uv1{tag}{k}"][:live]), (tag, k)
+                assert np.array_equal(m["mesh_idx"], g[f"ref_mesh_idx{tag}{k}"]), (tag, k)
+    # world scale and a bigger set against the oracle
+    em = sg.make_emitters(9, max_particles=900, spawn_rate=0.0015, vary=True)
+    o = oracle.Emitters(em)
+    o.step(np.float32(1 / 60), 80)
+    scale = np.linspace(0.5, 3.0, len(em)).astype(np.float32)
+    with capi.SceneHandle(max_nodes=1, max_emitters=9, max_particles_per_emitter=900) as h:
+        h.particles_configure(em)
+        for _ in range(80):
+            h.particles_step(float(np.float32(1 / 60)))
+        h.particles_build_mesh(world_scale_x=scale)
+        for k in range(len(em)):
+            ref = o.mesh(k, world_scale_x=float(scale[k]))
+            m = h.particles_download_mesh(k, int(em["max_particles"][k]))
+            live = 4 * o.read(k)[0].shape[0]
+            for key in ("mesh_pos", "mesh_color", "mesh_uv0", "mesh_uv1"):
+                assert same_floats(m[key][:live], ref[key][:live]), (k, key)
+            assert np.array_equal(m["mesh_idx"], ref["mesh_idx"])
