@@ -171,7 +171,8 @@ def run_ours(args) -> dict:
     ncam = len(fr)
     t0 = time.time()
     rs = capi.RankedScene(scene)
-    h = capi.SceneHandle(max_nodes=scene.n, device=local, max_emitters=args.emitters, max_particles_per_emitter=4000)
+    h = capi.SceneHandle(max_nodes=scene.n, device=local, max_emitters=args.emitters, max_particles_per_emitter=4000,
+                         tile_nodes=args.tile_nodes, tile_inner_nodes=args.inner_nodes, tile_unit_nodes=args.unit_nodes)
     h.upload(rs)
     st = h.stats()
     log(f"[bench] rank {rank}: upload+tiling {time.time() - t0:.1f}s tiles={st.tiles} spine={st.spine_nodes} levels={st.spine_levels}")
@@ -369,6 +370,9 @@ def main():
     ap.add_argument("--trees", type=int, default=768, help="trees per GPU (768 = 16.8 M nodes)")
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--tile-nodes", type=int, default=0, help="rn_scene_desc.tile_nodes (0 = library default)")
+    ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")
+    ap.add_argument("--unit-nodes", type=int, default=0, help="rn_scene_desc.tile_unit_nodes (0 = library default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     out = run_reference(args) if args.impl == "reference" else run_ours(args)

@@ -43,7 +43,7 @@ class RNError(RuntimeError):
 class SceneDesc(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_nodes", C.c_uint32), ("tile_nodes", C.c_uint32),
                 ("max_emitters", C.c_uint32), ("max_particles_per_emitter", C.c_uint32), ("tile_inner_nodes", C.c_uint32),
-                ("reserved", C.c_uint32 * 2)]
+                ("tile_unit_nodes", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class NodeColumns(C.Structure):
@@ -185,9 +185,10 @@ class SceneHandle:
     """Owns one rn_scene_t."""
 
     def __init__(self, max_nodes: int, device: int = 0, tile_nodes: int = 0, max_emitters: int = 0,
-                 max_particles_per_emitter: int = 0, tile_inner_nodes: int = 0):
+                 max_particles_per_emitter: int = 0, tile_inner_nodes: int = 0, tile_unit_nodes: int = 0):
         self.lib = load()
-        desc = SceneDesc(device, max_nodes, tile_nodes, max_emitters, max_particles_per_emitter, tile_inner_nodes)
+        desc = SceneDesc(device, max_nodes, tile_nodes, max_emitters, max_particles_per_emitter, tile_inner_nodes,
+                         tile_unit_nodes)
         self._h = C.c_void_p()
         _check(self.lib.rn_scene_create(C.byref(self._h), C.byref(desc)))
         self.max_nodes = max_nodes

@@ -851,7 +851,7 @@ struct Tiling
 };
 
 // Builds the tiling described in DESIGN.md §3.  O(n) time and memory; returns false on an invalid hierarchy.
-static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint32_t inner_cap, Tiling &t)
+static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint32_t inner_cap, uint32_t unit_cap, Tiling &t)
 {
 	const uint32_t kMaxHeight = kMaxSublevels - 2; // sublevels 1..kMaxSublevels-1 hold depths 0..kMaxHeight
 	t.depth.assign(n, 0);
@@ -920,7 +920,7 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint3
 		t.max_depth = std::max(t.max_depth, t.depth[u]);
 		if(p != RN_NO_PARENT && unit_root[p] != RN_NO_PARENT)
 			unit_root[u] = unit_root[p];
-		else if(hi[u] - lo[u] + 1 == size[u] && size[u] <= cap && inner[u] <= inner_cap && height[u] <= kMaxHeight)
+		else if(hi[u] - lo[u] + 1 == size[u] && size[u] <= unit_cap && inner[u] <= inner_cap && height[u] <= kMaxHeight)
 			unit_root[u] = u;
 		if(unit_root[u] == RN_NO_PARENT)
 			t.spine[u] = 1;
@@ -1184,6 +1184,8 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	RN_REQUIRE(inner_cap >= 16 && inner_cap <= 1024 && (inner_cap % 2) == 0 &&
 	           (size_t)warp_smem_bytes(inner_cap) * kWarpsPerCta <= 227u * 1024u,
 	           RN_ERR_INVALID, "tile_inner_nodes must be an even number in 16..%u, got %u", (227u * 1024u / kWarpsPerCta - 64u - kStageBytes - 16u) / 88u, inner_cap);
+	const uint32_t unit_cap = desc->tile_unit_nodes ? desc->tile_unit_nodes : cap;
+	RN_REQUIRE(unit_cap >= 8 && unit_cap <= cap, RN_ERR_INVALID, "tile_unit_nodes must be in 8..tile_nodes, got %u", unit_cap);
 	RN_REQUIRE(desc->max_particles_per_emitter < 16383, RN_ERR_INVALID,
 	           "max_particles_per_emitter must be < 16383 (reference: RNParticleEmitter.cpp:115)");
 	int ndev = 0;
@@ -1199,6 +1201,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	s->device = desc->device;
 	s->tile_cap = cap;
 	s->inner_cap = inner_cap;
+	s->unit_cap = unit_cap;
 	const size_t n = desc->max_nodes;
 	int rc = RN_OK;
 	if(!rc) rc = dev_alloc(s, &s->c0, n);
@@ -1248,7 +1251,7 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	           RN_ERR_INVALID, "a full upload needs every column");
 	RN_REQUIRE(count <= s->desc.max_nodes, RN_ERR_CAPACITY, "%u nodes exceed max_nodes %u", count, s->desc.max_nodes);
 	Tiling t;
-	if(!build_tiling(count, cols->parent, s->tile_cap, s->inner_cap, t))
+	if(!build_tiling(count, cols->parent, s->tile_cap, s->inner_cap, s->unit_cap, t))
 		return RN_ERR_INVALID;
 	RN_CUDA(cudaSetDevice(s->device));
 	RN_CUDA(cudaDeviceSynchronize());
