@@ -308,6 +308,44 @@ def run_ours(args) -> dict:
             dist.destroy_process_group()
         return {}
     peak, peak_kind = measured_peak()
+
+    # ---- the rows next to the headline (§8(f) P6): kernel times on rank 0 ----
+    def timed(fn, reps=10):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    extras = None
+    if not args.no_extras:
+        extras = {}
+        if world > 1:
+            h.set_list_mode(False, 0)
+        h.transform_cull(fr, stream)
+        ms = timed(lambda: h.transform_inverse(stream))
+        extras["transform_inverse"] = {"ms": ms, "bytes_per_node": 112, "roofline_frac": n * 112.0 / (ms * 1e-3) / 1e9 / peak}
+        ms = timed(lambda: h.bounds_update(stream))
+        extras["bounds_update"] = {"ms": ms, "bytes_per_node": 96, "roofline_frac": n * 96.0 / (ms * 1e-3) / 1e9 / peak}
+        fr_sort = fr.copy()
+        fr_sort["flags"][:] = 0
+        fr_sort["flags"][ncam - 1] = capi.CAM_SORT_FRONT_TO_BACK
+        h.transform_cull(fr_sort, stream)
+        entries = int(h.read_counts(stream)[ncam - 1])
+        campos = np.ascontiguousarray(cams["pos"], dtype=np.float32)
+        ms = timed(lambda: h.cull_sort(campos, stream), reps=5)
+        # 4 radix passes x (key + entry read and written) + key build (entry + world position in, key + entry out) + write-back
+        sort_bytes = entries * (4 * 16.0 + 28.0 + 8.0)
+        extras["cull_sort_front_to_back"] = {"ms": ms, "entries": entries, "Mentries_per_s": entries / ms / 1e3,
+                                             "roofline_frac": sort_bytes / (ms * 1e-3) / 1e9 / peak}
+        if particles:
+            ms = timed(lambda: h.particles_build_mesh(stream=stream))
+            extras["particles_build_mesh"] = {"ms": ms, "bytes_per_particle": 236,
+                                              "roofline_frac": particles["live_per_gpu"] * 236.0 / (ms * 1e-3) / 1e9 / peak}
     traffic, traffic_src = ncu_traffic(n, ncam)
     alg_bytes = n * (BYTES_PER_NODE + 4.0 * sum(vis_frac))
     tile_avg_ms = tile_ms / max(tile_n, 1)
@@ -334,6 +372,8 @@ def run_ours(args) -> dict:
     }
     if particles:
         out["particles"] = particles
+    if extras:
+        out["extras"] = extras
     if not args.no_cpu:
         t0 = time.time()
         out["cpu_baseline"] = cpu_reference(CPU_SAMPLE_TREES, 6, 2)
@@ -370,6 +410,7 @@ def main():
     ap.add_argument("--trees", type=int, default=768, help="trees per GPU (768 = 16.8 M nodes)")
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side timings of inverse / bounds / sort / mesh")
     ap.add_argument("--tile-nodes", type=int, default=0, help="rn_scene_desc.tile_nodes (0 = library default)")
     ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")
     ap.add_argument("--unit-nodes", type=int, default=0, help="rn_scene_desc.tile_unit_nodes (0 = library default)")

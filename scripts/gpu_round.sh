@@ -13,7 +13,7 @@ timeout 900 python bench.py --steps 20 --warmup 5 > $OUT/${TAG}_bench.json 2> $O
 echo "bench exit $?"; cat $OUT/${TAG}_bench.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_ref.json 2> $OUT/${TAG}_bench_ref.err
 echo "bench ref exit $?"; cat $OUT/${TAG}_bench_ref.json
-SHORT="python bench.py --steps 3 --warmup 3 --no-cpu --emitters 0"
+SHORT="python bench.py --steps 3 --warmup 3 --no-cpu --no-extras --emitters 0"
 $SHORT > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
