@@ -162,7 +162,9 @@ def run_ours(args) -> dict:
         raise SystemExit("bench.py needs a CUDA device: librn_cuda has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a collective that does not complete within two minutes is a bug here, not a slow link: fail fast
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
 
     trees = args.trees
     scene = build_scene(trees, seed=12345 + rank)
@@ -234,12 +236,14 @@ def run_ours(args) -> dict:
         clocks = sampler.stop(m0, m1)
         clocks["sampled"] = "during the timed region"
     # a timed region shorter than a few nvidia-smi periods: keep running the same step (untimed) under the sampler
-    need_ext = torch.tensor([1 if (rank == 0 and clocks is None) else 0], device="cuda")
+    # rank 0 decides - and how many steps - for everybody: every step holds collectives, so the count must agree
+    reps0 = max(1, int(400.0 / max(ms_total / args.steps, 1e-3))) if (rank == 0 and clocks is None) else 0
+    need_ext = torch.tensor([reps0], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.broadcast(need_ext, 0)
-    if int(need_ext.item()):
+    reps = int(need_ext.item())
+    if reps > 0:
         m0 = sampler.mark()
-        reps = max(1, int(400.0 / max(ms_total / args.steps, 1e-3)))
         for _ in range(reps):
             step()
         barrier()
@@ -260,9 +264,27 @@ def run_ours(args) -> dict:
     pin_caps = [p.numel() for p in pinned]
     d2h = 0
 
+    # One GPU: the frame is pipelined over S rank ranges on S streams (rayne_b200/pipeline.py) so that the PCIe copy of
+    # range k's lists overlaps the kernels of range k+1.  With several GPUs the lists are gathered on the devices
+    # (NCCL) from the single per-GPU scene, so the unpipelined frame is used there.
+    shards = args.e2e_shards if world == 1 else 1
+    pipe = None
+    if shards > 1:
+        from rayne_b200 import pipeline
+        tstreams = [torch.cuda.Stream() for _ in range(shards)]
+        torch.cuda.synchronize()
+        pipe = pipeline.PipelinedScene(rs, [t.cuda_stream for t in tstreams], device=local, tile_nodes=args.tile_nodes,
+                                       tile_inner_nodes=args.inner_nodes, tile_unit_nodes=args.unit_nodes)
+
     def e2e_step():
         nonlocal d2h
         rootpos[:, 0] += np.float32(0.01)
+        if pipe is not None:
+            pipe.update_nodes(roots, position=rootpos)
+            pipe.transform_cull(fr)
+            got = pipe.read_lists_into(pin_ptrs, pin_caps)
+            d2h = int(got.sum()) * 4 + ncam * 4 * shards
+            return
         h.update_nodes(roots, position=rootpos)
         h.transform_cull(fr, stream)
         got = h.read_lists_into(pin_ptrs, pin_caps, stream)
@@ -282,6 +304,8 @@ def run_ours(args) -> dict:
         t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
+    if pipe is not None:
+        pipe.close()
 
     # ---- particles (config C3 on rank 0's GPU share; reported beside the headline) ----
     particles = None
@@ -305,6 +329,7 @@ def run_ours(args) -> dict:
 
     if rank != 0:
         if world > 1:
+            dist.barrier()          # rank 0 is still timing its side kernels on its GPU
             dist.destroy_process_group()
         return {}
     peak, peak_kind = measured_peak()
@@ -346,6 +371,10 @@ def run_ours(args) -> dict:
             ms = timed(lambda: h.particles_build_mesh(stream=stream))
             extras["particles_build_mesh"] = {"ms": ms, "bytes_per_particle": 236,
                                               "roofline_frac": particles["live_per_gpu"] * 236.0 / (ms * 1e-3) / 1e9 / peak}
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
     traffic, traffic_src = ncu_traffic(n, ncam)
     alg_bytes = n * (BYTES_PER_NODE + 4.0 * sum(vis_frac))
     tile_avg_ms = tile_ms / max(tile_n, 1)
@@ -361,7 +390,10 @@ def run_ours(args) -> dict:
                    "parallelism": f"node-range sharding x{world}, NCCL allgather of counts + lists" if world > 1 else "single GPU"},
         "e2e": {"value": n * world / e2e_ms / 1e3, "unit": "Mnodes/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": int(roots.shape[0] * 16), "d2h_bytes_per_step": int(d2h),
-                "what": "rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + 6 lists) into pinned host buffers"},
+                "what": ("rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + 6 lists) "
+                         "into pinned host buffers" + (f"; frame pipelined over {shards} rank ranges on {shards} streams "
+                                                       "(rayne_b200/pipeline.py), every range's copy inside the timed region" if shards > 1 else "")),
+                "shards": shards},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "rn::tile_kernel<true,true>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic, "traffic_source": traffic_src,
@@ -378,8 +410,6 @@ def run_ours(args) -> dict:
         t0 = time.time()
         out["cpu_baseline"] = cpu_reference(CPU_SAMPLE_TREES, 6, 2)
         log(f"[bench] cpu baseline took {time.time() - t0:.1f}s")
-    if world > 1:
-        dist.destroy_process_group()
     return out
 
 
@@ -410,6 +440,7 @@ def main():
     ap.add_argument("--trees", type=int, default=768, help="trees per GPU (768 = 16.8 M nodes)")
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
     ap.add_argument("--no-extras", action="store_true", help="skip the side timings of inverse / bounds / sort / mesh")
     ap.add_argument("--tile-nodes", type=int, default=0, help="rn_scene_desc.tile_nodes (0 = library default)")
     ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")

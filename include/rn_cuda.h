@@ -152,6 +152,10 @@ void rn_scene_destroy(rn_scene_t *scene);
  * Host arrays are consumed before the call returns. */
 int rn_scene_upload(rn_scene_t *scene, const rn_node_columns *cols, uint32_t first, uint32_t count);
 int rn_scene_update_nodes(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count);
+/* The same on a caller-chosen stream: the staged copy and the scatter kernel are enqueued on `cuda_stream` (the two
+ * calls above use the legacy default stream).  Host arrays are still consumed before the call returns. */
+int rn_scene_update_nodes_async(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count,
+                                void *cuda_stream);
 int rn_scene_node_count(const rn_scene_t *scene, uint32_t *out_count);
 
 /* rn_transform_propagate: SceneNode::UpdateInternalData + UpdateInternalTransformData for every node
@@ -181,6 +185,15 @@ int rn_cull_read_list(rn_scene_t *scene, uint32_t camera, uint32_t *out_slots, u
  * synchronisation for the counts, then all list copies back to back).  out_slots[c] has capacities[c] entries. */
 int rn_cull_read_lists(rn_scene_t *scene, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
                        uint32_t *out_counts, void *cuda_stream);
+
+/* The same without the final wait: the counts are valid on return (one synchronisation), the list copies are only
+ * enqueued on `cuda_stream` - the host buffers must be page-locked and stay untouched until that stream has been
+ * synchronised (rn_stream_synchronize).  Lets the copy of one scene's lists overlap the kernels of another scene
+ * on another stream (rayne_b200/pipeline.py). */
+int rn_cull_read_lists_async(rn_scene_t *scene, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
+                             uint32_t *out_counts, void *cuda_stream);
+/* cudaStreamSynchronize for hosts that do not link the CUDA runtime themselves. */
+int rn_stream_synchronize(void *cuda_stream);
 
 /* Synchronous read-back in RANK order (parity tests, SetWorldPosition & co on the host side). */
 int rn_scene_download(rn_scene_t *scene, rn_download_what what, uint32_t first, uint32_t count, void *dst);

@@ -24,8 +24,8 @@ PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
 
 EXPORTS = [
     "rn_last_error", "rn_abi_version", "rn_scene_create", "rn_scene_destroy", "rn_scene_upload",
-    "rn_scene_update_nodes", "rn_scene_node_count", "rn_transform_propagate", "rn_cull", "rn_transform_cull",
-    "rn_scene_set_list_mode", "rn_cull_read_counts", "rn_cull_read_list", "rn_cull_read_lists", "rn_scene_download", "rn_scene_device_outputs",
+    "rn_scene_update_nodes", "rn_scene_update_nodes_async", "rn_scene_node_count", "rn_transform_propagate", "rn_cull", "rn_transform_cull",
+    "rn_scene_set_list_mode", "rn_cull_read_counts", "rn_cull_read_list", "rn_cull_read_lists", "rn_cull_read_lists_async", "rn_stream_synchronize", "rn_scene_download", "rn_scene_device_outputs",
     "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
     "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
     "rn_scene_profile", "rn_scene_profile_read",
@@ -105,6 +105,10 @@ def load(build: bool = True) -> C.CDLL:
 def _check(rc: int) -> None:
     if rc != 0:
         raise RNError(rc, load().rn_last_error().decode("utf-8", "replace"))
+
+
+def stream_synchronize(stream: int) -> None:
+    _check(load().rn_stream_synchronize(C.c_void_p(stream)))
 
 
 def _f32(a, shape_last=None) -> np.ndarray:
@@ -228,13 +232,16 @@ class SceneHandle:
         self.n = rs.n
 
     def update_nodes(self, ranks: np.ndarray, position=None, scale=None, rotation=None, flags=None, group=None,
-                     sphere=None) -> None:
+                     sphere=None, stream: int | None = None) -> None:
         ranks = np.ascontiguousarray(ranks, dtype=np.uint32)
         keep = [None if a is None else _f32(a) for a in (position, scale, rotation, sphere)]
         fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
         gr = None if group is None else np.ascontiguousarray(group, dtype=np.uint32)
         cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, _ptr(fl), _ptr(gr), _ptr(keep[3]))
-        _check(self.lib.rn_scene_update_nodes(self._h, C.byref(cols), _ptr(ranks), ranks.shape[0]))
+        if stream is None:
+            _check(self.lib.rn_scene_update_nodes(self._h, C.byref(cols), _ptr(ranks), ranks.shape[0]))
+        else:
+            _check(self.lib.rn_scene_update_nodes_async(self._h, C.byref(cols), _ptr(ranks), ranks.shape[0], C.c_void_p(stream)))
 
     def update_range(self, first: int, count: int, position=None, scale=None, rotation=None) -> None:
         keep = [None if a is None else _f32(a) for a in (position, scale, rotation)]
@@ -288,13 +295,14 @@ class SceneHandle:
         _check(self.lib.rn_cull_read_list(self._h, camera, C.c_void_p(out_ptr), capacity, C.byref(cnt), C.c_void_p(stream)))
         return cnt.value
 
-    def read_lists_into(self, out_ptrs: list[int], capacities: list[int], stream: int = 0) -> np.ndarray:
-        """rn_cull_read_lists into caller-owned (pinned) host buffers; returns the counts."""
+    def read_lists_into(self, out_ptrs: list[int], capacities: list[int], stream: int = 0, wait: bool = True) -> np.ndarray:
+        """rn_cull_read_lists[_async] into caller-owned (pinned) host buffers; returns the counts."""
         n = len(out_ptrs)
         ptrs = (C.c_void_p * n)(*out_ptrs)
         caps = (C.c_uint32 * n)(*capacities)
         counts = np.zeros(n, dtype=np.uint32)
-        _check(self.lib.rn_cull_read_lists(self._h, n, ptrs, caps, _ptr(counts), C.c_void_p(stream)))
+        fn = self.lib.rn_cull_read_lists if wait else self.lib.rn_cull_read_lists_async
+        _check(fn(self._h, n, ptrs, caps, _ptr(counts), C.c_void_p(stream)))
         return counts
 
     def download(self, what: int, first: int = 0, count: int | None = None) -> np.ndarray:

@@ -1366,7 +1366,8 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	return RN_OK;
 }
 
-static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t first, uint32_t count)
+static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t first, uint32_t count,
+                            cudaStream_t stream = 0)
 {
 	RN_REQUIRE(cols->parent == nullptr, RN_ERR_INVALID, "the hierarchy can only change through a full upload");
 	RN_REQUIRE(cols->bounding_box == nullptr && cols->render_priority == nullptr, RN_ERR_INVALID,
@@ -1374,7 +1375,8 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 	if(count == 0) return RN_OK;
 	RN_CUDA(cudaSetDevice(s->device));
 	// staging layout (words): slots | pos | scale | rot | sphere | flags | group ; packed into ONE pinned buffer
-	// and moved with ONE async copy on the legacy default stream, followed by the scatter kernel.
+	// and moved with ONE async copy on `stream` (the legacy default stream for the two original entry points),
+	// followed by the scatter kernel on the same stream.
 	const size_t per = 1 + 3 + 3 + 4 + 4 + 1 + 1;
 	if(s->scratch_cap < count)
 	{
@@ -1421,9 +1423,9 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 	u.sphere = stage(cols->bounding_sphere, (size_t)count * 4);
 	u.flags = reinterpret_cast<const uint32_t *>(stage(cols->flags, count));
 	u.group = reinterpret_cast<const uint32_t *>(stage(cols->render_group, count));
-	RN_CUDA(cudaMemcpyAsync(d, h, ofs * sizeof(float), cudaMemcpyHostToDevice, 0));
-	RN_CUDA(cudaEventRecord(s->scratch_done, 0));
-	update_kernel<<<(count + 255) / 256, 256>>>(u);
+	RN_CUDA(cudaMemcpyAsync(d, h, ofs * sizeof(float), cudaMemcpyHostToDevice, stream));
+	RN_CUDA(cudaEventRecord(s->scratch_done, stream));
+	update_kernel<<<(count + 255) / 256, 256, 0, stream>>>(u);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
 	s->have_world = false;
@@ -1447,6 +1449,13 @@ extern "C" int rn_scene_update_nodes(rn_scene_t *s, const rn_node_columns *cols,
 {
 	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
 	return update_scattered(s, cols, ranks, 0, count);
+}
+
+extern "C" int rn_scene_update_nodes_async(rn_scene_t *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count,
+                                           void *cuda_stream)
+{
+	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
+	return update_scattered(s, cols, ranks, 0, count, static_cast<cudaStream_t>(cuda_stream));
 }
 
 extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
@@ -1583,13 +1592,12 @@ extern "C" int rn_cull_read_list(rn_scene_t *s, uint32_t camera, uint32_t *out_s
 	return RN_OK;
 }
 
-extern "C" int rn_cull_read_lists(rn_scene_t *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
-                                  uint32_t *out_counts, void *cuda_stream)
+static int read_lists(rn_scene *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities, uint32_t *out_counts,
+                      cudaStream_t stream, bool wait)
 {
 	RN_REQUIRE(s && out_slots && capacities && out_counts, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(n_cameras <= s->last_ncams, RN_ERR_STATE, "the last cull had %u cameras, %u requested", s->last_ncams, n_cameras);
 	RN_CUDA(cudaSetDevice(s->device));
-	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 	RN_CUDA(cudaMemcpyAsync(out_counts, s->list_counts, sizeof(uint32_t) * n_cameras, cudaMemcpyDeviceToHost, stream));
 	RN_CUDA(cudaStreamSynchronize(stream));
 	for(uint32_t c = 0; c < n_cameras; c++)
@@ -1598,7 +1606,26 @@ extern "C" int rn_cull_read_lists(rn_scene_t *s, uint32_t n_cameras, uint32_t *c
 		if(out_counts[c] && out_slots[c])
 			RN_CUDA(cudaMemcpyAsync(out_slots[c], s->lists[c], sizeof(uint32_t) * out_counts[c], cudaMemcpyDeviceToHost, stream));
 	}
-	RN_CUDA(cudaStreamSynchronize(stream));
+	if(wait)
+		RN_CUDA(cudaStreamSynchronize(stream));
+	return RN_OK;
+}
+
+extern "C" int rn_cull_read_lists(rn_scene_t *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
+                                  uint32_t *out_counts, void *cuda_stream)
+{
+	return read_lists(s, n_cameras, out_slots, capacities, out_counts, static_cast<cudaStream_t>(cuda_stream), true);
+}
+
+extern "C" int rn_cull_read_lists_async(rn_scene_t *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
+                                        uint32_t *out_counts, void *cuda_stream)
+{
+	return read_lists(s, n_cameras, out_slots, capacities, out_counts, static_cast<cudaStream_t>(cuda_stream), false);
+}
+
+extern "C" int rn_stream_synchronize(void *cuda_stream)
+{
+	RN_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(cuda_stream)));
 	return RN_OK;
 }
 

@@ -1,0 +1,83 @@
+"""Frame pipelining on ONE GPU: the render list is cut into S rank ranges (the same edge-free cuts the multi-GPU
+path uses, shard.plan_shards), each range lives in its own rn_scene_t on its own CUDA stream, and a frame is
+
+    for every range:  rn_scene_update_nodes_async (dirty rows, pinned staging)  ->  rn_transform_cull
+    for every range:  rn_cull_read_lists into the caller's host buffers, behind the lists of the earlier ranges
+
+Everything is enqueued before the first read-back blocks, so the device-to-host copy of range k's lists (the PCIe-bound
+part of a frame that hands its visibility lists to a CPU renderer) runs while the SMs work on range k+1.  Lists travel
+as global render-list ranks (rn_scene_set_list_mode), and because the ranges ascend and every range's compaction is
+order-stable, the concatenation per camera IS the single-scene list (tests/test_gpu_scene.py::test_pipelined_*).
+
+Host-side plumbing only: transforms, culling and compaction are librn_cuda's kernels.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi, shard
+
+
+class PipelinedScene:
+    def __init__(self, rs, streams: list[int], device: int = 0, **scene_kw):
+        """rs: capi.RankedScene (node columns in render-list order); streams: one cudaStream_t (as int) per range."""
+        self.n = rs.n
+        self.ranges = shard.plan_shards(rs.parent, len(streams))
+        self.streams = list(streams)
+        self.handles = []
+        self.bounds = np.array([a for a, _ in self.ranges] + [rs.n], dtype=np.int64)
+        for (a, b) in self.ranges:
+            h = capi.SceneHandle(max_nodes=b - a, device=device, **scene_kw)
+            h.upload(shard.extract_shard(rs, a, b))
+            h.set_list_mode(True, a)
+            self.handles.append(h)
+        self._split_cache = None
+
+    def close(self) -> None:
+        for h in self.handles:
+            h.close()
+        self.handles = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _split(self, ranks: np.ndarray):
+        """Per range: (selector into `ranks`, local ranks).  Cached for a repeated dirty set (same array object)."""
+        if self._split_cache is not None and self._split_cache[0] is ranks:
+            return self._split_cache[1]
+        r = np.asarray(ranks, dtype=np.int64)
+        which = np.searchsorted(self.bounds, r, side="right") - 1
+        parts = []
+        for k, (a, _) in enumerate(self.ranges):
+            sel = np.nonzero(which == k)[0]
+            parts.append((sel, (r[sel] - a).astype(np.uint32)))
+        self._split_cache = (ranks, parts)
+        return parts
+
+    def update_nodes(self, ranks: np.ndarray, position=None, scale=None, rotation=None) -> None:
+        """SetPosition / SetScale / SetRotation on a dirty set of GLOBAL ranks, enqueued per range on its stream."""
+        for (sel, local), h, st in zip(self._split(ranks), self.handles, self.streams):
+            if sel.shape[0] == 0:
+                continue
+            pick = lambda a: None if a is None else np.ascontiguousarray(a[sel])
+            h.update_nodes(local, position=pick(position), scale=pick(scale), rotation=pick(rotation), stream=st)
+
+    def transform_cull(self, frustums: np.ndarray) -> None:
+        for h, st in zip(self.handles, self.streams):
+            h.transform_cull(frustums, st)
+        self.ncams = len(np.atleast_1d(frustums))
+
+    def read_lists_into(self, out_ptrs: list[int], capacities: list[int]) -> np.ndarray:
+        """Per camera one host buffer (pinned for an asynchronous copy): the ranges' lists land one behind the other.
+        Returns the total count per camera.  Blocks until the last copy has finished."""
+        total = np.zeros(self.ncams, dtype=np.int64)
+        for h, st in zip(self.handles, self.streams):
+            ptrs = [int(p) + 4 * int(t) for p, t in zip(out_ptrs, total)]
+            caps = [max(int(c) - int(t), 0) for c, t in zip(capacities, total)]
+            total += h.read_lists_into(ptrs, caps, st, wait=False)
+        for st in self.streams:
+            capi.stream_synchronize(st)
+        return total
