@@ -271,18 +271,15 @@ def run_ours(args) -> dict:
     pipe = None
     if shards > 1:
         from rayne_b200 import pipeline
-        tstreams = [torch.cuda.Stream() for _ in range(shards)]
         torch.cuda.synchronize()
-        pipe = pipeline.PipelinedScene(rs, [t.cuda_stream for t in tstreams], device=local, tile_nodes=args.tile_nodes,
+        pipe = pipeline.PipelinedScene(rs, shards, device=local, tile_nodes=args.tile_nodes,
                                        tile_inner_nodes=args.inner_nodes, tile_unit_nodes=args.unit_nodes)
 
     def e2e_step():
         nonlocal d2h
         rootpos[:, 0] += np.float32(0.01)
         if pipe is not None:
-            pipe.update_nodes(roots, position=rootpos)
-            pipe.transform_cull(fr)
-            got = pipe.read_lists_into(pin_ptrs, pin_caps)
+            got = pipe.frame(fr, pin_ptrs, pin_caps, dirty_ranks=roots, position=rootpos)
             d2h = int(got.sum()) * 4 + ncam * 4 * shards
             return
         h.update_nodes(roots, position=rootpos)

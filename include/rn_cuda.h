@@ -192,7 +192,11 @@ int rn_cull_read_lists(rn_scene_t *scene, uint32_t n_cameras, uint32_t *const *o
  * on another stream (rayne_b200/pipeline.py). */
 int rn_cull_read_lists_async(rn_scene_t *scene, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
                              uint32_t *out_counts, void *cuda_stream);
-/* cudaStreamSynchronize for hosts that do not link the CUDA runtime themselves. */
+/* Streams for hosts that do not link the CUDA runtime themselves (on the current device).  urgency 0 = the lowest
+ * stream priority, every step up is one priority level more urgent, clamped to what the device offers: when the
+ * kernels of several scenes are in flight, the thread blocks of the more urgent stream are scheduled first. */
+int rn_stream_create(void **out_stream, int urgency);
+int rn_stream_destroy(void *cuda_stream);
 int rn_stream_synchronize(void *cuda_stream);
 
 /* Synchronous read-back in RANK order (parity tests, SetWorldPosition & co on the host side). */

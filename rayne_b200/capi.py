@@ -25,7 +25,7 @@ PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
 EXPORTS = [
     "rn_last_error", "rn_abi_version", "rn_scene_create", "rn_scene_destroy", "rn_scene_upload",
     "rn_scene_update_nodes", "rn_scene_update_nodes_async", "rn_scene_node_count", "rn_transform_propagate", "rn_cull", "rn_transform_cull",
-    "rn_scene_set_list_mode", "rn_cull_read_counts", "rn_cull_read_list", "rn_cull_read_lists", "rn_cull_read_lists_async", "rn_stream_synchronize", "rn_scene_download", "rn_scene_device_outputs",
+    "rn_scene_set_list_mode", "rn_cull_read_counts", "rn_cull_read_list", "rn_cull_read_lists", "rn_cull_read_lists_async", "rn_stream_synchronize", "rn_stream_create", "rn_stream_destroy", "rn_scene_download", "rn_scene_device_outputs",
     "rn_camera_build_frustum", "rn_scenebasic_render_order", "rn_particles_configure", "rn_particles_step",
     "rn_particles_sort", "rn_particles_counts", "rn_particles_download", "rn_scene_get_stats",
     "rn_scene_profile", "rn_scene_profile_read",
@@ -105,6 +105,16 @@ def load(build: bool = True) -> C.CDLL:
 def _check(rc: int) -> None:
     if rc != 0:
         raise RNError(rc, load().rn_last_error().decode("utf-8", "replace"))
+
+
+def stream_create(urgency: int = 0) -> int:
+    out = C.c_void_p()
+    _check(load().rn_stream_create(C.byref(out), int(urgency)))
+    return int(out.value or 0)
+
+
+def stream_destroy(stream: int) -> None:
+    _check(load().rn_stream_destroy(C.c_void_p(stream)))
 
 
 def stream_synchronize(stream: int) -> None:

@@ -1623,6 +1623,25 @@ extern "C" int rn_cull_read_lists_async(rn_scene_t *s, uint32_t n_cameras, uint3
 	return read_lists(s, n_cameras, out_slots, capacities, out_counts, static_cast<cudaStream_t>(cuda_stream), false);
 }
 
+extern "C" int rn_stream_create(void **out_stream, int urgency)
+{
+	RN_REQUIRE(out_stream, RN_ERR_INVALID, "NULL argument");
+	int least = 0, greatest = 0;   // numerically: greatest priority <= least priority
+	RN_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+	int prio = least - (urgency < 0 ? 0 : urgency);
+	if(prio < greatest) prio = greatest;
+	cudaStream_t st = nullptr;
+	RN_CUDA(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio));
+	*out_stream = st;
+	return RN_OK;
+}
+
+extern "C" int rn_stream_destroy(void *cuda_stream)
+{
+	if(cuda_stream) RN_CUDA(cudaStreamDestroy(static_cast<cudaStream_t>(cuda_stream)));
+	return RN_OK;
+}
+
 extern "C" int rn_stream_synchronize(void *cuda_stream)
 {
 	RN_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(cuda_stream)));

@@ -19,15 +19,18 @@ from . import capi, shard
 
 
 class PipelinedScene:
-    def __init__(self, rs, streams: list[int], device: int = 0, **scene_kw):
-        """rs: capi.RankedScene (node columns in render-list order); streams: one cudaStream_t (as int) per range."""
+    def __init__(self, rs, n_ranges: int = 4, device: int = 0, **scene_kw):
+        """rs: capi.RankedScene (node columns in render-list order).  Range k gets its own stream, earlier ranges
+        more urgent ones: without priorities the compaction of range k queues behind the (already launched) transform
+        kernels of ranges k+1.., and the first copy would only start when nearly all kernels are done."""
         self.n = rs.n
-        self.ranges = shard.plan_shards(rs.parent, len(streams))
-        self.streams = list(streams)
+        self.ranges = shard.plan_shards(rs.parent, n_ranges)
         self.handles = []
+        self.streams = []
         self.bounds = np.array([a for a, _ in self.ranges] + [rs.n], dtype=np.int64)
         for (a, b) in self.ranges:
-            h = capi.SceneHandle(max_nodes=b - a, device=device, **scene_kw)
+            h = capi.SceneHandle(max_nodes=b - a, device=device, **scene_kw)    # makes `device` current
+            self.streams.append(capi.stream_create(n_ranges - 1 - len(self.streams)))
             h.upload(shard.extract_shard(rs, a, b))
             h.set_list_mode(True, a)
             self.handles.append(h)
@@ -36,7 +39,10 @@ class PipelinedScene:
     def close(self) -> None:
         for h in self.handles:
             h.close()
+        for st in self.streams:
+            capi.stream_destroy(st)
         self.handles = []
+        self.streams = []
 
     def __enter__(self):
         return self
@@ -69,6 +75,21 @@ class PipelinedScene:
         for h, st in zip(self.handles, self.streams):
             h.transform_cull(frustums, st)
         self.ncams = len(np.atleast_1d(frustums))
+
+    def frame(self, frustums: np.ndarray, out_ptrs: list[int], capacities: list[int], dirty_ranks=None, position=None,
+              scale=None, rotation=None) -> np.ndarray:
+        """One whole frame: per range (update of its dirty rows ->) transform + cull, enqueued range after range so
+        that range 0 is already running while the host still prepares range 1.., then the read-back."""
+        parts = self._split(dirty_ranks) if dirty_ranks is not None else [None] * len(self.handles)
+        fr = np.ascontiguousarray(np.atleast_1d(frustums), dtype=capi.FRUSTUM_DTYPE)
+        for part, h, st in zip(parts, self.handles, self.streams):
+            if part is not None and part[0].shape[0]:
+                sel, local = part
+                pick = lambda a: None if a is None else np.ascontiguousarray(a[sel])
+                h.update_nodes(local, position=pick(position), scale=pick(scale), rotation=pick(rotation), stream=st)
+            h.transform_cull(fr, st)
+        self.ncams = fr.shape[0]
+        return self.read_lists_into(out_ptrs, capacities)
 
     def read_lists_into(self, out_ptrs: list[int], capacities: list[int]) -> np.ndarray:
         """Per camera one host buffer (pinned for an asynchronous copy): the ranges' lists land one behind the other.

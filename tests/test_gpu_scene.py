@@ -138,10 +138,7 @@ def test_pipelined_frame_matches_single(shards):
     roots = rs.roots
     moved = rs.position[roots] + np.float32([0.5, 0, 0])
     pinned = [torch.empty(scene.n, dtype=torch.int32).pin_memory() for _ in fr]
-    streams = [torch.cuda.Stream() for _ in range(shards)]
-    torch.cuda.synchronize()
-    with capi.SceneHandle(max_nodes=scene.n) as h, \
-            pipeline.PipelinedScene(rs, [t.cuda_stream for t in streams]) as pipe:
+    with capi.SceneHandle(max_nodes=scene.n) as h, pipeline.PipelinedScene(rs, shards) as pipe:
         h.upload(rs)
         h.set_list_mode(True, 0)
         for step in range(2):
@@ -151,6 +148,10 @@ def test_pipelined_frame_matches_single(shards):
             h.transform_cull(fr)
             pipe.transform_cull(fr)
             total = pipe.read_lists_into([p.data_ptr() for p in pinned], [p.numel() for p in pinned])
+            if step == 1:   # the one-call form of the same frame
+                again = pipe.frame(fr, [p.data_ptr() for p in pinned], [p.numel() for p in pinned], dirty_ranks=roots,
+                                   position=moved)
+                assert np.array_equal(again, total)
             for c in range(len(fr)):
                 want = h.read_list(c)
                 assert total[c] == want.shape[0]
