@@ -104,6 +104,10 @@ struct CullParams
 {
 	rn_camera_frustum cam[RN_MAX_CAMERAS];
 	uint32_t n;
+	uint32_t simple;                   // bit c: camera c has UseSimpleCulling
+	// built on the host (fill_cull_params), copied into shared memory by every CTA:
+	float4 test[RN_MAX_CAMERAS * 7];   // [c*7] = frustum sphere (centre xyz, radius); [c*7 + 1 + k] = plane k (normal xyz, d)
+	uint32_t group_mask[64];           // 256 bytes: _renderGroup byte -> bit mask of the cameras whose render group intersects it
 };
 
 struct NodeWorld
@@ -165,14 +169,20 @@ __device__ __forceinline__ bool cull_exact(const CullParams &cp, float px, float
 	return inside;
 }
 
-__device__ __forceinline__ int float_to_ordered(float f)
+// Warp-wide fp32 min / max in one instruction (sm_100a: redux.sync.{min,max}.NaN.f32 -> CREDUX.F32.NAN).  A NaN in
+// any lane makes the result NaN, which the `sane` guard of cull_node turns into "undecided".
+__device__ __forceinline__ float warp_min(float f)
 {
-	const int i = __float_as_int(f);
-	return i ^ ((i >> 31) & 0x7fffffff);
+	float r;
+	asm volatile("redux.sync.min.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(f));
+	return r;
 }
-__device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
-__device__ __forceinline__ float warp_min(float f) { return ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(f))); }
-__device__ __forceinline__ float warp_max(float f) { return ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(f))); }
+__device__ __forceinline__ float warp_max(float f)
+{
+	float r;
+	asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(f));
+	return r;
+}
 
 struct WarpBox
 {
@@ -281,35 +291,10 @@ __device__ __forceinline__ uint32_t cull_node(const CullParams &cp, const CullTa
 __device__ __forceinline__ void cull_setup(const CullParams &cp, CullTable &tab, LaneTests &lt)
 {
 	for(uint32_t t = threadIdx.x; t < RN_MAX_CAMERAS * 7; t += blockDim.x)
-	{
-		const uint32_t c = t / 7, k = t % 7;
-		float4 e = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll
-		for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
-		{
-			if(c == (uint32_t)cc)
-			{
-				const rn_camera_frustum &cam = cp.cam[cc];
-				e = make_float4(cam.center[0], cam.center[1], cam.center[2], cam.radius);
-#pragma unroll
-				for(int kk = 0; kk < 6; kk++)
-					if(k == (uint32_t)kk + 1) e = make_float4(cam.planes[kk][0], cam.planes[kk][1], cam.planes[kk][2], cam.planes[kk][3]);
-			}
-		}
-		tab.test[t] = e;
-	}
-	uint32_t simple = 0;
-#pragma unroll
-	for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
-		if(cp.cam[cc].flags & RN_CAMERA_USE_SIMPLE_CULLING) simple |= 1u << cc;
-	for(uint32_t g = threadIdx.x; g < 256; g += blockDim.x)
-	{
-		uint32_t m = 0;
-#pragma unroll
-		for(int cc = 0; cc < RN_MAX_CAMERAS; cc++)
-			if((uint32_t)cc < cp.n && (g & cp.cam[cc].render_group & 0xffu)) m |= 1u << cc;
-		tab.group_mask[g] = (uint8_t)m;
-	}
+		tab.test[t] = cp.test[t];
+	for(uint32_t g = threadIdx.x; g < 64; g += blockDim.x)
+		reinterpret_cast<uint32_t *>(tab.group_mask)[g] = cp.group_mask[g];
+	const uint32_t simple = cp.simple;
 	__syncthreads();
 	const uint32_t lane = threadIdx.x & 31u;
 	lt.kind0 = lt.kind1 = 0;
@@ -1147,6 +1132,21 @@ static int fill_cull_params(const rn_camera_frustum *cams, uint32_t ncams, CullP
 	memset(&cp, 0, sizeof(cp));
 	memcpy(cp.cam, cams, sizeof(rn_camera_frustum) * ncams);
 	cp.n = ncams;
+	for(uint32_t c = 0; c < ncams; c++)
+	{
+		if(cams[c].flags & RN_CAMERA_USE_SIMPLE_CULLING) cp.simple |= 1u << c;
+		cp.test[c * 7] = make_float4(cams[c].center[0], cams[c].center[1], cams[c].center[2], cams[c].radius);
+		for(int k = 0; k < 6; k++)
+			cp.test[c * 7 + 1 + k] = make_float4(cams[c].planes[k][0], cams[c].planes[k][1], cams[c].planes[k][2], cams[c].planes[k][3]);
+	}
+	uint8_t *gm = reinterpret_cast<uint8_t *>(cp.group_mask);
+	for(uint32_t g = 0; g < 256; g++)
+	{
+		uint32_t m = 0;
+		for(uint32_t c = 0; c < ncams; c++)
+			if(g & cams[c].render_group & 0xffu) m |= 1u << c;
+		gm[g] = (uint8_t)m;
+	}
 	return RN_OK;
 }
 
