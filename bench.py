@@ -191,6 +191,7 @@ def run_ours(args) -> dict:
     if world > 1:
         from rayne_b200 import shard
         exch = shard.ListExchange()
+        pexch = shard.PipelinedListExchange()
         count_t = torch.as_tensor(DevArray(lists[0].count, ncam), device="cuda")
         list_t = [torch.as_tensor(DevArray(lists[c].slots, n), device="cuda") for c in range(ncam)]
 
@@ -199,9 +200,11 @@ def run_ours(args) -> dict:
         return exch.exchange(count_t, list_t)
 
     def step():
+        # every frame's lists ARE gathered on every GPU; the gather of frame i runs on a side stream under the kernels
+        # of frame i+1 (shard.PipelinedListExchange) and the last one is flushed inside the timed region
         h.transform_cull(fr, stream)
         if world > 1:
-            exchange()
+            pexch.submit(count_t, list_t)
 
     def barrier():
         torch.cuda.synchronize()
@@ -224,6 +227,8 @@ def run_ours(args) -> dict:
     e0.record()
     for _ in range(args.steps):
         step()
+    if world > 1:
+        pexch.flush()
     e1.record()
     barrier()
     m1 = sampler.mark()
@@ -392,6 +397,8 @@ def run_ours(args) -> dict:
                                                        "(rayne_b200/pipeline.py), every range's copy inside the timed region" if shards > 1 else "")),
                 "shards": shards},
         "gpu_launches": int(launches),
+        "exchange": ({"kind": "NCCL all-gather of per-camera counts + index lists, one frame deep on a side stream",
+                      "overflows": int(pexch.overflows), "entries_per_rank_and_camera": list(pexch.sizes or [])} if world > 1 else None),
         "roofline": {"bound": "hbm", "kernel": "rn::tile_kernel<true,true>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
@@ -444,7 +451,14 @@ def main():
     ap.add_argument("--unit-nodes", type=int, default=0, help="rn_scene_desc.tile_unit_nodes (0 = library default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    # stdout carries exactly ONE line, the JSON: libraries that print to fd 1 (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    os.close(real_stdout)
     if out:
         print(json.dumps(out), flush=True)
 

@@ -130,3 +130,101 @@ class ListExchange:
         """Full exchange.  Returns (all_counts_host [world, ncams], per-camera list of per-rank views)."""
         all_counts = self.gather_counts(counts).cpu()
         return all_counts, self.gather_lists(lists, all_counts)
+
+
+class PipelinedListExchange(ListExchange):
+    """The same exchange, one frame deep: frame i's lists are snapshotted right behind its compaction and gathered on
+    a side stream while frame i+1 is transformed and culled on the main stream.
+
+    No host synchronisation per frame: the gather sizes of frame i come from the counts table of frame i-1 (identical
+    on every rank, because every rank holds the same table) times ``margin``; the table of frame i is read on the host
+    one frame later, when it has long arrived.  A camera whose visible count grew beyond the margin within one frame is
+    reported through ``overflows`` (its snapshot was cut) - the caller falls back to ``exchange`` for that frame.
+    ``flush`` makes the current stream wait for the outstanding gathers and returns the last result.
+    With CPU tensors (gloo, the CPU tests) the same protocol runs without streams."""
+
+    def __init__(self, group=None, margin: float = 1.25, slack: int = 4096, cuda: bool = True):
+        super().__init__(group)
+        import torch
+        self.torch = torch
+        self.cuda = cuda
+        self.side = torch.cuda.Stream() if cuda else None
+        self.margin, self.slack = margin, slack
+        self.sizes = None        # per camera: entries gathered per rank
+        self.capacities = None
+        self.pending = None
+        self.result = None       # (counts table [world, ncams] on the host, per-camera gathered tensors, sizes used)
+        self.overflows = 0
+
+    def _set_sizes(self, table):
+        mx = table.max(dim=0).values.tolist()
+        self.sizes = [int(min(cap, int(m * self.margin) + self.slack)) for m, cap in zip(mx, self.capacities)]
+
+    def _retire(self):
+        """Host side of the previous frame: its counts table is on the host by now."""
+        if self.pending is None:
+            return
+        ev, host_counts, outs, used_sizes, _keep = self.pending
+        if ev is not None:
+            ev.synchronize()
+        table = host_counts.view(self.world, -1).clone()
+        if any(int(table[:, c].max()) > used_sizes[c] for c in range(table.shape[1])):
+            self.overflows += 1
+        self.result = (table, outs, used_sizes)
+        self._set_sizes(table)
+        self.pending = None
+
+    def submit(self, counts, lists):
+        """counts: int32 tensor [ncams]; lists[c]: int32 tensor (full capacity) of camera c."""
+        torch = self.torch
+        self.capacities = [int(l.numel()) for l in lists]
+        if self.sizes is None:                       # first frame: one synchronous exchange seeds the size table
+            table, _ = self.exchange(counts, lists)
+            self._set_sizes(table)
+        self._retire()
+        sizes = list(self.sizes)
+        snap_counts = counts.clone()
+        snaps = [l[:m].clone() for l, m in zip(lists, sizes)]
+
+        def gather():
+            all_counts = torch.empty(self.world * snap_counts.numel(), dtype=snap_counts.dtype, device=snap_counts.device)
+            self.dist.all_gather_into_tensor(all_counts, snap_counts, group=self.group)
+            if self.cuda:
+                host_counts = torch.empty(all_counts.numel(), dtype=all_counts.dtype).pin_memory()
+                host_counts.copy_(all_counts, non_blocking=True)
+                ev_counts = torch.cuda.Event()
+                ev_counts.record()
+            else:
+                host_counts, ev_counts = all_counts, None
+            outs = []
+            for s in snaps:
+                dst = torch.empty(self.world * s.numel(), dtype=s.dtype, device=s.device)
+                if s.numel():
+                    self.dist.all_gather_into_tensor(dst, s, group=self.group)
+                outs.append(dst)
+            return ev_counts, host_counts, outs, all_counts
+
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            for t in [snap_counts] + snaps:
+                t.record_stream(self.side)
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(ev)
+                ev_counts, host_counts, outs, all_counts = gather()
+        else:
+            ev_counts, host_counts, outs, all_counts = gather()
+        self.pending = (ev_counts, host_counts, outs, sizes, (snap_counts, snaps, all_counts))
+
+    def flush(self):
+        """Current stream waits for every outstanding gather; returns (counts table, gathered lists, sizes used)."""
+        if self.cuda:
+            self.torch.cuda.current_stream().wait_stream(self.side)
+        self._retire()
+        return self.result
+
+    @staticmethod
+    def views(result, world: int):
+        """Per camera the list of per-rank views (rank r's visible global ranks) of a flushed result."""
+        table, outs, sizes = result
+        return [[outs[c][r * sizes[c]: r * sizes[c] + min(int(table[r, c]), sizes[c])] for r in range(world)] for c in range(len(outs))]

@@ -82,8 +82,20 @@ def _worker(rank: int, world: int, port: int, q):
         ex = shard.ListExchange()
         all_counts, gathered = ex.exchange(counts, lists)
         merged = [torch.cat(parts).numpy().astype(np.uint32) for parts in gathered]
+        # the one-frame-deep variant: frame 0 full lists, frame 1 half of every list, frame 2 full lists again with a
+        # tight margin (-> reported as an overflow, because the sizes came from frame 1's halved counts)
+        pex = shard.PipelinedListExchange(cuda=False, margin=1.0, slack=0)
+        frames = []
+        for f, keep in enumerate((1.0, 0.5, 1.0)):
+            cnt = torch.tensor([int(len(l) * keep) for l in local], dtype=torch.int32)
+            pex.submit(cnt, lists)
+            if f > 0:
+                frames.append((pex.result[0].numpy().copy(), pex.overflows))
+        table, outs, sizes = pex.flush()
+        frames.append((table.numpy().copy(), pex.overflows))
+        pmerged = [torch.cat(v).numpy().astype(np.uint32) for v in shard.PipelinedListExchange.views((table, outs, sizes), world)]
         if rank == 0:
-            q.put((all_counts.numpy(), merged, ranges))
+            q.put((all_counts.numpy(), merged, ranges, frames, pmerged, sizes))
     finally:
         dist.destroy_process_group()
 
@@ -96,7 +108,7 @@ def test_two_rank_exchange_matches_single_process():
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    all_counts, merged, ranges = q.get(timeout=300)
+    all_counts, merged, ranges, frames, pmerged, sizes = q.get(timeout=300)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -109,3 +121,14 @@ def test_two_rank_exchange_matches_single_process():
         want_ranks = rs.rank_of[ref["lists"][c]]            # creation ids -> global ranks, already ascending
         assert np.array_equal(merged[c], want_ranks), f"camera {c}"
         assert int(all_counts[:, c].sum()) == len(want_ranks)
+    # pipelined exchange: tables arrive one frame late and equal the submitted counts; the third frame was sized from
+    # the halved counts of the second one with no margin -> flagged as an overflow, its lists cut at `sizes`
+    assert np.array_equal(frames[0][0], all_counts) and frames[0][1] == 0
+    assert np.array_equal(frames[1][0], all_counts // 2 + 0 * all_counts) or np.array_equal(frames[1][0], (all_counts * 0.5).astype(all_counts.dtype))
+    assert frames[1][1] == 0
+    assert np.array_equal(frames[2][0], all_counts) and frames[2][1] == 1
+    for c in range(len(cams)):
+        want_ranks = rs.rank_of[ref["lists"][c]]
+        got = pmerged[c]
+        # per rank only the first sizes[c] entries travelled: the merged list is a prefix-per-rank subset
+        assert set(got.tolist()) <= set(want_ranks.tolist())
