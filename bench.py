@@ -164,7 +164,12 @@ def run_ours(args) -> dict:
     if world > 1:
         import datetime
         # a collective that does not complete within two minutes is a bug here, not a slow link: fail fast
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
+        # NCCL's stream gets a high priority: the gather of frame i must be scheduled AHEAD of the thousands of pending
+        # thread blocks of frame i+1's transform kernel, or it only starts in that kernel's tail
+        opts = dist.ProcessGroupNCCL.Options()
+        opts.is_high_priority_stream = True
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120),
+                                pg_options=opts)
 
     trees = args.trees
     scene = build_scene(trees, seed=12345 + rank)

@@ -136,14 +136,15 @@ class PipelinedListExchange(ListExchange):
     """The same exchange, one frame deep: frame i's lists are snapshotted right behind its compaction and gathered on
     a side stream while frame i+1 is transformed and culled on the main stream.
 
-    No host synchronisation per frame: the gather sizes of frame i come from the counts table of frame i-1 (identical
-    on every rank, because every rank holds the same table) times ``margin``; the table of frame i is read on the host
-    one frame later, when it has long arrived.  A camera whose visible count grew beyond the margin within one frame is
+    No host synchronisation per frame: the gather sizes of frame i come from the newest counts table the host has
+    seen (frame i-depth; identical on every rank, because every rank holds the same table) times ``margin``; the
+    table of a frame is read on the host ``depth`` frames later, when it has long arrived, so the host never waits
+    and keeps the device queue full.  A camera whose visible count grew beyond the margin within one frame is
     reported through ``overflows`` (its snapshot was cut) - the caller falls back to ``exchange`` for that frame.
     ``flush`` makes the current stream wait for the outstanding gathers and returns the last result.
     With CPU tensors (gloo, the CPU tests) the same protocol runs without streams."""
 
-    def __init__(self, group=None, margin: float = 1.25, slack: int = 4096, cuda: bool = True):
+    def __init__(self, group=None, margin: float = 1.125, slack: int = 4096, cuda: bool = True, depth: int = 2):
         super().__init__(group)
         import torch
         self.torch = torch
@@ -152,79 +153,89 @@ class PipelinedListExchange(ListExchange):
         self.margin, self.slack = margin, slack
         self.sizes = None        # per camera: entries gathered per rank
         self.capacities = None
-        self.pending = None
-        self.result = None       # (counts table [world, ncams] on the host, per-camera gathered tensors, sizes used)
+        self.depth = max(1, depth)   # frames in flight before the host looks at the oldest one's counts table
+        self.pending = []
+        self.result = None       # (counts table [world, ncams] on the host, gathered buffer, sizes used)
         self.overflows = 0
+        self._host = [None] * (self.depth + 1)    # pinned count tables, one per frame in flight
+        self._frame = 0
 
     def _set_sizes(self, table):
         mx = table.max(dim=0).values.tolist()
         self.sizes = [int(min(cap, int(m * self.margin) + self.slack)) for m, cap in zip(mx, self.capacities)]
 
-    def _retire(self):
-        """Host side of the previous frame: its counts table is on the host by now."""
-        if self.pending is None:
-            return
-        ev, host_counts, outs, used_sizes, _keep = self.pending
+    def _retire(self, keep: int):
+        """Host side of the oldest frames in flight (all but the newest `keep`): their counts tables have arrived."""
+        while len(self.pending) > keep:
+            self._retire_one(self.pending.pop(0))
+
+    def _retire_one(self, item):
+        ev, host_counts, outs, used_sizes, _keep = item
         if ev is not None:
             ev.synchronize()
-        table = host_counts.view(self.world, -1).clone()
+        table = host_counts.view(self.world, -1).clone().to(self.torch.int64)
         if any(int(table[:, c].max()) > used_sizes[c] for c in range(table.shape[1])):
             self.overflows += 1
         self.result = (table, outs, used_sizes)
         self._set_sizes(table)
-        self.pending = None
 
     def submit(self, counts, lists):
-        """counts: int32 tensor [ncams]; lists[c]: int32 tensor (full capacity) of camera c."""
+        """counts: int32 tensor [ncams]; lists[c]: int32 tensor (full capacity) of camera c.
+        ONE collective per frame: the first sizes[c] entries of every list and the counts are packed into one buffer
+        (one copy kernel) and all-gathered as a whole; the counts columns of the result go to the host asynchronously."""
         torch = self.torch
         self.capacities = [int(l.numel()) for l in lists]
         if self.sizes is None:                       # first frame: one synchronous exchange seeds the size table
             table, _ = self.exchange(counts, lists)
             self._set_sizes(table)
-        self._retire()
+        self._retire(self.depth - 1)
         sizes = list(self.sizes)
-        snap_counts = counts.clone()
-        snaps = [l[:m].clone() for l, m in zip(lists, sizes)]
+        ncam = counts.numel()
+        packed = torch.cat([l[:m] for l, m in zip(lists, sizes)] + [counts.to(lists[0].dtype)])
+        width = packed.numel()
 
         def gather():
-            all_counts = torch.empty(self.world * snap_counts.numel(), dtype=snap_counts.dtype, device=snap_counts.device)
-            self.dist.all_gather_into_tensor(all_counts, snap_counts, group=self.group)
+            dst = torch.empty(self.world * width, dtype=packed.dtype, device=packed.device)
+            self.dist.all_gather_into_tensor(dst, packed, group=self.group)
+            tail = dst.view(self.world, width)[:, width - ncam:].contiguous()
             if self.cuda:
-                host_counts = torch.empty(all_counts.numel(), dtype=all_counts.dtype).pin_memory()
-                host_counts.copy_(all_counts, non_blocking=True)
+                self._frame += 1
+                slot = self._frame % len(self._host)
+                host_counts = self._host[slot]
+                if host_counts is None or host_counts.numel() != tail.numel():
+                    host_counts = torch.empty(tail.numel(), dtype=tail.dtype).pin_memory()
+                    self._host[slot] = host_counts
+                host_counts.copy_(tail.view(-1), non_blocking=True)
                 ev_counts = torch.cuda.Event()
                 ev_counts.record()
             else:
-                host_counts, ev_counts = all_counts, None
-            outs = []
-            for s in snaps:
-                dst = torch.empty(self.world * s.numel(), dtype=s.dtype, device=s.device)
-                if s.numel():
-                    self.dist.all_gather_into_tensor(dst, s, group=self.group)
-                outs.append(dst)
-            return ev_counts, host_counts, outs, all_counts
+                host_counts, ev_counts = tail.view(-1), None
+            return ev_counts, host_counts, dst
 
         if self.cuda:
             ev = torch.cuda.Event()
             ev.record()
-            for t in [snap_counts] + snaps:
-                t.record_stream(self.side)
+            packed.record_stream(self.side)
             with torch.cuda.stream(self.side):
                 self.side.wait_event(ev)
-                ev_counts, host_counts, outs, all_counts = gather()
+                ev_counts, host_counts, dst = gather()
         else:
-            ev_counts, host_counts, outs, all_counts = gather()
-        self.pending = (ev_counts, host_counts, outs, sizes, (snap_counts, snaps, all_counts))
+            ev_counts, host_counts, dst = gather()
+        self.pending.append((ev_counts, host_counts, dst, sizes, packed))
 
     def flush(self):
-        """Current stream waits for every outstanding gather; returns (counts table, gathered lists, sizes used)."""
+        """Current stream waits for every outstanding gather; returns (counts table, gathered buffer, sizes used)."""
         if self.cuda:
             self.torch.cuda.current_stream().wait_stream(self.side)
-        self._retire()
+        self._retire(0)
         return self.result
 
     @staticmethod
     def views(result, world: int):
         """Per camera the list of per-rank views (rank r's visible global ranks) of a flushed result."""
-        table, outs, sizes = result
-        return [[outs[c][r * sizes[c]: r * sizes[c] + min(int(table[r, c]), sizes[c])] for r in range(world)] for c in range(len(outs))]
+        table, dst, sizes = result
+        ncam = len(sizes)
+        width = sum(sizes) + ncam
+        offs = [sum(sizes[:c]) for c in range(ncam)]
+        return [[dst[r * width + offs[c]: r * width + offs[c] + min(int(table[r, c]), sizes[c])] for r in range(world)]
+                for c in range(ncam)]

@@ -84,7 +84,7 @@ def _worker(rank: int, world: int, port: int, q):
         merged = [torch.cat(parts).numpy().astype(np.uint32) for parts in gathered]
         # the one-frame-deep variant: frame 0 full lists, frame 1 half of every list, frame 2 full lists again with a
         # tight margin (-> reported as an overflow, because the sizes came from frame 1's halved counts)
-        pex = shard.PipelinedListExchange(cuda=False, margin=1.0, slack=0)
+        pex = shard.PipelinedListExchange(cuda=False, margin=1.0, slack=0, depth=1)
         frames = []
         for f, keep in enumerate((1.0, 0.5, 1.0)):
             cnt = torch.tensor([int(len(l) * keep) for l in local], dtype=torch.int32)
