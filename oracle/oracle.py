@@ -130,6 +130,16 @@ def sort_list(lst: np.ndarray, prio: np.ndarray, wpos: np.ndarray, cam_pos, fron
     return lst
 
 
+def instances(ids, wmat, winv, view, projview) -> np.ndarray:
+    """Per list entry 64 floats: model, inverse model, view * model, projView * model."""
+    ids = np.ascontiguousarray(ids, dtype=np.uint32)
+    wmat = np.ascontiguousarray(wmat, dtype=np.float32); winv = np.ascontiguousarray(winv, dtype=np.float32)
+    view = np.ascontiguousarray(view, dtype=np.float32); projview = np.ascontiguousarray(projview, dtype=np.float32)
+    out = np.zeros((ids.shape[0], 64), np.float32)
+    load().rn_oracle_instances(C.c_uint32(ids.shape[0]), _p(ids), _p(wmat), _p(winv), _p(view), _p(projview), _p(out))
+    return out
+
+
 def frustums(cameras: np.ndarray) -> np.ndarray:
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
     out = np.zeros(cameras.shape[0], dtype=FRUSTUM_DTYPE)

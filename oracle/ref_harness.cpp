@@ -218,9 +218,11 @@ namespace
 		std::vector<CameraDesc> cameras;
 	};
 
+	// kOptInstances: the dump gains, per camera, the view and projection*view matrices and, for camera 0, view*world
+	//          and projView*world of every node (the matrix uniforms a renderer derives per drawable).
 	// kOptVisLists: drive SceneWithVisibilityLists (default volume only) instead of SceneBasic.
 	// kOptBox: the input carries a local AABB column (SceneNode::SetBoundingBox).
-	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1, kOptVisLists = 1u << 2, kOptBox = 1u << 3 };
+	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1, kOptVisLists = 1u << 2, kOptBox = 1u << 3, kOptInstances = 1u << 4 };
 
 	SceneInput ReadScene(const char *path)
 	{
@@ -400,6 +402,31 @@ namespace
 			w.put<uint32_t>(static_cast<uint32_t>(cam->GetRenderGroup()));
 			w.put<uint32_t>(static_cast<uint32_t>(rec.lists[c].size()));
 			w.vec(rec.lists[c]);
+		}
+		if(in.options & kOptInstances)
+		{
+			// the matrix products of a renderer's uniform upload (Modules/Vulkan/Sources/RNVulkanRenderer.cpp:1134-1168)
+			// evaluated with the reference's own Matrix class.  (LOD selection, the other per-drawable step of
+			// Entity::Render, is compiled out in this reference: RN_MODEL_LOD_DISABLED 1, Source/Rendering/RNModel.h:9.)
+			for(size_t c = 0; c < b.cameras.size(); c++)
+			{
+				Camera *cam = b.cameras[c];
+				Matrix view = cam->GetViewMatrix();
+				Matrix projView = cam->GetProjectionMatrix() * view;
+				for(int k = 0; k < 16; k++) w.put<float>(view.m[k]);
+				for(int k = 0; k < 16; k++) w.put<float>(projView.m[k]);
+				if(c == 0)
+				{
+					std::vector<float> mv((size_t)in.nNodes * 16), mvp((size_t)in.nNodes * 16);
+					for(uint32_t i = 0; i < in.nNodes; i++)
+					{
+						Matrix model = b.nodes[i]->GetWorldTransform();
+						Matrix a = view * model, p = projView * model;
+						for(int k = 0; k < 16; k++) { mv[(size_t)i*16 + k] = a.m[k]; mvp[(size_t)i*16 + k] = p.m[k]; }
+					}
+					w.vec(mv); w.vec(mvp);
+				}
+			}
 		}
 		return 0;
 	}

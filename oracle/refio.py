@@ -31,6 +31,7 @@ OPT_INVERSE = 1
 OPT_TOUCH_MATRICES = 2
 OPT_VISLISTS = 4      # SceneWithVisibilityLists (default volume) instead of SceneBasic
 OPT_BOX = 8           # the input carries scene.box (local AABB column)
+OPT_INSTANCES = 16    # dump view / projView per camera and view*world, projView*world of every node for camera 0
 POPT_ROLL, POPT_INVERSED, POPT_MESH = 1, 2, 4
 
 # columns of the 24-float particle record written by the harness
@@ -66,7 +67,7 @@ def write_scene_input(path: str, scene: Scene, cameras: np.ndarray, frames: int 
         f.write(cameras.tobytes())
 
 
-def read_scene_output(path: str) -> dict:
+def read_scene_output(path: str, with_instances: bool = False) -> dict:
     buf = np.fromfile(path, dtype=np.uint8)
     off = 0
 
@@ -98,6 +99,13 @@ def read_scene_output(path: str) -> dict:
         out["frustum"][c] = take("<f4", 28)
         out["cam_flags"][c], out["cam_group"][c], cnt = take("<u4", 3)
         out["lists"].append(take("<u4", int(cnt)).copy())
+    if with_instances:
+        out["view"] = np.zeros((ncam, 16), np.float32); out["projview"] = np.zeros((ncam, 16), np.float32)
+        for c in range(ncam):
+            out["view"][c] = take("<f4", 16); out["projview"][c] = take("<f4", 16)
+            if c == 0:
+                out["mv"] = take("<f4", n * 16).reshape(n, 16).copy()
+                out["mvp"] = take("<f4", n * 16).reshape(n, 16).copy()
     assert off == buf.shape[0], (off, buf.shape[0])
     return out
 
@@ -109,7 +117,7 @@ def run_scene(scene: Scene, cameras: np.ndarray, frames: int = 1, options: int =
         fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
         write_scene_input(fin, scene, cameras, frames, options, root_translate)
         subprocess.run([harness_path(kind), "scene", fin, fout], check=True, stdout=subprocess.DEVNULL)
-        return read_scene_output(fout)
+        return read_scene_output(fout, with_instances=bool(options & OPT_INSTANCES))
 
 
 def bench_scene(scene: Scene, cameras: np.ndarray, frames: int, warmup: int,

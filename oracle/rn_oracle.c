@@ -891,3 +891,29 @@ void rn_oracle_emitter_mesh(const oracle_emitter_state *s, uint32_t k, float wor
 	for(int i = stop; i < maxp; i++)
 		for(int c = 0; c < 6; c++) idx[(size_t)i * 6 + c] = (uint16_t)(i * 4);
 }
+
+/* ---- next row: per-drawable matrices --------------------------------------------------------------------------- */
+/* (LOD selection, the other per-drawable step of Entity::Render, is compiled out in this reference:
+ * RN_MODEL_LOD_DISABLED 1, Source/Rendering/RNModel.h:9 - there is no live behaviour to restate.) */
+
+/* Drawable::Update (Source/Rendering/RNRenderer.h:65-76) + the matrix uniforms a renderer derives per drawable
+ * (Modules/Vulkan/Sources/RNVulkanRenderer.cpp:1112-1168): modelMatrix = world, inverseModelMatrix = inverse world,
+ * modelView = view * model, modelViewProjection = projectionView * model (Matrix::operator*).  64 floats per entry. */
+void rn_oracle_instances(uint32_t count, const uint32_t *ids, const float *wmat, const float *winv, const float *view,
+                         const float *projview, float *out)
+{
+	mat4 v, pv;
+	memcpy(v.m, view, 64); memcpy(pv.m, projview, 64);
+	for(uint32_t q = 0; q < count; q++)
+	{
+		uint32_t i = ids[q];
+		mat4 m;
+		memcpy(m.m, wmat + (size_t)i * 16, 64);
+		mat4 a = mat_mul(&v, &m), p = mat_mul(&pv, &m);
+		float *o = out + (size_t)q * 64;
+		memcpy(o, m.m, 64);
+		memcpy(o + 16, winv + (size_t)i * 16, 64);
+		memcpy(o + 32, a.m, 64);
+		memcpy(o + 48, p.m, 64);
+	}
+}
