@@ -193,23 +193,40 @@ def run_ours(args) -> dict:
     counts = h.read_counts(stream)
     vis_frac = [float(c) / n for c in counts]
     exch = None
+    use_masks = False
     if world > 1:
         from rayne_b200 import shard
-        exch = shard.ListExchange()
-        pexch = shard.PipelinedListExchange()
+        use_masks = args.exchange == "masks"
         count_t = torch.as_tensor(DevArray(lists[0].count, ncam), device="cuda")
-        list_t = [torch.as_tensor(DevArray(lists[c].slots, n), device="cuda") for c in range(ncam)]
+        if use_masks:
+            # compact form: rank-order visibility bitmasks (rn_cull_build_masks), 1 bit per node and view
+            h.build_masks(stream)
+            mptr, mwords, _ = h.device_masks()
+            mask_t = torch.as_tensor(DevArray(mptr, ncam * mwords), device="cuda")
+            pexch = shard.PipelinedMaskExchange([mwords] * world, ncam)
+        else:
+            exch = shard.ListExchange()
+            pexch = shard.PipelinedListExchange()
+            list_t = [torch.as_tensor(DevArray(lists[c].slots, n), device="cuda") for c in range(ncam)]
 
     def exchange():
-        # the path's only collective: all-gather of the per-camera counts, then of the index lists
+        # the path's only collective, synchronous form: all-gather of the visibility of every view
+        if use_masks:
+            h.build_masks(stream)
+            pexch.submit(mask_t)
+            return pexch.flush()
         return exch.exchange(count_t, list_t)
 
     def step():
-        # every frame's lists ARE gathered on every GPU; the gather of frame i runs on a side stream under the kernels
-        # of frame i+1 (shard.PipelinedListExchange) and the last one is flushed inside the timed region
+        # every frame's visibility IS gathered on every GPU; the gather of frame i runs on a side stream under the
+        # kernels of frame i+1 (two frames in flight) and the last ones are flushed inside the timed region
         h.transform_cull(fr, stream)
         if world > 1:
-            pexch.submit(count_t, list_t)
+            if use_masks:
+                h.build_masks(stream)
+                pexch.submit(mask_t)
+            else:
+                pexch.submit(count_t, list_t)
 
     def barrier():
         torch.cuda.synchronize()
@@ -265,6 +282,41 @@ def run_ours(args) -> dict:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     ms_step = ms_total / args.steps
+
+    # the gathered masks expand to the global lists: count check against the all-reduced counts, and the cost of
+    # materialising all views' lists on one GPU (outside the timed region; a consumer expands what it draws)
+    exchange_info = None
+    if world > 1 and use_masks:
+        gathered = pexch.flush()
+        tot = count_t.clone().to(torch.int64)
+        dist.all_reduce(tot)
+        tot = tot.cpu().tolist()
+        starts = [r * n for r in range(world)]
+        out_l = torch.empty(max(tot) + 1, dtype=torch.int32, device="cuda")
+        out_c = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ok = True
+        for c in range(ncam):
+            pexch.expand(h, gathered, c, starts, out_l, out_c, stream)
+            k = int(out_c.item())
+            asc = bool((out_l[1:k] > out_l[:k - 1]).all().item()) if k > 1 else True
+            ok = ok and k == tot[c] and asc
+        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        x0.record()
+        for _ in range(5):
+            for c in range(ncam):
+                pexch.expand(h, gathered, c, starts, out_l, out_c, stream)
+        x1.record()
+        torch.cuda.synchronize()
+        exchange_info = {"kind": "NCCL all-gather of rank-order visibility bitmasks (rn_cull_build_masks), fixed size, "
+                                 "two frames in flight on a side stream",
+                         "bytes_per_gpu_and_frame": int(ncam * mwords * 4), "global_list_entries_per_view": tot,
+                         "expanded_lists_match_counts_and_ascend": ok,
+                         "expand_all_views_ms": x0.elapsed_time(x1) / 5,
+                         "expand_note": "rn_masks_expand of all views' global lists on one GPU; not part of the step"}
+        del out_l
+    elif world > 1:
+        exchange_info = {"kind": "NCCL all-gather of per-camera counts + index lists, two frames in flight on a side stream",
+                         "overflows": int(pexch.overflows), "entries_per_rank_and_camera": list(pexch.sizes or [])}
 
     # ---- end to end through the C ABI with host buffers (pinned) ----
     roots = rs.roots
@@ -374,6 +426,13 @@ def run_ours(args) -> dict:
         sort_bytes = entries * (4 * 16.0 + 28.0 + 8.0)
         extras["cull_sort_front_to_back"] = {"ms": ms, "entries": entries, "Mentries_per_s": entries / ms / 1e3,
                                              "roofline_frac": sort_bytes / (ms * 1e-3) / 1e9 / peak}
+        # §8(f) drawable uniform packing: 256-byte matrix records of the largest list
+        view, _, projview = capi.build_camera_matrices(cams)
+        inst = torch.empty((max(entries, 1), 64), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: h.pack_instances(ncam - 1, view[ncam - 1], projview[ncam - 1], inst.data_ptr(), entries, stream))
+        extras["cull_pack_instances"] = {"ms": ms, "entries": entries, "bytes_per_entry": 388,
+                                         "roofline_frac": entries * 388.0 / (ms * 1e-3) / 1e9 / peak}
+        del inst
         if particles:
             ms = timed(lambda: h.particles_build_mesh(stream=stream))
             extras["particles_build_mesh"] = {"ms": ms, "bytes_per_particle": 236,
@@ -394,7 +453,7 @@ def run_ours(args) -> dict:
                                "(2 eye + 4 shadow-cascade cameras), every node re-propagated each frame",
                    "nodes_per_gpu": n, "views": ncam, "visible_fraction_per_view": [round(v, 5) for v in vis_frac],
                    "l2": "inputs (1.07 GB of node columns) exceed the 126 MB L2; no flush needed",
-                   "parallelism": f"node-range sharding x{world}, NCCL allgather of counts + lists" if world > 1 else "single GPU"},
+                   "parallelism": (f"node-range sharding x{world}, NCCL all-gather of " + ("visibility bitmasks" if args.exchange == "masks" else "counts + lists")) if world > 1 else "single GPU"},
         "e2e": {"value": n * world / e2e_ms / 1e3, "unit": "Mnodes/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": int(roots.shape[0] * 16), "d2h_bytes_per_step": int(d2h),
                 "what": ("rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + 6 lists) "
@@ -402,8 +461,7 @@ def run_ours(args) -> dict:
                                                        "(rayne_b200/pipeline.py), every range's copy inside the timed region" if shards > 1 else "")),
                 "shards": shards},
         "gpu_launches": int(launches),
-        "exchange": ({"kind": "NCCL all-gather of per-camera counts + index lists, one frame deep on a side stream",
-                      "overflows": int(pexch.overflows), "entries_per_rank_and_camera": list(pexch.sizes or [])} if world > 1 else None),
+        "exchange": exchange_info,
         "roofline": {"bound": "hbm", "kernel": "rn::tile_kernel<true,true>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_kind": peak_kind, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": tile_avg_ms,
@@ -450,6 +508,8 @@ def main():
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
+    ap.add_argument("--exchange", choices=("masks", "lists"), default="masks",
+                    help="N>1: what the per-frame all-gather ships (rank-order bitmasks, or counts + index lists)")
     ap.add_argument("--no-extras", action="store_true", help="skip the side timings of inverse / bounds / sort / mesh")
     ap.add_argument("--tile-nodes", type=int, default=0, help="rn_scene_desc.tile_nodes (0 = library default)")
     ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")

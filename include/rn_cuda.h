@@ -234,9 +234,52 @@ int rn_scene_device_extras(rn_scene_t *scene, const float **inverse_world_matrix
  * column for anything but an all-RenderNormal scene.  Asynchronous on `cuda_stream`, no host synchronisation. */
 int rn_cull_sort(rn_scene_t *scene, const float *camera_world_positions, uint32_t n_cameras, void *cuda_stream);
 
+/* The visibility of the last cull as bitmasks in render-list order: bit (r & 31) of word (r >> 5) of camera c is set
+ * iff the node of rank r is in camera c's list - the same information as the (unsorted) list of
+ * SceneBasic::Render's cull loop (Source/Scene/RNSceneBasic.cpp:576-593) in 1/32 of the bytes per node.  Ranks are
+ * local to the scene (rank_offset of rn_scene_set_list_mode is not applied).  This is what the multi-GPU exchange
+ * ships; rn_masks_expand turns gathered masks back into lists.  Asynchronous on `cuda_stream`. */
+int rn_cull_build_masks(rn_scene_t *scene, void *cuda_stream);
+/* Device pointer of the masks (camera c at masks + c * words_per_camera), words per camera = ceil(nodes / 32), and
+ * the number of cameras they hold; *masks = NULL before rn_cull_build_masks or after a newer cull. */
+int rn_cull_device_masks(rn_scene_t *scene, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras);
+/* Copies the masks of cameras 0..n_cameras-1 into out_words[n_cameras][words_per_camera] (host memory, pinned for a
+ * truly asynchronous copy) behind the work of `cuda_stream`; the caller synchronises the stream. */
+int rn_cull_read_masks_async(rn_scene_t *scene, uint32_t n_cameras, uint32_t *out_words, void *cuda_stream);
+/* One rank range of a gathered mask: n_words words in DEVICE memory, bit b of word w = rank rank_base + 32 w + b. */
+typedef struct rn_mask_segment {
+	const uint32_t *device_words;
+	uint32_t        n_words;
+	uint32_t        rank_base;
+} rn_mask_segment;
+/* Appends the ranks of the set bits of the segments, in segment order and ascending inside a segment, to device_list
+ * at position *device_count and adds their number to *device_count (a uint32 in DEVICE memory; no host round trip).
+ * With the segments = the rank ranges of all GPUs in order (what the all-gather of rn_cull_build_masks' output
+ * delivers) the result is the visibility list of the whole scene in global ranks, bit for bit.  Entries beyond
+ * `capacity` are counted but not written.  `scene` only provides the device and scratch memory.  Asynchronous. */
+int rn_masks_expand(rn_scene_t *scene, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
+                    uint32_t capacity, uint32_t *device_count, void *cuda_stream);
+
+/* Per-drawable matrix records for the list of `camera` left by the last cull (and rn_cull_sort): what a renderer
+ * writes per drawable before a draw - model and inverse model matrix (Drawable::Update,
+ * Source/Rendering/RNRenderer.h:65-76), view * model and projection * view * model
+ * (Modules/Vulkan/Sources/RNVulkanRenderer.cpp:1134-1168).  Entry e of the list becomes 64 floats at
+ * device_out + e * 256 bytes: model[16], inverse model[16], view * model[16], proj_view * model[16] (column-major).
+ * `device_out` is DEVICE memory of the caller (e.g. an instance / storage buffer mapped through graphics interop),
+ * 16-byte aligned, room for `capacity` records; entries beyond `capacity` are not written.  The entry count stays on
+ * the device (rn_cull_read_counts).  Needs rn_transform_propagate and rn_transform_inverse.  Asynchronous.
+ * LOD selection, the other per-drawable step of Entity::Render, is compiled out in the reference
+ * (RN_MODEL_LOD_DISABLED, Source/Rendering/RNModel.h:9) and has no counterpart here. */
+int rn_cull_pack_instances(rn_scene_t *scene, uint32_t camera, const float *view, const float *proj_view,
+                           void *device_out, uint32_t capacity, void *cuda_stream);
+
 /* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
  * Pure host function; V <= 8 cameras per frame make this negligible. */
 int rn_camera_build_frustum(const rn_camera_desc *camera, rn_camera_frustum *out);
+
+/* Camera::GetViewMatrix / GetProjectionMatrix as Camera::PostUpdate leaves them (Source/Scene/RNCamera.cpp:296-340)
+ * and their product projection * view; 16 floats each, column-major, any of the outputs may be NULL.  Host function. */
+int rn_camera_build_matrices(const rn_camera_desc *camera, float *view, float *projection, float *proj_view);
 
 /* SceneBasic::AddNode / AddRenderNode list order (Source/Scene/RNSceneBasic.cpp:652-676,683-736 and
  * Source/Scene/RNSceneNode.cpp:270-294) for nodes given in CREATION order: parent[i] < i is the creation index of

@@ -140,6 +140,16 @@ def instances(ids, wmat, winv, view, projview) -> np.ndarray:
     return out
 
 
+def camera_matrices(cameras: np.ndarray):
+    """(view, projection, proj_view) per camera, each [V, 16]."""
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    v = np.zeros((cameras.shape[0], 16), np.float32); p = np.zeros_like(v); pv = np.zeros_like(v)
+    for i in range(cameras.shape[0]):
+        load().rn_oracle_camera_matrices(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(v[i].ctypes.data),
+                                         C.c_void_p(p[i].ctypes.data), C.c_void_p(pv[i].ctypes.data))
+    return v, p, pv
+
+
 def frustums(cameras: np.ndarray) -> np.ndarray:
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
     out = np.zeros(cameras.shape[0], dtype=FRUSTUM_DTYPE)

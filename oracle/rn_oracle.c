@@ -311,19 +311,9 @@ static void plane_posnormal(vec3 p, vec3 n, float out[4])
 	out[3] = vec_dot(n, p) + 0.0f;
 }
 
-/* Camera::PostUpdate / UpdateProjection / UpdateFrustum, Source/Scene/RNCamera.cpp:296-384 */
-int rn_oracle_frustum(const oracle_camera *cam, oracle_frustum *out)
+/* Camera::PostUpdate (inverse view matrix) and UpdateProjection, Source/Scene/RNCamera.cpp:296-340 */
+static void camera_matrices(const oracle_camera *cam, mat4 *inv_view_out, mat4 *proj_out)
 {
-	memset(out, 0, sizeof(*out));
-	out->flags = cam->flags;
-	out->render_group = cam->render_group;
-	if(cam->flags & CAM_SIMPLE)
-	{
-		out->center[2] = cam->clip_far * 0.5f;
-		out->radius = (float)(cam->clip_far * 1.5);
-		for(int k = 0; k < 6; k++) out->planes[k][1] = 1.0f; /* default Plane(), RNPlane.h:49-54 */
-		return 0;
-	}
 	vec3 wp = {cam->pos[0], cam->pos[1], cam->pos[2]}, sc = {cam->scale[0], cam->scale[1], cam->scale[2]};
 	quat wr = {cam->rot[0], cam->rot[1], cam->rot[2], cam->rot[3]};
 	mat4 inv_view = local_matrix(wp, wr, sc); /* :303-305 */
@@ -352,6 +342,37 @@ int rn_oracle_frustum(const oracle_camera *cam, oracle_frustum *out)
 		proj.m[14] = (cam->clip_far * cam->clip_near) / (cam->clip_far - cam->clip_near);
 		proj.m[15] = 0.0f;
 	}
+	*inv_view_out = inv_view;
+	*proj_out = proj;
+}
+
+/* Camera::GetViewMatrix (= GetInverse of the inverse view matrix, RNCamera.cpp:307), GetProjectionMatrix and
+ * projection * view (Modules/Vulkan/Sources/RNVulkanRenderer.cpp:1134-1168) */
+void rn_oracle_camera_matrices(const oracle_camera *cam, float *view, float *projection, float *proj_view)
+{
+	mat4 inv_view, proj;
+	camera_matrices(cam, &inv_view, &proj);
+	mat4 v = mat_inverse(&inv_view), pv = mat_mul(&proj, &v);
+	memcpy(view, v.m, 64); memcpy(projection, proj.m, 64); memcpy(proj_view, pv.m, 64);
+}
+
+/* Camera::PostUpdate / UpdateProjection / UpdateFrustum, Source/Scene/RNCamera.cpp:296-384 */
+int rn_oracle_frustum(const oracle_camera *cam, oracle_frustum *out)
+{
+	memset(out, 0, sizeof(*out));
+	out->flags = cam->flags;
+	out->render_group = cam->render_group;
+	if(cam->flags & CAM_SIMPLE)
+	{
+		out->center[2] = cam->clip_far * 0.5f;
+		out->radius = (float)(cam->clip_far * 1.5);
+		for(int k = 0; k < 6; k++) out->planes[k][1] = 1.0f; /* default Plane(), RNPlane.h:49-54 */
+		return 0;
+	}
+	quat wr = {cam->rot[0], cam->rot[1], cam->rot[2], cam->rot[3]};
+	vec3 wp = {cam->pos[0], cam->pos[1], cam->pos[2]};
+	mat4 inv_view, proj;
+	camera_matrices(cam, &inv_view, &proj);
 	mat4 inv_proj = mat_inverse(&proj);
 	mat4 tw = mat_mul(&inv_view, &inv_proj);
 	vec3 pos1 = to_world(&tw, -1.0f, 1.0f, 1.0f), pos2 = to_world(&tw, -1.0f, 1.0f, 0.0f), pos3 = to_world(&tw, -1.0f, -1.0f, 0.0f);

@@ -31,6 +31,8 @@ EXPORTS = [
     "rn_scene_profile", "rn_scene_profile_read",
     "rn_transform_inverse", "rn_bounds_update", "rn_scene_device_extras", "rn_cull_sort",
     "rn_scenevis_default_volume_order", "rn_particles_build_mesh", "rn_particles_download_mesh",
+    "rn_cull_pack_instances", "rn_camera_build_matrices",
+    "rn_cull_build_masks", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
 
@@ -55,6 +57,10 @@ class NodeColumns(C.Structure):
 class ParticleMesh(C.Structure):
     _fields_ = [("position", C.c_void_p), ("color", C.c_void_p), ("uv0", C.c_void_p), ("uv1", C.c_void_p),
                 ("indices", C.c_void_p), ("vertex_stride_per_emitter", C.c_uint32), ("index_stride_per_emitter", C.c_uint32)]
+
+
+class MaskSegment(C.Structure):
+    _fields_ = [("device_words", C.c_void_p), ("n_words", C.c_uint32), ("rank_base", C.c_uint32)]
 
 
 class VisList(C.Structure):
@@ -151,6 +157,17 @@ def build_frustums(cameras: np.ndarray) -> np.ndarray:
     for i in range(cameras.shape[0]):
         _check(lib.rn_camera_build_frustum(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(out[i:i + 1].ctypes.data)))
     return out
+
+
+def build_camera_matrices(cameras: np.ndarray):
+    """rn_camera_build_matrices for an array of camera records: (view, projection, proj_view), each [V, 16]."""
+    lib = load()
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    v = np.zeros((cameras.shape[0], 16), np.float32); p = np.zeros_like(v); pv = np.zeros_like(v)
+    for i in range(cameras.shape[0]):
+        _check(lib.rn_camera_build_matrices(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(v[i].ctypes.data),
+                                            C.c_void_p(p[i].ctypes.data), C.c_void_p(pv[i].ctypes.data)))
+    return v, p, pv
 
 
 def render_order(parent: np.ndarray, priority: np.ndarray | None = None) -> np.ndarray:
@@ -283,6 +300,40 @@ class SceneHandle:
     def cull_sort(self, camera_positions: np.ndarray, stream: int = 0) -> None:
         cp = _f32(np.atleast_2d(camera_positions), 3)
         _check(self.lib.rn_cull_sort(self._h, _ptr(cp), C.c_uint32(cp.shape[0]), C.c_void_p(stream)))
+
+    def pack_instances(self, camera: int, view: np.ndarray, proj_view: np.ndarray, device_out: int, capacity: int,
+                       stream: int = 0) -> None:
+        """rn_cull_pack_instances: 256-byte matrix records of camera's list into DEVICE memory at `device_out`."""
+        v = _f32(view).reshape(16); pv = _f32(proj_view).reshape(16)
+        _check(self.lib.rn_cull_pack_instances(self._h, C.c_uint32(camera), _ptr(v), _ptr(pv), C.c_void_p(device_out),
+                                               C.c_uint32(capacity), C.c_void_p(stream)))
+
+    def build_masks(self, stream: int = 0) -> None:
+        _check(self.lib.rn_cull_build_masks(self._h, C.c_void_p(stream)))
+
+    def device_masks(self):
+        """(device pointer, words per camera, cameras) of the rank-order visibility bitmasks."""
+        p = C.c_void_p(); w = C.c_uint32(); k = C.c_uint32()
+        _check(self.lib.rn_cull_device_masks(self._h, C.byref(p), C.byref(w), C.byref(k)))
+        return int(p.value or 0), int(w.value), int(k.value)
+
+    def read_masks(self, stream: int = 0, out: np.ndarray | None = None, wait: bool = True) -> np.ndarray:
+        """[ncams, words] uint32; `out` may be a pinned host array for an asynchronous copy (wait=False)."""
+        _, words, k = self.device_masks()
+        if out is None:
+            out = np.zeros((k, words), dtype=np.uint32)
+        _check(self.lib.rn_cull_read_masks_async(self._h, C.c_uint32(out.shape[0]), C.c_void_p(out.ctypes.data), C.c_void_p(stream)))
+        if wait:
+            stream_synchronize(stream)
+        return out
+
+    def masks_expand(self, segments, device_list: int, capacity: int, device_count: int, stream: int = 0) -> None:
+        """segments: iterable of (device pointer of the words, n_words, rank_base), expanded in order."""
+        segs = (MaskSegment * max(len(segments), 1))()
+        for k, (p, nw, base) in enumerate(segments):
+            segs[k].device_words, segs[k].n_words, segs[k].rank_base = int(p), int(nw), int(base)
+        _check(self.lib.rn_masks_expand(self._h, segs, C.c_uint32(len(segments)), C.c_void_p(device_list),
+                                        C.c_uint32(capacity), C.c_void_p(device_count), C.c_void_p(stream)))
 
     def set_list_mode(self, ranks: bool, rank_offset: int = 0) -> None:
         _check(self.lib.rn_scene_set_list_mode(self._h, int(ranks), C.c_uint32(rank_offset)))

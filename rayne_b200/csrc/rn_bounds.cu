@@ -260,12 +260,15 @@ int aabb_filter_launch(rn_scene *s, const rn_camera_frustum *cams, uint32_t ncam
 
 void extras_free(rn_scene *s)
 {
-	void *ptrs[] = {s->box0, s->box1, s->winv, s->bsphere, s->baabb, s->prio_group, s->sort_scratch, s->sort_hist, s->sort_ranges};
+	void *ptrs[] = {s->box0, s->box1, s->winv, s->bsphere, s->baabb, s->prio_group, s->sort_scratch, s->sort_hist, s->sort_ranges,
+	                s->rank_masks, s->expand_totals};
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
 	s->box0 = nullptr; s->box1 = nullptr; s->winv = nullptr; s->bsphere = nullptr; s->baabb = nullptr;
 	s->prio_group = nullptr; s->sort_scratch = s->sort_hist = s->sort_ranges = nullptr;
-	s->have_inverse = s->have_bounds = false;
+	s->rank_masks = s->expand_totals = nullptr;
+	s->expand_blocks_cap = 0;
+	s->have_inverse = s->have_bounds = s->have_masks = false;
 }
 
 } // namespace rn

@@ -157,27 +157,11 @@ Plane plane_position_normal(const V3 &p, const V3 &n)
 
 } // namespace
 
-extern "C" int rn_camera_build_frustum(const rn_camera_desc *cam, rn_camera_frustum *out)
+// Camera::PostUpdate (RNCamera.cpp:300-305) and UpdateProjection (:314-340) / SetProjectionMatrix (:221-228)
+static void camera_matrices(const rn_camera_desc *cam, M4 &invView, M4 &proj)
 {
-	RN_REQUIRE(cam && out, RN_ERR_INVALID, "NULL argument");
-	memset(out, 0, sizeof(*out));
-	out->flags = cam->flags;
-	out->render_group = cam->render_group;
-
-	// Camera::UpdateFrustum, UseSimpleCulling branch (RNCamera.cpp:347-352): centre is camera-local (reference quirk)
-	if(cam->flags & RN_CAMERA_USE_SIMPLE_CULLING)
-	{
-		out->center[0] = 0.0f;
-		out->center[1] = 0.0f;
-		out->center[2] = cam->clip_far * 0.5f;
-		out->radius = static_cast<float>(cam->clip_far * 1.5);
-		// the six planes keep their default-constructed value (Plane::Plane, RNPlane.h:49-54); they are never tested
-		for(int k = 0; k < 6; k++) out->planes[k][1] = 1.0f;
-		return RN_OK;
-	}
-
 	// Camera::PostUpdate (RNCamera.cpp:300-305): inverse view = T(worldPos) * R(worldRot) * S(local scale)
-	M4 invView = identity();
+	invView = identity();
 	invView.m[12] = cam->world_position[0];
 	invView.m[13] = cam->world_position[1];
 	invView.m[14] = cam->world_position[2];
@@ -187,7 +171,7 @@ extern "C" int rn_camera_build_frustum(const rn_camera_desc *cam, rn_camera_frus
 	invView = mul(invView, sc);
 
 	// Camera::UpdateProjection (RNCamera.cpp:314-340) / SetProjectionMatrix (:221-228)
-	M4 proj = identity();
+	proj = identity();
 	if(cam->has_projection)
 	{
 		memcpy(proj.m, cam->projection, sizeof(proj.m));
@@ -222,6 +206,29 @@ extern "C" int rn_camera_build_frustum(const rn_camera_desc *cam, rn_camera_frus
 		proj.m[14] = (cam->clip_far * cam->clip_near) / (cam->clip_far - cam->clip_near);
 		proj.m[15] = 0.0f;
 	}
+}
+
+extern "C" int rn_camera_build_frustum(const rn_camera_desc *cam, rn_camera_frustum *out)
+{
+	RN_REQUIRE(cam && out, RN_ERR_INVALID, "NULL argument");
+	memset(out, 0, sizeof(*out));
+	out->flags = cam->flags;
+	out->render_group = cam->render_group;
+
+	// Camera::UpdateFrustum, UseSimpleCulling branch (RNCamera.cpp:347-352): centre is camera-local (reference quirk)
+	if(cam->flags & RN_CAMERA_USE_SIMPLE_CULLING)
+	{
+		out->center[0] = 0.0f;
+		out->center[1] = 0.0f;
+		out->center[2] = cam->clip_far * 0.5f;
+		out->radius = static_cast<float>(cam->clip_far * 1.5);
+		// the six planes keep their default-constructed value (Plane::Plane, RNPlane.h:49-54); they are never tested
+		for(int k = 0; k < 6; k++) out->planes[k][1] = 1.0f;
+		return RN_OK;
+	}
+
+	M4 invView, proj;
+	camera_matrices(cam, invView, proj);
 	const M4 invProj = inverse(proj);
 
 	// Camera::__ToWorld (RNCamera.cpp:386-396): (invView * invProj) * ndc, then divide by w
@@ -273,6 +280,25 @@ extern "C" int rn_camera_build_frustum(const rn_camera_desc *cam, rn_camera_frus
 		out->planes[k][1] = planes[k].n.y;
 		out->planes[k][2] = planes[k].n.z;
 		out->planes[k][3] = planes[k].d;
+	}
+	return RN_OK;
+}
+
+// Camera::GetViewMatrix / GetProjectionMatrix after PostUpdate (RNCamera.cpp:296-311): view = GetInverse of the inverse
+// view matrix; proj_view = projection * view, the product the renderers form per camera
+// (Modules/Vulkan/Sources/RNVulkanRenderer.cpp:1134-1168).
+extern "C" int rn_camera_build_matrices(const rn_camera_desc *cam, float *view, float *projection, float *proj_view)
+{
+	RN_REQUIRE(cam, RN_ERR_INVALID, "NULL argument");
+	M4 invView, proj;
+	camera_matrices(cam, invView, proj);
+	const M4 v = inverse(invView);
+	if(view) memcpy(view, v.m, sizeof(v.m));
+	if(projection) memcpy(projection, proj.m, sizeof(proj.m));
+	if(proj_view)
+	{
+		const M4 pv = mul(proj, v);
+		memcpy(proj_view, pv.m, sizeof(pv.m));
 	}
 	return RN_OK;
 }

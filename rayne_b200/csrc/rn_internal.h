@@ -95,6 +95,11 @@ struct rn_scene
 	uint32_t *sort_hist = nullptr;
 	uint32_t *sort_ranges = nullptr;   // [RN_MAX_CAMERAS][2]: transparent range begin, end (device)
 	uint32_t sort_blocks_cap = 0;
+	uint32_t *rank_masks = nullptr;    // [RN_MAX_CAMERAS][ceil(max_nodes / 32)] visibility bits in rank order (rn_masks.cu)
+	bool have_masks = false;
+	uint32_t mask_ncams = 0;
+	uint32_t *expand_totals = nullptr; // rn_masks_expand: per-CTA totals / offsets
+	uint32_t expand_blocks_cap = 0;
 	uint32_t *spine_slots = nullptr;   // all spine slots grouped by depth
 	std::vector<uint32_t> spine_level_ofs; // host: offsets into spine_slots per depth (size levels+1)
 	float *scratch_cols = nullptr;     // device staging for rn_scene_update_nodes

@@ -1,0 +1,296 @@
+// Visibility of the last cull as bitmasks in render-list (rank) order, and their expansion back into lists.
+//
+// A visibility list of SceneBasic::Render (Source/Scene/RNSceneBasic.cpp:576-593) is the ascending sequence of the
+// render-list ranks that passed CanRender, so one bit per rank holds exactly the same information in 1/32 of a list
+// entry: 2.1 MB per camera for 16.8 M nodes instead of 4 B per visible node (61 MB for the six views of the
+// benchmark frame).  That is the form the multi-GPU exchange ships (shard.PipelinedMaskExchange): every rank
+// all-gathers the masks of its rank range and expands the cameras it consumes with rn_masks_expand, which reproduces
+// the reference list bit for bit (tests/test_gpu_masks.py).
+//
+// Both kernels are HBM-bound integer work: rank_mask_kernel reads 4 B (rank -> slot) + 1 B (mask byte) per node and
+// writes V/8 B; the expansion reads the words once or twice and writes 4 B per visible node.
+#include "rn_internal.h"
+#include <algorithm>
+#include <string.h>
+
+namespace rn {
+
+constexpr uint32_t kMaskThreads = 256;
+
+// One warp builds 32 consecutive words (1024 ranks) of every camera: in iteration i the warp's lanes hold ranks
+// base + 32 i .. +31, one ballot per camera gives word i, lane i keeps it; after 32 iterations lane i stores word i
+// of every camera - 128-byte coalesced stores.
+__global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *__restrict__ vis,
+                                                                 const uint32_t *__restrict__ slot_of_rank, uint32_t n,
+                                                                 uint32_t words, uint32_t ncams, uint32_t *__restrict__ masks)
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp = (blockIdx.x * kMaskThreads + threadIdx.x) >> 5;
+	const uint32_t word0 = warp * 32u;
+	if(word0 >= words)
+		return;
+	uint32_t mine[RN_MAX_CAMERAS];
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) mine[c] = 0;
+#pragma unroll 8
+	for(uint32_t i = 0; i < 32; i++)
+	{
+		const uint32_t r = (word0 + i) * 32u + lane;
+		uint32_t v = 0;
+		if(r < n)
+			v = __ldg(vis + __ldg(slot_of_rank + r));
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		{
+			const uint32_t b = __ballot_sync(0xffffffffu, (v >> c) & 1u);
+			if(lane == i) mine[c] = b;
+		}
+	}
+	if(word0 + lane < words)
+	{
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			if((uint32_t)c < ncams)
+				masks[(size_t)c * words + word0 + lane] = mine[c];
+	}
+}
+
+// ---- expansion: words -> ascending ranks -----------------------------------------------------------------------
+constexpr uint32_t kExpandThreads = 256;
+constexpr uint32_t kExpandWordsPerBlock = kExpandThreads * 4;   // 32 768 ranks per CTA
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *s_warp, uint32_t *total)
+{
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	uint32_t x = v;
+#pragma unroll
+	for(int o = 1; o < 32; o <<= 1)
+	{
+		const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+		if(lane >= (uint32_t)o) x += y;
+	}
+	if(lane == 31) s_warp[warp] = x;
+	__syncthreads();
+	if(warp == 0)
+	{
+		uint32_t w = lane < kExpandThreads / 32 ? s_warp[lane] : 0u, z = w;
+#pragma unroll
+		for(int o = 1; o < 32; o <<= 1)
+		{
+			const uint32_t y = __shfl_up_sync(0xffffffffu, z, o);
+			if(lane >= (uint32_t)o) z += y;
+		}
+		if(lane < kExpandThreads / 32) s_warp[lane] = z - w;
+		if(lane == 31) *total = z;
+	}
+	__syncthreads();
+	return s_warp[warp] + x - v;
+}
+
+constexpr uint32_t kExpandMaxSegments = 32;
+
+// The rank ranges of several GPUs as ONE virtual word array: CTA b works on words [1024 (b - first_block[s]), ...) of
+// the segment s that holds it.
+struct ExpandArgs
+{
+	const uint32_t *words[kExpandMaxSegments];
+	uint32_t n_words[kExpandMaxSegments];
+	uint32_t rank_base[kExpandMaxSegments];
+	uint32_t first_block[kExpandMaxSegments + 1];
+	uint32_t n_segments;
+};
+
+__device__ __forceinline__ uint32_t segment_of(const ExpandArgs &a, uint32_t block)
+{
+	uint32_t s = 0;
+	while(s + 1 < a.n_segments && block >= a.first_block[s + 1]) s++;
+	return s;
+}
+
+// pass 1: set bits per CTA
+__global__ void __launch_bounds__(kExpandThreads) expand_count_kernel(const __grid_constant__ ExpandArgs a,
+                                                                      uint32_t *__restrict__ block_totals)
+{
+	__shared__ uint32_t s_warp[32];
+	const uint32_t seg = segment_of(a, blockIdx.x);
+	const uint32_t *__restrict__ words = a.words[seg];
+	const uint32_t n_words = a.n_words[seg];
+	const uint32_t w0 = (blockIdx.x - a.first_block[seg]) * kExpandWordsPerBlock + threadIdx.x;
+	uint32_t cnt = 0;
+#pragma unroll
+	for(int k = 0; k < 4; k++)
+		if(w0 + k * kExpandThreads < n_words) cnt += __popc(__ldg(words + w0 + k * kExpandThreads));
+	cnt = __reduce_add_sync(0xffffffffu, cnt);
+	if((threadIdx.x & 31u) == 0) s_warp[threadIdx.x >> 5] = cnt;
+	__syncthreads();
+	if(threadIdx.x < 32)
+	{
+		uint32_t v = threadIdx.x < kExpandThreads / 32 ? s_warp[threadIdx.x] : 0u;
+		v = __reduce_add_sync(0xffffffffu, v);
+		if(threadIdx.x == 0) block_totals[blockIdx.x] = v;
+	}
+}
+
+// pass 2 (one CTA): exclusive scan of the CTA totals on top of the running count of the output list
+__global__ void __launch_bounds__(kExpandThreads) expand_scan_kernel(uint32_t *__restrict__ block_totals, uint32_t n_blocks,
+                                                                     uint32_t *__restrict__ list_count)
+{
+	__shared__ uint32_t s_warp[32];
+	__shared__ uint32_t s_total;
+	uint32_t base = *list_count;
+	for(uint32_t b0 = 0; b0 < n_blocks; b0 += kExpandThreads)
+	{
+		const uint32_t b = b0 + threadIdx.x;
+		const uint32_t v = b < n_blocks ? block_totals[b] : 0u;
+		const uint32_t ex = block_exclusive_scan(v, s_warp, &s_total);
+		if(b < n_blocks) block_totals[b] = base + ex;
+		base += s_total;
+		__syncthreads();
+	}
+	if(threadIdx.x == 0) *list_count = base;
+}
+
+// pass 3: four rounds of 256 words; a thread unpacks its word into shared memory behind the entries of the threads
+// before it, then the CTA copies the round's entries out with coalesced stores
+__global__ void __launch_bounds__(kExpandThreads) expand_emit_kernel(const __grid_constant__ ExpandArgs a,
+                                                                     const uint32_t *__restrict__ block_offsets,
+                                                                     uint32_t *__restrict__ list, uint32_t capacity)
+{
+	__shared__ uint32_t s_warp[32];
+	__shared__ uint32_t s_total;
+	__shared__ uint32_t s_out[kExpandThreads * 32];
+	const uint32_t seg = segment_of(a, blockIdx.x);
+	const uint32_t *__restrict__ words = a.words[seg];
+	const uint32_t n_words = a.n_words[seg];
+	const uint32_t wblock = (blockIdx.x - a.first_block[seg]) * kExpandWordsPerBlock;
+	uint32_t out = block_offsets[blockIdx.x];
+	uint32_t w[4];
+#pragma unroll
+	for(int k = 0; k < 4; k++)
+	{
+		const uint32_t wi = wblock + k * kExpandThreads + threadIdx.x;
+		w[k] = wi < n_words ? __ldg(words + wi) : 0u;
+	}
+#pragma unroll
+	for(int k = 0; k < 4; k++)
+	{
+		uint32_t bits = w[k];
+		uint32_t pos = block_exclusive_scan(__popc(bits), s_warp, &s_total);
+		const uint32_t r0 = a.rank_base[seg] + (wblock + k * kExpandThreads + threadIdx.x) * 32u;
+		while(bits)
+		{
+			s_out[pos++] = r0 + __ffs(bits) - 1u;
+			bits &= bits - 1u;
+		}
+		__syncthreads();
+		const uint32_t total = s_total;
+		for(uint32_t j = threadIdx.x; j < total; j += kExpandThreads)
+			if(out + j < capacity) __stcs(list + out + j, s_out[j]);
+		out += total;
+		__syncthreads();
+	}
+}
+
+} // namespace rn
+
+using namespace rn;
+
+static inline uint32_t mask_words(const rn_scene *s) { return (s->n + 31u) / 32u; }
+
+extern "C" int rn_cull_build_masks(rn_scene_t *s, void *cuda_stream)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_build_masks needs a cull");
+	RN_CUDA(cudaSetDevice(s->device));
+	if(!s->rank_masks)
+	{
+		const size_t cap_words = ((size_t)s->desc.max_nodes + 31) / 32;
+		int rc = dev_alloc(s, &s->rank_masks, cap_words * RN_MAX_CAMERAS);
+		if(rc) return rc;
+	}
+	s->have_masks = false;
+	if(s->n == 0)
+		return RN_OK;
+	const uint32_t words = mask_words(s);
+	const uint32_t warps = (words + 31) / 32;
+	const uint32_t grid = (warps + kMaskThreads / 32 - 1) / (kMaskThreads / 32);
+	rank_mask_kernel<<<grid, kMaskThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(s->vis, s->d_slot_of_rank, s->n, words,
+	                                                                                   s->last_ncams, s->rank_masks);
+	RN_CUDA(cudaGetLastError());
+	s->launches++;
+	s->have_masks = true;
+	s->mask_ncams = s->last_ncams;
+	return RN_OK;
+}
+
+extern "C" int rn_cull_device_masks(rn_scene_t *s, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	if(masks) *masks = s->have_masks ? s->rank_masks : nullptr;
+	if(words_per_camera) *words_per_camera = mask_words(s);
+	if(n_cameras) *n_cameras = s->have_masks ? s->mask_ncams : 0;
+	return RN_OK;
+}
+
+extern "C" int rn_cull_read_masks_async(rn_scene_t *s, uint32_t n_cameras, uint32_t *out_words, void *cuda_stream)
+{
+	RN_REQUIRE(s && out_words, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(s->have_masks, RN_ERR_STATE, "no masks: run rn_cull_build_masks after the cull");
+	RN_REQUIRE(n_cameras <= s->mask_ncams, RN_ERR_INVALID, "%u cameras asked, the masks hold %u", n_cameras, s->mask_ncams);
+	RN_CUDA(cudaSetDevice(s->device));
+	// the camera rows are contiguous on both sides: one copy
+	RN_CUDA(cudaMemcpyAsync(out_words, s->rank_masks, (size_t)n_cameras * mask_words(s) * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+	                        static_cast<cudaStream_t>(cuda_stream)));
+	return RN_OK;
+}
+
+extern "C" int rn_masks_expand(rn_scene_t *s, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
+                               uint32_t capacity, uint32_t *device_count, void *cuda_stream)
+{
+	RN_REQUIRE(s && (segments || n_segments == 0) && device_list && device_count, RN_ERR_INVALID, "NULL argument");
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	// at most 32 segments per launch set; longer inputs continue on the running device-side count
+	for(uint32_t s0 = 0; s0 < n_segments; s0 += kExpandMaxSegments)
+	{
+		ExpandArgs a;
+		memset(&a, 0, sizeof(a));
+		uint32_t n_blocks = 0;
+		for(uint32_t k = s0; k < std::min(n_segments, s0 + kExpandMaxSegments); k++)
+		{
+			if(segments[k].n_words == 0)
+				continue;
+			RN_REQUIRE(segments[k].device_words, RN_ERR_INVALID, "segment %u: NULL words", k);
+			const uint32_t q = a.n_segments++;
+			a.words[q] = segments[k].device_words;
+			a.n_words[q] = segments[k].n_words;
+			a.rank_base[q] = segments[k].rank_base;
+			a.first_block[q] = n_blocks;
+			n_blocks += (segments[k].n_words + kExpandWordsPerBlock - 1) / kExpandWordsPerBlock;
+			a.first_block[q + 1] = n_blocks;
+		}
+		if(n_blocks == 0)
+			continue;
+		if(n_blocks > s->expand_blocks_cap)
+		{
+			// grows only; cudaFree synchronises, so no kernel of an earlier call still reads the old buffer
+			if(s->expand_totals)
+			{
+				RN_CUDA(cudaFree(s->expand_totals));
+				s->device_bytes -= (uint64_t)s->expand_blocks_cap * sizeof(uint32_t);
+				s->expand_totals = nullptr;
+				s->expand_blocks_cap = 0;
+			}
+			const uint32_t cap = std::max(n_blocks, 4096u);
+			int rc = dev_alloc(s, &s->expand_totals, cap);
+			if(rc) return rc;
+			s->expand_blocks_cap = cap;
+		}
+		expand_count_kernel<<<n_blocks, kExpandThreads, 0, stream>>>(a, s->expand_totals);
+		expand_scan_kernel<<<1, kExpandThreads, 0, stream>>>(s->expand_totals, n_blocks, device_count);
+		expand_emit_kernel<<<n_blocks, kExpandThreads, 0, stream>>>(a, s->expand_totals, device_list, capacity);
+		RN_CUDA(cudaGetLastError());
+		s->launches += 3;
+	}
+	return RN_OK;
+}

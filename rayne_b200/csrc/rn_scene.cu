@@ -1363,6 +1363,7 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	s->rank_of_slot.swap(t.rank_of_slot);
 	s->have_world = false;
 	s->last_ncams = 0;
+	s->have_masks = false;
 	return RN_OK;
 }
 
@@ -1496,6 +1497,7 @@ static int cull_stored(rn_scene *s, const rn_camera_frustum *cameras, uint32_t n
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->last_ncams = n_cameras;
+	s->have_masks = false;
 	for(uint32_t c = 0; c < n_cameras; c++) s->last_cam_flags[c] = cameras[c].flags;
 	fill_lists(s, n_cameras, out_lists);
 	return RN_OK;
@@ -1545,6 +1547,7 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	s->have_world = true;
 	s->have_bounds = false;
 	s->last_ncams = n_cameras;
+	s->have_masks = false;
 	for(uint32_t c = 0; c < n_cameras; c++) s->last_cam_flags[c] = cameras[c].flags;
 	fill_lists(s, n_cameras, out_lists);
 	return RN_OK;

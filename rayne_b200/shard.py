@@ -239,3 +239,81 @@ class PipelinedListExchange(ListExchange):
         offs = [sum(sizes[:c]) for c in range(ncam)]
         return [[dst[r * width + offs[c]: r * width + offs[c] + min(int(table[r, c]), sizes[c])] for r in range(world)]
                 for c in range(ncam)]
+
+
+class PipelinedMaskExchange:
+    """The exchange in its compact form: instead of the lists (4 B per visible node and camera, 61 MB per GPU for the
+    benchmark frame) every rank ships the rank-order visibility bitmasks of its range (rn_cull_build_masks: one bit
+    per node and camera, 12.6 MB) - the same information, since a list of the cull loop is the ascending sequence of
+    the ranks that passed.  Sizes are static (fixed by the shard plan), so there is no counts table, no size
+    prediction and no overflow: ONE fixed-size all_gather_into_tensor per frame on a side stream, ``depth`` frames in
+    flight, no host synchronisation.  The consumer expands the cameras it needs with rn_masks_expand
+    (``expand``), rank range after rank range, which reproduces the single-scene list bit for bit.
+
+    words_per_rank[r] = ceil(nodes of rank r / 32); every rank contributes ncams rows padded to the largest."""
+
+    def __init__(self, words_per_rank, ncams: int, group=None, cuda: bool = True, depth: int = 2):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.group = torch, dist, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert len(words_per_rank) == self.world
+        self.words_per_rank = [int(w) for w in words_per_rank]
+        self.row = max(self.words_per_rank)            # padded words per camera
+        self.ncams = int(ncams)
+        self.cuda = cuda
+        self.side = torch.cuda.Stream() if cuda else None
+        self.depth = max(1, depth)
+        self.pending = []
+        self.result = None
+        self._bufs = [None] * (self.depth + 1)        # gathered buffers, recycled round robin
+        self._send = [None] * (self.depth + 1)
+        self._frame = 0
+
+    def submit(self, masks):
+        """masks: int32 tensor [ncams * words_local] (camera rows one behind the other, the library's buffer)."""
+        torch = self.torch
+        wl = self.words_per_rank[self.rank]
+        k = self._frame % len(self._bufs)
+        self._frame += 1
+        while len(self.pending) > self.depth - 1:      # the buffers of frame i-depth are free again
+            self._retire_one(self.pending.pop(0))
+        if self._send[k] is None:
+            self._send[k] = torch.zeros(self.ncams * self.row, dtype=masks.dtype, device=masks.device)
+            self._bufs[k] = torch.empty(self.world * self.ncams * self.row, dtype=masks.dtype, device=masks.device)
+        send, dst = self._send[k], self._bufs[k]
+        # snapshot on the producing stream (the next cull overwrites the library's buffer), padded rows
+        send.view(self.ncams, self.row)[:, :wl].copy_(masks.view(self.ncams, wl))
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(ev)
+                self.dist.all_gather_into_tensor(dst, send, group=self.group)
+                done = torch.cuda.Event()
+                done.record()
+        else:
+            self.dist.all_gather_into_tensor(dst, send, group=self.group)
+            done = None
+        self.pending.append((done, dst))
+
+    def _retire_one(self, item):
+        done, dst = item
+        if done is not None:
+            self.torch.cuda.current_stream().wait_event(done)   # device-side order only; the host does not block
+        self.result = dst
+
+    def flush(self):
+        """Current stream waits for every outstanding gather; returns the newest gathered buffer
+        [world, ncams, row] (rank r's words of camera c: result[r, c, :words_per_rank[r]])."""
+        while self.pending:
+            self._retire_one(self.pending.pop(0))
+        return None if self.result is None else self.result.view(self.world, self.ncams, self.row)
+
+    def expand(self, handle, gathered, camera: int, starts, out_list, out_count, stream: int = 0):
+        """rn_masks_expand over the rank ranges in order: out_list (int32 device tensor) receives camera's global list,
+        out_count (int32 device tensor [1], zeroed here) its length.  starts[r] = first global rank of rank r."""
+        out_count.zero_()
+        segs = [(gathered[r, camera].data_ptr(), self.words_per_rank[r], int(starts[r])) for r in range(self.world)]
+        handle.masks_expand(segs, out_list.data_ptr(), out_list.numel(), out_count.data_ptr(), stream)

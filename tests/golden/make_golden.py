@@ -47,7 +47,7 @@ def main() -> None:
         if scene.box is not None:
             cams = np.concatenate([cams, sort_cameras()])
         opts = refio.OPT_INVERSE | (refio.OPT_BOX if scene.box is not None else 0)
-        ref = refio.run_scene(scene, cams, options=opts)
+        ref = refio.run_scene(scene, cams, options=opts | refio.OPT_INSTANCES)
         out = {f"in_{k}": getattr(scene, k) for k in SCENE_COLS}
         if scene.box is not None:
             out["in_box"] = scene.box
@@ -56,6 +56,9 @@ def main() -> None:
             out[f"ref_{k}"] = ref[k]
         for c, lst in enumerate(ref["lists"]):
             out[f"ref_list{c}"] = lst
+        # per camera GetViewMatrix and projection * view; for camera 0 view * world and projView * world of every node
+        for k in ("view", "projview", "mv", "mvp"):
+            out[f"ref_{k}"] = ref[k]
         # the same scene through SceneWithVisibilityLists (default volume): A10 order + its lists
         vis = refio.run_scene(scene, cams, options=opts | refio.OPT_VISLISTS)
         out["ref_vis_order"] = vis["order"]

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from oracle import oracle, refio
-from rayne_b200 import scenegen as sg
+from rayne_b200 import capi, scenegen as sg
 from tests.helpers import same_floats, same_list_mod_ties, standard_cameras, load_golden_scene, GOLDEN_DIR
 
 SCENE_FIXTURES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "scene_*.npz")))
@@ -38,6 +38,21 @@ def test_oracle_scene_matches_golden(name):
     for c in range(len(cams)):
         ftb = bool(int(cams[c]["flags"]) & (1 << 6))
         assert same_list_mod_ties(o["lists"][c], g[f"ref_list{c}"], scene.priority, ftb), f"camera {c}"
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_oracle_instance_matrices_match_golden(name):
+    """Camera view / projection * view and the per-drawable products view * world, projView * world, bit-exact
+    against the reference's Camera and Matrix classes; the host side of the library (rn_camera_build_matrices) too."""
+    scene, cams, g = load_golden_scene(name)
+    v, _, pv = oracle.camera_matrices(cams)
+    assert same_floats(v, g["ref_view"]) and same_floats(pv, g["ref_projview"])
+    lv, _, lpv = capi.build_camera_matrices(cams)
+    assert same_floats(lv, g["ref_view"]) and same_floats(lpv, g["ref_projview"])
+    ids = np.arange(scene.n, dtype=np.uint32)
+    inst = oracle.instances(ids, g["ref_wmat"], g["ref_winv"], v[0], pv[0])
+    assert same_floats(inst[:, 0:16], g["ref_wmat"]) and same_floats(inst[:, 16:32], g["ref_winv"])
+    assert same_floats(inst[:, 32:48], g["ref_mv"]) and same_floats(inst[:, 48:64], g["ref_mvp"])
 
 
 @pytest.mark.parametrize("name", SCENE_FIXTURES)

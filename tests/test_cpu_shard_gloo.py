@@ -94,8 +94,28 @@ def _worker(rank: int, world: int, port: int, q):
         table, outs, sizes = pex.flush()
         frames.append((table.numpy().copy(), pex.overflows))
         pmerged = [torch.cat(v).numpy().astype(np.uint32) for v in shard.PipelinedListExchange.views((table, outs, sizes), world)]
+        # the compact exchange: rank-order bitmasks of the local range (what rn_cull_build_masks leaves), static sizes,
+        # two frames in flight; frame 0 = empty masks, frames 1 and 2 = the real ones
+        words = [(e - s + 31) // 32 for s, e in ranges]
+        bits = np.zeros((len(fr), words[rank] * 32), np.uint8)
+        for c, l in enumerate(local):
+            bits[c, l] = 1
+        mask = np.packbits(bits, axis=1, bitorder="little").view(np.uint32).reshape(-1)
+        mex = shard.PipelinedMaskExchange(words, len(fr), cuda=False, depth=2)
+        mex.submit(torch.zeros(mask.shape[0], dtype=torch.int32))
+        first = mex.flush().clone()
+        mex.submit(torch.from_numpy(mask.view(np.int32)))
+        mex.submit(torch.from_numpy(mask.view(np.int32)))
+        g = mex.flush().numpy().view(np.uint32)
+        mmerged = []
+        for c in range(len(fr)):
+            parts = []
+            for r, (s, e) in enumerate(ranges):
+                seg = np.unpackbits(np.ascontiguousarray(g[r, c, :words[r]]).view(np.uint8), bitorder="little")
+                parts.append(np.nonzero(seg)[0].astype(np.uint32) + np.uint32(s))
+            mmerged.append(np.concatenate(parts))
         if rank == 0:
-            q.put((all_counts.numpy(), merged, ranges, frames, pmerged, sizes))
+            q.put((all_counts.numpy(), merged, ranges, frames, pmerged, sizes, mmerged, int(first.abs().sum())))
     finally:
         dist.destroy_process_group()
 
@@ -108,7 +128,7 @@ def test_two_rank_exchange_matches_single_process():
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    all_counts, merged, ranges, frames, pmerged, sizes = q.get(timeout=300)
+    all_counts, merged, ranges, frames, pmerged, sizes, mmerged, first_sum = q.get(timeout=300)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -121,6 +141,10 @@ def test_two_rank_exchange_matches_single_process():
         want_ranks = rs.rank_of[ref["lists"][c]]            # creation ids -> global ranks, already ascending
         assert np.array_equal(merged[c], want_ranks), f"camera {c}"
         assert int(all_counts[:, c].sum()) == len(want_ranks)
+    # bitmask exchange: gathered masks expand to exactly the single-process lists
+    assert first_sum == 0
+    for c in range(len(cams)):
+        assert np.array_equal(mmerged[c], rs.rank_of[ref["lists"][c]]), f"camera {c} (masks)"
     # pipelined exchange: tables arrive one frame late and equal the submitted counts; the third frame was sized from
     # the halved counts of the second one with no margin -> flagged as an overflow, its lists cut at `sizes`
     assert np.array_equal(frames[0][0], all_counts) and frames[0][1] == 0

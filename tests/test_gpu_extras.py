@@ -229,3 +229,70 @@ def test_particle_mesh_matches_golden_and_oracle():
             for key in ("mesh_pos", "mesh_color", "mesh_uv0", "mesh_uv1"):
                 assert same_floats(m[key][:live], ref[key][:live]), (k, key)
             assert np.array_equal(m["mesh_idx"], ref["mesh_idx"])
+
+
+def _pack(h, camera, view, projview, count, capacity):
+    import torch
+    buf = torch.full((capacity + 2, 64), float("nan"), dtype=torch.float32, device="cuda")
+    h.pack_instances(camera, view, projview, buf.data_ptr(), capacity)
+    torch.cuda.synchronize()
+    got = buf.cpu().numpy()
+    assert np.isnan(got[min(count, capacity):]).all(), "wrote past min(count, capacity)"
+    return got[:min(count, capacity)]
+
+
+@pytest.mark.parametrize("name", SCENE_FIXTURES)
+def test_instance_records_match_golden(name):
+    """§8(f) drawable uniform packing: per list entry model, inverse model, view * model, projView * model - bit-exact
+    against the products the reference's Matrix class gives for camera 0 of the fixture."""
+    scene, cams, g = load_golden_scene(name)
+    rs = capi.RankedScene(scene)
+    fr = capi.build_frustums(cams[:capi.RN_MAX_CAMERAS])
+    v, _, pv = capi.build_camera_matrices(cams)
+    assert same_floats(v, g["ref_view"]) and same_floats(pv, g["ref_projview"])
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        h.transform_cull(fr)
+        with pytest.raises(capi.RNError):
+            _pack(h, 0, v[0], pv[0], 0, 4)           # inverse matrices not computed yet: loud
+        h.transform_inverse()
+        lst = h.read_list(0)
+        ids = rs.order[h.download(capi.DL_RANK_OF_SLOT)[lst]]
+        got = _pack(h, 0, v[0], pv[0], len(lst), scene.n)
+        assert len(got) == len(lst) > 0
+        assert same_floats(got[:, 0:16], g["ref_wmat"][ids]) and same_floats(got[:, 16:32], g["ref_winv"][ids])
+        assert same_floats(got[:, 32:48], g["ref_mv"][ids]) and same_floats(got[:, 48:64], g["ref_mvp"][ids])
+        # a buffer smaller than the list: the first `capacity` entries, nothing behind them
+        half = _pack(h, 0, v[0], pv[0], len(lst), len(lst) // 2)
+        assert same_floats(half, got[:len(lst) // 2])
+        with pytest.raises(capi.RNError):
+            h.pack_instances(len(fr), v[0], pv[0], 256, 1)
+
+
+@pytest.mark.parametrize("rank_mode", [False, True])
+def test_instance_records_match_oracle_after_sort(rank_mode):
+    """Records follow the list order left by rn_cull_sort, in slot and in rank list mode, for every camera."""
+    scene = sg.make_scene(n_trees=4, branching=5, depth=7, seed=12, nonuniform_scale=True, random_bounds=True,
+                          priorities=True, transparent_frac=0.2)
+    cams = np.concatenate([standard_cameras()[:2], sort_cameras()])[:capi.RN_MAX_CAMERAS]
+    fr = capi.build_frustums(cams)
+    fr["flags"] |= sg.CAM_DEFAULTS
+    v, _, pv = capi.build_camera_matrices(cams)
+    ov, _, opv = oracle.camera_matrices(cams)
+    assert same_floats(v, ov) and same_floats(pv, opv)
+    ref = oracle.scene_reference(scene, oracle.frustums(cams), cameras=cams)
+    rs = capi.RankedScene(scene)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        if rank_mode:
+            h.set_list_mode(True, 77)
+        h.transform_cull(fr)
+        h.transform_inverse()
+        h.cull_sort(cams["pos"])
+        ros = h.download(capi.DL_RANK_OF_SLOT)
+        for c in range(len(cams)):
+            lst = h.read_list(c)
+            ids = rs.order[lst - 77] if rank_mode else rs.order[ros[lst]]
+            want = oracle.instances(ids, ref["wmat"], ref["winv"], ov[c], opv[c])
+            got = _pack(h, c, v[c], pv[c], len(lst), len(lst) + 5)
+            assert same_floats(got, want), f"camera {c}"
