@@ -327,6 +327,10 @@ class SceneHandle:
             stream_synchronize(stream)
         return out
 
+    def read_masks_into(self, host_ptr: int, n_cameras: int, stream: int = 0) -> None:
+        """rn_cull_read_masks_async into raw (pinned) host memory; the caller synchronises the stream."""
+        _check(self.lib.rn_cull_read_masks_async(self._h, C.c_uint32(n_cameras), C.c_void_p(host_ptr), C.c_void_p(stream)))
+
     def masks_expand(self, segments, device_list: int, capacity: int, device_count: int, stream: int = 0) -> None:
         """segments: iterable of (device pointer of the words, n_words, rank_base), expanded in order."""
         segs = (MaskSegment * max(len(segments), 1))()

@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(SortView v, Pas
 	h[threadIdx.x] = 0;
 	__syncthreads();
 	const uint32_t base = blockIdx.x * kSortTile;
-	const uint32_t *keys = v.keys[a.src], *vals = v.vals[a.src];
+	const uint32_t *keys = a.src ? v.keys[1] : v.keys[0], *vals = a.src ? v.vals[1] : v.vals[0];
 #pragma unroll
 	for(uint32_t i = 0; i < kSortItems; i++)
 	{
@@ -207,8 +207,9 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		dbase[threadIdx.x] = before + s - x + v.hist[(size_t)threadIdx.x * v.nb_max + blockIdx.x];
 	}
 	__syncthreads();
-	const uint32_t *keys = v.keys[a.src], *vals = v.vals[a.src];
-	uint32_t *okeys = v.keys[a.src ^ 1u], *ovals = v.vals[a.src ^ 1u];
+	// selects, not v.keys[a.src]: a dynamically indexed kernel parameter is copied to local memory by every thread
+	const uint32_t *keys = a.src ? v.keys[1] : v.keys[0], *vals = a.src ? v.vals[1] : v.vals[0];
+	uint32_t *okeys = a.src ? v.keys[0] : v.keys[1], *ovals = a.src ? v.vals[0] : v.vals[1];
 	// warp w owns entries [w*256, (w+1)*256) of the block, 32 consecutive entries per round: stable inside the warp
 	const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32u);
 	uint32_t key[kSortItems], val[kSortItems], dig[kSortItems], rank[kSortItems];
@@ -262,7 +263,7 @@ __global__ void __launch_bounds__(256) sort_writeback_kernel(SortView v, uint32_
 	const uint32_t begin = v.range[0], end = v.range[1];
 	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
 	if(e < end - begin)
-		v.list[begin + e] = v.vals[src][e];
+		v.list[begin + e] = (src ? v.vals[1] : v.vals[0])[e];
 }
 
 static int run_passes(rn_scene *s, const SortView &v, bool with_priority_digit, cudaStream_t stream)

@@ -91,6 +91,35 @@ class PipelinedScene:
         self.ncams = fr.shape[0]
         return self.read_lists_into(out_ptrs, capacities)
 
+    def frame_masks(self, frustums: np.ndarray, out_ptr: int, dirty_ranks=None, position=None, scale=None,
+                    rotation=None) -> None:
+        """The same frame with the visibility read back in its compact form: per range the rank-order bitmasks of
+        every view (rn_cull_build_masks), copied to host memory at out_ptr + 4 * mask_offsets[k] as [views, words_k]
+        (mask_layout()).  Bit b of word w of range k = global rank ranges[k][0] + 32 w + b.  Blocks until the last
+        copy has finished."""
+        parts = self._split(dirty_ranks) if dirty_ranks is not None else [None] * len(self.handles)
+        fr = np.ascontiguousarray(np.atleast_1d(frustums), dtype=capi.FRUSTUM_DTYPE)
+        offs, _ = self.mask_layout(fr.shape[0])
+        for k, (part, h, st) in enumerate(zip(parts, self.handles, self.streams)):
+            if part is not None and part[0].shape[0]:
+                sel, local = part
+                pick = lambda a: None if a is None else np.ascontiguousarray(a[sel])
+                h.update_nodes(local, position=pick(position), scale=pick(scale), rotation=pick(rotation), stream=st)
+            h.transform_cull(fr, st)
+            h.build_masks(st)
+            h.read_masks_into(int(out_ptr) + 4 * offs[k], fr.shape[0], st)
+        self.ncams = fr.shape[0]
+        for st in self.streams:
+            capi.stream_synchronize(st)
+
+    def mask_layout(self, n_views: int):
+        """(word offset of every range's block in the host buffer, total words) for frame_masks."""
+        offs, total = [], 0
+        for a, b in self.ranges:
+            offs.append(total)
+            total += n_views * ((b - a + 31) // 32)
+        return offs, total
+
     def read_lists_into(self, out_ptrs: list[int], capacities: list[int]) -> np.ndarray:
         """Per camera one host buffer (pinned for an asynchronous copy): the ranges' lists land one behind the other.
         Returns the total count per camera.  Blocks until the last copy has finished."""
