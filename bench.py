@@ -392,7 +392,7 @@ def run_ours(args) -> dict:
         for k, (a, b) in enumerate(pipe.ranges):
             w = (b - a + 31) // 32
             blk = mk[offs[k]: offs[k] + ncam * w].reshape(ncam, w)
-            pop += np.unpackbits(blk.view(np.uint8), axis=1).sum(axis=1)
+            pop += np.unpackbits(blk.view(np.uint8), axis=1).sum(axis=1, dtype=np.int64)
         e2e_masks = {"value": n / mms / 1e3, "unit": "Mnodes/s", "ms_per_step": mms,
                      "h2d_bytes_per_step": int(roots.shape[0] * 16), "d2h_bytes_per_step": int(total_words * 4),
                      "what": "as e2e, but rn_cull_build_masks + rn_cull_read_masks_async: the views' visibility as "

@@ -182,7 +182,11 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 {
 	__shared__ uint32_t wcount[kSortWarps][256];
 	__shared__ uint32_t dbase[256];
+	__shared__ uint32_t lpre[256];
 	__shared__ uint32_t wsum[8];
+	__shared__ uint32_t s_valid;
+	__shared__ uint32_t s_key[kSortTile], s_val[kSortTile];
+	__shared__ uint8_t s_dig[kSortTile];
 	const uint32_t m = v.range[1] - v.range[0];
 	const uint32_t nb = (m + kSortTile - 1) / kSortTile;
 	if(blockIdx.x >= nb)
@@ -234,26 +238,57 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		__syncwarp();
 	}
 	__syncthreads();
-	// per digit: exclusive prefix over the warps (thread = digit)
-	{
-		uint32_t run = 0;
+	// per digit: exclusive prefix over the warps (thread = digit); `run` ends as the digit's total in this block
+	uint32_t run = 0;
 #pragma unroll
-		for(uint32_t w = 0; w < kSortWarps; w++)
+	for(uint32_t w = 0; w < kSortWarps; w++)
+	{
+		const uint32_t t = wcount[w][threadIdx.x];
+		wcount[w][threadIdx.x] = run;
+		run += t;
+	}
+	// block-local exclusive prefix over the digits: where a digit's run starts in the reordered tile
+	{
+		uint32_t sc = run;
+#pragma unroll
+		for(int o = 1; o < 32; o <<= 1)
 		{
-			const uint32_t t = wcount[w][threadIdx.x];
-			wcount[w][threadIdx.x] = run;
-			run += t;
+			const uint32_t y = __shfl_up_sync(0xffffffffu, sc, o);
+			if(lane >= (uint32_t)o) sc += y;
 		}
+		if(lane == 31) wsum[warp] = sc;
+		__syncthreads();
+		uint32_t before = 0;
+		for(uint32_t w = 0; w < warp; w++) before += wsum[w];
+		lpre[threadIdx.x] = before + sc - run;
+		if(threadIdx.x == kSortThreads - 1) s_valid = before + sc;
 	}
 	__syncthreads();
+	// reorder through shared memory, then write digit runs with consecutive threads on consecutive addresses
+	// (a thread-per-entry scatter leaves 32 partial sectors per store instruction)
 #pragma unroll
 	for(uint32_t r = 0; r < kSortItems; r++)
 	{
 		if(dig[r] != 0xffffu)
 		{
-			const uint32_t dst = dbase[dig[r]] + wcount[warp][dig[r]] + rank[r];
-			okeys[dst] = key[r];
-			ovals[dst] = val[r];
+			const uint32_t lp = lpre[dig[r]] + wcount[warp][dig[r]] + rank[r];
+			s_key[lp] = key[r];
+			s_val[lp] = val[r];
+			s_dig[lp] = (uint8_t)dig[r];
+		}
+	}
+	__syncthreads();
+	const uint32_t n_valid = s_valid;
+#pragma unroll
+	for(uint32_t r = 0; r < kSortItems; r++)
+	{
+		const uint32_t idx = r * kSortThreads + threadIdx.x;
+		if(idx < n_valid)
+		{
+			const uint32_t d = s_dig[idx];
+			const uint32_t dst = dbase[d] + (idx - lpre[d]);
+			okeys[dst] = s_key[idx];
+			ovals[dst] = s_val[idx];
 		}
 	}
 }
