@@ -471,6 +471,11 @@ def run_ours(args) -> dict:
             ms = timed(lambda: h.particles_build_mesh(stream=stream))
             extras["particles_build_mesh"] = {"ms": ms, "bytes_per_particle": 236,
                                               "roofline_frac": particles["live_per_gpu"] * 236.0 / (ms * 1e-3) / 1e9 / peak}
+            # vertex stage of Shaders/Particles.hlsl over that mesh: 36 B read + 32 B written per vertex
+            ident = np.tile(np.eye(4, dtype=np.float32).reshape(16), (args.emitters, 1))
+            ms = timed(lambda: h.particles_expand_billboards(ident, ident, stream=stream))
+            extras["particles_expand_billboards"] = {"ms": ms, "bytes_per_particle": 272,
+                                                     "roofline_frac": particles["live_per_gpu"] * 272.0 / (ms * 1e-3) / 1e9 / peak}
     if world > 1:
         torch.cuda.synchronize()
         dist.barrier()

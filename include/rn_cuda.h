@@ -350,6 +350,24 @@ int rn_particles_build_mesh(rn_scene_t *scene, const float *world_scale_x, const
 int rn_particles_download_mesh(rn_scene_t *scene, uint32_t emitter, float *position, float *color, float *uv0, float *uv1,
                                uint16_t *indices);
 
+/* The vertex stage of the reference's particle shader (Shaders/Particles.hlsl:52-71, `particles_vertex`) for every
+ * vertex of the live quads of the mesh left by rn_particles_build_mesh:
+ *   clip = modelViewProjection * (float4(position, 1) + inverseModelView * float4(texCoords2, 0, 0)),
+ *   colour = colour * cameraAmbientColor.
+ * inverse_model_view / model_view_projection: 16 floats PER EMITTER (column-major, as Rayne uploads them: each emitter
+ * is a SceneNode with its own model matrix); ambient_color: 4 floats.  Output: headless device arrays, 4 + 4 floats per
+ * vertex (vertices of dead slots stay zero).  The shader itself cannot run here (no graphics stack); parity is against
+ * its C restatement in the oracle. */
+typedef struct rn_particle_clip {
+	const float *clip_position;   /* device, 4 floats per vertex */
+	const float *color;           /* device, 4 floats per vertex */
+	uint32_t     vertex_stride_per_emitter;
+	uint32_t     reserved;
+} rn_particle_clip;
+int rn_particles_expand_billboards(rn_scene_t *scene, const float *inverse_model_view, const float *model_view_projection,
+                                   const float *ambient_color, rn_particle_clip *out, void *cuda_stream);
+int rn_particles_download_clip(rn_scene_t *scene, uint32_t emitter, float *clip_position, float *color);
+
 /* ---- introspection for the bench / tests ---------------------------------------------------------------- */
 typedef struct rn_scene_stats {
 	uint32_t nodes, tiles, spine_nodes, spine_levels, max_depth, tile_nodes;

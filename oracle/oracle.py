@@ -140,6 +140,18 @@ def instances(ids, wmat, winv, view, projview) -> np.ndarray:
     return out
 
 
+def billboards(pos, color, uv1, inv_mv, mvp, ambient):
+    """Shaders/Particles.hlsl particles_vertex for n vertices: (clip [n, 4], colour [n, 4])."""
+    pos = np.ascontiguousarray(pos, np.float32); color = np.ascontiguousarray(color, np.float32)
+    uv1 = np.ascontiguousarray(uv1, np.float32)
+    inv_mv = np.ascontiguousarray(inv_mv, np.float32); mvp = np.ascontiguousarray(mvp, np.float32)
+    ambient = np.ascontiguousarray(ambient, np.float32)
+    n = pos.shape[0]
+    clip = np.zeros((n, 4), np.float32); col = np.zeros((n, 4), np.float32)
+    load().rn_oracle_billboards(C.c_uint32(n), _p(pos), _p(color), _p(uv1), _p(inv_mv), _p(mvp), _p(ambient), _p(clip), _p(col))
+    return clip, col
+
+
 def camera_matrices(cameras: np.ndarray):
     """(view, projection, proj_view) per camera, each [V, 16]."""
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)

@@ -938,3 +938,27 @@ void rn_oracle_instances(uint32_t count, const uint32_t *ids, const float *wmat,
 		memcpy(o + 48, p.m, 64);
 	}
 }
+
+/* Vertex stage of the reference's particle shader, Shaders/Particles.hlsl:52-71 (particles_vertex), restated:
+ *   clip = modelViewProjection * (float4(position, 1) + inverseModelView * float4(texCoords2, 0, 0)); colour * ambient.
+ * HLSL's mul(M, v) with Rayne's column-major upload is the ordinary M * v; the order of the additions inside a
+ * compiled shader is not defined by the source - this restatement sums left to right.  UNPINNED: the shader cannot
+ * be executed here (no graphics stack), so no reference output exists for it. */
+void rn_oracle_billboards(uint32_t n_vertices, const float *pos, const float *color, const float *uv1, const float *inv_mv,
+                          const float *mvp, const float *ambient, float *clip_out, float *color_out)
+{
+	for(uint32_t v = 0; v < n_vertices; v++)
+	{
+		float tx = uv1[v * 2], ty = uv1[v * 2 + 1];
+		float p[4];
+		for(int i = 0; i < 4; i++)
+		{
+			float base = i < 3 ? pos[v * 3 + i] : 1.0f;
+			p[i] = base + (inv_mv[i] * tx + inv_mv[4 + i] * ty);
+		}
+		for(int i = 0; i < 4; i++)
+			clip_out[v * 4 + i] = mvp[i] * p[0] + mvp[4 + i] * p[1] + mvp[8 + i] * p[2] + mvp[12 + i] * p[3];
+		for(int i = 0; i < 4; i++)
+			color_out[v * 4 + i] = color[v * 4 + i] * ambient[i];
+	}
+}

@@ -32,6 +32,7 @@ EXPORTS = [
     "rn_transform_inverse", "rn_bounds_update", "rn_scene_device_extras", "rn_cull_sort",
     "rn_scenevis_default_volume_order", "rn_particles_build_mesh", "rn_particles_download_mesh",
     "rn_cull_pack_instances", "rn_camera_build_matrices",
+    "rn_particles_expand_billboards", "rn_particles_download_clip",
     "rn_cull_build_masks", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
@@ -57,6 +58,11 @@ class NodeColumns(C.Structure):
 class ParticleMesh(C.Structure):
     _fields_ = [("position", C.c_void_p), ("color", C.c_void_p), ("uv0", C.c_void_p), ("uv1", C.c_void_p),
                 ("indices", C.c_void_p), ("vertex_stride_per_emitter", C.c_uint32), ("index_stride_per_emitter", C.c_uint32)]
+
+
+class ParticleClip(C.Structure):
+    _fields_ = [("clip_position", C.c_void_p), ("color", C.c_void_p), ("vertex_stride_per_emitter", C.c_uint32),
+                ("reserved", C.c_uint32)]
 
 
 class MaskSegment(C.Structure):
@@ -419,6 +425,21 @@ class SceneHandle:
                "mesh_idx": np.zeros(max_particles * 6, np.uint16)}
         _check(self.lib.rn_particles_download_mesh(self._h, emitter, _ptr(out["mesh_pos"]), _ptr(out["mesh_color"]),
                                                    _ptr(out["mesh_uv0"]), _ptr(out["mesh_uv1"]), _ptr(out["mesh_idx"])))
+        return out
+
+    def particles_expand_billboards(self, inverse_model_view: np.ndarray, model_view_projection: np.ndarray,
+                                    ambient=(1.0, 1.0, 1.0, 1.0), stream: int = 0) -> "ParticleClip":
+        """rn_particles_expand_billboards; matrices [n_emitters, 16] column-major."""
+        im = _f32(inverse_model_view).reshape(self.n_emitters, 16)
+        mvp = _f32(model_view_projection).reshape(self.n_emitters, 16)
+        amb = _f32(ambient).reshape(4)
+        out = ParticleClip()
+        _check(self.lib.rn_particles_expand_billboards(self._h, _ptr(im), _ptr(mvp), _ptr(amb), C.byref(out), C.c_void_p(stream)))
+        return out
+
+    def particles_download_clip(self, emitter: int, max_particles: int) -> dict:
+        out = {"clip_pos": np.zeros((max_particles * 4, 4), np.float32), "clip_color": np.zeros((max_particles * 4, 4), np.float32)}
+        _check(self.lib.rn_particles_download_clip(self._h, emitter, _ptr(out["clip_pos"]), _ptr(out["clip_color"])))
         return out
 
     def particles_counts(self) -> tuple[np.ndarray, np.ndarray]:

@@ -62,6 +62,10 @@ struct ParticleStore
 	float *mesh_scale = nullptr;    // per emitter: GetWorldScale().x
 	uint32_t *mesh_flags = nullptr; // per emitter: RN_EMITTER_*
 	bool have_mesh = false;
+	// vertex stage of Shaders/Particles.hlsl (rn_particles_expand_billboards): clip position + colour per vertex
+	float4 *clip_pos = nullptr, *clip_color = nullptr;
+	float *clip_mats = nullptr;     // per emitter: inverse model-view [16], model-view-projection [16]
+	bool have_clip = false;
 };
 
 struct ParticleView
@@ -426,10 +430,53 @@ __global__ void __launch_bounds__(128) particles_mesh_kernel(MeshView mv)
 	idx32[2] = ((b + 1u) & 0xffffu) | (((b + 3u) & 0xffffu) << 16);
 }
 
+// particles_vertex of Shaders/Particles.hlsl:52-71 for every vertex of the live quads:
+//   clip = modelViewProjection * (float4(position, 1) + inverseModelView * float4(texCoords2, 0, 0)),  colour * ambient.
+// Column-major m[16] as Rayne uploads it; products summed left to right, the two zero components of texCoords2 dropped.
+struct BillboardView
+{
+	const float *pos;
+	const float4 *col;
+	const float2 *uv1;
+	const EmitterState *emitters;
+	const float *mats;     // [emitter][32]
+	float4 *clip, *out_col;
+	float4 ambient;
+	uint32_t cap;
+};
+
+__global__ void __launch_bounds__(128) particles_billboard_kernel(BillboardView bv)
+{
+	const uint32_t e = blockIdx.y;
+	const uint32_t vtx = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t maxp = bv.emitters[e].d.max_particles;
+	const uint32_t count = bv.emitters[e].count;
+	const uint32_t stop = count < maxp ? count : maxp;
+	if(vtx >= stop * 4u)
+		return;
+	const size_t v = (size_t)e * bv.cap * 4 + vtx;
+	const float *im = bv.mats + (size_t)e * 32, *mvp = im + 16;
+	const float px = bv.pos[v * 3 + 0], py = bv.pos[v * 3 + 1], pz = bv.pos[v * 3 + 2];
+	const float2 t = bv.uv1[v];
+	const float x = px + (__ldg(im + 0) * t.x + __ldg(im + 4) * t.y);
+	const float y = py + (__ldg(im + 1) * t.x + __ldg(im + 5) * t.y);
+	const float z = pz + (__ldg(im + 2) * t.x + __ldg(im + 6) * t.y);
+	const float w = 1.0f + (__ldg(im + 3) * t.x + __ldg(im + 7) * t.y);
+	float4 c;
+	c.x = __ldg(mvp + 0) * x + __ldg(mvp + 4) * y + __ldg(mvp + 8) * z + __ldg(mvp + 12) * w;
+	c.y = __ldg(mvp + 1) * x + __ldg(mvp + 5) * y + __ldg(mvp + 9) * z + __ldg(mvp + 13) * w;
+	c.z = __ldg(mvp + 2) * x + __ldg(mvp + 6) * y + __ldg(mvp + 10) * z + __ldg(mvp + 14) * w;
+	c.w = __ldg(mvp + 3) * x + __ldg(mvp + 7) * y + __ldg(mvp + 11) * z + __ldg(mvp + 15) * w;
+	bv.clip[v] = c;
+	const float4 k = bv.col[v];
+	bv.out_col[v] = make_float4(k.x * bv.ambient.x, k.y * bv.ambient.y, k.z * bv.ambient.z, k.w * bv.ambient.w);
+}
+
 static void free_store(ParticleStore *p)
 {
 	if(!p) return;
-	void *mesh[] = {p->mesh_pos, p->mesh_color, p->mesh_uv0, p->mesh_uv1, p->mesh_idx, p->mesh_scale, p->mesh_flags};
+	void *mesh[] = {p->mesh_pos, p->mesh_color, p->mesh_uv0, p->mesh_uv1, p->mesh_idx, p->mesh_scale, p->mesh_flags,
+	                p->clip_pos, p->clip_color, p->clip_mats};
 	for(void *q : mesh)
 		if(q) cudaFree(q);
 	for(int g = 0; g < 2; g++)
@@ -713,5 +760,71 @@ extern "C" int rn_particles_download_mesh(rn_scene_t *s, uint32_t emitter, float
 	if(uv0) RN_CUDA(cudaMemcpy(uv0, p->mesh_uv0 + seg * 4, nv * sizeof(float2), cudaMemcpyDeviceToHost));
 	if(uv1) RN_CUDA(cudaMemcpy(uv1, p->mesh_uv1 + seg * 4, nv * sizeof(float2), cudaMemcpyDeviceToHost));
 	if(indices) RN_CUDA(cudaMemcpy(indices, p->mesh_idx + seg * 6, ni * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+	return RN_OK;
+}
+
+extern "C" int rn_particles_expand_billboards(rn_scene_t *s, const float *inverse_model_view, const float *model_view_projection,
+                                              const float *ambient_color, rn_particle_clip *out, void *cuda_stream)
+{
+	RN_REQUIRE(s && inverse_model_view && model_view_projection && ambient_color, RN_ERR_INVALID, "NULL argument");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
+	RN_REQUIRE(p->have_mesh, RN_ERR_STATE, "rn_particles_build_mesh has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	const size_t total = (size_t)s->desc.max_emitters * p->cap * 4;
+	if(!p->clip_pos)
+	{
+		int rc = palloc(s, &p->clip_pos, total);
+		if(!rc) rc = palloc(s, &p->clip_color, total);
+		if(!rc) rc = palloc(s, &p->clip_mats, (size_t)s->desc.max_emitters * 32);
+		if(rc) return rc;
+		RN_CUDA(cudaMemsetAsync(p->clip_pos, 0, total * sizeof(float4), stream));
+		RN_CUDA(cudaMemsetAsync(p->clip_color, 0, total * sizeof(float4), stream));
+	}
+	{
+		// per emitter 2 x 64 bytes of matrices, interleaved; staged copy (pageable host memory)
+		std::vector<float> m((size_t)p->n_emitters * 32);
+		for(uint32_t e = 0; e < p->n_emitters; e++)
+		{
+			memcpy(&m[(size_t)e * 32], inverse_model_view + (size_t)e * 16, 64);
+			memcpy(&m[(size_t)e * 32 + 16], model_view_projection + (size_t)e * 16, 64);
+		}
+		RN_CUDA(cudaMemcpyAsync(p->clip_mats, m.data(), m.size() * sizeof(float), cudaMemcpyHostToDevice, stream));
+		RN_CUDA(cudaStreamSynchronize(stream));
+	}
+	BillboardView bv;
+	bv.pos = p->mesh_pos; bv.col = p->mesh_color; bv.uv1 = p->mesh_uv1; bv.emitters = p->emitters; bv.mats = p->clip_mats;
+	bv.clip = p->clip_pos; bv.out_col = p->clip_color;
+	bv.ambient = make_float4(ambient_color[0], ambient_color[1], ambient_color[2], ambient_color[3]);
+	bv.cap = p->cap;
+	const dim3 grid((p->cap * 4 + 127) / 128, p->n_emitters);
+	particles_billboard_kernel<<<grid, 128, 0, stream>>>(bv);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	p->have_clip = true;
+	if(out)
+	{
+		out->clip_position = reinterpret_cast<const float *>(p->clip_pos);
+		out->color = reinterpret_cast<const float *>(p->clip_color);
+		out->vertex_stride_per_emitter = p->cap * 4;
+		out->reserved = 0;
+	}
+	return RN_OK;
+}
+
+extern "C" int rn_particles_download_clip(rn_scene_t *s, uint32_t emitter, float *clip_position, float *color)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && emitter < p->n_emitters, RN_ERR_INVALID, "emitter %u out of range", emitter);
+	RN_REQUIRE(p->have_clip, RN_ERR_STATE, "rn_particles_expand_billboards has not been called");
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	EmitterState es;
+	RN_CUDA(cudaMemcpy(&es, p->emitters + emitter, sizeof(es), cudaMemcpyDeviceToHost));
+	const size_t seg = (size_t)emitter * p->cap * 4, nv = (size_t)es.d.max_particles * 4;
+	if(clip_position) RN_CUDA(cudaMemcpy(clip_position, p->clip_pos + seg, nv * sizeof(float4), cudaMemcpyDeviceToHost));
+	if(color) RN_CUDA(cudaMemcpy(color, p->clip_color + seg, nv * sizeof(float4), cudaMemcpyDeviceToHost));
 	return RN_OK;
 }

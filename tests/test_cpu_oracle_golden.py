@@ -179,3 +179,25 @@ def test_oracle_particles_match_live_reference():
         assert rec.shape == ref[k]["rec"].shape
         assert same_floats(rec[:, :23], ref[k]["rec"][:, :23])
         assert same_floats(t, ref[k]["time"])
+
+
+def test_oracle_billboard_vertex_stage():
+    """Shaders/Particles.hlsl particles_vertex restated (unpinned: the shader cannot run here) against the formula in
+    float64: clip = MVP * (float4(pos, 1) + invMV * float4(uv1, 0, 0)), colour * ambient."""
+    rng = np.random.default_rng(1)
+    n = 64
+    pos = rng.normal(size=(n, 3)).astype(np.float32); col = rng.random((n, 4)).astype(np.float32)
+    uv = rng.normal(size=(n, 2)).astype(np.float32)
+    im = rng.normal(size=16).astype(np.float32); mvp = rng.normal(size=16).astype(np.float32)
+    amb = np.float32([0.5, 0.6, 0.7, 1.0])
+    clip, c = oracle.billboards(pos, col, uv, im, mvp, amb)
+    p4 = np.concatenate([pos.astype(np.float64), np.ones((n, 1))], axis=1)
+    t4 = np.concatenate([uv.astype(np.float64), np.zeros((n, 2))], axis=1)
+    want = (p4 + t4 @ im.reshape(4, 4).astype(np.float64)) @ mvp.reshape(4, 4).astype(np.float64)
+    assert np.allclose(clip, want, rtol=1e-5, atol=1e-5)
+    assert np.array_equal(c, col * amb)
+    # a quad's corners: centre + invMV * (+-hx, +-hy): opposite corners are symmetric about the centre before MVP
+    centre = np.float32([[1, 2, 3]] * 4); corners = np.float32([[-1, -2], [1, -2], [-1, 2], [1, 2]])
+    ident = np.eye(4, dtype=np.float32).reshape(16)
+    q, _ = oracle.billboards(centre, np.ones((4, 4), np.float32), corners, ident, ident, np.ones(4, np.float32))
+    assert np.array_equal(q[:, :3], centre + np.concatenate([corners, np.zeros((4, 1), np.float32)], axis=1))

@@ -296,3 +296,46 @@ def test_instance_records_match_oracle_after_sort(rank_mode):
             want = oracle.instances(ids, ref["wmat"], ref["winv"], ov[c], opv[c])
             got = _pack(h, c, v[c], pv[c], len(lst), len(lst) + 5)
             assert same_floats(got, want), f"camera {c}"
+
+
+def test_particle_billboards_match_oracle():
+    """§8(f) rank 2, second half: the vertex stage of Shaders/Particles.hlsl (camera-facing quad expansion) over the
+    mesh of rn_particles_build_mesh - bit-exact against the C restatement (the shader itself cannot run here), and
+    the four corners of a quad really are centre +- the camera's right / up vectors in clip space."""
+    em = sg.make_emitters(6, max_particles=700, spawn_rate=0.003, vary=True)
+    cams = standard_cameras()
+    view, _, projview = capi.build_camera_matrices(cams[:1])
+    rng = np.random.default_rng(4)
+    n = len(em)
+    # every emitter its own model matrix (translation + uniform scale): inverse model-view and MVP per emitter
+    inv_mv = np.zeros((n, 16), np.float32); mvp = np.zeros((n, 16), np.float32)
+    for k in range(n):
+        model = np.eye(4); model[:3, 3] = rng.uniform(-5, 5, 3); model[:3, :3] *= rng.uniform(0.5, 2.0)
+        mv = view[0].reshape(4, 4).T.astype(np.float64) @ model
+        inv_mv[k] = np.linalg.inv(mv).T.reshape(16).astype(np.float32)
+        mvp[k] = (projview[0].reshape(4, 4).T.astype(np.float64) @ model).T.reshape(16).astype(np.float32)
+    ambient = np.float32([0.9, 0.8, 0.7, 1.0])
+    with capi.SceneHandle(max_nodes=1, max_emitters=n, max_particles_per_emitter=700) as h:
+        h.particles_configure(em)
+        with pytest.raises(capi.RNError):
+            h.particles_expand_billboards(inv_mv, mvp, ambient)       # no mesh yet
+        for _ in range(50):
+            h.particles_step(float(np.float32(1 / 60)))
+        counts, _ = h.particles_counts()
+        h.particles_build_mesh(flags=np.full(n, capi.EMITTER_CAN_ROLL, np.uint32))
+        h.particles_expand_billboards(inv_mv, mvp, ambient)
+        for k in range(n):
+            mx = int(em["max_particles"][k])
+            live = 4 * min(int(counts[k]), mx)
+            assert live > 0
+            m = h.particles_download_mesh(k, mx)
+            got = h.particles_download_clip(k, mx)
+            clip, col = oracle.billboards(m["mesh_pos"][:live], m["mesh_color"][:live], m["mesh_uv1"][:live], inv_mv[k], mvp[k], ambient)
+            assert same_floats(got["clip_pos"][:live], clip), k
+            assert same_floats(got["clip_color"][:live], col), k
+            assert not got["clip_pos"][live:].any() and not got["clip_color"][live:].any()
+            # float64 check of the formula itself
+            p4 = np.concatenate([m["mesh_pos"][:live].astype(np.float64), np.ones((live, 1))], axis=1)
+            t4 = np.concatenate([m["mesh_uv1"][:live].astype(np.float64), np.zeros((live, 2))], axis=1)
+            want = (p4 + t4 @ inv_mv[k].reshape(4, 4).astype(np.float64)) @ mvp[k].reshape(4, 4).astype(np.float64)
+            assert np.allclose(got["clip_pos"][:live], want, rtol=1e-4, atol=1e-4)
