@@ -32,18 +32,29 @@ __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *
 	uint32_t mine[RN_MAX_CAMERAS];
 #pragma unroll
 	for(int c = 0; c < RN_MAX_CAMERAS; c++) mine[c] = 0;
-#pragma unroll 8
-	for(uint32_t i = 0; i < 32; i++)
+	// 16 iterations at a time: all rank -> slot loads, then all mask-byte loads, in flight together
+#pragma unroll 1
+	for(uint32_t i0 = 0; i0 < 32; i0 += 16)
 	{
-		const uint32_t r = (word0 + i) * 32u + lane;
-		uint32_t v = 0;
-		if(r < n)
-			v = __ldg(vis + __ldg(slot_of_rank + r));
+		uint32_t slot[16], v[16];
 #pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		for(uint32_t k = 0; k < 16; k++)
 		{
-			const uint32_t b = __ballot_sync(0xffffffffu, (v >> c) & 1u);
-			if(lane == i) mine[c] = b;
+			const uint32_t r = (word0 + i0 + k) * 32u + lane;
+			slot[k] = r < n ? __ldg(slot_of_rank + r) : 0xffffffffu;
+		}
+#pragma unroll
+		for(uint32_t k = 0; k < 16; k++)
+			v[k] = slot[k] != 0xffffffffu ? __ldg(vis + slot[k]) : 0u;
+#pragma unroll
+		for(uint32_t k = 0; k < 16; k++)
+		{
+#pragma unroll
+			for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			{
+				const uint32_t b = __ballot_sync(0xffffffffu, (v[k] >> c) & 1u);
+				if(lane == i0 + k) mine[c] = b;
+			}
 		}
 	}
 	if(word0 + lane < words)

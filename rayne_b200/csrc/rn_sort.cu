@@ -114,6 +114,7 @@ struct PassArgs
 {
 	uint32_t src;      // 0 / 1: which scratch pair is read
 	uint32_t shift;    // bit offset of the digit inside the key; 32 = the priority digit
+	uint32_t last;     // 1: final pass - the entries go straight back into the list, the keys are dropped
 };
 
 __device__ __forceinline__ uint32_t digit_of(const SortView &v, const PassArgs &a, uint32_t key, uint32_t val)
@@ -213,7 +214,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 	__syncthreads();
 	// selects, not v.keys[a.src]: a dynamically indexed kernel parameter is copied to local memory by every thread
 	const uint32_t *keys = a.src ? v.keys[1] : v.keys[0], *vals = a.src ? v.vals[1] : v.vals[0];
-	uint32_t *okeys = a.src ? v.keys[0] : v.keys[1], *ovals = a.src ? v.vals[0] : v.vals[1];
+	uint32_t *okeys = a.src ? v.keys[0] : v.keys[1];
+	uint32_t *ovals = a.last ? v.list + v.range[0] : (a.src ? v.vals[0] : v.vals[1]);
 	// warp w owns entries [w*256, (w+1)*256) of the block, 32 consecutive entries per round: stable inside the warp
 	const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32u);
 	uint32_t key[kSortItems], val[kSortItems], dig[kSortItems], rank[kSortItems];
@@ -287,24 +289,15 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		{
 			const uint32_t d = s_dig[idx];
 			const uint32_t dst = dbase[d] + (idx - lpre[d]);
-			okeys[dst] = s_key[idx];
+			if(!a.last) okeys[dst] = s_key[idx];
 			ovals[dst] = s_val[idx];
 		}
 	}
 }
 
-__global__ void __launch_bounds__(256) sort_writeback_kernel(SortView v, uint32_t src)
-{
-	const uint32_t begin = v.range[0], end = v.range[1];
-	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-	if(e < end - begin)
-		v.list[begin + e] = (src ? v.vals[1] : v.vals[0])[e];
-}
-
 static int run_passes(rn_scene *s, const SortView &v, bool with_priority_digit, cudaStream_t stream)
 {
 	const uint32_t grid_tiles = (s->n + kSortTile - 1) / kSortTile;
-	const uint32_t grid_flat = (s->n + 255) / 256;
 	uint32_t src = 0;
 	const uint32_t n_pass = with_priority_digit ? 5u : 4u;
 	for(uint32_t p = 0; p < n_pass; p++)
@@ -312,14 +305,14 @@ static int run_passes(rn_scene *s, const SortView &v, bool with_priority_digit, 
 		PassArgs a;
 		a.src = src;
 		a.shift = p * 8u;
+		a.last = p + 1 == n_pass ? 1u : 0u;
 		sort_hist_kernel<<<grid_tiles, kSortThreads, 0, stream>>>(v, a);
 		sort_scan_kernel<<<256, 256, 0, stream>>>(v);
 		sort_scatter_kernel<<<grid_tiles, kSortThreads, 0, stream>>>(v, a);
 		s->launches += 3;
 		src ^= 1u;
 	}
-	sort_writeback_kernel<<<grid_flat, 256, 0, stream>>>(v, src);
-	s->launches++;
+	// no write-back pass: the last scatter wrote the entries straight into the list
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
