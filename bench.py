@@ -168,6 +168,11 @@ def run_ours(args) -> dict:
         # thread blocks of frame i+1's transform kernel, or it only starts in that kernel's tail
         opts = dist.ProcessGroupNCCL.Options()
         opts.is_high_priority_stream = True
+        if args.nccl_ctas > 0:
+            # the gather is small and hides under the next frame: a few CTAs are enough, and every CTA NCCL takes is an
+            # SM slot the transform kernel of the next frame does not get
+            opts.config.max_ctas = args.nccl_ctas
+            opts.config.min_ctas = min(args.nccl_ctas, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120),
                                 pg_options=opts)
 
@@ -223,8 +228,9 @@ def run_ours(args) -> dict:
         h.transform_cull(fr, stream)
         if world > 1:
             if use_masks:
-                h.build_masks(stream)
-                pexch.submit(mask_t)
+                # the masks go straight into the send buffer of this frame's gather (no staging copy)
+                h.build_masks_to(pexch.begin().data_ptr(), pexch.row, stream)
+                pexch.submit()
             else:
                 pexch.submit(count_t, list_t)
 
@@ -461,6 +467,23 @@ def run_ours(args) -> dict:
         sort_bytes = entries * (4 * 16.0 - 4.0 + 28.0)
         extras["cull_sort_front_to_back"] = {"ms": ms, "entries": entries, "Mentries_per_s": entries / ms / 1e3,
                                              "roofline_frac": sort_bytes / (ms * 1e-3) / 1e9 / peak}
+        # visibility as rank-order bitmasks (the multi-GPU exchange format) and back: 5 B + V/8 B per node; expansion of
+        # the largest view reads its words twice and writes 4 B per entry
+        ms = timed(lambda: h.build_masks(stream))
+        extras["cull_build_masks"] = {"ms": ms, "bytes_per_node": 5 + ncam / 8.0,
+                                      "roofline_frac": n * (5 + ncam / 8.0) / (ms * 1e-3) / 1e9 / peak}
+        mptr_x, mwords_x, _ = h.device_masks()
+        xl = torch.empty(max(entries, 1), dtype=torch.int32, device="cuda")
+        xc = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+        def expand_largest():
+            xc.zero_()
+            h.masks_expand([(mptr_x + 4 * (ncam - 1) * mwords_x, mwords_x, 0)], xl.data_ptr(), xl.numel(), xc.data_ptr(), stream)
+
+        ms = timed(expand_largest)
+        extras["masks_expand_largest_view"] = {"ms": ms, "entries": int(xc.item()),
+                                               "roofline_frac": (mwords_x * 8.0 + entries * 4.0) / (ms * 1e-3) / 1e9 / peak}
+        del xl
         # §8(f) drawable uniform packing: 256-byte matrix records of the largest list
         view, _, projview = capi.build_camera_matrices(cams)
         inst = torch.empty((max(entries, 1), 64), dtype=torch.float32, device="cuda")
@@ -549,6 +572,7 @@ def main():
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
+    ap.add_argument("--nccl-ctas", type=int, default=0, help="N>1: cap on NCCL's CTAs per collective (0 = NCCL's default)")
     ap.add_argument("--exchange", choices=("masks", "lists"), default="masks",
                     help="N>1: what the per-frame all-gather ships (rank-order bitmasks, or counts + index lists)")
     ap.add_argument("--no-extras", action="store_true", help="skip the side timings of inverse / bounds / sort / mesh")

@@ -240,6 +240,9 @@ int rn_cull_sort(rn_scene_t *scene, const float *camera_world_positions, uint32_
  * local to the scene (rank_offset of rn_scene_set_list_mode is not applied).  This is what the multi-GPU exchange
  * ships; rn_masks_expand turns gathered masks back into lists.  Asynchronous on `cuda_stream`. */
 int rn_cull_build_masks(rn_scene_t *scene, void *cuda_stream);
+/* The same masks written into DEVICE memory of the caller (e.g. the send buffer of an all-gather): camera c at
+ * device_out + c * row_stride_words, row_stride_words >= ceil(nodes / 32); words beyond the scene's are not touched. */
+int rn_cull_build_masks_to(rn_scene_t *scene, uint32_t *device_out, uint32_t row_stride_words, void *cuda_stream);
 /* Device pointer of the masks (camera c at masks + c * words_per_camera), words per camera = ceil(nodes / 32), and
  * the number of cameras they hold; *masks = NULL before rn_cull_build_masks or after a newer cull. */
 int rn_cull_device_masks(rn_scene_t *scene, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras);

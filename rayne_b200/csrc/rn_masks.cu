@@ -17,26 +17,45 @@ namespace rn {
 
 constexpr uint32_t kMaskThreads = 256;
 
-// One warp builds 32 consecutive words (1024 ranks) of every camera: in iteration i the warp's lanes hold ranks
-// base + 32 i .. +31, one ballot per camera gives word i, lane i keeps it; after 32 iterations lane i stores word i
-// of every camera - 128-byte coalesced stores.
+// One warp builds 32 consecutive words (1024 ranks) of every camera.  Lane L loads the mask bytes of ranks
+// base + 32 i + L for i = 0..31 (coalesced rank -> slot loads, then the byte gathers), regroups its own 32 bytes into
+// one 32-bit column per camera (bit i = iteration i) with a multiply-gather per four bytes, and a 32 x 32 bit-matrix
+// transpose over the warp (five shuffle stages per camera) turns "lane L, bit i" into "lane i, bit L" - word i of
+// that camera.  A ballot per (iteration, camera) gives the same words with 4x the instructions (this kernel is
+// issue-bound, not bandwidth-bound).  Lane i then stores word i of every camera: 128-byte coalesced stores.
+__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, uint32_t lane)
+{
+#pragma unroll
+	for(int k = 0; k < 5; k++)
+	{
+		const uint32_t j = 16u >> k;
+		const uint32_t lo = k == 0 ? 0x0000ffffu : k == 1 ? 0x00ff00ffu : k == 2 ? 0x0f0f0f0fu : k == 3 ? 0x33333333u : 0x55555555u;
+		const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+		// [[A, B], [C, D]] -> [[A, C], [B, D]]: rows (lanes) with bit j clear take the partner's low columns into their
+		// high columns, rows with bit j set take the partner's high columns into their low columns
+		x = (lane & j) ? ((x & ~lo) | ((y >> j) & lo)) : ((x & lo) | ((y << j) & ~lo));
+	}
+	return x;
+}
+
+template <uint32_t NCAMS>
 __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *__restrict__ vis,
                                                                  const uint32_t *__restrict__ slot_of_rank, uint32_t n,
-                                                                 uint32_t words, uint32_t ncams, uint32_t *__restrict__ masks)
+                                                                 uint32_t words, uint32_t stride, uint32_t *__restrict__ masks)
 {
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t warp = (blockIdx.x * kMaskThreads + threadIdx.x) >> 5;
 	const uint32_t word0 = warp * 32u;
 	if(word0 >= words)
 		return;
-	uint32_t mine[RN_MAX_CAMERAS];
+	uint32_t col[NCAMS];
 #pragma unroll
-	for(int c = 0; c < RN_MAX_CAMERAS; c++) mine[c] = 0;
+	for(uint32_t c = 0; c < NCAMS; c++) col[c] = 0;
 	// 16 iterations at a time: all rank -> slot loads, then all mask-byte loads, in flight together
 #pragma unroll 1
 	for(uint32_t i0 = 0; i0 < 32; i0 += 16)
 	{
-		uint32_t slot[16], v[16];
+		uint32_t slot[16], packed[4];
 #pragma unroll
 		for(uint32_t k = 0; k < 16; k++)
 		{
@@ -44,25 +63,37 @@ __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *
 			slot[k] = r < n ? __ldg(slot_of_rank + r) : 0xffffffffu;
 		}
 #pragma unroll
-		for(uint32_t k = 0; k < 16; k++)
-			v[k] = slot[k] != 0xffffffffu ? __ldg(vis + slot[k]) : 0u;
+		for(uint32_t g = 0; g < 4; g++)
+		{
+			uint32_t p = 0;
 #pragma unroll
-		for(uint32_t k = 0; k < 16; k++)
+			for(uint32_t b = 0; b < 4; b++)
+			{
+				const uint32_t s = slot[g * 4 + b];
+				const uint32_t v = s != 0xffffffffu ? (uint32_t)__ldg(vis + s) : 0u;
+				p |= v << (8 * b);
+			}
+			packed[g] = p;
+		}
+		// four iterations per register: bits c, 8 + c, 16 + c, 24 + c -> one nibble, shifted in from the top
+#pragma unroll
+		for(uint32_t g = 0; g < 4; g++)
 		{
 #pragma unroll
-			for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			for(uint32_t c = 0; c < NCAMS; c++)
 			{
-				const uint32_t b = __ballot_sync(0xffffffffu, (v[k] >> c) & 1u);
-				if(lane == i0 + k) mine[c] = b;
+				const uint32_t t = (packed[g] >> c) & 0x01010101u;
+				col[c] = (col[c] >> 4) | ((t * 0x10204080u) & 0xf0000000u);
 			}
 		}
 	}
-	if(word0 + lane < words)
-	{
+	const bool store = word0 + lane < words;
 #pragma unroll
-		for(int c = 0; c < RN_MAX_CAMERAS; c++)
-			if((uint32_t)c < ncams)
-				masks[(size_t)c * words + word0 + lane] = mine[c];
+	for(uint32_t c = 0; c < NCAMS; c++)
+	{
+		const uint32_t w = warp_bit_transpose(col[c], lane);
+		if(store)
+			masks[(size_t)c * stride + word0 + lane] = w;
 	}
 }
 
@@ -208,6 +239,23 @@ using namespace rn;
 
 static inline uint32_t mask_words(const rn_scene *s) { return (s->n + 31u) / 32u; }
 
+static int build_masks(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t stream)
+{
+	const uint32_t words = mask_words(s);
+	const uint32_t warps = (words + 31) / 32;
+	const uint32_t grid = (warps + kMaskThreads / 32 - 1) / (kMaskThreads / 32);
+	switch(s->last_ncams)
+	{
+#define RN_MASK_CASE(V) case V: rank_mask_kernel<V><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+		RN_MASK_CASE(1) RN_MASK_CASE(2) RN_MASK_CASE(3) RN_MASK_CASE(4) RN_MASK_CASE(5) RN_MASK_CASE(6) RN_MASK_CASE(7)
+		default: rank_mask_kernel<8><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+#undef RN_MASK_CASE
+	}
+	RN_CUDA(cudaGetLastError());
+	s->launches++;
+	return RN_OK;
+}
+
 extern "C" int rn_cull_build_masks(rn_scene_t *s, void *cuda_stream)
 {
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
@@ -222,16 +270,22 @@ extern "C" int rn_cull_build_masks(rn_scene_t *s, void *cuda_stream)
 	s->have_masks = false;
 	if(s->n == 0)
 		return RN_OK;
-	const uint32_t words = mask_words(s);
-	const uint32_t warps = (words + 31) / 32;
-	const uint32_t grid = (warps + kMaskThreads / 32 - 1) / (kMaskThreads / 32);
-	rank_mask_kernel<<<grid, kMaskThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(s->vis, s->d_slot_of_rank, s->n, words,
-	                                                                                   s->last_ncams, s->rank_masks);
-	RN_CUDA(cudaGetLastError());
-	s->launches++;
+	int rc = build_masks(s, s->rank_masks, mask_words(s), static_cast<cudaStream_t>(cuda_stream));
+	if(rc) return rc;
 	s->have_masks = true;
 	s->mask_ncams = s->last_ncams;
 	return RN_OK;
+}
+
+extern "C" int rn_cull_build_masks_to(rn_scene_t *s, uint32_t *device_out, uint32_t row_stride_words, void *cuda_stream)
+{
+	RN_REQUIRE(s && device_out, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_build_masks_to needs a cull");
+	RN_REQUIRE(row_stride_words >= mask_words(s), RN_ERR_INVALID, "row stride %u < %u words per camera", row_stride_words, mask_words(s));
+	RN_CUDA(cudaSetDevice(s->device));
+	if(s->n == 0)
+		return RN_OK;
+	return build_masks(s, device_out, row_stride_words, static_cast<cudaStream_t>(cuda_stream));
 }
 
 extern "C" int rn_cull_device_masks(rn_scene_t *s, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras)

@@ -271,20 +271,34 @@ class PipelinedMaskExchange:
         self._send = [None] * (self.depth + 1)
         self._frame = 0
 
-    def submit(self, masks):
-        """masks: int32 tensor [ncams * words_local] (camera rows one behind the other, the library's buffer)."""
+    def begin(self):
+        """Send buffer of the coming frame, [ncams, row] int32 on the device: the producer may write its masks straight
+        into it (rn_cull_build_masks_to with row stride ``row``) and then call ``submit()`` without an argument."""
         torch = self.torch
-        wl = self.words_per_rank[self.rank]
         k = self._frame % len(self._bufs)
-        self._frame += 1
         while len(self.pending) > self.depth - 1:      # the buffers of frame i-depth are free again
             self._retire_one(self.pending.pop(0))
         if self._send[k] is None:
-            self._send[k] = torch.zeros(self.ncams * self.row, dtype=masks.dtype, device=masks.device)
-            self._bufs[k] = torch.empty(self.world * self.ncams * self.row, dtype=masks.dtype, device=masks.device)
+            dev = "cuda" if self.cuda else "cpu"
+            self._send[k] = torch.zeros(self.ncams * self.row, dtype=torch.int32, device=dev)
+            self._bufs[k] = torch.empty(self.world * self.ncams * self.row, dtype=torch.int32, device=dev)
+        self._begun = True
+        return self._send[k].view(self.ncams, self.row)
+
+    def submit(self, masks=None):
+        """masks: int32 tensor [ncams * words_local] (camera rows one behind the other, e.g. the library's buffer) -
+        copied into the send buffer - or None if the producer already filled the buffer ``begin()`` returned."""
+        torch = self.torch
+        wl = self.words_per_rank[self.rank]
+        if not getattr(self, "_begun", False):
+            self.begin()
+        self._begun = False
+        k = self._frame % len(self._bufs)
+        self._frame += 1
         send, dst = self._send[k], self._bufs[k]
-        # snapshot on the producing stream (the next cull overwrites the library's buffer), padded rows
-        send.view(self.ncams, self.row)[:, :wl].copy_(masks.view(self.ncams, wl))
+        if masks is not None:
+            # snapshot on the producing stream (the next cull overwrites the library's buffer), padded rows
+            send.view(self.ncams, self.row)[:, :wl].copy_(masks.view(self.ncams, wl))
         if self.cuda:
             ev = torch.cuda.Event()
             ev.record()

@@ -63,6 +63,15 @@ def test_masks_and_expansion_match_lists(kw, fused):
         h.build_masks()
         ptr, words, k = h.device_masks()
         m = h.read_masks()
+        # the same masks into a caller-owned buffer with a wider row (the send buffer of the all-gather)
+        stride = words + 5
+        ext = torch.full((len(cams), stride), 0x5a5a5a5a, dtype=torch.int32, device="cuda")
+        h.build_masks_to(ext.data_ptr(), stride)
+        torch.cuda.synchronize()
+        ext = ext.cpu().numpy().view(np.uint32)
+        assert np.array_equal(ext[:, :words], m) and (ext[:, words:] == 0x5a5a5a5a).all()
+        with pytest.raises(capi.RNError):
+            h.build_masks_to(1024, words - 1)
         out = torch.full((scene.n + 8,), -1, dtype=torch.int32, device="cuda")
         cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
         for c in range(len(cams)):
