@@ -372,6 +372,37 @@ def run_ours(args) -> dict:
     # the same frame with the visibility read back as rank-order bitmasks (1 bit per node and view instead of 4 B per
     # visible node): the compact form of the same result, 12.6 MB instead of 61 MB over PCIe
     e2e_masks = None
+    if world > 1 and use_masks:
+        # several GPUs: the same frame with the compact read-back (one scene per GPU, unpipelined) + the mask gather
+        mw = (n + 31) // 32
+        pinned_masks = torch.empty(ncam * mw, dtype=torch.int32).pin_memory()
+
+        def e2e_mask_step_n():
+            rootpos[:, 0] += np.float32(0.01)
+            h.update_nodes(roots, position=rootpos)
+            h.transform_cull(fr, stream)
+            h.build_masks_to(pexch.begin().data_ptr(), pexch.row, stream)
+            pexch.submit()
+            h.build_masks(stream)
+            h.read_masks_into(pinned_masks.data_ptr(), ncam, stream)
+            pexch.flush()
+            torch.cuda.current_stream().synchronize()
+
+        for _ in range(min(3, args.warmup)):
+            e2e_mask_step_n()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_mask_step_n()
+        barrier()
+        mms = (time.perf_counter() - t0) * 1e3 / args.steps
+        t = torch.tensor([mms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        mms = float(t.item())
+        e2e_masks = {"value": n * world / mms / 1e3, "unit": "Mnodes/s", "ms_per_step": mms,
+                     "h2d_bytes_per_step": int(roots.shape[0] * 16), "d2h_bytes_per_step": int(ncam * mw * 4),
+                     "what": "per GPU: rn_scene_update_nodes + rn_transform_cull + rn_cull_build_masks + "
+                             "rn_cull_read_masks_async into pinned host memory, and the all-gather of the masks"}
     if pipe is not None:
         offs, total_words = pipe.mask_layout(ncam)
         pinned_masks = torch.empty(total_words, dtype=torch.int32).pin_memory()
