@@ -720,17 +720,39 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 			break;
 		// cameras that see anything of this tile (most tiles are invisible to most cameras)
 		uint32_t cams = 0;
-		uint32_t off[RN_MAX_CAMERAS];
 #pragma unroll
 		for(int c = 0; c < RN_MAX_CAMERAS; c++)
-		{
-			off[c] = s_off[k][c];
 			if((uint32_t)c < ev.n_cams && s_cnt[k][c])
 				cams |= 1u << c;
-		}
 		if(!cams)
 			continue;
 		const uint32_t start = ev.tiles[t].start, count = ev.tiles[t].count;
+		// A camera that sees EVERY node of the tile (the common case next to "sees nothing": tiles are subtrees, and a
+		// subtree is usually inside or outside a frustum as a whole) needs no mask bytes and no ranking - its part of
+		// the list is the tile's rank range itself, copied with coalesced loads and stores.
+		uint32_t full = 0;
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			if(((cams >> c) & 1u) && s_cnt[k][c] == count)
+				full |= 1u << c;
+		if(full)
+		{
+			for(uint32_t j = lane; j < count; j += 32)
+			{
+				const uint32_t id = ev.rank_mode ? start + j + ev.rank_offset : __ldg(ev.slot_of_rank + start + j);
+#pragma unroll
+				for(int c = 0; c < RN_MAX_CAMERAS; c++)
+					if((full >> c) & 1u)
+						ev.lists[c][s_off[k][c] + j] = id;
+			}
+			cams &= ~full;
+			if(!cams)
+				continue;
+		}
+		uint32_t off[RN_MAX_CAMERAS];
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			off[c] = s_off[k][c];
 		// 128 ranks per iteration, four consecutive ranks per lane: one warp scan per camera instead of four ballots
 		for(uint32_t r0 = 0; r0 < count; r0 += 32 * kEmitUnroll)
 		{
