@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <vector>
 
 namespace {
@@ -326,33 +327,25 @@ extern "C" int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, con
 		for(uint32_t i = 0; i < n; i++)
 			if(parent[i] >= 0) child[fill[parent[i]]++] = i;
 	}
-	// doubly linked list over node ids
-	const uint32_t NIL = 0xffffffffu;
-	std::vector<uint32_t> next(n, NIL), prev(n, NIL);
-	uint32_t head = NIL, tail = NIL;
+	// AddRenderNode keeps the list sorted by priority.  Inside one priority a node lands BEHIND its equals (cases 2
+	// and 3) unless its priority is <= the head's, i.e. <= the smallest priority seen so far (case 1: PushFront, in
+	// front of its equals).  So the list is, per priority ascending, a deque: reverse(front pushes) ++ back pushes -
+	// the same order as the reference's linked-list walk without its O(list) step per insert.
+	struct Group { std::vector<uint32_t> front, back; };
+	std::map<int32_t, Group> groups;
+	bool empty = true;
+	int32_t minp = 0;
 	auto priority = [&](uint32_t i) { return prio ? prio[i] : 0; };
 	auto insert = [&](uint32_t node) {
 		const int32_t p = priority(node);
-		if(head == NIL || priority(head) >= p)
+		if(empty || minp >= p)
 		{
-			next[node] = head; prev[node] = NIL;
-			if(head != NIL) prev[head] = node; else tail = node;
-			head = node;
-		}
-		else if(priority(tail) <= p)
-		{
-			prev[node] = tail; next[node] = NIL;
-			next[tail] = node;
-			tail = node;
+			groups[p].front.push_back(node);
+			minp = p;
+			empty = false;
 		}
 		else
-		{
-			uint32_t m = tail;
-			while(priority(m) > p) m = prev[m];
-			const uint32_t after = next[m];
-			next[m] = node; prev[node] = m; next[node] = after;
-			if(after != NIL) prev[after] = node; else tail = node;
-		}
+			groups[p].back.push_back(node);
 	};
 	// iterative post-order from every root, roots in creation order
 	std::vector<uint32_t> stack_node, stack_pos;
@@ -380,7 +373,12 @@ extern "C" int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, con
 		}
 	}
 	uint32_t r = 0;
-	for(uint32_t i = head; i != NIL; i = next[i]) order[r++] = i;
+	for(const auto &kv : groups)
+	{
+		const Group &g = kv.second;
+		for(size_t q = g.front.size(); q-- > 0;) order[r++] = g.front[q];
+		for(uint32_t id : g.back) order[r++] = id;
+	}
 	RN_REQUIRE(r == n, RN_ERR_INVALID, "internal error: %u of %u nodes ordered", r, n);
 	return RN_OK;
 }

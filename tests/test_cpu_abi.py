@@ -82,6 +82,18 @@ def test_render_order_probe_from_the_survey():
     assert np.array_equal(order, oracle.render_order(parent, prio))
 
 
+def test_render_order_matches_the_linked_list_walk_on_random_forests():
+    """rn_scenebasic_render_order keeps one deque per priority instead of the reference's walk from the tail; the
+    oracle restates the walk literally (and is pinned by the golden orders).  Heavy ties, descending minima, many
+    roots - the cases where PushFront / PushBack / insert-after differ."""
+    rng = np.random.default_rng(0)
+    for trial in range(40):
+        n = int(rng.integers(1, 2500))
+        parent = np.array([-1 if (i == 0 or rng.random() < 0.05) else int(rng.integers(0, i)) for i in range(n)], np.int32)
+        prio = rng.choice([-5, 0, 0, 0, 3, 7, 100000, 200000, 300000], size=n).astype(np.int32)
+        assert np.array_equal(capi.render_order(parent, prio), oracle.render_order(parent, prio)), trial
+
+
 def test_render_order_rejects_bad_hierarchy():
     with pytest.raises(capi.RNError):
         capi.render_order(np.array([1, -1], np.int32), None)   # parent after child
