@@ -422,52 +422,6 @@ __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t
 	store_world_global(sv, slot, W);
 }
 
-// The same pre-pass as ONE launch when the spine is small (it is: 16 128 of 16.8 M nodes in the benchmark scene): a
-// cluster of 8 CTAs walks the depths one after the other with a cluster barrier (release / acquire at cluster scope, so
-// a depth sees the world transforms the depth before it stored) in between - two barriers instead of two more launches
-// on the critical path of every frame.
-constexpr uint32_t kSpineClusterCtas = 8;
-constexpr uint32_t kSpineClusterThreads = 512;
-constexpr uint32_t kSpineMaxLevels = 16;
-constexpr uint32_t kSpineClusterMaxNodes = 1u << 17;
-
-struct SpineLevels
-{
-	uint32_t ofs[kSpineMaxLevels + 1];
-	uint32_t levels;
-};
-
-__device__ __forceinline__ void cluster_barrier()
-{
-	asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
-__global__ void __cluster_dims__(kSpineClusterCtas, 1, 1) __launch_bounds__(kSpineClusterThreads)
-    spine_cluster_kernel(SceneView sv, const uint32_t *__restrict__ slots, const __grid_constant__ SpineLevels lv)
-{
-	const uint32_t tid = blockIdx.x * kSpineClusterThreads + threadIdx.x;
-	for(uint32_t d = 0; d < lv.levels; d++)
-	{
-		for(uint32_t i = lv.ofs[d] + tid; i < lv.ofs[d + 1]; i += kSpineClusterCtas * kSpineClusterThreads)
-		{
-			const uint32_t slot = slots[i];
-			const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
-			const Vec3 pos = {a.x, a.y, a.z};
-			const Vec3 scale = {a.w, c.x, c.y};
-			const Quat rot = {b.x, b.y, b.z, b.w};
-			const uint32_t parent = __float_as_uint(c.z);
-			NodeWorld P, W;
-			const bool hasParent = parent != RN_NO_PARENT;
-			if(hasParent)
-				load_world_global(sv, parent, P);
-			compute_world(pos, rot, scale, hasParent, P, W);
-			store_world_global(sv, slot, W);
-		}
-		if(d + 1 < lv.levels)
-			cluster_barrier();
-	}
-}
-
 // Per-warp shared memory: the world TRS + matrix of the tile's INNER nodes (nodes with children), SoA (88 bytes
 // per inner node), the tile descriptor, one staging buffer for the four input columns of a pass (4 x 32 x float4,
 // filled by TMA bulk copies) and the mbarrier those copies complete on.
@@ -1113,18 +1067,6 @@ static int ensure_lists(rn_scene *s, uint32_t ncams)
 static int launch_spine(rn_scene *s, cudaStream_t stream)
 {
 	const SceneView v = make_view(s);
-	const size_t levels = s->spine_level_ofs.empty() ? 0 : s->spine_level_ofs.size() - 1;
-	if(levels > 1 && levels <= kSpineMaxLevels && s->spine_level_ofs.back() <= kSpineClusterMaxNodes)
-	{
-		SpineLevels lv;
-		memset(&lv, 0, sizeof(lv));
-		lv.levels = (uint32_t)levels;
-		for(size_t d = 0; d <= levels; d++) lv.ofs[d] = s->spine_level_ofs[d];
-		spine_cluster_kernel<<<kSpineClusterCtas, kSpineClusterThreads, 0, stream>>>(v, s->spine_slots, lv);
-		s->launches++;
-		RN_CUDA(cudaGetLastError());
-		return RN_OK;
-	}
 	for(size_t d = 0; d + 1 < s->spine_level_ofs.size(); d++)
 	{
 		const uint32_t cnt = s->spine_level_ofs[d + 1] - s->spine_level_ofs[d];
