@@ -296,6 +296,20 @@ int rn_scenebasic_render_order(uint32_t n, const int32_t *parent, const int32_t 
  * submit for the default volume (:116-123). */
 int rn_scenevis_default_volume_order(uint32_t n, const int32_t *parent, uint32_t *order);
 
+/* SceneWithVisibilityLists volumes (Source/Scene/RNSceneWithVisibilityLists.cpp:29-37,157-207): AddVolume moves its
+ * nodes out of the default volume, and a camera submits the default volume's nodes followed by those of the FIRST
+ * volume that contains its world position.  Here: upload the node columns as [default volume in
+ * rn_scenevis_default_volume_order][nodes of volume 1 in the order of its `nodes` vector][volume 2]..., tag every rank
+ * with its volume (0 = default, k = volume k, 255 = in no volume: never rendered - the children of a node that was
+ * added through AddVolume, :181-190), and give every camera of the next culls the volume it is in
+ * (rn_scenevis_choose_volume; 0 = none).  The culls then drop the entries of the other volumes, and the lists are the
+ * reference's submissions.  A node listed in several volumes cannot be expressed (it has one rank).
+ * rn_scenevis_set_camera_volumes(scene, NULL, 0) switches the filter off; a full rn_scene_upload clears the tags. */
+int rn_scenevis_set_node_volumes(rn_scene_t *scene, const uint8_t *volume_of_rank, uint32_t first, uint32_t count);
+int rn_scenevis_set_camera_volumes(rn_scene_t *scene, const uint8_t *volume_per_camera, uint32_t n_cameras);
+/* bounds: 6 floats per AxisAlignedBoxVolume (boundsMin xyz, boundsMax xyz), in AddVolume order.  Host function. */
+int rn_scenevis_choose_volume(const float *bounds, uint32_t n_volumes, const float *camera_world_position, uint8_t *out_volume);
+
 /* ---- particles ------------------------------------------------------------------------------------------- */
 /* GenericParticleEmitter state (Source/Scene/RNParticleEmitter.cpp:24-36,379-395). */
 typedef struct rn_emitter_desc {

@@ -152,6 +152,27 @@ def billboards(pos, color, uv1, inv_mv, mvp, ambient):
     return clip, col
 
 
+def choose_volume(bounds, camera_position) -> int:
+    """SceneWithVisibilityLists::Render's volume choice (Source/Scene/RNSceneWithVisibilityLists.cpp:157-166) with
+    AxisAlignedBoxVolume::ContainsPosition (:34-37): index + 1 of the FIRST box that contains the position, 0 = none."""
+    x, y, z = (np.float32(v) for v in camera_position)
+    for k, b in enumerate(np.asarray(bounds, np.float32).reshape(-1, 6)):
+        if z >= b[2] and y >= b[1] and x >= b[0] and x <= b[3] and y <= b[4] and z <= b[5]:
+            return k + 1
+    return 0
+
+
+def volume_lists(order, volume_of_node, chosen, visible_ids):
+    """RenderVolumeList(default) then RenderVolumeList(chosen volume) (:116-123,168-175) for one camera: `order` = the
+    default volume's nodes followed by every volume's nodes (creation ids), visible_ids = the ids CanRender accepts."""
+    vol = np.asarray(volume_of_node)
+    vis = np.zeros(vol.shape[0], bool)
+    vis[np.asarray(visible_ids, dtype=np.int64)] = True
+    o = np.asarray(order, dtype=np.int64)
+    keep = vis[o] & ((vol[o] == 0) | (vol[o] == chosen))
+    return o[keep].astype(np.uint32)
+
+
 def camera_matrices(cameras: np.ndarray):
     """(view, projection, proj_view) per camera, each [V, 16]."""
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)

@@ -215,6 +215,10 @@ namespace
 		std::vector<int32_t> priority;
 		std::vector<float> sphere;
 		std::vector<float> box;   // optional (kOptBox): minExtend xyz, maxExtend xyz per node
+		// optional (kOptVolumes): AxisAlignedBoxVolumes (boundsMin xyz, boundsMax xyz) and the volume of every node
+		// (0 = stays in the default volume, k = listed in volume k)
+		std::vector<float> volumeBounds;
+		std::vector<uint32_t> volumeOfNode;
 		std::vector<CameraDesc> cameras;
 	};
 
@@ -222,7 +226,8 @@ namespace
 	//          and projView*world of every node (the matrix uniforms a renderer derives per drawable).
 	// kOptVisLists: drive SceneWithVisibilityLists (default volume only) instead of SceneBasic.
 	// kOptBox: the input carries a local AABB column (SceneNode::SetBoundingBox).
-	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1, kOptVisLists = 1u << 2, kOptBox = 1u << 3, kOptInstances = 1u << 4 };
+	enum : uint32_t { kOptInverse = 1u << 0, kOptTouchMatrices = 1u << 1, kOptVisLists = 1u << 2, kOptBox = 1u << 3, kOptInstances = 1u << 4,
+	                  kOptVolumes = 1u << 5 };   // kOptVolumes (with kOptVisLists): SceneWithVisibilityLists::AddVolume
 
 	SceneInput ReadScene(const char *path)
 	{
@@ -239,6 +244,12 @@ namespace
 		in.flags = r.vec<uint32_t>(n); in.group = r.vec<uint32_t>(n); in.priority = r.vec<int32_t>(n);
 		in.sphere = r.vec<float>(n * 4);
 		if(in.options & kOptBox) in.box = r.vec<float>(n * 6);
+		if(in.options & kOptVolumes)
+		{
+			uint32_t nVolumes = r.get<uint32_t>();
+			in.volumeBounds = r.vec<float>((size_t)nVolumes * 6);
+			in.volumeOfNode = r.vec<uint32_t>(n);
+		}
 		in.cameras = r.vec<CameraDesc>(in.nCameras);
 		return in;
 	}
@@ -282,6 +293,20 @@ namespace
 			else b.roots.push_back(b.nodes[i]);
 		}
 		for(CullNode *root : b.roots) b.scene->AddNode(root);
+		if(b.vis && (in.options & kOptVolumes))
+		{
+			// the reference flow: nodes enter the scene (default volume), AddVolume then moves the listed ones out of it
+			// (Source/Scene/RNSceneWithVisibilityLists.cpp:181-207); a volume lists its nodes in creation order here
+			for(size_t k = 0; k < in.volumeBounds.size() / 6; k++)
+			{
+				auto *volume = new SceneWithVisibilityLists::AxisAlignedBoxVolume();
+				volume->boundsMin = Vector3(in.volumeBounds[k*6], in.volumeBounds[k*6+1], in.volumeBounds[k*6+2]);
+				volume->boundsMax = Vector3(in.volumeBounds[k*6+3], in.volumeBounds[k*6+4], in.volumeBounds[k*6+5]);
+				for(uint32_t i = 0; i < in.nNodes; i++)
+					if(in.volumeOfNode[i] == k + 1) volume->nodes.push_back(b.nodes[i]);
+				b.vis->AddVolume(volume);
+			}
+		}
 
 		for(uint32_t c = 0; c < in.nCameras; c++)
 		{

@@ -31,6 +31,7 @@ OPT_INVERSE = 1
 OPT_TOUCH_MATRICES = 2
 OPT_VISLISTS = 4      # SceneWithVisibilityLists (default volume) instead of SceneBasic
 OPT_BOX = 8           # the input carries scene.box (local AABB column)
+OPT_VOLUMES = 32      # with OPT_VISLISTS: volumes = (bounds [V, 6], volume_of_node [n]) -> SceneWithVisibilityLists::AddVolume
 OPT_INSTANCES = 16    # dump view / projView per camera and view*world, projView*world of every node for camera 0
 POPT_ROLL, POPT_INVERSED, POPT_MESH = 1, 2, 4
 
@@ -49,7 +50,7 @@ def have_harness(kind: str = "strict") -> bool:
 
 
 def write_scene_input(path: str, scene: Scene, cameras: np.ndarray, frames: int = 1, options: int = 0,
-                      root_translate=(0.0, 0.0, 0.0)) -> None:
+                      root_translate=(0.0, 0.0, 0.0), volumes=None) -> None:
     cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
     with open(path, "wb") as f:
         f.write(np.array([0x49534E52, 1, scene.n, cameras.shape[0], frames, options], dtype="<u4").tobytes())
@@ -64,6 +65,12 @@ def write_scene_input(path: str, scene: Scene, cameras: np.ndarray, frames: int 
         f.write(np.ascontiguousarray(scene.sphere, dtype="<f4").tobytes())
         if options & OPT_BOX:
             f.write(np.ascontiguousarray(scene.box, dtype="<f4").tobytes())
+        if options & OPT_VOLUMES:
+            bounds, volume_of_node = volumes
+            bounds = np.ascontiguousarray(bounds, dtype="<f4").reshape(-1, 6)
+            f.write(np.array([bounds.shape[0]], dtype="<u4").tobytes())
+            f.write(bounds.tobytes())
+            f.write(np.ascontiguousarray(volume_of_node, dtype="<u4").tobytes())
         f.write(cameras.tobytes())
 
 
@@ -111,11 +118,11 @@ def read_scene_output(path: str, with_instances: bool = False) -> dict:
 
 
 def run_scene(scene: Scene, cameras: np.ndarray, frames: int = 1, options: int = 0,
-              root_translate=(0.0, 0.0, 0.0), kind: str = "strict") -> dict:
+              root_translate=(0.0, 0.0, 0.0), kind: str = "strict", volumes=None) -> dict:
     """Run the real reference (SceneBasic::Update + Render) on the scene; returns the parsed dump."""
     with tempfile.TemporaryDirectory() as tmp:
         fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
-        write_scene_input(fin, scene, cameras, frames, options, root_translate)
+        write_scene_input(fin, scene, cameras, frames, options, root_translate, volumes)
         subprocess.run([harness_path(kind), "scene", fin, fout], check=True, stdout=subprocess.DEVNULL)
         return read_scene_output(fout, with_instances=bool(options & OPT_INSTANCES))
 

@@ -32,6 +32,7 @@ EXPORTS = [
     "rn_transform_inverse", "rn_bounds_update", "rn_scene_device_extras", "rn_cull_sort",
     "rn_scenevis_default_volume_order", "rn_particles_build_mesh", "rn_particles_download_mesh",
     "rn_cull_pack_instances", "rn_camera_build_matrices",
+    "rn_scenevis_set_node_volumes", "rn_scenevis_set_camera_volumes", "rn_scenevis_choose_volume",
     "rn_particles_expand_billboards", "rn_particles_download_clip",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
@@ -186,6 +187,15 @@ def render_order(parent: np.ndarray, priority: np.ndarray | None = None) -> np.n
     return order
 
 
+def choose_volume(bounds: np.ndarray, camera_position) -> int:
+    """rn_scenevis_choose_volume: index + 1 of the first AxisAlignedBoxVolume containing the position, 0 = none."""
+    b = _f32(np.asarray(bounds, np.float32).reshape(-1, 6))
+    p = _f32(camera_position).reshape(3)
+    out = C.c_uint8()
+    _check(load().rn_scenevis_choose_volume(_ptr(b), C.c_uint32(b.shape[0]), _ptr(p), C.byref(out)))
+    return int(out.value)
+
+
 def vislist_order(parent: np.ndarray) -> np.ndarray:
     """rn_scenevis_default_volume_order: order[rank] = creation index (SceneWithVisibilityLists default volume)."""
     lib = load()
@@ -199,8 +209,19 @@ class RankedScene:
     """A scenegen.Scene re-ordered into the reference's render-list order (what a Scene subclass hands over).
     vislists=True: the default-volume order of SceneWithVisibilityLists instead of SceneBasic's render list."""
 
-    def __init__(self, scene: Scene, vislists: bool = False):
+    def __init__(self, scene: Scene, vislists: bool = False, volume_of_node: np.ndarray | None = None):
         self.order = vislist_order(scene.parent) if vislists else render_order(scene.parent, scene.priority)
+        self.volume = None
+        if volume_of_node is not None:
+            # SceneWithVisibilityLists with user volumes: the default volume's nodes in its order, then every volume's
+            # nodes in the order of its `nodes` vector (creation order here); self.volume = volume of every rank
+            assert vislists
+            vol = np.asarray(volume_of_node, dtype=np.uint8)
+            parts = [self.order[vol[self.order] == 0]]
+            for k in sorted(set(int(v) for v in np.unique(vol)) - {0}):
+                parts.append(np.nonzero(vol == k)[0].astype(np.uint32))
+            self.order = np.concatenate(parts).astype(np.uint32)
+            self.volume = np.ascontiguousarray(vol[self.order])
         self.rank_of = np.empty(scene.n, dtype=np.uint32)                # creation id -> rank
         self.rank_of[self.order] = np.arange(scene.n, dtype=np.uint32)
         o = self.order
@@ -313,6 +334,17 @@ class SceneHandle:
         v = _f32(view).reshape(16); pv = _f32(proj_view).reshape(16)
         _check(self.lib.rn_cull_pack_instances(self._h, C.c_uint32(camera), _ptr(v), _ptr(pv), C.c_void_p(device_out),
                                                C.c_uint32(capacity), C.c_void_p(stream)))
+
+    def set_node_volumes(self, volume_of_rank: np.ndarray, first: int = 0) -> None:
+        v = np.ascontiguousarray(volume_of_rank, dtype=np.uint8)
+        _check(self.lib.rn_scenevis_set_node_volumes(self._h, _ptr(v), C.c_uint32(first), C.c_uint32(v.shape[0])))
+
+    def set_camera_volumes(self, volume_per_camera) -> None:
+        if volume_per_camera is None:
+            _check(self.lib.rn_scenevis_set_camera_volumes(self._h, None, 0))
+            return
+        v = np.ascontiguousarray(volume_per_camera, dtype=np.uint8)
+        _check(self.lib.rn_scenevis_set_camera_volumes(self._h, _ptr(v), C.c_uint32(v.shape[0])))
 
     def build_masks(self, stream: int = 0) -> None:
         _check(self.lib.rn_cull_build_masks(self._h, C.c_void_p(stream)))

@@ -12,6 +12,8 @@
 //
 // Compiled with -fmad=false like the rest of the library (rn_math.cuh).
 #include "rn_internal.h"
+#include <vector>
+#include <string.h>
 #include "rn_math.cuh"
 
 #include <cstring>
@@ -258,8 +260,81 @@ int aabb_filter_launch(rn_scene *s, const rn_camera_frustum *cams, uint32_t ncam
 	return RN_OK;
 }
 
+// SceneWithVisibilityLists::Render (Source/Scene/RNSceneWithVisibilityLists.cpp:157-175): a camera submits the default
+// volume's nodes and then those of the first volume that contains its position.  With the nodes uploaded as
+// [default volume][volume 1][volume 2]... the list of the cull over ALL nodes, minus the entries of the volumes the
+// camera is not in, is exactly that sequence.  One warp per tile, same recount as the AABB filter.
+struct VolumeCams
+{
+	uint32_t keep[8];      // 256 bits per camera would be overkill: keep[c] = the volume id camera c may see besides 0
+	uint32_t ncams;
+};
+
+__global__ void __launch_bounds__(256) volume_filter_kernel(const __grid_constant__ ExtraView v, const uint8_t *__restrict__ node_volume,
+                                                            const __grid_constant__ VolumeCams vc)
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if(tile >= v.n_tiles)
+		return;
+	const uint32_t start = v.tiles[tile].start, count = v.tiles[tile].count;
+	uint32_t total[RN_MAX_CAMERAS];
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) total[c] = 0;
+	for(uint32_t j0 = 0; j0 < count; j0 += 32)
+	{
+		const bool active = j0 + lane < count;
+		const uint32_t slot = start + j0 + lane;
+		uint32_t mask = active ? v.vis[slot] : 0u;
+		if(mask)
+		{
+			const uint32_t vol = node_volume[slot];
+			if(vol)
+			{
+				uint32_t allowed = 0;
+#pragma unroll
+				for(int c = 0; c < RN_MAX_CAMERAS; c++)
+					if(vc.keep[c] == vol) allowed |= 1u << c;
+				if((mask & allowed) != mask)
+				{
+					mask &= allowed;
+					v.vis[slot] = (uint8_t)mask;
+				}
+			}
+		}
+#pragma unroll
+		for(int c = 0; c < RN_MAX_CAMERAS; c++)
+			total[c] += __popc(__ballot_sync(0xffffffffu, (mask >> c) & 1u));
+	}
+	uint32_t mine = 0;
+#pragma unroll
+	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+		if(lane == (uint32_t)c) mine = total[c];
+	if(lane < RN_MAX_CAMERAS)
+	{
+		v.tile_counts[tile * RN_MAX_CAMERAS + lane] = mine;
+		if(mine)
+			atomicAdd(&v.super_totals[(tile / kSuperTiles) * RN_MAX_CAMERAS + lane], mine);
+	}
+}
+
+int volume_filter_launch(rn_scene *s, uint32_t ncams, cudaStream_t stream)
+{
+	VolumeCams vc;
+	memset(&vc, 0, sizeof(vc));
+	vc.ncams = ncams;
+	for(uint32_t c = 0; c < RN_MAX_CAMERAS; c++)
+		vc.keep[c] = c < ncams && s->cam_volume[c] ? s->cam_volume[c] : 0x100u;   // 0x100: matches no node
+	volume_filter_kernel<<<(s->n_tiles + 7) / 8, 256, 0, stream>>>(make_extra_view(s), s->node_volume, vc);
+	s->launches++;
+	RN_CUDA(cudaGetLastError());
+	return RN_OK;
+}
+
 void extras_free(rn_scene *s)
 {
+	if(s->node_volume) { cudaFree(s->node_volume); s->node_volume = nullptr; }
+	s->volumes_on = false;
 	void *ptrs[] = {s->box0, s->box1, s->winv, s->bsphere, s->baabb, s->prio_group, s->sort_scratch, s->sort_hist, s->sort_ranges,
 	                s->rank_masks, s->expand_totals};
 	for(void *p : ptrs)
@@ -332,5 +407,44 @@ extern "C" int rn_scene_device_extras(rn_scene_t *s, const float **inverse_world
 	if(inverse_world_matrix) *inverse_world_matrix = s->have_inverse ? reinterpret_cast<const float *>(s->winv) : nullptr;
 	if(bounding_sphere) *bounding_sphere = s->have_bounds ? reinterpret_cast<const float *>(s->bsphere) : nullptr;
 	if(bounding_box) *bounding_box = s->have_bounds ? reinterpret_cast<const float *>(s->baabb) : nullptr;
+	return RN_OK;
+}
+
+extern "C" int rn_scenevis_set_node_volumes(rn_scene_t *s, const uint8_t *volume_of_rank, uint32_t first, uint32_t count)
+{
+	RN_REQUIRE(s && volume_of_rank, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE((uint64_t)first + count <= s->n, RN_ERR_INVALID, "ranks [%u, %u) outside the %u uploaded nodes", first, first + count, s->n);
+	RN_CUDA(cudaSetDevice(s->device));
+	const bool fresh = !s->node_volume;
+	if(fresh)
+	{
+		int rc = dev_alloc(s, &s->node_volume, (size_t)s->desc.max_nodes);
+		if(rc) return rc;
+		RN_CUDA(cudaMemset(s->node_volume, 0, s->desc.max_nodes));
+	}
+	if(count == 0)
+		return RN_OK;
+	// rank order -> slot order through the host mirror; a tile is a rank range AND a slot range, so the touched slots are
+	// the range [min slot, max slot] plus untouched neighbours that are re-written with their old value: copy back first
+	std::vector<uint8_t> all(s->n, 0);
+	if(!fresh)
+		RN_CUDA(cudaMemcpy(all.data(), s->node_volume, s->n, cudaMemcpyDeviceToHost));
+	for(uint32_t k = 0; k < count; k++)
+		all[s->slot_of_rank[first + k]] = volume_of_rank[k];
+	RN_CUDA(cudaMemcpy(s->node_volume, all.data(), s->n, cudaMemcpyHostToDevice));
+	return RN_OK;
+}
+
+extern "C" int rn_scenevis_set_camera_volumes(rn_scene_t *s, const uint8_t *volume_per_camera, uint32_t n_cameras)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	RN_REQUIRE(n_cameras <= RN_MAX_CAMERAS, RN_ERR_INVALID, "%u cameras, at most %u", n_cameras, (unsigned)RN_MAX_CAMERAS);
+	memset(s->cam_volume, 0, sizeof(s->cam_volume));
+	s->volumes_on = volume_per_camera != nullptr;
+	if(volume_per_camera)
+	{
+		RN_REQUIRE(s->node_volume, RN_ERR_STATE, "rn_scenevis_set_node_volumes has not been called");
+		for(uint32_t c = 0; c < n_cameras; c++) s->cam_volume[c] = volume_per_camera[c];
+	}
 	return RN_OK;
 }

@@ -430,3 +430,23 @@ extern "C" int rn_scenevis_default_volume_order(uint32_t n, const int32_t *paren
 	RN_REQUIRE(r == n, RN_ERR_INVALID, "internal error: %u of %u nodes ordered", r, n);
 	return RN_OK;
 }
+
+// SceneWithVisibilityLists::Render picks, per camera, the FIRST volume whose ContainsPosition is true
+// (RNSceneWithVisibilityLists.cpp:157-166); AxisAlignedBoxVolume::ContainsPosition (:34-37) is the closed box test.
+extern "C" int rn_scenevis_choose_volume(const float *bounds, uint32_t n_volumes, const float *camera_world_position, uint8_t *out_volume)
+{
+	RN_REQUIRE((bounds || n_volumes == 0) && camera_world_position && out_volume, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(n_volumes <= 254, RN_ERR_INVALID, "%u volumes, at most 254", n_volumes);
+	const float x = camera_world_position[0], y = camera_world_position[1], z = camera_world_position[2];
+	*out_volume = 0;
+	for(uint32_t k = 0; k < n_volumes; k++)
+	{
+		const float *b = bounds + (size_t)k * 6;
+		if(z >= b[2] && y >= b[1] && x >= b[0] && x <= b[3] && y <= b[4] && z <= b[5])
+		{
+			*out_volume = (uint8_t)(k + 1);
+			break;
+		}
+	}
+	return RN_OK;
+}

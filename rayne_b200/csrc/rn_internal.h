@@ -95,6 +95,9 @@ struct rn_scene
 	uint32_t *sort_hist = nullptr;
 	uint32_t *sort_ranges = nullptr;   // [RN_MAX_CAMERAS][2]: transparent range begin, end (device)
 	uint32_t sort_blocks_cap = 0;
+	uint8_t *node_volume = nullptr;    // per slot: 0 = default volume, 1..254 = user volume, 255 = in no volume (rn_bounds.cu)
+	uint8_t cam_volume[RN_MAX_CAMERAS] = {};   // per camera of the next culls: the user volume that contains it, 0 = none
+	bool volumes_on = false;
 	uint32_t *rank_masks = nullptr;    // [RN_MAX_CAMERAS][ceil(max_nodes / 32)] visibility bits in rank order (rn_masks.cu)
 	bool have_masks = false;
 	uint32_t mask_ncams = 0;
@@ -125,6 +128,9 @@ void extras_free(rn_scene *scene);      // rn_bounds.cu / rn_sort.cu storage
 // Extension RN_CAMERA_TEST_AABB: clears the visibility bits of the flagged cameras for nodes whose transformed AABB
 // fails the plane test and recounts tile_counts / super_totals (between the cull kernel and the emit kernel).
 int aabb_filter_launch(rn_scene *scene, const rn_camera_frustum *cams, uint32_t ncams, cudaStream_t stream);
+// SceneWithVisibilityLists volumes: keeps camera c's bit only for nodes of the default volume or of the volume chosen for
+// c, recounts like the AABB filter.
+int volume_filter_launch(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
 
 template <class T>
 inline int dev_alloc(rn_scene *s, T **p, size_t count)

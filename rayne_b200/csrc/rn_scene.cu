@@ -1364,6 +1364,9 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	}
 	else if(s->prio_group) { cudaFree(s->prio_group); s->prio_group = nullptr; }
 	s->have_inverse = s->have_bounds = false;
+	// a full upload re-tiles the scene: volume assignments (slot order) of an earlier upload are void
+	if(s->node_volume) { cudaFree(s->node_volume); s->node_volume = nullptr; }
+	s->volumes_on = false;
 
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
@@ -1516,6 +1519,11 @@ static int cull_stored(rn_scene *s, const rn_camera_frustum *cameras, uint32_t n
 		rc = clear_super_totals(s, stream);
 		if(!rc) rc = aabb_filter_launch(s, cameras, n_cameras, stream);
 	}
+	if(!rc && s->volumes_on)
+	{
+		rc = clear_super_totals(s, stream);
+		if(!rc) rc = volume_filter_launch(s, n_cameras, stream);
+	}
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->last_ncams = n_cameras;
@@ -1564,6 +1572,11 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	rc = clear_super_totals(s, stream);
 	if(!rc) rc = launch_spine(s, stream);
 	if(!rc) rc = launch_tiles<true>(s, cp, stream);
+	if(!rc && s->volumes_on)
+	{
+		rc = clear_super_totals(s, stream);
+		if(!rc) rc = volume_filter_launch(s, n_cameras, stream);
+	}
 	if(!rc) rc = launch_compaction(s, n_cameras, stream);
 	if(rc) return rc;
 	s->have_world = true;

@@ -66,6 +66,19 @@ def main() -> None:
             out[f"ref_vis_list{c}"] = lst
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
         print(name, scene.n, [len(l) for l in ref["lists"]])
+    # SceneWithVisibilityLists with user volumes (AddVolume + the camera-position choice of Render): three
+    # AxisAlignedBoxVolumes, the second of the overlapping ones never chosen where the first contains the camera
+    scene = sg.make_scene(n_trees=6, branching=3, depth=5, seed=77, random_bounds=True, random_groups=True)
+    vol = np.random.default_rng(5).choice([0, 0, 0, 1, 2, 3], size=scene.n).astype(np.uint32)
+    bounds = np.float32([[-5, -5, -5, 5, 5, 5], [5, 0, -10, 20, 10, 5], [-1000, -1000, -1000, 1000, 1000, 1000]])
+    cams = np.concatenate([standard_cameras(), np.stack([sg.make_camera(pos=(5000, 0, 0), far=9000)])])
+    ref = refio.run_scene(scene, cams, options=refio.OPT_VISLISTS | refio.OPT_VOLUMES, volumes=(bounds, vol))
+    out = {f"in_{k}": getattr(scene, k) for k in SCENE_COLS}
+    out.update(in_cameras=cams, in_volume=vol, in_bounds=bounds, ref_default_order=ref["order"])
+    for c, lst in enumerate(ref["lists"]):
+        out[f"ref_list{c}"] = lst
+    np.savez_compressed(os.path.join(HERE, "volumes_basic.npz"), **out)
+    print("volumes_basic", scene.n, [len(l) for l in ref["lists"]])
     for name, (kw, steps) in PARTICLES.items():
         kw = dict(kw)
         em = sg.make_emitters(kw.pop("n"), **kw)

@@ -201,3 +201,31 @@ def test_oracle_billboard_vertex_stage():
     ident = np.eye(4, dtype=np.float32).reshape(16)
     q, _ = oracle.billboards(centre, np.ones((4, 4), np.float32), corners, ident, ident, np.ones(4, np.float32))
     assert np.array_equal(q[:, :3], centre + np.concatenate([corners, np.zeros((4, 1), np.float32)], axis=1))
+
+
+def _volumes_fixture():
+    g = np.load(os.path.join(GOLDEN_DIR, "volumes_basic.npz"))
+    scene = sg.Scene(**{k: g["in_" + k] for k in ("parent", "pos", "scale", "rot", "flags", "group", "priority", "sphere")})
+    return scene, g["in_cameras"], g["in_volume"], g["in_bounds"], g
+
+
+def test_volumes_match_golden():
+    """SceneWithVisibilityLists with AddVolume: default-volume order after the move, the first-containing-volume choice
+    (closed box test, library and restatement), and per camera default volume ++ chosen volume - against the lists
+    the reference's Render submitted."""
+    scene, cams, vol, bounds, g = _volumes_fixture()
+    rs = capi.RankedScene(scene, vislists=True, volume_of_node=vol)
+    nd = int((vol == 0).sum())
+    assert np.array_equal(rs.order[:nd], g["ref_default_order"])
+    chosen = [oracle.choose_volume(bounds, c["pos"]) for c in cams]
+    assert chosen == [capi.choose_volume(bounds, c["pos"]) for c in cams]
+    assert set(chosen) == {0, 1, 2, 3}                  # volume 3 contains everything but is only the first match far out
+    ref = oracle.scene_reference(scene, oracle.frustums(cams), vislists=True)
+    for c in range(len(cams)):
+        want = oracle.volume_lists(rs.order, vol, chosen[c], ref["lists"][c])
+        assert np.array_equal(want, g[f"ref_list{c}"]), f"camera {c}"
+    # closed bounds, first match wins
+    b = np.float32([[0, 0, 0, 1, 1, 1], [0, 0, 0, 2, 2, 2]])
+    for p, want in (((1, 1, 1), 1), ((0, 0, 0), 1), ((1.5, 1, 1), 2), ((2.0001, 1, 1), 0), ((-0.0001, 0.5, 0.5), 0)):
+        assert capi.choose_volume(b, p) == want == oracle.choose_volume(b, p)
+    assert capi.choose_volume(np.zeros((0, 6), np.float32), (0, 0, 0)) == 0

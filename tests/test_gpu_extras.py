@@ -339,3 +339,53 @@ def test_particle_billboards_match_oracle():
             t4 = np.concatenate([m["mesh_uv1"][:live].astype(np.float64), np.zeros((live, 2))], axis=1)
             want = (p4 + t4 @ inv_mv[k].reshape(4, 4).astype(np.float64)) @ mvp[k].reshape(4, 4).astype(np.float64)
             assert np.allclose(got["clip_pos"][:live], want, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("rank_mode", [False, True])
+@pytest.mark.parametrize("fused", [True, False])
+def test_volumes_match_golden(rank_mode, fused):
+    """A10 with user volumes: nodes uploaded as [default volume][volume 1][volume 2].., tagged with their volume; every
+    camera gets the first volume containing it; lists == what SceneWithVisibilityLists::Render submitted."""
+    g = np.load(os.path.join(GOLDEN_DIR, "volumes_basic.npz"))
+    scene = sg.Scene(**{k: g["in_" + k] for k in ("parent", "pos", "scale", "rot", "flags", "group", "priority", "sphere")})
+    cams, vol, bounds = g["in_cameras"], g["in_volume"], g["in_bounds"]
+    rs = capi.RankedScene(scene, vislists=True, volume_of_node=vol)
+    fr = capi.build_frustums(cams)
+    chosen = np.array([capi.choose_volume(bounds, c["pos"]) for c in cams], np.uint8)
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        with pytest.raises(capi.RNError):
+            h.set_camera_volumes(chosen[:1])                  # no node volumes yet
+        h.set_node_volumes(rs.volume)
+        if rank_mode:
+            h.set_list_mode(True, 500)
+        ros = h.download(capi.DL_RANK_OF_SLOT)
+        conv = (lambda l: rs.order[l - 500]) if rank_mode else (lambda l: rs.order[ros[l]])
+        plain = None
+        for c0 in range(0, len(cams), capi.RN_MAX_CAMERAS):
+            sub = slice(c0, min(c0 + capi.RN_MAX_CAMERAS, len(cams)))
+            h.set_camera_volumes(chosen[sub])
+            if fused:
+                h.transform_cull(fr[sub])
+            else:
+                h.transform_propagate()
+                h.cull(fr[sub])
+            counts = h.read_counts()
+            for c in range(sub.start, sub.stop):
+                got = conv(h.read_list(c - c0))
+                assert np.array_equal(got, g[f"ref_list{c}"]), f"camera {c}"
+                assert counts[c - c0] == len(got)
+            # masks follow the filtered visibility too
+            h.build_masks()
+            m = h.read_masks()
+            for c in range(sub.start, sub.stop):
+                bits = np.nonzero(np.unpackbits(m[c - c0].view(np.uint8), bitorder="little")[:scene.n])[0]
+                assert np.array_equal(rs.order[bits], g[f"ref_list{c}"])
+            if c0 == 0:
+                h.set_camera_volumes(None)                    # filter off: every volume's nodes are back
+                h.transform_cull(fr[sub])
+                plain = [conv(h.read_list(c)) for c in range(sub.stop - sub.start)]
+        ref = oracle.scene_reference(scene, oracle.frustums(cams), vislists=True)
+        for c, l in enumerate(plain):
+            vis = np.zeros(scene.n, bool); vis[ref["lists"][c]] = True
+            assert np.array_equal(l, rs.order[vis[rs.order]]), f"camera {c} (filter off)"
