@@ -753,7 +753,7 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 #pragma unroll
 		for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			off[c] = s_off[k][c];
-		// 128 ranks per iteration, four consecutive ranks per lane: one warp scan per camera instead of four ballots
+		// 128 ranks per iteration, four consecutive ranks per lane
 		for(uint32_t r0 = 0; r0 < count; r0 += 32 * kEmitUnroll)
 		{
 			const uint32_t r = r0 + lane * kEmitUnroll;
@@ -770,31 +770,48 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 				if(ev.rank_mode)
 					slot[u] = start + r + u + ev.rank_offset;
 			}
+			// per-lane visible counts of ALL cameras at once, one byte per camera (cameras 0-3 in ca, 4-7 in cb): the four
+			// low (high) bits of a mask byte spread to the four bytes of a register by one multiply.  A lane counts at most
+			// 4 and a warp at most 128 per camera, so the packed bytes never carry and ONE pair of warp scans ranks every
+			// camera (instead of one scan per camera).
+			uint32_t ca = 0, cb = 0;
+#pragma unroll
+			for(int u = 0; u < (int)kEmitUnroll; u++)
+			{
+				const uint32_t b = (vv >> (8 * u)) & 0xffu;
+				ca += ((b & 0xfu) * 0x00204081u) & 0x01010101u;
+				cb += ((b >> 4) * 0x00204081u) & 0x01010101u;
+			}
+			uint32_t xa = ca, xb = cb;
+#pragma unroll
+			for(int o = 1; o < 32; o <<= 1)
+			{
+				const uint32_t ya = __shfl_up_sync(0xffffffffu, xa, o), yb = __shfl_up_sync(0xffffffffu, xb, o);
+				if(lane >= (uint32_t)o)
+				{
+					xa += ya;
+					xb += yb;
+				}
+			}
+			const uint32_t ta = __shfl_sync(0xffffffffu, xa, 31), tb = __shfl_sync(0xffffffffu, xb, 31);
+			const uint32_t ea = xa - ca, eb = xb - cb;     // exclusive prefixes, still packed
 #pragma unroll
 			for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			{
 				if((cams >> c) & 1u)
 				{
-					const uint32_t bits = (vv >> c) & 0x01010101u;
-					if(__any_sync(0xffffffffu, bits != 0))
+					const uint32_t sh = 8u * (uint32_t)(c & 3);
+					const uint32_t tot = ((c < 4 ? ta : tb) >> sh) & 0xffu;
+					if(tot)
 					{
-						const uint32_t cnt = __popc(bits);
-						uint32_t x = cnt;
-#pragma unroll
-						for(int o = 1; o < 32; o <<= 1)
-						{
-							const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-							if(lane >= (uint32_t)o)
-								x += y;
-						}
-						uint32_t *out = ev.lists[c] + off[c] + (x - cnt);
+						uint32_t *out = ev.lists[c] + off[c] + (((c < 4 ? ea : eb) >> sh) & 0xffu);
 #pragma unroll
 						for(int u = 0; u < (int)kEmitUnroll; u++)
 						{
-							if((bits >> (8 * u)) & 1u)
+							if((vv >> (8 * u + c)) & 1u)
 								*out++ = slot[u];
 						}
-						off[c] += __shfl_sync(0xffffffffu, x, 31);
+						off[c] += tot;
 					}
 				}
 			}
