@@ -804,13 +804,13 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 					const uint32_t tot = ((c < 4 ? ta : tb) >> sh) & 0xffu;
 					if(tot)
 					{
-						// the lane's entries go to consecutive positions: position of entry u = prefix + visible entries before it
 						uint32_t *out = ev.lists[c] + off[c] + (((c < 4 ? ea : eb) >> sh) & 0xffu);
-						const uint32_t bits = (vv >> c) & 0x01010101u;
-						if(bits & 0x00000001u) out[0] = slot[0];
-						if(bits & 0x00000100u) out[bits & 1u] = slot[1];
-						if(bits & 0x00010000u) out[__popc(bits & 0x00000101u)] = slot[2];
-						if(bits & 0x01000000u) out[__popc(bits & 0x00010101u)] = slot[3];
+#pragma unroll
+						for(int u = 0; u < (int)kEmitUnroll; u++)
+						{
+							if((vv >> (8 * u + c)) & 1u)
+								*out++ = slot[u];
+						}
 						off[c] += tot;
 					}
 				}
