@@ -199,6 +199,7 @@ def run_ours(args) -> dict:
     vis_frac = [float(c) / n for c in counts]
     exch = None
     use_masks = False
+    use_multicast = False
     if world > 1:
         from rayne_b200 import shard
         use_masks = args.exchange == "masks"
@@ -208,17 +209,38 @@ def run_ours(args) -> dict:
             h.build_masks(stream)
             mptr, mwords, _ = h.device_masks()
             mask_t = torch.as_tensor(DevArray(mptr, ncam * mwords), device="cuda")
-            pexch = shard.PipelinedMaskExchange([mwords] * world, ncam)
+            pexch = None
+            if args.exchange_transport == "multicast":
+                try:
+                    pexch = shard.MulticastMaskExchange([mwords] * world, ncam)
+                except Exception as e:                      # no NVLS / no symmetric memory: say so and use NCCL
+                    log(f"[bench] rank {rank}: multicast exchange unavailable ({type(e).__name__}: {e}); using NCCL")
+                # every rank must take the same path: agree on the minimum
+                okt = torch.tensor([1 if pexch is not None else 0], dtype=torch.int32, device="cuda")
+                dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+                if int(okt.item()) == 0:
+                    pexch = None
+            use_multicast = pexch is not None
+            if pexch is None:
+                pexch = shard.PipelinedMaskExchange([mwords] * world, ncam)
         else:
             exch = shard.ListExchange()
             pexch = shard.PipelinedListExchange()
             list_t = [torch.as_tensor(DevArray(lists[c].slots, n), device="cuda") for c in range(ncam)]
 
+    def submit_masks():
+        if use_multicast:
+            # the mask kernel stores through the NVLS multicast address: building the masks IS the gather
+            h.build_masks_multicast(pexch.begin(), pexch.row, stream)
+        else:
+            # the masks go straight into the send buffer of this frame's NCCL gather (no staging copy)
+            h.build_masks_to(pexch.begin().data_ptr(), pexch.row, stream)
+        pexch.submit()
+
     def exchange():
         # the path's only collective, synchronous form: all-gather of the visibility of every view
         if use_masks:
-            h.build_masks(stream)
-            pexch.submit(mask_t)
+            submit_masks()
             return pexch.flush()
         return exch.exchange(count_t, list_t)
 
@@ -228,9 +250,7 @@ def run_ours(args) -> dict:
         h.transform_cull(fr, stream)
         if world > 1:
             if use_masks:
-                # the masks go straight into the send buffer of this frame's gather (no staging copy)
-                h.build_masks_to(pexch.begin().data_ptr(), pexch.row, stream)
-                pexch.submit()
+                submit_masks()
             else:
                 pexch.submit(count_t, list_t)
 
@@ -313,8 +333,12 @@ def run_ours(args) -> dict:
                 pexch.expand(h, gathered, c, starts, out_l, out_c, stream)
         x1.record()
         torch.cuda.synchronize()
-        exchange_info = {"kind": "NCCL all-gather of rank-order visibility bitmasks (rn_cull_build_masks), fixed size, "
-                                 "two frames in flight on a side stream",
+        exchange_info = {"kind": ("rank-order visibility bitmasks stored through the NVLS multicast address by the mask kernel itself "
+                                  "(rn_cull_build_masks_multicast) + a symmetric-memory barrier, two frames in flight"
+                                  if use_multicast else
+                                  "NCCL all-gather of rank-order visibility bitmasks (rn_cull_build_masks), fixed size, "
+                                  "two frames in flight on a side stream"),
+                         "transport": "nvls-multicast" if use_multicast else "nccl",
                          "bytes_per_gpu_and_frame": int(ncam * mwords * 4), "global_list_entries_per_view": tot,
                          "expanded_lists_match_counts_and_ascend": ok,
                          "expand_all_views_ms": x0.elapsed_time(x1) / 5,
@@ -381,8 +405,7 @@ def run_ours(args) -> dict:
             rootpos[:, 0] += np.float32(0.01)
             h.update_nodes(roots, position=rootpos)
             h.transform_cull(fr, stream)
-            h.build_masks_to(pexch.begin().data_ptr(), pexch.row, stream)
-            pexch.submit()
+            submit_masks()
             h.build_masks(stream)
             h.read_masks_into(pinned_masks.data_ptr(), ncam, stream)
             pexch.flush()
@@ -603,6 +626,8 @@ def main():
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
+    ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="nccl",
+                    help="N>1, masks: NCCL all-gather, or multimem stores of the mask kernel through NVLS multicast")
     ap.add_argument("--nccl-ctas", type=int, default=0, help="N>1: cap on NCCL's CTAs per collective (0 = NCCL's default)")
     ap.add_argument("--exchange", choices=("masks", "lists"), default="masks",
                     help="N>1: what the per-frame all-gather ships (rank-order bitmasks, or counts + index lists)")

@@ -243,6 +243,11 @@ int rn_cull_build_masks(rn_scene_t *scene, void *cuda_stream);
 /* The same masks written into DEVICE memory of the caller (e.g. the send buffer of an all-gather): camera c at
  * device_out + c * row_stride_words, row_stride_words >= ceil(nodes / 32); words beyond the scene's are not touched. */
 int rn_cull_build_masks_to(rn_scene_t *scene, uint32_t *device_out, uint32_t row_stride_words, void *cuda_stream);
+/* The same, with `multicast_out` an NVLS MULTICAST address (CUDA multicast object / torch symmetric memory
+ * `multicast_ptr`, pointing at this GPU's block of a buffer that every GPU of the group maps): the kernel stores with
+ * multimem.st, the NVSwitch replicates every word into all GPUs' copies - building the masks IS the all-gather; what
+ * remains is a barrier between the GPUs before the gathered buffer is read.  Only valid on such an address. */
+int rn_cull_build_masks_multicast(rn_scene_t *scene, uint32_t *multicast_out, uint32_t row_stride_words, void *cuda_stream);
 /* Device pointer of the masks (camera c at masks + c * words_per_camera), words per camera = ceil(nodes / 32), and
  * the number of cameras they hold; *masks = NULL before rn_cull_build_masks or after a newer cull. */
 int rn_cull_device_masks(rn_scene_t *scene, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras);

@@ -34,7 +34,7 @@ EXPORTS = [
     "rn_cull_pack_instances", "rn_camera_build_matrices",
     "rn_scenevis_set_node_volumes", "rn_scenevis_set_camera_volumes", "rn_scenevis_choose_volume",
     "rn_particles_expand_billboards", "rn_particles_download_clip",
-    "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
+    "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
 
@@ -351,6 +351,9 @@ class SceneHandle:
 
     def build_masks_to(self, device_out: int, row_stride_words: int, stream: int = 0) -> None:
         _check(self.lib.rn_cull_build_masks_to(self._h, C.c_void_p(device_out), C.c_uint32(row_stride_words), C.c_void_p(stream)))
+
+    def build_masks_multicast(self, multicast_out: int, row_stride_words: int, stream: int = 0) -> None:
+        _check(self.lib.rn_cull_build_masks_multicast(self._h, C.c_void_p(multicast_out), C.c_uint32(row_stride_words), C.c_void_p(stream)))
 
     def device_masks(self):
         """(device pointer, words per camera, cameras) of the rank-order visibility bitmasks."""

@@ -38,7 +38,10 @@ __device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, uint32_t lane
 	return x;
 }
 
-template <uint32_t NCAMS>
+// MULTICAST: `masks` is an NVLS multicast address (one virtual address mapped onto the same buffer of every GPU of
+// the group): a multimem store is replicated by the NVSwitch to all of them, so the kernel that BUILDS the masks also
+// performs the all-gather - every GPU's block lands in every GPU's copy while the warps are still computing.
+template <uint32_t NCAMS, bool MULTICAST>
 __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *__restrict__ vis,
                                                                  const uint32_t *__restrict__ slot_of_rank, uint32_t n,
                                                                  uint32_t words, uint32_t stride, uint32_t *__restrict__ masks)
@@ -93,7 +96,13 @@ __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *
 	{
 		const uint32_t w = warp_bit_transpose(col[c], lane);
 		if(store)
-			masks[(size_t)c * stride + word0 + lane] = w;
+		{
+			uint32_t *dst = masks + (size_t)c * stride + word0 + lane;
+			if(MULTICAST)
+				asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(w) : "memory");
+			else
+				*dst = w;
+		}
 	}
 }
 
@@ -239,21 +248,27 @@ using namespace rn;
 
 static inline uint32_t mask_words(const rn_scene *s) { return (s->n + 31u) / 32u; }
 
-static int build_masks(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t stream)
+template <bool MULTICAST>
+static int build_masks_launch(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t stream)
 {
 	const uint32_t words = mask_words(s);
 	const uint32_t warps = (words + 31) / 32;
 	const uint32_t grid = (warps + kMaskThreads / 32 - 1) / (kMaskThreads / 32);
 	switch(s->last_ncams)
 	{
-#define RN_MASK_CASE(V) case V: rank_mask_kernel<V><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+#define RN_MASK_CASE(V) case V: rank_mask_kernel<V, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
 		RN_MASK_CASE(1) RN_MASK_CASE(2) RN_MASK_CASE(3) RN_MASK_CASE(4) RN_MASK_CASE(5) RN_MASK_CASE(6) RN_MASK_CASE(7)
-		default: rank_mask_kernel<8><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+		default: rank_mask_kernel<8, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
 #undef RN_MASK_CASE
 	}
 	RN_CUDA(cudaGetLastError());
 	s->launches++;
 	return RN_OK;
+}
+
+static int build_masks(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t stream, bool multicast = false)
+{
+	return multicast ? build_masks_launch<true>(s, out, stride, stream) : build_masks_launch<false>(s, out, stride, stream);
 }
 
 extern "C" int rn_cull_build_masks(rn_scene_t *s, void *cuda_stream)
@@ -286,6 +301,17 @@ extern "C" int rn_cull_build_masks_to(rn_scene_t *s, uint32_t *device_out, uint3
 	if(s->n == 0)
 		return RN_OK;
 	return build_masks(s, device_out, row_stride_words, static_cast<cudaStream_t>(cuda_stream));
+}
+
+extern "C" int rn_cull_build_masks_multicast(rn_scene_t *s, uint32_t *multicast_out, uint32_t row_stride_words, void *cuda_stream)
+{
+	RN_REQUIRE(s && multicast_out, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_build_masks_multicast needs a cull");
+	RN_REQUIRE(row_stride_words >= mask_words(s), RN_ERR_INVALID, "row stride %u < %u words per camera", row_stride_words, mask_words(s));
+	RN_CUDA(cudaSetDevice(s->device));
+	if(s->n == 0)
+		return RN_OK;
+	return build_masks(s, multicast_out, row_stride_words, static_cast<cudaStream_t>(cuda_stream), true);
 }
 
 extern "C" int rn_cull_device_masks(rn_scene_t *s, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras)

@@ -331,3 +331,86 @@ class PipelinedMaskExchange:
         out_count.zero_()
         segs = [(gathered[r, camera].data_ptr(), self.words_per_rank[r], int(starts[r])) for r in range(self.world)]
         handle.masks_expand(segs, out_list.data_ptr(), out_list.numel(), out_count.data_ptr(), stream)
+
+
+class MulticastMaskExchange:
+    """The mask exchange with NO collective kernel: the gathered buffer lives in symmetric memory
+    (torch.distributed._symmetric_memory: the same allocation on every GPU of the group, mapped behind one NVLS
+    multicast address), and rn_cull_build_masks_multicast stores every mask word through that address - the NVSwitch
+    replicates it into all GPUs' copies while the kernel is still computing.  What is left of the "all-gather" is a
+    barrier between the GPUs (signal pads of the symmetric memory, one tiny kernel on a side stream), two frames deep
+    like the NCCL variants, so the transform kernel of the next frame never shares the SMs with a collective.
+
+    Buffer: [slots = depth + 1][world][ncams][row] int32; frame i uses slot i % slots.  Ordering contract (same as
+    PipelinedMaskExchange): a consumer of frame j's gathered masks is enqueued on the producing stream before the
+    masks of frame j + 1 are built; then slot reuse is safe, because building frame i waits for the barrier of frame
+    i - depth, which every GPU only reaches after everything it enqueued before building frame i - depth + 1."""
+
+    def __init__(self, words_per_rank, ncams: int, group=None, depth: int = 2):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.torch, self.dist = torch, dist
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.words_per_rank = [int(w) for w in words_per_rank]
+        self.row = max(self.words_per_rank)
+        self.ncams = int(ncams)
+        self.depth = max(1, depth)
+        self.slots = self.depth + 1
+        self.block = self.ncams * self.row                        # words per rank and frame
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.buf = symm.empty(self.slots * self.world * self.block, dtype=torch.int32, device=dev)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        self.multicast_ptr = int(self.hdl.multicast_ptr or 0)
+        if not self.multicast_ptr:
+            raise RuntimeError("no NVLS multicast mapping for the symmetric buffer on this system")
+        self.side = torch.cuda.Stream()
+        self.pending = []
+        self.result = None
+        self._frame = 0
+        torch.cuda.synchronize()
+        self.hdl.barrier(channel=0)                                # every copy is zeroed before the first multicast store
+        torch.cuda.synchronize()
+
+    def begin(self) -> int:
+        """Multicast address of this rank's block of the coming frame (row stride = ``row`` words); the current stream
+        first waits for the barrier of frame i - depth (device side only)."""
+        while len(self.pending) > self.depth - 1:
+            self._retire_one(self.pending.pop(0))
+        k = self._frame % self.slots
+        return self.multicast_ptr + 4 * ((k * self.world + self.rank) * self.block)
+
+    def submit(self):
+        """After rn_cull_build_masks_multicast(begin(), row) on the current stream: the barrier that makes the frame's
+        gathered masks readable, on the side stream."""
+        torch = self.torch
+        k = self._frame % self.slots
+        self._frame += 1
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(ev)
+            self.hdl.barrier(channel=1 + k)
+            done = torch.cuda.Event()
+            done.record()
+        self.pending.append((done, k))
+
+    def _retire_one(self, item):
+        done, k = item
+        self.torch.cuda.current_stream().wait_event(done)
+        self.result = k
+
+    def flush(self):
+        """Current stream waits for every outstanding barrier; returns the newest frame's gathered masks
+        [world, ncams, row] (a view into the symmetric buffer)."""
+        while self.pending:
+            self._retire_one(self.pending.pop(0))
+        if self.result is None:
+            return None
+        k = self.result
+        return self.buf.view(self.slots, self.world, self.ncams, self.row)[k]
+
+    expand = PipelinedMaskExchange.expand
