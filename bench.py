@@ -570,7 +570,8 @@ def run_ours(args) -> dict:
                                "(2 eye + 4 shadow-cascade cameras), every node re-propagated each frame",
                    "nodes_per_gpu": n, "views": ncam, "visible_fraction_per_view": [round(v, 5) for v in vis_frac],
                    "l2": "inputs (1.07 GB of node columns) exceed the 126 MB L2; no flush needed",
-                   "parallelism": (f"node-range sharding x{world}, NCCL all-gather of " + ("visibility bitmasks" if args.exchange == "masks" else "counts + lists")) if world > 1 else "single GPU"},
+                   "parallelism": (f"node-range sharding x{world}, " + ("visibility bitmasks multicast through NVLS by the mask kernel" if use_multicast else
+                                                                          "NCCL all-gather of " + ("visibility bitmasks" if args.exchange == "masks" else "counts + lists"))) if world > 1 else "single GPU"},
         "e2e": {"value": n * world / e2e_ms / 1e3, "unit": "Mnodes/s", "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": int(roots.shape[0] * 16), "d2h_bytes_per_step": int(d2h),
                 "what": ("rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + 6 lists) "

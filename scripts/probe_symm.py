@@ -13,8 +13,7 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=d
 t = symm.empty(world * 1024, dtype=torch.int32, device=torch.device("cuda", local))
 t.fill_(-1)
 hdl = symm.rendezvous(t, dist.group.WORLD)
-print(rank, "multicast_ptr", hex(hdl.multicast_ptr or 0), "buffer_ptrs", [hex(p) for p in hdl.buffer_ptrs], "backend",
-      getattr(hdl, "get_backend", lambda: "?")() if hasattr(hdl, "get_backend") else "?", flush=True)
+print(rank, "multicast_ptr", hex(hdl.multicast_ptr or 0), "buffer_ptrs", [hex(p) for p in hdl.buffer_ptrs], flush=True)
 hdl.barrier(channel=0)
 # every rank writes its block into every peer's buffer through the peer pointers (P2P stores from a torch kernel)
 for p in range(world):
