@@ -627,8 +627,9 @@ def main():
     ap.add_argument("--emitters", type=int, default=1000, help="particle emitters per GPU for the side metric (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
-    ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="nccl",
-                    help="N>1, masks: NCCL all-gather, or multimem stores of the mask kernel through NVLS multicast")
+    ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="multicast",
+                    help="N>1, masks: multimem stores of the mask kernel through NVLS multicast (falls back to NCCL where "
+                         "symmetric memory / NVLS is unavailable), or the NCCL all-gather")
     ap.add_argument("--nccl-ctas", type=int, default=0, help="N>1: cap on NCCL's CTAs per collective (0 = NCCL's default)")
     ap.add_argument("--exchange", choices=("masks", "lists"), default="masks",
                     help="N>1: what the per-frame all-gather ships (rank-order bitmasks, or counts + index lists)")
