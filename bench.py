@@ -489,6 +489,7 @@ def run_ours(args) -> dict:
 
     # ---- the rows next to the headline (§8(f) P6): kernel times on rank 0 ----
     def timed(fn, reps=10):
+        reps = max(1, min(reps, args.extras_reps))
         fn()
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -633,6 +634,7 @@ def main():
     ap.add_argument("--nccl-ctas", type=int, default=0, help="N>1: cap on NCCL's CTAs per collective (0 = NCCL's default)")
     ap.add_argument("--exchange", choices=("masks", "lists"), default="masks",
                     help="N>1: what the per-frame all-gather ships (rank-order bitmasks, or counts + index lists)")
+    ap.add_argument("--extras-reps", type=int, default=10, help="timed repetitions of each side kernel (1 for an ncu capture)")
     ap.add_argument("--no-extras", action="store_true", help="skip the side timings of inverse / bounds / sort / mesh")
     ap.add_argument("--tile-nodes", type=int, default=0, help="rn_scene_desc.tile_nodes (0 = library default)")
     ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")
