@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RN_ABI_VERSION 2
+#define RN_ABI_VERSION 3
 #define RN_MAX_CAMERAS 8          /* views culled by one rn_cull call (stereo + 4 cascades = 6) */
 #define RN_NO_PARENT 0xffffffffu
 
@@ -70,8 +70,15 @@ typedef struct rn_scene_desc {
 	uint32_t tile_unit_nodes;            /* largest subtree kept whole inside a tile (0 = default; 8..tile_nodes).  Smaller
 	                                        units put more subtrees into a tile, which fills the 32-wide passes of
 	                                        every hierarchy level; the nodes above the units go through the spine pre-pass */
-	uint32_t reserved;
+	uint32_t flags;                      /* RN_SCENE_* bits, 0 = defaults */
 } rn_scene_desc;
+/* World MATRICES (rn_transform_propagate / rn_transform_cull, RN_DL_WORLD_MATRIX) are by default evaluated with fused
+ * multiply-adds: one rounding less per term than the reference's strict-FP build, within the 1e-5 relative tolerance
+ * the matrices carry (the reference's own release build, -funsafe-math-optimizations, differs from its strict build in
+ * the same way).  With this flag they follow the reference operation by operation and match its strict-FP build bit
+ * for bit.  World position / rotation / scale, bounding spheres and everything the cull reads are ALWAYS evaluated in
+ * the reference's exact operation order, so visibility lists are bit-identical in both modes. */
+#define RN_SCENE_STRICT_MATRICES (1u << 0)
 
 /* Host node columns in RANK order.  Replaces the per-object state SceneNode keeps
  * (Source/Scene/RNSceneNode.h:204-246: _position/_scale/_rotation, _parent, _flags, _renderGroup,
@@ -152,8 +159,10 @@ void rn_scene_destroy(rn_scene_t *scene);
  * Host arrays are consumed before the call returns. */
 int rn_scene_upload(rn_scene_t *scene, const rn_node_columns *cols, uint32_t first, uint32_t count);
 int rn_scene_update_nodes(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count);
-/* The same on a caller-chosen stream: the staged copy and the scatter kernel are enqueued on `cuda_stream` (the two
- * calls above use the legacy default stream).  Host arrays are still consumed before the call returns. */
+/* The same on a caller-chosen stream: the staged copy and the scatter kernel are only ENQUEUED on `cuda_stream` (the
+ * two calls above run on the default stream and return when the update is complete, so it is visible to later work on
+ * any stream); work that must see the update has to follow on the same stream.  Host arrays are still consumed before
+ * the call returns. */
 int rn_scene_update_nodes_async(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count,
                                 void *cuda_stream);
 int rn_scene_node_count(const rn_scene_t *scene, uint32_t *out_count);
@@ -276,10 +285,24 @@ int rn_masks_expand(rn_scene_t *scene, const rn_mask_segment *segments, uint32_t
  * `device_out` is DEVICE memory of the caller (e.g. an instance / storage buffer mapped through graphics interop),
  * 16-byte aligned, room for `capacity` records; entries beyond `capacity` are not written.  The entry count stays on
  * the device (rn_cull_read_counts).  Needs rn_transform_propagate and rn_transform_inverse.  Asynchronous.
- * LOD selection, the other per-drawable step of Entity::Render, is compiled out in the reference
- * (RN_MODEL_LOD_DISABLED, Source/Rendering/RNModel.h:9) and has no counterpart here. */
+ * LOD selection, the other per-drawable step of Entity::Render, is rn_cull_select_lod below. */
 int rn_cull_pack_instances(rn_scene_t *scene, uint32_t camera, const float *view, const float *proj_view,
                            void *device_out, uint32_t capacity, void *cuda_stream);
+
+/* LOD selection per list entry - EXTENSION: the reference compiles it out (RN_MODEL_LOD_DISABLED 1,
+ * Source/Rendering/RNModel.h:9; Entity::Render then always takes the single stage); this is its #else branch
+ * (Source/Scene/RNEntity.cpp:98-106): lodDistance = |node.worldPosition - lodCamera.worldPosition| / lodCamera.clipFar,
+ * and Model::GetLODStageForDistance (Source/Rendering/RNModel.cpp:260-281): stage 0 if the model has <= 1 stage or
+ * lodDistance <= epsilon, else the first stage with lodDistance <= stage.distance, else the last stage.
+ *   rn_lod_set_models      : model m owns stage_distances[stage_offsets[m] .. stage_offsets[m + 1]) (LODStage::GetDistance, ascending)
+ *   rn_lod_set_node_models : Entity::_model of ranks [first, first + count) as a model index, 0xffff = not an Entity (stage 0);
+ *                            a full rn_scene_upload re-tiles the scene and clears the table - set it again after one
+ *   rn_cull_select_lod     : one byte per entry of `camera`'s list (after rn_cull_sort, in the sorted order) into DEVICE
+ *                            memory of the caller; entries beyond `capacity` are not written.  Asynchronous. */
+int rn_lod_set_models(rn_scene_t *scene, const uint32_t *stage_offsets, const float *stage_distances, uint32_t n_models);
+int rn_lod_set_node_models(rn_scene_t *scene, const uint16_t *model_of_rank, uint32_t first, uint32_t count);
+int rn_cull_select_lod(rn_scene_t *scene, uint32_t camera, const float *lod_camera_world_position, float lod_camera_clip_far,
+                       uint8_t *device_out, uint32_t capacity, void *cuda_stream);
 
 /* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
  * Pure host function; V <= 8 cameras per frame make this negligible. */
@@ -325,7 +348,20 @@ typedef struct rn_emitter_desc {
 	float    start_color[4], end_color[4];
 	float    start_size[2], end_size[2], start_rotation[2], end_rotation[2];
 	float    gravity[3], velocity[3], velocity_min[3], velocity_max[3], position_min[3], position_max[3];
+	uint32_t flags;                   /* RN_EMITTER_DESC_* */
+	uint32_t max_particles_soft;      /* with RN_EMITTER_DESC_SOFT_MAX: SetMaxParticlesSoft (Source/Scene/RNParticleEmitter.cpp:128-132) */
+	float    world_position[3];       /* with RN_EMITTER_DESC_NONLOCAL: the emitter node's GetWorldPosition() ... */
+	float    world_scale[3];          /* ... and GetWorldScale() at spawn time (rn_particles_set_emitter_transforms updates them) */
 } rn_emitter_desc;
+/* !GetIsLocal() (Source/Scene/RNParticleEmitter.cpp:428-437): new particles are created in WORLD space - position scaled by
+ * the emitter's world scale and moved to its world position, velocity and the particle's own gravity scaled, sizes
+ * scaled by the largest scale component.  Costs 16 B more per particle and step (the per-particle gravity column). */
+#define RN_EMITTER_DESC_NONLOCAL (1u << 0)
+/* max_particles_soft is a soft maximum distinct from max_particles.  As in the reference (:204-205) the spawn count is
+ * min(soft - live, spawn) in UNSIGNED arithmetic: with more live particles than the soft maximum the difference wraps
+ * and the emitter spawns unbounded; here spawning additionally stops at max_particles_per_emitter, the storage a
+ * segment has (rn_particles_counts reports such an emitter through RN_ERR_CAPACITY). 0 = no limit, as in the reference. */
+#define RN_EMITTER_DESC_SOFT_MAX (1u << 1)
 
 typedef enum rn_particle_field {
 	RN_PF_POSITION = 0,   /* 3 floats */
@@ -333,11 +369,17 @@ typedef enum rn_particle_field {
 	RN_PF_TIMING   = 2,   /* 3 floats: time, lifespan, duration */
 	RN_PF_RANGES   = 3,   /* 4 floats: size start, size end, rotation start, rotation end */
 	RN_PF_DERIVED  = 4,   /* 7 floats: rotation, size x, size y, color r, g, b, a */
-	RN_PF_SORTED   = 5    /* 1 uint32: per-emitter depth-sorted particle indices (after rn_particles_sort) */
+	RN_PF_SORTED   = 5,   /* 1 uint32: per-emitter depth-sorted particle indices (after rn_particles_sort) */
+	RN_PF_GRAVITY  = 6    /* 3 floats: GenericParticle::gravity (the emitter's for local emitters, scaled at spawn otherwise) */
 } rn_particle_field;
 
 /* (Re)creates `count` emitters with no live particles (new GenericParticleEmitter + Seed). */
 int rn_particles_configure(rn_scene_t *scene, const rn_emitter_desc *emitters, uint32_t count);
+/* SetMaxParticlesSoft / the emitter node's world transform for emitters [first, first + count): host arrays of count (x3)
+ * values, NULL = leave.  Takes effect with the next rn_particles_step (synchronous, tiny). */
+int rn_particles_set_soft_max(rn_scene_t *scene, uint32_t first, uint32_t count, const uint32_t *max_particles_soft);
+int rn_particles_set_emitter_transforms(rn_scene_t *scene, uint32_t first, uint32_t count, const float *world_position,
+                                        const float *world_scale);
 /* ParticleEmitter::UpdateParticles for every emitter (Source/Scene/RNParticleEmitter.cpp:180-211):
  * integrate/age/interpolate, order-preserving kill, spawn with the emitter's own MT19937 stream. */
 int rn_particles_step(rn_scene_t *scene, float delta, void *cuda_stream);

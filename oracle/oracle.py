@@ -233,7 +233,8 @@ def scene_reference(scene: Scene, frustum_records: np.ndarray, cameras: np.ndarr
 
 class Emitters:
     def __init__(self, emitters: np.ndarray):
-        self.em = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+        from rayne_b200.scenegen import upgrade_emitters
+        self.em = np.ascontiguousarray(upgrade_emitters(emitters), dtype=EMITTER_DTYPE)
         self.n = self.em.shape[0]
         self.h = C.c_void_p(load().rn_oracle_emitters_create(_p(self.em), C.c_uint32(self.n)))
 
@@ -241,9 +242,18 @@ class Emitters:
         for _ in range(steps):
             load().rn_oracle_emitters_step(self.h, C.c_uint32(self.n), C.c_float(delta))
 
+    def set_soft_max(self, k: int, soft: int) -> None:
+        load().rn_oracle_emitter_set_soft_max(self.h, C.c_uint32(k), C.c_uint32(soft))
+
+    def set_transform(self, k: int, world_position=None, world_scale=None) -> None:
+        wp = None if world_position is None else np.ascontiguousarray(world_position, np.float32)
+        ws = None if world_scale is None else np.ascontiguousarray(world_scale, np.float32)
+        load().rn_oracle_emitter_set_transform(self.h, C.c_uint32(k), _p(wp) if wp is not None else None,
+                                               _p(ws) if ws is not None else None)
+
     def read(self, k: int):
         t = C.c_float()
-        cap = int(self.em["max_particles"][k]) + 1
+        cap = int(load().rn_oracle_emitter_read(self.h, C.c_uint32(k), None, C.c_uint32(0), C.byref(t))) + 1
         rec = np.zeros((cap, REC), np.float32)
         cnt = load().rn_oracle_emitter_read(self.h, C.c_uint32(k), _p(rec), C.c_uint32(cap), C.byref(t))
         return rec[:cnt].copy(), np.float32(t.value)
@@ -276,3 +286,16 @@ class Emitters:
             self.close()
         except Exception:
             pass
+
+
+def select_lod(ids: np.ndarray, wpos: np.ndarray, model_of_node: np.ndarray, stage_offsets: np.ndarray, stage_distances: np.ndarray,
+               cam_pos, clip_far: float) -> np.ndarray:
+    """LOD stage per list entry (extension, see rn_oracle_select_lod); ids index wpos / model_of_node."""
+    ids = np.ascontiguousarray(ids, np.uint32); wpos = np.ascontiguousarray(wpos, np.float32)
+    mo = np.ascontiguousarray(model_of_node, np.uint16)
+    so = np.ascontiguousarray(stage_offsets, np.uint32); sd = np.ascontiguousarray(stage_distances, np.float32)
+    cam = np.ascontiguousarray(cam_pos, np.float32)
+    out = np.zeros(ids.shape[0], np.uint8)
+    load().rn_oracle_select_lod(_p(ids), C.c_uint32(ids.shape[0]), _p(wpos), _p(mo), _p(so), _p(sd), C.c_uint32(so.shape[0] - 1),
+                                _p(cam), C.c_float(clip_far), _p(out))
+    return out

@@ -493,6 +493,9 @@ namespace
 		float startColor[4], endColor[4];
 		float startSize[2], endSize[2], startRotation[2], endRotation[2];
 		float gravity[3], velocity[3], velMin[3], velMax[3], posMin[3], posMax[3];
+		uint32_t flags;                // bit 0: SetIsLocal(false); bit 1: SetMaxParticlesSoft(maxParticlesSoft)
+		uint32_t maxParticlesSoft;
+		float worldPosition[3], worldScale[3];
 	};
 
 	// options: the emitter switches UpdateMesh looks at (Source/Scene/RNParticleEmitter.cpp:229,235) + "dump the mesh"
@@ -503,6 +506,7 @@ namespace
 		uint32_t nEmitters, nSteps;
 		float delta;
 		uint32_t options;
+		uint32_t softAfterSteps;       // SetMaxParticlesSoft is applied after this many steps (0 = at creation)
 		std::vector<EmitterDesc> emitters;
 	};
 
@@ -511,8 +515,9 @@ namespace
 		Reader r(path);
 		ParticleInput in;
 		uint32_t magic = r.get<uint32_t>(); uint32_t version = r.get<uint32_t>();
-		if(magic != 0x49504e52u || version != 2) { fprintf(stderr, "bad particle file\n"); exit(2); }
+		if(magic != 0x49504e52u || version != 3) { fprintf(stderr, "bad particle file\n"); exit(2); }
 		in.nEmitters = r.get<uint32_t>(); in.nSteps = r.get<uint32_t>(); in.delta = r.get<float>(); in.options = r.get<uint32_t>();
+		in.softAfterSteps = r.get<uint32_t>();
 		in.emitters = r.vec<EmitterDesc>(in.nEmitters);
 		return in;
 	}
@@ -541,6 +546,13 @@ namespace
 			e->SetPositionRandomizeMax(Vector3(d.posMax[0], d.posMax[1], d.posMax[2]));
 			e->SetCanRollParticles((in.options & kPOptRoll) != 0);
 			e->SetIsRenderedInversed((in.options & kPOptInversed) != 0);
+			if(d.flags & 1u)
+			{
+				e->SetIsLocal(false);
+				e->SetWorldPosition(Vector3(d.worldPosition[0], d.worldPosition[1], d.worldPosition[2]));
+				e->SetWorldScale(Vector3(d.worldScale[0], d.worldScale[1], d.worldScale[2]));
+			}
+			if((d.flags & 2u) && in.softAfterSteps == 0) e->SetMaxParticlesSoft(d.maxParticlesSoft);
 			scene->AddNode(e);
 			out.push_back(e);
 		}
@@ -552,7 +564,13 @@ namespace
 		ParticleInput in = ReadParticles(inPath);
 		HarnessScene *scene = new HarnessScene();
 		std::vector<GenericParticleEmitter *> emitters = BuildEmitters(in, scene);
-		for(uint32_t s = 0; s < in.nSteps; s++) scene->Update(in.delta);
+		for(uint32_t s = 0; s < in.nSteps; s++)
+		{
+			if(in.softAfterSteps && s == in.softAfterSteps)
+				for(size_t k = 0; k < emitters.size(); k++)
+					if(in.emitters[k].flags & 2u) emitters[k]->SetMaxParticlesSoft(in.emitters[k].maxParticlesSoft);
+			scene->Update(in.delta);
+		}
 
 		Writer w(outPath);
 		w.put<uint32_t>(0x4f504e52u); w.put<uint32_t>(2); w.put<uint32_t>(in.nEmitters);

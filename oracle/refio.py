@@ -9,7 +9,7 @@ Scene output ("RNSO" v2: + f32 aabb[n,6] (world minExtend, maxExtend) after winv
     head->tail, creation ids); f32 wpos[n,3]; wrot[n,4]; wscale[n,3]; wmat[n,16]; sphere[n,4] (centre, radius);
     u32 has_inv; f32 winv[n,16] if has_inv; per camera: f32 frustum[28] (centre3, radius, 6x(normal3, d) in the
     order left,right,top,bottom,near,far), u32 flags, u32 group, u32 count, u32 list[count] (creation ids)
-Particle input ("RNPI" v2): u32 magic, version, n_emitters, n_steps; f32 delta; u32 options; EMITTER_DTYPE emitters[n]
+Particle input ("RNPI" v3): u32 magic, version, n_emitters, n_steps; f32 delta; u32 options, soft_after_steps; EMITTER_DTYPE emitters[n]
 Particle output ("RNPO" v2): u32 magic, version, n_emitters; per emitter u32 count, f32 time, f32 rec[count,24],
     u32 mesh_max (0 = no mesh); if mesh_max: f32 pos[4m,3], color[4m,4], uv0[4m,2], uv1[4m,2], u16 idx[6m]
 """
@@ -137,12 +137,14 @@ def bench_scene(scene: Scene, cameras: np.ndarray, frames: int, warmup: int,
         return json.loads(r.stdout.strip().splitlines()[-1])
 
 
-def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float, options: int = 0) -> None:
-    emitters = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float, options: int = 0,
+                         soft_after_steps: int = 0) -> None:
+    from rayne_b200.scenegen import upgrade_emitters
+    emitters = np.ascontiguousarray(upgrade_emitters(emitters), dtype=EMITTER_DTYPE)
     with open(path, "wb") as f:
-        f.write(np.array([0x49504E52, 2, emitters.shape[0], steps], dtype="<u4").tobytes())
+        f.write(np.array([0x49504E52, 3, emitters.shape[0], steps], dtype="<u4").tobytes())
         f.write(np.array([delta], dtype="<f4").tobytes())
-        f.write(np.array([options], dtype="<u4").tobytes())
+        f.write(np.array([options, soft_after_steps], dtype="<u4").tobytes())
         f.write(emitters.tobytes())
 
 
@@ -173,10 +175,12 @@ def read_particle_output(path: str) -> list[dict]:
 
 
 def run_particles(emitters: np.ndarray, steps: int, delta: float = 1.0 / 60.0, kind: str = "strict",
-                  options: int = 0) -> list[dict]:
+                  options: int = 0, soft_after_steps: int = 0) -> list[dict]:
+    """soft_after_steps: emitters with EMITTER_SOFT_MAX get SetMaxParticlesSoft only after that many steps (0 = at
+    creation) - lowering the soft maximum below the live count exercises the reference's unsigned wrap."""
     with tempfile.TemporaryDirectory() as tmp:
         fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
-        write_particle_input(fin, emitters, steps, delta, options)
+        write_particle_input(fin, emitters, steps, delta, options, soft_after_steps)
         subprocess.run([harness_path(kind), "particles", fin, fout], check=True, stdout=subprocess.DEVNULL)
         return read_particle_output(fout)
 

@@ -595,6 +595,9 @@ typedef struct
 	float start_color[4], end_color[4];
 	float start_size[2], end_size[2], start_rotation[2], end_rotation[2];
 	float gravity[3], velocity[3], vel_min[3], vel_max[3], pos_min[3], pos_max[3];
+	uint32_t flags;                /* bit 0: !GetIsLocal(); bit 1: max_particles_soft set through SetMaxParticlesSoft */
+	uint32_t max_particles_soft;
+	float world_position[3], world_scale[3];
 } oracle_emitter;
 
 typedef struct
@@ -664,8 +667,22 @@ typedef struct
 	oracle_mt rng;
 	float time;
 	uint32_t count, cap;
+	int grow;
 	float *rec; /* cap * REC */
 } oracle_emitter_state;
+
+/* ParticleEmitter::SetMaxParticlesSoft, Source/Scene/RNParticleEmitter.cpp:128-132 */
+void rn_oracle_emitter_set_soft_max(oracle_emitter_state *s, uint32_t k, uint32_t soft)
+{
+	s[k].e.flags |= 2u;
+	s[k].e.max_particles_soft = soft;
+}
+/* the emitter node's world transform (read by CreateParticle when !GetIsLocal()) */
+void rn_oracle_emitter_set_transform(oracle_emitter_state *s, uint32_t k, const float *world_position, const float *world_scale)
+{
+	if(world_position) memcpy(s[k].e.world_position, world_position, 12);
+	if(world_scale) memcpy(s[k].e.world_scale, world_scale, 12);
+}
 
 oracle_emitter_state *rn_oracle_emitters_create(const oracle_emitter *e, uint32_t n)
 {
@@ -675,6 +692,7 @@ oracle_emitter_state *rn_oracle_emitters_create(const oracle_emitter *e, uint32_
 		s[i].e = e[i];
 		mt_seed(&s[i].rng, e[i].seed);
 		s[i].cap = e[i].max_particles + 1;
+		s[i].grow = 1;
 		s[i].rec = malloc(sizeof(float) * REC * s[i].cap);
 	}
 	return s;
@@ -686,7 +704,7 @@ void rn_oracle_emitters_destroy(oracle_emitter_state *s, uint32_t n)
 }
 
 /* ParticleEmitter::UpdateParticles, Source/Scene/RNParticleEmitter.cpp:180-211;
- * GenericParticleEmitter::CreateParticle :416-454 (isLocal == true) */
+ * GenericParticleEmitter::CreateParticle :416-454 (both branches of GetIsLocal()) */
 void rn_oracle_emitters_step(oracle_emitter_state *s, uint32_t n, float delta)
 {
 	for(uint32_t k = 0; k < n; k++)
@@ -708,13 +726,21 @@ void rn_oracle_emitters_step(oracle_emitter_state *s, uint32_t n, float delta)
 		em->time = fmodf((em->time + delta), e->spawn_rate);
 		if(spawn > 0)
 		{
-			if(e->max_particles > 0)
+			/* :204-205  if(_maxParticles > 0 && _maxParticlesSoft > 0) spawn = std::min(_maxParticlesSoft - size, spawn), uint32 */
+			uint32_t soft = (e->flags & 2u) ? e->max_particles_soft : e->max_particles;
+			if(e->max_particles > 0 && soft > 0)
 			{
-				uint32_t room = e->max_particles - em->count;
+				uint32_t room = soft - em->count;
 				spawn = room < spawn ? room : spawn;
 			}
 			for(uint32_t j = 0; j < spawn; j++)
 			{
+				if(em->count >= em->cap)
+				{
+					/* only reachable through the unsigned wrap above (count > soft): the vector just grows */
+					em->cap *= 2;
+					em->rec = realloc(em->rec, sizeof(float) * REC * em->cap);
+				}
 				float *p = em->rec + (size_t)em->count * REC;
 				memset(p, 0, sizeof(float) * REC);
 				for(int c = 0; c < 3; c++) p[PX + c] = rand_range(&em->rng, fmin_std(e->pos_min[c], e->pos_max[c]), fmax_std(e->pos_min[c], e->pos_max[c]));
@@ -723,6 +749,16 @@ void rn_oracle_emitters_step(oracle_emitter_state *s, uint32_t n, float delta)
 				for(int c = 0; c < 3; c++) p[GR + c] = e->gravity[c];
 				for(int c = 0; c < 3; c++) p[VX + c] = e->velocity[c] + rand_range(&em->rng, fmin_std(e->vel_min[c], e->vel_max[c]), fmax_std(e->vel_min[c], e->vel_max[c]));
 				float sizeScale = 1.0f;
+				if(e->flags & 1u)
+				{
+					/* :428-437  !GetIsLocal() */
+					const float *sc = e->world_scale;
+					sizeScale = fmax_std(fmax_std(sc[0], sc[1]), sc[2]);
+					for(int c = 0; c < 3; c++) p[PX + c] *= sc[c];
+					for(int c = 0; c < 3; c++) p[PX + c] += e->world_position[c];
+					for(int c = 0; c < 3; c++) p[GR + c] *= sc[c];
+					for(int c = 0; c < 3; c++) p[VX + c] *= sc[c];
+				}
 				p[S0] = rand_range(&em->rng, e->start_size[0], e->start_size[1]) * sizeScale;
 				p[S1] = rand_range(&em->rng, e->end_size[0], e->end_size[1]) * sizeScale;
 				p[PD] = lifespan;
@@ -960,5 +996,35 @@ void rn_oracle_billboards(uint32_t n_vertices, const float *pos, const float *co
 			clip_out[v * 4 + i] = mvp[i] * p[0] + mvp[4 + i] * p[1] + mvp[8 + i] * p[2] + mvp[12 + i] * p[3];
 		for(int i = 0; i < 4; i++)
 			color_out[v * 4 + i] = color[v * 4 + i] * ambient[i];
+	}
+}
+
+/* ---- LOD selection (EXTENSION: compiled out in the reference, RN_MODEL_LOD_DISABLED, Source/Rendering/RNModel.h:9) ---- */
+/* The #else branch of Entity::Render, Source/Scene/RNEntity.cpp:98-106:
+ *     lodDistance = GetWorldPosition().GetDistance(distanceCamera->GetWorldPosition()) / distanceCamera->GetClipFar()
+ * and Model::GetLODStageForDistance, Source/Rendering/RNModel.cpp:260-281.  Parity UNPINNED by nature (no live
+ * reference behaviour); this restatement is what the CUDA kernel is checked against.
+ * ids[e] indexes wpos / model_of_node; model 0xffff = not an Entity -> stage 0. */
+void rn_oracle_select_lod(const uint32_t *ids, uint32_t n_entries, const float *wpos, const uint16_t *model_of_node,
+                          const uint32_t *stage_offsets, const float *stage_distances, uint32_t n_models, const float cam[3],
+                          float clip_far, uint8_t *out)
+{
+	for(uint32_t e = 0; e < n_entries; e++)
+	{
+		uint32_t id = ids[e], model = model_of_node[id], stage = 0;
+		if(model < n_models)
+		{
+			uint32_t first = stage_offsets[model], count = stage_offsets[model + 1] - first;
+			float dx = wpos[id * 3] - cam[0], dy = wpos[id * 3 + 1] - cam[1], dz = wpos[id * 3 + 2] - cam[2];
+			float d = sqrtf(dx * dx + dy * dy + dz * dz);
+			d /= clip_far;
+			if(!(count <= 1 || d <= FLT_EPSILON))
+			{
+				stage = count - 1;
+				for(uint32_t i = 0; i < count; i++)
+					if(d <= stage_distances[first + i]) { stage = i; break; }
+			}
+		}
+		out[e] = (uint8_t)stage;
 	}
 }

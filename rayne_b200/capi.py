@@ -20,7 +20,7 @@ DL_WORLD_POSITION, DL_WORLD_ROTATION, DL_WORLD_SCALE, DL_WORLD_MATRIX, DL_SLOT_O
 DL_INVERSE_WORLD_MATRIX, DL_BOUNDING_SPHERE, DL_BOUNDING_BOX = 6, 7, 8
 CAM_SORT_TRANSPARENT_BACK_TO_FRONT, CAM_SORT_FRONT_TO_BACK, CAM_TEST_AABB = 1 << 5, 1 << 6, 1 << 31
 EMITTER_CAN_ROLL, EMITTER_RENDERED_INVERSED = 1, 2
-PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED = range(6)
+PF_POSITION, PF_VELOCITY, PF_TIMING, PF_RANGES, PF_DERIVED, PF_SORTED, PF_GRAVITY = range(7)
 
 EXPORTS = [
     "rn_last_error", "rn_abi_version", "rn_scene_create", "rn_scene_destroy", "rn_scene_upload",
@@ -33,7 +33,8 @@ EXPORTS = [
     "rn_scenevis_default_volume_order", "rn_particles_build_mesh", "rn_particles_download_mesh",
     "rn_cull_pack_instances", "rn_camera_build_matrices",
     "rn_scenevis_set_node_volumes", "rn_scenevis_set_camera_volumes", "rn_scenevis_choose_volume",
-    "rn_particles_expand_billboards", "rn_particles_download_clip",
+    "rn_particles_expand_billboards", "rn_particles_download_clip", "rn_particles_set_soft_max",
+    "rn_particles_set_emitter_transforms", "rn_lod_set_models", "rn_lod_set_node_models", "rn_cull_select_lod",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
@@ -47,7 +48,7 @@ class RNError(RuntimeError):
 class SceneDesc(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_nodes", C.c_uint32), ("tile_nodes", C.c_uint32),
                 ("max_emitters", C.c_uint32), ("max_particles_per_emitter", C.c_uint32), ("tile_inner_nodes", C.c_uint32),
-                ("tile_unit_nodes", C.c_uint32), ("reserved", C.c_uint32)]
+                ("tile_unit_nodes", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class NodeColumns(C.Structure):
@@ -85,7 +86,7 @@ FRUSTUM_DTYPE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("planes", "<
 assert FRUSTUM_DTYPE.itemsize == 120
 # rn_camera_desc has the same layout as scenegen.CAMERA_DTYPE (pos/rot are the WORLD position/rotation)
 assert CAMERA_DTYPE.itemsize == 164
-assert EMITTER_DTYPE.itemsize == 156
+assert EMITTER_DTYPE.itemsize == 188
 
 _lib = None
 
@@ -239,14 +240,20 @@ class RankedScene:
         self.roots = np.nonzero(self.parent == RN_NO_PARENT)[0].astype(np.uint32)
 
 
+SCENE_STRICT_MATRICES = 1 << 0
+
+
 class SceneHandle:
     """Owns one rn_scene_t."""
 
     def __init__(self, max_nodes: int, device: int = 0, tile_nodes: int = 0, max_emitters: int = 0,
-                 max_particles_per_emitter: int = 0, tile_inner_nodes: int = 0, tile_unit_nodes: int = 0):
+                 max_particles_per_emitter: int = 0, tile_inner_nodes: int = 0, tile_unit_nodes: int = 0,
+                 strict_matrices: bool = False):
+        """strict_matrices: RN_SCENE_STRICT_MATRICES - world matrices operation by operation like the reference's
+        strict-FP build (bit-exact) instead of the default fused multiply-adds (within 1e-5)."""
         self.lib = load()
         desc = SceneDesc(device, max_nodes, tile_nodes, max_emitters, max_particles_per_emitter, tile_inner_nodes,
-                         tile_unit_nodes)
+                         tile_unit_nodes, SCENE_STRICT_MATRICES if strict_matrices else 0)
         self._h = C.c_void_p()
         _check(self.lib.rn_scene_create(C.byref(self._h), C.byref(desc)))
         self.max_nodes = max_nodes
@@ -334,6 +341,19 @@ class SceneHandle:
         v = _f32(view).reshape(16); pv = _f32(proj_view).reshape(16)
         _check(self.lib.rn_cull_pack_instances(self._h, C.c_uint32(camera), _ptr(v), _ptr(pv), C.c_void_p(device_out),
                                                C.c_uint32(capacity), C.c_void_p(stream)))
+
+    def lod_set_models(self, stage_offsets, stage_distances) -> None:
+        so = np.ascontiguousarray(stage_offsets, dtype=np.uint32); sd = _f32(stage_distances)
+        _check(self.lib.rn_lod_set_models(self._h, _ptr(so), _ptr(sd), C.c_uint32(so.shape[0] - 1)))
+
+    def lod_set_node_models(self, model_of_rank, first: int = 0) -> None:
+        m = np.ascontiguousarray(model_of_rank, dtype=np.uint16)
+        _check(self.lib.rn_lod_set_node_models(self._h, _ptr(m), C.c_uint32(first), C.c_uint32(m.shape[0])))
+
+    def select_lod(self, camera: int, lod_camera_position, clip_far: float, device_out: int, capacity: int, stream: int = 0) -> None:
+        cp = _f32(lod_camera_position).reshape(3)
+        _check(self.lib.rn_cull_select_lod(self._h, C.c_uint32(camera), _ptr(cp), C.c_float(clip_far), C.c_void_p(device_out),
+                                           C.c_uint32(capacity), C.c_void_p(stream)))
 
     def set_node_volumes(self, volume_of_rank: np.ndarray, first: int = 0) -> None:
         v = np.ascontiguousarray(volume_of_rank, dtype=np.uint8)
@@ -439,9 +459,20 @@ class SceneHandle:
 
     # ---- particles ----
     def particles_configure(self, emitters: np.ndarray) -> None:
-        em = np.ascontiguousarray(emitters, dtype=EMITTER_DTYPE)
+        from .scenegen import upgrade_emitters
+        em = np.ascontiguousarray(upgrade_emitters(emitters), dtype=EMITTER_DTYPE)
         _check(self.lib.rn_particles_configure(self._h, _ptr(em), em.shape[0]))
         self.n_emitters = em.shape[0]
+
+    def particles_set_soft_max(self, soft, first: int = 0) -> None:
+        v = np.ascontiguousarray(soft, dtype=np.uint32)
+        _check(self.lib.rn_particles_set_soft_max(self._h, C.c_uint32(first), C.c_uint32(v.shape[0]), _ptr(v)))
+
+    def particles_set_emitter_transforms(self, world_position=None, world_scale=None, first: int = 0) -> None:
+        wp = None if world_position is None else _f32(world_position, 3)
+        ws = None if world_scale is None else _f32(world_scale, 3)
+        cnt = (wp if wp is not None else ws).shape[0]
+        _check(self.lib.rn_particles_set_emitter_transforms(self._h, C.c_uint32(first), C.c_uint32(cnt), _ptr(wp), _ptr(ws)))
 
     def particles_step(self, delta: float, stream: int = 0) -> None:
         _check(self.lib.rn_particles_step(self._h, C.c_float(delta), C.c_void_p(stream)))
@@ -490,7 +521,8 @@ class SceneHandle:
         cnt = C.c_uint32()
         _check(self.lib.rn_particles_download(self._h, emitter, field, None, 0, C.byref(cnt)))
         width, dt = {PF_POSITION: (3, np.float32), PF_VELOCITY: (3, np.float32), PF_TIMING: (3, np.float32),
-                     PF_RANGES: (4, np.float32), PF_DERIVED: (7, np.float32), PF_SORTED: (1, np.uint32)}[field]
+                     PF_RANGES: (4, np.float32), PF_DERIVED: (7, np.float32), PF_SORTED: (1, np.uint32),
+                     PF_GRAVITY: (3, np.float32)}[field]
         out = np.zeros((cnt.value, width), dtype=dt)
         if cnt.value:
             _check(self.lib.rn_particles_download(self._h, emitter, field, _ptr(out), cnt.value, C.byref(cnt)))

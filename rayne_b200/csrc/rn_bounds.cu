@@ -200,9 +200,12 @@ __global__ void __launch_bounds__(256) aabb_filter_kernel(const __grid_constant_
 	{
 		const bool active = j0 + lane < count;
 		const uint32_t slot = start + j0 + lane;
-		uint32_t mask = active ? v.vis[slot] : 0u;
+		// the mask bytes are stored in rank order: the node's rank offset inside the tile sits in its flags word
+		const uint32_t fw = active ? __float_as_uint(v.c2[slot].w) : 0u;
+		const uint32_t vidx = start + ((fw >> kRankShift) & kRankMask);
+		uint32_t mask = active ? v.vis[vidx] : 0u;
 		const uint32_t todo = mask & ac.test_mask;
-		if(todo && !(__float_as_uint(v.c2[slot].w) & RN_NODE_NOCULLING))
+		if(todo && !(fw & RN_NODE_NOCULLING))
 		{
 			const float4 a = v.wpos[slot], b = v.wrot[slot];
 			const float2 c = v.wsyz[slot];
@@ -228,7 +231,7 @@ __global__ void __launch_bounds__(256) aabb_filter_kernel(const __grid_constant_
 					if(!inside) mask &= ~(1u << cc);
 				}
 			}
-			v.vis[slot] = (uint8_t)mask;
+			v.vis[vidx] = (uint8_t)mask;
 		}
 #pragma unroll
 		for(int c = 0; c < RN_MAX_CAMERAS; c++)
@@ -285,7 +288,8 @@ __global__ void __launch_bounds__(256) volume_filter_kernel(const __grid_constan
 	{
 		const bool active = j0 + lane < count;
 		const uint32_t slot = start + j0 + lane;
-		uint32_t mask = active ? v.vis[slot] : 0u;
+		const uint32_t vidx = start + (active ? (__float_as_uint(v.c2[slot].w) >> kRankShift) & kRankMask : 0u);
+		uint32_t mask = active ? v.vis[vidx] : 0u;
 		if(mask)
 		{
 			const uint32_t vol = node_volume[slot];
@@ -298,7 +302,7 @@ __global__ void __launch_bounds__(256) volume_filter_kernel(const __grid_constan
 				if((mask & allowed) != mask)
 				{
 					mask &= allowed;
-					v.vis[slot] = (uint8_t)mask;
+					v.vis[vidx] = (uint8_t)mask;
 				}
 			}
 		}
@@ -336,9 +340,10 @@ void extras_free(rn_scene *s)
 	if(s->node_volume) { cudaFree(s->node_volume); s->node_volume = nullptr; }
 	s->volumes_on = false;
 	void *ptrs[] = {s->box0, s->box1, s->winv, s->bsphere, s->baabb, s->prio_group, s->sort_scratch, s->sort_hist, s->sort_ranges,
-	                s->rank_masks, s->expand_totals};
+	                s->rank_masks, s->expand_totals, s->lod_node_model, s->lod_stage_ofs, s->lod_stage_dist};
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
+	s->lod_node_model = nullptr; s->lod_stage_ofs = nullptr; s->lod_stage_dist = nullptr; s->lod_models = 0;
 	s->box0 = nullptr; s->box1 = nullptr; s->winv = nullptr; s->bsphere = nullptr; s->baabb = nullptr;
 	s->prio_group = nullptr; s->sort_scratch = s->sort_hist = s->sort_ranges = nullptr;
 	s->rank_masks = s->expand_totals = nullptr;

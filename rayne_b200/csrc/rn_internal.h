@@ -26,6 +26,8 @@ constexpr uint32_t kMaxSublevels = 12;   // sublevel 0 = spine nodes of the tile
 constexpr uint32_t kWarpsPerCta = 4;     // tile kernel: one tile per warp
 constexpr uint32_t kTileThreads = kWarpsPerCta * 32;
 constexpr uint32_t kSuperTiles = 256;    // tiles per superblock of the compaction offsets
+constexpr uint32_t kRankShift = 16;      // c2.w bits 16-25: rank - tile start (the tile kernel stores mask bytes in RANK order)
+constexpr uint32_t kRankMask = 0x3ffu;
 constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 // One tile = a contiguous range of ranks [start, start+count) stored at the same slots, permuted so that each
@@ -58,6 +60,8 @@ struct rn_scene
 	uint32_t spine_nodes = 0;
 	uint64_t device_bytes = 0;
 	uint64_t launches = 0;
+	bool fma_matrices = true;    // world matrices with fused multiply-adds (rn_scene_desc.flags & RN_SCENE_STRICT_MATRICES clears it)
+	size_t tile_smem_configured[4] = {};   // dynamic shared memory opted in per tile_kernel instantiation on THIS device
 	bool have_world = false;     // world TRS valid (a propagate ran since the last upload)
 	uint32_t last_ncams = 0;
 	uint32_t list_rank_mode = 0;     // 1: visibility lists hold rank + list_rank_offset instead of slots
@@ -72,7 +76,7 @@ struct rn_scene
 	float2 *wsyz = nullptr;      // world scale y, z
 	float4 *wmat = nullptr;      // 4 x float4 per slot (column-major 4x4)
 	uint32_t *d_slot_of_rank = nullptr; // rank -> slot
-	uint8_t *vis = nullptr;      // slot -> camera bit mask of the last cull
+	uint8_t *vis = nullptr;      // RANK -> camera bit mask of the last cull (padded to a multiple of 32 bytes, padding zero)
 	rn::TileMeta *tiles = nullptr;
 	uint32_t *tile_counts = nullptr;   // [n_tiles][RN_MAX_CAMERAS] visible nodes per tile (last cull)
 	uint32_t *super_totals = nullptr;  // [n_tiles / 256][RN_MAX_CAMERAS]
@@ -98,6 +102,11 @@ struct rn_scene
 	uint8_t *node_volume = nullptr;    // per slot: 0 = default volume, 1..254 = user volume, 255 = in no volume (rn_bounds.cu)
 	uint8_t cam_volume[RN_MAX_CAMERAS] = {};   // per camera of the next culls: the user volume that contains it, 0 = none
 	bool volumes_on = false;
+	// LOD extension (rn_instances.cu): per slot the model id (0xffff = none), per model its stages' distances
+	uint16_t *lod_node_model = nullptr;
+	uint32_t *lod_stage_ofs = nullptr;
+	float *lod_stage_dist = nullptr;
+	uint32_t lod_models = 0;
 	uint32_t *rank_masks = nullptr;    // [RN_MAX_CAMERAS][ceil(max_nodes / 32)] visibility bits in rank order (rn_masks.cu)
 	bool have_masks = false;
 	uint32_t mask_ncams = 0;

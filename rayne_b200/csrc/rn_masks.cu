@@ -17,92 +17,39 @@ namespace rn {
 
 constexpr uint32_t kMaskThreads = 256;
 
-// One warp builds 32 consecutive words (1024 ranks) of every camera.  Lane L loads the mask bytes of ranks
-// base + 32 i + L for i = 0..31 (coalesced rank -> slot loads, then the byte gathers), regroups its own 32 bytes into
-// one 32-bit column per camera (bit i = iteration i) with a multiply-gather per four bytes, and a 32 x 32 bit-matrix
-// transpose over the warp (five shuffle stages per camera) turns "lane L, bit i" into "lane i, bit L" - word i of
-// that camera.  A ballot per (iteration, camera) gives the same words with 4x the instructions (this kernel is
-// issue-bound, not bandwidth-bound).  Lane i then stores word i of every camera: 128-byte coalesced stores.
-__device__ __forceinline__ uint32_t warp_bit_transpose(uint32_t x, uint32_t lane)
-{
-#pragma unroll
-	for(int k = 0; k < 5; k++)
-	{
-		const uint32_t j = 16u >> k;
-		const uint32_t lo = k == 0 ? 0x0000ffffu : k == 1 ? 0x00ff00ffu : k == 2 ? 0x0f0f0f0fu : k == 3 ? 0x33333333u : 0x55555555u;
-		const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
-		// [[A, B], [C, D]] -> [[A, C], [B, D]]: rows (lanes) with bit j clear take the partner's low columns into their
-		// high columns, rows with bit j set take the partner's high columns into their low columns
-		x = (lane & j) ? ((x & ~lo) | ((y >> j) & lo)) : ((x & lo) | ((y << j) & ~lo));
-	}
-	return x;
-}
-
+// The cull kernels store the mask bytes in RANK order (rn_scene.cu), so word w of camera c is bit c of the 32 bytes
+// [32 w, 32 w + 32): one thread per word loads its 32 bytes (two 128-bit loads; the bytes beyond the node count are
+// kept zero) and gathers bit c of four bytes at a time into a nibble with one multiply.  Consecutive threads store
+// consecutive words: coalesced 128-byte stores.  1 B read and V/8 B written per node.
+//
 // MULTICAST: `masks` is an NVLS multicast address (one virtual address mapped onto the same buffer of every GPU of
 // the group): a multimem store is replicated by the NVSwitch to all of them, so the kernel that BUILDS the masks also
 // performs the all-gather - every GPU's block lands in every GPU's copy while the warps are still computing.
 template <uint32_t NCAMS, bool MULTICAST>
-__global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *__restrict__ vis,
-                                                                 const uint32_t *__restrict__ slot_of_rank, uint32_t n,
-                                                                 uint32_t words, uint32_t stride, uint32_t *__restrict__ masks)
+__global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *__restrict__ vis, uint32_t words, uint32_t stride,
+                                                                 uint32_t *__restrict__ masks)
 {
-	const uint32_t lane = threadIdx.x & 31u;
-	const uint32_t warp = (blockIdx.x * kMaskThreads + threadIdx.x) >> 5;
-	const uint32_t word0 = warp * 32u;
-	if(word0 >= words)
+	const uint32_t w = blockIdx.x * kMaskThreads + threadIdx.x;
+	if(w >= words)
 		return;
-	uint32_t col[NCAMS];
-#pragma unroll
-	for(uint32_t c = 0; c < NCAMS; c++) col[c] = 0;
-	// 16 iterations at a time: all rank -> slot loads, then all mask-byte loads, in flight together
-#pragma unroll 1
-	for(uint32_t i0 = 0; i0 < 32; i0 += 16)
-	{
-		uint32_t slot[16], packed[4];
-#pragma unroll
-		for(uint32_t k = 0; k < 16; k++)
-		{
-			const uint32_t r = (word0 + i0 + k) * 32u + lane;
-			slot[k] = r < n ? __ldg(slot_of_rank + r) : 0xffffffffu;
-		}
-#pragma unroll
-		for(uint32_t g = 0; g < 4; g++)
-		{
-			uint32_t p = 0;
-#pragma unroll
-			for(uint32_t b = 0; b < 4; b++)
-			{
-				const uint32_t s = slot[g * 4 + b];
-				const uint32_t v = s != 0xffffffffu ? (uint32_t)__ldg(vis + s) : 0u;
-				p |= v << (8 * b);
-			}
-			packed[g] = p;
-		}
-		// four iterations per register: bits c, 8 + c, 16 + c, 24 + c -> one nibble, shifted in from the top
-#pragma unroll
-		for(uint32_t g = 0; g < 4; g++)
-		{
-#pragma unroll
-			for(uint32_t c = 0; c < NCAMS; c++)
-			{
-				const uint32_t t = (packed[g] >> c) & 0x01010101u;
-				col[c] = (col[c] >> 4) | ((t * 0x10204080u) & 0xf0000000u);
-			}
-		}
-	}
-	const bool store = word0 + lane < words;
+	const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(vis) + 2u * w), hi = __ldg(reinterpret_cast<const uint4 *>(vis) + 2u * w + 1u);
+	const uint32_t v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
 #pragma unroll
 	for(uint32_t c = 0; c < NCAMS; c++)
 	{
-		const uint32_t w = warp_bit_transpose(col[c], lane);
-		if(store)
+		uint32_t word = 0;
+#pragma unroll
+		for(uint32_t g = 0; g < 8; g++)
 		{
-			uint32_t *dst = masks + (size_t)c * stride + word0 + lane;
-			if(MULTICAST)
-				asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(w) : "memory");
-			else
-				*dst = w;
+			// bits c, 8 + c, 16 + c, 24 + c of v[g] -> bits 28..31 of the product, shifted in from the top
+			const uint32_t t = (v[g] >> c) & 0x01010101u;
+			word = (word >> 4) | ((t * 0x10204080u) & 0xf0000000u);
 		}
+		uint32_t *dst = masks + (size_t)c * stride + w;
+		if(MULTICAST)
+			asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(word) : "memory");
+		else
+			*dst = word;
 	}
 }
 
@@ -252,13 +199,12 @@ template <bool MULTICAST>
 static int build_masks_launch(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t stream)
 {
 	const uint32_t words = mask_words(s);
-	const uint32_t warps = (words + 31) / 32;
-	const uint32_t grid = (warps + kMaskThreads / 32 - 1) / (kMaskThreads / 32);
+	const uint32_t grid = (words + kMaskThreads - 1) / kMaskThreads;
 	switch(s->last_ncams)
 	{
-#define RN_MASK_CASE(V) case V: rank_mask_kernel<V, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+#define RN_MASK_CASE(V) case V: rank_mask_kernel<V, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, words, stride, out); break;
 		RN_MASK_CASE(1) RN_MASK_CASE(2) RN_MASK_CASE(3) RN_MASK_CASE(4) RN_MASK_CASE(5) RN_MASK_CASE(6) RN_MASK_CASE(7)
-		default: rank_mask_kernel<8, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, s->d_slot_of_rank, s->n, words, stride, out); break;
+		default: rank_mask_kernel<8, MULTICAST><<<grid, kMaskThreads, 0, stream>>>(s->vis, words, stride, out); break;
 #undef RN_MASK_CASE
 	}
 	RN_CUDA(cudaGetLastError());

@@ -50,25 +50,50 @@ struct Affine
 // Matrix::WithTranslation(pos); Rotate(rot); Scale(scale)  (reference: Source/Scene/RNSceneNode.cpp:530-532,
 // Source/Math/RNMatrix.h:32-87,544-566; Quaternion::GetRotationMatrix Source/Math/RNQuaternion.h:468-493).
 // The two full 4x4 products reduce exactly to: column c of the rotation matrix times scale_c, translation = pos.
+// FMA = false: the reference's operations one by one (bit-exact with its strict-FP build).
+// FMA = true : the same formula with fused multiply-adds (explicit __fmaf_rn; the TU is built with -fmad=false), one
+//              rounding less per term - within the 1e-5 the north star grants the matrices, like the reference's own
+//              release build (-funsafe-math-optimizations), never used for anything the cull reads.
+template <bool FMA>
 __device__ __forceinline__ Affine local_matrix(const Vec3 &p, const Quat &q, const Vec3 &s)
 {
-	float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
-	float xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w;
-	float yz = q.y * q.z, yw = q.y * q.w, zw = q.z * q.w;
-	float r0 = 1.0f - 2.0f * (yy + zz), r4 = 2.0f * (xy - zw), r8 = 2.0f * (xz + yw);
-	float r1 = 2.0f * (xy + zw), r5 = 1.0f - 2.0f * (xx + zz), r9 = 2.0f * (yz - xw);
-	float r2 = 2.0f * (xz - yw), r6 = 2.0f * (yz + xw), r10 = 1.0f - 2.0f * (xx + yy);
 	Affine a;
-	a.m[0] = r0 * s.x; a.m[1] = r1 * s.x; a.m[2] = r2 * s.x;
-	a.m[3] = r4 * s.y; a.m[4] = r5 * s.y; a.m[5] = r6 * s.y;
-	a.m[6] = r8 * s.z; a.m[7] = r9 * s.z; a.m[8] = r10 * s.z;
+	if(FMA)
+	{
+		const float sx2 = s.x + s.x, sy2 = s.y + s.y, sz2 = s.z + s.z;
+		const float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
+		const float zw = q.z * q.w, yw = q.y * q.w, xw = q.x * q.w;
+		a.m[0] = __fmaf_rn(-sx2, yy + zz, s.x);
+		a.m[1] = sx2 * __fmaf_rn(q.x, q.y, zw);
+		a.m[2] = sx2 * __fmaf_rn(q.x, q.z, -yw);
+		a.m[3] = sy2 * __fmaf_rn(q.x, q.y, -zw);
+		a.m[4] = __fmaf_rn(-sy2, xx + zz, s.y);
+		a.m[5] = sy2 * __fmaf_rn(q.y, q.z, xw);
+		a.m[6] = sz2 * __fmaf_rn(q.x, q.z, yw);
+		a.m[7] = sz2 * __fmaf_rn(q.y, q.z, -xw);
+		a.m[8] = __fmaf_rn(-sz2, xx + yy, s.z);
+	}
+	else
+	{
+		float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z;
+		float xy = q.x * q.y, xz = q.x * q.z, xw = q.x * q.w;
+		float yz = q.y * q.z, yw = q.y * q.w, zw = q.z * q.w;
+		float r0 = 1.0f - 2.0f * (yy + zz), r4 = 2.0f * (xy - zw), r8 = 2.0f * (xz + yw);
+		float r1 = 2.0f * (xy + zw), r5 = 1.0f - 2.0f * (xx + zz), r9 = 2.0f * (yz - xw);
+		float r2 = 2.0f * (xz - yw), r6 = 2.0f * (yz + xw), r10 = 1.0f - 2.0f * (xx + yy);
+		a.m[0] = r0 * s.x; a.m[1] = r1 * s.x; a.m[2] = r2 * s.x;
+		a.m[3] = r4 * s.y; a.m[4] = r5 * s.y; a.m[5] = r6 * s.y;
+		a.m[6] = r8 * s.z; a.m[7] = r9 * s.z; a.m[8] = r10 * s.z;
+	}
 	a.m[9] = p.x; a.m[10] = p.y; a.m[11] = p.z;
 	return a;
 }
+__device__ __forceinline__ Affine local_matrix(const Vec3 &p, const Quat &q, const Vec3 &s) { return local_matrix<false>(p, q, s); }
 
 // Matrix::operator* (reference: Source/Math/RNMatrix.h:90-142) restricted to affine operands:
 // r[c][r] = P[0][r]*L[c][0] + P[1][r]*L[c][1] + P[2][r]*L[c][2] (+ P[3][r] for the translation column),
-// summed left to right like the reference.
+// summed left to right like the reference (FMA = true: the same sums as chains of fused multiply-adds).
+template <bool FMA>
 __device__ __forceinline__ Affine affine_mul(const Affine &P, const Affine &L)
 {
 	Affine o;
@@ -77,13 +102,24 @@ __device__ __forceinline__ Affine affine_mul(const Affine &P, const Affine &L)
 	{
 #pragma unroll
 		for(int r = 0; r < 3; r++)
-			o.m[c * 3 + r] = P.m[r] * L.m[c * 3] + P.m[3 + r] * L.m[c * 3 + 1] + P.m[6 + r] * L.m[c * 3 + 2];
+		{
+			if(FMA)
+				o.m[c * 3 + r] = __fmaf_rn(P.m[6 + r], L.m[c * 3 + 2], __fmaf_rn(P.m[3 + r], L.m[c * 3 + 1], P.m[r] * L.m[c * 3]));
+			else
+				o.m[c * 3 + r] = P.m[r] * L.m[c * 3] + P.m[3 + r] * L.m[c * 3 + 1] + P.m[6 + r] * L.m[c * 3 + 2];
+		}
 	}
 #pragma unroll
 	for(int r = 0; r < 3; r++)
-		o.m[9 + r] = P.m[r] * L.m[9] + P.m[3 + r] * L.m[10] + P.m[6 + r] * L.m[11] + P.m[9 + r];
+	{
+		if(FMA)
+			o.m[9 + r] = __fmaf_rn(P.m[6 + r], L.m[11], __fmaf_rn(P.m[3 + r], L.m[10], __fmaf_rn(P.m[r], L.m[9], P.m[9 + r])));
+		else
+			o.m[9 + r] = P.m[r] * L.m[9] + P.m[3 + r] * L.m[10] + P.m[6 + r] * L.m[11] + P.m[9 + r];
+	}
 	return o;
 }
+__device__ __forceinline__ Affine affine_mul(const Affine &P, const Affine &L) { return affine_mul<false>(P, L); }
 
 // ---- A3: inverse transforms -----------------------------------------------------------------------------------
 // SceneNode::UpdateInternalInverseTransformData (reference: Source/Scene/RNSceneNode.cpp:552-554):

@@ -4,7 +4,9 @@
 //   GenericParticle::Update                    Source/Scene/RNParticle.cpp:31-53     age, interpolate, integrate
 //   Interpolator<T>::GetValue (Linear)         Source/Math/RNInterpolation.h:101-103 start + (difference * t / duration)
 //   ParticleEmitter::UpdateParticles           Source/Scene/RNParticleEmitter.cpp:180-211 ordered kill, spawn count
-//   GenericParticleEmitter::CreateParticle     Source/Scene/RNParticleEmitter.cpp:416-454 11 RNG draws per particle
+//   GenericParticleEmitter::CreateParticle     Source/Scene/RNParticleEmitter.cpp:416-454 11 RNG draws per particle; both
+//                                              branches of GetIsLocal() (:428-437)
+//   ParticleEmitter::SetMaxParticlesSoft       Source/Scene/RNParticleEmitter.cpp:128-132,204-205 (unsigned wrap kept)
 //   Random::MersenneTwister                    Source/Math/RNRandom.cpp:313-358      _offset = 0 after Seed, 31-bit outputs
 //   Generator::GetRandomFloatRange             Source/Math/RNRandom.cpp:213-222      float(double(k) * 2^-31 * range + min)
 //
@@ -32,7 +34,7 @@ struct EmitterState
 	float time;        // ParticleEmitter::_time
 	uint32_t count;    // _particles.size()
 	uint32_t mt_index; // MersenneTwister::_offset
-	uint32_t pad;
+	uint32_t overflow; // sticky: a spawn was cut at the segment capacity (only reachable through the soft-maximum wrap)
 };
 
 struct ParticleBuffers
@@ -41,6 +43,7 @@ struct ParticleBuffers
 	float4 *b;  // velocity xyz, lifespan
 	float4 *c;  // duration, size start, size end, rotation start
 	float *d;   // rotation end
+	float4 *g;  // GenericParticle::gravity xyz - only allocated when some emitter is non-local (else the emitter's gravity)
 };
 
 struct ParticleStore
@@ -83,6 +86,7 @@ struct PState
 	float px, py, pz, time;
 	float vx, vy, vz, life;
 	float dur, s0, s1, r0, r1;
+	float gx, gy, gz;   // GenericParticle::gravity
 };
 
 // GenericParticle::Update (RNParticle.cpp:43-53) for one particle; writes the derived fields.
@@ -100,7 +104,7 @@ __device__ __forceinline__ void particle_update(PState &p, float delta, const rn
 	const float size = p.s0 + ((p.s1 - p.s0) * t) / dur;
 	misc = make_float4(rotation, size, size, 0.0f);
 	// velocity += gravity * delta; position += velocity * delta
-	p.vx += e.gravity[0] * delta; p.vy += e.gravity[1] * delta; p.vz += e.gravity[2] * delta;
+	p.vx += p.gx * delta; p.vy += p.gy * delta; p.vz += p.gz * delta;
 	p.px += p.vx * delta; p.py += p.vy * delta; p.pz += p.vz * delta;
 }
 
@@ -170,6 +174,8 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 	__syncthreads();
 	const size_t seg = (size_t)e * pv.cap;
 	const float delta = pv.delta;
+	// non-local emitters carry a per-particle gravity column (CTA-uniform branch: local emitters never touch it)
+	const bool nonlocal = (s_e.flags & RN_EMITTER_DESC_NONLOCAL) != 0u;
 
 	// ---- update + order-preserving kill (RNParticleEmitter.cpp:182-196) ----
 	uint32_t out = 0;
@@ -186,6 +192,12 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 			p.vx = b.x; p.vy = b.y; p.vz = b.z; p.life = b.w;
 			p.dur = c.x; p.s0 = c.y; p.s1 = c.z; p.r0 = c.w;
 			p.r1 = pv.in.d[seg + i];
+			p.gx = s_e.gravity[0]; p.gy = s_e.gravity[1]; p.gz = s_e.gravity[2];
+			if(nonlocal)
+			{
+				const float4 g = pv.in.g[seg + i];
+				p.gx = g.x; p.gy = g.y; p.gz = g.z;
+			}
 			particle_update(p, delta, s_e, color, misc);
 			alive = !(p.life <= 0.0f);
 		}
@@ -204,6 +216,7 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 		{
 			const size_t o = seg + out + pre + __popc(m & ((1u << lane) - 1u));
 			store_particle(pv.out, o, p);
+			if(nonlocal) pv.out.g[o] = make_float4(p.gx, p.gy, p.gz, 0.0f);
 			pv.color[o] = color;
 			pv.misc[o] = misc;
 		}
@@ -221,10 +234,18 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 			const float t = etime + delta;
 			spawn = (uint32_t)floorf(t / s_e.spawn_rate);
 			newtime = fmodf(t, s_e.spawn_rate);
-			if(spawn > 0 && s_e.max_particles > 0)
+			// if(_maxParticles > 0 && _maxParticlesSoft > 0) spawn = min(_maxParticlesSoft - size, spawn)   (:204-205)
+			const uint32_t soft = (s_e.flags & RN_EMITTER_DESC_SOFT_MAX) ? s_e.max_particles_soft : s_e.max_particles;
+			if(spawn > 0 && s_e.max_particles > 0 && soft > 0)
 			{
-				const uint32_t room = s_e.max_particles - out; // unsigned, like the reference
+				const uint32_t room = soft - out; // unsigned, like the reference: wraps when out > soft
 				spawn = room < spawn ? room : spawn;
+			}
+			// the segment holds pv.cap particles; only the wrap above can ask for more
+			if(spawn > pv.cap - out)
+			{
+				spawn = pv.cap - out;
+				es->overflow = 1u;
 			}
 		}
 		s_spawn = spawn;
@@ -286,8 +307,21 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 			p.vx = d.velocity[0] + random_range(dr[4], fmin_std(d.velocity_min[0], d.velocity_max[0]), fmax_std(d.velocity_min[0], d.velocity_max[0]));
 			p.vy = d.velocity[1] + random_range(dr[5], fmin_std(d.velocity_min[1], d.velocity_max[1]), fmax_std(d.velocity_min[1], d.velocity_max[1]));
 			p.vz = d.velocity[2] + random_range(dr[6], fmin_std(d.velocity_min[2], d.velocity_max[2]), fmax_std(d.velocity_min[2], d.velocity_max[2]));
-			p.s0 = random_range(dr[7], d.start_size[0], d.start_size[1]) * 1.0f;
-			p.s1 = random_range(dr[8], d.end_size[0], d.end_size[1]) * 1.0f;
+			p.gx = d.gravity[0]; p.gy = d.gravity[1]; p.gz = d.gravity[2];
+			float sizeScale = 1.0f;
+			if(nonlocal)
+			{
+				// RNParticleEmitter.cpp:428-437: sizeScale = max(max(scale.x, scale.y), scale.z); position *= scale;
+				// position += GetWorldPosition(); gravity *= scale; velocity *= scale
+				const float sx = d.world_scale[0], sy = d.world_scale[1], sz = d.world_scale[2];
+				sizeScale = fmax_std(fmax_std(sx, sy), sz);
+				p.px *= sx; p.py *= sy; p.pz *= sz;
+				p.px += d.world_position[0]; p.py += d.world_position[1]; p.pz += d.world_position[2];
+				p.gx *= sx; p.gy *= sy; p.gz *= sz;
+				p.vx *= sx; p.vy *= sy; p.vz *= sz;
+			}
+			p.s0 = random_range(dr[7], d.start_size[0], d.start_size[1]) * sizeScale;
+			p.s1 = random_range(dr[8], d.end_size[0], d.end_size[1]) * sizeScale;
 			p.r0 = random_range(dr[9], d.start_rotation[0], d.start_rotation[1]) * 0.01745329251994329577f;
 			p.r1 = random_range(dr[10], d.end_rotation[0], d.end_rotation[1]) * 0.01745329251994329577f;
 			p.dur = lifespan;
@@ -296,6 +330,7 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 			particle_update(p, 0.0f, d, color, misc); // particle->Update(0.0f), RNParticleEmitter.cpp:451
 			const size_t o = seg + out + done + tid;
 			store_particle(pv.out, o, p);
+			if(nonlocal) pv.out.g[o] = make_float4(p.gx, p.gy, p.gz, 0.0f);
 			pv.color[o] = color;
 			pv.misc[o] = misc;
 		}
@@ -485,6 +520,7 @@ static void free_store(ParticleStore *p)
 		if(p->buf[g].b) cudaFree(p->buf[g].b);
 		if(p->buf[g].c) cudaFree(p->buf[g].c);
 		if(p->buf[g].d) cudaFree(p->buf[g].d);
+		if(p->buf[g].g) cudaFree(p->buf[g].g);
 	}
 	if(p->color) cudaFree(p->color);
 	if(p->misc) cudaFree(p->misc);
@@ -526,6 +562,9 @@ extern "C" int rn_particles_configure(rn_scene_t *s, const rn_emitter_desc *emit
 		RN_REQUIRE(emitters[i].max_particles > 0 && emitters[i].max_particles <= cap, RN_ERR_CAPACITY,
 		           "emitter %u: max_particles %u must be in 1..%u", i, emitters[i].max_particles, cap);
 	}
+	bool any_nonlocal = false;
+	for(uint32_t i = 0; i < count; i++)
+		any_nonlocal = any_nonlocal || (emitters[i].flags & RN_EMITTER_DESC_NONLOCAL);
 	RN_CUDA(cudaSetDevice(s->device));
 	RN_CUDA(cudaDeviceSynchronize());
 	particles_destroy(s);
@@ -542,6 +581,7 @@ extern "C" int rn_particles_configure(rn_scene_t *s, const rn_emitter_desc *emit
 		if(!rc) rc = palloc(s, &p->buf[g].b, total);
 		if(!rc) rc = palloc(s, &p->buf[g].c, total);
 		if(!rc) rc = palloc(s, &p->buf[g].d, total);
+		if(!rc && any_nonlocal) rc = palloc(s, &p->buf[g].g, total);
 	}
 	if(!rc) rc = palloc(s, &p->color, total);
 	if(!rc) rc = palloc(s, &p->misc, total);
@@ -623,12 +663,52 @@ extern "C" int rn_particles_counts(rn_scene_t *s, uint32_t *out_counts, float *o
 	RN_CUDA(cudaDeviceSynchronize());
 	std::vector<EmitterState> es(n_emitters);
 	RN_CUDA(cudaMemcpy(es.data(), p->emitters, sizeof(EmitterState) * n_emitters, cudaMemcpyDeviceToHost));
+	uint32_t overflowed = 0xffffffffu;
 	for(uint32_t i = 0; i < n_emitters; i++)
 	{
 		if(out_counts) out_counts[i] = es[i].count;
 		if(out_times) out_times[i] = es[i].time;
+		if(es[i].overflow && overflowed == 0xffffffffu) overflowed = i;
 	}
+	RN_REQUIRE(overflowed == 0xffffffffu, RN_ERR_CAPACITY,
+	           "emitter %u asked for more particles than max_particles_per_emitter (%u): its live count exceeded the soft maximum, "
+	           "so the reference's unsigned `soft - size` wrapped (RNParticleEmitter.cpp:204-205)", overflowed, p->cap);
 	return RN_OK;
+}
+
+// host-side edit of a few fields of the emitter records (tiny, synchronous)
+template <class F>
+static int edit_emitters(rn_scene *s, uint32_t first, uint32_t count, F &&f)
+{
+	ParticleStore *p = s->particles;
+	RN_REQUIRE(p && (uint64_t)first + count <= p->n_emitters, RN_ERR_INVALID, "emitters [%u, %u) out of range", first, first + count);
+	if(count == 0) return RN_OK;
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	std::vector<EmitterState> es(count);
+	RN_CUDA(cudaMemcpy(es.data(), p->emitters + first, sizeof(EmitterState) * count, cudaMemcpyDeviceToHost));
+	for(uint32_t i = 0; i < count; i++) f(es[i], i);
+	RN_CUDA(cudaMemcpy(p->emitters + first, es.data(), sizeof(EmitterState) * count, cudaMemcpyHostToDevice));
+	return RN_OK;
+}
+
+extern "C" int rn_particles_set_soft_max(rn_scene_t *s, uint32_t first, uint32_t count, const uint32_t *soft)
+{
+	RN_REQUIRE(s && soft, RN_ERR_INVALID, "NULL argument");
+	return edit_emitters(s, first, count, [&](EmitterState &e, uint32_t i) {
+		e.d.flags |= RN_EMITTER_DESC_SOFT_MAX;
+		e.d.max_particles_soft = soft[i];
+	});
+}
+
+extern "C" int rn_particles_set_emitter_transforms(rn_scene_t *s, uint32_t first, uint32_t count, const float *world_position,
+                                                   const float *world_scale)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	return edit_emitters(s, first, count, [&](EmitterState &e, uint32_t i) {
+		if(world_position) memcpy(e.d.world_position, world_position + (size_t)i * 3, 12);
+		if(world_scale) memcpy(e.d.world_scale, world_scale + (size_t)i * 3, 12);
+	});
 }
 
 extern "C" int rn_particles_download(rn_scene_t *s, uint32_t emitter, rn_particle_field field, void *dst, uint32_t capacity,
@@ -679,6 +759,15 @@ extern "C" int rn_particles_download(rn_scene_t *s, uint32_t emitter, rn_particl
 			break;
 		case RN_PF_SORTED:
 			RN_CUDA(cudaMemcpy(dst, p->sorted + seg, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+			break;
+		case RN_PF_GRAVITY:
+			if(b.g && (es.d.flags & RN_EMITTER_DESC_NONLOCAL))
+			{
+				RN_CUDA(cudaMemcpy(t0.data(), b.g + seg, sizeof(float4) * n, cudaMemcpyDeviceToHost));
+				for(uint32_t i = 0; i < n; i++) { out[i * 3] = t0[i].x; out[i * 3 + 1] = t0[i].y; out[i * 3 + 2] = t0[i].z; }
+			}
+			else
+				for(uint32_t i = 0; i < n; i++) { out[i * 3] = es.d.gravity[0]; out[i * 3 + 1] = es.d.gravity[1]; out[i * 3 + 2] = es.d.gravity[2]; }
 			break;
 		default:
 			RN_REQUIRE(false, RN_ERR_INVALID, "unknown particle field %d", (int)field);

@@ -102,7 +102,6 @@ struct SceneView
 
 struct CullParams
 {
-	rn_camera_frustum cam[RN_MAX_CAMERAS];
 	uint32_t n;
 	uint32_t simple;                   // bit c: camera c has UseSimpleCulling
 	// built on the host (fill_cull_params), copied into shared memory by every CTA:
@@ -136,33 +135,39 @@ struct CullTable
 {
 	float4 test[RN_MAX_CAMERAS * 7];   // [c*7] = frustum sphere (centre xyz, radius); [c*7 + 1 + k] = plane k (normal xyz, d)
 	uint8_t group_mask[256];           // _renderGroup byte -> bit mask of the cameras whose render group intersects it
+	// per-LANE constants of the classifier (the same for every warp of the CTA; read at cull time instead of living in
+	// ten registers for the whole kernel)
+	float4 lane_e0[32], lane_e1[32];
+	uint32_t lane_kind[32];            // kind0 | kind1 << 8
 };
 
 // Per-lane constants of the classifier: round 0 = lane l < 30 tests plane l%6 of camera l/6 (cameras 0-4);
 // round 1 = lane l < 18 tests plane l%6 of camera 5 + l/6, lanes 18-25 test the frustum sphere of camera l-18.
-struct LaneTests
+// kind: 0 = none, 1 = plane, 2 = plane of a simple-culling camera (always inside), 3 = sphere
+// The predicate for ONE camera whose seven test vectors sit in registers (loaded warp-uniformly from the CTA's cull
+// table): frustum-sphere pre-test, then the six planes, in the reference's fp32 operation order.
+struct CamTests
 {
-	float4 e0, e1;
-	uint32_t kind0, kind1;   // 0 = none, 1 = plane, 2 = plane of a simple-culling camera (always inside), 3 = sphere
+	float4 sphere;      // frustum centre xyz, radius
+	float4 plane[6];    // normal xyz, d
+	bool simple;        // Camera::Flags::UseSimpleCulling
 };
 
-template <int C>
-__device__ __forceinline__ bool cull_exact(const CullParams &cp, float px, float py, float pz, float radius)
+__device__ __forceinline__ bool cull_exact(const CamTests &cam, float px, float py, float pz, float radius)
 {
-	const rn_camera_frustum &cam = cp.cam[C];
 	// _frustumCenter.GetDistance(position) > _frustumRadius + radius  (Source/Scene/RNCamera.cpp:444-445)
-	const float dx = cam.center[0] - px, dy = cam.center[1] - py, dz = cam.center[2] - pz;
+	const float dx = cam.sphere.x - px, dy = cam.sphere.y - py, dz = cam.sphere.z - pz;
 	const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
-	if(dist > cam.radius + radius)
+	if(dist > cam.sphere.w + radius)
 		return false;
-	if(cam.flags & RN_CAMERA_USE_SIMPLE_CULLING)
+	if(cam.simple)
 		return true;
 	bool inside = true;
 #pragma unroll
 	for(int k = 0; k < 6; k++)
 	{
 		// Plane::GetDistance: position.Dot(normal) - d   (Source/Math/RNPlane.h:99-102)
-		const float d = px * cam.planes[k][0] + py * cam.planes[k][1] + pz * cam.planes[k][2] - cam.planes[k][3];
+		const float d = px * cam.plane[k].x + py * cam.plane[k].y + pz * cam.plane[k].z - cam.plane[k].w;
 		if(d > radius)
 			inside = false;
 	}
@@ -181,6 +186,20 @@ __device__ __forceinline__ float warp_max(float f)
 {
 	float r;
 	asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(f));
+	return r;
+}
+
+// NaN-propagating two-input min / max (fminf / fmaxf would DROP a NaN, and the classifier's guard relies on seeing it)
+__device__ __forceinline__ float min_nan(float a, float b)
+{
+	float r;
+	asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+	return r;
+}
+__device__ __forceinline__ float max_nan(float a, float b)
+{
+	float r;
+	asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
 	return r;
 }
 
@@ -233,87 +252,117 @@ __device__ __forceinline__ uint32_t classify(uint32_t kind, const float4 &e, con
 	return kind == 2 ? 2u : 0u;
 }
 
-// SceneNode::UpdateInternalBoundsData (sphere part) + the predicate above for all cameras.
-// Converged call (all 32 lanes); a lane without a node passes a copy of a real node and active = false.
-// Returns the camera bit mask.
-__device__ __forceinline__ uint32_t cull_node(const CullParams &cp, const CullTable &tab, const LaneTests &lt, bool active,
-                                              uint32_t flagsword, const Vec3 &wp, const Quat &wr, const Vec3 &ws, const float4 &sph)
+// What the cull needs of one node: the tested sphere (SceneNode::UpdateInternalBoundsData, sphere part), the flags word
+// and where its mask byte goes.
+struct CullItem
 {
-	// Sphere::operator*=(Vector3) then SetRotation (Source/Math/RNSphere.h:62-73)
+	float px, py, pz, radius;
+	uint32_t fw;        // flags | render group << 8 | (rank - tile start) << 16
+	uint32_t vidx;      // index of the node's mask byte (rank order)
+	bool active;        // false: the lane carries a copy of a real node (keeps the warp converged) and stores nothing
+};
+
+// Sphere::operator*=(Vector3) then SetRotation (Source/Math/RNSphere.h:62-73); Camera::InFrustum(const Sphere&) tests
+// position + offset (Source/Scene/RNCamera.cpp:469-473).
+__device__ __forceinline__ void bound_sphere(const Vec3 &wp, const Quat &wr, const Vec3 &ws, const float4 &sph, CullItem &it)
+{
 	const float s = std_max(std_max(ws.x, ws.y), ws.z);
-	const float radius = sph.w * s;
-	float px = wp.x, py = wp.y, pz = wp.z;
+	it.radius = sph.w * s;
+	it.px = wp.x; it.py = wp.y; it.pz = wp.z;
 	// A zero offset stays (+-)0 through the scaling and the rotation and `position + offset` returns the position:
 	// skipping the rotation is exact (up to the sign of a zero, which no comparison below can see).
 	if(sph.x != 0.0f || sph.y != 0.0f || sph.z != 0.0f)
 	{
 		Vec3 off = {sph.x * s, sph.y * s, sph.z * s};
 		off = quat_rotate(wr, off);
-		// Camera::InFrustum(const Sphere&): position + offset (Source/Scene/RNCamera.cpp:469-473)
-		px = wp.x + off.x; py = wp.y + off.y; pz = wp.z + off.z;
+		it.px = wp.x + off.x; it.py = wp.y + off.y; it.pz = wp.z + off.z;
 	}
+}
+
+// The predicate for all cameras and TWO nodes per lane (64 nodes per call: two consecutive passes of a tile are
+// siblings / cousins, so one bounding box serves both and the warp-level work - 8 reductions, 2 classification rounds,
+// the votes - is paid once per 64 nodes).  Converged call (all 32 lanes).  Returns the camera bit masks.
+__device__ __forceinline__ void cull_pair(const CullParams &cp, const CullTable &tab, const CullItem &A, const CullItem &B,
+                                          uint32_t &maskA, uint32_t &maskB)
+{
+	const uint32_t lane = threadIdx.x & 31u;
 	__syncwarp();
 	WarpBox b;
-	b.lox = warp_min(px); b.hix = warp_max(px);
-	b.loy = warp_min(py); b.hiy = warp_max(py);
-	b.loz = warp_min(pz); b.hiz = warp_max(pz);
-	b.rlo = warp_min(radius); b.rhi = warp_max(radius);
+	b.lox = warp_min(min_nan(A.px, B.px)); b.hix = warp_max(max_nan(A.px, B.px));
+	b.loy = warp_min(min_nan(A.py, B.py)); b.hiy = warp_max(max_nan(A.py, B.py));
+	b.loz = warp_min(min_nan(A.pz, B.pz)); b.hiz = warp_max(max_nan(A.pz, B.pz));
+	b.rlo = warp_min(min_nan(A.radius, B.radius)); b.rhi = warp_max(max_nan(A.radius, B.radius));
 	// NaN / inf-inf anywhere makes `guard` NaN: then nothing is decided at warp level
 	const float guard = (b.lox - b.hix) + (b.loy - b.hiy) + (b.loz - b.hiz) + (b.rlo - b.rhi);
 	const bool sane = guard <= 0.0f;
-	const uint32_t nc = cp.n;
-	const uint32_t r0 = sane ? classify(lt.kind0, lt.e0, b) : 0u;
+	const uint32_t kinds = tab.lane_kind[lane];
+	const uint32_t r0 = sane ? classify(kinds & 0xffu, tab.lane_e0[lane], b) : 0u;
 	const uint32_t out0 = __ballot_sync(0xffffffffu, r0 == 1), in0 = __ballot_sync(0xffffffffu, r0 == 2);
-	const uint32_t r1 = sane ? classify(lt.kind1, lt.e1, b) : 0u;
+	const uint32_t r1 = sane ? classify(kinds >> 8, tab.lane_e1[lane], b) : 0u;
 	const uint32_t out1 = __ballot_sync(0xffffffffu, r1 == 1), in1 = __ballot_sync(0xffffffffu, r1 == 2);
-
-	uint32_t frustum = 0;   // per lane: cameras whose frustum test the node passes
-#define RN_CULL_CAM(C)                                                                                              \
-	if(nc > C)                                                                                                      \
-	{                                                                                                               \
-		const uint32_t pout = C < 5 ? (out0 >> (6 * C)) & 63u : (out1 >> (6 * (C - 5))) & 63u;                      \
-		const uint32_t pin = C < 5 ? (in0 >> (6 * C)) & 63u : (in1 >> (6 * (C - 5))) & 63u;                         \
-		const uint32_t sout = (out1 >> (18 + C)) & 1u, sin = (in1 >> (18 + C)) & 1u;                                \
-		if(sout | pout) { }                                                                                         \
-		else if(sin && pin == 63u) frustum |= 1u << C;                                                              \
-		else if(cull_exact<C>(cp, px, py, pz, radius)) frustum |= 1u << C;                                          \
+	// lane c (< 8) folds the votes of camera c: culled for all 64 nodes / visible for all / undecided
+	const uint32_t c = lane & 7u;
+	const uint32_t sh = c < 5u ? 6u * c : 6u * (c - 5u);
+	const uint32_t pout = ((c < 5u ? out0 : out1) >> sh) & 63u, pin = ((c < 5u ? in0 : in1) >> sh) & 63u;
+	const uint32_t sout = (out1 >> (18u + c)) & 1u, sin = (in1 >> (18u + c)) & 1u;
+	const bool culled = (sout | pout) != 0u;
+	const uint32_t cams = (1u << cp.n) - 1u;
+	const uint32_t all_out = __ballot_sync(0xffffffffu, culled) & cams;
+	const uint32_t all_in = __ballot_sync(0xffffffffu, !culled && sin && pin == 63u) & cams;
+	uint32_t fa = all_in, fb = all_in;   // per lane: cameras whose frustum test the node passes
+	uint32_t undecided = cams & ~(all_out | all_in);
+	while(undecided)
+	{
+		const uint32_t k = (uint32_t)__ffs((int)undecided) - 1u;
+		undecided &= undecided - 1u;
+		CamTests cam;
+		cam.sphere = tab.test[k * 7u];
+#pragma unroll
+		for(int q = 0; q < 6; q++)
+			cam.plane[q] = tab.test[k * 7u + 1u + q];
+		cam.simple = (cp.simple >> k) & 1u;
+		if(cull_exact(cam, A.px, A.py, A.pz, A.radius)) fa |= 1u << k;
+		if(cull_exact(cam, B.px, B.py, B.pz, B.radius)) fb |= 1u << k;
 	}
-	RN_CULL_CAM(0) RN_CULL_CAM(1) RN_CULL_CAM(2) RN_CULL_CAM(3) RN_CULL_CAM(4) RN_CULL_CAM(5) RN_CULL_CAM(6) RN_CULL_CAM(7)
-#undef RN_CULL_CAM
 	__syncwarp();
-	if(!active || (flagsword & RN_NODE_HIDDEN))
-		return 0;
-	const uint32_t groups = tab.group_mask[(flagsword >> 8) & 0xffu];
-	return (flagsword & RN_NODE_NOCULLING) ? groups : (groups & frustum);
+	const uint32_t ga = tab.group_mask[(A.fw >> 8) & 0xffu], gb = tab.group_mask[(B.fw >> 8) & 0xffu];
+	maskA = (!A.active || (A.fw & RN_NODE_HIDDEN)) ? 0u : ((A.fw & RN_NODE_NOCULLING) ? ga : (ga & fa));
+	maskB = (!B.active || (B.fw & RN_NODE_HIDDEN)) ? 0u : ((B.fw & RN_NODE_NOCULLING) ? gb : (gb & fb));
 }
 
-// Fills the CTA's cull table and the lane constants (all threads of the CTA; contains a __syncthreads).
-__device__ __forceinline__ void cull_setup(const CullParams &cp, CullTable &tab, LaneTests &lt)
+// Fills the CTA's cull table incl. the lane constants (all threads of the CTA; contains a __syncthreads).
+__device__ __forceinline__ void cull_setup(const CullParams &cp, CullTable &tab)
 {
 	for(uint32_t t = threadIdx.x; t < RN_MAX_CAMERAS * 7; t += blockDim.x)
 		tab.test[t] = cp.test[t];
 	for(uint32_t g = threadIdx.x; g < 64; g += blockDim.x)
 		reinterpret_cast<uint32_t *>(tab.group_mask)[g] = cp.group_mask[g];
 	const uint32_t simple = cp.simple;
+	if(threadIdx.x < 32)
+	{
+		const uint32_t lane = threadIdx.x;
+		uint32_t kind0 = 0, kind1 = 0;
+		float4 e0 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), e1 = e0;
+		if(lane < 30)
+		{
+			const uint32_t c = lane / 6, k = lane % 6;
+			if(c < cp.n) { kind0 = ((simple >> c) & 1u) ? 2u : 1u; e0 = cp.test[c * 7 + 1 + k]; }
+		}
+		if(lane < 18)
+		{
+			const uint32_t c = 5 + lane / 6, k = lane % 6;
+			if(c < cp.n) { kind1 = ((simple >> c) & 1u) ? 2u : 1u; e1 = cp.test[c * 7 + 1 + k]; }
+		}
+		else if(lane < 26)
+		{
+			const uint32_t c = lane - 18;
+			if(c < cp.n) { kind1 = 3u; e1 = cp.test[c * 7]; }
+		}
+		tab.lane_e0[lane] = e0;
+		tab.lane_e1[lane] = e1;
+		tab.lane_kind[lane] = kind0 | (kind1 << 8);
+	}
 	__syncthreads();
-	const uint32_t lane = threadIdx.x & 31u;
-	lt.kind0 = lt.kind1 = 0;
-	lt.e0 = lt.e1 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-	if(lane < 30)
-	{
-		const uint32_t c = lane / 6, k = lane % 6;
-		if(c < cp.n) { lt.kind0 = ((simple >> c) & 1u) ? 2u : 1u; lt.e0 = tab.test[c * 7 + 1 + k]; }
-	}
-	if(lane < 18)
-	{
-		const uint32_t c = 5 + lane / 6, k = lane % 6;
-		if(c < cp.n) { lt.kind1 = ((simple >> c) & 1u) ? 2u : 1u; lt.e1 = tab.test[c * 7 + 1 + k]; }
-	}
-	else if(lane < 26)
-	{
-		const uint32_t c = lane - 18;
-		if(c < cp.n) { lt.kind1 = 3u; lt.e1 = tab.test[c * 7]; }
-	}
 }
 
 // Per-lane visible counters of a tile, one byte per camera (a tile has at most 255 passes).
@@ -348,10 +397,11 @@ __device__ __forceinline__ void vis_count_store(const SceneView &sv, uint32_t ti
 	}
 }
 
+template <bool FMA>
 __device__ __forceinline__ void compute_world(const Vec3 &pos, const Quat &rot, const Vec3 &scale, bool hasParent,
                                               const NodeWorld &P, NodeWorld &out)
 {
-	const Affine L = local_matrix(pos, rot, scale);
+	const Affine L = local_matrix<FMA>(pos, rot, scale);
 	if(hasParent)
 	{
 		// SceneNode::UpdateInternalData (RNSceneNode.cpp:509-511)
@@ -364,7 +414,7 @@ __device__ __forceinline__ void compute_world(const Vec3 &pos, const Quat &rot, 
 		out.ws.y = P.ws.y * scale.y;
 		out.ws.z = P.ws.z * scale.z;
 		// SceneNode::UpdateInternalTransformData (RNSceneNode.cpp:537)
-		out.M = affine_mul(P.M, L);
+		out.M = affine_mul<FMA>(P.M, L);
 	}
 	else
 	{
@@ -403,6 +453,7 @@ __device__ __forceinline__ void store_world_global(const SceneView &sv, uint32_t
 }
 
 // Spine pre-pass: one launch per hierarchy depth of the spine (the few nodes whose subtree does not fit a tile).
+template <bool FMA>
 __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t *__restrict__ slots, uint32_t count)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -418,7 +469,7 @@ __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t
 	const bool hasParent = parent != RN_NO_PARENT;
 	if(hasParent)
 		load_world_global(sv, parent, P);
-	compute_world(pos, rot, scale, hasParent, P, W);
+	compute_world<FMA>(pos, rot, scale, hasParent, P, W);
 	store_world_global(sv, slot, W);
 }
 
@@ -483,20 +534,21 @@ __device__ __forceinline__ void prefetch_l2(const void *p)
 
 // World-transform propagation (+ culling) of one tile per WARP.  A tile is a contiguous slot range holding whole
 // compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every sublevel first.
-// The warp walks the sublevels in order, 32 nodes per pass: coalesced float4 loads of the four input columns,
-// parent world TRS + matrix from the warp's shared memory (written by an earlier pass of the same warp, so only
-// __syncwarp separates the levels - no block barrier, the warps of a CTA never wait for each other), one coalesced
-// write of the outputs.  Every node is read once and written once; parents never come back from HBM.
-// The lanes of a pass stay converged (a lane without a node recomputes the last node of the level and stores
-// nothing) so that the cull can use warp votes.
-template <bool CULL>
+// The warp walks the sublevels in order, 32 nodes per pass: the four input columns of the NEXT pass arrive by TMA bulk
+// copies while the current one computes, parent world TRS + matrix come from the warp's shared memory (written by an
+// earlier pass of the same warp, so only __syncwarp separates the levels - no block barrier, the warps of a CTA
+// never wait for each other), the outputs are written once.  Every node is read once and written once; parents never
+// come back from HBM.  Sublevel 0 (spine nodes stored in this tile, transformed by the pre-pass) goes through the same
+// loop with its world TRS loaded instead of computed.  The lanes of a pass stay converged (a lane without a node
+// recomputes the last node of the level and stores nothing) so that the cull can use warp votes.
+// The cull of a pass is deferred by one pass and done for two passes at once (cull_pair).
+template <bool CULL, bool FMA>
 __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	__shared__ CullTable tab;
-	LaneTests lt;
 	if(CULL)
-		cull_setup(cp, tab, lt);
+		cull_setup(cp, tab);
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	const uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
 	if(tile >= sv.n_tiles)
@@ -514,27 +566,6 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 	const uint32_t nlev = s.meta->nlev;
 	VisCount vc = {0u, 0u};
 
-	if(CULL)
-	{
-		// sublevel 0: spine nodes stored inside this tile - world transform already computed by the pre-pass
-		const uint32_t e0 = s.meta->lvl_end[0];
-		for(uint32_t j0 = 0; j0 < e0; j0 += 32)
-		{
-			const bool active = j0 + lane < e0;
-			const uint32_t slot = start + (active ? j0 + lane : e0 - 1);
-			const float4 a = sv.wpos[slot], b = sv.wrot[slot];
-			const float2 c = sv.wsyz[slot];
-			const uint32_t fw = __float_as_uint(sv.c2[slot].w);
-			const Vec3 wp = {a.x, a.y, a.z};
-			const Quat wr = {b.x, b.y, b.z, b.w};
-			const Vec3 ws = {a.w, c.x, c.y};
-			const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
-			if(active)
-				sv.vis[slot] = (uint8_t)mask;
-			vis_count_add(vc, mask);
-		}
-	}
-	// ---- the passes of sublevels 1.. : a flat sequence over the tile's slots, 32 at a time, never across a level ----
 	// The four input columns of pass p+1 are fetched by TMA bulk copies (one elected lane, completion on the warp's
 	// mbarrier) while pass p computes; a pass starts by moving its 4 x float4 from the stage to registers.
 	const uint32_t ncols = CULL ? 4u : 3u;
@@ -546,13 +577,22 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 		bulk_g2s(s.stage + 64, sv.c2 + start + j0, bytes, s.bar);
 		if(CULL) bulk_g2s(s.stage + 96, sv.c3 + start + j0, bytes, s.bar);
 	};
-	if(nlev > 1)
+	// first pass: sublevel 0 only matters to the cull
+	uint32_t lev = 0, j0 = 0, je = s.meta->lvl_end[0];
+	if(!CULL || je == 0)
 	{
-		uint32_t lev = 1;
-		uint32_t j0 = s.meta->lvl_end[0], je = s.meta->lvl_end[1], jb = j0;
-		uint32_t ib = 0, ni = s.meta->inner_end[1];
+		lev = 1;
+		j0 = je;
+		je = s.meta->lvl_end[nlev > 1 ? 1 : 0];
+	}
+	if(lev < nlev)
+	{
+		uint32_t jb = j0;                                    // first slot offset of the current sublevel
+		uint32_t ib = 0, ni = lev ? s.meta->inner_end[1] : 0;   // inner nodes: first index, count in this sublevel
 		uint32_t phase = 0;
-		if(lane == 0)
+		bool pending = false;
+		CullItem held;
+		if(lev && lane == 0)
 			issue(j0, min(32u, je - j0));
 		for(;;)
 		{
@@ -561,12 +601,6 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 			const uint32_t l = active ? lane : n_cur - 1;
 			const uint32_t j = j0 + l;
 			const uint32_t slot = start + j;
-			mbar_wait(s.bar, phase);
-			phase ^= 1u;
-			const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
-			float4 d;
-			if(CULL) d = s.stage[96 + l];
-			__syncwarp();
 			// next pass
 			uint32_t nlv = lev, nj0 = j0 + 32, nje = je;
 			if(nj0 >= je)
@@ -576,44 +610,88 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 				nje = s.meta->lvl_end[nlv < nlev ? nlv : lev];
 			}
 			const bool has_next = nlv < nlev;
-			if(has_next && lane == 0)
-				issue(nj0, min(32u, nje - nj0));
-
-			const Vec3 pos = {a.x, a.y, a.z};
-			const Vec3 scale = {a.w, c.x, c.y};
-			const Quat rot = {b.x, b.y, b.z, b.w};
-			const uint32_t parent = __float_as_uint(c.z);
-			const uint32_t fw = __float_as_uint(c.w);
-			NodeWorld P, W;
-			const bool hasParent = parent != RN_NO_PARENT;
-			if(hasParent)
+			NodeWorld W;
+			float4 d;
+			uint32_t fw;
+			if(!CULL || lev)
 			{
-				if(parent & kParentInTile)
-					load_world_smem(s, parent & 0xffffu, P);
-				else
-					load_world_global(sv, parent, P);
+				mbar_wait(s.bar, phase);
+				phase ^= 1u;
+				const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
+				if(CULL) d = s.stage[96 + l];
+				__syncwarp();
+				if(has_next && lane == 0)
+					issue(nj0, min(32u, nje - nj0));
+				const Vec3 pos = {a.x, a.y, a.z};
+				const Vec3 scale = {a.w, c.x, c.y};
+				const Quat rot = {b.x, b.y, b.z, b.w};
+				const uint32_t parent = __float_as_uint(c.z);
+				fw = __float_as_uint(c.w);
+				NodeWorld P;
+				const bool hasParent = parent != RN_NO_PARENT;
+				if(hasParent)
+				{
+					if(parent & kParentInTile)
+						load_world_smem(s, parent & 0xffffu, P);
+					else
+						load_world_global(sv, parent, P);
+				}
+				compute_world<FMA>(pos, rot, scale, hasParent, P, W);
+				if(active)
+				{
+					store_world_global(sv, slot, W);
+					if(j - jb < ni)
+						store_world_smem(s, ib + (j - jb), W);
+				}
+				__syncwarp();
 			}
-			compute_world(pos, rot, scale, hasParent, P, W);
-			if(active)
+			else
 			{
-				store_world_global(sv, slot, W);
-				if(j - jb < ni)
-					store_world_smem(s, ib + (j - jb), W);
+				// spine nodes stored inside this tile: world transform already computed by the pre-pass (CULL only)
+				if(has_next && nlv && lane == 0)
+					issue(nj0, min(32u, nje - nj0));
+				const float4 a = sv.wpos[slot], b = sv.wrot[slot];
+				const float2 c = sv.wsyz[slot];
+				fw = __float_as_uint(sv.c2[slot].w);
+				d = sv.c3[slot];
+				W.wp = {a.x, a.y, a.z};
+				W.wr = {b.x, b.y, b.z, b.w};
+				W.ws = {a.w, c.x, c.y};
 			}
-			__syncwarp();
 			if(CULL)
 			{
-				const uint32_t mask = cull_node(cp, tab, lt, active, fw, W.wp, W.wr, W.ws, d);
-				if(active)
-					sv.vis[slot] = (uint8_t)mask;
-				vis_count_add(vc, mask);
+				CullItem cur;
+				bound_sphere(W.wp, W.wr, W.ws, d, cur);
+				cur.fw = fw;
+				cur.vidx = start + ((fw >> kRankShift) & kRankMask);
+				cur.active = active;
+				if(!pending && has_next)
+				{
+					held = cur;
+					pending = true;
+				}
+				else
+				{
+					if(!pending)
+					{
+						held = cur;
+						held.active = false;
+					}
+					uint32_t ma, mb;
+					cull_pair(cp, tab, held, cur, ma, mb);
+					if(held.active) sv.vis[held.vidx] = (uint8_t)ma;
+					if(cur.active) sv.vis[cur.vidx] = (uint8_t)mb;
+					vis_count_add(vc, ma);
+					vis_count_add(vc, mb);
+					pending = false;
+				}
 			}
 			if(!has_next)
 				break;
 			if(nlv != lev)
 			{
 				jb = nj0;
-				ib = s.meta->inner_end[lev];
+				ib = lev ? s.meta->inner_end[lev] : 0;
 				ni = s.meta->inner_end[nlv] - ib;
 			}
 			lev = nlv; j0 = nj0; je = nje;
@@ -623,32 +701,42 @@ __global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_cons
 		vis_count_store(sv, tile, vc, lane);
 }
 
-// rn_cull on stored world transforms: one warp per tile, 32 consecutive slots per pass.
+// rn_cull on stored world transforms: one warp per tile, 64 consecutive slots per pass.
 __global__ void __launch_bounds__(256) cull_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	__shared__ CullTable tab;
-	LaneTests lt;
-	cull_setup(cp, tab, lt);
+	cull_setup(cp, tab);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if(tile >= sv.n_tiles)
 		return;
 	const uint32_t start = sv.tiles[tile].start, count = sv.tiles[tile].count;
 	VisCount vc = {0u, 0u};
-	for(uint32_t j0 = 0; j0 < count; j0 += 32)
+	for(uint32_t j0 = 0; j0 < count; j0 += 64)
 	{
-		const bool active = j0 + lane < count;
-		const uint32_t slot = start + (active ? j0 + lane : count - 1);
-		const float4 a = sv.wpos[slot], b = sv.wrot[slot];
-		const float2 c = sv.wsyz[slot];
-		const uint32_t fw = __float_as_uint(sv.c2[slot].w);
-		const Vec3 wp = {a.x, a.y, a.z};
-		const Quat wr = {b.x, b.y, b.z, b.w};
-		const Vec3 ws = {a.w, c.x, c.y};
-		const uint32_t mask = cull_node(cp, tab, lt, active, fw, wp, wr, ws, sv.c3[slot]);
-		if(active)
-			sv.vis[slot] = (uint8_t)mask;
-		vis_count_add(vc, mask);
+		CullItem it[2];
+#pragma unroll
+		for(int h = 0; h < 2; h++)
+		{
+			const uint32_t j = j0 + 32u * h + lane;
+			it[h].active = j < count;
+			const uint32_t slot = start + (it[h].active ? j : count - 1);
+			const float4 a = sv.wpos[slot], b = sv.wrot[slot];
+			const float2 c = sv.wsyz[slot];
+			const uint32_t fw = __float_as_uint(sv.c2[slot].w);
+			const Vec3 wp = {a.x, a.y, a.z};
+			const Quat wr = {b.x, b.y, b.z, b.w};
+			const Vec3 ws = {a.w, c.x, c.y};
+			bound_sphere(wp, wr, ws, sv.c3[slot], it[h]);
+			it[h].fw = fw;
+			it[h].vidx = start + ((fw >> kRankShift) & kRankMask);
+		}
+		uint32_t ma, mb;
+		cull_pair(cp, tab, it[0], it[1], ma, mb);
+		if(it[0].active) sv.vis[it[0].vidx] = (uint8_t)ma;
+		if(it[1].active) sv.vis[it[1].vidx] = (uint8_t)mb;
+		vis_count_add(vc, ma);
+		vis_count_add(vc, mb);
 	}
 	vis_count_store(sv, tile, vc, lane);
 }
@@ -679,7 +767,7 @@ struct EmitView
 	uint32_t rank_offset;
 };
 
-__global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_constant__ EmitView ev)
+__global__ void __launch_bounds__(kEmitThreads, 6) emit_kernel(const __grid_constant__ EmitView ev)
 {
 	__shared__ uint32_t s_off[kEmitTiles][RN_MAX_CAMERAS];
 	__shared__ uint32_t s_cnt[kEmitTiles][RN_MAX_CAMERAS];
@@ -753,22 +841,24 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 #pragma unroll
 		for(int c = 0; c < RN_MAX_CAMERAS; c++)
 			off[c] = s_off[k][c];
-		// 128 ranks per iteration, four consecutive ranks per lane
-		for(uint32_t r0 = 0; r0 < count; r0 += 32 * kEmitUnroll)
+		// 128 ranks per iteration, four consecutive ranks per lane.  The mask bytes are stored in RANK order, so a lane's
+		// four bytes are one aligned 32-bit load (and its four slots one 128-bit load); bytes of the neighbouring tiles
+		// that share the first / last word are masked off.
+		const uint32_t end = start + count;
+		for(uint32_t q0 = start & ~3u; q0 < end; q0 += 32 * kEmitUnroll)
 		{
-			const uint32_t r = r0 + lane * kEmitUnroll;
-			uint32_t slot[kEmitUnroll];
+			const uint32_t q = q0 + lane * kEmitUnroll;
 			uint32_t vv = 0;
-#pragma unroll
-			for(int u = 0; u < (int)kEmitUnroll; u++)
-				slot[u] = r + u < count ? ev.slot_of_rank[start + r + u] : 0xffffffffu;
-#pragma unroll
-			for(int u = 0; u < (int)kEmitUnroll; u++)
+			uint4 id = make_uint4(0u, 0u, 0u, 0u);
+			if(q < end)
 			{
-				if(slot[u] != 0xffffffffu)
-					vv |= (uint32_t)ev.vis[slot[u]] << (8 * u);
+				vv = __ldg(reinterpret_cast<const uint32_t *>(ev.vis + q));
+				if(q < start) vv &= 0xffffffffu << (8u * (start - q));
+				if(q + 4u > end) vv &= 0xffffffffu >> (8u * (q + 4u - end));
 				if(ev.rank_mode)
-					slot[u] = start + r + u + ev.rank_offset;
+					id = make_uint4(q + ev.rank_offset, q + 1u + ev.rank_offset, q + 2u + ev.rank_offset, q + 3u + ev.rank_offset);
+				else if(vv)
+					id = __ldg(reinterpret_cast<const uint4 *>(ev.slot_of_rank + q));
 			}
 			// per-lane visible counts of ALL cameras at once, one byte per camera (cameras 0-3 in ca, 4-7 in cb): the four
 			// low (high) bits of a mask byte spread to the four bytes of a register by one multiply.  A lane counts at most
@@ -804,13 +894,14 @@ __global__ void __launch_bounds__(kEmitThreads, 8) emit_kernel(const __grid_cons
 					const uint32_t tot = ((c < 4 ? ta : tb) >> sh) & 0xffu;
 					if(tot)
 					{
-						uint32_t *out = ev.lists[c] + off[c] + (((c < 4 ? ea : eb) >> sh) & 0xffu);
-#pragma unroll
-						for(int u = 0; u < (int)kEmitUnroll; u++)
-						{
-							if((vv >> (8 * u + c)) & 1u)
-								*out++ = slot[u];
-						}
+						uint32_t *out = ev.lists[c];
+						const uint32_t p0 = off[c] + (((c < 4 ? ea : eb) >> sh) & 0xffu);
+						const uint32_t b0 = (vv >> c) & 1u, b1 = (vv >> (8 + c)) & 1u, b2 = (vv >> (16 + c)) & 1u, b3 = (vv >> (24 + c)) & 1u;
+						const uint32_t p1 = p0 + b0, p2 = p1 + b1, p3 = p2 + b2;
+						if(b0) out[p0] = id.x;
+						if(b1) out[p1] = id.y;
+						if(b2) out[p2] = id.z;
+						if(b3) out[p3] = id.w;
 						off[c] += tot;
 					}
 				}
@@ -1088,22 +1179,26 @@ static int launch_spine(rn_scene *s, cudaStream_t stream)
 	{
 		const uint32_t cnt = s->spine_level_ofs[d + 1] - s->spine_level_ofs[d];
 		if(!cnt) continue;
-		spine_kernel<<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots + s->spine_level_ofs[d], cnt);
+		if(s->fma_matrices)
+			spine_kernel<true><<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots + s->spine_level_ofs[d], cnt);
+		else
+			spine_kernel<false><<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots + s->spine_level_ofs[d], cnt);
 		s->launches++;
 	}
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
 
-template <bool CULL>
-static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
+template <bool CULL, bool FMA>
+static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 {
 	const size_t smem = (size_t)warp_smem_bytes(s->inner_cap) * kWarpsPerCta;
-	static size_t configured = 0;
+	// cudaFuncSetAttribute is per device (and per function): remembered in the scene's device slot, not in a static
+	size_t &configured = s->tile_smem_configured[(CULL ? 1 : 0) + (FMA ? 2 : 0)];
 	if(configured < smem)
 	{
-		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		configured = smem;
 	}
 	const bool prof = s->profile && s->prof_used < rn_scene::kProfileSlots;
@@ -1117,7 +1212,7 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][0], stream));
 	}
 	const uint32_t grid = (s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
-	tile_kernel<CULL><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
+	tile_kernel<CULL, FMA><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
 	s->launches++;
 	if(prof)
 	{
@@ -1126,6 +1221,12 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 	}
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
+}
+
+template <bool CULL>
+static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
+{
+	return s->fma_matrices ? launch_tiles_impl<CULL, true>(s, cp, stream) : launch_tiles_impl<CULL, false>(s, cp, stream);
 }
 
 static int clear_super_totals(rn_scene *s, cudaStream_t stream)
@@ -1169,7 +1270,6 @@ static int fill_cull_params(const rn_camera_frustum *cams, uint32_t ncams, CullP
 	RN_REQUIRE(cams != nullptr, RN_ERR_INVALID, "cameras is NULL");
 	RN_REQUIRE(ncams >= 1 && ncams <= RN_MAX_CAMERAS, RN_ERR_INVALID, "n_cameras must be 1..%d, got %u", RN_MAX_CAMERAS, ncams);
 	memset(&cp, 0, sizeof(cp));
-	memcpy(cp.cam, cams, sizeof(rn_camera_frustum) * ncams);
 	cp.n = ncams;
 	for(uint32_t c = 0; c < ncams; c++)
 	{
@@ -1233,7 +1333,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	RN_CUDA(cudaSetDevice(desc->device));
 	cudaDeviceProp prop;
 	RN_CUDA(cudaGetDeviceProperties(&prop, desc->device));
-	RN_REQUIRE(prop.major >= 9, RN_ERR_CUDA, "device %d is sm_%d%d; librn_cuda is built for sm_100a only", desc->device, prop.major, prop.minor);
+	RN_REQUIRE(prop.major == 10, RN_ERR_CUDA, "device %d is sm_%d%d; librn_cuda is built for sm_100a only", desc->device, prop.major, prop.minor);
 	rn_scene *s = new(std::nothrow) rn_scene();
 	RN_REQUIRE(s, RN_ERR_NOMEM, "out of host memory");
 	s->desc = *desc;
@@ -1241,6 +1341,7 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	s->tile_cap = cap;
 	s->inner_cap = inner_cap;
 	s->unit_cap = unit_cap;
+	s->fma_matrices = !(desc->flags & RN_SCENE_STRICT_MATRICES);
 	const size_t n = desc->max_nodes;
 	int rc = RN_OK;
 	if(!rc) rc = dev_alloc(s, &s->c0, n);
@@ -1251,8 +1352,9 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	if(!rc) rc = dev_alloc(s, &s->wrot, n);
 	if(!rc) rc = dev_alloc(s, &s->wsyz, n);
 	if(!rc) rc = dev_alloc(s, &s->wmat, n * 4);
-	if(!rc) rc = dev_alloc(s, &s->d_slot_of_rank, n);
-	if(!rc) rc = dev_alloc(s, &s->vis, n);
+	if(!rc) rc = dev_alloc(s, &s->d_slot_of_rank, n + 4);                  // read four at a time by the compaction
+	const size_t vis_bytes = ((n + 31) / 32) * 32 + 32;                    // mask bytes in rank order, read 4 / 32 at a time
+	if(!rc) rc = dev_alloc(s, &s->vis, vis_bytes);
 
 	if(!rc) rc = dev_alloc(s, &s->list_counts, (size_t)RN_MAX_CAMERAS);
 	if(!rc) rc = dev_alloc(s, &s->spine_slots, n);
@@ -1263,6 +1365,8 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 		return rc;
 	}
 	cudaMemset(s->list_counts, 0, sizeof(uint32_t) * RN_MAX_CAMERAS);
+	cudaMemset(s->vis, 0, vis_bytes);
+	cudaMemset(s->d_slot_of_rank, 0, sizeof(uint32_t) * (n + 4));
 	*out = s;
 	return RN_OK;
 }
@@ -1311,7 +1415,8 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 			uint32_t pbits = RN_NO_PARENT;
 			if(pr != RN_NO_PARENT)
 				pbits = (!t.spine[r] && !t.spine[pr]) ? (kParentInTile | t.inner_idx[pr]) : t.slot_of_rank[pr];
-			const uint32_t fw = (cols->flags[r] & 0xffu) | ((cols->render_group[r] & 0xffu) << 8);
+			// flags word: SceneNode flags | render group << 8 | (rank - tile start) << 16 (where the node's mask byte goes)
+			const uint32_t fw = (cols->flags[r] & 0xffu) | ((cols->render_group[r] & 0xffu) << 8) | ((r - tm.start) << kRankShift);
 			float pf, ff;
 			memcpy(&pf, &pbits, 4);
 			memcpy(&ff, &fw, 4);
@@ -1326,6 +1431,8 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	RN_CUDA(cudaMemcpy(s->c2, h2.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
 	RN_CUDA(cudaMemcpy(s->c3, h3.data(), sizeof(float4) * count, cudaMemcpyHostToDevice));
 	RN_CUDA(cudaMemcpy(s->d_slot_of_rank, t.slot_of_rank.data(), sizeof(uint32_t) * count, cudaMemcpyHostToDevice));
+	// mask bytes of ranks beyond the new node count must read as "invisible" (rn_cull_build_masks reads whole words)
+	RN_CUDA(cudaMemset(s->vis, 0, (((size_t)s->desc.max_nodes + 31) / 32) * 32 + 32));
 	if(!t.spine_slots.empty())
 		RN_CUDA(cudaMemcpy(s->spine_slots, t.spine_slots.data(), sizeof(uint32_t) * t.spine_slots.size(), cudaMemcpyHostToDevice));
 
@@ -1384,6 +1491,7 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	// a full upload re-tiles the scene: volume assignments (slot order) of an earlier upload are void
 	if(s->node_volume) { cudaFree(s->node_volume); s->node_volume = nullptr; }
 	s->volumes_on = false;
+	if(s->lod_node_model) { cudaFree(s->lod_node_model); s->lod_node_model = nullptr; }   // the same goes for the node -> model table
 
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
@@ -1409,8 +1517,10 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	return RN_OK;
 }
 
+// wait = true (the two synchronous entry points): the update is complete on return, so a following rn_transform_* on ANY
+// stream (rn_stream_create hands out non-blocking streams, which do not order against the legacy default stream) sees it.
 static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t first, uint32_t count,
-                            cudaStream_t stream = 0)
+                            cudaStream_t stream = 0, bool wait = true)
 {
 	RN_REQUIRE(cols->parent == nullptr, RN_ERR_INVALID, "the hierarchy can only change through a full upload");
 	RN_REQUIRE(cols->bounding_box == nullptr && cols->render_priority == nullptr, RN_ERR_INVALID,
@@ -1467,10 +1577,14 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 	u.flags = reinterpret_cast<const uint32_t *>(stage(cols->flags, count));
 	u.group = reinterpret_cast<const uint32_t *>(stage(cols->render_group, count));
 	RN_CUDA(cudaMemcpyAsync(d, h, ofs * sizeof(float), cudaMemcpyHostToDevice, stream));
-	RN_CUDA(cudaEventRecord(s->scratch_done, stream));
 	update_kernel<<<(count + 255) / 256, 256, 0, stream>>>(u);
 	s->launches++;
 	RN_CUDA(cudaGetLastError());
+	// both staging buffers (pinned host AND device) are free again once the scatter kernel has read them: the next
+	// update - on whatever stream - waits for this event before it overwrites them
+	RN_CUDA(cudaEventRecord(s->scratch_done, stream));
+	if(wait)
+		RN_CUDA(cudaStreamSynchronize(stream));
 	s->have_world = false;
 	s->have_inverse = s->have_bounds = false;
 	return RN_OK;
@@ -1498,7 +1612,7 @@ extern "C" int rn_scene_update_nodes_async(rn_scene_t *s, const rn_node_columns 
                                            void *cuda_stream)
 {
 	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
-	return update_scattered(s, cols, ranks, 0, count, static_cast<cudaStream_t>(cuda_stream));
+	return update_scattered(s, cols, ranks, 0, count, static_cast<cudaStream_t>(cuda_stream), false);
 }
 
 extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)

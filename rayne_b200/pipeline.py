@@ -19,7 +19,7 @@ from . import capi, shard
 
 
 class PipelinedScene:
-    def __init__(self, rs, n_ranges: int = 4, device: int = 0, **scene_kw):
+    def __init__(self, rs, n_ranges: int = 4, device: int = 0, rank_base: int = 0, **scene_kw):
         """rs: capi.RankedScene (node columns in render-list order).  Range k gets its own stream, earlier ranges
         more urgent ones: without priorities the compaction of range k queues behind the (already launched) transform
         kernels of ranges k+1.., and the first copy would only start when nearly all kernels are done."""
@@ -32,7 +32,7 @@ class PipelinedScene:
             h = capi.SceneHandle(max_nodes=b - a, device=device, **scene_kw)    # makes `device` current
             self.streams.append(capi.stream_create(n_ranges - 1 - len(self.streams)))
             h.upload(shard.extract_shard(rs, a, b))
-            h.set_list_mode(True, a)
+            h.set_list_mode(True, rank_base + a)    # rank_base: first global rank of `rs` when it is itself one GPU's range
             self.handles.append(h)
         self._split_cache = None
 

@@ -81,9 +81,14 @@ def euler_to_quat(euler_deg: np.ndarray) -> np.ndarray:
     return q.astype(np.float32)
 
 
-def _forest_parents(n_trees: int, branching: int, depth: int) -> tuple[np.ndarray, np.ndarray]:
-    """Complete `branching`-ary trees of `depth` levels, each tree in BFS order, trees back to back."""
-    level_sizes = [branching ** k for k in range(depth)]
+def _forest_parents(n_trees: int, branching, depth: int) -> tuple[np.ndarray, np.ndarray]:
+    """Complete `branching`-ary trees of `depth` levels, each tree in BFS order, trees back to back.  `branching` may
+    be a sequence of depth-1 fan-outs, one per level (SURVEY.md's C1: (9, 10, 10) -> 1 + 9 + 90 + 900 nodes per tree)."""
+    fan = [int(branching)] * (depth - 1) if np.isscalar(branching) else [int(b) for b in branching]
+    assert len(fan) == depth - 1, "one fan-out per level below the root"
+    level_sizes = [1]
+    for b in fan:
+        level_sizes.append(level_sizes[-1] * b)
     per_tree = sum(level_sizes)
     local_parent = np.empty(per_tree, dtype=np.int64)
     local_level = np.empty(per_tree, dtype=np.int32)
@@ -93,7 +98,7 @@ def _forest_parents(n_trees: int, branching: int, depth: int) -> tuple[np.ndarra
     prev_start = 0
     for k in range(1, depth):
         cnt = level_sizes[k]
-        local_parent[start:start + cnt] = prev_start + np.arange(cnt) // branching
+        local_parent[start:start + cnt] = prev_start + np.arange(cnt) // fan[k - 1]
         local_level[start:start + cnt] = k
         prev_start = start
         start += cnt
@@ -189,6 +194,15 @@ def make_scene(n_trees: int = 10, branching: int = 4, depth: int = 8, seed: int 
         prio[rng.random(n) < transparent_frac] = RENDER_TRANSPARENT
     return Scene(parent=parent, pos=pos, scale=scale, rot=rot, flags=flags, group=group, priority=prio, sphere=sphere,
                  box=box)
+
+
+def config_scene(name: str, seed: int = 12345, trees: int | None = None) -> Scene:
+    """The scenes BASELINE.json's configs name (SURVEY.md §8(d)): C1 = 10 x (1+9+90+900) = 10 000 nodes, depth 4;
+    C2 = 48 complete 4-ary depth-8 trees = 1 048 560; C4 = 768 trees = 16 776 960; C5 = 3 072 trees = 67 107 840."""
+    if name == "C1":
+        return make_scene(n_trees=trees or 10, branching=(9, 10, 10), depth=4, seed=seed)
+    n = {"C2": 48, "C4": 768, "C5": 3072}[name]
+    return make_scene(n_trees=trees or n, branching=4, depth=8, seed=seed)
 
 
 def flat_scene(n: int, seed: int = 1) -> Scene:
@@ -291,8 +305,22 @@ EMITTER_DTYPE = np.dtype([
     ("start_size", "<f4", 2), ("end_size", "<f4", 2), ("start_rotation", "<f4", 2), ("end_rotation", "<f4", 2),
     ("gravity", "<f4", 3), ("velocity", "<f4", 3), ("vel_min", "<f4", 3), ("vel_max", "<f4", 3),
     ("pos_min", "<f4", 3), ("pos_max", "<f4", 3),
+    ("flags", "<u4"), ("max_particles_soft", "<u4"), ("world_position", "<f4", 3), ("world_scale", "<f4", 3),
 ])
-assert EMITTER_DTYPE.itemsize == 156
+assert EMITTER_DTYPE.itemsize == 188
+EMITTER_NONLOCAL, EMITTER_SOFT_MAX = 1, 2
+
+
+def upgrade_emitters(e: np.ndarray) -> np.ndarray:
+    """Emitter records of an older fixture (without flags / soft maximum / world transform) in the current layout."""
+    e = np.asarray(e)
+    if e.dtype == EMITTER_DTYPE:
+        return e
+    out = np.zeros(e.shape, dtype=EMITTER_DTYPE)
+    for name in e.dtype.names:
+        out[name] = e[name]
+    out["world_scale"] = 1.0
+    return out
 
 
 def make_emitters(n: int, *, max_particles: int = 4000, spawn_rate: float = 3.0 / 4000.0, seed_base: int = 1000,
@@ -314,6 +342,7 @@ def make_emitters(n: int, *, max_particles: int = 4000, spawn_rate: float = 3.0 
     e["vel_max"] = (0.5, 0.5, 0.5)
     e["pos_min"] = (-0.5, -0.5, -0.5)
     e["pos_max"] = (0.5, 0.5, 0.5)
+    e["world_scale"] = 1.0
     if vary:
         rng = np.random.Generator(np.random.PCG64(seed))
         e["life_span"][:, 0] = 0.2 + rng.random(n).astype(np.float32)

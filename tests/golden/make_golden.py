@@ -98,6 +98,33 @@ def main() -> None:
                         out[f"ref_{key}{tag}{k}"] = r[key]
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
         print(name, [r["count"] for r in ref])
+    # emitter modes: !GetIsLocal() (world-space spawn, per-particle gravity) and SetMaxParticlesSoft applied mid-run - one
+    # emitter capped below its hard maximum, one whose soft maximum drops below its live count (the unsigned wrap of
+    # RNParticleEmitter.cpp:204-205 lets it spawn past max_particles)
+    em, steps, soft_after = nonlocal_soft_emitters()
+    ref = refio.run_particles(em, steps, soft_after_steps=soft_after)
+    out = {"in_emitters": em, "in_steps": np.int32(steps), "in_delta": np.float32(1.0 / 60.0), "in_soft_after": np.int32(soft_after)}
+    for k, r in enumerate(ref):
+        out[f"ref_rec{k}"] = r["rec"]
+        out[f"ref_time{k}"] = r["time"]
+    np.savez_compressed(os.path.join(HERE, "particles_nonlocal_soft.npz"), **out)
+    print("particles_nonlocal_soft", [r["count"] for r in ref])
+
+
+def nonlocal_soft_emitters():
+    em = sg.make_emitters(4, max_particles=500, spawn_rate=0.0021, vary=True, seed=7)
+    em["max_particles"] = (500, 350, 500, 300)
+    em["flags"][0] = em["flags"][1] = sg.EMITTER_NONLOCAL
+    em["world_position"][0] = (10.5, -3.25, 7.0)
+    em["world_scale"][0] = (2.0, 0.5, 1.25)
+    em["world_position"][1] = (-100.0, 40.0, 0.125)
+    em["world_scale"][1] = (-1.5, 3.0, 0.75)          # a negative component: the size scale is a plain max
+    em["flags"][2] = em["flags"][3] = sg.EMITTER_SOFT_MAX
+    em["max_particles_soft"][2] = 400
+    em["max_particles_soft"][3] = 20
+    em["spawn_rate"][2] = em["spawn_rate"][3] = 0.002
+    em["life_span"][2] = em["life_span"][3] = (3.0, 4.0)
+    return em, 120, 40
 
 
 if __name__ == "__main__":

@@ -104,12 +104,37 @@ def test_oracle_bounding_sphere_matches_golden(name):
     assert same_floats(sph, g["ref_sphere"])
 
 
+def run_emitter_fixture(o, g) -> None:
+    """Steps an oracle.Emitters through a particle fixture; `in_soft_after` (particles_nonlocal_soft): the soft maxima
+    are only applied after that many steps (SetMaxParticlesSoft on a running emitter)."""
+    em = sg.upgrade_emitters(g["in_emitters"])
+    steps, delta = int(g["in_steps"]), np.float32(g["in_delta"])
+    soft_after = int(g["in_soft_after"]) if "in_soft_after" in g.files else 0
+    if soft_after:
+        # the emitters start WITHOUT their soft maximum: the oracle is created from records whose flag is cleared
+        o.step(delta, soft_after)
+        for k in np.nonzero(em["flags"] & sg.EMITTER_SOFT_MAX)[0]:
+            o.set_soft_max(int(k), int(em["max_particles_soft"][k]))
+        o.step(delta, steps - soft_after)
+    else:
+        o.step(delta, steps)
+
+
+def emitters_without_late_soft_max(g) -> np.ndarray:
+    """The records an implementation is configured with at step 0 of a fixture: a soft maximum that the fixture applies
+    later is not set yet."""
+    em = sg.upgrade_emitters(g["in_emitters"]).copy()
+    if "in_soft_after" in g.files and int(g["in_soft_after"]):
+        em["flags"] &= ~np.uint32(sg.EMITTER_SOFT_MAX)
+    return em
+
+
 @pytest.mark.parametrize("name", PARTICLE_FIXTURES)
 def test_oracle_particles_match_golden(name):
     g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     em = g["in_emitters"]
-    o = oracle.Emitters(em)
-    o.step(np.float32(g["in_delta"]), int(g["in_steps"]))
+    o = oracle.Emitters(emitters_without_late_soft_max(g))
+    run_emitter_fixture(o, g)
     for k in range(len(em)):
         rec, t = o.read(k)
         ref = g[f"ref_rec{k}"]
@@ -181,6 +206,30 @@ def test_oracle_particles_match_live_reference():
         assert same_floats(t, ref[k]["time"])
 
 
+@pytest.mark.ref
+@pytest.mark.skipif(not refio.have_harness("strict"), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_emitter_modes_match_live_reference():
+    """!GetIsLocal() and a soft maximum set at creation (RNParticleEmitter.cpp:128-132,204-205,428-437) against the reference."""
+    em = sg.make_emitters(5, max_particles=400, spawn_rate=0.0013, vary=True, seed=3)
+    em["flags"][:3] = sg.EMITTER_NONLOCAL
+    em["world_position"][:3] = [(1, 2, 3), (-50, 0.5, 9), (0, 0, 0)]
+    em["world_scale"][:3] = [(1, 1, 1), (0.25, 4, 2), (3, 3, -3)]
+    em["flags"][3:] |= sg.EMITTER_SOFT_MAX
+    em["max_particles_soft"][3:] = (37, 0)          # 0: no limit at all (the reference skips the min)
+    em["max_particles"][4] = 90
+    em["spawn_rate"][4] = 0.001
+    em["life_span"][4] = (2.0, 3.0)
+    ref = refio.run_particles(em, 130)
+    o = oracle.Emitters(em)
+    o.step(np.float32(1.0 / 60.0), 130)
+    for k in range(len(em)):
+        rec, t = o.read(k)
+        assert rec.shape == ref[k]["rec"].shape, k
+        assert same_floats(rec[:, :23], ref[k]["rec"][:, :23]), k
+        assert same_floats(t, ref[k]["time"])
+    assert ref[3]["count"] == 37 and ref[4]["count"] > 90
+
+
 def test_oracle_billboard_vertex_stage():
     """Shaders/Particles.hlsl particles_vertex restated (unpinned: the shader cannot run here) against the formula in
     float64: clip = MVP * (float4(pos, 1) + invMV * float4(uv1, 0, 0)), colour * ambient."""
@@ -229,3 +278,36 @@ def test_volumes_match_golden():
     for p, want in (((1, 1, 1), 1), ((0, 0, 0), 1), ((1.5, 1, 1), 2), ((2.0001, 1, 1), 0), ((-0.0001, 0.5, 0.5), 0)):
         assert capi.choose_volume(b, p) == want == oracle.choose_volume(b, p)
     assert capi.choose_volume(np.zeros((0, 6), np.float32), (0, 0, 0)) == 0
+
+
+def test_oracle_lod_selection_restatement():
+    """The LOD extension's C restatement against a literal numpy evaluation of RNEntity.cpp:98-106 + RNModel.cpp:260-281."""
+    rng = np.random.default_rng(4)
+    n = 500
+    wpos = (rng.random((n, 3)).astype(np.float32) - np.float32(0.5)) * np.float32(400)
+    so = np.array([0, 1, 4, 6], np.uint32)
+    sd = np.array([0.5, 0.05, 0.2, 0.6, 0.1, 0.3], np.float32)
+    model = rng.integers(0, 4, size=n).astype(np.uint16)
+    model[model == 3] = 0xffff
+    cam = wpos[7].copy()
+    ids = rng.permutation(n).astype(np.uint32)
+    got = oracle.select_lod(ids, wpos, model, so, sd, cam, 300.0)
+    for e, i in enumerate(ids):
+        m = int(model[i])
+        if m == 0xffff:
+            want = 0
+        else:
+            dist = sg_dist(wpos[i], cam) / np.float32(300.0)
+            stages = sd[so[m]:so[m + 1]]
+            if len(stages) <= 1 or dist <= np.finfo(np.float32).eps:
+                want = 0
+            else:
+                hit = np.nonzero(dist <= stages)[0]
+                want = int(hit[0]) if len(hit) else len(stages) - 1
+        assert got[e] == want, (e, i, m)
+    assert got[list(ids).index(7)] == 0
+
+
+def sg_dist(a, b) -> np.float32:
+    d = (a - b).astype(np.float32)
+    return np.sqrt(np.float32(np.float32(np.float32(d[0] * d[0]) + np.float32(d[1] * d[1])) + np.float32(d[2] * d[2])))

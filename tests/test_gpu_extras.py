@@ -28,7 +28,7 @@ def test_inverse_and_bounds_match_golden(name):
     """A3 + A4 bit-exact against the reference's GetInverseWorldTransform / GetBoundingSphere / GetBoundingBox."""
     scene, cams, g = load_golden_scene(name)
     rs = capi.RankedScene(scene)
-    with capi.SceneHandle(max_nodes=scene.n) as h:
+    with capi.SceneHandle(max_nodes=scene.n, strict_matrices=True) as h:
         h.upload(rs)
         with pytest.raises(capi.RNError):
             h.download(capi.DL_INVERSE_WORLD_MATRIX)     # not computed yet: loud, not stale
@@ -250,7 +250,7 @@ def test_instance_records_match_golden(name):
     fr = capi.build_frustums(cams[:capi.RN_MAX_CAMERAS])
     v, _, pv = capi.build_camera_matrices(cams)
     assert same_floats(v, g["ref_view"]) and same_floats(pv, g["ref_projview"])
-    with capi.SceneHandle(max_nodes=scene.n) as h:
+    with capi.SceneHandle(max_nodes=scene.n, strict_matrices=True) as h:
         h.upload(rs)
         h.transform_cull(fr)
         with pytest.raises(capi.RNError):
@@ -282,7 +282,7 @@ def test_instance_records_match_oracle_after_sort(rank_mode):
     assert same_floats(v, ov) and same_floats(pv, opv)
     ref = oracle.scene_reference(scene, oracle.frustums(cams), cameras=cams)
     rs = capi.RankedScene(scene)
-    with capi.SceneHandle(max_nodes=scene.n) as h:
+    with capi.SceneHandle(max_nodes=scene.n, strict_matrices=True) as h:
         h.upload(rs)
         if rank_mode:
             h.set_list_mode(True, 77)
@@ -389,3 +389,51 @@ def test_volumes_match_golden(rank_mode, fused):
         for c, l in enumerate(plain):
             vis = np.zeros(scene.n, bool); vis[ref["lists"][c]] = True
             assert np.array_equal(l, rs.order[vis[rs.order]]), f"camera {c} (filter off)"
+
+
+@pytest.mark.parametrize("rank_mode", [False, True])
+def test_lod_selection_extension_matches_oracle(rank_mode):
+    """rn_cull_select_lod (extension: Entity::Render's #else branch + Model::GetLODStageForDistance, compiled out in the
+    reference) against the C restatement, per entry of an unsorted and of a front-to-back sorted list; nodes without a
+    model, single-stage models, a camera sitting exactly on a node (distance <= epsilon) and distances beyond the last
+    stage included."""
+    import torch
+    from oracle import oracle
+    scene = sg.make_scene(n_trees=20, branching=4, depth=5, seed=31, random_bounds=True)
+    cams = np.stack([sg.make_camera(flags=sg.CAM_USE_SIMPLE_CULLING), sg.make_camera(pos=(20, 3, 4), far=800, flags=capi.CAM_SORT_FRONT_TO_BACK)])
+    fr = capi.build_frustums(cams)
+    rs = capi.RankedScene(scene)
+    rng = np.random.default_rng(9)
+    stage_counts = np.array([1, 2, 3, 5, 4], np.uint32)
+    so = np.concatenate([[0], np.cumsum(stage_counts)]).astype(np.uint32)
+    sd = np.concatenate([np.sort(rng.random(int(c)).astype(np.float32) * np.float32(0.8)) for c in stage_counts]).astype(np.float32)
+    model = rng.integers(0, 6, size=scene.n).astype(np.uint16)
+    model[model == 5] = 0xffff                                       # not an Entity
+    with capi.SceneHandle(max_nodes=scene.n) as h:
+        h.upload(rs)
+        if rank_mode:
+            h.set_list_mode(True, 1000)
+        h.lod_set_models(so, sd)
+        h.lod_set_node_models(model[rs.order])
+        ref = oracle.scene_reference(scene, fr)
+        # the LOD camera of view 0 sits exactly on a node of its list: distance 0 <= epsilon -> stage 0
+        probe = int(ref["lists"][0][len(ref["lists"][0]) // 2])
+        lod_pos = [ref["wpos"][probe], cams["pos"][1]]
+        h.transform_cull(fr)
+        h.cull_sort(np.ascontiguousarray(cams["pos"], np.float32))
+        rank_of_slot = h.download(capi.DL_RANK_OF_SLOT)
+        for c in range(2):
+            ids = h.read_list(c)
+            ranks = (ids - 1000) if rank_mode else rank_of_slot[ids]
+            creation = rs.order[ranks]
+            out = torch.zeros(len(ids) + 8, dtype=torch.uint8, device="cuda")
+            h.select_lod(c, lod_pos[c], float(cams["far"][c]), out.data_ptr(), len(ids))
+            torch.cuda.synchronize()
+            got = out.cpu().numpy()
+            want = oracle.select_lod(creation, ref["wpos"], model, so, sd, lod_pos[c], float(cams["far"][c]))
+            assert np.array_equal(got[:len(ids)], want), f"camera {c}"
+            assert (got[len(ids):] == 0).all()                        # nothing written beyond the list
+            assert len(np.unique(want)) >= 3
+        assert oracle.select_lod(np.array([probe], np.uint32), ref["wpos"], np.full(scene.n, 3, np.uint16), so, sd, lod_pos[0], 500.0)[0] == 0
+        with pytest.raises(capi.RNError):
+            h.select_lod(5, lod_pos[0], 500.0, 256, 1)

@@ -9,7 +9,7 @@ from tests.helpers import check_against_oracle, standard_cameras, run_cuda, same
 pytestmark = pytest.mark.gpu
 
 CASES = {
-    "c1_10k_depth4": dict(n_trees=10, branching=9, depth=4, seed=12345),       # ~8.2k nodes (9-ary, 4 levels)
+    "c1_10k_depth4": dict(n_trees=10, branching=(9, 10, 10), depth=4, seed=12345),   # SURVEY's C1: 10 x (1+9+90+900) = 10 000
     "uniform_4ary_depth8": dict(n_trees=3, branching=4, depth=8, seed=2),
     "nonuniform_groups_prio": dict(n_trees=12, branching=4, depth=6, seed=4, nonuniform_scale=True,
                                    random_bounds=True, random_groups=True, priorities=True),
@@ -22,10 +22,36 @@ CASES = {
 
 @pytest.mark.parametrize("name", list(CASES))
 @pytest.mark.parametrize("fused", [True, False])
-def test_scene_parity(name, fused):
+@pytest.mark.parametrize("strict", [True, False])
+def test_scene_parity(name, fused, strict):
+    """strict: RN_SCENE_STRICT_MATRICES, matrices bit-exact; otherwise the library default (FMA matrix chain, 1e-5).
+    Lists and world TRS are bit-exact in both."""
     scene = sg.make_scene(**CASES[name])
-    got, ref = check_against_oracle(scene, standard_cameras(), fused=fused)
+    got, ref = check_against_oracle(scene, standard_cameras(), fused=fused, strict=strict)
     assert got["stats"]["nodes"] == scene.n
+    if name == "c1_10k_depth4":
+        assert scene.n == 10000
+
+
+def test_c2_full_size_against_the_oracle():
+    """Config C2 exactly (48 complete 4-ary depth-8 trees = 1 048 560 nodes): lists, world TRS and matrices against
+    the C oracle for the single default camera BASELINE.json names AND for the 6-view rig, in both matrix modes,
+    fused and unfused.  (And against the reference itself where oracle/_ref travels with the snapshot.)"""
+    from oracle import oracle, refio
+    scene = sg.config_scene("C2")
+    assert scene.n == 1048560
+    for cams in (np.atleast_1d(sg.make_camera()), sg.six_view_rig()):
+        fr = capi.build_frustums(cams)
+        ref = oracle.scene_reference(scene, fr)
+        check_against_oracle(scene, cams, strict=True, ref=ref)
+        check_against_oracle(scene, cams, strict=False, ref=ref)
+        check_against_oracle(scene, cams, strict=True, ref=ref, fused=False)
+        if refio.have_harness("strict"):
+            real = refio.run_scene(scene, cams, kind="strict")
+            assert np.array_equal(real["order"], ref["order"])
+            assert same_floats(real["wmat"], ref["wmat"])
+            for a, b in zip(real["lists"], ref["lists"]):
+                assert np.array_equal(a, b)
 
 
 @pytest.mark.parametrize("tile", [64, 256, 1024])
@@ -79,7 +105,7 @@ def test_errors_are_loud():
 
 
 def test_full_size_properties():
-    """1 M nodes (config C2): order-independent properties instead of the (slow) scalar oracle."""
+    """1 M nodes (config C2): order-independent properties (the oracle comparison is the test above)."""
     scene = sg.make_scene(n_trees=48, branching=4, depth=8, seed=12345)
     cams = standard_cameras()
     fr = capi.build_frustums(cams)
