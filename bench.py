@@ -131,8 +131,16 @@ def ncu_traffic(nodes: int, views: int):
     return None, None
 
 
+RIG = "reference"
+
+
 def config_cameras(cfg: dict) -> np.ndarray:
-    return sg.six_view_rig() if cfg["views"] == 6 else np.atleast_1d(sg.make_camera())
+    """6 views: the two VR eye cameras + the four cascade cameras the reference's Light::UpdateShadows derives for a
+    directional light with the default ShadowParameter and the head camera as target (rn_light_build_cascades, pinned by
+    tests/golden/cascades_basic.npz).  --rig legacy: round 1's hand-parameterised cascade cameras (scenegen.six_view_rig)."""
+    if cfg["views"] != 6:
+        return np.atleast_1d(sg.make_camera())
+    return sg.vr_cascade_rig() if RIG == "reference" else sg.six_view_rig()
 
 
 def build_scene(cfg: dict, trees: int, seed: int):
@@ -856,7 +864,8 @@ def run_ours(args) -> dict:
     achieved = tile_bytes / (tile_avg_ms * 1e-3) / 1e9
     desc = {"C1": "C1: 10 x (1+9+90+900) = 10 000 SceneNodes, depth 4, 1 camera",
             "C2": f"C2: {n} SceneNodes ({trees} complete 4-ary depth-8 trees), 1 camera frustum cull with visibility list",
-            "C4": f"C4: {n} SceneNodes per GPU ({trees} complete 4-ary depth-8 trees), 6-view cull (2 eye + 4 shadow-cascade cameras)",
+            "C4": f"C4: {n} SceneNodes per GPU ({trees} complete 4-ary depth-8 trees), 6-view cull (2 eye + 4 shadow-cascade cameras"
+                  + (" as Light::UpdateShadows derives them)" if RIG == "reference" else ", round-1 hand-set rig)"),
             "C4-strong": f"C4-strong: one fixed scene of {n_total} SceneNodes ({trees} trees) cut over {world} GPU(s) by plan_shards, 6-view cull",
             "C5": f"C5: one scene of {n_total} SceneNodes ({trees} trees) + {n_emitters} emitters x 4000 particles cut over {world} GPU(s), "
                   "6-view cull + particle step per frame"}[args.config]
@@ -968,6 +977,8 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the parity gate")
     ap.add_argument("--verify-full", action="store_true", help="parity gate over the WHOLE scene through the C oracle (~25 s at 16.8 M nodes; N = 1)")
     ap.add_argument("--strict-matrices", action="store_true", help="RN_SCENE_STRICT_MATRICES: world matrices bit-exact (no FMA on the matrix chain)")
+    ap.add_argument("--rig", choices=("reference", "legacy"), default="reference",
+                    help="6-view configs: cascade cameras derived like the reference's Light::UpdateShadows (default) or round 1's hand-set ones")
     ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
     ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="multicast",
                     help="N>1: multimem stores of the mask kernel through NVLS multicast (falls back to NCCL where "
@@ -979,6 +990,8 @@ def main():
     ap.add_argument("--inner-nodes", type=int, default=0, help="rn_scene_desc.tile_inner_nodes (0 = library default)")
     ap.add_argument("--unit-nodes", type=int, default=0, help="rn_scene_desc.tile_unit_nodes (0 = library default)")
     args = ap.parse_args()
+    global RIG
+    RIG = args.rig
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # stdout carries exactly ONE line, the JSON: libraries that print to fd 1 (NCCL's version banner) go to stderr
     sys.stdout.flush()

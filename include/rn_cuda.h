@@ -48,6 +48,7 @@ typedef struct rn_scene rn_scene_t;
 #define RN_NODE_HIDDEN     (1u << 1)
 #define RN_NODE_NOCULLING  (1u << 2)
 /* RN::Camera::Flags bits the path looks at (Source/Scene/RNCamera.h:30-50). */
+#define RN_CAMERA_RENDER_EARLY       (1u << 19)
 #define RN_CAMERA_ORTHOGONAL         (1u << 21)
 #define RN_CAMERA_USE_SIMPLE_CULLING (1u << 26)
 #define RN_CAMERA_SORT_TRANSPARENT_BACK_TO_FRONT (1u << 5)   /* part of Camera::Flags::Defaults */
@@ -311,6 +312,24 @@ int rn_camera_build_frustum(const rn_camera_desc *camera, rn_camera_frustum *out
 /* Camera::GetViewMatrix / GetProjectionMatrix as Camera::PostUpdate leaves them (Source/Scene/RNCamera.cpp:296-340)
  * and their product projection * view; 16 floats each, column-major, any of the outputs may be NULL.  Host function. */
 int rn_camera_build_matrices(const rn_camera_desc *camera, float *view, float *projection, float *proj_view);
+
+/* The shadow-cascade cameras of a directional light: Light::UpdateShadows (Source/Scene/RNLight.cpp:475-529: split
+ * distances = blend of a linear and a logarithmic subdivision of the target camera's depth range, unless a split carries
+ * its own maxDistance) and Camera::MakeShadowSplit (Source/Scene/RNCamera.cpp:240-287: bounding sphere of the split's
+ * frustum slice, light camera placed directional_shadow_distance up the light direction, snapped to the shadow map's
+ * texel grid in light space, square orthographic frustum).  Writes n_splits camera records ready for
+ * rn_camera_build_frustum / rn_cull and, if out_proj_view != NULL, the 16 floats per split the reference keeps in
+ * Light::_shadowCameraMatrices (projection * inverse world transform).  Pure host function. */
+typedef struct rn_shadow_desc {
+	uint32_t n_splits;                        /* ShadowParameter::splits.size(), 1..RN_MAX_CAMERAS */
+	float    split_max_distance[RN_MAX_CAMERAS]; /* ShadowSplit::maxDistance (0 = derive from the blend) */
+	float    resolution;                      /* ShadowParameter::resolution: width = height of a cascade's frame */
+	float    clip_near, clip_far;             /* of the cascade cameras (ShadowParameter::clipNear / clipFar) */
+	float    directional_shadow_distance, distance_blend_factor, max_shadow_dist;
+	float    light_world_rotation[4];         /* the Light's GetWorldRotation(), x y z w */
+} rn_shadow_desc;
+int rn_light_build_cascades(const rn_camera_desc *target, const rn_shadow_desc *shadow, rn_camera_desc *out_cameras,
+                            float *out_proj_view);
 
 /* SceneBasic::AddNode / AddRenderNode list order (Source/Scene/RNSceneBasic.cpp:652-676,683-736 and
  * Source/Scene/RNSceneNode.cpp:270-294) for nodes given in CREATION order: parent[i] < i is the creation index of

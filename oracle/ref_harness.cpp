@@ -9,6 +9,7 @@
 //   ref_harness particles <in.bin> <out.bin>      run K emitter steps, dump every live particle
 //   ref_harness bench-scene     <in.bin> <frames> <warmup>   print JSON timing line (ms per frame)
 //   ref_harness bench-particles <in.bin> <steps>  <warmup>   print JSON timing line
+//   ref_harness cascades  <in.bin> <out.bin>      Light::UpdateShadows + Camera::MakeShadowSplit for a directional light
 //
 // File formats are documented in oracle/refio.py (the only reader/writer on the Python side).
 //
@@ -623,6 +624,101 @@ namespace
 		return 0;
 	}
 
+	// ---- shadow cascades ---------------------------------------------------------------------------------
+	// The REAL Light::UpdateShadows (Source/Scene/RNLight.cpp:475-529) and Camera::MakeShadowSplit
+	// (Source/Scene/RNCamera.cpp:240-287) for a directional light.  Light::ActivateDirectionalShadows wants depth
+	// textures and framebuffers from the renderer; the harness fills the members it would have set (shadow cameras as
+	// it configures them, :314-326, _shadowTarget, _shadowParameter) directly and gives every shadow camera's render
+	// pass the frame its framebuffer would have had (resolution x resolution).
+	// in : "RNCI" v1: u32 magic, version; CameraDesc target; f32 lightRot[4]; u32 nSplits; f32 maxDistance[nSplits];
+	//      f32 resolution, clipNear, clipFar, directionalShadowDistance, distanceBlendFactor, maxShadowDist
+	// out: "RNCO" v1: u32 magic, version, nSplits; per split: f32 pos[3], rot[4], ortho[4] (l, r, b, t), clipNear, clipFar,
+	//      u32 flags, f32 frustum[28], f32 projview[16] (_shadowCameraMatrices)
+	int CmdCascades(const char *inPath, const char *outPath)
+	{
+		Reader r(inPath);
+		uint32_t magic = r.get<uint32_t>(); uint32_t version = r.get<uint32_t>();
+		if(magic != 0x49434e52u || version != 1) { fprintf(stderr, "bad cascade file\n"); return 2; }
+		CameraDesc d = r.get<CameraDesc>();
+		float lq[4]; for(int i = 0; i < 4; i++) lq[i] = r.get<float>();
+		uint32_t nSplits = r.get<uint32_t>();
+		std::vector<float> maxDistance = r.vec<float>(nSplits);
+		float resolution = r.get<float>(), clipNear = r.get<float>(), clipFar = r.get<float>();
+		float shadowDistance = r.get<float>(), blend = r.get<float>(), maxShadowDist = r.get<float>();
+
+		HarnessScene *scene = new HarnessScene();
+		Camera *target = new Camera();
+		target->SetFlags(target->GetFlags() | d.flags);
+		target->SetPosition(Vector3(d.pos[0], d.pos[1], d.pos[2]));
+		target->SetRotation(Quaternion(d.rot[0], d.rot[1], d.rot[2], d.rot[3]));
+		target->SetScale(Vector3(d.scale[0], d.scale[1], d.scale[2]));
+		target->SetFOV(d.fov);
+		target->SetAspectRatio(d.aspect);
+		target->SetClipNear(d.clipNear);
+		target->SetClipFar(d.clipFar);
+		if(d.hasProjection)
+		{
+			Matrix m;
+			for(int i = 0; i < 16; i++) m.m[i] = d.projection[i];
+			target->SetProjectionMatrix(m);
+		}
+		scene->AddNode(target);
+
+		Light *light = new Light(Light::Type::DirectionalLight);
+		light->SetWorldRotation(Quaternion(lq[0], lq[1], lq[2], lq[3]));
+		scene->AddNode(light);
+
+		ShadowParameter param(target, static_cast<size_t>(resolution));
+		param.splits.clear();
+		for(uint32_t i = 0; i < nSplits; i++) param.splits.push_back(ShadowSplit(1, 0, 2.0f, 512.0f, maxDistance[i]));
+		param.clipNear = clipNear; param.clipFar = clipFar;
+		param.directionalShadowDistance = shadowDistance; param.distanceBlendFactor = blend; param.maxShadowDist = maxShadowDist;
+		light->_shadowParameter = param;
+		light->_shadowTarget = target->Retain();
+		std::vector<Camera *> cams;
+		for(uint32_t i = 0; i < nSplits; i++)
+		{
+			light->_shadowCameraMatrices.push_back(Matrix());
+			Camera *tempcam = new Camera();
+			tempcam->GetRenderPass()->SetFrame(Rect(0.0f, 0.0f, resolution, resolution));
+			tempcam->SetFlags(Camera::Flags::Orthogonal | Camera::Flags::RenderEarly);
+			tempcam->SetLODCamera(target);
+			tempcam->SetClipNear(param.clipNear);
+			tempcam->SetClipFar(param.clipFar);
+			scene->AddNode(tempcam);
+			light->_shadowDepthCameras.AddObject(tempcam);
+			cams.push_back(tempcam);
+		}
+		light->UpdateShadows();
+
+		Writer w(outPath);
+		w.put<uint32_t>(0x4f434e52u); w.put<uint32_t>(1); w.put<uint32_t>(nSplits);
+		for(uint32_t i = 0; i < nSplits; i++)
+		{
+			Camera *cam = cams[i];
+			cam->PostUpdate();
+			cam->UpdateFrustum();
+			Vector3 p = cam->GetWorldPosition(); Quaternion q = cam->GetWorldRotation();
+			w.put<float>(p.x); w.put<float>(p.y); w.put<float>(p.z);
+			w.put<float>(q.x); w.put<float>(q.y); w.put<float>(q.z); w.put<float>(q.w);
+			w.put<float>(cam->_orthoLeft); w.put<float>(cam->_orthoRight); w.put<float>(cam->_orthoBottom); w.put<float>(cam->_orthoTop);
+			w.put<float>(cam->GetClipNear()); w.put<float>(cam->GetClipFar());
+			w.put<uint32_t>(static_cast<uint32_t>(cam->GetFlags()));
+			float fr[28];
+			fr[0] = cam->_frustumCenter.x; fr[1] = cam->_frustumCenter.y; fr[2] = cam->_frustumCenter.z; fr[3] = cam->_frustumRadius;
+			const Plane *planes[6] = { &cam->frustums._frustumLeft, &cam->frustums._frustumRight, &cam->frustums._frustumTop,
+			                           &cam->frustums._frustumBottom, &cam->frustums._frustumNear, &cam->frustums._frustumFar };
+			for(int k = 0; k < 6; k++)
+			{
+				fr[4 + k*4 + 0] = planes[k]->_normal.x; fr[4 + k*4 + 1] = planes[k]->_normal.y;
+				fr[4 + k*4 + 2] = planes[k]->_normal.z; fr[4 + k*4 + 3] = planes[k]->_d;
+			}
+			for(int k = 0; k < 28; k++) w.put<float>(fr[k]);
+			for(int k = 0; k < 16; k++) w.put<float>(light->_shadowCameraMatrices[i].m[k]);
+		}
+		return 0;
+	}
+
 	int CmdBenchParticles(const char *inPath, int steps, int warmup)
 	{
 		ParticleInput in = ReadParticles(inPath);
@@ -659,7 +755,7 @@ int main(int argc, char **argv)
 	signal(SIGSEGV, OnSegv);
 	if(argc < 3)
 	{
-		fprintf(stderr, "usage: %s scene|particles|bench-scene|bench-particles <in> ...\n", argv[0]);
+		fprintf(stderr, "usage: %s scene|particles|bench-scene|bench-particles|cascades <in> ...\n", argv[0]);
 		return 2;
 	}
 	// Minimal bootstrap: no Kernel, no manifest, no files (reference: RNBase.cpp:164-176, RNWorkQueue.cpp:65-71).
@@ -675,6 +771,7 @@ int main(int argc, char **argv)
 	else if(cmd == "particles" && argc >= 4) rc = CmdParticles(argv[2], argv[3]);
 	else if(cmd == "bench-scene" && argc >= 5) rc = CmdBenchScene(argv[2], atoi(argv[3]), atoi(argv[4]), renderer);
 	else if(cmd == "bench-particles" && argc >= 5) rc = CmdBenchParticles(argv[2], atoi(argv[3]), atoi(argv[4]));
+	else if(cmd == "cascades" && argc >= 4) rc = CmdCascades(argv[2], argv[3]);
 	else fprintf(stderr, "bad arguments\n");
 	fflush(stdout);
 	(void)pool;

@@ -137,6 +137,34 @@ def bench_scene(scene: Scene, cameras: np.ndarray, frames: int, warmup: int,
         return json.loads(r.stdout.strip().splitlines()[-1])
 
 
+def run_cascades(target: np.ndarray, shadow: np.ndarray, kind: str = "strict") -> dict:
+    """The reference's Light::UpdateShadows + Camera::MakeShadowSplit (harness command `cascades`).  target: one
+    CAMERA_DTYPE record; shadow: one scenegen.SHADOW_DTYPE record.  Returns per split: pos [n,3], rot [n,4], ortho
+    [n,4] (left, right, bottom, top), clip [n,2], flags [n], frustum [n,28], projview [n,16]."""
+    from rayne_b200.scenegen import SHADOW_DTYPE
+    t = np.ascontiguousarray(np.atleast_1d(target), dtype=CAMERA_DTYPE)[:1]
+    sh = np.ascontiguousarray(np.atleast_1d(shadow), dtype=SHADOW_DTYPE)[0]
+    n = int(sh["n_splits"])
+    with tempfile.TemporaryDirectory() as tmp:
+        fin, fout = os.path.join(tmp, "in.bin"), os.path.join(tmp, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(np.array([0x49434E52, 1], dtype="<u4").tobytes())
+            f.write(t.tobytes())
+            f.write(np.asarray(sh["light_rot"], "<f4").tobytes())
+            f.write(np.array([n], dtype="<u4").tobytes())
+            f.write(np.asarray(sh["split_max_distance"][:n], "<f4").tobytes())
+            f.write(np.array([sh["resolution"], sh["clip_near"], sh["clip_far"], sh["directional_shadow_distance"],
+                              sh["distance_blend_factor"], sh["max_shadow_dist"]], dtype="<f4").tobytes())
+        subprocess.run([harness_path(kind), "cascades", fin, fout], check=True, stdout=subprocess.DEVNULL)
+        buf = np.fromfile(fout, dtype=np.uint8)
+    magic, version, ns = np.frombuffer(buf, dtype="<u4", count=3)
+    assert magic == 0x4F434E52 and version == 1 and ns == n
+    rec = np.dtype([("pos", "<f4", 3), ("rot", "<f4", 4), ("ortho", "<f4", 4), ("clip", "<f4", 2), ("flags", "<u4"),
+                    ("frustum", "<f4", 28), ("projview", "<f4", 16)])
+    arr = np.frombuffer(buf, dtype=rec, count=n, offset=12)
+    return {k: arr[k].copy() for k in rec.names}
+
+
 def write_particle_input(path: str, emitters: np.ndarray, steps: int, delta: float, options: int = 0,
                          soft_after_steps: int = 0) -> None:
     from rayne_b200.scenegen import upgrade_emitters

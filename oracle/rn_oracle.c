@@ -1028,3 +1028,281 @@ void rn_oracle_select_lod(const uint32_t *ids, uint32_t n_entries, const float *
 		out[e] = (uint8_t)stage;
 	}
 }
+
+/* ---- C8: software occlusion culling of SceneBasic::Render ----------------------------------------------------- */
+/* Source/Scene/RNSceneBasic.cpp:152-208 RasterizeClipSpaceTriangle, :210-318 RasterizeMesh, :320-405 TestBoundingBox,
+ * :445-573 the occluder selection and the per-node test with its 50-frame hysteresis.  Matrices column-major
+ * (RN::Matrix::m), products summed left to right (Source/Math/RNMatrix.h:90-142, 226-232).
+ * The 40 x 40 depth buffer holds reverse-Z depth (1 = near), cleared to 0. */
+enum { OCC_W = 40, OCC_H = 40 };
+
+typedef struct { float x, y, z, w; } ovec4;
+
+static ovec4 omat_vec(const float *m, ovec4 v)
+{
+	ovec4 r;
+	r.x = m[0] * v.x + m[4] * v.y + m[8] * v.z + m[12] * v.w;
+	r.y = m[1] * v.x + m[5] * v.y + m[9] * v.z + m[13] * v.w;
+	r.z = m[2] * v.x + m[6] * v.y + m[10] * v.z + m[14] * v.w;
+	r.w = m[3] * v.x + m[7] * v.y + m[11] * v.z + m[15] * v.w;
+	return r;
+}
+static void omat_mul(const float *a, const float *b, float *o)
+{
+	for(int c = 0; c < 4; c++)
+		for(int r = 0; r < 4; r++)
+			o[c * 4 + r] = a[r] * b[c * 4] + a[4 + r] * b[c * 4 + 1] + a[8 + r] * b[c * 4 + 2] + a[12 + r] * b[c * 4 + 3];
+}
+/* edgeFunction, RNSceneBasic.cpp:27-30 */
+static float oedge(float ax, float ay, float bx, float by, float cx, float cy)
+{
+	return (cx - ax) * (by - ay) - (cy - ay) * (bx - ax);
+}
+static ovec4 ovadd(ovec4 a, ovec4 b) { ovec4 r = {a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w}; return r; }
+static ovec4 ovsub(ovec4 a, ovec4 b) { ovec4 r = {a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w}; return r; }
+static ovec4 ovscale(ovec4 a, float n) { ovec4 r = {a.x * n, a.y * n, a.z * n, a.w * n}; return r; }
+
+/* RasterizeClipSpaceTriangle, :152-208 */
+static void occ_raster_triangle(float *depthbuf, ovec4 A, ovec4 B, ovec4 C)
+{
+	ovec4 *v[3] = {&A, &B, &C};
+	for(int k = 0; k < 3; k++)
+	{
+		ovec4 *p = v[k];
+		float w = p->w;
+		p->x /= w; p->y /= w; p->z /= w; p->w /= w;
+		p->x = p->x * 0.5f + 0.5f;
+		p->x *= (float)OCC_W;
+		p->y = p->y * 0.5f + 0.5f;
+		p->y *= (float)OCC_H;
+	}
+	float area = oedge(A.x, A.y, B.x, B.y, C.x, C.y);
+	if(area < 0) return;
+	uint16_t minX = (uint16_t)fmin_std(fmax_std(fmin_std(A.x, fmin_std(B.x, C.x)), 0.0f), (float)(OCC_W - 1));
+	uint16_t minY = (uint16_t)fmin_std(fmax_std(fmin_std(A.y, fmin_std(B.y, C.y)), 0.0f), (float)(OCC_H - 1));
+	uint16_t maxX = (uint16_t)fmin_std(fmax_std(fmax_std(A.x, fmax_std(B.x, C.x)), 0.0f), (float)(OCC_W - 1));
+	uint16_t maxY = (uint16_t)fmin_std(fmax_std(fmax_std(A.y, fmax_std(B.y, C.y)), 0.0f), (float)(OCC_H - 1));
+	for(uint16_t y = minY; y <= maxY; y++)
+	{
+		for(uint16_t x = minX; x <= maxX; x++)
+		{
+			float px = (float)x, py = (float)y;
+			float w0 = oedge(B.x, B.y, C.x, C.y, px, py);
+			float w1 = oedge(C.x, C.y, A.x, A.y, px, py);
+			float w2 = oedge(A.x, A.y, B.x, B.y, px, py);
+			if(w0 >= 0 && w1 >= 0 && w2 >= 0)
+			{
+				w0 /= area; w1 /= area; w2 /= area;
+				float depth = w0 * A.z + w1 * B.z + w2 * C.z - 0.000001f;
+				if(depth <= 1.0f)
+				{
+					float *cell = &depthbuf[OCC_W * (OCC_H - y - 1) + x];
+					if(depth > *cell) *cell = depth;
+				}
+			}
+		}
+	}
+}
+
+/* RasterizeMesh, :210-318: tris = 9 floats per triangle as the mesh's triangle chunk iterator yields them (posA, posB, posC) */
+static void occ_raster_mesh(float *depthbuf, const float *mvp, const float *tris, uint32_t ntris)
+{
+	for(uint32_t i = 0; i < ntris; i++)
+	{
+		const float *t = tris + (size_t)i * 9;
+		ovec4 pa = {t[0], t[1], t[2], 1.0f}, pb = {t[3], t[4], t[5], 1.0f}, pc = {t[6], t[7], t[8], 1.0f};
+		ovec4 A = omat_vec(mvp, pb);      /* the reference swaps A and B on purpose (:227-229) */
+		ovec4 B = omat_vec(mvp, pa);
+		ovec4 C = omat_vec(mvp, pc);
+		if(A.z < -A.w && B.z < -B.w && C.z < -C.w) continue;
+		if(A.z > A.w && B.z > B.w && C.z > C.w) continue;
+		float dA = (A.z - (A.w)), dB = (B.z - (B.w)), dC = (C.z - (C.w));
+		if(A.z > A.w && B.z > B.w)
+		{
+			float tA = dA / (dA - dC), tB = dB / (dB - dC);
+			A = ovadd(A, ovscale(ovsub(C, A), tA));
+			B = ovadd(B, ovscale(ovsub(C, B), tB));
+		}
+		else if(A.z > A.w && C.z > C.w)
+		{
+			float tA = dA / (dA - dB), tC = dC / (dC - dB);
+			A = ovadd(A, ovscale(ovsub(B, A), tA));
+			C = ovadd(C, ovscale(ovsub(B, C), tC));
+		}
+		else if(B.z > B.w && C.z > C.w)
+		{
+			float tB = dB / (dB - dA), tC = dC / (dC - dA);
+			B = ovadd(B, ovscale(ovsub(A, B), tB));
+			C = ovadd(C, ovscale(ovsub(A, C), tC));
+		}
+		else if(A.z > A.w)
+		{
+			float tB = dA / (dA - dB), tC = dA / (dA - dC);
+			ovec4 AB = ovadd(A, ovscale(ovsub(B, A), tB));
+			ovec4 AC = ovadd(A, ovscale(ovsub(C, A), tC));
+			A = AB;
+			occ_raster_triangle(depthbuf, C, AC, AB);
+		}
+		else if(B.z > B.w)
+		{
+			float tA = dB / (dB - dA), tC = dB / (dB - dC);
+			ovec4 BA = ovadd(B, ovscale(ovsub(A, B), tA));
+			ovec4 BC = ovadd(B, ovscale(ovsub(C, B), tC));
+			B = BA;
+			occ_raster_triangle(depthbuf, C, BA, BC);
+		}
+		else if(C.z > C.w)
+		{
+			float tA = dC / (dC - dA), tB = dC / (dC - dB);
+			ovec4 CA = ovadd(C, ovscale(ovsub(A, C), tA));
+			ovec4 CB = ovadd(C, ovscale(ovsub(B, C), tB));
+			C = CA;
+			occ_raster_triangle(depthbuf, B, CB, CA);
+		}
+		occ_raster_triangle(depthbuf, A, B, C);
+	}
+}
+
+/* TestBoundingBox, :320-405.  aabb: world position xyz (the node's), minExtend xyz, maxExtend xyz */
+static int occ_test_box(const float *depthbuf, const float *vp, const float *pos, const float *mn, const float *mx, const float pixel[2])
+{
+	const float ex[8][3] = {{mx[0], mx[1], mx[2]}, {mx[0], mx[1], mn[2]}, {mx[0], mn[1], mn[2]}, {mx[0], mn[1], mx[2]},
+	                        {mn[0], mx[1], mx[2]}, {mn[0], mx[1], mn[2]}, {mn[0], mn[1], mn[2]}, {mn[0], mn[1], mx[2]}};
+	float maxx = 0, maxy = 0, maxz = 0, minx = 0, miny = 0;
+	for(int i = 0; i < 8; i++)
+	{
+		ovec4 c = {pos[0] + ex[i][0], pos[1] + ex[i][1], pos[2] + ex[i][2], 1.0f + 0.0f};
+		c = omat_vec(vp, c);
+		if(c.z > c.w) return 1;
+		float w = c.w;
+		c.x /= w; c.y /= w; c.z /= w; c.w /= w;
+		c.x = c.x * 0.5f + 0.5f;
+		c.y = c.y * 0.5f + 0.5f;
+		if(i == 0)
+		{
+			maxx = minx = c.x; maxy = miny = c.y; maxz = c.z;
+		}
+		else
+		{
+			maxx = fmax_std(maxx, c.x); maxy = fmax_std(maxy, c.y); maxz = fmax_std(maxz, c.z);
+			minx = fmin_std(minx, c.x); miny = fmin_std(miny, c.y);
+		}
+	}
+	if((maxx - minx) < pixel[0] && (maxy - miny) < pixel[1]) return 0;
+	minx *= (float)OCC_W; miny *= (float)OCC_H;
+	maxx *= (float)OCC_W; maxy *= (float)OCC_H;
+	uint16_t x0 = (uint16_t)fmax_std(fmin_std(floorf(minx) - 1.0f, (float)(OCC_W - 1)), 0.0f);
+	uint16_t x1 = (uint16_t)fmax_std(fmin_std(ceilf(maxx) + 1.0f, (float)(OCC_W - 1)), 0.0f);
+	uint16_t y0 = (uint16_t)fmax_std(fmin_std(floorf(miny) - 1.0f, (float)(OCC_H - 1)), 0.0f);
+	uint16_t y1 = (uint16_t)fmax_std(fmin_std(ceilf(maxy) + 1.0f, (float)(OCC_H - 1)), 0.0f);
+	for(uint16_t y = y0; y <= y1; y++)
+		for(uint16_t x = x0; x <= x1; x++)
+			if(maxz > depthbuf[OCC_W * (OCC_H - y - 1) + x]) return 1;
+	return 0;
+}
+
+typedef struct
+{
+	float view[16], projection[16];   /* Camera::GetViewMatrix / GetProjectionMatrix */
+	float offset[3];                  /* the random camera offset of this frame (:488) */
+	float pixel[2];                   /* 1 / frame width, 1 / frame height (:486) */
+	float cam_pos[3];                 /* camera->GetWorldPosition() */
+} oracle_occlusion_params;
+
+typedef struct { uint32_t id; float score, dist; } occ_cand;
+
+/* The camera loop body of SceneBasic::Render with occluders present (:445-573) for ONE camera.
+ *   n, order[n]        : render list, order[rank] = node id
+ *   can_render[n]      : node->CanRender(renderer, camera) per id (hidden / group / frustum), as the cull computed it
+ *   flags, priority    : per id (bit 3 = Occluder)
+ *   wpos[n*3], radius[n] (GetBoundingSphere().radius), aabb[n*6] (GetBoundingBox(): min / max extents relative to wpos),
+ *   wmat[n*16]         : world state per id
+ *   mesh_of[n]         : mesh index of an Entity, -1 = no mesh;  tri_ofs / tris: triangle soups in model space
+ *   counter[n]         : SceneBasicInfo::occludedFrameCounter, in/out
+ * Writes the ids submitted for rendering in order to out_list (capacity n), the depth buffer (1600 floats) if asked,
+ * returns the count; *used = 0 if no occluder passed CanRender (then the caller takes the plain cull list).
+ * std::sort leaves equal keys in unspecified order; ties are broken by render-list rank here (stable). */
+uint32_t rn_oracle_occlusion(uint32_t n, const uint32_t *order, const uint8_t *can_render, const uint32_t *flags, const int32_t *priority,
+                             const float *wpos, const float *radius, const float *aabb, const float *wmat, const int32_t *mesh_of,
+                             const uint32_t *tri_ofs, const float *tris, uint32_t *counter, const oracle_occlusion_params *p,
+                             uint32_t *out_list, float *out_depth, int *used)
+{
+	occ_cand *occ = malloc(sizeof(occ_cand) * (n ? n : 1));
+	uint32_t nocc = 0;
+	for(uint32_t r = 0; r < n; r++)
+	{
+		uint32_t id = order[r];
+		if((flags[id] & 8u) && can_render[id])
+		{
+			float dx = wpos[id * 3] - p->cam_pos[0], dy = wpos[id * 3 + 1] - p->cam_pos[1], dz = wpos[id * 3 + 2] - p->cam_pos[2];
+			float d2 = dx * dx + dy * dy + dz * dz;       /* GetSquaredDistance: difference.GetDotProduct(difference) */
+			occ[nocc].id = id;
+			occ[nocc].dist = d2;
+			occ[nocc].score = radius[id] * radius[id] / fmax_std(d2, 1.0f);
+			nocc++;
+		}
+	}
+	*used = nocc > 0;
+	if(nocc == 0) { free(occ); return 0; }
+	/* biggest 30 by approximated screen size (descending score), then front to back; insertion sorts keep ties in list order */
+	for(uint32_t i = 1; i < nocc; i++)
+	{
+		occ_cand c = occ[i];
+		uint32_t j = i;
+		while(j > 0 && occ[j - 1].score < c.score) { occ[j] = occ[j - 1]; j--; }
+		occ[j] = c;
+	}
+	if(nocc > 30) nocc = 30;
+	for(uint32_t i = 1; i < nocc; i++)
+	{
+		occ_cand c = occ[i];
+		uint32_t j = i;
+		while(j > 0 && occ[j - 1].dist > c.dist) { occ[j] = occ[j - 1]; j--; }
+		occ[j] = c;
+	}
+	float depthbuf[OCC_W * OCC_H];
+	for(int i = 0; i < OCC_W * OCC_H; i++) depthbuf[i] = 0.0f;
+	/* matViewProj = projection * WithTranslation(offset) * view */
+	float tr[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, p->offset[0], p->offset[1], p->offset[2], 1};
+	float pt[16], vp[16];
+	omat_mul(p->projection, tr, pt);
+	omat_mul(pt, p->view, vp);
+	uint8_t *visible_occluder = calloc(n ? n : 1, 1);
+	for(uint32_t k = 0; k < nocc; k++)
+	{
+		uint32_t id = occ[k].id;
+		int res = occ_test_box(depthbuf, vp, wpos + id * 3, aabb + id * 6, aabb + id * 6 + 3, p->pixel);
+		if(!res && counter[id] < 1000) counter[id] += 1;
+		if(res || counter[id] < 50)
+		{
+			if(res) counter[id] = 0;
+			visible_occluder[id] = 1;
+		}
+		if(res && mesh_of[id] >= 0)
+		{
+			float mvp[16];
+			omat_mul(vp, wmat + (size_t)id * 16, mvp);
+			uint32_t m = (uint32_t)mesh_of[id];
+			occ_raster_mesh(depthbuf, mvp, tris + (size_t)tri_ofs[m] * 9, tri_ofs[m + 1] - tri_ofs[m]);
+		}
+	}
+	uint32_t count = 0;
+	for(uint32_t r = 0; r < n; r++)
+	{
+		uint32_t id = order[r];
+		if(!can_render[id]) continue;
+		if(priority[id] >= 200000) { out_list[count++] = id; continue; }          /* RenderSky and above are never tested */
+		if((flags[id] & 8u) && visible_occluder[id]) { out_list[count++] = id; continue; }
+		int res = occ_test_box(depthbuf, vp, wpos + id * 3, aabb + id * 6, aabb + id * 6 + 3, p->pixel);
+		if(!res && counter[id] < 1000) counter[id] += 1;
+		if(res || counter[id] < 50)
+		{
+			if(res) counter[id] = 0;
+			out_list[count++] = id;
+		}
+	}
+	if(out_depth) memcpy(out_depth, depthbuf, sizeof(depthbuf));
+	free(occ);
+	free(visible_occluder);
+	return count;
+}

@@ -34,7 +34,7 @@ EXPORTS = [
     "rn_cull_pack_instances", "rn_camera_build_matrices",
     "rn_scenevis_set_node_volumes", "rn_scenevis_set_camera_volumes", "rn_scenevis_choose_volume",
     "rn_particles_expand_billboards", "rn_particles_download_clip", "rn_particles_set_soft_max",
-    "rn_particles_set_emitter_transforms", "rn_lod_set_models", "rn_lod_set_node_models", "rn_cull_select_lod",
+    "rn_particles_set_emitter_transforms", "rn_light_build_cascades", "rn_lod_set_models", "rn_lod_set_node_models", "rn_cull_select_lod",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
@@ -176,6 +176,20 @@ def build_camera_matrices(cameras: np.ndarray):
         _check(lib.rn_camera_build_matrices(C.c_void_p(cameras[i:i + 1].ctypes.data), C.c_void_p(v[i].ctypes.data),
                                             C.c_void_p(p[i].ctypes.data), C.c_void_p(pv[i].ctypes.data)))
     return v, p, pv
+
+
+def build_cascades(target: np.ndarray, shadow: np.ndarray):
+    """rn_light_build_cascades: (camera records [n_splits] (scenegen.CAMERA_DTYPE), proj_view [n_splits, 16])."""
+    from .scenegen import SHADOW_DTYPE
+    lib = load()
+    t = np.ascontiguousarray(np.atleast_1d(target), dtype=CAMERA_DTYPE)[:1]
+    sh = np.ascontiguousarray(np.atleast_1d(shadow), dtype=SHADOW_DTYPE)[:1]
+    n = int(sh["n_splits"][0])
+    out = np.zeros(max(n, 1), dtype=CAMERA_DTYPE)
+    pv = np.zeros((max(n, 1), 16), np.float32)
+    _check(lib.rn_light_build_cascades(C.c_void_p(t.ctypes.data), C.c_void_p(sh.ctypes.data), C.c_void_p(out.ctypes.data),
+                                       C.c_void_p(pv.ctypes.data)))
+    return out[:n], pv[:n]
 
 
 def render_order(parent: np.ndarray, priority: np.ndarray | None = None) -> np.ndarray:

@@ -304,6 +304,95 @@ extern "C" int rn_camera_build_matrices(const rn_camera_desc *cam, float *view, 
 	return RN_OK;
 }
 
+// Light::UpdateShadows (Source/Scene/RNLight.cpp:475-529, directional branch) + Camera::MakeShadowSplit
+// (Source/Scene/RNCamera.cpp:240-287): the orthographic cascade cameras of a directional light for a target camera.
+extern "C" int rn_light_build_cascades(const rn_camera_desc *target, const rn_shadow_desc *sh, rn_camera_desc *out_cameras,
+                                       float *out_proj_view)
+{
+	RN_REQUIRE(target && sh && out_cameras, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(sh->n_splits >= 1 && sh->n_splits <= RN_MAX_CAMERAS, RN_ERR_INVALID, "n_splits must be 1..%d, got %u", RN_MAX_CAMERAS, sh->n_splits);
+	M4 invView, proj;
+	camera_matrices(target, invView, proj);
+	const M4 invProj = inverse(proj);
+	// Camera::ToWorld (RNCamera.cpp:399-415): un-project (x, y) at ndc z = 0, normalise to |view z| = 1, scale to the
+	// view distance dir.z, then to world space
+	auto to_world = [&](float x, float y, float dist) -> V3 {
+		V4 v = mul(invProj, V4{x, y, 0.0f, 1.0f});
+		const float w = v.w;
+		v.x /= w; v.y /= w; v.z /= w; v.w /= w;
+		const float sign = v.z < 0.0f ? -1.0f : 1.0f;
+		const float dz = v.z * sign;
+		v.x /= dz; v.y /= dz; v.z /= dz; v.w /= dz;
+		v.x *= dist; v.y *= dist; v.z *= dist;
+		v.w = 1.0f;
+		v = mul(invView, v);
+		return V3{v.x, v.y, v.z};
+	};
+	const float *lq = sh->light_world_rotation;
+	const V3 forward = rotate(lq, V3{0.0f, 0.0f, -1.0f});          // SceneNode::GetForward
+	const M4 rot = rotation_matrix(lq);
+	const M4 rotInv = inverse(rot);
+	auto mul3 = [](const M4 &a, const V3 &v) -> V3 {                 // Matrix::operator*(Vector3), RNMatrix.h:145-151
+		V3 r;
+		r.x = a.m[0] * v.x + a.m[4] * v.y + a.m[8] * v.z + a.m[12];
+		r.y = a.m[1] * v.x + a.m[5] * v.y + a.m[9] * v.z + a.m[13];
+		r.z = a.m[2] * v.x + a.m[6] * v.y + a.m[10] * v.z + a.m[14];
+		return r;
+	};
+	float near = target->clip_near;
+	float far = 0.01f;
+	const float n = float(sh->n_splits);
+	for(uint32_t i = 0; i < sh->n_splits; i++)
+	{
+		// RNLight.cpp:505-514: the split distance, a blend of a linear and a logarithmic subdivision of the target's depth range
+		if(sh->split_max_distance[i] < far)
+		{
+			const float linear = target->clip_near + (sh->max_shadow_dist * target->clip_far - target->clip_near) * (i + 1.0f) / n;
+			const float log = target->clip_near * powf(sh->max_shadow_dist * target->clip_far / target->clip_near, (i + 1.0f) / n);
+			far = linear * sh->distance_blend_factor + log * (1.0f - sh->distance_blend_factor);
+		}
+		else
+			far = sh->split_max_distance[i];
+
+		// Camera::MakeShadowSplit (RNCamera.cpp:240-287)
+		const V3 nearcenter = to_world(0.0f, 0.0f, near);
+		const V3 farcorner1 = to_world(1.0f, 1.0f, far);
+		const V3 farcorner2 = to_world(-1.0f, -1.0f, far);
+		const V3 farcenter = scale(add(farcorner1, farcorner2), 0.5f);
+		const V3 center = scale(add(nearcenter, farcenter), 0.5f);
+		const V3 dv = sub(center, farcorner1);
+		const float dist = sqrtf(dv.x * dv.x + dv.y * dv.y + dv.z * dv.z);
+		const V3 pixelsize = {dist * 2.0f / sh->resolution, dist * 2.0f / sh->resolution, 1.0f / 1.0f};
+		V3 pos = sub(center, scale(forward, sh->directional_shadow_distance));
+		pos = mul3(rotInv, pos);
+		pos.x /= pixelsize.x; pos.y /= pixelsize.y; pos.z /= pixelsize.z;      // snap to the texel grid in light space
+		pos.x = floorf(pos.x); pos.y = floorf(pos.y); pos.z = floorf(pos.z);
+		pos.x *= pixelsize.x; pos.y *= pixelsize.y; pos.z *= pixelsize.z;
+		pos = mul3(rot, pos);
+
+		rn_camera_desc &c = out_cameras[i];
+		memset(&c, 0, sizeof(c));
+		c.flags = RN_CAMERA_ORTHOGONAL | RN_CAMERA_RENDER_EARLY;     // RNLight.cpp:318
+		c.render_group = 1;                                          // Camera::Camera default (_renderGroup = 1)
+		c.world_position[0] = pos.x; c.world_position[1] = pos.y; c.world_position[2] = pos.z;
+		memcpy(c.world_rotation, lq, sizeof(float) * 4);
+		c.scale[0] = c.scale[1] = c.scale[2] = 1.0f;
+		c.fov = 70.0f; c.aspect = 1.0f;                              // unused by an orthogonal camera
+		c.clip_near = sh->clip_near; c.clip_far = sh->clip_far;
+		c.ortho[0] = -dist; c.ortho[1] = dist; c.ortho[2] = -dist; c.ortho[3] = dist;
+		if(out_proj_view)
+		{
+			// _projectionMatrix * GetWorldTransform().GetInverse(); the node's world transform is T * R * S(1) (RNSceneNode.cpp:530-532)
+			M4 cInvView, cProj;
+			camera_matrices(&c, cInvView, cProj);
+			const M4 pv = mul(cProj, inverse(cInvView));
+			memcpy(out_proj_view + (size_t)i * 16, pv.m, sizeof(pv.m));
+		}
+		near = far;
+	}
+	return RN_OK;
+}
+
 // SceneBasic::AddNode (RNSceneBasic.cpp:683-736): UpdateSceneInfo adds the children first, in child order
 // (RNSceneNode.cpp:286-291), then the node itself goes through AddRenderNode (:652-676):
 //   (1) list empty or head.priority >= p  -> PushFront

@@ -60,8 +60,9 @@ struct rn_scene
 	uint32_t spine_nodes = 0;
 	uint64_t device_bytes = 0;
 	uint64_t launches = 0;
+	int sm_count = 0;
 	bool fma_matrices = true;    // world matrices with fused multiply-adds (rn_scene_desc.flags & RN_SCENE_STRICT_MATRICES clears it)
-	size_t tile_smem_configured[4] = {};   // dynamic shared memory opted in per tile_kernel instantiation on THIS device
+	size_t tile_smem_configured[8] = {};   // dynamic shared memory opted in per tile_kernel instantiation on THIS device
 	bool have_world = false;     // world TRS valid (a propagate ran since the last upload)
 	uint32_t last_ncams = 0;
 	uint32_t list_rank_mode = 0;     // 1: visibility lists hold rank + list_rank_offset instead of slots

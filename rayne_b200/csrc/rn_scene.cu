@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -67,6 +68,11 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
 	             ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// pulls `bytes` (a multiple of 16) at `src` into L2 without a destination: cp.async.bulk.prefetch.L2 (SASS UBLKPF)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes)
+{
+	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
 	asm volatile(
@@ -93,6 +99,7 @@ struct SceneView
 	uint8_t *vis;              // camera bit mask per SLOT
 	uint32_t *tile_counts;     // [tile][RN_MAX_CAMERAS] visible nodes of the last cull
 	uint32_t *super_totals;    // [tile / kSuperTiles][RN_MAX_CAMERAS]
+	uint32_t *tile_counter;    // dynamic tile hand-out of the persistent tile kernel (zeroed before every launch)
 	const TileMeta *tiles;
 	uint32_t n_tiles;
 	uint32_t inner_cap;        // P: parents kept in shared memory per tile
@@ -532,173 +539,249 @@ __device__ __forceinline__ void prefetch_l2(const void *p)
 	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
-// World-transform propagation (+ culling) of one tile per WARP.  A tile is a contiguous slot range holding whole
-// compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every sublevel first.
-// The warp walks the sublevels in order, 32 nodes per pass: the four input columns of the NEXT pass arrive by TMA bulk
-// copies while the current one computes, parent world TRS + matrix come from the warp's shared memory (written by an
-// earlier pass of the same warp, so only __syncwarp separates the levels - no block barrier, the warps of a CTA
-// never wait for each other), the outputs are written once.  Every node is read once and written once; parents never
-// come back from HBM.  Sublevel 0 (spine nodes stored in this tile, transformed by the pre-pass) goes through the same
-// loop with its world TRS loaded instead of computed.  The lanes of a pass stay converged (a lane without a node
-// recomputes the last node of the level and stores nothing) so that the cull can use warp votes.
-// The cull of a pass is deferred by one pass and done for two passes at once (cull_pair).
-template <bool CULL, bool FMA>
-__global__ void __launch_bounds__(kTileThreads, 5) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
+// World-transform propagation (+ culling): PERSISTENT warps, one tile per warp at a time.  A tile is a contiguous slot
+// range holding whole compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every
+// sublevel first.  The warp walks the sublevels in order, 32 nodes per pass: the four input columns of the NEXT pass
+// arrive by TMA bulk copies while the current one computes (and the pass after that is pulled into L2 by bulk
+// prefetches), parent world TRS + matrix come from the warp's shared memory (written by an earlier pass of the same
+// warp, so only __syncwarp separates the levels - no block barrier, the warps of a CTA never wait for each other),
+// the outputs are written once.  Every node is read once and written once; parents never come back from HBM.
+// Sublevel 0 (spine nodes stored in this tile, transformed by the pre-pass) goes through the same loop with its world
+// TRS loaded instead of computed.  The lanes of a pass stay converged (a lane without a node recomputes the last node of
+// the level and stores nothing) so that the cull can use warp votes.  The cull of a pass is deferred by one pass and
+// done for two passes at once (cull_pair).
+// Tiles are handed out dynamically (first round by warp index, then an atomic counter); the descriptor of the next tile
+// is fetched while the current one is processed and the TMA pipeline runs across the tile boundary, so a warp never
+// sits through the load latency of a tile's first pass.
+struct PassPos
+{
+	uint32_t lev, j0, je;
+};
+
+template <bool CULL, bool FMA, int CTAS>
+__global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_constant__ SceneView sv, const __grid_constant__ CullParams cp)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	__shared__ CullTable tab;
+	__shared__ __align__(16) TileMeta s_meta[kWarpsPerCta][2];
 	if(CULL)
 		cull_setup(cp, tab);
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-	const uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
+	uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
 	if(tile >= sv.n_tiles)
 		return;
 	const WarpSmem s = carve_warp_smem(smem_raw + (size_t)warp * sv.warp_smem, sv.inner_cap);
+	const uint32_t first_dynamic = gridDim.x * kWarpsPerCta;
+	// the tile after this one: claimed now, its descriptor loaded during the first pass of the current tile
+	uint32_t claim = 0;
+	if(lane == 0)
+		claim = atomicAdd(sv.tile_counter, 1u);
 	if(lane < sizeof(TileMeta) / 4)
-		reinterpret_cast<uint32_t *>(const_cast<TileMeta *>(s.meta))[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
+		reinterpret_cast<uint32_t *>(&s_meta[warp][0])[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
 	if(lane == 0)
 	{
 		mbar_init(s.bar, 1);
 		mbar_fence_init();
 	}
 	__syncwarp();
-	const uint32_t start = s.meta->start;
-	const uint32_t nlev = s.meta->nlev;
-	VisCount vc = {0u, 0u};
+	uint32_t cur = 0;                 // which of the two descriptor slots holds the current tile
+	uint32_t phase = 0;
 
-	// The four input columns of pass p+1 are fetched by TMA bulk copies (one elected lane, completion on the warp's
-	// mbarrier) while pass p computes; a pass starts by moving its 4 x float4 from the stage to registers.
+	// The four input columns of pass p+1 are fetched by TMA bulk copies (completion on the warp's mbarrier) while pass p
+	// computes; a pass starts by moving its 4 x float4 from the stage to registers.  The 32 slots behind it (the pass
+	// after the next; the columns are padded, so running past the tile or the scene is harmless) are pulled into L2.
+	// Lane k < 4 issues the copy of column k, lane 4 + k its prefetch: eight bulk operations for the price of two
+	// instruction streams instead of eight executed by one lane.
 	const uint32_t ncols = CULL ? 4u : 3u;
-	auto issue = [&](uint32_t j0, uint32_t cnt) {
+	const float4 *const my_col = (&sv.c0)[lane & 3u];       // c0..c3 are consecutive kernel parameters
+	auto issue = [&](uint32_t slot0, uint32_t cnt) {
 		const uint32_t bytes = cnt * 16u;
-		mbar_expect_tx(s.bar, bytes * ncols);
-		bulk_g2s(s.stage, sv.c0 + start + j0, bytes, s.bar);
-		bulk_g2s(s.stage + 32, sv.c1 + start + j0, bytes, s.bar);
-		bulk_g2s(s.stage + 64, sv.c2 + start + j0, bytes, s.bar);
-		if(CULL) bulk_g2s(s.stage + 96, sv.c3 + start + j0, bytes, s.bar);
+		if(lane == 0)
+			mbar_expect_tx(s.bar, bytes * ncols);
+		if(lane < ncols)
+			bulk_g2s(s.stage + 32u * lane, my_col + slot0, bytes, s.bar);
+		else if(lane >= 4u && lane < 4u + ncols)
+			bulk_prefetch_l2(my_col + slot0 + cnt, 512u);
 	};
-	// first pass: sublevel 0 only matters to the cull
-	uint32_t lev = 0, j0 = 0, je = s.meta->lvl_end[0];
-	if(!CULL || je == 0)
-	{
-		lev = 1;
-		j0 = je;
-		je = s.meta->lvl_end[nlev > 1 ? 1 : 0];
-	}
-	if(lev < nlev)
-	{
-		uint32_t jb = j0;                                    // first slot offset of the current sublevel
-		uint32_t ib = 0, ni = lev ? s.meta->inner_end[1] : 0;   // inner nodes: first index, count in this sublevel
-		uint32_t phase = 0;
-		bool pending = false;
-		CullItem held;
-		if(lev && lane == 0)
-			issue(j0, min(32u, je - j0));
-		for(;;)
+	// first pass of a tile: sublevel 0 only matters to the cull
+	auto first_pass = [&](const TileMeta &m, PassPos &p) -> bool {
+		p.lev = 0; p.j0 = 0; p.je = m.lvl_end[0];
+		if(!CULL || p.je == 0)
 		{
-			const uint32_t n_cur = min(32u, je - j0);
-			const bool active = lane < n_cur;
-			const uint32_t l = active ? lane : n_cur - 1;
-			const uint32_t j = j0 + l;
-			const uint32_t slot = start + j;
-			// next pass
-			uint32_t nlv = lev, nj0 = j0 + 32, nje = je;
-			if(nj0 >= je)
+			p.lev = 1;
+			p.j0 = p.je;
+			p.je = m.lvl_end[m.nlev > 1 ? 1 : 0];
+		}
+		return p.lev < m.nlev;
+	};
+	PassPos pos;
+	bool have = first_pass(s_meta[warp][0], pos);
+	if(have && pos.lev)
+		issue(s_meta[warp][0].start + pos.j0, min(32u, pos.je - pos.j0));
+	for(;;)
+	{
+		const TileMeta &meta = s_meta[warp][cur];
+		const uint32_t start = meta.start, nlev = meta.nlev;
+		// ---- the descriptor of the next tile: load issued now, parked in the other slot after the first pass ----
+		claim = __shfl_sync(0xffffffffu, claim, 0);
+		const uint32_t next_tile = first_dynamic + claim;
+		const bool more = next_tile < sv.n_tiles;
+		uint32_t mreg = 0;
+		if(more && lane < sizeof(TileMeta) / 4)
+			mreg = __ldg(reinterpret_cast<const uint32_t *>(sv.tiles + next_tile) + lane);
+		if(more && lane == 0)
+			claim = atomicAdd(sv.tile_counter, 1u);
+		bool next_ready = !more;
+		auto park_next = [&]() {
+			if(!next_ready)
 			{
-				nlv = lev + 1;
-				nj0 = je;
-				nje = s.meta->lvl_end[nlv < nlev ? nlv : lev];
-			}
-			const bool has_next = nlv < nlev;
-			NodeWorld W;
-			float4 d;
-			uint32_t fw;
-			if(!CULL || lev)
-			{
-				mbar_wait(s.bar, phase);
-				phase ^= 1u;
-				const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
-				if(CULL) d = s.stage[96 + l];
+				if(lane < sizeof(TileMeta) / 4)
+					reinterpret_cast<uint32_t *>(&s_meta[warp][cur ^ 1u])[lane] = mreg;
 				__syncwarp();
-				if(has_next && lane == 0)
-					issue(nj0, min(32u, nje - nj0));
-				const Vec3 pos = {a.x, a.y, a.z};
-				const Vec3 scale = {a.w, c.x, c.y};
-				const Quat rot = {b.x, b.y, b.z, b.w};
-				const uint32_t parent = __float_as_uint(c.z);
-				fw = __float_as_uint(c.w);
-				NodeWorld P;
-				const bool hasParent = parent != RN_NO_PARENT;
-				if(hasParent)
-				{
-					if(parent & kParentInTile)
-						load_world_smem(s, parent & 0xffffu, P);
-					else
-						load_world_global(sv, parent, P);
-				}
-				compute_world<FMA>(pos, rot, scale, hasParent, P, W);
-				if(active)
-				{
-					store_world_global(sv, slot, W);
-					if(j - jb < ni)
-						store_world_smem(s, ib + (j - jb), W);
-				}
-				__syncwarp();
+				next_ready = true;
 			}
-			else
+		};
+		VisCount vc = {0u, 0u};
+		if(have)
+		{
+			uint32_t lev = pos.lev, j0 = pos.j0, je = pos.je;
+			uint32_t jb = j0;                                    // first slot offset of the current sublevel
+			uint32_t ib = 0, ni = lev ? meta.inner_end[1] : 0;   // inner nodes: first index, count in this sublevel
+			bool pending = false;
+			CullItem held;
+			for(;;)
 			{
-				// spine nodes stored inside this tile: world transform already computed by the pre-pass (CULL only)
-				if(has_next && nlv && lane == 0)
-					issue(nj0, min(32u, nje - nj0));
-				const float4 a = sv.wpos[slot], b = sv.wrot[slot];
-				const float2 c = sv.wsyz[slot];
-				fw = __float_as_uint(sv.c2[slot].w);
-				d = sv.c3[slot];
-				W.wp = {a.x, a.y, a.z};
-				W.wr = {b.x, b.y, b.z, b.w};
-				W.ws = {a.w, c.x, c.y};
-			}
-			if(CULL)
-			{
-				CullItem cur;
-				bound_sphere(W.wp, W.wr, W.ws, d, cur);
-				cur.fw = fw;
-				cur.vidx = start + ((fw >> kRankShift) & kRankMask);
-				cur.active = active;
-				if(!pending && has_next)
+				const uint32_t n_cur = min(32u, je - j0);
+				const bool active = lane < n_cur;
+				const uint32_t l = active ? lane : n_cur - 1;
+				const uint32_t j = j0 + l;
+				const uint32_t slot = start + j;
+				// next pass of this tile
+				uint32_t nlv = lev, nj0 = j0 + 32, nje = je;
+				if(nj0 >= je)
 				{
-					held = cur;
-					pending = true;
+					nlv = lev + 1;
+					nj0 = je;
+					nje = meta.lvl_end[nlv < nlev ? nlv : lev];
+				}
+				const bool has_next = nlv < nlev;
+				// what the TMA engine fetches while this pass computes: the next pass of this tile, or the first pass
+				// of the next tile
+				uint32_t f_slot = start + nj0, f_cnt = min(32u, nje - nj0);
+				bool fetch = has_next && nlv;
+				if(!has_next && more)
+				{
+					park_next();
+					const TileMeta &nm = s_meta[warp][cur ^ 1u];
+					PassPos npos;
+					fetch = first_pass(nm, npos) && npos.lev;
+					f_slot = nm.start + npos.j0;
+					f_cnt = min(32u, npos.je - npos.j0);
+				}
+				NodeWorld W;
+				float4 d;
+				uint32_t fw;
+				if(!CULL || lev)
+				{
+					mbar_wait(s.bar, phase);
+					phase ^= 1u;
+					const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
+					if(CULL) d = s.stage[96 + l];
+					__syncwarp();
+					if(fetch)
+						issue(f_slot, f_cnt);
+					const Vec3 pos3 = {a.x, a.y, a.z};
+					const Vec3 scale = {a.w, c.x, c.y};
+					const Quat rot = {b.x, b.y, b.z, b.w};
+					const uint32_t parent = __float_as_uint(c.z);
+					fw = __float_as_uint(c.w);
+					NodeWorld P;
+					const bool hasParent = parent != RN_NO_PARENT;
+					if(hasParent)
+					{
+						if(parent & kParentInTile)
+							load_world_smem(s, parent & 0xffffu, P);
+						else
+							load_world_global(sv, parent, P);
+					}
+					compute_world<FMA>(pos3, rot, scale, hasParent, P, W);
+					if(active)
+					{
+						store_world_global(sv, slot, W);
+						if(j - jb < ni)
+							store_world_smem(s, ib + (j - jb), W);
+					}
+					__syncwarp();
 				}
 				else
 				{
-					if(!pending)
-					{
-						held = cur;
-						held.active = false;
-					}
-					uint32_t ma, mb;
-					cull_pair(cp, tab, held, cur, ma, mb);
-					if(held.active) sv.vis[held.vidx] = (uint8_t)ma;
-					if(cur.active) sv.vis[cur.vidx] = (uint8_t)mb;
-					vis_count_add(vc, ma);
-					vis_count_add(vc, mb);
-					pending = false;
+					// spine nodes stored inside this tile: world transform already computed by the pre-pass (CULL only)
+					if(fetch)
+						issue(f_slot, f_cnt);
+					const float4 a = sv.wpos[slot], b = sv.wrot[slot];
+					const float2 c = sv.wsyz[slot];
+					fw = __float_as_uint(sv.c2[slot].w);
+					d = sv.c3[slot];
+					W.wp = {a.x, a.y, a.z};
+					W.wr = {b.x, b.y, b.z, b.w};
+					W.ws = {a.w, c.x, c.y};
 				}
+				park_next();      // after the first pass of the tile the descriptor load has long landed
+				if(CULL)
+				{
+					CullItem cur_item;
+					bound_sphere(W.wp, W.wr, W.ws, d, cur_item);
+					cur_item.fw = fw;
+					cur_item.vidx = start + ((fw >> kRankShift) & kRankMask);
+					cur_item.active = active;
+					if(!pending && has_next)
+					{
+						held = cur_item;
+						pending = true;
+					}
+					else
+					{
+						if(!pending)
+						{
+							held = cur_item;
+							held.active = false;
+						}
+						uint32_t ma, mb;
+						cull_pair(cp, tab, held, cur_item, ma, mb);
+						if(held.active) sv.vis[held.vidx] = (uint8_t)ma;
+						if(cur_item.active) sv.vis[cur_item.vidx] = (uint8_t)mb;
+						vis_count_add(vc, ma);
+						vis_count_add(vc, mb);
+						pending = false;
+					}
+				}
+				if(!has_next)
+					break;
+				if(nlv != lev)
+				{
+					jb = nj0;
+					ib = meta.inner_end[lev];
+					ni = meta.inner_end[nlv] - ib;
+				}
+				lev = nlv; j0 = nj0; je = nje;
 			}
-			if(!has_next)
-				break;
-			if(nlv != lev)
-			{
-				jb = nj0;
-				ib = lev ? s.meta->inner_end[lev] : 0;
-				ni = s.meta->inner_end[nlv] - ib;
-			}
-			lev = nlv; j0 = nj0; je = nje;
 		}
+		else if(more)
+		{
+			// a tile without a pass (a tile of spine nodes in a propagate-only launch): nothing was fetched ahead
+			park_next();
+			PassPos npos;
+			if(first_pass(s_meta[warp][cur ^ 1u], npos) && npos.lev)
+				issue(s_meta[warp][cur ^ 1u].start + npos.j0, min(32u, npos.je - npos.j0));
+		}
+		if(CULL)
+			vis_count_store(sv, tile, vc, lane);
+		if(!more)
+			break;
+		tile = next_tile;
+		cur ^= 1u;
+		have = first_pass(s_meta[warp][cur], pos);
 	}
-	if(CULL)
-		vis_count_store(sv, tile, vc, lane);
 }
 
 // rn_cull on stored world transforms: one warp per tile, 64 consecutive slots per pass.
@@ -1155,6 +1238,7 @@ static SceneView make_view(const rn_scene *s)
 	v.c0 = s->c0; v.c1 = s->c1; v.c2 = s->c2; v.c3 = s->c3;
 	v.wpos = s->wpos; v.wrot = s->wrot; v.wsyz = s->wsyz; v.wmat = s->wmat;
 	v.vis = s->vis; v.tiles = s->tiles; v.tile_counts = s->tile_counts; v.super_totals = s->super_totals;
+	v.tile_counter = s->super_totals + ((size_t)(s->n_tiles + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS;
 	v.n_tiles = s->n_tiles; v.inner_cap = s->inner_cap; v.warp_smem = warp_smem_bytes(s->inner_cap); v.n = s->n;
 	return v;
 }
@@ -1189,16 +1273,24 @@ static int launch_spine(rn_scene *s, cudaStream_t stream)
 	return RN_OK;
 }
 
-template <bool CULL, bool FMA>
-static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t stream)
+// Experiment knobs (environment, read once): RN_TILE_CTAS = 4 | 5 resident CTAs per SM the tile kernel is compiled for
+// (5: 96 registers, 4: 128 - the default: no spills, measured fastest, profiles/r02_tile_sweep.jsonl); RN_TILE_PERSIST = CTAs per SM of the launch grid (0 = one warp per tile, no persistence).
+static int tile_env(const char *name, int dflt)
+{
+	const char *v = getenv(name);
+	return v && *v ? atoi(v) : dflt;
+}
+
+template <bool CULL, bool FMA, int CTAS>
+static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t stream, int persist)
 {
 	const size_t smem = (size_t)warp_smem_bytes(s->inner_cap) * kWarpsPerCta;
 	// cudaFuncSetAttribute is per device (and per function): remembered in the scene's device slot, not in a static
-	size_t &configured = s->tile_smem_configured[(CULL ? 1 : 0) + (FMA ? 2 : 0)];
+	size_t &configured = s->tile_smem_configured[(CULL ? 1 : 0) + (FMA ? 2 : 0) + (CTAS == 4 ? 4 : 0)];
 	if(configured < smem)
 	{
-		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		RN_CUDA(cudaFuncSetAttribute(tile_kernel<CULL, FMA, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		configured = smem;
 	}
 	const bool prof = s->profile && s->prof_used < rn_scene::kProfileSlots;
@@ -1211,8 +1303,13 @@ static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t str
 		}
 		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][0], stream));
 	}
-	const uint32_t grid = (s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
-	tile_kernel<CULL, FMA><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
+	// persistent warps: as many CTAs as fit on the device at once, the rest of the tiles is handed out dynamically
+	if(!s->sm_count)
+		RN_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, s->device));
+	uint32_t grid = (s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta;
+	if(persist > 0)
+		grid = std::min<uint32_t>(grid, (uint32_t)s->sm_count * (uint32_t)persist);
+	tile_kernel<CULL, FMA, CTAS><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
 	s->launches++;
 	if(prof)
 	{
@@ -1226,13 +1323,18 @@ static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t str
 template <bool CULL>
 static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 {
-	return s->fma_matrices ? launch_tiles_impl<CULL, true>(s, cp, stream) : launch_tiles_impl<CULL, false>(s, cp, stream);
+	static const int ctas = tile_env("RN_TILE_CTAS", 4);
+	static const int persist = tile_env("RN_TILE_PERSIST", ctas);
+	if(ctas == 4)
+		return s->fma_matrices ? launch_tiles_impl<CULL, true, 4>(s, cp, stream, persist) : launch_tiles_impl<CULL, false, 4>(s, cp, stream, persist);
+	return s->fma_matrices ? launch_tiles_impl<CULL, true, 5>(s, cp, stream, persist) : launch_tiles_impl<CULL, false, 5>(s, cp, stream, persist);
 }
 
 static int clear_super_totals(rn_scene *s, cudaStream_t stream)
 {
+	// + the tile counter of the persistent tile kernel, which lives right behind the totals
 	const size_t supers = (s->n_tiles + kSuperTiles - 1) / kSuperTiles;
-	RN_CUDA(cudaMemsetAsync(s->super_totals, 0, supers * RN_MAX_CAMERAS * sizeof(uint32_t), stream));
+	RN_CUDA(cudaMemsetAsync(s->super_totals, 0, (supers * RN_MAX_CAMERAS + 1) * sizeof(uint32_t), stream));
 	return RN_OK;
 }
 
@@ -1344,10 +1446,10 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	s->fma_matrices = !(desc->flags & RN_SCENE_STRICT_MATRICES);
 	const size_t n = desc->max_nodes;
 	int rc = RN_OK;
-	if(!rc) rc = dev_alloc(s, &s->c0, n);
-	if(!rc) rc = dev_alloc(s, &s->c1, n);
-	if(!rc) rc = dev_alloc(s, &s->c2, n);
-	if(!rc) rc = dev_alloc(s, &s->c3, n);
+	if(!rc) rc = dev_alloc(s, &s->c0, n + 64);   // + the reach of the L2 prefetch
+	if(!rc) rc = dev_alloc(s, &s->c1, n + 64);   // + the reach of the L2 prefetch
+	if(!rc) rc = dev_alloc(s, &s->c2, n + 64);   // + the reach of the L2 prefetch
+	if(!rc) rc = dev_alloc(s, &s->c3, n + 64);   // + the reach of the L2 prefetch
 	if(!rc) rc = dev_alloc(s, &s->wpos, n);
 	if(!rc) rc = dev_alloc(s, &s->wrot, n);
 	if(!rc) rc = dev_alloc(s, &s->wsyz, n);
@@ -1500,7 +1602,7 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	const size_t nt = t.tiles.size();
 	int rc = dev_alloc(s, &s->tiles, nt);
 	if(!rc) rc = dev_alloc(s, &s->tile_counts, nt * RN_MAX_CAMERAS);
-	if(!rc) rc = dev_alloc(s, &s->super_totals, ((nt + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS);
+	if(!rc) rc = dev_alloc(s, &s->super_totals, ((nt + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS + 1);   // + tile counter
 	if(rc) return rc;
 	if(nt) RN_CUDA(cudaMemcpy(s->tiles, t.tiles.data(), sizeof(TileMeta) * nt, cudaMemcpyHostToDevice));
 
@@ -1621,7 +1723,8 @@ extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	RN_CUDA(cudaSetDevice(s->device));
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-	int rc = launch_spine(s, stream);
+	int rc = clear_super_totals(s, stream);      // zeroes the tile counter of the persistent kernel
+	if(!rc) rc = launch_spine(s, stream);
 	if(rc) return rc;
 	CullParams cp;
 	memset(&cp, 0, sizeof(cp));
@@ -1693,7 +1796,8 @@ extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras
 	if(wants_aabb(cameras, n_cameras))
 	{
 		// extension path: the AABB filter works on stored transforms
-		rc = launch_spine(s, stream);
+		rc = clear_super_totals(s, stream);
+		if(!rc) rc = launch_spine(s, stream);
 		if(!rc) rc = launch_tiles<false>(s, cp, stream);
 		if(rc) return rc;
 		s->have_world = true;

@@ -295,6 +295,44 @@ def six_view_rig(seed: int = 7) -> np.ndarray:
     return np.stack(cams)
 
 
+# rn_shadow_desc (include/rn_cuda.h): ShadowParameter of a directional Light + the light's world rotation
+SHADOW_DTYPE = np.dtype([
+    ("n_splits", "<u4"), ("split_max_distance", "<f4", 8), ("resolution", "<f4"), ("clip_near", "<f4"), ("clip_far", "<f4"),
+    ("directional_shadow_distance", "<f4"), ("distance_blend_factor", "<f4"), ("max_shadow_dist", "<f4"),
+    ("light_rot", "<f4", 4),
+])
+assert SHADOW_DTYPE.itemsize == 76
+
+
+def make_shadow(light_euler=(0.0, -50.0, 0.0), n_splits=4, resolution=1024.0, clip_near=0.0, clip_far=100000.0,
+                directional_shadow_distance=5000.0, distance_blend_factor=0.05, max_shadow_dist=1.0,
+                split_max_distance=None) -> np.ndarray:
+    """Defaults = ShadowParameter(Camera *target, 1024) (Source/Scene/RNLight.h:50-64): four splits without a maxDistance."""
+    s = np.zeros((), dtype=SHADOW_DTYPE)
+    s["n_splits"] = n_splits
+    if split_max_distance is not None:
+        s["split_max_distance"][:n_splits] = split_max_distance
+    s["resolution"] = resolution
+    s["clip_near"], s["clip_far"] = clip_near, clip_far
+    s["directional_shadow_distance"] = directional_shadow_distance
+    s["distance_blend_factor"] = distance_blend_factor
+    s["max_shadow_dist"] = max_shadow_dist
+    s["light_rot"] = euler_to_quat(np.asarray([light_euler], dtype=np.float64))[0]
+    return s
+
+
+def vr_cascade_rig(light_euler=(30.0, -50.0, 0.0)) -> np.ndarray:
+    """Config C4 with the cascade cameras the REFERENCE derives: the two eye cameras of six_view_rig + the four
+    orthographic cameras Light::UpdateShadows / Camera::MakeShadowSplit produce for a directional light with the
+    default ShadowParameter(target) and the head camera as shadow target (rn_light_build_cascades; pinned against the
+    reference by tests/golden/cascades_basic.npz)."""
+    from . import capi
+    eyes = six_view_rig()[:2]
+    head = make_camera(pos=(0.0, 1.7, 0.0), euler=(20.0, -5.0, 0.0))
+    casc, _ = capi.build_cascades(head, make_shadow(light_euler))
+    return np.concatenate([eyes, casc])
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # Particle emitters (GenericParticleEmitter parameters; defaults from Source/Scene/RNParticleEmitter.cpp:379-395)
 # ---------------------------------------------------------------------------------------------------------------

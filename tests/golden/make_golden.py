@@ -109,6 +109,30 @@ def main() -> None:
         out[f"ref_time{k}"] = r["time"]
     np.savez_compressed(os.path.join(HERE, "particles_nonlocal_soft.npz"), **out)
     print("particles_nonlocal_soft", [r["count"] for r in ref])
+    make_cascades()
+
+
+def cascade_cases():
+    """(target camera, shadow parameters) pairs of cascades_basic.npz: the default ShadowParameter(target) of a VR head
+    camera, and a three-split setup with explicit maxDistance on two splits, another resolution / blend / range."""
+    head = sg.make_camera(pos=(0.0, 1.7, 0.0), euler=(20.0, -5.0, 0.0))
+    other = sg.make_camera(pos=(-40.0, 12.0, 7.5), euler=(110.0, 15.0, -5.0), fov=55.0, aspect=1.25, near=0.5, far=900.0)
+    return [(head, sg.make_shadow((30.0, -50.0, 0.0))),
+            (other, sg.make_shadow((0.0, -90.0, 10.0), n_splits=3, split_max_distance=(5.0, 0.0, 300.0), resolution=2048.0,
+                                   distance_blend_factor=0.4, max_shadow_dist=0.5, clip_near=1.0, clip_far=20000.0,
+                                   directional_shadow_distance=800.0))]
+
+
+def make_cascades() -> None:
+    out = {}
+    for k, (target, shadow) in enumerate(cascade_cases()):
+        ref = refio.run_cascades(target, shadow)
+        out[f"in_target{k}"] = target
+        out[f"in_shadow{k}"] = shadow
+        for key, val in ref.items():
+            out[f"ref_{key}{k}"] = val
+        print("cascades", k, ref["ortho"][:, 1])
+    np.savez_compressed(os.path.join(HERE, "cascades_basic.npz"), **out)
 
 
 def nonlocal_soft_emitters():

@@ -128,3 +128,30 @@ def test_product_sources_never_touch_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
                 assert "rn_oracle" not in text and "oracle/_ref" not in text, f
+
+
+def test_light_cascades_match_golden():
+    """rn_light_build_cascades (Light::UpdateShadows + Camera::MakeShadowSplit) against the reference's own cascade
+    cameras (tests/golden/cascades_basic.npz): world position after the texel snap, rotation, orthographic extents,
+    clip planes, flags, the 28 frustum floats rn_camera_build_frustum derives from them, and _shadowCameraMatrices -
+    all bit-exact."""
+    import os
+    from tests.helpers import GOLDEN_DIR
+    g = np.load(os.path.join(GOLDEN_DIR, "cascades_basic.npz"))
+    k = 0
+    while f"in_target{k}" in g.files:
+        cams, pv = capi.build_cascades(g[f"in_target{k}"], g[f"in_shadow{k}"])
+        assert cams["pos"].tobytes() == g[f"ref_pos{k}"].tobytes()
+        assert cams["rot"].tobytes() == g[f"ref_rot{k}"].tobytes()
+        assert cams["ortho"].tobytes() == g[f"ref_ortho{k}"].tobytes()
+        assert np.stack([cams["clip_near"], cams["clip_far"]], 1).astype(np.float32).tobytes() == g[f"ref_clip{k}"].tobytes()
+        assert np.array_equal(cams["flags"], g[f"ref_flags{k}"])
+        assert pv.tobytes() == g[f"ref_projview{k}"].tobytes()
+        fr = capi.build_frustums(cams)
+        got28 = np.concatenate([fr["center"], fr["radius"][:, None], fr["planes"].reshape(-1, 24)], 1).astype(np.float32)
+        assert got28.tobytes() == g[f"ref_frustum{k}"].tobytes()
+        k += 1
+    assert k == 2
+    # the C4 rig built from the reference-derived cascades: 2 eye cameras + 4 orthogonal cascade cameras
+    rig = sg.vr_cascade_rig()
+    assert rig.shape[0] == 6 and (rig["flags"][2:] & sg.CAM_ORTHOGONAL).all()

@@ -427,10 +427,10 @@ def test_lod_selection_extension_matches_oracle(rank_mode):
             ranks = (ids - 1000) if rank_mode else rank_of_slot[ids]
             creation = rs.order[ranks]
             out = torch.zeros(len(ids) + 8, dtype=torch.uint8, device="cuda")
-            h.select_lod(c, lod_pos[c], float(cams["far"][c]), out.data_ptr(), len(ids))
+            h.select_lod(c, lod_pos[c], float(cams["clip_far"][c]), out.data_ptr(), len(ids))
             torch.cuda.synchronize()
             got = out.cpu().numpy()
-            want = oracle.select_lod(creation, ref["wpos"], model, so, sd, lod_pos[c], float(cams["far"][c]))
+            want = oracle.select_lod(creation, ref["wpos"], model, so, sd, lod_pos[c], float(cams["clip_far"][c]))
             assert np.array_equal(got[:len(ids)], want), f"camera {c}"
             assert (got[len(ids):] == 0).all()                        # nothing written beyond the list
             assert len(np.unique(want)) >= 3
