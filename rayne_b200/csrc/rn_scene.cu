@@ -596,6 +596,13 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 	const float4 *const my_col = (&sv.c0)[lane & 3u];       // c0..c3 are consecutive kernel parameters
 	auto issue = [&](uint32_t slot0, uint32_t cnt) {
 		const uint32_t bytes = cnt * 16u;
+		// The stage was just read through the generic proxy and is about to be overwritten through the async proxy (TMA):
+		// every lane orders its own reads before the copies with a proxy fence, then the warp meets, then the elected
+		// lanes issue.  __syncwarp alone does NOT order the two proxies - without the fence a pass now and then computed
+		// on the columns of the NEXT pass (seen on scenes whose tiles are mostly single-leaf units with parents in global
+		// memory: the long parent loads keep the stage registers' producers in flight; profiles/r02_tile_proxy_fence.txt).
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+		__syncwarp();
 		if(lane == 0)
 			mbar_expect_tx(s.bar, bytes * ncols);
 		if(lane < ncols)
@@ -687,9 +694,8 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 					phase ^= 1u;
 					const float4 a = s.stage[l], b = s.stage[32 + l], c = s.stage[64 + l];
 					if(CULL) d = s.stage[96 + l];
-					__syncwarp();
 					if(fetch)
-						issue(f_slot, f_cnt);
+						issue(f_slot, f_cnt);      // proxy fence + __syncwarp inside
 					const Vec3 pos3 = {a.x, a.y, a.z};
 					const Vec3 scale = {a.w, c.x, c.y};
 					const Quat rot = {b.x, b.y, b.z, b.w};

@@ -54,6 +54,22 @@ def test_c2_full_size_against_the_oracle():
                 assert np.array_equal(a, b)
 
 
+def test_scattered_priorities_1m_repeated():
+    """1 M nodes with random render priorities: the render list separates children from their parents, so ~20 % of the
+    nodes are spine nodes (7 spine depths) and the tiles are mostly single-leaf units whose parents sit in global memory -
+    the shape on which the tile kernel once read a stage the next TMA copy was already overwriting (generic-proxy read
+    vs async-proxy write without a proxy fence; profiles/r02_tile_proxy_fence.txt).  Fresh handle per repetition, fused
+    and unfused, everything bit-exact against the oracle."""
+    from oracle import oracle
+    scene = sg.make_scene(n_trees=48, branching=4, depth=8, seed=12345, priorities=True, transparent_frac=0.05)
+    cams = standard_cameras()[:3]
+    ref = oracle.scene_reference(scene, capi.build_frustums(cams))
+    for rep in range(2):
+        for fused in (True, False):
+            got, _ = check_against_oracle(scene, cams, strict=True, ref=ref, fused=fused)
+    assert got["stats"]["spine_nodes"] > 100000
+
+
 @pytest.mark.parametrize("tile", [64, 256, 1024])
 def test_tile_size_independent(tile):
     scene = sg.make_scene(n_trees=5, branching=4, depth=7, seed=11, random_bounds=True)
