@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RN_ABI_VERSION 3
+#define RN_ABI_VERSION 4
 #define RN_MAX_CAMERAS 8          /* views culled by one rn_cull call (stereo + 4 cascades = 6) */
 #define RN_NO_PARENT 0xffffffffu
 
@@ -47,6 +47,7 @@ typedef struct rn_scene rn_scene_t;
 #define RN_NODE_STATIC     (1u << 0)
 #define RN_NODE_HIDDEN     (1u << 1)
 #define RN_NODE_NOCULLING  (1u << 2)
+#define RN_NODE_OCCLUDER   (1u << 3)
 /* RN::Camera::Flags bits the path looks at (Source/Scene/RNCamera.h:30-50). */
 #define RN_CAMERA_RENDER_EARLY       (1u << 19)
 #define RN_CAMERA_ORTHOGONAL         (1u << 21)
@@ -304,6 +305,49 @@ int rn_lod_set_models(rn_scene_t *scene, const uint32_t *stage_offsets, const fl
 int rn_lod_set_node_models(rn_scene_t *scene, const uint16_t *model_of_rank, uint32_t first, uint32_t count);
 int rn_cull_select_lod(rn_scene_t *scene, uint32_t camera, const float *lod_camera_world_position, float lod_camera_clip_far,
                        uint8_t *device_out, uint32_t capacity, void *cuda_stream);
+
+/* Software occlusion culling - the pass SceneBasic::Render runs for a camera that sees at least one Flags::Occluder node
+ * (Source/Scene/RNSceneBasic.cpp:445-573; RasterizeClipSpaceTriangle :152-208, RasterizeMesh :210-318, TestBoundingBox
+ * :320-405): the 30 occluders with the largest radius^2 / max(squared distance, 1), front to back, are box-tested and
+ * rasterised (LOD 0 / mesh 0 of an Entity) into a 40 x 40 reverse-Z depth buffer; every node that passed CanRender is then
+ * box-tested against it, except priorities >= RenderSky and the visible occluders; a node stays submitted for 50 frames
+ * after it was last seen (SceneBasicInfo::occludedFrameCounter, kept per node on the device, shared by the cameras of a
+ * frame - hence `camera_order`).  Runs AFTER rn_transform_cull / rn_cull and rn_bounds_update, BEFORE rn_cull_sort; it
+ * clears visibility bits and re-emits the lists of ALL cameras.  A camera without a visible occluder keeps its list and
+ * touches no counter, as in the reference.
+ *   rn_occlusion_set_meshes      : triangle soups in model space, 9 floats per triangle (posA, posB, posC exactly as
+ *                                  Mesh::GetTrianglesChunk()'s vertex iterator yields them in RasterizeMesh :213-224);
+ *                                  mesh m owns triangles [triangle_offsets[m], triangle_offsets[m + 1])
+ *   rn_occlusion_set_node_meshes : per rank the mesh of the Entity (its model's LOD 0 / mesh 0), -1 = not an Entity
+ *                                  (an Occluder that is no Entity is box-tested but never rasterised, :516-525).  A full
+ *                                  rn_scene_upload re-tiles the scene: set the table again (the counters restart at 0,
+ *                                  like the SceneBasicInfo a node gets from AddNode)
+ *   rn_cull_occlusion            : `cameras[c]` belongs to camera c of the last cull; `camera_order` (may be NULL = 0, 1, ...)
+ *                                  is the order in which SceneBasic::Render visits them (:420-439: RenderEarly cameras, then
+ *                                  the ordinary ones, then RenderLate; inside a class newest first)
+ *   rn_occlusion_download        : number of occluders used by `camera` (0 = plain path), the jitter it took, the number of
+ *                                  jitter draws the whole call consumed, the camera's depth buffer (1 600 floats as the
+ *                                  reference indexes them), the counters of ranks [first, first + count); any may be NULL
+ * The jitter of :488 comes from Rayne's shared random generator, and only a camera that found occluders draws one - which
+ * the host cannot know before the cull has run.  The caller therefore passes the NEXT n_cameras draws of that generator
+ * (`jitter`, x y z each, in draw order; GetRandomVector3Range((-0.15, -0.15, 0), (0.15, 0.15, 0))); the cameras take them in
+ * order on the device, and rn_occlusion_download reports how many were consumed, so that a shim keeps the unconsumed ones
+ * queued for the next frame and the sequence of jitters equals the reference's.  That also makes the pass reproducible. */
+typedef struct rn_occlusion_camera
+{
+	float view[16];            /* Camera::GetViewMatrix() */
+	float projection[16];      /* Camera::GetProjectionMatrix() */
+	float pixel_size[2];       /* 1 / width, 1 / height of camera->GetRenderPass()->GetFrame() */
+	float world_position[3];   /* camera->GetWorldPosition() */
+	uint32_t enabled;          /* 0: leave this camera's list alone */
+} rn_occlusion_camera;
+int rn_occlusion_set_meshes(rn_scene_t *scene, const uint32_t *triangle_offsets, const float *triangles, uint32_t n_meshes);
+int rn_occlusion_set_node_meshes(rn_scene_t *scene, const int32_t *mesh_of_rank, uint32_t first, uint32_t count);
+int rn_occlusion_reset_counters(rn_scene_t *scene);
+int rn_cull_occlusion(rn_scene_t *scene, const rn_occlusion_camera *cameras, const uint32_t *camera_order, uint32_t n_cameras,
+                      const float *jitter, void *cuda_stream);
+int rn_occlusion_download(rn_scene_t *scene, uint32_t camera, uint32_t *used, float *jitter_taken, uint32_t *draws_consumed,
+                          float *depth_buffer, uint32_t *counters_by_rank, uint32_t first, uint32_t count);
 
 /* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
  * Pure host function; V <= 8 cameras per frame make this negligible. */

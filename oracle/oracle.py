@@ -299,3 +299,92 @@ def select_lod(ids: np.ndarray, wpos: np.ndarray, model_of_node: np.ndarray, sta
     load().rn_oracle_select_lod(_p(ids), C.c_uint32(ids.shape[0]), _p(wpos), _p(mo), _p(so), _p(sd), C.c_uint32(so.shape[0] - 1),
                                 _p(cam), C.c_float(clip_far), _p(out))
     return out
+
+
+OCC_PARAMS_DTYPE = np.dtype([("view", "<f4", 16), ("projection", "<f4", 16), ("offset", "<f4", 3), ("pixel", "<f4", 2),
+                             ("cam_pos", "<f4", 3)])
+FLAG_OCCLUDER = 8
+
+
+def jitter(seed: int, n_draws: int) -> np.ndarray:
+    """The occlusion pass's camera offsets as the reference's shared generator yields them after Seed(seed)."""
+    out = np.zeros((n_draws, 3), np.float32)
+    load().rn_oracle_jitter(C.c_uint32(seed), C.c_uint32(n_draws), _p(out))
+    return out
+
+
+def occlusion(order, can_render, flags, priority, wpos, radius, aabb, wmat, mesh_of, tri_ofs, tris, counter, view, projection,
+              offset, pixel, cam_pos):
+    """C8 for ONE camera and frame (rn_oracle_occlusion).  Arrays in creation order; `counter` is updated in place.
+    Returns (used, list of creation ids, depth buffer [40, 40]); used False = no occluder passed CanRender (plain cull)."""
+    lib = load()
+    lib.rn_oracle_occlusion.restype = C.c_uint32
+    n = len(order)
+    order = np.ascontiguousarray(order, np.uint32)
+    can_render = np.ascontiguousarray(can_render, np.uint8)
+    flags = np.ascontiguousarray(flags, np.uint32); priority = np.ascontiguousarray(priority, np.int32)
+    wpos = np.ascontiguousarray(wpos, np.float32); radius = np.ascontiguousarray(radius, np.float32)
+    aabb = np.ascontiguousarray(aabb, np.float32); wmat = np.ascontiguousarray(wmat, np.float32)
+    mesh_of = np.ascontiguousarray(mesh_of, np.int32)
+    tri_ofs = np.ascontiguousarray(tri_ofs, np.uint32); tris = np.ascontiguousarray(tris, np.float32)
+    assert counter.dtype == np.uint32 and counter.flags.c_contiguous
+    p = np.zeros((), OCC_PARAMS_DTYPE)
+    p["view"] = view; p["projection"] = projection; p["offset"] = offset; p["pixel"] = pixel; p["cam_pos"] = cam_pos
+    out = np.zeros(max(n, 1), np.uint32)
+    depth = np.zeros(1600, np.float32)
+    used = C.c_int(0)
+    cnt = lib.rn_oracle_occlusion(C.c_uint32(n), _p(order), _p(can_render), _p(flags), _p(priority), _p(wpos), _p(radius), _p(aabb),
+                                  _p(wmat), _p(mesh_of), _p(tri_ofs), _p(tris), _p(counter), C.c_void_p(p.ctypes.data), _p(out),
+                                  _p(depth), C.byref(used))
+    return bool(used.value), out[:cnt].copy(), depth.reshape(40, 40)
+
+
+def occlusion_frames(scene: Scene, cameras: np.ndarray, tri_ofs, tris, mesh_of, frames: int, seed: int,
+                     frame_size=(1280.0, 720.0), root_translate=(0.0, 0.0, 0.0), camera_translate=(0.0, 0.0, 0.0)) -> list:
+    """SceneBasic::Update + Render over `frames` frames with the software occlusion pass, restated: per frame a list of
+    per-camera dicts (used, offset, list of creation ids after the post-cull sorts, view, projection, cam_pos, frustum)
+    plus the counters after the frame.  Cameras are visited in SceneBasic::Render's order; every camera that takes the
+    occlusion path consumes one jitter draw of the generator seeded with `seed`."""
+    from rayne_b200.scenegen import CAM_DEFAULTS, camera_render_order
+    cams = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE).copy()
+    order = render_order(scene.parent, scene.priority)
+    parent = np.where(scene.parent >= 0, scene.parent, RN_NO_PARENT).astype(np.uint32)
+    pos = scene.pos.copy()
+    roots = np.nonzero(scene.parent < 0)[0]
+    counter = np.zeros(scene.n, np.uint32)
+    draws = jitter(seed, frames * len(cams))
+    drawn = 0
+    pixel = np.float32(1.0) / np.float32(frame_size)
+    visit = camera_render_order(cams["flags"])
+    out = []
+    for f in range(frames):
+        if f > 0:
+            pos[roots] += np.float32(root_translate)
+            cams["pos"] += np.float32(camera_translate)
+        wpos, wrot, wscale, wmat = world(parent, pos, scene.scale, scene.rot)
+        aabb = bounds(wrot, wscale, scene.box)
+        fr = frustums(cams)
+        view, proj, _ = camera_matrices(cams)
+        frame = {"cams": [None] * len(cams)}
+        for c in visit:
+            vis, sph = cull(wpos[order], wrot[order], wscale[order], scene.sphere[order], scene.flags[order], scene.group[order], fr[c],
+                            want_sphere=True)
+            radius = np.zeros(scene.n, np.float32); radius[order] = sph[:, 3]
+            can = np.zeros(scene.n, np.uint8); can[order[vis]] = 1
+            offset = draws[drawn]
+            used, lst, depth = occlusion(order, can, scene.flags, scene.priority, wpos, radius, aabb, wmat, mesh_of, tri_ofs, tris,
+                                         counter, view[c], proj[c], offset, pixel, cams["pos"][c])
+            if used:
+                drawn += 1
+            else:
+                lst, offset = order[vis], np.zeros(3, np.float32)
+            flags = int(cams[c]["flags"]) | CAM_DEFAULTS
+            unsorted = lst
+            lst = sort_list(lst, scene.priority, wpos, cams["pos"][c], bool(flags & (1 << 6)), bool(flags & (1 << 5)))
+            frame["cams"][c] = {"used": int(used), "offset": offset.copy(), "list": lst, "list_unsorted": unsorted, "view": view[c].copy(),
+                                "projection": proj[c].copy(), "cam_pos": cams["pos"][c].copy(), "frustum": fr[c].copy(),
+                                "depth": depth if used else None}
+        frame["counters"] = counter.copy()
+        frame["wpos"] = wpos; frame["aabb"] = aabb; frame["wmat"] = wmat
+        out.append(frame)
+    return out

@@ -10,6 +10,7 @@
 //   ref_harness bench-scene     <in.bin> <frames> <warmup>   print JSON timing line (ms per frame)
 //   ref_harness bench-particles <in.bin> <steps>  <warmup>   print JSON timing line
 //   ref_harness cascades  <in.bin> <out.bin>      Light::UpdateShadows + Camera::MakeShadowSplit for a directional light
+//   ref_harness occlusion <scene.bin> <occ.bin> <out.bin>   SceneBasic::Render with Flags::Occluder entities (software occlusion culling)
 //
 // File formats are documented in oracle/refio.py (the only reader/writer on the Python side).
 //
@@ -719,6 +720,244 @@ namespace
 		return 0;
 	}
 
+	// ---- software occlusion culling (SceneBasic::Render with Flags::Occluder nodes, RNSceneBasic.cpp:445-573) ----------
+	// Occluders are real Entities (Model + Mesh built by the reference's Mesh::WithColoredCube / WithSphereMesh); every node
+	// records its submission like CullNode does.  The jitter of :488 comes from the shared generator, seeded here; a second
+	// generator with the same seed is drawn in lock step so that the offsets the reference used can be written out.
+	struct OccNodeBase { uint32_t id = 0; };
+	static void RecordSubmission(uint32_t id, Camera *camera)
+	{
+		if(!g_recorder) return;
+		for(size_t i = 0; i < g_recorder->cameras.size(); i++)
+			if(g_recorder->cameras[i] == camera) { g_recorder->lists[i].push_back(id); break; }
+	}
+	class OccEntity : public Entity
+	{
+	public:
+		explicit OccEntity(Model *model) : Entity(model) {}
+		uint32_t id = 0;
+		void Render(Renderer *, Camera *camera) const override { RecordSubmission(id, camera); }
+	};
+	class OccPlain : public SceneNode
+	{
+	public:
+		uint32_t id = 0;
+		bool CanRender(Renderer *renderer, Camera *camera) const override { return CanRenderUtil(renderer, camera); }
+		void Render(Renderer *, Camera *camera) const override { RecordSubmission(id, camera); }
+	};
+
+	int CmdOcclusion(const char *scenePath, const char *occPath, const char *outPath, Renderer *renderer)
+	{
+		SceneInput in = ReadScene(scenePath);
+		Reader r(occPath);
+		uint32_t magic = r.get<uint32_t>(), version = r.get<uint32_t>();
+		if(magic != 0x494f4e52u || version != 1) { fprintf(stderr, "bad occlusion file\n"); return 2; }
+		uint32_t seed = r.get<uint32_t>();
+		float frameW = r.get<float>(), frameH = r.get<float>();
+		float camMove[3]; for(int i = 0; i < 3; i++) camMove[i] = r.get<float>();
+		uint32_t nMeshes = r.get<uint32_t>();
+		struct MeshDesc { uint32_t kind; float p[4]; };
+		std::vector<MeshDesc> meshDescs = r.vec<MeshDesc>(nMeshes);
+		std::vector<int32_t> meshOfNode = r.vec<int32_t>(in.nNodes);
+
+		std::vector<Mesh *> meshes;
+		std::vector<Model *> models;
+		Material *material = Material::WithShaders(renderer->GetDefaultShader(Shader::Type::Vertex, nullptr, Shader::UsageHint::Default),
+		                                           renderer->GetDefaultShader(Shader::Type::Fragment, nullptr, Shader::UsageHint::Default));
+		for(const MeshDesc &md : meshDescs)
+		{
+			Mesh *mesh = Mesh::WithColoredCube(Vector3(md.p[0], md.p[1], md.p[2]), Color(1.0f, 1.0f, 1.0f, 1.0f));
+			mesh->Retain();
+			meshes.push_back(mesh);
+			models.push_back(new Model(mesh, material));
+		}
+		// custom indexed meshes (ids continue after the cubes): positions + uint16 indices through the reference's Mesh class
+		uint32_t nCustom = r.get<uint32_t>();
+		for(uint32_t k = 0; k < nCustom; k++)
+		{
+			uint32_t nv = r.get<uint32_t>(), ni = r.get<uint32_t>();
+			std::vector<float> verts = r.vec<float>((size_t)nv * 3);
+			std::vector<uint16_t> idx = r.vec<uint16_t>(ni);
+			Mesh *mesh = new Mesh({Mesh::VertexAttribute(Mesh::VertexAttribute::Feature::Vertices, PrimitiveType::Vector3),
+			                       Mesh::VertexAttribute(Mesh::VertexAttribute::Feature::Indices, PrimitiveType::Uint16)}, nv, ni);
+			mesh->BeginChanges();
+			Mesh::Chunk chunk = mesh->GetChunk();
+			Mesh::ElementIterator<Vector3> vit = chunk.GetIterator<Vector3>(Mesh::VertexAttribute::Feature::Vertices);
+			for(uint32_t v = 0; v < nv; v++) *vit++ = Vector3(verts[v*3], verts[v*3+1], verts[v*3+2]);
+			Mesh::ElementIterator<uint16> iit = chunk.GetIterator<uint16>(Mesh::VertexAttribute::Feature::Indices);
+			for(uint32_t v = 0; v < ni; v++) *iit++ = idx[v];
+			mesh->changedVertices = true;
+			mesh->changedIndices = true;
+			mesh->EndChanges();
+			meshes.push_back(mesh);
+			models.push_back(new Model(mesh, material));
+		}
+
+		HarnessScene *scene = new HarnessScene();
+		std::vector<SceneNode *> nodes(in.nNodes);
+		std::vector<SceneNode *> roots;
+		for(uint32_t i = 0; i < in.nNodes; i++)
+		{
+			SceneNode *node;
+			if(meshOfNode[i] >= 0) { OccEntity *e = new OccEntity(models[meshOfNode[i]]); e->id = i; node = e; }
+			else { OccPlain *pn = new OccPlain(); pn->id = i; node = pn; }
+			node->SetPosition(Vector3(in.pos[i*3], in.pos[i*3+1], in.pos[i*3+2]));
+			node->SetScale(Vector3(in.scale[i*3], in.scale[i*3+1], in.scale[i*3+2]));
+			node->SetRotation(Quaternion(in.rot[i*4], in.rot[i*4+1], in.rot[i*4+2], in.rot[i*4+3]));
+			node->SetFlags(in.flags[i]);
+			node->SetRenderGroup(static_cast<uint8>(in.group[i]));
+			if(in.priority[i] != SceneNode::RenderNormal) node->SetRenderPriority(in.priority[i]);
+			// the bounds of the input file win over the model's (the same columns go to the oracle and to the GPU)
+			if(in.options & kOptBox)
+				node->SetBoundingBox(AABB(Vector3(in.box[i*6], in.box[i*6+1], in.box[i*6+2]), Vector3(in.box[i*6+3], in.box[i*6+4], in.box[i*6+5])), false);
+			else
+				node->SetBoundingBox(AABB(Vector3(-1.0f), Vector3(1.0f)), false);
+			node->SetBoundingSphere(Sphere(Vector3(in.sphere[i*4], in.sphere[i*4+1], in.sphere[i*4+2]), in.sphere[i*4+3]));
+			nodes[i] = node;
+		}
+		for(uint32_t i = 0; i < in.nNodes; i++)
+		{
+			if(in.parent[i] >= 0) nodes[in.parent[i]]->AddChild(nodes[i]);
+			else roots.push_back(nodes[i]);
+		}
+		for(SceneNode *root : roots) scene->AddNode(root);
+		std::vector<Camera *> cameras;
+		for(uint32_t c = 0; c < in.nCameras; c++)
+		{
+			const CameraDesc &d = in.cameras[c];
+			Camera *camera = new Camera();
+			camera->SetFlags(camera->GetFlags() | d.flags);
+			camera->SetRenderGroup(static_cast<uint8>(d.renderGroup));
+			camera->SetPosition(Vector3(d.pos[0], d.pos[1], d.pos[2]));
+			camera->SetRotation(Quaternion(d.rot[0], d.rot[1], d.rot[2], d.rot[3]));
+			camera->SetScale(Vector3(d.scale[0], d.scale[1], d.scale[2]));
+			camera->SetFOV(d.fov);
+			camera->SetAspectRatio(d.aspect);
+			camera->SetClipNear(d.clipNear);
+			camera->SetClipFar(d.clipFar);
+			if(d.flags & Camera::Flags::Orthogonal)
+				camera->SetOrthogonalFrustum(d.ortho[3], d.ortho[2], d.ortho[0], d.ortho[1]);
+			camera->SetFrustumPlaneOffset(d.planeOffsets[0], d.planeOffsets[1], d.planeOffsets[2], d.planeOffsets[3]);
+			camera->GetRenderPass()->SetFrame(Rect(0.0f, 0.0f, frameW, frameH));
+			scene->AddNode(camera);
+			cameras.push_back(camera);
+		}
+
+		RandomNumberGenerator *shared = RandomNumberGenerator::GetSharedGenerator();
+		if(!shared) { fprintf(stderr, "no shared random number generator\n"); return 2; }
+		shared->Seed(seed);
+		RandomNumberGenerator *mirror = new RandomNumberGenerator(RandomNumberGenerator::Type::MersenneTwister);
+		mirror->Seed(seed);
+
+		Recorder rec;
+		rec.cameras = cameras;
+		rec.lists.resize(cameras.size());
+		g_recorder = &rec;
+		uint32_t frames = in.nFrames ? in.nFrames : 1;
+
+		Writer w(outPath);
+		w.put<uint32_t>(0x4f4f4e52u); w.put<uint32_t>(1);
+		w.put<uint32_t>(in.nNodes); w.put<uint32_t>(in.nCameras); w.put<uint32_t>(frames);
+		std::vector<uint32_t> order;
+		for(IntrusiveList<SceneNode>::Member *m = scene->_renderNodes.GetHead(); m; m = m->GetNext())
+		{
+			SceneNode *node = m->Get();
+			OccEntity *e = node->Downcast<OccEntity>();
+			order.push_back(e ? e->id : static_cast<OccPlain *>(node)->id);
+		}
+		w.put<uint32_t>(static_cast<uint32_t>(order.size()));
+		w.vec(order);
+		// the triangle soups exactly as RasterizeMesh's iterator walk yields them (posA, posB, posC per triangle, :216-224)
+		w.put<uint32_t>(static_cast<uint32_t>(meshes.size()));
+		for(Mesh *mesh : meshes)
+		{
+			Mesh::Chunk chunk = mesh->GetTrianglesChunk();
+			Mesh::ElementIterator<Vector3> iterator = chunk.GetIterator<Vector3>(Mesh::VertexAttribute::Feature::Vertices);
+			size_t triangleCount = mesh->GetIndicesCount() / 3;
+			w.put<uint32_t>(static_cast<uint32_t>(triangleCount));
+			for(size_t i = 0; i < triangleCount; i++)
+			{
+				const Vector3 &posA = *iterator++;
+				const Vector3 &posB = *iterator++;
+				const Vector3 &posC = *iterator;
+				if(i < triangleCount - 1) iterator++;
+				w.put<float>(posA.x); w.put<float>(posA.y); w.put<float>(posA.z);
+				w.put<float>(posB.x); w.put<float>(posB.y); w.put<float>(posB.z);
+				w.put<float>(posC.x); w.put<float>(posC.y); w.put<float>(posC.z);
+			}
+		}
+		for(uint32_t f = 0; f < frames; f++)
+		{
+			for(auto &l : rec.lists) l.clear();
+			if(f > 0)
+			{
+				Vector3 t(in.rootTranslate[0], in.rootTranslate[1], in.rootTranslate[2]);
+				for(SceneNode *root : roots) root->Translate(t);
+				for(Camera *camera : cameras) camera->Translate(Vector3(camMove[0], camMove[1], camMove[2]));
+			}
+			scene->Update(1.0f / 60.0f);
+			// which cameras will take the occlusion path, in the order SceneBasic::Render visits them (:420-439): one jitter
+			// draw each
+			for(Camera *camera : cameras) camera->PostUpdate();
+			std::vector<uint32_t> used(cameras.size(), 0);
+			std::vector<Vector3> offsets(cameras.size());
+			for(int prio = 0; prio < 3; prio++)
+			{
+				for(IntrusiveList<Camera>::Member *cm = scene->_cameras.GetHead(); cm; cm = cm->GetNext())
+				{
+					Camera *camera = cm->Get();
+					if(camera->GetFlags() & Camera::Flags::NoRender || (prio == 0 && !(camera->GetFlags() & Camera::Flags::RenderEarly)) ||
+					   (prio == 1 && (camera->GetFlags() & Camera::Flags::RenderEarly || camera->GetFlags() & Camera::Flags::RenderLate)) ||
+					   (prio == 2 && !(camera->GetFlags() & Camera::Flags::RenderLate))) continue;
+					bool any = false;
+					for(SceneNode *node : nodes)
+						if(node->HasFlags(SceneNode::Flags::Occluder) && node->CanRender(renderer, camera)) { any = true; break; }
+					if(!any) continue;
+					size_t ci = std::find(cameras.begin(), cameras.end(), camera) - cameras.begin();
+					used[ci] = 1;
+					offsets[ci] = mirror->GetRandomVector3Range(Vector3(-0.15f, -0.15f, 0.0f), Vector3(0.15f, 0.15f, 0.0f));
+				}
+			}
+			scene->Render(renderer);
+			for(size_t c = 0; c < cameras.size(); c++)
+			{
+				Camera *cam = cameras[c];
+				w.put<uint32_t>(used[c]);
+				w.put<float>(offsets[c].x); w.put<float>(offsets[c].y); w.put<float>(offsets[c].z);
+				Matrix view = cam->GetViewMatrix(), proj = cam->GetProjectionMatrix();
+				for(int k = 0; k < 16; k++) w.put<float>(view.m[k]);
+				for(int k = 0; k < 16; k++) w.put<float>(proj.m[k]);
+				Vector3 cp = cam->GetWorldPosition();
+				w.put<float>(cp.x); w.put<float>(cp.y); w.put<float>(cp.z);
+				float fr[28];
+				fr[0] = cam->_frustumCenter.x; fr[1] = cam->_frustumCenter.y; fr[2] = cam->_frustumCenter.z; fr[3] = cam->_frustumRadius;
+				const Plane *planes[6] = { &cam->frustums._frustumLeft, &cam->frustums._frustumRight, &cam->frustums._frustumTop,
+				                           &cam->frustums._frustumBottom, &cam->frustums._frustumNear, &cam->frustums._frustumFar };
+				for(int k = 0; k < 6; k++)
+				{
+					fr[4 + k*4 + 0] = planes[k]->_normal.x; fr[4 + k*4 + 1] = planes[k]->_normal.y;
+					fr[4 + k*4 + 2] = planes[k]->_normal.z; fr[4 + k*4 + 3] = planes[k]->_d;
+				}
+				for(int k = 0; k < 28; k++) w.put<float>(fr[k]);
+				w.put<uint32_t>(static_cast<uint32_t>(cam->GetFlags()));
+				w.put<uint32_t>(static_cast<uint32_t>(cam->GetRenderGroup()));
+				w.put<uint32_t>(static_cast<uint32_t>(rec.lists[c].size()));
+				w.vec(rec.lists[c]);
+			}
+			// SceneBasicInfo::occludedFrameCounter of every node and the depth buffer the LAST camera left
+			std::vector<uint32_t> counters(in.nNodes);
+			for(uint32_t i = 0; i < in.nNodes; i++)
+				counters[i] = static_cast<uint32_t>(static_cast<SceneBasicInfo *>(nodes[i]->GetSceneInfo())->occludedFrameCounter);
+			w.vec(counters);
+			for(int k = 0; k < 40 * 40; k++) w.put<float>(scene->_occlusionDepthBuffer[k]);
+		}
+		g_recorder = nullptr;
+		// the shared generator must have been drawn exactly as often as the mirror
+		Vector3 a = shared->GetRandomVector3Range(Vector3(0.0f), Vector3(1.0f)), b = mirror->GetRandomVector3Range(Vector3(0.0f), Vector3(1.0f));
+		if(a.x != b.x || a.y != b.y || a.z != b.z) { fprintf(stderr, "jitter draws out of step with the reference\n"); return 3; }
+		return 0;
+	}
+
 	int CmdBenchParticles(const char *inPath, int steps, int warmup)
 	{
 		ParticleInput in = ReadParticles(inPath);
@@ -772,6 +1011,7 @@ int main(int argc, char **argv)
 	else if(cmd == "bench-scene" && argc >= 5) rc = CmdBenchScene(argv[2], atoi(argv[3]), atoi(argv[4]), renderer);
 	else if(cmd == "bench-particles" && argc >= 5) rc = CmdBenchParticles(argv[2], atoi(argv[3]), atoi(argv[4]));
 	else if(cmd == "cascades" && argc >= 4) rc = CmdCascades(argv[2], argv[3]);
+	else if(cmd == "occlusion" && argc >= 5) rc = CmdOcclusion(argv[2], argv[3], argv[4], renderer);
 	else fprintf(stderr, "bad arguments\n");
 	fflush(stdout);
 	(void)pool;

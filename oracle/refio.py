@@ -221,3 +221,71 @@ def bench_particles(emitters: np.ndarray, steps: int, warmup: int, delta: float 
         r = subprocess.run([harness_path(kind), "bench-particles", fin, str(steps), str(warmup)], check=True,
                            capture_output=True, text=True)
         return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+MESH_DESC_DTYPE = np.dtype([("kind", "<u4"), ("p", "<f4", 4)])   # kind 0: Mesh::WithColoredCube(size xyz)
+
+
+def run_occlusion(scene: Scene, cameras: np.ndarray, meshes: np.ndarray, mesh_of_node: np.ndarray, frames: int, seed: int,
+                  frame_size=(1280.0, 720.0), root_translate=(0.0, 0.0, 0.0), camera_translate=(0.0, 0.0, 0.0),
+                  kind: str = "strict", custom_meshes=()) -> dict:
+    """SceneBasic::Render with Flags::Occluder entities (software occlusion culling, RNSceneBasic.cpp:445-573) for
+    `frames` frames; harness command `occlusion`.  meshes: MESH_DESC_DTYPE records (cubes); custom_meshes: (vertices [V, 3],
+    uint16 indices) pairs built through the reference's Mesh class, ids continuing after the cubes; mesh_of_node: i32 [n],
+    -1 = plain node.
+    Returns order, mesh triangle soups (tri_ofs, tris [T, 9]) and per frame and camera: used, offset, view, projection,
+    cam_pos, frustum, flags, group, list; per frame the counters and the depth buffer the last camera left."""
+    cameras = np.ascontiguousarray(np.atleast_1d(cameras), dtype=CAMERA_DTYPE)
+    meshes = np.ascontiguousarray(np.atleast_1d(meshes), dtype=MESH_DESC_DTYPE)
+    with tempfile.TemporaryDirectory() as tmp:
+        fin, focc, fout = (os.path.join(tmp, x) for x in ("in.bin", "occ.bin", "out.bin"))
+        write_scene_input(fin, scene, cameras, frames, OPT_BOX if scene.box is not None else 0, root_translate)
+        with open(focc, "wb") as f:
+            f.write(np.array([0x494F4E52, 1, seed], dtype="<u4").tobytes())
+            f.write(np.asarray(list(frame_size) + list(camera_translate), dtype="<f4").tobytes())
+            f.write(np.array([meshes.shape[0]], dtype="<u4").tobytes())
+            f.write(meshes.tobytes())
+            f.write(np.ascontiguousarray(mesh_of_node, dtype="<i4").tobytes())
+            f.write(np.array([len(custom_meshes)], dtype="<u4").tobytes())
+            for verts, idx in custom_meshes:
+                verts = np.ascontiguousarray(verts, dtype="<f4").reshape(-1, 3)
+                idx = np.ascontiguousarray(idx, dtype="<u2")
+                f.write(np.array([verts.shape[0], idx.shape[0]], dtype="<u4").tobytes())
+                f.write(verts.tobytes())
+                f.write(idx.tobytes())
+        subprocess.run([harness_path(kind), "occlusion", fin, focc, fout], check=True, stdout=subprocess.DEVNULL)
+        buf = np.fromfile(fout, dtype=np.uint8)
+    off = 0
+
+    def take(dtype, count):
+        nonlocal off
+        dt = np.dtype(dtype)
+        a = np.frombuffer(buf, dtype=dt, count=count, offset=off)
+        off += dt.itemsize * count
+        return a
+
+    magic, version, n, ncam, nframes = (int(x) for x in take("<u4", 5))
+    assert magic == 0x4F4F4E52 and version == 1
+    out = {"order": take("<u4", int(take("<u4", 1)[0])).copy()}
+    nm = int(take("<u4", 1)[0])
+    tri_ofs, tris = [0], []
+    for _ in range(nm):
+        nt = int(take("<u4", 1)[0])
+        tris.append(take("<f4", nt * 9).reshape(nt, 9).copy())
+        tri_ofs.append(tri_ofs[-1] + nt)
+    out["tri_ofs"] = np.asarray(tri_ofs, np.uint32)
+    out["tris"] = np.concatenate(tris) if tris else np.zeros((0, 9), np.float32)
+    out["frames"] = []
+    for _ in range(nframes):
+        fr = {"cams": []}
+        for _c in range(ncam):
+            cam = {"used": int(take("<u4", 1)[0]), "offset": take("<f4", 3).copy(), "view": take("<f4", 16).copy(),
+                   "projection": take("<f4", 16).copy(), "cam_pos": take("<f4", 3).copy(), "frustum": take("<f4", 28).copy()}
+            cam["flags"], cam["group"], cnt = (int(x) for x in take("<u4", 3))
+            cam["list"] = take("<u4", cnt).copy()
+            fr["cams"].append(cam)
+        fr["counters"] = take("<u4", n).copy()
+        fr["depth"] = take("<f4", 1600).reshape(40, 40).copy()
+        out["frames"].append(fr)
+    assert off == buf.shape[0], (off, buf.shape[0])
+    return out

@@ -1306,3 +1306,18 @@ uint32_t rn_oracle_occlusion(uint32_t n, const uint32_t *order, const uint8_t *c
 	free(visible_occluder);
 	return count;
 }
+
+/* The camera jitter of :488: GetRandomVector3Range(Vector3(-0.15, -0.15, 0), Vector3(0.15, 0.15, 0)) drawn n times from a
+ * MersenneTwister seeded with `seed` (Source/Math/RNRandom.cpp:246-255: x, y, z in that order; the z draw is consumed
+ * although its range is empty). */
+void rn_oracle_jitter(uint32_t seed, uint32_t n_draws, float *out)
+{
+	oracle_mt g;
+	mt_seed(&g, seed);
+	for(uint32_t i = 0; i < n_draws; i++)
+	{
+		out[i * 3 + 0] = rand_range(&g, -0.15f, 0.15f);
+		out[i * 3 + 1] = rand_range(&g, -0.15f, 0.15f);
+		out[i * 3 + 2] = rand_range(&g, 0.0f, 0.0f);
+	}
+}

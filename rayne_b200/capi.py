@@ -35,6 +35,7 @@ EXPORTS = [
     "rn_scenevis_set_node_volumes", "rn_scenevis_set_camera_volumes", "rn_scenevis_choose_volume",
     "rn_particles_expand_billboards", "rn_particles_download_clip", "rn_particles_set_soft_max",
     "rn_particles_set_emitter_transforms", "rn_light_build_cascades", "rn_lod_set_models", "rn_lod_set_node_models", "rn_cull_select_lod",
+    "rn_occlusion_set_meshes", "rn_occlusion_set_node_meshes", "rn_occlusion_reset_counters", "rn_cull_occlusion", "rn_occlusion_download",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
@@ -81,6 +82,9 @@ class SceneStats(C.Structure):
                 ("kernel_launches", C.c_uint64)]
 
 
+OCCLUSION_CAMERA_DTYPE = np.dtype([("view", "<f4", 16), ("projection", "<f4", 16), ("pixel_size", "<f4", 2),
+                                   ("world_position", "<f4", 3), ("enabled", "<u4")])
+assert OCCLUSION_CAMERA_DTYPE.itemsize == 152
 FRUSTUM_DTYPE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("planes", "<f4", (6, 4)),
                           ("flags", "<u4"), ("render_group", "<u4")])
 assert FRUSTUM_DTYPE.itemsize == 120
@@ -368,6 +372,37 @@ class SceneHandle:
         cp = _f32(lod_camera_position).reshape(3)
         _check(self.lib.rn_cull_select_lod(self._h, C.c_uint32(camera), _ptr(cp), C.c_float(clip_far), C.c_void_p(device_out),
                                            C.c_uint32(capacity), C.c_void_p(stream)))
+
+    def occlusion_set_meshes(self, tri_ofs: np.ndarray, tris: np.ndarray) -> None:
+        to = np.ascontiguousarray(tri_ofs, np.uint32); tr = np.ascontiguousarray(tris, np.float32)
+        _check(self.lib.rn_occlusion_set_meshes(self._h, _ptr(to), _ptr(tr), C.c_uint32(to.shape[0] - 1)))
+
+    def occlusion_set_node_meshes(self, mesh_of_rank: np.ndarray, first: int = 0) -> None:
+        m = np.ascontiguousarray(mesh_of_rank, np.int32)
+        _check(self.lib.rn_occlusion_set_node_meshes(self._h, _ptr(m), C.c_uint32(first), C.c_uint32(m.shape[0])))
+
+    def occlusion_reset_counters(self) -> None:
+        _check(self.lib.rn_occlusion_reset_counters(self._h))
+
+    def cull_occlusion(self, cameras: np.ndarray, jitter: np.ndarray, order=None, stream: int = 0) -> None:
+        """cameras: OCCLUSION_CAMERA_DTYPE records, one per camera of the last cull; jitter: the next len(cameras) draws
+        [V, 3]; order: SceneBasic::Render's camera order."""
+        cams = np.ascontiguousarray(np.atleast_1d(cameras), dtype=OCCLUSION_CAMERA_DTYPE)
+        j = np.ascontiguousarray(jitter, np.float32).reshape(-1, 3)
+        assert j.shape[0] >= cams.shape[0]
+        o = None if order is None else np.ascontiguousarray(order, np.uint32)
+        _check(self.lib.rn_cull_occlusion(self._h, C.c_void_p(cams.ctypes.data), None if o is None else _ptr(o),
+                                          C.c_uint32(cams.shape[0]), _ptr(j), C.c_void_p(stream)))
+
+    def occlusion_download(self, camera: int, n: int):
+        """(occluders used, jitter taken [3], draws consumed by the call, depth buffer [40, 40], counters of ranks [0, n))"""
+        used = C.c_uint32(0); draws = C.c_uint32(0)
+        taken = np.zeros(3, np.float32)
+        depth = np.zeros(1600, np.float32)
+        counters = np.zeros(max(n, 1), np.uint32)
+        _check(self.lib.rn_occlusion_download(self._h, C.c_uint32(camera), C.byref(used), _ptr(taken), C.byref(draws), _ptr(depth),
+                                              _ptr(counters), C.c_uint32(0), C.c_uint32(n)))
+        return int(used.value), taken, int(draws.value), depth.reshape(40, 40), counters[:n]
 
     def set_node_volumes(self, volume_of_rank: np.ndarray, first: int = 0) -> None:
         v = np.ascontiguousarray(volume_of_rank, dtype=np.uint8)

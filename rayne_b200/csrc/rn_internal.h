@@ -108,6 +108,15 @@ struct rn_scene
 	uint32_t *lod_stage_ofs = nullptr;
 	float *lod_stage_dist = nullptr;
 	uint32_t lod_models = 0;
+	// software occlusion culling (rn_occlusion.cu), allocated on first use
+	uint16_t *occ_counter = nullptr;       // per slot: SceneBasicInfo::occludedFrameCounter
+	int32_t *occ_mesh_of_slot = nullptr;   // per slot: mesh index of the Entity, -1 = none
+	uint32_t *occ_tri_ofs = nullptr;       // [occ_meshes + 1]
+	float *occ_tris = nullptr;             // 9 floats per triangle
+	uint32_t occ_meshes = 0;
+	uint32_t *occ_cand = nullptr;          // candidate occluders of the camera being processed
+	uint32_t *occ_sel = nullptr;           // [RN_MAX_CAMERAS] selected occluders + flags
+	float *occ_depth = nullptr;            // [RN_MAX_CAMERAS][40 * 40]
 	uint32_t *rank_masks = nullptr;    // [RN_MAX_CAMERAS][ceil(max_nodes / 32)] visibility bits in rank order (rn_masks.cu)
 	bool have_masks = false;
 	uint32_t mask_ncams = 0;
@@ -141,6 +150,10 @@ int aabb_filter_launch(rn_scene *scene, const rn_camera_frustum *cams, uint32_t 
 // SceneWithVisibilityLists volumes: keeps camera c's bit only for nodes of the default volume or of the volume chosen for
 // c, recounts like the AABB filter.
 int volume_filter_launch(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
+// rn_scene.cu: zeroes the per-superblock totals (every mask filter recounts them) / emits the lists of the last cull
+int clear_super_totals(rn_scene *scene, cudaStream_t stream);
+int launch_compaction(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
+void occlusion_free(rn_scene *scene);   // rn_occlusion.cu
 
 template <class T>
 inline int dev_alloc(rn_scene *s, T **p, size_t count)

@@ -1227,6 +1227,7 @@ static void free_nodes(rn_scene *s)
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
 		if(s->lists[c]) { cudaFree(s->lists[c]); s->lists[c] = nullptr; }
 	extras_free(s);
+	occlusion_free(s);
 	if(s->scratch_host) { cudaFreeHost(s->scratch_host); s->scratch_host = nullptr; }
 	if(s->scratch_done) { cudaEventDestroy(s->scratch_done); s->scratch_done = nullptr; }
 	for(int i = 0; i < rn_scene::kProfileSlots; i++)
@@ -1336,7 +1337,7 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 	return s->fma_matrices ? launch_tiles_impl<CULL, true, 5>(s, cp, stream, persist) : launch_tiles_impl<CULL, false, 5>(s, cp, stream, persist);
 }
 
-static int clear_super_totals(rn_scene *s, cudaStream_t stream)
+int clear_super_totals(rn_scene *s, cudaStream_t stream)
 {
 	// + the tile counter of the persistent tile kernel, which lives right behind the totals
 	const size_t supers = (s->n_tiles + kSuperTiles - 1) / kSuperTiles;
@@ -1353,7 +1354,7 @@ static int launch_cull_flat(rn_scene *s, const CullParams &cp, cudaStream_t stre
 	return RN_OK;
 }
 
-static int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
+int launch_compaction(rn_scene *s, uint32_t ncams, cudaStream_t stream)
 {
 	EmitView ev;
 	ev.vis = s->vis;
@@ -1600,6 +1601,9 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	if(s->node_volume) { cudaFree(s->node_volume); s->node_volume = nullptr; }
 	s->volumes_on = false;
 	if(s->lod_node_model) { cudaFree(s->lod_node_model); s->lod_node_model = nullptr; }   // the same goes for the node -> model table
+	// ... and for the occlusion pass's per-slot mesh table and frame counters (a node that re-enters a scene starts at 0)
+	if(s->occ_mesh_of_slot) { cudaFree(s->occ_mesh_of_slot); s->occ_mesh_of_slot = nullptr; }
+	if(s->occ_counter) { cudaFree(s->occ_counter); s->occ_counter = nullptr; }
 
 	// per-tile arrays
 	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }

@@ -29,6 +29,7 @@ RENDER_TRANSPARENT = 300000
 CAM_ORTHOGONAL = 1 << 21
 CAM_USE_SIMPLE_CULLING = 1 << 26
 CAM_DEFAULTS = (1 << 24) | (1 << 5)
+CAM_NO_RENDER, CAM_RENDER_EARLY, CAM_RENDER_LATE = 1 << 7, 1 << 19, 1 << 20
 
 DEFAULT_RADIUS = np.sqrt(np.float32(3.0), dtype=np.float32)  # Sphere(AABB(-1, 1)), RNSphere.h:44-49
 
@@ -203,6 +204,93 @@ def config_scene(name: str, seed: int = 12345, trees: int | None = None) -> Scen
         return make_scene(n_trees=trees or 10, branching=(9, 10, 10), depth=4, seed=seed)
     n = {"C2": 48, "C4": 768, "C5": 3072}[name]
     return make_scene(n_trees=trees or n, branching=4, depth=8, seed=seed)
+
+
+MESH_DESC_DTYPE = np.dtype([("kind", "<u4"), ("p", "<f4", 4)])   # 0: Mesh::WithColoredCube(size xyz)
+
+
+def make_occlusion_scene(seed: int = 1, n_small: int = 3000, n_occluders: int = 40, n_groups: int = 12):
+    """A scene for the software occlusion pass (SceneBasic::Render with Flags::Occluder nodes, RNSceneBasic.cpp:445-573):
+    big box / sphere occluder Entities between a camera at the origin (looking down -z) and a cloud of small nodes, more
+    occluders than the 30 the reference keeps, an Occluder-flagged node that is no Entity (never rasterised), sky /
+    transparent nodes (never tested), hidden nodes, everything parented to a few slowly moving group roots.
+    Returns (Scene with local boxes, MESH_DESC_DTYPE records of three cubes, [(vertices, indices)] of one custom mesh with
+    id 3 - an octahedron whose first index is not 0 -, mesh_of_node i32 [n] with -1 = plain node)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    meshes = np.zeros(3, dtype=MESH_DESC_DTYPE)
+    meshes["p"][0] = (6.0, 5.0, 0.5, 0.0)
+    meshes["p"][1] = (2.0, 8.0, 2.0, 0.0)
+    meshes["p"][2] = (12.0, 1.5, 1.0, 0.0)
+    octa_v = np.float32([[4, 0, 0], [-4, 0, 0], [0, 4, 0], [0, -4, 0], [0, 0, 4], [0, 0, -4]])
+    octa_i = np.uint16([2, 4, 0, 2, 0, 5, 2, 5, 1, 2, 1, 4, 3, 0, 4, 3, 5, 0, 3, 1, 5, 3, 4, 1])
+    custom = [(octa_v, octa_i)]
+    half = np.float32([[6.0, 5.0, 0.5], [2.0, 8.0, 2.0], [12.0, 1.5, 1.0], [4.0, 4.0, 4.0]])
+    n = n_groups + n_occluders + n_small
+    parent = np.full(n, -1, np.int32)
+    pos = np.zeros((n, 3), np.float32); scale = np.ones((n, 3), np.float32)
+    rot = np.zeros((n, 4), np.float32); rot[:, 3] = 1.0
+    flags = np.zeros(n, np.uint32); group = np.ones(n, np.uint32); prio = np.zeros(n, np.int32)
+    sphere = np.zeros((n, 4), np.float32); box = np.zeros((n, 6), np.float32)
+    mesh_of = np.full(n, -1, np.int32)
+    # group roots: small offsets and rotations
+    g = np.arange(n_groups)
+    pos[g] = ((rng.random((n_groups, 3)) - 0.5) * (8.0, 4.0, 8.0)).astype(np.float32)
+    rot[g] = euler_to_quat((rng.random((n_groups, 3)) - 0.5) * 10.0)
+    scale[g] = (0.9 + 0.2 * rng.random(n_groups)).astype(np.float32)[:, None]
+    box[g] = (-1, -1, -1, 1, 1, 1); sphere[g, 3] = DEFAULT_RADIUS
+    flags[g] = FLAG_HIDDEN
+    # occluders
+    o = n_groups + np.arange(n_occluders)
+    parent[o] = rng.integers(0, n_groups, n_occluders)
+    z = -(12.0 + 110.0 * rng.random(n_occluders))
+    pos[o, 0] = ((rng.random(n_occluders) - 0.5) * 1.6 * -z).astype(np.float32)
+    pos[o, 1] = ((rng.random(n_occluders) - 0.5) * 0.8 * -z).astype(np.float32)
+    pos[o, 2] = z.astype(np.float32)
+    rot[o] = euler_to_quat((rng.random((n_occluders, 3)) - 0.5) * 30.0)
+    m = rng.integers(0, 4, n_occluders)
+    mesh_of[o] = m
+    box[o, :3] = -half[m]; box[o, 3:] = half[m]
+    sphere[o, 3] = np.sqrt((half[m] ** 2).sum(axis=1)).astype(np.float32)
+    flags[o] = FLAG_OCCLUDER
+    mesh_of[o[3]] = -1                                   # an Occluder that is no Entity: tested, never rasterised
+    flags[o[5]] &= ~np.uint32(FLAG_OCCLUDER)             # an Entity that is no Occluder: an ordinary tested node
+    # the small nodes: inside and around the view cone, most of them behind the occluders
+    k = n_groups + n_occluders + np.arange(n_small)
+    parent[k] = rng.integers(0, n_groups, n_small)
+    z = -(3.0 + 300.0 * rng.random(n_small) ** 0.7)
+    pos[k, 0] = ((rng.random(n_small) - 0.5) * 2.2 * -z).astype(np.float32)
+    pos[k, 1] = ((rng.random(n_small) - 0.5) * 1.2 * -z).astype(np.float32)
+    pos[k, 2] = z.astype(np.float32)
+    rot[k] = euler_to_quat(rng.random((n_small, 3)) * 360.0)
+    sz = (0.05 + 1.2 * rng.random((n_small, 3)) ** 2).astype(np.float32)
+    box[k, :3] = -sz; box[k, 3:] = sz
+    sphere[k, 3] = np.sqrt((sz ** 2).sum(axis=1)).astype(np.float32)
+    r = rng.random(n_small)
+    prio[k[r < 0.03]] = RENDER_SKY
+    prio[k[(r >= 0.03) & (r < 0.08)]] = RENDER_TRANSPARENT
+    prio[k[(r >= 0.08) & (r < 0.10)]] = RENDER_EARLY
+    flags[k[(r >= 0.10) & (r < 0.12)]] |= FLAG_HIDDEN
+    flags[k[(r >= 0.12) & (r < 0.14)]] |= FLAG_NOCULLING
+    tiny = k[(r >= 0.14) & (r < 0.18)]                   # sub-pixel boxes far away: fail the size test
+    box[tiny] *= np.float32(0.01)
+    return (Scene(parent=parent, pos=pos, scale=scale, rot=rot, flags=flags, group=group, priority=prio, sphere=sphere, box=box),
+            meshes, custom, mesh_of)
+
+
+def camera_render_order(cam_flags) -> list:
+    """The order in which SceneBasic::Render visits the cameras of a scene (RNSceneBasic.cpp:420-439): three passes
+    (RenderEarly, neither, RenderLate) over a list that AddNode fills with PushFront (:719), i.e. newest first."""
+    early, late, norender = CAM_RENDER_EARLY, CAM_RENDER_LATE, CAM_NO_RENDER
+    out = []
+    for want in (0, 1, 2):
+        for c in reversed(range(len(cam_flags))):
+            f = int(cam_flags[c])
+            if f & norender:
+                continue
+            cls = 0 if f & early else (2 if f & late else 1)
+            if cls == want:
+                out.append(c)
+    return out
 
 
 def flat_scene(n: int, seed: int = 1) -> Scene:

@@ -110,6 +110,7 @@ def main() -> None:
     np.savez_compressed(os.path.join(HERE, "particles_nonlocal_soft.npz"), **out)
     print("particles_nonlocal_soft", [r["count"] for r in ref])
     make_cascades()
+    make_occlusion()
 
 
 def cascade_cases():
@@ -133,6 +134,44 @@ def make_cascades() -> None:
             out[f"ref_{key}{k}"] = val
         print("cascades", k, ref["ortho"][:, 1])
     np.savez_compressed(os.path.join(HERE, "cascades_basic.npz"), **out)
+
+
+OCCLUSION_CASE = dict(seed=3, n_small=900, n_occluders=40, n_groups=8, frames=60, rng_seed=4242, frame_size=(1280.0, 720.0),
+                      root_translate=(0.02, 0.0, 0.0), camera_translate=(0.0, 0.0, -0.25))
+
+
+def occlusion_inputs():
+    kw = OCCLUSION_CASE
+    scene, meshes, custom, mesh_of = sg.make_occlusion_scene(seed=kw["seed"], n_small=kw["n_small"], n_occluders=kw["n_occluders"],
+                                                             n_groups=kw["n_groups"])
+    # camera 1 is added last, so SceneBasic::Render visits it first; camera 2 has no occluder in view (plain path)
+    cams = np.stack([sg.make_camera(), sg.make_camera(pos=(4, 1, 10), euler=(8, -3, 0), fov=60),
+                     sg.make_camera(pos=(0, 0, 30), euler=(180, 0, 0), far=200)])
+    return scene, meshes, custom, mesh_of, cams
+
+
+def make_occlusion() -> None:
+    """Software occlusion culling (RNSceneBasic.cpp:445-573) over 60 frames: lists, counters, depth buffers and the jitter
+    the reference drew, with occluder Entities built from the reference's own Mesh / Model classes."""
+    kw = OCCLUSION_CASE
+    scene, meshes, custom, mesh_of, cams = occlusion_inputs()
+    ref = refio.run_occlusion(scene, cams, meshes, mesh_of, frames=kw["frames"], seed=kw["rng_seed"], frame_size=kw["frame_size"],
+                              root_translate=kw["root_translate"], camera_translate=kw["camera_translate"], custom_meshes=custom)
+    out = {f"in_{k}": getattr(scene, k) for k in SCENE_COLS}
+    out.update(in_box=scene.box, in_cameras=cams, in_mesh_of=mesh_of, ref_order=ref["order"], ref_tri_ofs=ref["tri_ofs"], ref_tris=ref["tris"])
+    nf, nc = kw["frames"], len(cams)
+    out["ref_used"] = np.array([[fr["cams"][c]["used"] for c in range(nc)] for fr in ref["frames"]], np.uint8)
+    out["ref_offset"] = np.array([[fr["cams"][c]["offset"] for c in range(nc)] for fr in ref["frames"]], np.float32)
+    lists = [fr["cams"][c]["list"] for fr in ref["frames"] for c in range(nc)]
+    out["ref_list_ofs"] = np.concatenate([[0], np.cumsum([len(l) for l in lists])]).astype(np.uint32)
+    out["ref_lists"] = np.concatenate(lists).astype(np.uint16)
+    out["ref_counters"] = np.stack([fr["counters"] for fr in ref["frames"]]).astype(np.uint16)
+    out["ref_depth"] = np.stack([fr["depth"] for fr in ref["frames"]])
+    out["ref_view"] = np.array([[fr["cams"][c]["view"] for c in range(nc)] for fr in ref["frames"]], np.float32)
+    out["ref_projection"] = np.array([ref["frames"][0]["cams"][c]["projection"] for c in range(nc)], np.float32)
+    np.savez_compressed(os.path.join(HERE, "occlusion_basic.npz"), **out)
+    print("occlusion_basic", scene.n, "used", out["ref_used"].sum(axis=0).tolist(), "list sizes first/last frame",
+          [len(ref["frames"][0]["cams"][c]["list"]) for c in range(nc)], [len(ref["frames"][-1]["cams"][c]["list"]) for c in range(nc)])
 
 
 def nonlocal_soft_emitters():

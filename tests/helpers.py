@@ -138,3 +138,62 @@ def check_against_oracle(scene: sg.Scene, cameras: np.ndarray, strict: bool = Tr
         r = got["slot_lists_rank"][c]
         assert (np.diff(r.astype(np.int64)) > 0).all(), "list is not in render-list order"
     return got, ref
+
+
+def load_golden_occlusion():
+    """(scene, cameras, mesh_of, tri_ofs, tris, case dict, npz) of tests/golden/occlusion_basic.npz."""
+    from tests.golden.make_golden import OCCLUSION_CASE
+    g = np.load(os.path.join(GOLDEN_DIR, "occlusion_basic.npz"))
+    scene = sg.Scene(**{k: g["in_" + k] for k in ("parent", "pos", "scale", "rot", "flags", "group", "priority", "sphere")})
+    scene.box = g["in_box"]
+    return scene, g["in_cameras"], g["in_mesh_of"], g["ref_tri_ofs"], g["ref_tris"], dict(OCCLUSION_CASE), g
+
+
+def run_cuda_occlusion(scene: sg.Scene, cameras: np.ndarray, tri_ofs, tris, mesh_of, frames: int, seed: int,
+                       frame_size=(1280.0, 720.0), root_translate=(0.0, 0.0, 0.0), camera_translate=(0.0, 0.0, 0.0),
+                       rank_mode: bool = False):
+    """The frames of oracle.occlusion_frames through the C ABI: dirty roots -> rn_scene_update_nodes, rn_transform_cull,
+    rn_bounds_update, rn_cull_occlusion (jitter queue as a shim would keep it), rn_cull_sort.  Returns per frame a dict
+    with cams[c] = {used, offset, list (creation ids), depth}, counters (creation order)."""
+    cams = np.ascontiguousarray(np.atleast_1d(cameras), dtype=sg.CAMERA_DTYPE).copy()
+    rs = capi.RankedScene(scene)
+    roots = np.nonzero(scene.parent < 0)[0]
+    pos = scene.pos.copy()
+    draws = oracle.jitter(seed, frames * len(cams) + len(cams))      # what Rayne's shared generator would yield
+    drawn = 0
+    visit = np.asarray(sg.camera_render_order(cams["flags"]), np.uint32)
+    pixel = np.float32(1.0) / np.float32(frame_size)
+    out = []
+    with capi.SceneHandle(max_nodes=scene.n, strict_matrices=True) as h:
+        h.upload(rs)
+        if rank_mode:
+            h.set_list_mode(True, 500)
+        h.occlusion_set_meshes(tri_ofs, tris)
+        h.occlusion_set_node_meshes(np.asarray(mesh_of, np.int32)[rs.order])
+        rank_of_slot = h.download(capi.DL_RANK_OF_SLOT)
+        for f in range(frames):
+            if f > 0:
+                pos[roots] += np.float32(root_translate)
+                cams["pos"] += np.float32(camera_translate)
+                h.update_nodes(rs.rank_of[roots], position=pos[roots])
+            fr = capi.build_frustums(cams)
+            fr["flags"] |= sg.CAM_DEFAULTS
+            view, proj, _ = capi.build_camera_matrices(cams)
+            oc = np.zeros(len(cams), capi.OCCLUSION_CAMERA_DTYPE)
+            oc["view"] = view; oc["projection"] = proj; oc["pixel_size"] = pixel; oc["world_position"] = cams["pos"]; oc["enabled"] = 1
+            h.transform_cull(fr)
+            h.bounds_update()
+            h.cull_occlusion(oc, draws[drawn:drawn + len(cams)], order=visit)
+            h.cull_sort(np.ascontiguousarray(cams["pos"], np.float32))
+            frame = {"cams": []}
+            consumed = 0
+            for c in range(len(cams)):
+                used, taken, consumed, depth, counters = h.occlusion_download(c, scene.n)
+                ids = h.read_list(c)
+                ranks = (ids - 500) if rank_mode else rank_of_slot[ids]
+                frame["cams"].append({"used": used, "offset": taken if used else np.zeros(3, np.float32), "list": rs.order[ranks], "depth": depth})
+            full = np.zeros(scene.n, np.uint32); full[rs.order] = counters
+            frame["counters"] = full
+            drawn += consumed
+            out.append(frame)
+    return out

@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} is declared in include/rn_cuda.h but not exported by librn_cuda.so"
     assert sorted(capi.EXPORTS) == names, "capi.EXPORTS and the header disagree"
     lib.rn_abi_version.restype = C.c_int
-    assert lib.rn_abi_version() == 3
+    assert lib.rn_abi_version() == 4
 
 
 def test_pod_layouts_match_the_header():
@@ -50,6 +50,7 @@ def test_pod_layouts_match_the_header():
     assert sg.CAMERA_DTYPE.itemsize == (2 + 3 + 4 + 3 + 4 + 4 + 4 + 1 + 16) * 4
     assert sg.EMITTER_DTYPE.itemsize == (2 + 1 + 2 + 8 + 8 + 18 + 2 + 6) * 4
     assert C.sizeof(capi.SceneStats) == 6 * 4 + 2 * 8
+    assert capi.OCCLUSION_CAMERA_DTYPE.itemsize == (16 + 16 + 2 + 3 + 1) * 4
 
 
 def test_build_frustum_matches_oracle_and_golden():

@@ -311,3 +311,51 @@ def test_oracle_lod_selection_restatement():
 def sg_dist(a, b) -> np.float32:
     d = (a - b).astype(np.float32)
     return np.sqrt(np.float32(np.float32(np.float32(d[0] * d[0]) + np.float32(d[1] * d[1])) + np.float32(d[2] * d[2])))
+
+
+def test_occlusion_oracle_matches_golden():
+    """C8: the C restatement of the software occlusion pass against the reference's own run (60 frames, three cameras):
+    the jitter sequence of the seeded shared generator, which cameras take the pass, every list after the transparent sort,
+    every node's occludedFrameCounter after every frame and the depth buffer the last camera left."""
+    from rayne_b200 import scenegen as sg
+    from tests.helpers import load_golden_occlusion
+    scene, cams, mesh_of, tri_ofs, tris, kw, g = load_golden_occlusion()
+    frames = oracle.occlusion_frames(scene, cams, tri_ofs, tris, mesh_of, kw["frames"], kw["rng_seed"], kw["frame_size"],
+                                     kw["root_translate"], kw["camera_translate"])
+    assert np.array_equal(frames[0]["cams"][0]["projection"], g["ref_projection"][0])
+    nc = len(cams)
+    ofs = g["ref_list_ofs"]
+    visit = sg.camera_render_order(cams["flags"])
+    assert visit == [2, 1, 0]
+    for f, fr in enumerate(frames):
+        for c in range(nc):
+            k = f * nc + c
+            cam = fr["cams"][c]
+            assert cam["used"] == int(g["ref_used"][f, c]), (f, c)
+            assert np.array_equal(cam["offset"], g["ref_offset"][f, c]), (f, c)
+            assert np.array_equal(cam["view"], g["ref_view"][f, c]), (f, c)
+            assert np.array_equal(cam["list"], g["ref_lists"][ofs[k]:ofs[k + 1]]), (f, c)
+        assert np.array_equal(fr["counters"], g["ref_counters"][f]), f
+        last = [c for c in visit if fr["cams"][c]["used"]][-1]
+        assert np.array_equal(fr["cams"][last]["depth"], g["ref_depth"][f]), f
+    assert g["ref_counters"].max() >= 50 and g["ref_used"][:, 2].sum() == 0
+
+
+def test_occlusion_oracle_matches_the_live_reference():
+    """The same comparison on another scene where oracle/_ref exists (skipped on machines without it)."""
+    from oracle import refio
+    from rayne_b200 import scenegen as sg
+    if not refio.have_harness("strict"):
+        pytest.skip("oracle/_ref not built here")
+    scene, meshes, custom, mesh_of = sg.make_occlusion_scene(seed=21, n_small=1500, n_occluders=64, n_groups=6)
+    cams = np.stack([sg.make_camera(pos=(0, 1, 3)), sg.make_camera(pos=(-3, 0, 8), euler=(-6, 2, 0), flags=sg.CAM_RENDER_EARLY)])
+    ref = refio.run_occlusion(scene, cams, meshes, mesh_of, frames=5, seed=9, frame_size=(800.0, 600.0), root_translate=(0.1, 0, 0),
+                              camera_translate=(0, 0, -2.0), custom_meshes=custom)
+    got = oracle.occlusion_frames(scene, cams, ref["tri_ofs"], ref["tris"], mesh_of, 5, 9, (800.0, 600.0), (0.1, 0, 0), (0, 0, -2.0))
+    for f in range(5):
+        for c in range(2):
+            r = ref["frames"][f]["cams"][c]
+            assert got[f]["cams"][c]["used"] == r["used"]
+            assert np.array_equal(got[f]["cams"][c]["offset"], r["offset"])
+            assert np.array_equal(got[f]["cams"][c]["list"], r["list"]), (f, c)
+        assert np.array_equal(got[f]["counters"], ref["frames"][f]["counters"])
