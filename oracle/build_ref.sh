@@ -6,7 +6,7 @@
 # except RN_PLATFORM_LINUX 0 / RN_PLATFORM_POSIX 1 (avoids <xcb/xcb.h>, Source/Base/RNBase.h:53-55).
 # The reference's own cmake build is NOT run (it needs XCB/X11 and Vendor/OIS, absent here).
 #
-#   oracle/build_ref.sh [strict|release|all]
+#   oracle/build_ref.sh [strict|release|shim|all]
 #     strict : -O2 -ffp-contract=off                      -> parity goldens (librayne_strict.a, ref_harness_strict)
 #     release: the reference's flags (CMakeLists.txt:70)  -> timed CPU baseline (ref_harness_release)
 set -euo pipefail
@@ -62,8 +62,21 @@ build_one() {
         -Wl,--unresolved-symbols=ignore-all -ldl -o "$OUT/ref_harness_$name"
     echo "built $OUT/ref_harness_$name"
 }
+# RN::SceneCUDA (integration/RNSceneCUDA.cpp, the Rayne-side binding of librn_cuda) + its twin-scene test, linked against
+# the strict build of the reference and against rayne_b200/librn_cuda.so (found at run time through $ORIGIN)
+build_shim() {
+    local root; root=$(cd "$HERE/.." && pwd)
+    [ -f "$OUT/librayne_strict.a" ] || build_one strict "$STRICT_FLAGS"
+    [ -f "$root/rayne_b200/librn_cuda.so" ] || { echo "build librn_cuda.so first (python -m rayne_b200.build)"; exit 1; }
+    g++ $COMMON $STRICT_FLAGS -g -fno-access-control -I"$root/include" -I"$root/integration" \
+        "$root/integration/shim_test.cpp" "$root/integration/RNSceneCUDA.cpp" "$OUT/librayne_strict.a" \
+        -L"$root/rayne_b200" -lrn_cuda -Wl,-rpath,'$ORIGIN/../../rayne_b200' \
+        -Wl,--unresolved-symbols=ignore-all -ldl -o "$OUT/shim_test"
+    echo "built $OUT/shim_test"
+}
 case "$MODE" in
+    shim)    build_shim ;;
     strict)  build_one strict "$STRICT_FLAGS" ;;
     release) build_one release "$RELEASE_FLAGS" ;;
-    all)     build_one strict "$STRICT_FLAGS"; build_one release "$RELEASE_FLAGS" ;;
+    all)     build_one strict "$STRICT_FLAGS"; build_one release "$RELEASE_FLAGS"; build_shim ;;
 esac
