@@ -667,89 +667,88 @@ def run_ours(args) -> dict:
     h.update_nodes(roots, position=rs.position[roots])
     rootpos = rs.position[roots].copy()
 
-    # ---- end to end through the C ABI with host buffers (pinned) ----
-    pinned = [torch.empty(max(int(c * 1.3) + 4096, 4096), dtype=torch.int32).pin_memory() for c in counts]
-    pin_ptrs = [p.data_ptr() for p in pinned]
-    pin_caps = [p.numel() for p in pinned]
-    d2h = 0
-    # The frame is pipelined over S rank ranges on S streams (rayne_b200/pipeline.py) so that the PCIe copy of range
-    # k's lists overlaps the kernels of range k+1 - on every GPU (each rank pipelines its own range of the scene).
+    # ---- end to end through the C ABI with host buffers: rn_pipeline (rayne_b200/csrc/rn_pipeline.cu) ----
+    # dirty rows -> device, transform + cull over `shards` rank ranges on prioritised streams, visibility written into mapped
+    # pinned HOST memory by the device, two frames in flight (frame i's copy-out runs under frame i + 1's kernels).  Three
+    # encodings of the same visibility are timed; `e2e` is the adaptive one (per range and view the smaller of list and
+    # rank-order bitmask, chosen on the device), the one a host consumer would ask for.
     shards = max(1, min(args.e2e_shards, len(roots)))
-    pipe = None
-    if shards > 1:
-        from rayne_b200 import pipeline
-        torch.cuda.synchronize()
-        pipe = pipeline.PipelinedScene(rs, shards, device=local, rank_base=rank_offset if world > 1 else 0, tile_nodes=args.tile_nodes,
-                                       tile_inner_nodes=args.inner_nodes, tile_unit_nodes=args.unit_nodes,
-                                       strict_matrices=args.strict_matrices)
+    torch.cuda.synchronize()
+    pipe = capi.Pipeline(rs, n_ranges=shards, frames_in_flight=2, device=local, rank_base=rank_offset if world > 1 else 0,
+                         strict_matrices=args.strict_matrices, tile_nodes=args.tile_nodes, tile_inner_nodes=args.inner_nodes,
+                         tile_unit_nodes=args.unit_nodes)
 
-    def e2e_step():
-        nonlocal d2h
-        rootpos[:, 0] += np.float32(0.01)
-        if pipe is not None:
-            got = pipe.frame(fr, pin_ptrs, pin_caps, dirty_ranks=roots, position=rootpos)
-            d2h = int(got.sum()) * 4 + ncam * 4 * shards
-        else:
-            h.update_nodes(roots, position=rootpos)
-            h.transform_cull(fr, stream)
-            got = h.read_lists_into(pin_ptrs, pin_caps, stream)
-            d2h = int(got.sum()) * 4 + ncam * 4
+    def time_form(form):
+        """steady state with two frames in flight: submit frame i + 1, then wait for frame i"""
+        bytes_io = [0, 0]
 
-    for _ in range(min(3, args.warmup)):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-    d2h_total = d2h
-    if world > 1:
-        t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
-        t = torch.tensor([d2h], dtype=torch.int64, device="cuda")
-        dist.all_reduce(t)
-        d2h_total = int(t.item())
-    # the same frame with the visibility read back as rank-order bitmasks (1 bit per node and view instead of 4 B per
-    # visible node): the compact form of the same result
-    e2e_masks = None
-    if pipe is not None:
-        offs, total_words = pipe.mask_layout(ncam)
-        pinned_masks = torch.empty(total_words, dtype=torch.int32).pin_memory()
-
-        def e2e_mask_step():
+        def produce():
             rootpos[:, 0] += np.float32(0.01)
-            pipe.frame_masks(fr, pinned_masks.data_ptr(), dirty_ranks=roots, position=rootpos)
+            pipe.update_nodes(roots, position=rootpos)
+            pipe.submit(fr, form)
 
+        def consume():
+            view = pipe.acquire()
+            bytes_io[0], bytes_io[1] = int(view.h2d_bytes), int(view.d2h_bytes)
+            pipe.release()
+
+        produce()
         for _ in range(min(3, args.warmup)):
-            e2e_mask_step()
+            produce(); consume()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            e2e_mask_step()
+            produce(); consume()
         barrier()
-        mms = (time.perf_counter() - t0) * 1e3 / args.steps
+        ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        consume()
+        io = list(bytes_io)
         if world > 1:
-            t = torch.tensor([mms], dtype=torch.float64, device="cuda")
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            mms = float(t.item())
-        # same visibility as the lists?  compare the population counts of a fresh pair of frames on the same positions
-        pipe.frame(fr, pin_ptrs, pin_caps, dirty_ranks=roots, position=rootpos)
-        got_lists = pipe.frame(fr, pin_ptrs, pin_caps, dirty_ranks=roots, position=rootpos)
-        pipe.frame_masks(fr, pinned_masks.data_ptr(), dirty_ranks=roots, position=rootpos)
-        mk = pinned_masks.numpy().view(np.uint32)
-        pop = np.zeros(ncam, dtype=np.int64)
-        for k, (a, b) in enumerate(pipe.ranges):
-            w = (b - a + 31) // 32
-            blk = mk[offs[k]: offs[k] + ncam * w].reshape(ncam, w)
-            pop += np.unpackbits(blk.view(np.uint8), axis=1).sum(axis=1, dtype=np.int64)
-        e2e_masks = {"value": n_total / mms / 1e3, "unit": "Mnodes/s", "ms_per_step": mms,
-                     "h2d_bytes_per_step": int(roots.shape[0] * 16) * world, "d2h_bytes_per_step": int(total_words * 4) * world,
-                     "what": "as e2e, but rn_cull_build_masks + rn_cull_read_masks_async: the views' visibility as "
-                             "rank-order bitmasks in pinned host memory",
-                     "set_bits_equal_list_counts": bool(np.array_equal(pop, np.asarray(got_lists, dtype=np.int64)))}
-        pipe.close()
+            ms = float(t.item())
+            t = torch.tensor(io, dtype=torch.int64, device="cuda")
+            dist.all_reduce(t)
+            io = [int(x) for x in t.tolist()]
+        return ms, io
+
+    e2e_forms = {}
+    for name, form in (("adaptive", capi.VIS_ADAPTIVE), ("lists", capi.VIS_LISTS), ("masks", capi.VIS_MASKS)):
+        e2e_forms[name] = time_form(form)
+    # the three encodings carry the same lists, and those are the lists of the plain handle on the same positions
+    h.update_nodes(roots, position=rootpos)
+    h.set_list_mode(True, rank_offset if world > 1 else 0)        # global ranks, like the pipeline's segments
+    h.transform_cull(fr, stream)
+    want = [h.read_list(c) for c in range(ncam)]
+    if world == 1:
+        h.set_list_mode(False, 0)
+    forms_equal = True
+    for form in (capi.VIS_ADAPTIVE, capi.VIS_LISTS, capi.VIS_MASKS):
+        pipe.update_nodes(roots, position=rootpos)
+        pipe.submit(fr, form)
+        view = pipe.acquire()
+        got = pipe.frame_lists(view)
+        forms_equal = forms_equal and all(np.array_equal(a, b) for a, b in zip(got, want))
+        if form == capi.VIS_ADAPTIVE:
+            taken = pipe.forms(view)
+            forms_taken = ["".join("L" if taken[k, c] == capi.VIS_LISTS else "M" for k in range(taken.shape[0])) for c in range(ncam)]
+        pipe.release()
+    pipe.close()
+    e2e_ms, (h2d_total, d2h_total) = e2e_forms["adaptive"]
+
+    def e2e_entry(name, what):
+        ms, (hb, db) = e2e_forms[name]
+        return {"value": n_total / ms / 1e3, "unit": "Mnodes/s", "ms_per_step": ms, "h2d_bytes_per_step": hb, "d2h_bytes_per_step": db,
+                "form": name, "what": what}
+
+    e2e_common = (f"rn_pipeline_update_nodes (dirty roots) + rn_pipeline_submit + rn_pipeline_acquire: {shards} rank ranges on prioritised streams, "
+                  "visibility stored into mapped pinned host memory by the device, 2 frames in flight; ")
+    e2e_lists = e2e_entry("lists", e2e_common + "every view as its list of render-list ranks (4 B per visible node) - the container the reference's Render fills")
+    e2e_masks = e2e_entry("masks", e2e_common + "every view as a rank-order bitmask (1 bit per node)")
+    e2e_adaptive = e2e_entry("adaptive", e2e_common + "per range and view the smaller of list and bitmask, chosen on the device from the compaction's "
+                             "count; rn_frame_list decodes either into the reference's list")
+    e2e_adaptive["encodings_equal_and_equal_to_rn_cull_read_list"] = bool(forms_equal)
+    e2e_adaptive["encoding_per_view_and_range"] = forms_taken
 
     # ---- particles beside the headline (config C3 on every GPU; C5 times them inside the step) ----
     particles = None
@@ -888,13 +887,8 @@ def run_ours(args) -> dict:
                           f"inputs + outputs ({n * 169 / 1e6:.1f} MB) FIT in the 126 MB L2 at this config's size: the number is an L2-resident one, "
                           "as the reference's own frame at this size is cache-resident on the CPU"),
                    "parallelism": par},
-        "e2e": {"value": n_total / e2e_ms / 1e3, "unit": "Mnodes/s", "ms_per_step": e2e_ms,
-                "h2d_bytes_per_step": int(roots.shape[0] * 16) * world, "d2h_bytes_per_step": int(d2h_total),
-                "what": ("rn_scene_update_nodes(dirty roots, pinned staging) + rn_transform_cull + rn_cull_read_lists (counts + lists) "
-                         "into pinned host buffers" + (f"; frame pipelined over {shards} rank ranges on {shards} streams "
-                                                       "(rayne_b200/pipeline.py), every range's copy inside the timed region" if shards > 1 else "")
-                         + ("; every GPU reads back the lists of its own rank range (h2d / d2h bytes are the totals over all GPUs)" if world > 1 else "")),
-                "shards": shards},
+        "e2e": dict(e2e_adaptive, shards=shards, gpus="every GPU reads back its own rank range; byte counts are totals over all GPUs" if world > 1 else "one GPU"),
+        "e2e_lists": e2e_lists,
         "e2e_masks": e2e_masks,
         "gpu_launches": int(launches),
         "parity": parity,

@@ -28,6 +28,7 @@ extern "C" {
 #endif
 
 #define RN_ABI_VERSION 4
+#define RN_MAX_GROUP 16          /* GPUs of one rn_group */
 #define RN_MAX_CAMERAS 8          /* views culled by one rn_cull call (stereo + 4 cascades = 6) */
 #define RN_NO_PARENT 0xffffffffu
 
@@ -38,7 +39,7 @@ typedef enum rn_status {
 	RN_ERR_NOMEM = -3,
 	RN_ERR_STATE = -4,        /* call order violated (e.g. cull before upload) */
 	RN_ERR_CAPACITY = -5,     /* exceeds the capacities given at creation */
-	RN_ERR_NCCL = -6
+	RN_ERR_PEER = -6          /* rn_group: no usable transport between the GPUs (no peer access, no multicast object) */
 } rn_status;
 
 typedef struct rn_scene rn_scene_t;
@@ -348,6 +349,97 @@ int rn_cull_occlusion(rn_scene_t *scene, const rn_occlusion_camera *cameras, con
                       const float *jitter, void *cuda_stream);
 int rn_occlusion_download(rn_scene_t *scene, uint32_t camera, uint32_t *used, float *jitter_taken, uint32_t *draws_consumed,
                           float *depth_buffer, uint32_t *counters_by_rank, uint32_t first, uint32_t count);
+
+/* ---- the pipelined frame: visibility in HOST memory, one GPU (rn_pipeline.cu) ------------------------------------------
+ * The reference's Render hands its list to host code (Source/Scene/RNSceneBasic.cpp:576-640); when the consumer is the CPU
+ * the frame is  dirty rows -> device, transform + cull, visibility -> host.  rn_pipeline cuts the render list into
+ * `n_ranges` rank ranges where no parent / child edge crosses (rn_plan_ranges), gives every range its own rn_scene_t and
+ * prioritised stream, and keeps `frames_in_flight` result buffers in mapped pinned memory, so that neither the kernels nor
+ * the copy-out of a frame ever wait for the host:
+ *     rn_pipeline_update_nodes(...);                    the frame's SetPosition & co (ranks 0-based in the given columns)
+ *     rn_pipeline_submit(p, cameras, n, form);          enqueue; returns at once
+ *     ... submit the next frame before looking at this one to overlap its copy-out with the next kernels ...
+ *     rn_pipeline_acquire(p, &view);                    blocks until the OLDEST submitted frame is in host memory
+ *     ... walk view.segments (or rn_frame_list) ...
+ *     rn_pipeline_release(p);
+ * view.segments[range * n_cameras + camera] describes one piece of a camera's visibility: `form` RN_VIS_LISTS = `count`
+ * global ranks ascending; RN_VIS_MASKS = ceil(rank_count / 32) words, bit b of word w = rank rank_first + 32 w + b.  The
+ * concatenation over the ranges in order is the reference's list.  RN_VIS_ADAPTIVE lets the device pick per segment the
+ * smaller of the two encodings (a list wins below 1/32 visible).  Ranks are global: rank_base + position in the columns. */
+typedef struct rn_pipeline rn_pipeline_t;
+typedef enum rn_visibility_form { RN_VIS_LISTS = 0, RN_VIS_MASKS = 1, RN_VIS_ADAPTIVE = 2 } rn_visibility_form;
+typedef struct rn_pipeline_desc
+{
+	int32_t  device;
+	uint32_t n_ranges;            /* 0 = 4 */
+	uint32_t frames_in_flight;    /* 0 = 2 */
+	uint32_t flags;               /* rn_scene_desc.flags of every range (RN_SCENE_STRICT_MATRICES) */
+	uint32_t rank_base;           /* global rank of the first node (a GPU's own range in a multi-GPU split) */
+	uint32_t tile_nodes, tile_inner_nodes, tile_unit_nodes;   /* rn_scene_desc, 0 = defaults */
+} rn_pipeline_desc;
+typedef struct rn_frame_segment
+{
+	uint32_t form;                /* RN_VIS_LISTS or RN_VIS_MASKS */
+	uint32_t count;               /* visible nodes of this range for this camera */
+	uint32_t rank_first, rank_count;
+	const uint32_t *data;         /* host memory owned by the pipeline, valid until rn_pipeline_release */
+} rn_frame_segment;
+typedef struct rn_frame_view
+{
+	uint64_t frame;               /* 0, 1, 2 ... in submit order */
+	uint32_t n_cameras, n_ranges;
+	const rn_frame_segment *segments;
+	uint64_t h2d_bytes, d2h_bytes;   /* what this frame moved over PCIe (dirty rows in, headers + payload out) */
+} rn_frame_view;
+int rn_plan_ranges(const uint32_t *parent, uint32_t n, uint32_t n_ranges, uint32_t *bounds /* n_ranges + 1 */);
+int rn_pipeline_create(rn_pipeline_t **out, const rn_pipeline_desc *desc, const rn_node_columns *cols, uint32_t count);
+void rn_pipeline_destroy(rn_pipeline_t *pipeline);
+int rn_pipeline_ranges(const rn_pipeline_t *pipeline, uint32_t *bounds, uint32_t capacity, uint32_t *n_ranges);
+int rn_pipeline_update_nodes(rn_pipeline_t *pipeline, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count);
+int rn_pipeline_submit(rn_pipeline_t *pipeline, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_visibility_form form);
+int rn_pipeline_acquire(rn_pipeline_t *pipeline, rn_frame_view *view);
+int rn_pipeline_release(rn_pipeline_t *pipeline);
+/* Host decode of one camera of an acquired frame into a flat ascending list of global ranks (out_ranks may be NULL to get
+ * the count only). */
+int rn_frame_list(const rn_frame_view *view, uint32_t camera, uint32_t *out_ranks, uint32_t capacity, uint32_t *out_count);
+/* The rn_scene_t and stream of one range (device-side consumers: rn_cull_pack_instances, rn_scene_device_outputs ...). */
+int rn_pipeline_scene(rn_pipeline_t *pipeline, uint32_t range, rn_scene_t **scene, void **cuda_stream);
+
+/* ---- several GPUs, ONE host process (rn_group.cu) -------------------------------------------------------------------
+ * Rayne is a single-process engine: rn_group gives such a host the multi-GPU path of SURVEY.md §8(e).  The render list is
+ * cut into one rank range per GPU (rn_plan_ranges), every GPU propagates and culls its range against all cameras, and the
+ * one exchange of the path - every GPU learns the visibility of the whole scene - is fused into the kernel that builds the
+ * rank-order bitmasks: its stores go through an NVLS multicast object (one multimem.st per word, replicated by the
+ * NVSwitch; RN_GROUP_MULTICAST) or through peer-mapped pointers over NVLink (RN_GROUP_PEER).  No collective library; the
+ * GPUs are ordered with CUDA events and the host never waits.
+ *     rn_group_update_nodes(g, ...);                       the frame's setters, ranks 0-based in the given columns
+ *     rn_group_frame(g, cameras, n);                       enqueue on every GPU, returns at once
+ *     rn_group_expand(g, member, camera, ...);             that GPU's list of the WHOLE scene for one view (global ranks,
+ *                                                          ascending = render-list order), enqueued on its stream
+ *     rn_group_member(g, member, &scene, &stream, &masks)  the GPU's rn_scene_t (local lists, world matrices), its stream and
+ *                                                          its copy of the gathered masks: [camera][row_words], GPU k's block
+ *                                                          at word bounds-derived offset (rn_group_info)
+ *     rn_group_synchronize(g);                             host wait for all GPUs */
+typedef struct rn_group rn_group_t;
+enum { RN_GROUP_AUTO = 0, RN_GROUP_PEER = 1, RN_GROUP_MULTICAST = 2 };
+typedef struct rn_group_desc
+{
+	uint32_t n_devices;
+	int32_t  devices[RN_MAX_GROUP];
+	uint32_t flags;               /* rn_scene_desc.flags of every member */
+	uint32_t transport;           /* RN_GROUP_AUTO: multicast if the driver and the GPUs offer it, else peer stores */
+	uint32_t tile_nodes, tile_inner_nodes, tile_unit_nodes;
+} rn_group_desc;
+int rn_group_create(rn_group_t **out, const rn_group_desc *desc, const rn_node_columns *cols, uint32_t count);
+void rn_group_destroy(rn_group_t *group);
+int rn_group_info(const rn_group_t *group, uint32_t *transport, uint32_t *bounds, uint32_t capacity, uint32_t *row_words, const char **note);
+int rn_group_update_nodes(rn_group_t *group, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count);
+int rn_group_frame(rn_group_t *group, const rn_camera_frustum *cameras, uint32_t n_cameras);
+int rn_group_synchronize(rn_group_t *group);
+int rn_group_member(rn_group_t *group, uint32_t member, rn_scene_t **scene, void **cuda_stream, const uint32_t **gathered_masks);
+int rn_group_expand(rn_group_t *group, uint32_t member, uint32_t camera, uint32_t *device_list, uint32_t capacity, uint32_t *device_count,
+                    const uint32_t **out_list, const uint32_t **out_count);
+int rn_group_read_list(rn_group_t *group, uint32_t member, uint32_t camera, uint32_t *out_ranks, uint32_t capacity, uint32_t *out_count);
 
 /* Camera::PostUpdate + UpdateProjection + UpdateFrustum on the host (Source/Scene/RNCamera.cpp:296-384).
  * Pure host function; V <= 8 cameras per frame make this negligible. */

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librn_cuda.so")
-SOURCES = ["rn_scene.cu", "rn_bounds.cu", "rn_sort.cu", "rn_instances.cu", "rn_masks.cu", "rn_particles.cu", "rn_occlusion.cu", "rn_host.cpp"]
+SOURCES = ["rn_scene.cu", "rn_bounds.cu", "rn_sort.cu", "rn_instances.cu", "rn_masks.cu", "rn_particles.cu", "rn_occlusion.cu", "rn_pipeline.cu", "rn_group.cu", "rn_host.cpp"]
 HEADERS = ["rn_internal.h", "rn_math.cuh", os.path.join("..", "..", "include", "rn_cuda.h")]
 
 NVCC_FLAGS = [

@@ -36,6 +36,10 @@ EXPORTS = [
     "rn_particles_expand_billboards", "rn_particles_download_clip", "rn_particles_set_soft_max",
     "rn_particles_set_emitter_transforms", "rn_light_build_cascades", "rn_lod_set_models", "rn_lod_set_node_models", "rn_cull_select_lod",
     "rn_occlusion_set_meshes", "rn_occlusion_set_node_meshes", "rn_occlusion_reset_counters", "rn_cull_occlusion", "rn_occlusion_download",
+    "rn_plan_ranges", "rn_pipeline_create", "rn_pipeline_destroy", "rn_pipeline_ranges", "rn_pipeline_update_nodes", "rn_pipeline_submit",
+    "rn_pipeline_acquire", "rn_pipeline_release", "rn_frame_list", "rn_pipeline_scene",
+    "rn_group_create", "rn_group_destroy", "rn_group_info", "rn_group_update_nodes", "rn_group_frame", "rn_group_synchronize",
+    "rn_group_member", "rn_group_expand", "rn_group_read_list",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
 ]
 
@@ -259,6 +263,164 @@ class RankedScene:
 
 
 SCENE_STRICT_MATRICES = 1 << 0
+VIS_LISTS, VIS_MASKS, VIS_ADAPTIVE = 0, 1, 2
+
+
+class PipelineDesc(C.Structure):
+    _fields_ = [("device", C.c_int32), ("n_ranges", C.c_uint32), ("frames_in_flight", C.c_uint32), ("flags", C.c_uint32),
+                ("rank_base", C.c_uint32), ("tile_nodes", C.c_uint32), ("tile_inner_nodes", C.c_uint32), ("tile_unit_nodes", C.c_uint32)]
+
+
+class FrameSegment(C.Structure):
+    _fields_ = [("form", C.c_uint32), ("count", C.c_uint32), ("rank_first", C.c_uint32), ("rank_count", C.c_uint32), ("data", C.c_void_p)]
+
+
+class FrameView(C.Structure):
+    _fields_ = [("frame", C.c_uint64), ("n_cameras", C.c_uint32), ("n_ranges", C.c_uint32), ("segments", C.POINTER(FrameSegment)),
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+
+
+RN_MAX_GROUP = 16
+GROUP_AUTO, GROUP_PEER, GROUP_MULTICAST = 0, 1, 2
+
+
+class GroupDesc(C.Structure):
+    _fields_ = [("n_devices", C.c_uint32), ("devices", C.c_int32 * RN_MAX_GROUP), ("flags", C.c_uint32), ("transport", C.c_uint32),
+                ("tile_nodes", C.c_uint32), ("tile_inner_nodes", C.c_uint32), ("tile_unit_nodes", C.c_uint32)]
+
+
+class Group:
+    """Owns one rn_group_t: several GPUs driven by this one process (rn_group.cu)."""
+
+    def __init__(self, rs, devices, transport: int = GROUP_AUTO, strict_matrices: bool = False):
+        self.lib = load()
+        self._h = C.c_void_p()
+        desc = GroupDesc()
+        desc.n_devices = len(devices)
+        for k, d in enumerate(devices):
+            desc.devices[k] = int(d)
+        desc.flags = SCENE_STRICT_MATRICES if strict_matrices else 0
+        desc.transport = transport
+        keep = [_f32(rs.position), _f32(rs.scale), _f32(rs.rotation), np.ascontiguousarray(rs.parent, np.uint32),
+                np.ascontiguousarray(rs.flags, np.uint32), np.ascontiguousarray(rs.group, np.uint32), _f32(rs.sphere)]
+        cols = NodeColumns(*[_ptr(a) for a in keep], None, None)
+        _check(self.lib.rn_group_create(C.byref(self._h), C.byref(desc), C.byref(cols), C.c_uint32(rs.n)))
+        self.n, self.n_dev = rs.n, len(devices)
+        t = C.c_uint32(0); rw = C.c_uint32(0); note = C.c_char_p()
+        b = np.zeros(self.n_dev + 1, np.uint32)
+        _check(self.lib.rn_group_info(self._h, C.byref(t), _ptr(b), C.c_uint32(b.shape[0]), C.byref(rw), C.byref(note)))
+        self.transport, self.bounds, self.row_words, self.note = int(t.value), b, int(rw.value), (note.value or b"").decode()
+
+    def close(self) -> None:
+        if self._h:
+            self.lib.rn_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def update_nodes(self, ranks, position=None, scale=None, rotation=None, flags=None) -> None:
+        ranks = np.ascontiguousarray(ranks, dtype=np.uint32)
+        keep = [None if a is None else _f32(a) for a in (position, scale, rotation)]
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
+        cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, _ptr(fl), None, None)
+        _check(self.lib.rn_group_update_nodes(self._h, C.byref(cols), _ptr(ranks), C.c_uint32(ranks.shape[0])))
+
+    def frame(self, frustums: np.ndarray) -> None:
+        fr = np.ascontiguousarray(np.atleast_1d(frustums), dtype=FRUSTUM_DTYPE)
+        _check(self.lib.rn_group_frame(self._h, _ptr(fr), C.c_uint32(fr.shape[0])))
+
+    def synchronize(self) -> None:
+        _check(self.lib.rn_group_synchronize(self._h))
+
+    def read_list(self, member: int, camera: int) -> np.ndarray:
+        """The whole scene's list of one view as GPU `member` built it from its gathered masks (global ranks), on the host."""
+        out = np.zeros(max(self.n, 1), np.uint32)
+        cnt = C.c_uint32(0)
+        _check(self.lib.rn_group_read_list(self._h, C.c_uint32(member), C.c_uint32(camera), _ptr(out), C.c_uint32(out.shape[0]), C.byref(cnt)))
+        return out[:cnt.value].copy()
+
+
+def plan_ranges(parent: np.ndarray, n_ranges: int) -> np.ndarray:
+    """rn_plan_ranges: n_ranges + 1 bounds of contiguous rank ranges that no parent / child edge crosses."""
+    parent = np.ascontiguousarray(parent, np.uint32)
+    bounds = np.zeros(n_ranges + 1, np.uint32)
+    _check(load().rn_plan_ranges(_ptr(parent), C.c_uint32(parent.shape[0]), C.c_uint32(n_ranges), _ptr(bounds)))
+    return bounds
+
+
+class Pipeline:
+    """Owns one rn_pipeline_t: the frame with its visibility delivered to host memory (rn_pipeline.cu)."""
+
+    def __init__(self, rs, n_ranges: int = 4, frames_in_flight: int = 2, device: int = 0, rank_base: int = 0, strict_matrices: bool = False,
+                 tile_nodes: int = 0, tile_inner_nodes: int = 0, tile_unit_nodes: int = 0):
+        self.lib = load()
+        self._h = C.c_void_p()
+        desc = PipelineDesc(device, n_ranges, frames_in_flight, SCENE_STRICT_MATRICES if strict_matrices else 0, rank_base, tile_nodes,
+                            tile_inner_nodes, tile_unit_nodes)
+        keep = [_f32(rs.position), _f32(rs.scale), _f32(rs.rotation), np.ascontiguousarray(rs.parent, np.uint32),
+                np.ascontiguousarray(rs.flags, np.uint32), np.ascontiguousarray(rs.group, np.uint32), _f32(rs.sphere)]
+        box = getattr(rs, "box", None)
+        box = None if box is None else _f32(box)
+        prio = getattr(rs, "priority", None)
+        prio = None if prio is None else np.ascontiguousarray(prio, np.int32)
+        cols = NodeColumns(*[_ptr(a) for a in keep], _ptr(box), _ptr(prio))
+        _check(self.lib.rn_pipeline_create(C.byref(self._h), C.byref(desc), C.byref(cols), C.c_uint32(rs.n)))
+        self.n = rs.n
+        self.rank_base = rank_base
+        nr = C.c_uint32(0)
+        b = np.zeros(n_ranges + 1, np.uint32)
+        _check(self.lib.rn_pipeline_ranges(self._h, _ptr(b), C.c_uint32(b.shape[0]), C.byref(nr)))
+        self.bounds = b
+
+    def close(self) -> None:
+        if self._h:
+            self.lib.rn_pipeline_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def update_nodes(self, ranks, position=None, scale=None, rotation=None, flags=None, group=None, sphere=None) -> None:
+        ranks = np.ascontiguousarray(ranks, dtype=np.uint32)
+        keep = [None if a is None else _f32(a) for a in (position, scale, rotation, sphere)]
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
+        gr = None if group is None else np.ascontiguousarray(group, dtype=np.uint32)
+        cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, _ptr(fl), _ptr(gr), _ptr(keep[3]))
+        _check(self.lib.rn_pipeline_update_nodes(self._h, C.byref(cols), _ptr(ranks), C.c_uint32(ranks.shape[0])))
+
+    def submit(self, frustums: np.ndarray, form: int = VIS_ADAPTIVE) -> None:
+        fr = np.ascontiguousarray(np.atleast_1d(frustums), dtype=FRUSTUM_DTYPE)
+        _check(self.lib.rn_pipeline_submit(self._h, _ptr(fr), C.c_uint32(fr.shape[0]), C.c_int(form)))
+
+    def acquire(self) -> FrameView:
+        view = FrameView()
+        _check(self.lib.rn_pipeline_acquire(self._h, C.byref(view)))
+        return view
+
+    def release(self) -> None:
+        _check(self.lib.rn_pipeline_release(self._h))
+
+    def frame_lists(self, view: FrameView) -> list:
+        """Every camera of an acquired frame as a flat array of global ranks (host decode, rn_frame_list)."""
+        out = []
+        for c in range(view.n_cameras):
+            cnt = C.c_uint32(0)
+            _check(self.lib.rn_frame_list(C.byref(view), C.c_uint32(c), None, C.c_uint32(0), C.byref(cnt)))
+            a = np.zeros(max(cnt.value, 1), np.uint32)
+            _check(self.lib.rn_frame_list(C.byref(view), C.c_uint32(c), _ptr(a), C.c_uint32(a.shape[0]), C.byref(cnt)))
+            out.append(a[:cnt.value])
+        return out
+
+    def forms(self, view: FrameView) -> np.ndarray:
+        """[n_ranges, n_cameras] of the encodings the device chose."""
+        return np.array([[view.segments[k * view.n_cameras + c].form for c in range(view.n_cameras)] for k in range(view.n_ranges)])
 
 
 class SceneHandle:

@@ -154,6 +154,8 @@ int volume_filter_launch(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
 int clear_super_totals(rn_scene *scene, cudaStream_t stream);
 int launch_compaction(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
 void occlusion_free(rn_scene *scene);   // rn_occlusion.cu
+// rn_masks.cu: the rank-order masks of the last cull stored into n_dst buffers at once (peer-mapped pointers)
+int build_masks_fanout(rn_scene *scene, uint32_t *const *dsts, uint32_t n_dst, uint32_t stride, cudaStream_t stream);
 
 template <class T>
 inline int dev_alloc(rn_scene *s, T **p, size_t count)

@@ -53,6 +53,39 @@ __global__ void __launch_bounds__(kMaskThreads) rank_mask_kernel(const uint8_t *
 	}
 }
 
+// The same words stored into the gathered buffers of several GPUs of ONE process through peer-mapped pointers (NVLink
+// stores): the fallback of rn_group where no NVLS multicast object can be had.  dst.p[k] = row 0 of this GPU's block inside
+// GPU k's buffer.
+struct FanoutDst
+{
+	uint32_t *p[RN_MAX_GROUP];
+	uint32_t n;
+};
+
+template <uint32_t NCAMS>
+__global__ void __launch_bounds__(kMaskThreads) rank_mask_fanout_kernel(const uint8_t *__restrict__ vis, uint32_t words, uint32_t stride,
+                                                                        const __grid_constant__ FanoutDst dst)
+{
+	const uint32_t w = blockIdx.x * kMaskThreads + threadIdx.x;
+	if(w >= words)
+		return;
+	const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(vis) + 2u * w), hi = __ldg(reinterpret_cast<const uint4 *>(vis) + 2u * w + 1u);
+	const uint32_t v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+	for(uint32_t c = 0; c < NCAMS; c++)
+	{
+		uint32_t word = 0;
+#pragma unroll
+		for(uint32_t g = 0; g < 8; g++)
+		{
+			const uint32_t t = (v[g] >> c) & 0x01010101u;
+			word = (word >> 4) | ((t * 0x10204080u) & 0xf0000000u);
+		}
+		for(uint32_t k = 0; k < dst.n; k++)
+			dst.p[k][(size_t)c * stride + w] = word;
+	}
+}
+
 // ---- expansion: words -> ascending ranks -----------------------------------------------------------------------
 constexpr uint32_t kExpandThreads = 256;
 constexpr uint32_t kExpandWordsPerBlock = kExpandThreads * 4;   // 32 768 ranks per CTA
@@ -258,6 +291,32 @@ extern "C" int rn_cull_build_masks_multicast(rn_scene_t *s, uint32_t *multicast_
 	if(s->n == 0)
 		return RN_OK;
 	return build_masks(s, multicast_out, row_stride_words, static_cast<cudaStream_t>(cuda_stream), true);
+}
+
+namespace rn {
+int build_masks_fanout(rn_scene *s, uint32_t *const *dsts, uint32_t n_dst, uint32_t stride, cudaStream_t stream)
+{
+	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "the mask fan-out needs a cull");
+	RN_REQUIRE(n_dst >= 1 && n_dst <= RN_MAX_GROUP, RN_ERR_INVALID, "1..%d destinations", RN_MAX_GROUP);
+	if(s->n == 0)
+		return RN_OK;
+	FanoutDst d;
+	memset(&d, 0, sizeof(d));
+	d.n = n_dst;
+	for(uint32_t k = 0; k < n_dst; k++) d.p[k] = dsts[k];
+	const uint32_t words = mask_words(s);
+	const uint32_t grid = (words + kMaskThreads - 1) / kMaskThreads;
+	switch(s->last_ncams)
+	{
+#define RN_FAN_CASE(V) case V: rank_mask_fanout_kernel<V><<<grid, kMaskThreads, 0, stream>>>(s->vis, words, stride, d); break;
+		RN_FAN_CASE(1) RN_FAN_CASE(2) RN_FAN_CASE(3) RN_FAN_CASE(4) RN_FAN_CASE(5) RN_FAN_CASE(6) RN_FAN_CASE(7)
+		default: rank_mask_fanout_kernel<8><<<grid, kMaskThreads, 0, stream>>>(s->vis, words, stride, d); break;
+#undef RN_FAN_CASE
+	}
+	RN_CUDA(cudaGetLastError());
+	s->launches++;
+	return RN_OK;
+}
 }
 
 extern "C" int rn_cull_device_masks(rn_scene_t *s, const uint32_t **masks, uint32_t *words_per_camera, uint32_t *n_cameras)

@@ -156,3 +156,22 @@ def test_light_cascades_match_golden():
     # the C4 rig built from the reference-derived cascades: 2 eye cameras + 4 orthogonal cascade cameras
     rig = sg.vr_cascade_rig()
     assert rig.shape[0] == 6 and (rig["flags"][2:] & sg.CAM_ORTHOGONAL).all()
+
+
+def test_plan_ranges_matches_the_python_planner():
+    """rn_plan_ranges (C) against shard.plan_shards on random forests: same cuts, all edge-free."""
+    from rayne_b200 import shard
+    for seed in range(6):
+        scene = sg.make_scene(ragged_nodes=3000 + 500 * seed, depth=6, seed=seed) if seed % 2 else sg.make_scene(n_trees=17 + seed, branching=3, depth=5, seed=seed)
+        rs = capi.RankedScene(scene)
+        for world in (1, 2, 3, 8):
+            try:
+                want = shard.plan_shards(rs.parent, world)
+            except ValueError:
+                with pytest.raises(capi.RNError):
+                    capi.plan_ranges(rs.parent, world)
+                continue
+            got = capi.plan_ranges(rs.parent, world)
+            assert [int(a) for a, _ in want] + [rs.n] == got.tolist(), (seed, world)
+    with pytest.raises(capi.RNError):
+        capi.plan_ranges(capi.RankedScene(sg.make_scene(n_trees=1, branching=2, depth=4, seed=1)).parent, 2)
