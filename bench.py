@@ -452,7 +452,7 @@ def run_ours(args) -> dict:
         parity_rank = 0
         local_roots = rs.roots
         n_total = n * world
-    h = capi.SceneHandle(max_nodes=n, device=local, max_emitters=n_emitters, max_particles_per_emitter=4000 if n_emitters else 0,
+    h = capi.SceneHandle(max_nodes=n + 65536, device=local, max_emitters=n_emitters, max_particles_per_emitter=4000 if n_emitters else 0,   # + room for incremental edits
                          tile_nodes=args.tile_nodes, tile_inner_nodes=args.inner_nodes, tile_unit_nodes=args.unit_nodes,
                          strict_matrices=args.strict_matrices)
     h.upload(rs)
@@ -817,6 +817,28 @@ def run_ours(args) -> dict:
         extras["cull_sort_front_to_back"] = {"ms": ms, "entries": entries, "Mentries_per_s": entries / ms / 1e3,
                                              "roofline_frac": sort_bytes / (ms * 1e-3) / 1e9 / peak,
                                              "how": "time of (rn_transform_cull + rn_cull_sort) minus rn_transform_cull: every repetition sorts a fresh, unsorted list"}
+        # the 1 %-dirty frame - one node in a hundred (spread over the whole render list) gets a new local
+        # position through rn_scene_update_nodes, then the usual frame.  The host wall clock covers the staging copy, the
+        # H2D copy, the scatter kernel and rn_transform_cull (which re-propagates every node: there is no dirty shortcut).
+        dirty = np.arange(0, n, 100, dtype=np.uint32)
+        dpos = np.ascontiguousarray(rs.position[dirty])
+
+        def dirty_frame():
+            h.update_nodes(dirty, position=dpos)
+            h.transform_cull(fr, stream)
+
+        for _ in range(3):
+            dirty_frame()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        reps = max(1, min(20, args.extras_reps * 2))
+        for _ in range(reps):
+            dirty_frame()
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3 / reps
+        extras["frame_1pct_dirty"] = {"ms": ms, "dirty_nodes": int(dirty.shape[0]), "h2d_bytes": int(dirty.shape[0]) * 16,
+                                      "Mnodes_per_s": n / ms / 1e3,
+                                      "what": "rn_scene_update_nodes (1 % of the nodes, host arrays) + rn_transform_cull, host wall clock"}
         # visibility as rank-order bitmasks (the multi-GPU exchange format) and back: 1 B + V/8 B per node; expansion of
         # the largest view reads its words twice and writes 4 B per entry
         ms = timed(lambda: h.build_masks(stream))
@@ -852,6 +874,34 @@ def run_ours(args) -> dict:
             ms = timed(lambda: h.particles_expand_billboards(ident, ident, stream=stream))
             extras["particles_expand_billboards"] = {"ms": ms, "bytes_per_particle": 272,
                                                      "roofline_frac": particles["live_per_gpu"] * 272.0 / (ms * 1e-3) / 1e9 / peak}
+        # incremental edits (SceneBasic::AddNode / RemoveNode without a new upload): 1 000 new nodes - 10 trees of 100 - into the
+        # uploaded scene, a frame, then out again.  Host wall clock around each call (they synchronise internally).
+        if world == 1 and not args.strict_matrices:
+            h.set_list_mode(False, 0)
+            ex = sg.make_scene(n_trees=10, branching=99, depth=2, seed=777)
+            exp = np.where(ex.parent >= 0, ex.parent, capi.RN_NO_PARENT).astype(np.uint32)
+            # call order = children before their parent: reverse creation order of every (root, 99 children) tree
+            seq = np.arange(ex.n)[::-1].copy()
+            pos_in = np.empty(ex.n, np.int64); pos_in[seq] = np.arange(ex.n)
+            par = np.where(ex.parent[seq] >= 0, pos_in[np.maximum(ex.parent[seq], 0)], capi.RN_NO_PARENT).astype(np.uint32)
+            h.transform_cull(fr, stream)
+            counts_before = h.read_counts()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            slots = h.add_nodes(ex.pos[seq], ex.scale[seq], ex.rot[seq], par, ex.flags[seq], ex.group[seq], ex.sphere[seq])
+            t_add = (time.perf_counter() - t0) * 1e3
+            ms_after = timed(lambda: h.transform_cull(fr, stream))
+            counts_after = h.read_counts()
+            t0 = time.perf_counter()
+            h.remove_nodes(slots)
+            t_rem = (time.perf_counter() - t0) * 1e3
+            h.transform_cull(fr, stream)
+            counts_removed = h.read_counts()
+            extras["incremental_edits"] = {"nodes": int(ex.n), "add_ms": t_add, "remove_ms": t_rem, "frame_ms_with_the_new_tiles": ms_after,
+                                           "visible_after_add": [int(c) for c in counts_after], "visible_after_remove": [int(c) for c in counts_removed],
+                                           "counts_back_to_before_the_edit": bool(np.array_equal(counts_removed, counts_before)),
+                                           "what": "rn_scene_add_nodes / rn_scene_remove_nodes on the uploaded scene, host wall clock; "
+                                                   "a full rn_scene_upload of this scene takes seconds (host re-tiling)"}
     if world > 1:
         torch.cuda.synchronize()
         dist.barrier()

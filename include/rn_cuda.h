@@ -39,6 +39,7 @@ typedef enum rn_status {
 	RN_ERR_NOMEM = -3,
 	RN_ERR_STATE = -4,        /* call order violated (e.g. cull before upload) */
 	RN_ERR_CAPACITY = -5,     /* exceeds the capacities given at creation */
+	RN_ERR_UNSUPPORTED = -7,  /* rn_scene_add_nodes: this edit needs a full rn_scene_upload (message says why) */
 	RN_ERR_PEER = -6          /* rn_group: no usable transport between the GPUs (no peer access, no multicast object) */
 } rn_status;
 
@@ -169,6 +170,31 @@ int rn_scene_update_nodes(rn_scene_t *scene, const rn_node_columns *cols, const 
 int rn_scene_update_nodes_async(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count,
                                 void *cuda_stream);
 int rn_scene_node_count(const rn_scene_t *scene, uint32_t *out_count);
+/* Incremental edits - SceneBasic::AddNode / RemoveNode (Source/Scene/RNSceneBasic.cpp:683-746, :120-150) without a new
+ * upload.  Nodes are named by their SLOT, which never changes while they exist (RN_DL_SLOT_OF_RANK gives the slots of an
+ * upload; lists in slot mode hold them); requires slot lists (the default list mode).
+ *   rn_scene_add_nodes   : `count` new nodes in the order SceneBasic::AddRenderNode would be CALLED for them (AddNode
+ *                          recurses into the children first, Source/Scene/RNSceneNode.cpp:286-291, so a subtree arrives
+ *                          children-before-parent).  cols->parent[i] = index of the parent inside this batch, or
+ *                          RN_PARENT_IS_SLOT | slot of a node that is already in the scene (AddChild on an in-scene
+ *                          parent), or RN_NO_PARENT.  One render priority per batch.  The batch lands where the
+ *                          reference's insert rules put it (:652-676): in front of the list when its priority does not
+ *                          exceed the list head's (in reverse call order - every PushFront lands before the previous
+ *                          one), behind it when it is not below the tail's.  New tiles are appended to the node arrays;
+ *                          nothing that exists moves.  out_slots[i] = slot of node i.
+ *                          RN_ERR_UNSUPPORTED (do a full rn_scene_upload instead): a priority that belongs in the middle
+ *                          of the list, a priority the upload did not contain, a subtree of more than tile_nodes nodes,
+ *                          a parent that was itself added under a tile-computed node.  RN_ERR_CAPACITY: max_nodes (every
+ *                          batch takes whole groups of 32 slots per tile) or the tile list's headroom is used up.
+ *   rn_scene_remove_nodes: the nodes (a removed node's whole subtree, as RemoveNode -> UpdateSceneInfo(nullptr) takes it
+ *                          out, Source/Scene/RNSceneNode.cpp:274-281) become holes: never visible, never listed.  Their
+ *                          slots are not reused before the next full upload.
+ *   rn_scene_update_nodes_by_slot : rn_scene_update_nodes addressed by slot. */
+#define RN_PARENT_IS_SLOT 0x80000000u
+int rn_scene_add_nodes(rn_scene_t *scene, const rn_node_columns *cols, uint32_t count, uint32_t *out_slots);
+int rn_scene_remove_nodes(rn_scene_t *scene, const uint32_t *slots, uint32_t count);
+int rn_scene_update_nodes_by_slot(rn_scene_t *scene, const rn_node_columns *cols, const uint32_t *slots, uint32_t count);
+int rn_scene_edit_stats(const rn_scene_t *scene, uint32_t *live_nodes, uint32_t *slots_in_use, uint32_t *late_tiles, uint64_t *edits);
 
 /* rn_transform_propagate: SceneNode::UpdateInternalData + UpdateInternalTransformData for every node
  * (Source/Scene/RNSceneNode.cpp:501-546): world position/rotation/scale and the world matrix.

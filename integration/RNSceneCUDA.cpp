@@ -22,7 +22,7 @@ namespace RN
 	}
 
 	SceneCUDA::SceneCUDA(uint32 maxNodes, int device, bool strictMatrices) :
-		_scene(nullptr), _maxNodes(maxNodes), _nodeCount(0), _structureDirty(true), _fullUploads(0), _dirtyRows(0)
+		_scene(nullptr), _maxNodes(maxNodes), _nodeCount(0), _structureDirty(true), _fullUploads(0), _dirtyRows(0), _incrementalEdits(0)
 	{
 		rn_scene_desc desc;
 		memset(&desc, 0, sizeof(desc));
@@ -81,8 +81,8 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 			SceneCUDAHook *hook = new SceneCUDAHook(this);
 			node->AddAttachment(hook);
 			hook->Release();
+			_edits.push_back(Edit{true, node, 0});      // applied by the next Update / Render (rn_scene_add_nodes)
 		}
-		_structureDirty = true;
 	}
 
 	// Where a node enters the render list (SceneBasic::AddRenderNode, RNSceneBasic.cpp:652-676): the list stays sorted by
@@ -135,12 +135,16 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 				{
 					_renderNodes.Erase(node->_sceneRenderEntry);
 					_nodeCount--;
+					const uint32 slot = static_cast<SceneCUDAInfo *>(node->GetSceneInfo())->slot;
+					if(slot != 0xffffffffu)
+						_edits.push_back(Edit{false, node, slot});
+					else      // never reached the device: forget its pending addition
+						_edits.erase(std::remove_if(_edits.begin(), _edits.end(), [node](const Edit &e) { return e.add && e.node == node; }), _edits.end());
 				}
 				_dirty.erase(std::remove(_dirty.begin(), _dirty.end(), node), _dirty.end());
 				node->UpdateSceneInfo(nullptr);
 				node->_scheduledForRemovalFromScene = false;
 				node->Autorelease();
-				_structureDirty = true;
 			}
 		}
 	}
@@ -221,10 +225,92 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 			Check(rn_scene_download(_scene, RN_DL_SLOT_OF_RANK, 0, static_cast<uint32_t>(n), _slotOfRank.data()));
 			_nodeOfSlot.assign(n, nullptr);
 			for(size_t r = 0; r < n; r++)
+			{
 				_nodeOfSlot[_slotOfRank[r]] = byRank[r];
+				static_cast<SceneCUDAInfo *>(byRank[r]->GetSceneInfo())->slot = _slotOfRank[r];
+			}
 		}
+		_edits.clear();
 		_structureDirty = false;
 		_fullUploads++;
+	}
+
+	// The AddNode / RemoveNode events since the last upload, replayed in order through the incremental entry points: runs
+	// of additions with one render priority become one rn_scene_add_nodes (the library places the run where
+	// AddRenderNode's rules put it), runs of removals one rn_scene_remove_nodes.  Returns false when the library wants a
+	// full upload instead (RN_ERR_UNSUPPORTED / RN_ERR_CAPACITY) - the render list kept here is authoritative either way.
+	bool SceneCUDA::ApplyEdits()
+	{
+		size_t at = 0;
+		while(at < _edits.size())
+		{
+			size_t end = at + 1;
+			if(!_edits[at].add)
+			{
+				std::vector<uint32> slots;
+				for(end = at; end < _edits.size() && !_edits[end].add; end++)
+					slots.push_back(_edits[end].slot);
+				if(!slots.empty() && rn_scene_remove_nodes(_scene, slots.data(), static_cast<uint32_t>(slots.size())) != RN_OK)
+					return false;
+				for(uint32 slot : slots) _nodeOfSlot[slot] = nullptr;
+				_incrementalEdits++;
+				at = end;
+				continue;
+			}
+			const int32 priority = _edits[at].node->GetRenderPriority();
+			while(end < _edits.size() && _edits[end].add && _edits[end].node->GetRenderPriority() == priority) end++;
+			const size_t m = end - at;
+			_pos.resize(std::max(_pos.size(), m * 3)); _scale.resize(std::max(_scale.size(), m * 3)); _rot.resize(std::max(_rot.size(), m * 4));
+			_sphere.resize(std::max(_sphere.size(), m * 4)); _box.resize(std::max(_box.size(), m * 6));
+			_flags.resize(std::max(_flags.size(), m)); _group.resize(std::max(_group.size(), m));
+			_parent.resize(std::max(_parent.size(), m)); _prio.resize(std::max(_prio.size(), m));
+			// batch index of every node of the run, to resolve parents inside it
+			for(size_t i = 0; i < m; i++)
+				static_cast<SceneCUDAInfo *>(_edits[at + i].node->GetSceneInfo())->rank = static_cast<uint32>(i);
+			for(size_t i = 0; i < m; i++)
+			{
+				SceneNode *node = _edits[at + i].node;
+				if(!node->GetSceneInfo() || node->GetSceneInfo()->GetScene() != this) return false;
+				FillRow(node, i);
+				_prio[i] = priority;
+				SceneNode *p = node->GetParent();
+				if(!p)
+					_parent[i] = RN_NO_PARENT;
+				else
+				{
+					SceneCUDAInfo *pinfo = static_cast<SceneCUDAInfo *>(p->GetSceneInfo());
+					if(!pinfo || pinfo->GetScene() != this || p->IsKindOfClass(Camera::GetMetaClass())) return false;
+					if(pinfo->slot != 0xffffffffu) _parent[i] = RN_PARENT_IS_SLOT | pinfo->slot;
+					else if(pinfo->rank < m && _edits[at + pinfo->rank].node == p) _parent[i] = pinfo->rank;
+					else return false;
+				}
+			}
+			rn_node_columns cols;
+			memset(&cols, 0, sizeof(cols));
+			cols.position = _pos.data(); cols.scale = _scale.data(); cols.rotation = _rot.data(); cols.parent = _parent.data();
+			cols.flags = _flags.data(); cols.render_group = _group.data(); cols.bounding_sphere = _sphere.data();
+			cols.bounding_box = _box.data(); cols.render_priority = _prio.data();
+			std::vector<uint32> slots(m);
+			if(rn_scene_add_nodes(_scene, &cols, static_cast<uint32_t>(m), slots.data()) != RN_OK)
+				return false;
+			for(size_t i = 0; i < m; i++)
+			{
+				SceneNode *node = _edits[at + i].node;
+				SceneCUDAInfo *info = static_cast<SceneCUDAInfo *>(node->GetSceneInfo());
+				info->slot = slots[i];
+				info->dirty = false;
+				uint32 row = 0;
+				Check(rn_scene_download(_scene, RN_DL_RANK_OF_SLOT, slots[i], 1, &row));
+				info->rank = row;
+				if(_nodeOfSlot.size() <= slots[i]) _nodeOfSlot.resize(slots[i] + 1, nullptr);
+				_nodeOfSlot[slots[i]] = node;
+				_dirty.erase(std::remove(_dirty.begin(), _dirty.end(), node), _dirty.end());
+			}
+			_incrementalEdits++;
+			at = end;
+		}
+		_edits.clear();
+		return true;
 	}
 
 	void SceneCUDA::UploadDirty()
@@ -232,14 +318,14 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 		const size_t m = _dirty.size();
 		if(!m)
 			return;
-		std::vector<uint32> ranks(m);
+		std::vector<uint32> slots(m);
 		_pos.resize(std::max(_pos.size(), m * 3)); _scale.resize(std::max(_scale.size(), m * 3)); _rot.resize(std::max(_rot.size(), m * 4));
 		_sphere.resize(std::max(_sphere.size(), m * 4)); _box.resize(std::max(_box.size(), m * 6));
 		_flags.resize(std::max(_flags.size(), m)); _group.resize(std::max(_group.size(), m));
 		for(size_t i = 0; i < m; i++)
 		{
 			SceneCUDAInfo *info = static_cast<SceneCUDAInfo *>(_dirty[i]->GetSceneInfo());
-			ranks[i] = info->rank;
+			slots[i] = info->slot;
 			info->dirty = false;
 			FillRow(_dirty[i], i);
 		}
@@ -247,7 +333,7 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 		memset(&cols, 0, sizeof(cols));
 		cols.position = _pos.data(); cols.scale = _scale.data(); cols.rotation = _rot.data();
 		cols.flags = _flags.data(); cols.render_group = _group.data(); cols.bounding_sphere = _sphere.data();
-		Check(rn_scene_update_nodes(_scene, &cols, ranks.data(), static_cast<uint32_t>(m)));
+		Check(rn_scene_update_nodes_by_slot(_scene, &cols, slots.data(), static_cast<uint32_t>(m)));
 		_dirtyRows += m;
 		_dirty.clear();
 	}
@@ -267,7 +353,7 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 		for(IntrusiveList<Camera>::Member *m = _cameras.GetHead(); m; m = m->GetNext())
 			UpdateNode(m->Get(), delta);
 		FlushDeletionQueue();
-		if(_structureDirty)
+		if(_structureDirty || _fullUploads == 0 || !ApplyEdits())
 			UploadAll();
 		else
 			UploadDirty();
@@ -278,8 +364,8 @@ if(node->GetSceneInfo() && node->GetSceneInfo()->GetScene() == this && node->_sc
 	void SceneCUDA::Render(Renderer *renderer)
 	{
 		WillRender(renderer);
-		if(_structureDirty)
-			UploadAll();        // AddNode between Update and Render
+		if(_structureDirty || _fullUploads == 0 || !ApplyEdits())
+			UploadAll();        // AddNode / reparenting between Update and Render
 		else
 			UploadDirty();
 		for(IntrusiveList<Camera>::Member *m = _cameras.GetHead(); m; m = m->GetNext())

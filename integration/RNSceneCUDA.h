@@ -24,8 +24,9 @@ namespace RN
 	class SceneCUDAInfo : public SceneInfo
 	{
 	public:
-		SceneCUDAInfo(Scene *scene) : SceneInfo(scene), rank(0), dirty(false) {}
-		uint32 rank;     // position in the render list = row of the uploaded columns
+		SceneCUDAInfo(Scene *scene) : SceneInfo(scene), rank(0), slot(0xffffffffu), dirty(false) {}
+		uint32 rank;     // row of the node on the device (rn_scene_download addresses rows)
+		uint32 slot;     // the node's device slot: what list entries name; 0xffffffff = not on the device yet
 		bool dirty;      // local state changed since the last upload
 	};
 
@@ -62,6 +63,7 @@ namespace RN
 		size_t GetNodeCount() const { return _nodeCount; }
 		rn_scene_t *GetHandle() const { return _scene; }
 		uint64 GetFullUploads() const { return _fullUploads; }
+		uint64 GetIncrementalEdits() const { return _incrementalEdits; }
 		uint64 GetDirtyRowsUploaded() const { return _dirtyRows; }
 
 	protected:
@@ -73,6 +75,7 @@ namespace RN
 		void AddRenderNode(SceneNode *node);
 		void MarkDirty(SceneNode *node, SceneNode::ChangeSet changeSet);
 		void UploadAll();
+		bool ApplyEdits();
 		void UploadDirty();
 		void FillRow(SceneNode *node, size_t row);
 		static void Check(int status);
@@ -86,9 +89,11 @@ namespace RN
 		IntrusiveList<Camera> _cameras;          // PushFront like SceneBasic (:719)
 		std::vector<SceneNode *> _nodeOfSlot;    // device slot -> node (what a list entry refers to)
 		std::vector<uint32> _slotOfRank;
-		bool _structureDirty;
+		bool _structureDirty;                    // something happened that only a full upload can express
+		struct Edit { bool add; SceneNode *node; uint32 slot; };
+		std::vector<Edit> _edits;                // AddRenderNode / removal events since the last upload, in order
 		std::mutex _lock;
-		uint64 _fullUploads, _dirtyRows;
+		uint64 _fullUploads, _dirtyRows, _incrementalEdits;
 
 		// host staging of the node columns (rank order)
 		std::vector<float> _pos, _scale, _rot, _sphere, _box;

@@ -292,10 +292,10 @@ int main(int argc, char **argv)
 	const bool ok = listMismatch == 0 && matrixMismatch == 0;
 	printf("{\"ok\": %s, \"frames\": %u, \"nodes_created\": %zu, \"nodes_in_scene\": %zu, \"cameras\": %zu, \"list_entries_compared\": %llu, "
 	       "\"matrices_compared\": %llu, \"list_mismatches\": %llu, \"matrix_mismatches\": %llu, \"first_bad_frame\": %d, "
-	       "\"full_uploads\": %llu, \"dirty_rows_uploaded\": %llu}\n",
+	       "\"full_uploads\": %llu, \"incremental_edits\": %llu, \"dirty_rows_uploaded\": %llu}\n",
 	       ok ? "true" : "false", frames, ref.nodes.size(), cuda->GetNodeCount(), ref.cameras.size(), (unsigned long long)entries,
 	       (unsigned long long)matricesCompared, (unsigned long long)listMismatch, (unsigned long long)matrixMismatch, firstBadFrame,
-	       (unsigned long long)cuda->GetFullUploads(), (unsigned long long)cuda->GetDirtyRowsUploaded());
+	       (unsigned long long)cuda->GetFullUploads(), (unsigned long long)cuda->GetIncrementalEdits(), (unsigned long long)cuda->GetDirtyRowsUploaded());
 	fflush(stdout);
 	(void)pool;
 	_Exit(ok ? 0 : 1);

@@ -15,6 +15,7 @@ from .scenegen import CAMERA_DTYPE, EMITTER_DTYPE, Scene
 
 RN_MAX_CAMERAS = 8
 RN_NO_PARENT = 0xFFFFFFFF
+PARENT_IS_SLOT = 0x80000000
 
 DL_WORLD_POSITION, DL_WORLD_ROTATION, DL_WORLD_SCALE, DL_WORLD_MATRIX, DL_SLOT_OF_RANK, DL_RANK_OF_SLOT = range(6)
 DL_INVERSE_WORLD_MATRIX, DL_BOUNDING_SPHERE, DL_BOUNDING_BOX = 6, 7, 8
@@ -38,6 +39,7 @@ EXPORTS = [
     "rn_occlusion_set_meshes", "rn_occlusion_set_node_meshes", "rn_occlusion_reset_counters", "rn_cull_occlusion", "rn_occlusion_download",
     "rn_plan_ranges", "rn_pipeline_create", "rn_pipeline_destroy", "rn_pipeline_ranges", "rn_pipeline_update_nodes", "rn_pipeline_submit",
     "rn_pipeline_acquire", "rn_pipeline_release", "rn_frame_list", "rn_pipeline_scene",
+    "rn_scene_add_nodes", "rn_scene_remove_nodes", "rn_scene_update_nodes_by_slot", "rn_scene_edit_stats",
     "rn_group_create", "rn_group_destroy", "rn_group_info", "rn_group_update_nodes", "rn_group_frame", "rn_group_synchronize",
     "rn_group_member", "rn_group_expand", "rn_group_read_list",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
@@ -484,6 +486,34 @@ class SceneHandle:
         else:
             _check(self.lib.rn_scene_update_nodes_async(self._h, C.byref(cols), _ptr(ranks), ranks.shape[0], C.c_void_p(stream)))
 
+    def add_nodes(self, position, scale, rotation, parent, flags, group, sphere, box=None, priority=None) -> np.ndarray:
+        """rn_scene_add_nodes: the batch in AddRenderNode call order; parent = index into the batch, PARENT_IS_SLOT | slot, or
+        RN_NO_PARENT.  Returns the slots of the new nodes."""
+        keep = [_f32(position), _f32(scale), _f32(rotation), np.ascontiguousarray(parent, np.uint32), np.ascontiguousarray(flags, np.uint32),
+                np.ascontiguousarray(group, np.uint32), _f32(sphere)]
+        bx = None if box is None else _f32(box)
+        pr = None if priority is None else np.ascontiguousarray(priority, np.int32)
+        cols = NodeColumns(*[_ptr(a) for a in keep], _ptr(bx), _ptr(pr))
+        out = np.zeros(keep[3].shape[0], np.uint32)
+        _check(self.lib.rn_scene_add_nodes(self._h, C.byref(cols), C.c_uint32(out.shape[0]), _ptr(out)))
+        return out
+
+    def remove_nodes(self, slots) -> None:
+        sl = np.ascontiguousarray(slots, np.uint32)
+        _check(self.lib.rn_scene_remove_nodes(self._h, _ptr(sl), C.c_uint32(sl.shape[0])))
+
+    def update_nodes_by_slot(self, slots, position=None, scale=None, rotation=None, flags=None) -> None:
+        sl = np.ascontiguousarray(slots, np.uint32)
+        keep = [None if a is None else _f32(a) for a in (position, scale, rotation)]
+        fl = None if flags is None else np.ascontiguousarray(flags, dtype=np.uint32)
+        cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, _ptr(fl), None, None)
+        _check(self.lib.rn_scene_update_nodes_by_slot(self._h, C.byref(cols), _ptr(sl), C.c_uint32(sl.shape[0])))
+
+    def edit_stats(self) -> dict:
+        live = C.c_uint32(0); used = C.c_uint32(0); late = C.c_uint32(0); edits = C.c_uint64(0)
+        _check(self.lib.rn_scene_edit_stats(self._h, C.byref(live), C.byref(used), C.byref(late), C.byref(edits)))
+        return {"live_nodes": live.value, "slots_in_use": used.value, "late_tiles": late.value, "edits": edits.value}
+
     def update_range(self, first: int, count: int, position=None, scale=None, rotation=None) -> None:
         keep = [None if a is None else _f32(a) for a in (position, scale, rotation)]
         cols = NodeColumns(_ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2]), None, None, None, None)
@@ -646,7 +676,10 @@ class SceneHandle:
         return counts
 
     def download(self, what: int, first: int = 0, count: int | None = None) -> np.ndarray:
-        count = self.n - first if count is None else count
+        if count is None:
+            total = C.c_uint32(0)
+            _check(self.lib.rn_scene_node_count(self._h, C.byref(total)))      # grows with rn_scene_add_nodes
+            count = total.value - first
         width, dt = {DL_WORLD_POSITION: (3, np.float32), DL_WORLD_ROTATION: (4, np.float32), DL_WORLD_SCALE: (3, np.float32),
                      DL_WORLD_MATRIX: (16, np.float32), DL_SLOT_OF_RANK: (1, np.uint32), DL_RANK_OF_SLOT: (1, np.uint32),
                      DL_INVERSE_WORLD_MATRIX: (16, np.float32), DL_BOUNDING_SPHERE: (4, np.float32),

@@ -383,6 +383,13 @@ extern "C" int rn_transform_inverse(rn_scene_t *s, void *cuda_stream)
 	}
 	inverse_tile_kernel<<<(s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta, kTileThreads, smem, stream>>>(v);
 	s->launches++;
+	if(!s->late_tiles.empty())
+	{
+		// tiles added under tile-computed nodes (rn_scene_add_nodes) read their parent's inverse from memory: a second
+		// sweep, now that every other tile has written its results, makes them right (rare, so no separate tile list)
+		inverse_tile_kernel<<<(s->n_tiles + kWarpsPerCta - 1) / kWarpsPerCta, kTileThreads, smem, stream>>>(v);
+		s->launches++;
+	}
 	RN_CUDA(cudaGetLastError());
 	s->have_inverse = true;
 	return RN_OK;

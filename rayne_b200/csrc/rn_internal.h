@@ -28,6 +28,7 @@ constexpr uint32_t kTileThreads = kWarpsPerCta * 32;
 constexpr uint32_t kSuperTiles = 256;    // tiles per superblock of the compaction offsets
 constexpr uint32_t kRankShift = 16;      // c2.w bits 16-25: rank - tile start (the tile kernel stores mask bytes in RANK order)
 constexpr uint32_t kRankMask = 0x3ffu;
+constexpr uint32_t kNodeRemoved = 0x80u;          // c2.w bit 7 (unused by RN::SceneNode::Flags): the slot is a hole - rn_scene_remove_nodes
 constexpr uint32_t kParentInTile = 0x80000000u;   // c2.z: bit 31 set (and not RN_NO_PARENT) -> low bits = inner index
 
 // One tile = a contiguous range of ranks [start, start+count) stored at the same slots, permuted so that each
@@ -39,7 +40,8 @@ struct TileMeta
 	uint16_t nlev;
 	uint16_t lvl_end[kMaxSublevels];   // end offset (exclusive) of sublevel k inside the tile
 	uint16_t inner_end[kMaxSublevels]; // number of inner nodes in sublevels 1..k (sublevel 0 holds none)
-	uint32_t pad[2];
+	uint32_t late;        // 1: holds nodes whose parent is computed by another tile -> second tile launch (rn_scene_add_nodes)
+	uint32_t pad;
 };
 static_assert(sizeof(TileMeta) == 64, "TileMeta must be 64 bytes");
 
@@ -137,6 +139,20 @@ struct rn_scene
 
 	// host mirrors
 	std::vector<uint32_t> slot_of_rank, rank_of_slot;
+
+	// incremental edits (rn_scene_add_nodes / rn_scene_remove_nodes, rn_scene.cu)
+	rn::TileMeta *tiles_base = nullptr;   // the allocation `tiles` points into: [tile_front_room][n_tiles][tile_back_room]
+	uint32_t tile_head = 0;               // tiles == tiles_base + tile_head
+	uint32_t tile_capacity = 0;
+	uint32_t slot_high = 0;               // slots [0, slot_high) are in use (nodes and holes); == n
+	uint32_t live_nodes = 0;              // nodes that are not holes
+	std::vector<uint8_t> slot_state;      // per slot: bit 0 spine, bit 1 in a late tile, bit 2 removed, bit 3 in use
+	std::vector<int32_t> prio_of_slot;    // only when the upload carried render priorities
+	std::vector<std::pair<int32_t, uint32_t>> live_by_prio;   // sorted by priority: live nodes per priority
+	std::vector<uint32_t> late_tiles;     // absolute indices (into tiles_base) of the late tiles
+	uint32_t *d_late_tiles = nullptr;
+	uint32_t d_late_cap = 0;
+	uint64_t edits_fast = 0, edits_nodes = 0;
 
 	rn::ParticleStore *particles = nullptr;
 };

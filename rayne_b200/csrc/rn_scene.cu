@@ -102,6 +102,11 @@ struct SceneView
 	uint32_t *tile_counter;    // dynamic tile hand-out of the persistent tile kernel (zeroed before every launch)
 	const TileMeta *tiles;
 	uint32_t n_tiles;
+	// second ("late") launch of the tile kernel: tiles whose nodes hang under a node that another tile computes
+	// (rn_scene_add_nodes); tile_list = absolute indices into tiles_abs, nullptr in the main launch
+	const TileMeta *tiles_abs;
+	const uint32_t *tile_list;
+	uint32_t n_list, tile_head;
 	uint32_t inner_cap;        // P: parents kept in shared memory per tile
 	uint32_t warp_smem;        // bytes of shared memory per warp
 	uint32_t n;
@@ -333,8 +338,8 @@ __device__ __forceinline__ void cull_pair(const CullParams &cp, const CullTable 
 	}
 	__syncwarp();
 	const uint32_t ga = tab.group_mask[(A.fw >> 8) & 0xffu], gb = tab.group_mask[(B.fw >> 8) & 0xffu];
-	maskA = (!A.active || (A.fw & RN_NODE_HIDDEN)) ? 0u : ((A.fw & RN_NODE_NOCULLING) ? ga : (ga & fa));
-	maskB = (!B.active || (B.fw & RN_NODE_HIDDEN)) ? 0u : ((B.fw & RN_NODE_NOCULLING) ? gb : (gb & fb));
+	maskA = (!A.active || (A.fw & (RN_NODE_HIDDEN | kNodeRemoved))) ? 0u : ((A.fw & RN_NODE_NOCULLING) ? ga : (ga & fa));
+	maskB = (!B.active || (B.fw & (RN_NODE_HIDDEN | kNodeRemoved))) ? 0u : ((B.fw & RN_NODE_NOCULLING) ? gb : (gb & fb));
 }
 
 // Fills the CTA's cull table incl. the lane constants (all threads of the CTA; contains a __syncthreads).
@@ -567,8 +572,13 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 	if(CULL)
 		cull_setup(cp, tab);
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	// work items: every tile in list order (main launch) or the late tiles (second launch)
+	const bool late_launch = sv.tile_list != nullptr;
+	const uint32_t n_work = late_launch ? sv.n_list : sv.n_tiles;
+	auto meta_of = [&](uint32_t i) -> const TileMeta * { return late_launch ? sv.tiles_abs + sv.tile_list[i] : sv.tiles + i; };
+	auto count_row = [&](uint32_t i) -> uint32_t { return late_launch ? sv.tile_list[i] - sv.tile_head : i; };
 	uint32_t tile = blockIdx.x * kWarpsPerCta + warp;
-	if(tile >= sv.n_tiles)
+	if(tile >= n_work)
 		return;
 	const WarpSmem s = carve_warp_smem(smem_raw + (size_t)warp * sv.warp_smem, sv.inner_cap);
 	const uint32_t first_dynamic = gridDim.x * kWarpsPerCta;
@@ -577,7 +587,7 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 	if(lane == 0)
 		claim = atomicAdd(sv.tile_counter, 1u);
 	if(lane < sizeof(TileMeta) / 4)
-		reinterpret_cast<uint32_t *>(&s_meta[warp][0])[lane] = reinterpret_cast<const uint32_t *>(sv.tiles + tile)[lane];
+		reinterpret_cast<uint32_t *>(&s_meta[warp][0])[lane] = reinterpret_cast<const uint32_t *>(meta_of(tile))[lane];
 	if(lane == 0)
 	{
 		mbar_init(s.bar, 1);
@@ -613,6 +623,8 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 	// first pass of a tile: sublevel 0 only matters to the cull
 	auto first_pass = [&](const TileMeta &m, PassPos &p) -> bool {
 		p.lev = 0; p.j0 = 0; p.je = m.lvl_end[0];
+		if(m.late && !late_launch)
+			return false;                 // this tile belongs to the second launch
 		if(!CULL || p.je == 0)
 		{
 			p.lev = 1;
@@ -632,10 +644,10 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 		// ---- the descriptor of the next tile: load issued now, parked in the other slot after the first pass ----
 		claim = __shfl_sync(0xffffffffu, claim, 0);
 		const uint32_t next_tile = first_dynamic + claim;
-		const bool more = next_tile < sv.n_tiles;
+		const bool more = next_tile < n_work;
 		uint32_t mreg = 0;
 		if(more && lane < sizeof(TileMeta) / 4)
-			mreg = __ldg(reinterpret_cast<const uint32_t *>(sv.tiles + next_tile) + lane);
+			mreg = __ldg(reinterpret_cast<const uint32_t *>(meta_of(next_tile)) + lane);
 		if(more && lane == 0)
 			claim = atomicAdd(sv.tile_counter, 1u);
 		bool next_ready = !more;
@@ -780,8 +792,8 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 			if(first_pass(s_meta[warp][cur ^ 1u], npos) && npos.lev)
 				issue(s_meta[warp][cur ^ 1u].start + npos.j0, min(32u, npos.je - npos.j0));
 		}
-		if(CULL)
-			vis_count_store(sv, tile, vc, lane);
+		if(CULL && !(meta.late && !late_launch))
+			vis_count_store(sv, count_row(tile), vc, lane);
 		if(!more)
 			break;
 		tile = next_tile;
@@ -1029,7 +1041,7 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateView u)
 		float4 c = u.c2[slot];
 		if(u.scale) { c.x = u.scale[i * 3 + 1]; c.y = u.scale[i * 3 + 2]; }
 		uint32_t fw = __float_as_uint(c.w);
-		if(u.flags) fw = (fw & ~0xffu) | (u.flags[i] & 0xffu);
+		if(u.flags) fw = (fw & ~0x7fu) | (u.flags[i] & 0x7fu);      // bit 7 is the library's hole mark
 		if(u.group) fw = (fw & ~0xff00u) | ((u.group[i] & 0xffu) << 8);
 		c.w = __uint_as_float(fw);
 		u.c2[slot] = c;
@@ -1220,8 +1232,9 @@ static bool build_tiling(uint32_t n, const uint32_t *parent, uint32_t cap, uint3
 
 static void free_nodes(rn_scene *s)
 {
-	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->d_slot_of_rank, s->vis, s->tiles,
-	                s->tile_counts, s->super_totals, s->list_counts, s->spine_slots, s->scratch_cols};
+	void *ptrs[] = {s->c0, s->c1, s->c2, s->c3, s->wpos, s->wrot, s->wsyz, s->wmat, s->d_slot_of_rank, s->vis, s->tiles_base,
+	                s->tile_counts, s->super_totals ? s->super_totals - 8 : nullptr, s->list_counts, s->spine_slots, s->scratch_cols,
+	                s->d_late_tiles};
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
@@ -1237,6 +1250,7 @@ static void free_nodes(rn_scene *s)
 	s->wsyz = nullptr; s->d_slot_of_rank = nullptr; s->vis = nullptr; s->tiles = nullptr;
 	s->tile_counts = s->super_totals = s->list_counts = s->spine_slots = nullptr;
 	s->scratch_cols = nullptr;
+	s->tiles_base = nullptr; s->d_late_tiles = nullptr; s->d_late_cap = 0;
 }
 
 static SceneView make_view(const rn_scene *s)
@@ -1245,7 +1259,8 @@ static SceneView make_view(const rn_scene *s)
 	v.c0 = s->c0; v.c1 = s->c1; v.c2 = s->c2; v.c3 = s->c3;
 	v.wpos = s->wpos; v.wrot = s->wrot; v.wsyz = s->wsyz; v.wmat = s->wmat;
 	v.vis = s->vis; v.tiles = s->tiles; v.tile_counts = s->tile_counts; v.super_totals = s->super_totals;
-	v.tile_counter = s->super_totals + ((size_t)(s->n_tiles + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS;
+	v.tile_counter = s->super_totals - 1;       // the word in front of the totals (one memset clears both)
+	v.tiles_abs = s->tiles_base; v.tile_list = nullptr; v.n_list = 0; v.tile_head = s->tile_head;
 	v.n_tiles = s->n_tiles; v.inner_cap = s->inner_cap; v.warp_smem = warp_smem_bytes(s->inner_cap); v.n = s->n;
 	return v;
 }
@@ -1318,6 +1333,18 @@ static int launch_tiles_impl(rn_scene *s, const CullParams &cp, cudaStream_t str
 		grid = std::min<uint32_t>(grid, (uint32_t)s->sm_count * (uint32_t)persist);
 	tile_kernel<CULL, FMA, CTAS><<<grid, kTileThreads, smem, stream>>>(make_view(s), cp);
 	s->launches++;
+	if(!s->late_tiles.empty())
+	{
+		// tiles added under nodes that the launch above computes (rn_scene_add_nodes): now their parents are in memory
+		SceneView lv = make_view(s);
+		lv.tile_list = s->d_late_tiles;
+		lv.n_list = (uint32_t)s->late_tiles.size();
+		RN_CUDA(cudaMemsetAsync(s->super_totals - 1, 0, sizeof(uint32_t), stream));     // the hand-out counter only
+		const uint32_t lgrid = std::min<uint32_t>((lv.n_list + kWarpsPerCta - 1) / kWarpsPerCta,
+		                                          persist > 0 ? (uint32_t)s->sm_count * (uint32_t)persist : 0xffffffffu);
+		tile_kernel<CULL, FMA, CTAS><<<lgrid, kTileThreads, smem, stream>>>(lv, cp);
+		s->launches++;
+	}
 	if(prof)
 	{
 		RN_CUDA(cudaEventRecord(s->prof_ev[s->prof_used][1], stream));
@@ -1339,9 +1366,9 @@ static int launch_tiles(rn_scene *s, const CullParams &cp, cudaStream_t stream)
 
 int clear_super_totals(rn_scene *s, cudaStream_t stream)
 {
-	// + the tile counter of the persistent tile kernel, which lives right behind the totals
+	// + the tile counter of the persistent tile kernel, which lives right in front of the totals
 	const size_t supers = (s->n_tiles + kSuperTiles - 1) / kSuperTiles;
-	RN_CUDA(cudaMemsetAsync(s->super_totals, 0, (supers * RN_MAX_CAMERAS + 1) * sizeof(uint32_t), stream));
+	RN_CUDA(cudaMemsetAsync(s->super_totals - 1, 0, (supers * RN_MAX_CAMERAS + 1) * sizeof(uint32_t), stream));
 	return RN_OK;
 }
 
@@ -1605,15 +1632,23 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	if(s->occ_mesh_of_slot) { cudaFree(s->occ_mesh_of_slot); s->occ_mesh_of_slot = nullptr; }
 	if(s->occ_counter) { cudaFree(s->occ_counter); s->occ_counter = nullptr; }
 
-	// per-tile arrays
-	if(s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; }
+	// per-tile arrays, with room in front of and behind the tiles of this upload: rn_scene_add_nodes puts new tiles at the
+	// head or at the tail of the list without moving a byte (every spare 32 slots of max_nodes can become one tile)
+	if(s->tiles_base) { cudaFree(s->tiles_base); s->tiles_base = nullptr; s->tiles = nullptr; }
 	if(s->tile_counts) { cudaFree(s->tile_counts); s->tile_counts = nullptr; }
-	if(s->super_totals) { cudaFree(s->super_totals); s->super_totals = nullptr; }
+	if(s->super_totals) { cudaFree(s->super_totals - 8); s->super_totals = nullptr; }
 	const size_t nt = t.tiles.size();
-	int rc = dev_alloc(s, &s->tiles, nt);
-	if(!rc) rc = dev_alloc(s, &s->tile_counts, nt * RN_MAX_CAMERAS);
-	if(!rc) rc = dev_alloc(s, &s->super_totals, ((nt + kSuperTiles - 1) / kSuperTiles) * RN_MAX_CAMERAS + 1);   // + tile counter
+	const size_t spare_tiles = std::min<size_t>(((size_t)s->desc.max_nodes - count) / 32, (size_t)1 << 20);
+	const size_t room = spare_tiles ? spare_tiles + 16 : 0;
+	s->tile_capacity = (uint32_t)(nt + 2 * room);
+	s->tile_head = (uint32_t)room;
+	int rc = dev_alloc(s, &s->tiles_base, std::max<size_t>(s->tile_capacity, 1));
+	if(!rc) rc = dev_alloc(s, &s->tile_counts, std::max<size_t>(s->tile_capacity, 1) * RN_MAX_CAMERAS);
+	uint32_t *totals_alloc = nullptr;
+	if(!rc) rc = dev_alloc(s, &totals_alloc, 8 + (((size_t)s->tile_capacity + kSuperTiles - 1) / kSuperTiles + 1) * RN_MAX_CAMERAS);
 	if(rc) return rc;
+	s->super_totals = totals_alloc + 8;          // the word in front of it is the persistent kernel's tile counter
+	s->tiles = s->tiles_base + s->tile_head;
 	if(nt) RN_CUDA(cudaMemcpy(s->tiles, t.tiles.data(), sizeof(TileMeta) * nt, cudaMemcpyHostToDevice));
 
 	s->n = count;
@@ -1621,8 +1656,35 @@ static int upload_full(rn_scene *s, const rn_node_columns *cols, uint32_t count)
 	s->max_depth = t.max_depth;
 	s->spine_nodes = (uint32_t)t.spine_slots.size();
 	s->spine_level_ofs = t.spine_level_ofs;
+	// host mirrors of what the incremental edits need
+	s->slot_high = count;
+	s->live_nodes = count;
+	s->slot_state.assign(s->desc.max_nodes, 0);
+	for(uint32_t r = 0; r < count; r++)
+		s->slot_state[t.slot_of_rank[r]] = (uint8_t)(8u | (t.spine[r] ? 1u : 0u));
+	s->prio_of_slot.clear();
+	s->live_by_prio.clear();
+	if(cols->render_priority)
+	{
+		s->prio_of_slot.assign(s->desc.max_nodes, 0);
+		std::vector<int32_t> sorted(cols->render_priority, cols->render_priority + count);
+		for(uint32_t r = 0; r < count; r++) s->prio_of_slot[t.slot_of_rank[r]] = cols->render_priority[r];
+		std::sort(sorted.begin(), sorted.end());
+		for(size_t i = 0; i < sorted.size();)
+		{
+			size_t j = i;
+			while(j < sorted.size() && sorted[j] == sorted[i]) j++;
+			s->live_by_prio.push_back({sorted[i], (uint32_t)(j - i)});
+			i = j;
+		}
+	}
+	else if(count)
+		s->live_by_prio.push_back({0, count});
+	s->late_tiles.clear();
 	s->slot_of_rank.swap(t.slot_of_rank);
 	s->rank_of_slot.swap(t.rank_of_slot);
+	s->slot_of_rank.resize(s->desc.max_nodes, 0);
+	s->rank_of_slot.resize(s->desc.max_nodes, 0);
 	s->have_world = false;
 	s->last_ncams = 0;
 	s->have_masks = false;
@@ -1725,6 +1787,292 @@ extern "C" int rn_scene_update_nodes_async(rn_scene_t *s, const rn_node_columns 
 {
 	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
 	return update_scattered(s, cols, ranks, 0, count, static_cast<cudaStream_t>(cuda_stream), false);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Incremental edits: SceneBasic::AddNode / RemoveNode without re-tiling the scene.
+//
+// New nodes become NEW tiles.  A tile's slot range (and with it the range of its mask bytes) may sit anywhere in the
+// node arrays - only the ORDER of the tile array is the order of the render list - so a batch is tiled on its own, its
+// tiles take the next free slots behind the high-water mark and their descriptors are written in front of (or behind) the
+// existing ones, into the room the upload left on both sides.  Nothing that exists moves; lists (slot mode) keep naming
+// every node by the slot it always had.  Where the reference puts the batch (SceneBasic::AddRenderNode,
+// Source/Scene/RNSceneBasic.cpp:652-676): at the very front if its priority does not exceed the head's - each PushFront
+// lands before the previous one, so the batch appears in REVERSE call order -, at the very back if it is not below the
+// tail's; a position in the middle of the list is left to a full upload (RN_ERR_UNSUPPORTED).
+// A new node may hang under an existing one (AddChild on a node that is in the scene).  If that parent is computed by a
+// tile (not by the spine pre-pass) the new tile is marked `late` and runs in a second launch of the tile kernel.
+// Removed nodes become holes: bit 7 of their flags word makes every cull treat them as hidden.
+// ---------------------------------------------------------------------------------------------------------------
+static bool live_head_tail(const rn_scene *s, int32_t &head, int32_t &tail)
+{
+	bool any = false;
+	for(const auto &g : s->live_by_prio)
+	{
+		if(!g.second) continue;
+		if(!any) head = g.first;
+		tail = g.first;
+		any = true;
+	}
+	return any;
+}
+
+static void live_add(rn_scene *s, int32_t prio, int64_t delta)
+{
+	for(auto &g : s->live_by_prio)
+		if(g.first == prio) { g.second = (uint32_t)((int64_t)g.second + delta); return; }
+	s->live_by_prio.push_back({prio, (uint32_t)delta});
+	std::sort(s->live_by_prio.begin(), s->live_by_prio.end());
+}
+
+__global__ void __launch_bounds__(256) remove_kernel(float4 *c2, const uint32_t *slots, uint32_t count)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= count) return;
+	float4 c = c2[slots[i]];
+	c.w = __uint_as_float(__float_as_uint(c.w) | kNodeRemoved);
+	c2[slots[i]] = c;
+}
+
+extern "C" int rn_scene_add_nodes(rn_scene_t *s, const rn_node_columns *cols, uint32_t count, uint32_t *out_slots)
+{
+	RN_REQUIRE(s && cols && out_slots, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(cols->position && cols->scale && cols->rotation && cols->parent && cols->flags && cols->render_group && cols->bounding_sphere,
+	           RN_ERR_INVALID, "rn_scene_add_nodes needs every node column");
+	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "rn_scene_add_nodes extends an uploaded scene");
+	RN_REQUIRE(!s->list_rank_mode, RN_ERR_STATE, "incremental edits need slot lists (rn_scene_set_list_mode(scene, 0, 0)): ranks are not stable under insertion");
+	if(count == 0) return RN_OK;
+	// ---- where does the reference put this batch? one priority per batch ----
+	const int32_t prio = cols->render_priority ? cols->render_priority[0] : 0;
+	for(uint32_t i = 0; i < count; i++)
+		if((cols->render_priority ? cols->render_priority[i] : 0) != prio)
+		{ set_error("rn_scene_add_nodes: one render priority per batch (split the batch)"); return RN_ERR_UNSUPPORTED; }
+	int32_t head = 0, tail = 0;
+	const bool any = live_head_tail(s, head, tail);
+	const bool front = !any || prio <= head;
+	if(!front && prio < tail) { set_error("rn_scene_add_nodes: priority %d belongs in the middle of the render list", prio); return RN_ERR_UNSUPPORTED; }
+	uint32_t group = 0;
+	if(s->prio_group)
+	{
+		// dense priority index of the sort: the priority must be one the upload already knew
+		bool found = false;
+		std::vector<int32_t> distinct;
+		for(uint32_t slot = 0; slot < s->slot_high; slot++) if(s->slot_state[slot] & 8u) distinct.push_back(s->prio_of_slot[slot]);
+		std::sort(distinct.begin(), distinct.end());
+		distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
+		for(size_t g = 0; g < distinct.size(); g++) if(distinct[g] == prio) { group = (uint32_t)g; found = true; }
+		if(!found || distinct.size() != s->n_prio_groups) { set_error("rn_scene_add_nodes: a render priority the scene has not seen yet"); return RN_ERR_UNSUPPORTED; }
+	}
+	else if(prio != 0) { set_error("rn_scene_add_nodes: the scene was uploaded without render priorities"); return RN_ERR_UNSUPPORTED; }
+	// ---- the batch in list order (front: every PushFront lands before the previous one) ----
+	std::vector<uint32_t> seq_of(count);              // list position -> call-sequence index
+	for(uint32_t q = 0; q < count; q++) seq_of[q] = front ? count - 1 - q : q;
+	std::vector<uint32_t> pos_of(count);
+	for(uint32_t q = 0; q < count; q++) pos_of[seq_of[q]] = q;
+	std::vector<uint32_t> lparent(count);             // parent inside the batch (list position) or none, for the tiling
+	std::vector<uint32_t> ext(count, RN_NO_PARENT);   // slot of an existing parent
+	for(uint32_t q = 0; q < count; q++)
+	{
+		const uint32_t pr = cols->parent[seq_of[q]];
+		lparent[q] = RN_NO_PARENT;
+		if(pr == RN_NO_PARENT) continue;
+		if(pr & RN_PARENT_IS_SLOT)
+		{
+			const uint32_t slot = pr & ~RN_PARENT_IS_SLOT;
+			RN_REQUIRE(slot < s->slot_high && (s->slot_state[slot] & 8u) && !(s->slot_state[slot] & 4u), RN_ERR_INVALID, "node %u: parent slot %u is not a live node", seq_of[q], slot);
+			if(s->slot_state[slot] & 2u) { set_error("rn_scene_add_nodes: the parent (slot %u) was itself added under a tile-computed node", slot); return RN_ERR_UNSUPPORTED; }
+			ext[q] = slot;
+		}
+		else
+		{
+			RN_REQUIRE(pr < count && pr != seq_of[q], RN_ERR_INVALID, "node %u has an invalid parent %u", seq_of[q], pr);
+			lparent[q] = pos_of[pr];
+		}
+	}
+	Tiling t;
+	if(!build_tiling(count, lparent.data(), s->tile_cap, s->inner_cap, s->unit_cap, t))
+		return RN_ERR_INVALID;
+	if(!t.spine_slots.empty()) { set_error("rn_scene_add_nodes: a subtree of the batch does not fit a tile (%zu spine nodes)", t.spine_slots.size()); return RN_ERR_UNSUPPORTED; }
+	// ---- room? ----
+	const uint32_t k_tiles = (uint32_t)t.tiles.size();
+	uint64_t need = 0;
+	for(const TileMeta &tm : t.tiles) need += (tm.count + 31u) & ~31u;
+	const uint32_t base = (s->slot_high + 31u) & ~31u;
+	RN_REQUIRE((uint64_t)base + need <= s->desc.max_nodes, RN_ERR_CAPACITY, "%u more nodes need %llu slots, %u are free (max_nodes %u)", count,
+	           (unsigned long long)need, s->desc.max_nodes - std::min(base, s->desc.max_nodes), s->desc.max_nodes);
+	if(front) RN_REQUIRE(s->tile_head >= k_tiles, RN_ERR_CAPACITY, "no room in front of the tile list (%u tiles)", k_tiles);
+	else RN_REQUIRE(s->tile_head + s->n_tiles + k_tiles <= s->tile_capacity, RN_ERR_CAPACITY, "no room behind the tile list (%u tiles)", k_tiles);
+	RN_CUDA(cudaSetDevice(s->device));
+	RN_CUDA(cudaDeviceSynchronize());
+	// ---- pack the new slots [base, base + need) ----
+	const size_t span = (size_t)need;
+	std::vector<float4> h0(span, make_float4(0, 0, 0, 0)), h1(span, make_float4(0, 0, 0, 1)), h2(span), h3(span, make_float4(0, 0, 0, 0));
+	{
+		float none, holefw;
+		const uint32_t nopar = RN_NO_PARENT, hole = kNodeRemoved | RN_NODE_HIDDEN;
+		memcpy(&none, &nopar, 4); memcpy(&holefw, &hole, 4);
+		for(size_t i = 0; i < span; i++) h2[i] = make_float4(0, 0, none, holefw);    // padding slots are never part of a pass
+	}
+	std::vector<uint32_t> sor(span);
+	for(size_t i = 0; i < span; i++) sor[i] = base + (uint32_t)i;
+	std::vector<float4> hb0; std::vector<float2> hb1;
+	if(s->box0) { hb0.assign(span, make_float4(-1, -1, -1, 1)); hb1.assign(span, make_float2(1, 1)); }
+	std::vector<TileMeta> metas(k_tiles);
+	uint32_t at = base;
+	for(uint32_t k = 0; k < k_tiles; k++)
+	{
+		TileMeta tm = t.tiles[k];
+		const uint32_t old_start = tm.start;          // position of the tile's first node in the batch's list order
+		bool late = false;
+		for(uint32_t j = 0; j < tm.count; j++)
+		{
+			const uint32_t bslot = old_start + j;     // slot inside the batch's own tiling
+			const uint32_t q = t.rank_of_slot[bslot]; // list position
+			const uint32_t i = seq_of[q];             // the caller's index
+			const uint32_t slot = at + j;
+			const float *p = cols->position + (size_t)i * 3, *sc = cols->scale + (size_t)i * 3, *qr = cols->rotation + (size_t)i * 4,
+			            *sp = cols->bounding_sphere + (size_t)i * 4;
+			uint32_t pbits = RN_NO_PARENT;
+			if(lparent[q] != RN_NO_PARENT)
+				pbits = kParentInTile | t.inner_idx[lparent[q]];
+			else if(ext[q] != RN_NO_PARENT)
+			{
+				pbits = ext[q];
+				if(!(s->slot_state[ext[q]] & 1u)) late = true;        // computed by a tile, not by the pre-pass
+			}
+			const uint32_t fw = (cols->flags[i] & 0x7fu) | ((cols->render_group[i] & 0xffu) << 8) | ((q - old_start) << kRankShift);
+			float pf, ff;
+			memcpy(&pf, &pbits, 4); memcpy(&ff, &fw, 4);
+			const size_t o = slot - base;
+			h0[o] = make_float4(p[0], p[1], p[2], sc[0]);
+			h1[o] = make_float4(qr[0], qr[1], qr[2], qr[3]);
+			h2[o] = make_float4(sc[1], sc[2], pf, ff);
+			h3[o] = make_float4(sp[0], sp[1], sp[2], sp[3]);
+			if(s->box0 && cols->bounding_box)
+			{
+				const float *b = cols->bounding_box + (size_t)i * 6;
+				hb0[o] = make_float4(b[0], b[1], b[2], b[3]);
+				hb1[o] = make_float2(b[4], b[5]);
+			}
+			// the tile's rank range IS its slot range: the mask byte / rank -> slot entry of list position q - old_start
+			sor[(at - base) + (q - old_start)] = slot;
+			out_slots[i] = slot;
+		}
+		tm.start = at;
+		tm.late = late ? 1u : 0u;
+		metas[k] = tm;
+		at += (tm.count + 31u) & ~31u;
+	}
+	RN_CUDA(cudaMemcpy(s->c0 + base, h0.data(), sizeof(float4) * span, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c1 + base, h1.data(), sizeof(float4) * span, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c2 + base, h2.data(), sizeof(float4) * span, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->c3 + base, h3.data(), sizeof(float4) * span, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemcpy(s->d_slot_of_rank + base, sor.data(), sizeof(uint32_t) * span, cudaMemcpyHostToDevice));
+	RN_CUDA(cudaMemset(s->vis + base, 0, span));
+	if(s->box0)
+	{
+		RN_CUDA(cudaMemcpy(s->box0 + base, hb0.data(), sizeof(float4) * span, cudaMemcpyHostToDevice));
+		RN_CUDA(cudaMemcpy(s->box1 + base, hb1.data(), sizeof(float2) * span, cudaMemcpyHostToDevice));
+	}
+	if(s->prio_group) RN_CUDA(cudaMemset(s->prio_group + base, (int)group, span));
+	if(s->node_volume) RN_CUDA(cudaMemset(s->node_volume + base, 0, span));
+	if(s->lod_node_model) RN_CUDA(cudaMemset(s->lod_node_model + base, 0xff, span * sizeof(uint16_t)));
+	if(s->occ_mesh_of_slot) RN_CUDA(cudaMemset(s->occ_mesh_of_slot + base, 0xff, span * sizeof(int32_t)));
+	if(s->occ_counter) RN_CUDA(cudaMemset(s->occ_counter + base, 0, span * sizeof(uint16_t)));
+	// ---- the tile descriptors: in front of the list or behind it ----
+	const uint32_t first_abs = front ? s->tile_head - k_tiles : s->tile_head + s->n_tiles;
+	RN_CUDA(cudaMemcpy(s->tiles_base + first_abs, metas.data(), sizeof(TileMeta) * k_tiles, cudaMemcpyHostToDevice));
+	if(front) { s->tile_head -= k_tiles; s->tiles = s->tiles_base + s->tile_head; }
+	s->n_tiles += k_tiles;
+	bool new_late = false;
+	for(uint32_t k = 0; k < k_tiles; k++)
+		if(metas[k].late) { s->late_tiles.push_back(first_abs + k); new_late = true; }
+	if(new_late)
+	{
+		if(s->late_tiles.size() > s->d_late_cap)
+		{
+			if(s->d_late_tiles) cudaFree(s->d_late_tiles);
+			s->d_late_cap = (uint32_t)std::max<size_t>(s->late_tiles.size() * 2, 256);
+			int rc = dev_alloc(s, &s->d_late_tiles, s->d_late_cap);
+			if(rc) return rc;
+		}
+		RN_CUDA(cudaMemcpy(s->d_late_tiles, s->late_tiles.data(), sizeof(uint32_t) * s->late_tiles.size(), cudaMemcpyHostToDevice));
+	}
+	// ---- host mirrors ----
+	for(uint32_t k = 0; k < k_tiles; k++)
+		for(uint32_t j = 0; j < metas[k].count; j++)
+		{
+			const uint32_t slot = metas[k].start + j;
+			s->slot_state[slot] = (uint8_t)(8u | (metas[k].late ? 2u : 0u));
+			if(!s->prio_of_slot.empty()) s->prio_of_slot[slot] = prio;
+		}
+	for(size_t i = 0; i < span; i++)
+	{
+		s->slot_of_rank[base + i] = sor[i];
+		s->rank_of_slot[sor[i]] = base + (uint32_t)i;
+	}
+	s->slot_high = base + (uint32_t)need;
+	s->n = s->slot_high;
+	s->live_nodes += count;
+	live_add(s, prio, (int64_t)count);
+	s->have_world = false;
+	s->have_inverse = s->have_bounds = s->have_masks = false;
+	s->last_ncams = 0;
+	s->edits_fast++;
+	s->edits_nodes += count;
+	return RN_OK;
+}
+
+extern "C" int rn_scene_remove_nodes(rn_scene_t *s, const uint32_t *slots, uint32_t count)
+{
+	RN_REQUIRE(s && (slots || count == 0), RN_ERR_INVALID, "NULL argument");
+	if(count == 0) return RN_OK;
+	for(uint32_t i = 0; i < count; i++)
+		RN_REQUIRE(slots[i] < s->slot_high && (s->slot_state[slots[i]] & 8u) && !(s->slot_state[slots[i]] & 4u), RN_ERR_INVALID,
+		           "slot %u is not a live node", slots[i]);
+	RN_CUDA(cudaSetDevice(s->device));
+	uint32_t *d = nullptr;
+	RN_CUDA(cudaMalloc(reinterpret_cast<void **>(&d), sizeof(uint32_t) * count));
+	cudaError_t e = cudaMemcpy(d, slots, sizeof(uint32_t) * count, cudaMemcpyHostToDevice);
+	if(e == cudaSuccess)
+	{
+		remove_kernel<<<(count + 255) / 256, 256>>>(s->c2, d, count);
+		e = cudaDeviceSynchronize();
+	}
+	cudaFree(d);
+	if(e != cudaSuccess) return cuda_fail(e, "rn_scene_remove_nodes", __FILE__, __LINE__);
+	s->launches++;
+	for(uint32_t i = 0; i < count; i++)
+	{
+		s->slot_state[slots[i]] |= 4u;
+		live_add(s, s->prio_of_slot.empty() ? 0 : s->prio_of_slot[slots[i]], -1);
+	}
+	s->live_nodes -= count;
+	s->edits_fast++;
+	s->edits_nodes += count;
+	return RN_OK;
+}
+
+extern "C" int rn_scene_update_nodes_by_slot(rn_scene_t *s, const rn_node_columns *cols, const uint32_t *slots, uint32_t count)
+{
+	RN_REQUIRE(s && cols && (slots || count == 0), RN_ERR_INVALID, "NULL argument");
+	std::vector<uint32_t> ranks(count);
+	for(uint32_t i = 0; i < count; i++)
+	{
+		RN_REQUIRE(slots[i] < s->slot_high && (s->slot_state[slots[i]] & 8u), RN_ERR_INVALID, "slot %u is not a node", slots[i]);
+		ranks[i] = s->rank_of_slot[slots[i]];
+	}
+	return update_scattered(s, cols, ranks.data(), 0, count);
+}
+
+extern "C" int rn_scene_edit_stats(const rn_scene_t *s, uint32_t *live_nodes, uint32_t *slots_in_use, uint32_t *late_tiles, uint64_t *edits)
+{
+	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
+	if(live_nodes) *live_nodes = s->live_nodes;
+	if(slots_in_use) *slots_in_use = s->slot_high;
+	if(late_tiles) *late_tiles = (uint32_t)s->late_tiles.size();
+	if(edits) *edits = s->edits_fast;
+	return RN_OK;
 }
 
 extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)

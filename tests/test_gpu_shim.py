@@ -24,4 +24,6 @@ def test_scene_cuda_matches_scene_basic(roots, frames):
     assert r.returncode == 0 and out["ok"], out
     assert out["list_mismatches"] == 0 and out["matrix_mismatches"] == 0
     assert out["list_entries_compared"] > 1000 and out["matrices_compared"] > roots * frames
-    assert out["dirty_rows_uploaded"] > 0           # frames without a hierarchy change went through rn_scene_update_nodes
+    assert out["dirty_rows_uploaded"] > 0           # frames without a hierarchy change went through rn_scene_update_nodes_by_slot
+    assert out["incremental_edits"] > 0             # AddNode / RemoveNode went through rn_scene_add_nodes / rn_scene_remove_nodes
+    assert out["full_uploads"] < frames             # ... and only reparenting / priority changes re-uploaded the scene
