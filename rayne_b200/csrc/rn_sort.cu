@@ -14,19 +14,22 @@
 // digit looked up through the entry (dense index of the node's render priority, built at upload).  Stable means
 // equal keys keep render-list order - one of the outcomes std::sort permits.
 //
-// Per pass: histogram (one 2048-entry block per CTA) -> per-digit exclusive scan over the blocks -> scatter with an
-// in-block stable rank (match.any per 32 consecutive entries + per-warp digit counters in shared memory).
-// HBM-bound in principle: 16 B per entry and pass (key + entry read and written) + the scattered writes.
+// The digit totals of all passes are counted while the keys are built; every pass is then ONE kernel (one sweep): tile
+// ticket, in-block stable rank (match.any per 32 consecutive entries + per-warp digit counters in shared memory),
+// decoupled look-back over the earlier tiles' digit counts, reorder through shared memory, coalesced stores.
+// HBM-bound in principle: 16 B per entry and pass (key + entry read once and written once).
 #include "rn_internal.h"
 
+#include <algorithm>
 #include <cstring>
 
 namespace rn {
 
 constexpr uint32_t kSortThreads = 256;
-constexpr uint32_t kSortItems = 8;
-constexpr uint32_t kSortTile = kSortThreads * kSortItems;   // 2048 entries per CTA
+constexpr uint32_t kSortItems = 16;
+constexpr uint32_t kSortTile = kSortThreads * kSortItems;   // 4096 entries per CTA
 constexpr uint32_t kSortWarps = kSortThreads / 32;
+constexpr uint32_t kSortDigits = 5;                         // four key bytes + the render-priority digit
 
 struct SortView
 {
@@ -36,8 +39,10 @@ struct SortView
 	uint32_t *list;                 // the camera's visibility list
 	const uint32_t *list_count;
 	uint32_t *range;                // [2]: begin, end of the current sort
-	uint32_t *keys[2], *vals[2];
-	uint32_t *hist;                 // [256][nb_max] block histograms, then [256] digit totals
+	uint2 *kv[2];                   // (key, entry) pairs, ping-pong: one 8-byte store per entry keeps a digit run contiguous
+	uint32_t *ghist;                // [kSortDigits][256] digit totals of the range, then [kSortDigits][256] their exclusive scans
+	uint32_t *ticket;               // [kSortDigits] tile hand-out counters, one per pass
+	uint32_t *status;               // [tiles][256] decoupled look-back words of the running pass
 	uint32_t nb_max;
 	uint32_t rank_mode, rank_offset;
 	uint32_t transparent_group, first_sky_group;
@@ -89,25 +94,78 @@ __global__ void sort_range_close_kernel(SortView v)
 	else { v.range[0] = 0; v.range[1] = 0; }
 }
 
-// keys + entries of the range into the scratch arrays.  DESC = back to front.
+// keys + entries of the range into the scratch arrays, and the digit histograms of ALL passes in the same sweep (they do
+// not depend on the order of the entries).  DESC = back to front.  Persistent grid, shared-memory histograms.
 template <bool DESC>
-__global__ void __launch_bounds__(256) sort_build_kernel(SortView v)
+__global__ void __launch_bounds__(256) sort_build_kernel(SortView v, uint32_t with_priority)
 {
-	const uint32_t begin = v.range[0], end = v.range[1];
-	const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-	if(e >= end - begin)
-		return;
-	const uint32_t entry = v.list[begin + e];
-	const float4 p = v.wpos[entry_slot(v, entry)];
-	// (a - b).GetDotProduct(a - b): x*x + y*y + z*z, separately rounded (-fmad=false)
-	const float dx = p.x - v.cam[0], dy = p.y - v.cam[1], dz = p.z - v.cam[2];
-	uint32_t key = __float_as_uint(dx * dx + dy * dy + dz * dz);
-	if(DESC)
-		key = ~key;
-	else if(entry_group(v, entry) >= v.first_sky_group)
-		key = 0;   // priorities >= RenderSky compare equal inside their priority (RNSceneBasic.cpp:601-605)
-	v.keys[0][e] = key;
-	v.vals[0][e] = entry;
+	__shared__ uint32_t h[kSortDigits][256];
+	for(uint32_t i = threadIdx.x; i < kSortDigits * 256; i += blockDim.x) (&h[0][0])[i] = 0;
+	__syncthreads();
+	const uint32_t begin = v.range[0], m = v.range[1] - v.range[0];
+	for(uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < m; e += gridDim.x * blockDim.x)
+	{
+		const uint32_t entry = v.list[begin + e];
+		const float4 p = v.wpos[entry_slot(v, entry)];
+		// (a - b).GetDotProduct(a - b): x*x + y*y + z*z, separately rounded (-fmad=false)
+		const float dx = p.x - v.cam[0], dy = p.y - v.cam[1], dz = p.z - v.cam[2];
+		uint32_t key = __float_as_uint(dx * dx + dy * dy + dz * dz);
+		uint32_t g = 0;
+		if(DESC)
+			key = ~key;
+		else
+		{
+			g = entry_group(v, entry);
+			if(g >= v.first_sky_group)
+				key = 0;   // priorities >= RenderSky compare equal inside their priority (RNSceneBasic.cpp:601-605)
+		}
+		v.kv[0][e] = make_uint2(key, entry);
+		atomicAdd(&h[0][key & 255u], 1u);
+		atomicAdd(&h[1][(key >> 8) & 255u], 1u);
+		// the upper digits take few values (exponent bits, a handful of priorities): count warp-wide, one atomic per value
+		const uint32_t act = __activemask();
+		{
+			const uint32_t d = (key >> 16) & 255u, peers = __match_any_sync(act, d);
+			if((uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31u)) atomicAdd(&h[2][d], __popc(peers));
+		}
+		{
+			const uint32_t d = key >> 24, peers = __match_any_sync(act, d);
+			if((uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31u)) atomicAdd(&h[3][d], __popc(peers));
+		}
+		if(with_priority)
+		{
+			const uint32_t peers = __match_any_sync(act, g);
+			if((uint32_t)(__ffs(peers) - 1) == (threadIdx.x & 31u)) atomicAdd(&h[4][g], __popc(peers));
+		}
+	}
+	__syncthreads();
+	for(uint32_t i = threadIdx.x; i < kSortDigits * 256; i += blockDim.x)
+	{
+		const uint32_t c = (&h[0][0])[i];
+		if(c) atomicAdd(&v.ghist[i], c);
+	}
+}
+
+// exclusive scan of every pass's 256 digit totals (one warp per pass)
+__global__ void __launch_bounds__(32 * kSortDigits) sort_prefix_kernel(SortView v)
+{
+	const uint32_t lane = threadIdx.x & 31u, pass = threadIdx.x >> 5;
+	const uint32_t *src = v.ghist + pass * 256u;
+	uint32_t *dst = v.ghist + (kSortDigits + pass) * 256u;
+	uint32_t carry = 0;
+	for(uint32_t b = 0; b < 256; b += 32)
+	{
+		const uint32_t x = src[b + lane];
+		uint32_t s = x;
+#pragma unroll
+		for(int o = 1; o < 32; o <<= 1)
+		{
+			const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
+			if(lane >= (uint32_t)o) s += y;
+		}
+		dst[b + lane] = carry + s - x;
+		carry += __shfl_sync(0xffffffffu, s, 31);
+	}
 }
 
 struct PassArgs
@@ -115,6 +173,7 @@ struct PassArgs
 	uint32_t src;      // 0 / 1: which scratch pair is read
 	uint32_t shift;    // bit offset of the digit inside the key; 32 = the priority digit
 	uint32_t last;     // 1: final pass - the entries go straight back into the list, the keys are dropped
+	uint32_t pass;     // histogram row / ticket of this pass
 };
 
 __device__ __forceinline__ uint32_t digit_of(const SortView &v, const PassArgs &a, uint32_t key, uint32_t val)
@@ -122,125 +181,65 @@ __device__ __forceinline__ uint32_t digit_of(const SortView &v, const PassArgs &
 	return a.shift < 32 ? (key >> a.shift) & 255u : entry_group(v, val);
 }
 
-__global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(SortView v, PassArgs a)
-{
-	__shared__ uint32_t h[256];
-	const uint32_t m = v.range[1] - v.range[0];
-	const uint32_t nb = (m + kSortTile - 1) / kSortTile;
-	if(blockIdx.x >= nb)
-		return;
-	h[threadIdx.x] = 0;
-	__syncthreads();
-	const uint32_t base = blockIdx.x * kSortTile;
-	const uint32_t *keys = a.src ? v.keys[1] : v.keys[0], *vals = a.src ? v.vals[1] : v.vals[0];
-#pragma unroll
-	for(uint32_t i = 0; i < kSortItems; i++)
-	{
-		const uint32_t e = base + i * kSortThreads + threadIdx.x;
-		if(e < m)
-			atomicAdd(&h[digit_of(v, a, keys[e], a.shift < 32 ? 0u : vals[e])], 1u);
-	}
-	__syncthreads();
-	v.hist[threadIdx.x * v.nb_max + blockIdx.x] = h[threadIdx.x];
-}
-
-// One CTA per digit: exclusive scan of that digit's block counts, total behind the table.
-__global__ void __launch_bounds__(256) sort_scan_kernel(SortView v)
-{
-	__shared__ uint32_t warp_sum[8];
-	__shared__ uint32_t carry_s;
-	const uint32_t m = v.range[1] - v.range[0];
-	const uint32_t nb = (m + kSortTile - 1) / kSortTile;
-	uint32_t *row = v.hist + (size_t)blockIdx.x * v.nb_max;
-	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-	if(threadIdx.x == 0) carry_s = 0;
-	__syncthreads();
-	for(uint32_t b0 = 0; b0 < nb; b0 += 256)
-	{
-		const uint32_t b = b0 + threadIdx.x;
-		const uint32_t x = b < nb ? row[b] : 0u;
-		uint32_t s = x;
-#pragma unroll
-		for(int o = 1; o < 32; o <<= 1)
-		{
-			const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
-			if(lane >= (uint32_t)o) s += y;
-		}
-		if(lane == 31) warp_sum[warp] = s;
-		__syncthreads();
-		uint32_t before = carry_s;
-		for(uint32_t w = 0; w < warp; w++) before += warp_sum[w];
-		if(b < nb) row[b] = before + s - x;
-		__syncthreads();
-		if(threadIdx.x == 255) carry_s = before + s;
-		__syncthreads();
-	}
-	if(threadIdx.x == 0)
-		v.hist[(size_t)256 * v.nb_max + blockIdx.x] = carry_s;
-}
-
-__global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, PassArgs a)
+// One pass of the LSD radix sort in ONE kernel ("one sweep"): a CTA takes the next tile of 4 096 entries (ticket), ranks
+// them by digit (stable: warp w owns entries [512 w, 512 w + 512) of the tile, 32 consecutive entries per round, match.any
+// + per-warp digit counters), publishes its 256 digit counts and finds the counts of all earlier tiles by decoupled
+// look-back (thread d follows digit d: status word = 2 flag bits + 30 count bits; 1 = this tile's count, 2 = inclusive
+// prefix), then writes the tile reordered by digit so that consecutive threads store to consecutive addresses.
+// 16 bytes per entry and pass move through HBM - the keys and entries are read once and written once.
+__global__ void __launch_bounds__(kSortThreads) sort_onesweep_kernel(SortView v, PassArgs a)
 {
 	__shared__ uint32_t wcount[kSortWarps][256];
 	__shared__ uint32_t dbase[256];
 	__shared__ uint32_t lpre[256];
 	__shared__ uint32_t wsum[8];
-	__shared__ uint32_t s_valid;
-	__shared__ uint32_t s_key[kSortTile], s_val[kSortTile];
+	__shared__ uint32_t s_valid, s_tile;
+	__shared__ uint2 s_kv[kSortTile];
 	__shared__ uint8_t s_dig[kSortTile];
 	const uint32_t m = v.range[1] - v.range[0];
 	const uint32_t nb = (m + kSortTile - 1) / kSortTile;
-	if(blockIdx.x >= nb)
-		return;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	if(threadIdx.x == 0)
+		s_tile = atomicAdd(&v.ticket[a.pass], 1u);
 	for(uint32_t i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads)
 		(&wcount[0][0])[i] = 0;
-	// exclusive scan of the 256 digit totals -> first output index of every digit
-	{
-		const uint32_t x = v.hist[(size_t)256 * v.nb_max + threadIdx.x];
-		uint32_t s = x;
-#pragma unroll
-		for(int o = 1; o < 32; o <<= 1)
-		{
-			const uint32_t y = __shfl_up_sync(0xffffffffu, s, o);
-			if(lane >= (uint32_t)o) s += y;
-		}
-		if(lane == 31) wsum[warp] = s;
-		__syncthreads();
-		uint32_t before = 0;
-		for(uint32_t w = 0; w < warp; w++) before += wsum[w];
-		dbase[threadIdx.x] = before + s - x + v.hist[(size_t)threadIdx.x * v.nb_max + blockIdx.x];
-	}
 	__syncthreads();
+	const uint32_t tile = s_tile;
+	if(tile >= nb)
+		return;
 	// selects, not v.keys[a.src]: a dynamically indexed kernel parameter is copied to local memory by every thread
-	const uint32_t *keys = a.src ? v.keys[1] : v.keys[0], *vals = a.src ? v.vals[1] : v.vals[0];
-	uint32_t *okeys = a.src ? v.keys[0] : v.keys[1];
-	uint32_t *ovals = a.last ? v.list + v.range[0] : (a.src ? v.vals[0] : v.vals[1]);
-	// warp w owns entries [w*256, (w+1)*256) of the block, 32 consecutive entries per round: stable inside the warp
-	const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32u);
-	uint32_t key[kSortItems], val[kSortItems], dig[kSortItems], rank[kSortItems];
+	const uint2 *__restrict__ kv = a.src ? v.kv[1] : v.kv[0];
+	uint2 *__restrict__ okv = a.src ? v.kv[0] : v.kv[1];
+	uint32_t *__restrict__ olist = v.list + v.range[0];
+	const uint32_t wbase = tile * kSortTile + warp * (kSortItems * 32u);
+	uint32_t key[kSortItems], val[kSortItems], dr[kSortItems];     // dr = digit | rank inside the warp's digit run << 8
 #pragma unroll
 	for(uint32_t r = 0; r < kSortItems; r++)
 	{
 		const uint32_t e = wbase + r * 32u + lane;
-		const bool valid = e < m;
-		key[r] = valid ? keys[e] : 0u;
-		val[r] = valid ? vals[e] : 0u;
-		dig[r] = valid ? digit_of(v, a, key[r], val[r]) : 0xffffu;
-		const uint32_t peers = __match_any_sync(0xffffffffu, dig[r]);
+		const uint2 x = e < m ? __ldg(kv + e) : make_uint2(0u, 0u);
+		key[r] = x.x;
+		val[r] = x.y;
+	}
+#pragma unroll
+	for(uint32_t r = 0; r < kSortItems; r++)
+	{
+		const bool valid = wbase + r * 32u + lane < m;
+		const uint32_t dig = valid ? digit_of(v, a, key[r], val[r]) : 0xffffu;
+		const uint32_t peers = __match_any_sync(0xffffffffu, dig);
 		const uint32_t leader = __ffs(peers) - 1u;
 		uint32_t base = 0;
 		if(valid && lane == leader)
 		{
-			base = wcount[warp][dig[r]];
-			wcount[warp][dig[r]] = base + __popc(peers);
+			base = wcount[warp][dig];
+			wcount[warp][dig] = base + __popc(peers);
 		}
 		base = __shfl_sync(0xffffffffu, base, leader);
-		rank[r] = base + __popc(peers & ((1u << lane) - 1u));
+		dr[r] = valid ? (dig | ((base + __popc(peers & ((1u << lane) - 1u))) << 8)) : 0xffffffffu;
 		__syncwarp();
 	}
 	__syncthreads();
-	// per digit: exclusive prefix over the warps (thread = digit); `run` ends as the digit's total in this block
+	// per digit (thread = digit): exclusive prefix over the warps; `run` ends as the digit's count in this tile
 	uint32_t run = 0;
 #pragma unroll
 	for(uint32_t w = 0; w < kSortWarps; w++)
@@ -248,6 +247,39 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		const uint32_t t = wcount[w][threadIdx.x];
 		wcount[w][threadIdx.x] = run;
 		run += t;
+	}
+	// decoupled look-back: the number of entries with this digit in all earlier tiles
+	{
+		volatile uint32_t *status = v.status;
+		const uint32_t d = threadIdx.x;
+		uint32_t excl = 0;
+		if(tile > 0)
+		{
+			status[(size_t)tile * 256u + d] = (1u << 30) | run;
+			// walk back eight tiles at a time: the eight loads are in flight together, so a window of several hundred
+			// concurrently running tiles costs a few dozen round trips instead of one per tile
+			int64_t t = (int64_t)tile - 1;
+			bool done = false;
+			while(!done)
+			{
+				uint32_t sv[8];
+#pragma unroll
+				for(int k = 0; k < 8; k++)
+					sv[k] = t - k >= 0 ? status[(size_t)(t - k) * 256u + d] : (2u << 30);
+#pragma unroll
+				for(int k = 0; k < 8; k++)
+				{
+					if(done) break;
+					uint32_t x = sv[k];
+					while((x >> 30) == 0u) x = status[(size_t)(t - k) * 256u + d];     // not published yet: wait for this one
+					excl += x & 0x3fffffffu;
+					if((x >> 30) == 2u) done = true;
+				}
+				t -= 8;
+			}
+		}
+		status[(size_t)tile * 256u + d] = (2u << 30) | (excl + run);
+		dbase[d] = v.ghist[(kSortDigits + a.pass) * 256u + d] + excl;
 	}
 	// block-local exclusive prefix over the digits: where a digit's run starts in the reordered tile
 	{
@@ -266,17 +298,15 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		if(threadIdx.x == kSortThreads - 1) s_valid = before + sc;
 	}
 	__syncthreads();
-	// reorder through shared memory, then write digit runs with consecutive threads on consecutive addresses
-	// (a thread-per-entry scatter leaves 32 partial sectors per store instruction)
 #pragma unroll
 	for(uint32_t r = 0; r < kSortItems; r++)
 	{
-		if(dig[r] != 0xffffu)
+		if(dr[r] != 0xffffffffu)
 		{
-			const uint32_t lp = lpre[dig[r]] + wcount[warp][dig[r]] + rank[r];
-			s_key[lp] = key[r];
-			s_val[lp] = val[r];
-			s_dig[lp] = (uint8_t)dig[r];
+			const uint32_t dig = dr[r] & 255u;
+			const uint32_t lp = lpre[dig] + wcount[warp][dig] + (dr[r] >> 8);
+			s_kv[lp] = make_uint2(key[r], val[r]);
+			s_dig[lp] = (uint8_t)dig;
 		}
 	}
 	__syncthreads();
@@ -289,8 +319,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(SortView v, 
 		{
 			const uint32_t d = s_dig[idx];
 			const uint32_t dst = dbase[d] + (idx - lpre[d]);
-			if(!a.last) okeys[dst] = s_key[idx];
-			ovals[dst] = s_val[idx];
+			if(a.last) olist[dst] = s_kv[idx].y;
+			else okv[dst] = s_kv[idx];
 		}
 	}
 }
@@ -300,19 +330,21 @@ static int run_passes(rn_scene *s, const SortView &v, bool with_priority_digit, 
 	const uint32_t grid_tiles = (s->n + kSortTile - 1) / kSortTile;
 	uint32_t src = 0;
 	const uint32_t n_pass = with_priority_digit ? 5u : 4u;
+	sort_prefix_kernel<<<1, 32 * kSortDigits, 0, stream>>>(v);
+	s->launches++;
 	for(uint32_t p = 0; p < n_pass; p++)
 	{
 		PassArgs a;
 		a.src = src;
 		a.shift = p * 8u;
 		a.last = p + 1 == n_pass ? 1u : 0u;
-		sort_hist_kernel<<<grid_tiles, kSortThreads, 0, stream>>>(v, a);
-		sort_scan_kernel<<<256, 256, 0, stream>>>(v);
-		sort_scatter_kernel<<<grid_tiles, kSortThreads, 0, stream>>>(v, a);
-		s->launches += 3;
+		a.pass = p;
+		RN_CUDA(cudaMemsetAsync(v.status, 0, (size_t)grid_tiles * 256u * sizeof(uint32_t), stream));
+		sort_onesweep_kernel<<<grid_tiles, kSortThreads, 0, stream>>>(v, a);
+		s->launches++;
 		src ^= 1u;
 	}
-	// no write-back pass: the last scatter wrote the entries straight into the list
+	// no write-back pass: the last sweep wrote the entries straight into the list
 	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
@@ -329,6 +361,7 @@ extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, 
 	RN_CUDA(cudaSetDevice(s->device));
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
 	const uint32_t nb_max = (s->desc.max_nodes + kSortTile - 1) / kSortTile;
+	RN_REQUIRE(s->desc.max_nodes < (1u << 30), RN_ERR_CAPACITY, "rn_cull_sort handles lists below 2^30 entries");
 	bool any = false;
 	for(uint32_t c = 0; c < n_cameras; c++)
 	{
@@ -341,11 +374,15 @@ extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, 
 	if(!s->sort_scratch)
 	{
 		int rc = dev_alloc(s, &s->sort_scratch, (size_t)s->desc.max_nodes * 4);
-		if(!rc) rc = dev_alloc(s, &s->sort_hist, (size_t)256 * nb_max + 256);
+		// look-back status words of one pass + digit totals and their scans + the passes' tile tickets
+		if(!rc) rc = dev_alloc(s, &s->sort_hist, (size_t)256 * nb_max + 2 * kSortDigits * 256 + 8);
 		if(!rc) rc = dev_alloc(s, &s->sort_ranges, (size_t)RN_MAX_CAMERAS * 2);
 		if(rc) return rc;
 	}
 	const uint32_t grid_flat = (s->n + 255) / 256;
+	if(!s->sm_count)
+		RN_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, s->device));
+	const uint32_t grid_build = std::max(1u, std::min(grid_flat, (uint32_t)s->sm_count * 8u));
 	for(uint32_t c = 0; c < n_cameras; c++)
 	{
 		const uint32_t f = s->last_cam_flags[c];
@@ -358,9 +395,11 @@ extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, 
 		v.list_count = s->list_counts + c;
 		v.range = s->sort_ranges + 2 * c;
 		const size_t cap = s->desc.max_nodes;
-		v.keys[0] = s->sort_scratch; v.vals[0] = s->sort_scratch + cap;
-		v.keys[1] = s->sort_scratch + 2 * cap; v.vals[1] = s->sort_scratch + 3 * cap;
-		v.hist = s->sort_hist;
+		v.kv[0] = reinterpret_cast<uint2 *>(s->sort_scratch);
+		v.kv[1] = reinterpret_cast<uint2 *>(s->sort_scratch) + cap;
+		v.status = s->sort_hist;
+		v.ghist = s->sort_hist + (size_t)256 * nb_max;
+		v.ticket = v.ghist + 2 * kSortDigits * 256;
 		v.nb_max = nb_max;
 		v.rank_mode = s->list_rank_mode;
 		v.rank_offset = s->list_rank_offset;
@@ -369,10 +408,12 @@ extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, 
 		memcpy(v.cam, camera_world_positions + 3 * c, sizeof(float) * 3);
 		if(f & RN_CAMERA_SORT_FRONT_TO_BACK)
 		{
+			const bool with_prio = s->n_prio_groups > 1;
 			sort_range_all_kernel<<<1, 1, 0, stream>>>(v);
-			sort_build_kernel<false><<<grid_flat, 256, 0, stream>>>(v);
+			RN_CUDA(cudaMemsetAsync(v.ghist, 0, (2 * kSortDigits * 256 + 8) * sizeof(uint32_t), stream));
+			sort_build_kernel<false><<<grid_build, 256, 0, stream>>>(v, with_prio ? 1u : 0u);
 			s->launches += 2;
-			int rc = run_passes(s, v, s->n_prio_groups > 1, stream);
+			int rc = run_passes(s, v, with_prio, stream);
 			if(rc) return rc;
 		}
 		if((f & RN_CAMERA_SORT_TRANSPARENT_BACK_TO_FRONT) && s->transparent_group != 0xffffffffu)
@@ -380,7 +421,8 @@ extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, 
 			sort_range_reset_kernel<<<1, 1, 0, stream>>>(v);
 			sort_range_scan_kernel<<<grid_flat, 256, 0, stream>>>(v);
 			sort_range_close_kernel<<<1, 1, 0, stream>>>(v);
-			sort_build_kernel<true><<<grid_flat, 256, 0, stream>>>(v);
+			RN_CUDA(cudaMemsetAsync(v.ghist, 0, (2 * kSortDigits * 256 + 8) * sizeof(uint32_t), stream));
+			sort_build_kernel<true><<<grid_build, 256, 0, stream>>>(v, 0u);
 			s->launches += 4;
 			int rc = run_passes(s, v, false, stream);
 			if(rc) return rc;
