@@ -357,6 +357,7 @@ using namespace rn;
 
 extern "C" int rn_transform_inverse(rn_scene_t *s, void *cuda_stream)
 {
+	RN_RANGE("rn_transform_inverse");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	RN_CUDA(cudaSetDevice(s->device));
@@ -397,6 +398,7 @@ extern "C" int rn_transform_inverse(rn_scene_t *s, void *cuda_stream)
 
 extern "C" int rn_bounds_update(rn_scene_t *s, void *cuda_stream)
 {
+	RN_RANGE("rn_bounds_update");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	RN_REQUIRE(s->have_world, RN_ERR_STATE, "rn_bounds_update needs world transforms: call rn_transform_propagate / rn_transform_cull first");

@@ -414,6 +414,7 @@ extern "C" int rn_group_update_nodes(rn_group_t *g, const rn_node_columns *cols,
 // preparation) sees the whole scene's visibility.
 extern "C" int rn_group_frame(rn_group_t *g, const rn_camera_frustum *cameras, uint32_t n_cameras)
 {
+	RN_RANGE("rn_group_frame");
 	RN_REQUIRE(g && cameras, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(n_cameras >= 1 && n_cameras <= RN_MAX_CAMERAS, RN_ERR_INVALID, "n_cameras must be 1..%d", RN_MAX_CAMERAS);
 	const uint32_t n = g->n_dev;
@@ -489,6 +490,7 @@ extern "C" int rn_group_member(rn_group_t *g, uint32_t member, rn_scene_t **scen
 extern "C" int rn_group_expand(rn_group_t *g, uint32_t member, uint32_t camera, uint32_t *device_list, uint32_t capacity, uint32_t *device_count,
                                const uint32_t **out_list, const uint32_t **out_count)
 {
+	RN_RANGE("rn_group_expand");
 	RN_REQUIRE(g && member < g->n_dev, RN_ERR_INVALID, "bad member index");
 	RN_REQUIRE(camera < g->last_ncams, RN_ERR_STATE, "camera %u was not part of the last frame (%u cameras)", camera, g->last_ncams);
 	GroupMember &m = g->dev[member];

@@ -178,6 +178,7 @@ extern "C" int rn_cull_select_lod(rn_scene_t *s, uint32_t camera, const float *l
 extern "C" int rn_cull_pack_instances(rn_scene_t *s, uint32_t camera, const float *view, const float *proj_view,
                                       void *device_out, uint32_t capacity, void *cuda_stream)
 {
+	RN_RANGE("rn_cull_pack_instances");
 	RN_REQUIRE(s && view && proj_view && device_out, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_pack_instances needs the lists of a cull");
 	RN_REQUIRE(camera < s->last_ncams, RN_ERR_INVALID, "camera %u of %u", camera, s->last_ncams);

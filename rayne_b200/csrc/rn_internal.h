@@ -2,6 +2,7 @@
 #pragma once
 #include "../../include/rn_cuda.h"
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include <string>
 #include <vector>
@@ -21,6 +22,15 @@ int cuda_fail(cudaError_t err, const char *what, const char *file, int line);
 	do {                                                                               \
 		if(!(cond)) { rn::set_error(__VA_ARGS__); return (status); }                   \
 	} while(0)
+
+// NVTX range around a C-ABI call (header-only NVTX 3: a no-op unless a profiler is attached) - the counterpart of the
+// reference's own frame markers
+struct NvtxRange
+{
+	explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+	~NvtxRange() { nvtxRangePop(); }
+};
+#define RN_RANGE(name) rn::NvtxRange rn_nvtx_range__(name)
 
 constexpr uint32_t kMaxSublevels = 12;   // sublevel 0 = spine nodes of the tile, 1.. = depth inside a unit
 constexpr uint32_t kWarpsPerCta = 4;     // tile kernel: one tile per warp

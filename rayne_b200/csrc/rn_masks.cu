@@ -252,6 +252,7 @@ static int build_masks(rn_scene *s, uint32_t *out, uint32_t stride, cudaStream_t
 
 extern "C" int rn_cull_build_masks(rn_scene_t *s, void *cuda_stream)
 {
+	RN_RANGE("rn_cull_build_masks");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_build_masks needs a cull");
 	RN_CUDA(cudaSetDevice(s->device));
@@ -343,6 +344,7 @@ extern "C" int rn_cull_read_masks_async(rn_scene_t *s, uint32_t n_cameras, uint3
 extern "C" int rn_masks_expand(rn_scene_t *s, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
                                uint32_t capacity, uint32_t *device_count, void *cuda_stream)
 {
+	RN_RANGE("rn_masks_expand");
 	RN_REQUIRE(s && (segments || n_segments == 0) && device_list && device_count, RN_ERR_INVALID, "NULL argument");
 	RN_CUDA(cudaSetDevice(s->device));
 	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);

@@ -655,6 +655,7 @@ extern "C" int rn_occlusion_reset_counters(rn_scene_t *s)
 extern "C" int rn_cull_occlusion(rn_scene_t *s, const rn_occlusion_camera *cameras, const uint32_t *camera_order, uint32_t n_cameras,
                                  const float *jitter, void *cuda_stream)
 {
+	RN_RANGE("rn_cull_occlusion");
 	RN_REQUIRE(s && cameras && jitter, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_occlusion needs the masks of a cull (rn_transform_cull / rn_cull)");
 	RN_REQUIRE(n_cameras == s->last_ncams, RN_ERR_INVALID, "the last cull had %u cameras, %u given", s->last_ncams, n_cameras);

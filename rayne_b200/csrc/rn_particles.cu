@@ -612,6 +612,7 @@ extern "C" int rn_particles_configure(rn_scene_t *s, const rn_emitter_desc *emit
 
 extern "C" int rn_particles_step(rn_scene_t *s, float delta, void *cuda_stream)
 {
+	RN_RANGE("rn_particles_step");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	ParticleStore *p = s->particles;
 	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
@@ -634,6 +635,7 @@ extern "C" int rn_particles_step(rn_scene_t *s, float delta, void *cuda_stream)
 
 extern "C" int rn_particles_sort(rn_scene_t *s, const float cam[3], void *cuda_stream)
 {
+	RN_RANGE("rn_particles_sort");
 	RN_REQUIRE(s && cam, RN_ERR_INVALID, "NULL argument");
 	ParticleStore *p = s->particles;
 	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
@@ -778,6 +780,7 @@ extern "C" int rn_particles_download(rn_scene_t *s, uint32_t emitter, rn_particl
 extern "C" int rn_particles_build_mesh(rn_scene_t *s, const float *world_scale_x, const uint32_t *flags, rn_particle_mesh *out,
                                        void *cuda_stream)
 {
+	RN_RANGE("rn_particles_build_mesh");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	ParticleStore *p = s->particles;
 	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");

@@ -342,6 +342,7 @@ static int slot_prepare(rn_pipeline *p, PipeSlot &s, uint32_t n_cams, uint32_t f
 
 extern "C" int rn_pipeline_submit(rn_pipeline_t *p, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_visibility_form form)
 {
+	RN_RANGE("rn_pipeline_submit");
 	RN_REQUIRE(p && cameras, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(n_cameras >= 1 && n_cameras <= RN_MAX_CAMERAS, RN_ERR_INVALID, "n_cameras must be 1..%d", RN_MAX_CAMERAS);
 	RN_REQUIRE(form == RN_VIS_LISTS || form == RN_VIS_MASKS || form == RN_VIS_ADAPTIVE, RN_ERR_INVALID, "unknown visibility form %d", (int)form);
@@ -389,6 +390,7 @@ extern "C" int rn_pipeline_submit(rn_pipeline_t *p, const rn_camera_frustum *cam
 
 extern "C" int rn_pipeline_acquire(rn_pipeline_t *p, rn_frame_view *view)
 {
+	RN_RANGE("rn_pipeline_acquire");
 	RN_REQUIRE(p && view, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(p->acquired < p->submitted, RN_ERR_STATE, "no submitted frame to acquire");
 	RN_REQUIRE(p->acquired == p->released, RN_ERR_STATE, "release the acquired frame first");

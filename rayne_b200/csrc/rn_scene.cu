@@ -1766,6 +1766,7 @@ static int update_scattered(rn_scene *s, const rn_node_columns *cols, const uint
 
 extern "C" int rn_scene_upload(rn_scene_t *s, const rn_node_columns *cols, uint32_t first, uint32_t count)
 {
+	RN_RANGE("rn_scene_upload");
 	RN_REQUIRE(s && cols, RN_ERR_INVALID, "NULL argument");
 	if(cols->parent)
 	{
@@ -1778,6 +1779,7 @@ extern "C" int rn_scene_upload(rn_scene_t *s, const rn_node_columns *cols, uint3
 
 extern "C" int rn_scene_update_nodes(rn_scene_t *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count)
 {
+	RN_RANGE("rn_scene_update_nodes");
 	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
 	return update_scattered(s, cols, ranks, 0, count);
 }
@@ -1785,6 +1787,7 @@ extern "C" int rn_scene_update_nodes(rn_scene_t *s, const rn_node_columns *cols,
 extern "C" int rn_scene_update_nodes_async(rn_scene_t *s, const rn_node_columns *cols, const uint32_t *ranks, uint32_t count,
                                            void *cuda_stream)
 {
+	RN_RANGE("rn_scene_update_nodes_async");
 	RN_REQUIRE(s && cols && (ranks || count == 0), RN_ERR_INVALID, "NULL argument");
 	return update_scattered(s, cols, ranks, 0, count, static_cast<cudaStream_t>(cuda_stream), false);
 }
@@ -1836,6 +1839,7 @@ __global__ void __launch_bounds__(256) remove_kernel(float4 *c2, const uint32_t 
 
 extern "C" int rn_scene_add_nodes(rn_scene_t *s, const rn_node_columns *cols, uint32_t count, uint32_t *out_slots)
 {
+	RN_RANGE("rn_scene_add_nodes");
 	RN_REQUIRE(s && cols && out_slots, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(cols->position && cols->scale && cols->rotation && cols->parent && cols->flags && cols->render_group && cols->bounding_sphere,
 	           RN_ERR_INVALID, "rn_scene_add_nodes needs every node column");
@@ -2025,6 +2029,7 @@ extern "C" int rn_scene_add_nodes(rn_scene_t *s, const rn_node_columns *cols, ui
 
 extern "C" int rn_scene_remove_nodes(rn_scene_t *s, const uint32_t *slots, uint32_t count)
 {
+	RN_RANGE("rn_scene_remove_nodes");
 	RN_REQUIRE(s && (slots || count == 0), RN_ERR_INVALID, "NULL argument");
 	if(count == 0) return RN_OK;
 	for(uint32_t i = 0; i < count; i++)
@@ -2077,6 +2082,7 @@ extern "C" int rn_scene_edit_stats(const rn_scene_t *s, uint32_t *live_nodes, ui
 
 extern "C" int rn_transform_propagate(rn_scene_t *s, void *cuda_stream)
 {
+	RN_RANGE("rn_transform_propagate");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	RN_CUDA(cudaSetDevice(s->device));
@@ -2127,6 +2133,7 @@ static int cull_stored(rn_scene *s, const rn_camera_frustum *cameras, uint32_t n
 
 extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists, void *cuda_stream)
 {
+	RN_RANGE("rn_cull");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	RN_REQUIRE(s->have_world, RN_ERR_STATE, "rn_cull needs world transforms: call rn_transform_propagate first (or rn_transform_cull)");
@@ -2142,6 +2149,7 @@ extern "C" int rn_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t
 extern "C" int rn_transform_cull(rn_scene_t *s, const rn_camera_frustum *cameras, uint32_t n_cameras, rn_vis_list *out_lists,
                                  void *cuda_stream)
 {
+	RN_RANGE("rn_transform_cull");
 	RN_REQUIRE(s, RN_ERR_INVALID, "NULL scene");
 	RN_REQUIRE(s->n > 0, RN_ERR_STATE, "no nodes uploaded");
 	CullParams cp;
@@ -2245,6 +2253,7 @@ static int read_lists(rn_scene *s, uint32_t n_cameras, uint32_t *const *out_slot
 extern "C" int rn_cull_read_lists(rn_scene_t *s, uint32_t n_cameras, uint32_t *const *out_slots, const uint32_t *capacities,
                                   uint32_t *out_counts, void *cuda_stream)
 {
+	RN_RANGE("rn_cull_read_lists");
 	return read_lists(s, n_cameras, out_slots, capacities, out_counts, static_cast<cudaStream_t>(cuda_stream), true);
 }
 

@@ -355,6 +355,7 @@ using namespace rn;
 
 extern "C" int rn_cull_sort(rn_scene_t *s, const float *camera_world_positions, uint32_t n_cameras, void *cuda_stream)
 {
+	RN_RANGE("rn_cull_sort");
 	RN_REQUIRE(s && camera_world_positions, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(s->last_ncams > 0, RN_ERR_STATE, "rn_cull_sort needs the lists of a cull");
 	RN_REQUIRE(n_cameras == s->last_ncams, RN_ERR_INVALID, "the last cull had %u cameras, %u positions given", s->last_ncams, n_cameras);

@@ -167,39 +167,6 @@ def test_sharded_matches_single():
             assert np.array_equal(np.concatenate(parts[c]), want[c]), (world, c)
 
 
-@pytest.mark.parametrize("shards", [1, 3, 5])
-def test_pipelined_frame_matches_single(shards):
-    """rayne_b200/pipeline.py: S rank ranges on S streams, lists copied one behind the other into pinned host
-    buffers == the single-scene lists in global-rank form, also after a scattered update of the roots."""
-    import torch
-    from rayne_b200 import pipeline
-    scene = sg.make_scene(n_trees=40, branching=4, depth=6, seed=19, random_bounds=True, random_groups=True)
-    cams = standard_cameras()
-    fr = capi.build_frustums(cams)
-    rs = capi.RankedScene(scene)
-    roots = rs.roots
-    moved = rs.position[roots] + np.float32([0.5, 0, 0])
-    pinned = [torch.empty(scene.n, dtype=torch.int32).pin_memory() for _ in fr]
-    with capi.SceneHandle(max_nodes=scene.n) as h, pipeline.PipelinedScene(rs, shards) as pipe:
-        h.upload(rs)
-        h.set_list_mode(True, 0)
-        for step in range(2):
-            if step == 1:
-                h.update_nodes(roots, position=moved)
-                pipe.update_nodes(roots, position=moved)
-            h.transform_cull(fr)
-            pipe.transform_cull(fr)
-            total = pipe.read_lists_into([p.data_ptr() for p in pinned], [p.numel() for p in pinned])
-            if step == 1:   # the one-call form of the same frame
-                again = pipe.frame(fr, [p.data_ptr() for p in pinned], [p.numel() for p in pinned], dirty_ranks=roots,
-                                   position=moved)
-                assert np.array_equal(again, total)
-            for c in range(len(fr)):
-                want = h.read_list(c)
-                assert total[c] == want.shape[0]
-                assert np.array_equal(pinned[c].numpy()[:int(total[c])].view(np.uint32), want), (step, c)
-
-
 def test_classifier_edge_cases():
     """Negative and huge scales, zero radii, nodes exactly on planes, clusters straddling every plane: the warp-level
     classifier must never change a decision of the exact test."""
