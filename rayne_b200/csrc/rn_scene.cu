@@ -485,6 +485,44 @@ __global__ void __launch_bounds__(256) spine_kernel(SceneView sv, const uint32_t
 	store_world_global(sv, slot, W);
 }
 
+// The same pre-pass in ONE launch for shallow spines (the usual case: the top few levels of big trees): every thread
+// recomputes the world transforms of its node's ancestors from their local columns - the same operations on the same
+// inputs, hence the same bits as the per-depth launches - and stores only its own node.  No dependency between threads,
+// no barrier, one launch instead of one per depth (each costs ~5 us of latency, a fifth of a 1 M-node frame).
+constexpr uint32_t kSpineChainMax = 12;
+
+template <bool FMA>
+__global__ void __launch_bounds__(256) spine_chain_kernel(SceneView sv, const uint32_t *__restrict__ slots, uint32_t count)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= count)
+		return;
+	uint32_t chain[kSpineChainMax];
+	uint32_t depth = 0, cur = slots[i];
+	for(;;)
+	{
+		chain[depth++] = cur;
+		const uint32_t parent = __float_as_uint(sv.c2[cur].z);
+		if(parent == RN_NO_PARENT || depth == kSpineChainMax)
+			break;
+		cur = parent;
+	}
+	NodeWorld P, W;
+	bool hasParent = false;
+	for(uint32_t k = depth; k-- > 0;)
+	{
+		const uint32_t slot = chain[k];
+		const float4 a = sv.c0[slot], b = sv.c1[slot], c = sv.c2[slot];
+		const Vec3 pos = {a.x, a.y, a.z};
+		const Vec3 scale = {a.w, c.x, c.y};
+		const Quat rot = {b.x, b.y, b.z, b.w};
+		compute_world<FMA>(pos, rot, scale, hasParent, P, W);
+		P = W;
+		hasParent = true;
+	}
+	store_world_global(sv, chain[0], W);
+}
+
 // Per-warp shared memory: the world TRS + matrix of the tile's INNER nodes (nodes with children), SoA (88 bytes
 // per inner node), the tile descriptor, one staging buffer for the four input columns of a pass (4 x 32 x float4,
 // filled by TMA bulk copies) and the mbarrier those copies complete on.
@@ -1281,6 +1319,19 @@ static int ensure_lists(rn_scene *s, uint32_t ncams)
 static int launch_spine(rn_scene *s, cudaStream_t stream)
 {
 	const SceneView v = make_view(s);
+	const size_t levels = s->spine_level_ofs.empty() ? 0 : s->spine_level_ofs.size() - 1;
+	if(levels >= 2 && levels <= kSpineChainMax)
+	{
+		// shallow spine: all depths in one launch (every thread walks its own ancestor chain)
+		const uint32_t cnt = s->spine_level_ofs[levels];
+		if(s->fma_matrices)
+			spine_chain_kernel<true><<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots, cnt);
+		else
+			spine_chain_kernel<false><<<(cnt + 255) / 256, 256, 0, stream>>>(v, s->spine_slots, cnt);
+		s->launches++;
+		RN_CUDA(cudaGetLastError());
+		return RN_OK;
+	}
 	for(size_t d = 0; d + 1 < s->spine_level_ofs.size(); d++)
 	{
 		const uint32_t cnt = s->spine_level_ofs[d + 1] - s->spine_level_ofs[d];

@@ -136,35 +136,3 @@ def test_sharded_masks_expand_to_the_single_scene_list(world):
     finally:
         for h in handles:
             h.close()
-
-
-@pytest.mark.parametrize("shards", [1, 4])
-def test_pipelined_mask_frame_matches_single(shards):
-    """pipeline.PipelinedScene.frame_masks: per rank range [views, words] in pinned host memory == the single-scene
-    lists (global ranks), also after a scattered update of the roots."""
-    import torch
-    from rayne_b200 import pipeline
-    scene = sg.make_scene(n_trees=40, branching=4, depth=6, seed=19, random_bounds=True, random_groups=True)
-    cams = standard_cameras()
-    fr = capi.build_frustums(cams)
-    rs = capi.RankedScene(scene)
-    roots = rs.roots
-    moved = rs.position[roots] + np.float32([0.5, 0, 0])
-    with capi.SceneHandle(max_nodes=scene.n) as h, pipeline.PipelinedScene(rs, shards) as pipe:
-        h.upload(rs)
-        h.set_list_mode(True, 0)
-        offs, total = pipe.mask_layout(len(fr))
-        pinned = torch.zeros(total, dtype=torch.int32).pin_memory()
-        for step in range(2):
-            kw = dict(dirty_ranks=roots, position=moved) if step == 1 else {}
-            if step == 1:
-                h.update_nodes(roots, position=moved)
-            h.transform_cull(fr)
-            pipe.frame_masks(fr, pinned.data_ptr(), **kw)
-            mk = pinned.numpy().view(np.uint32)
-            for c in range(len(fr)):
-                parts = []
-                for k, (a, b) in enumerate(pipe.ranges):
-                    w = (b - a + 31) // 32
-                    parts.append(bits_of(mk[offs[k] + c * w: offs[k] + (c + 1) * w], b - a) + np.uint32(a))
-                assert np.array_equal(np.concatenate(parts), h.read_list(c)), (step, c)
