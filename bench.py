@@ -647,6 +647,8 @@ def run_ours(args) -> dict:
             full_rank_of = rank_of_all
             v.rank_of = (full_rank_of.astype(np.int64) - rank_offset).astype(np.int64)   # creation id -> local rank (valid for ids in the shard)
             h.set_list_mode(False, 0)
+            # restore the positions the scene was generated with (the exchange check moved the roots)
+            h.update_nodes(local_roots, position=rs.position[local_roots])
             parity = parity_gate(h, v, scene, cams, fr, cfg, min(CPU_SAMPLE_TREES, max(1, trees // world // 2)), stream, args.strict_matrices)
             h.set_list_mode(True, rank_offset)
         else:

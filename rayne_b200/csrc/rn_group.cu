@@ -156,7 +156,7 @@ static bool setup_multicast(rn_group *g, size_t bytes)
 	mp.size = bytes;
 	mp.handleTypes = 0;
 	size_t gran = 0;
-	if(d.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || !gran)
+	if(d.MulticastGetGranularity(&gran, &mp, CU_MULTICAST_GRANULARITY_MINIMUM) != CUDA_SUCCESS || !gran)
 	{ snprintf(g->transport_note, sizeof(g->transport_note), "cuMulticastGetGranularity failed"); return false; }
 	CUmemAllocationProp ap;
 	memset(&ap, 0, sizeof(ap));
@@ -164,7 +164,7 @@ static bool setup_multicast(rn_group *g, size_t bytes)
 	ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
 	size_t mgran = 0;
 	ap.location.id = g->dev[0].device;
-	d.MemGetAllocationGranularity(&mgran, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
+	d.MemGetAllocationGranularity(&mgran, &ap, CU_MEM_ALLOC_GRANULARITY_MINIMUM);
 	gran = std::max(gran, mgran);
 	const size_t size = (bytes + gran - 1) / gran * gran;
 	mp.size = size;
