@@ -70,8 +70,8 @@ typedef struct rn_scene_desc {
 	uint32_t tile_nodes;                 /* nodes per tile (0 = default 512; 64..1024) */
 	uint32_t max_emitters;               /* 0 = no particle storage */
 	uint32_t max_particles_per_emitter;  /* < 16383 (Source/Scene/RNParticleEmitter.cpp:115) */
-	uint32_t tile_inner_nodes;           /* nodes WITH children per tile, kept in shared memory (0 = default 96; 16..1024) */
-	uint32_t tile_unit_nodes;            /* largest subtree kept whole inside a tile (0 = default; 8..tile_nodes).  Smaller
+	uint32_t tile_inner_nodes;           /* nodes WITH children per tile, kept in shared memory (0 = default 128; 16..1024) */
+	uint32_t tile_unit_nodes;            /* largest subtree kept whole inside a tile (0 = default 128; 8..tile_nodes).  Smaller
 	                                        units put more subtrees into a tile, which fills the 32-wide passes of
 	                                        every hierarchy level; the nodes above the units go through the spine pre-pass */
 	uint32_t flags;                      /* RN_SCENE_* bits, 0 = defaults */

@@ -64,8 +64,8 @@ struct rn_scene
 	rn_scene_desc desc{};
 	int device = 0;
 	uint32_t tile_cap = 512;
-	uint32_t inner_cap = 96;     // inner nodes (parents kept in shared memory) per tile
-	uint32_t unit_cap = 512;     // largest subtree kept whole inside a tile
+	uint32_t inner_cap = 128;    // inner nodes (parents kept in shared memory) per tile
+	uint32_t unit_cap = 128;     // largest subtree kept whole inside a tile
 	uint32_t n = 0;              // nodes
 	uint32_t n_tiles = 0;
 	uint32_t max_depth = 0;

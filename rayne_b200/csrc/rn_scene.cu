@@ -1506,11 +1506,14 @@ extern "C" int rn_scene_create(rn_scene_t **out, const rn_scene_desc *desc)
 	uint32_t cap = desc->tile_nodes ? desc->tile_nodes : 512;
 	RN_REQUIRE(cap >= 64 && cap <= 1024 && (cap % 16) == 0, RN_ERR_INVALID, "tile_nodes must be a multiple of 16 in 64..1024, got %u", cap);
 	RN_REQUIRE(desc->max_nodes < 0x80000000u, RN_ERR_INVALID, "max_nodes must be below 2^31");
-	uint32_t inner_cap = desc->tile_inner_nodes ? desc->tile_inner_nodes : 96;
+	uint32_t inner_cap = desc->tile_inner_nodes ? desc->tile_inner_nodes : 128;
 	RN_REQUIRE(inner_cap >= 16 && inner_cap <= 1024 && (inner_cap % 2) == 0 &&
 	           (size_t)warp_smem_bytes(inner_cap) * kWarpsPerCta <= 227u * 1024u,
 	           RN_ERR_INVALID, "tile_inner_nodes must be an even number in 16..%u, got %u", (227u * 1024u / kWarpsPerCta - 64u - kStageBytes - 16u) / 88u, inner_cap);
-	const uint32_t unit_cap = desc->tile_unit_nodes ? desc->tile_unit_nodes : cap;
+	// 128: several small subtrees per tile fill the 32-wide passes of every level (6 units of 85 nodes in a tile of the
+	// benchmark's 4-ary trees: 94 % of the lanes busy instead of 82 %); measured best on the benchmark scene together with
+	// 128 inner nodes, the most that still lets four CTAs share an SM (profiles/r02ae_tiling.jsonl)
+	const uint32_t unit_cap = desc->tile_unit_nodes ? desc->tile_unit_nodes : std::min(cap, 128u);
 	RN_REQUIRE(unit_cap >= 8 && unit_cap <= cap, RN_ERR_INVALID, "tile_unit_nodes must be in 8..tile_nodes, got %u", unit_cap);
 	RN_REQUIRE(desc->max_particles_per_emitter < 16383, RN_ERR_INVALID,
 	           "max_particles_per_emitter must be < 16383 (reference: RNParticleEmitter.cpp:115)");
