@@ -1025,7 +1025,7 @@ def main():
     ap.add_argument("--strict-matrices", action="store_true", help="RN_SCENE_STRICT_MATRICES: world matrices bit-exact (no FMA on the matrix chain)")
     ap.add_argument("--rig", choices=("reference", "legacy"), default="reference",
                     help="6-view configs: cascade cameras derived like the reference's Light::UpdateShadows (default) or round 1's hand-set ones")
-    ap.add_argument("--e2e-shards", type=int, default=4, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
+    ap.add_argument("--e2e-shards", type=int, default=8, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
     ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="multicast",
                     help="N>1: multimem stores of the mask kernel through NVLS multicast (falls back to NCCL where "
                          "symmetric memory / NVLS is unavailable), or the NCCL all-gather")

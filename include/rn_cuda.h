@@ -397,7 +397,7 @@ typedef enum rn_visibility_form { RN_VIS_LISTS = 0, RN_VIS_MASKS = 1, RN_VIS_ADA
 typedef struct rn_pipeline_desc
 {
 	int32_t  device;
-	uint32_t n_ranges;            /* 0 = 4 */
+	uint32_t n_ranges;            /* 0 = 8 (measured best on the 16.8 M-node scene: 2: 0.85 ms, 4: 0.80, 8: 0.74, 16: 0.75) */
 	uint32_t frames_in_flight;    /* 0 = 2 */
 	uint32_t flags;               /* rn_scene_desc.flags of every range (RN_SCENE_STRICT_MATRICES) */
 	uint32_t rank_base;           /* global rank of the first node (a GPU's own range in a multi-GPU split) */

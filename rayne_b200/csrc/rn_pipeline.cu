@@ -177,7 +177,7 @@ extern "C" int rn_pipeline_create(rn_pipeline_t **out, const rn_pipeline_desc *d
 	RN_REQUIRE(count > 0, RN_ERR_INVALID, "no nodes");
 	RN_REQUIRE(cols->position && cols->scale && cols->rotation && cols->parent && cols->flags && cols->render_group && cols->bounding_sphere,
 	           RN_ERR_INVALID, "rn_pipeline_create needs every node column");
-	const uint32_t n_ranges = desc->n_ranges ? desc->n_ranges : 4;
+	const uint32_t n_ranges = desc->n_ranges ? desc->n_ranges : 8;
 	const uint32_t ring = desc->frames_in_flight ? desc->frames_in_flight : 2;
 	RN_REQUIRE(n_ranges <= 64 && ring <= 8, RN_ERR_INVALID, "n_ranges <= 64 and frames_in_flight <= 8");
 	rn_pipeline *p = new(std::nothrow) rn_pipeline();
