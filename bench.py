@@ -743,12 +743,15 @@ def run_ours(args) -> dict:
         return {"value": n_total / ms / 1e3, "unit": "Mnodes/s", "ms_per_step": ms, "h2d_bytes_per_step": hb, "d2h_bytes_per_step": db,
                 "form": name, "what": what}
 
-    e2e_common = (f"rn_pipeline_update_nodes (dirty roots) + rn_pipeline_submit + rn_pipeline_acquire: {shards} rank ranges on prioritised streams, "
-                  "visibility stored into mapped pinned host memory by the device, 2 frames in flight; ")
+    e2e_common = (f"rn_pipeline_update_nodes (dirty roots) + rn_pipeline_submit + rn_pipeline_acquire, 2 frames in flight, visibility into pinned host "
+                  "memory; " + (f"{shards} rank ranges on prioritised streams, stored by the device (pack kernel); " if shards > 1 else
+                                "one range, two sets of cull outputs, the copy-out of frame i runs on its own stream beside the kernels of frame i + 1 "
+                                "(masks through the copy engine, lists through the pack kernel); "))
     e2e_lists = e2e_entry("lists", e2e_common + "every view as its list of render-list ranks (4 B per visible node) - the container the reference's Render fills")
     e2e_masks = e2e_entry("masks", e2e_common + "every view as a rank-order bitmask (1 bit per node)")
-    e2e_adaptive = e2e_entry("adaptive", e2e_common + "per range and view the smaller of list and bitmask, chosen on the device from the compaction's "
-                             "count; rn_frame_list decodes either into the reference's list")
+    e2e_adaptive = e2e_entry("adaptive", e2e_common + ("per range and view the smaller of list and bitmask, chosen on the device from the compaction's count; "
+                                                       if shards > 1 else "RN_VIS_ADAPTIVE, which delivers rank-order bitmasks in the one-range mode; ") +
+                             "rn_frame_list decodes either into the reference's list")
     e2e_adaptive["encodings_equal_and_equal_to_rn_cull_read_list"] = bool(forms_equal)
     e2e_adaptive["encoding_per_view_and_range"] = forms_taken
 
@@ -1025,7 +1028,7 @@ def main():
     ap.add_argument("--strict-matrices", action="store_true", help="RN_SCENE_STRICT_MATRICES: world matrices bit-exact (no FMA on the matrix chain)")
     ap.add_argument("--rig", choices=("reference", "legacy"), default="reference",
                     help="6-view configs: cascade cameras derived like the reference's Light::UpdateShadows (default) or round 1's hand-set ones")
-    ap.add_argument("--e2e-shards", type=int, default=8, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
+    ap.add_argument("--e2e-shards", type=int, default=1, help="rank ranges / streams of the pipelined end-to-end frame (1 = off)")
     ap.add_argument("--exchange-transport", choices=("nccl", "multicast"), default="multicast",
                     help="N>1: multimem stores of the mask kernel through NVLS multicast (falls back to NCCL where "
                          "symmetric memory / NVLS is unavailable), or the NCCL all-gather")

@@ -391,13 +391,17 @@ int rn_occlusion_download(rn_scene_t *scene, uint32_t camera, uint32_t *used, fl
  * view.segments[range * n_cameras + camera] describes one piece of a camera's visibility: `form` RN_VIS_LISTS = `count`
  * global ranks ascending; RN_VIS_MASKS = ceil(rank_count / 32) words, bit b of word w = rank rank_first + 32 w + b.  The
  * concatenation over the ranges in order is the reference's list.  RN_VIS_ADAPTIVE lets the device pick per segment the
- * smaller of the two encodings (a list wins below 1/32 visible).  Ranks are global: rank_base + position in the columns. */
+ * smaller of the two encodings (a list wins below 1/32 visible).  Ranks are global: rank_base + position in the columns.
+ * With n_ranges = 1 the scene keeps two sets of cull outputs and the copy-out runs on its own stream beside the next frame's
+ * kernels; the masks then travel through the copy engine (a copy kernel would wait for the persistent tile kernel's CTAs),
+ * so RN_VIS_ADAPTIVE delivers masks in that mode. */
 typedef struct rn_pipeline rn_pipeline_t;
 typedef enum rn_visibility_form { RN_VIS_LISTS = 0, RN_VIS_MASKS = 1, RN_VIS_ADAPTIVE = 2 } rn_visibility_form;
 typedef struct rn_pipeline_desc
 {
 	int32_t  device;
-	uint32_t n_ranges;            /* 0 = 8 (measured best on the 16.8 M-node scene: 2: 0.85 ms, 4: 0.80, 8: 0.74, 16: 0.75) */
+	uint32_t n_ranges;            /* 0 = 1: one range, copy-out beside the next frame's kernels (measured on the 16.8 M-node scene:
+	                                 1: 0.66 ms, 2: 0.85, 4: 0.80, 8: 0.73, 16: 0.75; device-only step 0.62) */
 	uint32_t frames_in_flight;    /* 0 = 2 */
 	uint32_t flags;               /* rn_scene_desc.flags of every range (RN_SCENE_STRICT_MATRICES) */
 	uint32_t rank_base;           /* global rank of the first node (a GPU's own range in a multi-GPU split) */

@@ -95,6 +95,11 @@ struct rn_scene
 	uint32_t *super_totals = nullptr;  // [n_tiles / 256][RN_MAX_CAMERAS]
 	uint32_t *list_counts = nullptr;   // [RN_MAX_CAMERAS]
 	uint32_t *lists[RN_MAX_CAMERAS] = {};
+	// second set of cull outputs (lists, counts, rank masks): rn_pipeline's single-range mode flips between the two so that
+	// the copy-out of frame i can run beside the kernels of frame i + 1 (scene_flip_outputs, rn_scene.cu)
+	uint32_t *lists_alt[RN_MAX_CAMERAS] = {};
+	uint32_t *list_counts_alt = nullptr;
+	uint32_t *rank_masks_alt = nullptr;
 	uint32_t list_capacity = 0;
 	// optional columns / outputs (allocated on first use; rn_bounds.cu, rn_sort.cu)
 	float4 *box0 = nullptr;      // local AABB: minExtend xyz, maxExtend x   (nullptr = default AABB(-1, 1))
@@ -180,6 +185,7 @@ int volume_filter_launch(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
 int clear_super_totals(rn_scene *scene, cudaStream_t stream);
 int launch_compaction(rn_scene *scene, uint32_t ncams, cudaStream_t stream);
 void occlusion_free(rn_scene *scene);   // rn_occlusion.cu
+int scene_flip_outputs(rn_scene *scene);   // rn_scene.cu: swaps the two sets of cull outputs
 // rn_masks.cu: the rank-order masks of the last cull stored into n_dst buffers at once (peer-mapped pointers)
 int build_masks_fanout(rn_scene *scene, uint32_t *const *dsts, uint32_t n_dst, uint32_t stride, cudaStream_t stream);
 

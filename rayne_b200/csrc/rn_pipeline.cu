@@ -89,6 +89,7 @@ struct PipeSlot
 	uint32_t form = 0;
 	uint64_t frame = 0;
 	bool busy = false;              // submitted, not yet released
+	bool engine_copy = false;       // single-range mode: masks + raw counts came through the copy engine (header = 8 counts)
 };
 
 } // namespace rn
@@ -104,6 +105,12 @@ struct rn_pipeline
 	uint64_t submitted = 0, acquired = 0, released = 0;
 	uint64_t h2d_bytes = 0;             // dirty rows staged since the last submit
 	uint64_t pending_h2d = 0;
+	// single-range mode: the copy-out runs on its own stream beside the next frame's kernels, the scene flips between two
+	// sets of cull outputs
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t cull_done = nullptr;
+	cudaEvent_t pack_done[2] = {nullptr, nullptr};
+	uint32_t out_set = 0;
 };
 
 using namespace rn;
@@ -167,6 +174,9 @@ static void pipeline_free(rn_pipeline *p)
 		if(r.scene) rn_scene_destroy(r.scene);
 		if(r.stream) cudaStreamDestroy(r.stream);
 	}
+	if(p->copy_stream) cudaStreamDestroy(p->copy_stream);
+	if(p->cull_done) cudaEventDestroy(p->cull_done);
+	for(cudaEvent_t e : p->pack_done) if(e) cudaEventDestroy(e);
 	delete p;
 }
 
@@ -177,7 +187,7 @@ extern "C" int rn_pipeline_create(rn_pipeline_t **out, const rn_pipeline_desc *d
 	RN_REQUIRE(count > 0, RN_ERR_INVALID, "no nodes");
 	RN_REQUIRE(cols->position && cols->scale && cols->rotation && cols->parent && cols->flags && cols->render_group && cols->bounding_sphere,
 	           RN_ERR_INVALID, "rn_pipeline_create needs every node column");
-	const uint32_t n_ranges = desc->n_ranges ? desc->n_ranges : 8;
+	const uint32_t n_ranges = desc->n_ranges ? desc->n_ranges : 1;
 	const uint32_t ring = desc->frames_in_flight ? desc->frames_in_flight : 2;
 	RN_REQUIRE(n_ranges <= 64 && ring <= 8, RN_ERR_INVALID, "n_ranges <= 64 and frames_in_flight <= 8");
 	rn_pipeline *p = new(std::nothrow) rn_pipeline();
@@ -229,6 +239,20 @@ extern "C" int rn_pipeline_create(rn_pipeline_t **out, const rn_pipeline_desc *d
 		if(!rc) rc = rn_scene_set_list_mode(r.scene, 1, desc->rank_base + r.first);
 	}
 	if(rc) { pipeline_free(p); return rc; }
+	if(n_ranges == 1 && ring >= 2)
+	{
+		void *st = nullptr;
+		rc = rn_stream_create(&st, 1);
+		cudaError_t e = cudaSuccess;
+		if(!rc)
+		{
+			p->copy_stream = static_cast<cudaStream_t>(st);
+			e = cudaEventCreateWithFlags(&p->cull_done, cudaEventDisableTiming);
+			if(e == cudaSuccess) e = cudaEventCreateWithFlags(&p->pack_done[0], cudaEventDisableTiming);
+			if(e == cudaSuccess) e = cudaEventCreateWithFlags(&p->pack_done[1], cudaEventDisableTiming);
+		}
+		if(rc || e != cudaSuccess) { pipeline_free(p); return rc ? rc : cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__); }
+	}
 	p->slots.resize(ring);
 	for(PipeSlot &s : p->slots)
 	{
@@ -353,11 +377,15 @@ extern "C" int rn_pipeline_submit(rn_pipeline_t *p, const rn_camera_frustum *cam
 	int rc = slot_prepare(p, s, n_cameras, (uint32_t)form);
 	if(rc) return rc;
 	const uint32_t nr = p->desc.n_ranges;
+	const bool overlap = p->copy_stream != nullptr;      // single range: copy-out on its own stream, two output sets
 	for(uint32_t k = 0; k < nr; k++)
 	{
 		PipeRange &r = p->ranges[k];
+		cudaStream_t pack_stream = r.stream;
 		if(r.count)
 		{
+			if(overlap && p->submitted >= 2)     // this output set was last read by the copy-out of the frame before the previous one
+				RN_CUDA(cudaStreamWaitEvent(r.stream, p->pack_done[p->out_set], 0));
 			rc = rn_transform_cull(r.scene, cameras, n_cameras, nullptr, r.stream);
 			if(!rc && form != RN_VIS_LISTS) rc = rn_cull_build_masks(r.scene, r.stream);
 			if(rc) return rc;
@@ -374,11 +402,38 @@ extern "C" int rn_pipeline_submit(rn_pipeline_t *p, const rn_camera_frustum *cam
 			v.host_header = s.header + (size_t)k * RN_MAX_CAMERAS * 2;
 			const uint32_t most = form == RN_VIS_LISTS ? r.count : v.words;
 			const uint32_t blocks = std::max(1u, std::min((most + kPackThreads * 16 - 1) / (kPackThreads * 16), 96u));
-			pack_kernel<<<dim3(blocks, n_cameras), kPackThreads, 0, r.stream>>>(v);
-			RN_CUDA(cudaGetLastError());
-			r.scene->launches++;
+			s.engine_copy = false;
+			if(overlap)
+			{
+				RN_CUDA(cudaEventRecord(p->cull_done, r.stream));
+				RN_CUDA(cudaStreamWaitEvent(p->copy_stream, p->cull_done, 0));
+				pack_stream = p->copy_stream;
+			}
+			if(overlap && form != RN_VIS_LISTS)
+			{
+				// The persistent tile kernel of the next frame fills every SM, so a copy KERNEL would not get a CTA slot
+				// until it retires; the masks have a fixed size, so the copy ENGINE moves them (and the counts) instead -
+				// it runs truly beside the next frame.  (The adaptive encoding therefore means masks in this mode.)
+				RN_CUDA(cudaMemcpy2DAsync(v.host_data, (size_t)v.region_words * 4, v.masks, (size_t)v.words * 4, (size_t)v.words * 4, n_cameras,
+				                          cudaMemcpyDeviceToHost, p->copy_stream));
+				RN_CUDA(cudaMemcpyAsync(v.host_header, v.list_counts, sizeof(uint32_t) * RN_MAX_CAMERAS, cudaMemcpyDeviceToHost, p->copy_stream));
+				s.engine_copy = true;
+			}
+			else
+			{
+				pack_kernel<<<dim3(blocks, n_cameras), kPackThreads, 0, pack_stream>>>(v);
+				RN_CUDA(cudaGetLastError());
+				r.scene->launches++;
+			}
+			if(overlap)
+			{
+				RN_CUDA(cudaEventRecord(p->pack_done[p->out_set], p->copy_stream));
+				rc = scene_flip_outputs(r.scene);          // the next frame writes the other set while this one is copied out
+				if(rc) return rc;
+				p->out_set ^= 1u;
+			}
 		}
-		RN_CUDA(cudaEventRecord(s.done[k], r.stream));
+		RN_CUDA(cudaEventRecord(s.done[k], pack_stream));
 	}
 	s.frame = p->submitted;
 	s.busy = true;
@@ -412,8 +467,8 @@ extern "C" int rn_pipeline_acquire(rn_pipeline_t *p, rn_frame_view *view)
 				continue;
 			}
 			const uint32_t *h = s.header + ((size_t)k * RN_MAX_CAMERAS + c) * 2;
-			g.form = h[0];
-			g.count = h[1];
+			g.form = s.engine_copy ? (uint32_t)RN_VIS_MASKS : h[0];
+			g.count = s.engine_copy ? s.header[c] : h[1];
 			g.data = s.data + s.range_ofs[k] + (size_t)c * s.region[k];
 			d2h += 8 + 4ull * (g.form == RN_VIS_LISTS ? g.count : (g.rank_count + 31u) / 32u);
 		}

@@ -1276,7 +1276,12 @@ static void free_nodes(rn_scene *s)
 	for(void *p : ptrs)
 		if(p) cudaFree(p);
 	for(int c = 0; c < RN_MAX_CAMERAS; c++)
+	{
 		if(s->lists[c]) { cudaFree(s->lists[c]); s->lists[c] = nullptr; }
+		if(s->lists_alt[c]) { cudaFree(s->lists_alt[c]); s->lists_alt[c] = nullptr; }
+	}
+	if(s->list_counts_alt) { cudaFree(s->list_counts_alt); s->list_counts_alt = nullptr; }
+	if(s->rank_masks_alt) { cudaFree(s->rank_masks_alt); s->rank_masks_alt = nullptr; }
 	extras_free(s);
 	occlusion_free(s);
 	if(s->scratch_host) { cudaFreeHost(s->scratch_host); s->scratch_host = nullptr; }
@@ -1313,6 +1318,23 @@ static int ensure_lists(rn_scene *s, uint32_t ncams)
 			if(rc) return rc;
 		}
 	}
+	return RN_OK;
+}
+
+// Swaps the two sets of cull outputs (visibility lists, their counts, the rank-order masks).  The second set is allocated
+// on the first flip (the lists per camera on demand, by ensure_lists, once they are current).
+int scene_flip_outputs(rn_scene *s)
+{
+	if(!s->list_counts_alt)
+	{
+		int rc = dev_alloc(s, &s->list_counts_alt, (size_t)RN_MAX_CAMERAS);
+		if(rc) return rc;
+		RN_CUDA(cudaMemset(s->list_counts_alt, 0, sizeof(uint32_t) * RN_MAX_CAMERAS));
+	}
+	for(int c = 0; c < RN_MAX_CAMERAS; c++) std::swap(s->lists[c], s->lists_alt[c]);
+	std::swap(s->list_counts, s->list_counts_alt);
+	std::swap(s->rank_masks, s->rank_masks_alt);
+	s->have_masks = false;
 	return RN_OK;
 }
 
