@@ -893,20 +893,26 @@ def run_ours(args) -> dict:
             counts_before = h.read_counts()
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            slots = h.add_nodes(ex.pos[seq], ex.scale[seq], ex.rot[seq], par, ex.flags[seq], ex.group[seq], ex.sphere[seq])
+            try:
+                slots = h.add_nodes(ex.pos[seq], ex.scale[seq], ex.rot[seq], par, ex.flags[seq], ex.group[seq], ex.sphere[seq])
+            except capi.RNError as err:
+                # small scenes get small tiles (rn_scene_desc.tile_nodes = 0): a 100-node tree then needs a full upload
+                slots = None
+                extras["incremental_edits"] = {"nodes": int(ex.n), "fast_path": False, "why": str(err)}
             t_add = (time.perf_counter() - t0) * 1e3
-            ms_after = timed(lambda: h.transform_cull(fr, stream))
-            counts_after = h.read_counts()
-            t0 = time.perf_counter()
-            h.remove_nodes(slots)
-            t_rem = (time.perf_counter() - t0) * 1e3
-            h.transform_cull(fr, stream)
-            counts_removed = h.read_counts()
-            extras["incremental_edits"] = {"nodes": int(ex.n), "add_ms": t_add, "remove_ms": t_rem, "frame_ms_with_the_new_tiles": ms_after,
-                                           "visible_after_add": [int(c) for c in counts_after], "visible_after_remove": [int(c) for c in counts_removed],
-                                           "counts_back_to_before_the_edit": bool(np.array_equal(counts_removed, counts_before)),
-                                           "what": "rn_scene_add_nodes / rn_scene_remove_nodes on the uploaded scene, host wall clock; "
-                                                   "a full rn_scene_upload of this scene takes seconds (host re-tiling)"}
+            if slots is not None:
+                ms_after = timed(lambda: h.transform_cull(fr, stream))
+                counts_after = h.read_counts()
+                t0 = time.perf_counter()
+                h.remove_nodes(slots)
+                t_rem = (time.perf_counter() - t0) * 1e3
+                h.transform_cull(fr, stream)
+                counts_removed = h.read_counts()
+                extras["incremental_edits"] = {"nodes": int(ex.n), "add_ms": t_add, "remove_ms": t_rem, "frame_ms_with_the_new_tiles": ms_after,
+                                               "visible_after_add": [int(c) for c in counts_after], "visible_after_remove": [int(c) for c in counts_removed],
+                                               "counts_back_to_before_the_edit": bool(np.array_equal(counts_removed, counts_before)),
+                                               "what": "rn_scene_add_nodes / rn_scene_remove_nodes on the uploaded scene, host wall clock; "
+                                                       "a full rn_scene_upload of this scene takes seconds (host re-tiling)"}
     if world > 1:
         torch.cuda.synchronize()
         dist.barrier()

@@ -67,7 +67,7 @@ typedef struct rn_scene rn_scene_t;
 typedef struct rn_scene_desc {
 	int32_t  device;                     /* CUDA device ordinal */
 	uint32_t max_nodes;                  /* capacity of the node columns */
-	uint32_t tile_nodes;                 /* nodes per tile (0 = default 512; 64..1024) */
+	uint32_t tile_nodes;                 /* nodes per tile (0 = chosen per upload: 512 for large scenes, down to 64 for small ones; 64..1024) */
 	uint32_t max_emitters;               /* 0 = no particle storage */
 	uint32_t max_particles_per_emitter;  /* < 16383 (Source/Scene/RNParticleEmitter.cpp:115) */
 	uint32_t tile_inner_nodes;           /* nodes WITH children per tile, kept in shared memory (0 = default 128; 16..1024) */
