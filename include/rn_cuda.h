@@ -306,6 +306,23 @@ typedef struct rn_mask_segment {
 int rn_masks_expand(rn_scene_t *scene, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
                     uint32_t capacity, uint32_t *device_count, void *cuda_stream);
 
+/* rn_masks_expand for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same inputs,
+ * outputs and result as rn_masks_expand, but it takes no scene: the per-CTA scratch of the three expand kernels is a
+ * file-scope __device__ array of librn_cuda (64 KiB, held by every GPU that loads the library until the process exits),
+ * so the call performs no cudaMalloc / cudaFree and no allocating library call.  `device` is the CUDA device ordinal
+ * (-1 = the current device).  Limits: at most 32 segments per call, and the segments - each rounded up to a multiple of
+ * 1024 words - may hold at most RN_MASKS_EXPAND_STATIC_MAX_WORDS mask words in total (16 Mi words = 536 870 912 ranks);
+ * beyond that the call returns RN_ERR_CAPACITY and launches nothing (use rn_masks_expand).  All calls on one GPU share
+ * the one scratch array: calls enqueued on the same stream are ordered and safe, calls that overlap on the GPU (different
+ * streams without an event between them, or several host threads) race on it.  The array keeps the previous call's
+ * contents; nothing in it has to start at zero, the first kernel of every call overwrites the entries the call reads.
+ * The first call on a device looks the array's device address up (cudaGetSymbolAddress) - make that call before, not
+ * inside, a stream capture.  Asynchronous. */
+#define RN_MASKS_EXPAND_STATIC_MAX_WORDS (16u * 1024u * 1024u)
+int rn_masks_expand_static(int device, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
+                           uint32_t capacity, uint32_t *device_count, void *cuda_stream);
+
 /* Per-drawable matrix records for the list of `camera` left by the last cull (and rn_cull_sort): what a renderer
  * writes per drawable before a draw - model and inverse model matrix (Drawable::Update,
  * Source/Rendering/RNRenderer.h:65-76), view * model and projection * view * model

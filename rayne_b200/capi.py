@@ -43,6 +43,7 @@ EXPORTS = [
     "rn_group_create", "rn_group_destroy", "rn_group_info", "rn_group_update_nodes", "rn_group_frame", "rn_group_synchronize",
     "rn_group_member", "rn_group_expand", "rn_group_read_list",
     "rn_cull_build_masks", "rn_cull_build_masks_to", "rn_cull_build_masks_multicast", "rn_cull_device_masks", "rn_cull_read_masks_async", "rn_masks_expand",
+    "rn_masks_expand_static",
 ]
 
 
@@ -352,6 +353,20 @@ def plan_ranges(parent: np.ndarray, n_ranges: int) -> np.ndarray:
     bounds = np.zeros(n_ranges + 1, np.uint32)
     _check(load().rn_plan_ranges(_ptr(parent), C.c_uint32(parent.shape[0]), C.c_uint32(n_ranges), _ptr(bounds)))
     return bounds
+
+
+MASKS_EXPAND_STATIC_MAX_WORDS = 16 * 1024 * 1024
+
+
+def masks_expand_static(segments, device_list: int, capacity: int, device_count: int, stream: int = 0, device: int = -1) -> None:
+    """rn_masks_expand_static: rn_masks_expand with its scratch in a __device__ array of the library - no scene, no
+    allocation.  segments: iterable of (device pointer of the words, n_words, rank_base), at most 32."""
+    segments = list(segments)
+    segs = (MaskSegment * max(len(segments), 1))()
+    for k, (p, nw, base) in enumerate(segments):
+        segs[k].device_words, segs[k].n_words, segs[k].rank_base = int(p), int(nw), int(base)
+    _check(load().rn_masks_expand_static(C.c_int(device), segs, C.c_uint32(len(segments)), C.c_void_p(device_list),
+                                         C.c_uint32(capacity), C.c_void_p(device_count), C.c_void_p(stream)))
 
 
 class Pipeline:

@@ -12,6 +12,7 @@
 #include "rn_internal.h"
 #include <algorithm>
 #include <string.h>
+#include <mutex>
 
 namespace rn {
 
@@ -390,5 +391,80 @@ extern "C" int rn_masks_expand(rn_scene_t *s, const rn_mask_segment *segments, u
 		RN_CUDA(cudaGetLastError());
 		s->launches += 3;
 	}
+	return RN_OK;
+}
+
+// ---- rn_masks_expand without any allocation ---------------------------------------------------------------------------
+// The per-CTA totals of the three expand kernels live in a file-scope device array instead of the scene's cudaMalloc'd
+// scratch.  Every GPU that loads librn_cuda holds these 64 KiB until the process exits.  The kernels are the ones above,
+// unchanged: they take the scratch as a pointer.
+namespace rn {
+constexpr uint32_t kExpandStaticBlocks = RN_MASKS_EXPAND_STATIC_MAX_WORDS / kExpandWordsPerBlock;   // 16 384 CTAs
+static_assert(RN_MASKS_EXPAND_STATIC_MAX_WORDS % kExpandWordsPerBlock == 0, "the limit is a whole number of CTAs");
+static __device__ __align__(256) uint32_t g_expand_static_totals[kExpandStaticBlocks];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_expand_static_lock;
+static uint32_t *g_expand_static_ptr[kStaticMaxDevices];   // device address of the array above, per device; nullptr = not asked yet
+
+// In host code `g_expand_static_totals` is only a stand-in for the symbol: the address a kernel may use comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int expand_static_scratch(int device, uint32_t **out)
+{
+	std::lock_guard<std::mutex> hold(g_expand_static_lock);
+	if(!g_expand_static_ptr[device])
+	{
+		uint32_t *p = nullptr;
+		RN_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_expand_static_totals));
+		RN_REQUIRE(p, RN_ERR_CUDA, "cudaGetSymbolAddress gave no address for the static expand scratch on device %d", device);
+		g_expand_static_ptr[device] = p;
+	}
+	*out = g_expand_static_ptr[device];
+	return RN_OK;
+}
+}
+
+extern "C" int rn_masks_expand_static(int device, const rn_mask_segment *segments, uint32_t n_segments, uint32_t *device_list,
+                                      uint32_t capacity, uint32_t *device_count, void *cuda_stream)
+{
+	RN_RANGE("rn_masks_expand_static");
+	RN_REQUIRE((segments || n_segments == 0) && device_list && device_count, RN_ERR_INVALID, "NULL argument");
+	RN_REQUIRE(n_segments <= kExpandMaxSegments, RN_ERR_INVALID, "rn_masks_expand_static takes at most %u segments per call, got %u",
+	           kExpandMaxSegments, n_segments);
+	if(device < 0)
+		RN_CUDA(cudaGetDevice(&device));
+	RN_REQUIRE(device < kStaticMaxDevices, RN_ERR_INVALID, "device %d: rn_masks_expand_static knows devices 0..%d", device, kStaticMaxDevices - 1);
+	ExpandArgs a;
+	memset(&a, 0, sizeof(a));
+	uint32_t n_blocks = 0;
+	for(uint32_t k = 0; k < n_segments; k++)
+	{
+		if(segments[k].n_words == 0)
+			continue;
+		RN_REQUIRE(segments[k].device_words, RN_ERR_INVALID, "segment %u: NULL words", k);
+		const uint32_t q = a.n_segments++;
+		a.words[q] = segments[k].device_words;
+		a.n_words[q] = segments[k].n_words;
+		a.rank_base[q] = segments[k].rank_base;
+		a.first_block[q] = n_blocks;
+		n_blocks += (uint32_t)(((uint64_t)segments[k].n_words + kExpandWordsPerBlock - 1) / kExpandWordsPerBlock);
+		a.first_block[q + 1] = n_blocks;
+		RN_REQUIRE(n_blocks <= kExpandStaticBlocks, RN_ERR_CAPACITY,
+		           "rn_masks_expand_static: the segments need more than %u CTAs of 1024 words (limit RN_MASKS_EXPAND_STATIC_MAX_WORDS = %u mask words "
+		           "= %llu ranks, every segment rounded up to 1024 words); use rn_masks_expand",
+		           kExpandStaticBlocks, (unsigned)RN_MASKS_EXPAND_STATIC_MAX_WORDS, (unsigned long long)RN_MASKS_EXPAND_STATIC_MAX_WORDS * 32ull);
+	}
+	if(n_blocks == 0)
+		return RN_OK;
+	RN_CUDA(cudaSetDevice(device));
+	uint32_t *totals = nullptr;
+	int rc = expand_static_scratch(device, &totals);
+	if(rc) return rc;
+	cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+	// nothing in the array has to start at zero: pass 1 writes entries [0, n_blocks), the only ones passes 2 and 3 read
+	expand_count_kernel<<<n_blocks, kExpandThreads, 0, stream>>>(a, totals);
+	expand_scan_kernel<<<1, kExpandThreads, 0, stream>>>(totals, n_blocks, device_count);
+	expand_emit_kernel<<<n_blocks, kExpandThreads, 0, stream>>>(a, totals, device_list, capacity);
+	RN_CUDA(cudaGetLastError());
 	return RN_OK;
 }
