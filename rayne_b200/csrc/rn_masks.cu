@@ -431,8 +431,6 @@ extern "C" int rn_masks_expand_static(int device, const rn_mask_segment *segment
 	RN_REQUIRE((segments || n_segments == 0) && device_list && device_count, RN_ERR_INVALID, "NULL argument");
 	RN_REQUIRE(n_segments <= kExpandMaxSegments, RN_ERR_INVALID, "rn_masks_expand_static takes at most %u segments per call, got %u",
 	           kExpandMaxSegments, n_segments);
-	if(device < 0)
-		RN_CUDA(cudaGetDevice(&device));
 	RN_REQUIRE(device < kStaticMaxDevices, RN_ERR_INVALID, "device %d: rn_masks_expand_static knows devices 0..%d", device, kStaticMaxDevices - 1);
 	ExpandArgs a;
 	memset(&a, 0, sizeof(a));
@@ -456,6 +454,10 @@ extern "C" int rn_masks_expand_static(int device, const rn_mask_segment *segment
 	}
 	if(n_blocks == 0)
 		return RN_OK;
+	// the arguments are checked; from here on a device is needed
+	if(device < 0)
+		RN_CUDA(cudaGetDevice(&device));
+	RN_REQUIRE(device < kStaticMaxDevices, RN_ERR_INVALID, "device %d: rn_masks_expand_static knows devices 0..%d", device, kStaticMaxDevices - 1);
 	RN_CUDA(cudaSetDevice(device));
 	uint32_t *totals = nullptr;
 	int rc = expand_static_scratch(device, &totals);

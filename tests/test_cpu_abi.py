@@ -111,6 +111,31 @@ def test_argument_errors_do_not_need_a_device():
     assert lib.rn_scene_create(C.byref(out), C.byref(desc)) == -1      # tile_nodes not a multiple of 16
 
 
+def test_static_expand_checks_its_limits_before_it_needs_a_device():
+    """rn_masks_expand_static: the segment count and the size of its __device__ scratch array are argument errors,
+    reported before any CUDA call (no compute here: every call below is rejected or has nothing to do)."""
+    limit = capi.MASKS_EXPAND_STATIC_MAX_WORDS
+    assert limit % 1024 == 0 and f"({limit // (1024 * 1024)}u * 1024u * 1024u)" in open(HEADER).read()
+    fake = 0x1000      # never dereferenced: the calls fail before any launch
+    with pytest.raises(capi.RNError) as e:
+        capi.masks_expand_static([(fake, 1, 0)] * 33, fake, 4, fake)
+    assert e.value.status == -1 and "32" in str(e.value)
+    with pytest.raises(capi.RNError) as e:
+        capi.masks_expand_static([(fake, limit + 1, 0)], fake, 4, fake)
+    assert e.value.status == -5 and "RN_MASKS_EXPAND_STATIC_MAX_WORDS" in str(e.value)
+    with pytest.raises(capi.RNError) as e:
+        capi.masks_expand_static([(fake, limit - 1024, 0), (fake, 1, 0), (fake, 1, 0)], fake, 4, fake)   # 1 + 1 word round up to 2 CTAs
+    assert e.value.status == -5
+    with pytest.raises(capi.RNError) as e:
+        capi.masks_expand_static([(0, 5, 0)], fake, 4, fake)              # NULL words
+    assert e.value.status == -1
+    with pytest.raises(capi.RNError) as e:
+        capi.masks_expand_static([(fake, 5, 0)], 0, 4, fake)              # NULL list
+    assert e.value.status == -1
+    capi.masks_expand_static([], fake, 4, fake)                           # nothing to do: no device needed
+    capi.masks_expand_static([(fake, 0, 0)], fake, 4, fake)
+
+
 @pytest.mark.skipif(have_gpu(), reason="only meaningful on a machine without a CUDA device")
 def test_no_cpu_fallback_without_a_device():
     """On a CPU-only box the product path must fail loudly (RN_ERR_CUDA), never compute on the host."""
