@@ -110,6 +110,7 @@ struct SceneView
 	uint32_t inner_cap;        // P: parents kept in shared memory per tile
 	uint32_t warp_smem;        // bytes of shared memory per warp
 	uint32_t n;
+	uint32_t prefetch_spine_rows;   // tile kernel: L2 prefetch of the next tile's sublevel-0 rows (experiment, RN_TILE_PREFETCH_SPINE=1)
 };
 
 struct CullParams
@@ -587,6 +588,19 @@ __device__ __forceinline__ void prefetch_l2(const void *p)
 	asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
+// Old value of *p, *p += 1 - as atom.inc with a bound below all-ones, not atom.add: ptxas turns every atom.add with a
+// uniform address (also one under `if(lane == 0)`, also as inline PTX, also an atom.inc bounded by 0xffffffff) into its
+// warp-aggregated form (vote, one ATOMG, SHFL of the result), and the shuffle waits for the atomic's round trip on the
+// spot.  The tile hand-out needs the value one tile later, so the latency can stay hidden behind the tile
+// (profiles/r02fin2_tile_kernel_ncu.txt: 3 % of the kernel's warp time sat on that shuffle).  The counter counts tiles: it
+// never comes near the bound, where atom.inc would wrap to zero.
+__device__ __forceinline__ uint32_t atomic_inc_relaxed(uint32_t *p)
+{
+	uint32_t old;
+	asm volatile("atom.global.relaxed.gpu.inc.u32 %0, [%1], 0xfffffffe;" : "=r"(old) : "l"(p) : "memory");
+	return old;
+}
+
 // World-transform propagation (+ culling): PERSISTENT warps, one tile per warp at a time.  A tile is a contiguous slot
 // range holding whole compact subtrees, sorted by sublevel (depth inside the subtree) with the inner nodes of every
 // sublevel first.  The warp walks the sublevels in order, 32 nodes per pass: the four input columns of the NEXT pass
@@ -628,7 +642,7 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 	// the tile after this one: claimed now, its descriptor loaded during the first pass of the current tile
 	uint32_t claim = 0;
 	if(lane == 0)
-		claim = atomicAdd(sv.tile_counter, 1u);
+		claim = atomic_inc_relaxed(sv.tile_counter);
 	if(lane < sizeof(TileMeta) / 4)
 		reinterpret_cast<uint32_t *>(&s_meta[warp][0])[lane] = reinterpret_cast<const uint32_t *>(meta_of(tile))[lane];
 	if(lane == 0)
@@ -692,7 +706,7 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 		if(more && lane < sizeof(TileMeta) / 4)
 			mreg = __ldg(reinterpret_cast<const uint32_t *>(meta_of(next_tile)) + lane);
 		if(more && lane == 0)
-			claim = atomicAdd(sv.tile_counter, 1u);
+			claim = atomic_inc_relaxed(sv.tile_counter);
 		bool next_ready = !more;
 		auto park_next = [&]() {
 			if(!next_ready)
@@ -701,6 +715,31 @@ __global__ void __launch_bounds__(kTileThreads, CTAS) tile_kernel(const __grid_c
 					reinterpret_cast<uint32_t *>(&s_meta[warp][cur ^ 1u])[lane] = mreg;
 				__syncwarp();
 				next_ready = true;
+				// The spine nodes stored in the next tile (its sublevel 0): their world TRS and local rows are read with
+				// plain loads at the start of that tile (the cull's sublevel-0 pass), and their world TRS + matrix are what
+				// the unit roots of this tile and the next one read as parents (children precede their parent in the render
+				// list, so a unit's spine parent sits in the unit's own tile or in the one after it).  Both reads sit at the
+				// head of a dependency chain with the load latency exposed (11 % of the kernel's warp time,
+				// profiles/r02fin2_tile_kernel_ncu.txt).  Experiment knob RN_TILE_PREFETCH_SPINE=1: pull them into L2 a tile
+				// (or at least a pass) ahead - measured without effect (profiles/r02ab_*: 0.5198 ms with, 0.5182 ms without;
+				// the latency that is exposed is not the DRAM's), so it is off by default.
+				if(sv.prefetch_spine_rows)
+				{
+					const TileMeta &nm = s_meta[warp][cur ^ 1u];
+					if(lane < nm.lvl_end[0])
+					{
+						const uint32_t ps = nm.start + lane;
+						prefetch_l2(sv.wmat + 4u * (size_t)ps);
+						prefetch_l2(sv.wpos + ps);
+						prefetch_l2(sv.wrot + ps);
+						prefetch_l2(sv.wsyz + ps);
+						if(CULL)
+						{
+							prefetch_l2(sv.c2 + ps);
+							prefetch_l2(sv.c3 + ps);
+						}
+					}
+				}
 			}
 		};
 		VisCount vc = {0u, 0u};
@@ -1301,6 +1340,8 @@ static void free_nodes(rn_scene *s)
 	s->tiles_base = nullptr; s->d_late_tiles = nullptr; s->d_late_cap = 0;
 }
 
+static int tile_env(const char *name, int dflt);
+
 static SceneView make_view(const rn_scene *s)
 {
 	SceneView v;
@@ -1310,6 +1351,8 @@ static SceneView make_view(const rn_scene *s)
 	v.tile_counter = s->super_totals - 1;       // the word in front of the totals (one memset clears both)
 	v.tiles_abs = s->tiles_base; v.tile_list = nullptr; v.n_list = 0; v.tile_head = s->tile_head;
 	v.n_tiles = s->n_tiles; v.inner_cap = s->inner_cap; v.warp_smem = warp_smem_bytes(s->inner_cap); v.n = s->n;
+	static const int prefetch_spine = tile_env("RN_TILE_PREFETCH_SPINE", 0);   // measured: no gain (0.5198 vs 0.5182 ms), stays off
+	v.prefetch_spine_rows = (uint32_t)prefetch_spine;
 	return v;
 }
 
