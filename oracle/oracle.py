@@ -54,13 +54,21 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def render_order(parent: np.ndarray, priority: np.ndarray | None) -> np.ndarray:
+RENDER_ORDER_WALK_LIMIT = 100_000
+
+
+def render_order(parent: np.ndarray, priority: np.ndarray | None, method: str = "auto") -> np.ndarray:
+    """SceneBasic's render-list order.  method "walk": the literal restatement of AddRenderNode's three insert rules
+    (quadratic when priorities are scattered); "fast": the same order derived from those rules with one sort
+    (rn_oracle_render_order_fast; equal to the walk, tests/test_cpu_oracle_golden.py); "auto": the walk up to
+    RENDER_ORDER_WALK_LIMIT nodes, the sort above (the GPU suite's 1 M-node scenes)."""
     parent = np.ascontiguousarray(parent, dtype=np.int32)
     prio = None if priority is None else np.ascontiguousarray(priority, dtype=np.int32)
     order = np.zeros(parent.shape[0], dtype=np.uint32)
-    import sys
-    old = sys.getrecursionlimit()
-    rc = load().rn_oracle_render_order(C.c_uint32(parent.shape[0]), _p(parent), _p(prio), _p(order))
+    if method == "auto":
+        method = "walk" if parent.shape[0] <= RENDER_ORDER_WALK_LIMIT else "fast"
+    fn = load().rn_oracle_render_order if method == "walk" else load().rn_oracle_render_order_fast
+    rc = fn(C.c_uint32(parent.shape[0]), _p(parent), _p(prio), _p(order))
     assert rc == 0
     return order
 

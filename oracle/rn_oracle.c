@@ -210,6 +210,68 @@ int rn_oracle_render_order(uint32_t n, const int32_t *parent, const int32_t *pri
 	return r == n ? 0 : -1;
 }
 
+/* The same order without walking the list (the walk of rule 3 makes rn_oracle_render_order quadratic when priorities are
+ * scattered: 11 minutes for 1 M nodes).  Derived from the three rules above, not from other code:
+ *   - every rule keeps the list sorted by priority (rule 1 inserts a value <= the head's at the head, rule 2 a value >= the
+ *     tail's at the tail, rule 3 behind the last element whose priority is <= the new one), so head = smallest priority seen;
+ *   - rule 1 (list empty, or smallest priority so far >= p) puts the node in FRONT of the nodes of its own priority,
+ *     rules 2 and 3 put it BEHIND them.
+ * Hence: nodes ascending by priority; inside one priority first the rule-1 nodes in reverse call order, then the others in
+ * call order.  Call order = AddNode's: children (in child order) before their parent, roots in creation order.
+ * tests/test_cpu_oracle_golden.py checks it against the literal walk on random forests; oracle.py uses it for large inputs. */
+typedef struct { int32_t prio; uint32_t side; int64_t seq; uint32_t node; } order_key;
+static int order_key_cmp(const void *a, const void *b)
+{
+	const order_key *x = a, *y = b;
+	if(x->prio != y->prio) return x->prio < y->prio ? -1 : 1;
+	if(x->side != y->side) return x->side < y->side ? -1 : 1;
+	if(x->seq != y->seq) return x->seq < y->seq ? -1 : 1;
+	return 0;
+}
+int rn_oracle_render_order_fast(uint32_t n, const int32_t *parent, const int32_t *prio, uint32_t *order)
+{
+	uint32_t *ofs = calloc(n + 2, 4), *child = malloc(4 * (n + 1)), *fill = malloc(4 * (n + 1));
+	uint32_t *stack = malloc(4 * (n + 1)), *next_child = malloc(4 * (n + 1));
+	order_key *keys = malloc(sizeof(order_key) * (n + 1));
+	for(uint32_t i = 0; i < n; i++) if(parent[i] >= 0) ofs[parent[i] + 1]++;
+	for(uint32_t i = 0; i < n; i++) ofs[i + 1] += ofs[i];
+	memcpy(fill, ofs, 4 * (n + 1));
+	for(uint32_t i = 0; i < n; i++) if(parent[i] >= 0) child[fill[parent[i]]++] = i;
+	memcpy(next_child, ofs, 4 * (n + 1));
+	int64_t calls = 0;
+	int have = 0;
+	int32_t smallest = 0;
+	for(uint32_t root = 0; root < n; root++)
+	{
+		if(parent[root] >= 0) continue;
+		uint32_t sp = 0;
+		stack[sp++] = root;
+		while(sp)
+		{
+			const uint32_t u = stack[sp - 1];
+			if(next_child[u] < ofs[u + 1]) { stack[sp++] = child[next_child[u]++]; continue; }   /* UpdateSceneInfo: children first */
+			sp--;
+			const int32_t p = prio ? prio[u] : 0;
+			const int front = !have || smallest >= p;                                               /* rule 1 */
+			keys[calls].prio = p;
+			keys[calls].side = front ? 0u : 1u;
+			keys[calls].seq = front ? -calls : calls;
+			keys[calls].node = u;
+			if(!have || p < smallest) smallest = p;
+			have = 1;
+			calls++;
+		}
+	}
+	int rc = calls == (int64_t)n ? 0 : -1;
+	if(rc == 0)
+	{
+		qsort(keys, n, sizeof(order_key), order_key_cmp);
+		for(uint32_t r = 0; r < n; r++) order[r] = keys[r].node;
+	}
+	free(ofs); free(child); free(fill); free(stack); free(next_child); free(keys);
+	return rc;
+}
+
 /* ---- SceneNode world transforms ----------------------------------------------------------------------------- */
 
 /* SceneNode::UpdateInternalData (Source/Scene/RNSceneNode.cpp:501-524) and UpdateInternalTransformData (:526-546).

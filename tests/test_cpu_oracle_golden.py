@@ -40,6 +40,29 @@ def test_oracle_scene_matches_golden(name):
         assert same_list_mod_ties(o["lists"][c], g[f"ref_list{c}"], scene.priority, ftb), f"camera {c}"
 
 
+def test_oracle_render_order_sort_equals_the_literal_walk():
+    """oracle.render_order has two forms: the literal walk of AddRenderNode's three insert rules (pinned by the golden
+    `ref_order` arrays above) and, for the 1 M-node scenes of the GPU suite, the same order derived from those rules with
+    one sort (the walk is quadratic when priorities are scattered: 11 minutes for 1 M nodes).  They must agree on every
+    input: random forests with no, few, many distinct and negative priorities, the golden scenes, a 60 k-node scene."""
+    rng = np.random.default_rng(1)
+    for trial in range(240):
+        n = int(rng.integers(1, 300))
+        parent = np.full(n, -1, np.int32)
+        for i in range(1, n):
+            if rng.random() < 0.85:
+                parent[i] = rng.integers(0, i)
+        prio = (None, rng.integers(-2, 3, n).astype(np.int32), rng.integers(-10 ** 6, 10 ** 6, n).astype(np.int32),
+                rng.choice(np.int32([0, 0, 0, 0, 1000000, 1]), n).astype(np.int32))[trial % 4]
+        assert np.array_equal(oracle.render_order(parent, prio, "walk"), oracle.render_order(parent, prio, "fast")), trial
+    for name in SCENE_FIXTURES:
+        scene, _, g = load_golden_scene(name)
+        assert np.array_equal(oracle.render_order(scene.parent, scene.priority, "fast"), g["ref_order"]), name
+    big = sg.make_scene(n_trees=3, branching=4, depth=8, seed=12345, priorities=True, transparent_frac=0.05)
+    assert np.array_equal(oracle.render_order(big.parent, big.priority, "walk"), oracle.render_order(big.parent, big.priority, "fast"))
+    assert oracle.RENDER_ORDER_WALK_LIMIT >= 65535      # the golden-size and test-size scenes below it keep the literal walk
+
+
 @pytest.mark.parametrize("name", SCENE_FIXTURES)
 def test_oracle_instance_matrices_match_golden(name):
     """Camera view / projection * view and the per-drawable products view * world, projView * world, bit-exact
